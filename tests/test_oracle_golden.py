@@ -1,0 +1,149 @@
+"""CPU: pin oracle/mr_oracle.c against the fixtures recorded from the unmodified reference library
+(tests/golden/make_golden.py).  Order-sensitive wherever the reference's in-core order is defined
+(first-appearance keys, arrival-order values, stable sort)."""
+import struct
+
+import numpy as np
+import pytest
+
+import mrhelpers as H
+from gpu_mapreduce_b200 import workloads as W
+
+
+def test_hashlittle_kat(golden, oracle):
+    for iv, hexkey, h in golden.manifest["hash"]:
+        assert oracle.hashlittle(bytes.fromhex(hexkey), iv) == h, (iv, hexkey)
+
+
+def test_hashlittle_survey_b1(oracle):
+    # SURVEY.md appendix B.1 (captured from src/hash.cpp during the survey)
+    assert oracle.hashlittle(b"", 0) == 0xDEADBEEF
+    assert oracle.hashlittle(b"abc", 8) == 0xEDF882B2
+    assert oracle.hashlittle(b"The quick brown fox jumps", 0) == 0x9D279883
+    assert oracle.hashlittle(struct.pack("<QQ", 3, 5), 0) == 0x08968719
+    assert oracle.hashlittle(b"hello world!!", 8) % 8 == 2
+
+
+@pytest.mark.parametrize("al", [4, 8])
+def test_kv_kmv_page_images_b2(golden, oracle, al):
+    kv = golden["pages_b2.in"]
+    assert oracle.kv_pages(kv, 64 << 20, al, al) == golden[f"pages_b2.kv.a{al}"]
+    kmv = oracle.convert(kv)
+    assert oracle.kmv_pages(kmv, 64 << 20, al, al) == golden[f"pages_b2.kmv.a{al}"]
+
+
+def test_reduce_sum_page_image_b2(golden, oracle):
+    kv = golden["pages_b2.in"]
+    out = oracle.reduce(oracle.convert(kv), "sum")
+    assert oracle.kv_pages(out, 64 << 20) == golden["pages_b2.reduce_sum"]
+
+
+def test_kv_multipage_greedy_fill(golden, oracle):
+    got = H.pages_decode(oracle.kv_pages(golden["pages_multi.in"], 32768))
+    ref = H.pages_decode(golden["pages_multi.kv"])
+    assert len(ref) > 2
+    assert [(n, len(b)) for n, b in got] == [(n, len(b)) for n, b in ref]
+    # the reference never writes padding bytes and reuses its page buffer, so compare decoded records
+    for (n, pg), (_, pr) in zip(got, ref):
+        assert H.kv_page_records(pg, n) == H.kv_page_records(pr, n)
+
+
+def test_convert_order_and_values(golden, oracle):
+    kv = golden["convert.in"]
+    assert oracle.convert(kv) == golden["convert.kmv"]
+    assert oracle.kmv_pages(oracle.convert(kv), 64 << 20) == golden["convert.kmvpages"]
+
+
+@pytest.mark.parametrize("cb", ["count", "sum", "cull"])
+def test_reduce_callbacks(golden, oracle, cb):
+    kmv = oracle.convert(golden["convert.in"])
+    assert oracle.reduce(kmv, cb) == golden[f"convert.reduce_{cb}"]
+
+
+def test_intcount_pipeline(golden, oracle):
+    m = golden.manifest["intcount"]
+    keys = W.intcount_keys_np(0, m["n"], ndistinct=m["ndistinct"])
+    assert keys.tobytes() == golden["intcount.in"]
+    kv = oracle.intcount_map(keys)
+    out = oracle.sort_keys(oracle.reduce(oracle.convert(kv), "count"), 1)
+    assert out == golden["intcount.out"]
+    recs = H.kv_decode(out)
+    assert sum(struct.unpack("<i", v)[0] for _, v in recs) == m["n"]
+
+
+def test_extended_kmv_count(golden, oracle):
+    # the reference walks key 7 as a multi-block KMV; totals must agree
+    got = H.canon_kv(H.kv_decode(oracle.reduce(oracle.convert(golden["extended.in"]), "count")))
+    ref = H.canon_kv(H.kv_decode(golden["extended.count"]))
+    assert got == ref
+    nhot = sum(1 for k, _ in H.kv_decode(golden["extended.in"]) if k == struct.pack("<i", 7))
+    assert nhot > 8191  # more values than one 32 KiB block holds -> the reference used the block protocol
+    assert dict(ref)[struct.pack("<i", 7)] == struct.pack("<i", nhot)
+
+
+def test_wordfreq(golden, oracle):
+    texts = [golden[f"wordfreq.in{i}"] for i in range(3)]
+    recs = []
+    for t in texts:
+        recs += H.kv_decode(oracle.tokenize(t))
+    assert H.kv_encode(recs) == golden["wordfreq.mapout"]
+    final = oracle.reduce(oracle.convert(H.kv_encode(recs)), "sum")
+    assert final == golden["wordfreq.final"]
+    assert (b"ignored\0", struct.pack("<i", 1)) not in H.kv_decode(final)
+
+
+def test_invindex(golden, oracle):
+    recs = []
+    for i in range(4):
+        recs += H.kv_decode(oracle.href(golden[f"invindex.in{i}"], f"part-{i:05d}"))
+    assert H.kv_encode(recs) == golden["invindex.mapout"]
+    assert oracle.convert(H.kv_encode(recs)) == golden["invindex.kmv"]
+
+
+def test_href_survey_b6(oracle):
+    # SURVEY.md appendix B.6 table
+    def keys(frag):
+        return [k for k, _ in H.kv_decode(oracle.href(frag, "part-00000"))]
+
+    assert keys(b'<a href="http://x/1">t</a>') == [b"http://x/1"]
+    assert keys(b'<a  href = "u2">') == [b"u2"]
+    assert keys(b'<ab href="u3">') == []
+    assert keys(b'<<a href="u6">') == []
+    assert keys(b'< a href="u7">') == [b"u7"]
+    assert keys(b'<a class="c" href="u8">') == []
+    assert keys(b'<a href="">empty <a href="u11">') == [b"", b"u11"]
+    assert keys(b'<a\thref="u14">') == []
+    assert keys(b'<a href="u16"><a href="u17">') == [b"u16", b"u17"]
+
+
+def test_rmat_and_degree(golden, oracle):
+    for ci, case in enumerate(golden.manifest["rmat"]):
+        N, ef, a, b, c, d, fr, seed, P, dup = case["args"]
+        kv, niter = oracle.rmat(N, ef, a, b, c, d, fr, seed, P)
+        assert niter == case["iterations"]
+        ref_edges = H.kv_decode(golden[f"rmat{ci}.edges"])
+        assert len(ref_edges) == (1 << N) * ef
+        assert H.canon_kv(H.kv_decode(kv)) == H.canon_kv(ref_edges)
+        # degree: map(edge_to_vertices) + collate + count on the reference's own edge order
+        verts = oracle.edge_to_vertices(golden[f"rmat{ci}.edges"], both=(dup != 1))
+        deg = oracle.reduce(oracle.convert(verts), "count")
+        assert deg == golden[f"rmat{ci}.degree"]
+
+
+def test_drand48_matches_survey_b4(oracle):
+    st = H.ctypes.c_uint64(oracle.lib.orc_srand48(12345))
+    v = [oracle.lib.orc_drand48(H.ctypes.byref(st)) for _ in range(3)]
+    # glibc: srand48(12345); drand48() x3
+    x = (12345 << 16) | 0x330E
+    exp = []
+    for _ in range(3):
+        x = (0x5DEECE66D * x + 0xB) & ((1 << 48) - 1)
+        exp.append(x / float(1 << 48))
+    assert v == exp
+
+
+@pytest.mark.parametrize("flag", [1, 2, 3, 4, 5, 6])
+def test_sort_keys_flags(golden, oracle, flag):
+    kv = golden[f"sort{flag}.in"]
+    assert oracle.sort_keys(kv, flag) == golden[f"sort{flag}.outp"]
+    assert oracle.sort_keys(kv, -flag) == golden[f"sort{flag}.outm"]
