@@ -1,0 +1,171 @@
+// Shared helpers for the sm_100a kernels: error plumbing, the stream-ordered HBM pool, vector
+// load/store wrappers and record-layout arithmetic (KV: src/keyvalue.cpp:345-352, KMV:
+// src/keymultivalue.cpp:830-838 of the reference).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+
+namespace mrgpu {
+
+constexpr int kSMs = 148;  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+struct Error {
+  int code;
+  std::string msg;
+};
+
+#define MR_CUDA(expr)                                                                          \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess)                                                                     \
+      throw ::mrgpu::Error{-2, std::string(#expr " failed: ") + cudaGetErrorString(_e)};       \
+  } while (0)
+
+#define MR_FAIL(code, text) throw ::mrgpu::Error{(code), std::string(text)}
+
+// ---------------------------------------------------------------------------------------------
+// Stream-ordered HBM pool.  The reference keeps a tagged pool of `memsize` pages and frees unused
+// ones after every operation (src/mapreduce.cpp:3318-3517); here HBM is the page pool: allocations
+// come from the device's default cudaMallocAsync pool with an unlimited release threshold, so after
+// warm-up an operation's KV/KMV/scratch buffers are recycled without touching the driver.
+struct Pool {
+  cudaStream_t stream = nullptr;
+  int device = 0;
+  uint64_t live = 0, hiwater = 0;  // the reference's msize / msizemax (src/mapreduce.h:54)
+
+  void init(int dev, cudaStream_t s)
+  {
+    device = dev;
+    stream = s;
+    cudaMemPool_t mp;
+    MR_CUDA(cudaDeviceGetDefaultMemPool(&mp, dev));
+    uint64_t thresh = UINT64_MAX;
+    MR_CUDA(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &thresh));
+  }
+  void *alloc(uint64_t bytes)
+  {
+    void *p = nullptr;
+    if (bytes == 0) bytes = 256;
+    MR_CUDA(cudaMallocAsync(&p, bytes, stream));
+    live += bytes;
+    if (live > hiwater) hiwater = live;
+    return p;
+  }
+  void free(void *p, uint64_t bytes)
+  {
+    if (!p) return;
+    if (bytes == 0) bytes = 256;
+    cudaFreeAsync(p, stream);
+    live -= bytes;
+  }
+};
+
+// RAII scratch buffer on the pool
+template <typename T>
+struct Buf {
+  Pool *pool = nullptr;
+  T *p = nullptr;
+  uint64_t n = 0;
+  Buf() {}
+  Buf(Pool &pl, uint64_t count) { alloc(pl, count); }
+  Buf(const Buf &) = delete;
+  Buf &operator=(const Buf &) = delete;
+  Buf(Buf &&o) noexcept { *this = static_cast<Buf &&>(o); }
+  Buf &operator=(Buf &&o) noexcept
+  {
+    if (this != &o) {
+      release();
+      pool = o.pool;
+      p = o.p;
+      n = o.n;
+      o.p = nullptr;
+      o.n = 0;
+    }
+    return *this;
+  }
+  void alloc(Pool &pl, uint64_t count)
+  {
+    release();
+    pool = &pl;
+    n = count;
+    p = (T *) pl.alloc(count * sizeof(T));
+  }
+  void release()
+  {
+    if (p && pool) pool->free(p, n * sizeof(T));
+    p = nullptr;
+    n = 0;
+  }
+  T *detach()
+  {
+    T *r = p;
+    p = nullptr;
+    return r;
+  }
+  ~Buf() { release(); }
+};
+
+// ---------------------------------------------------------------------------------------------
+// record layout
+
+struct Align {
+  int k = 4, v = 4, t = 4;  // kalign, valign, talign = max(k, v, sizeof(int)) src/mapreduce.cpp:3333-3335
+};
+
+__host__ __device__ inline uint64_t round_up(uint64_t x, uint32_t a) { return (x + a - 1) & ~(uint64_t) (a - 1); }
+
+// KV: int keybytes | int valuebytes | pad->k | key | pad->v | value | pad->t
+__host__ __device__ inline uint32_t kv_key_off(Align al) { return (uint32_t) round_up(8, al.k); }
+__host__ __device__ inline uint32_t kv_val_off(Align al, uint32_t kb) { return (uint32_t) round_up(kv_key_off(al) + kb, al.v); }
+__host__ __device__ inline uint32_t kv_rec_size(Align al, uint32_t kb, uint32_t vb)
+{
+  return (uint32_t) round_up(kv_val_off(al, kb) + vb, al.t);
+}
+
+// KMV: int nvalue | int keybytes | int mvbytes | int sizes[nvalue] | pad->k | key | pad->v | values | pad->t
+__host__ __device__ inline uint64_t kmv_key_off(Align al, uint64_t nv) { return round_up(12 + 4 * nv, al.k); }
+__host__ __device__ inline uint64_t kmv_val_off(Align al, uint64_t nv, uint32_t kb) { return round_up(kmv_key_off(al, nv) + kb, al.v); }
+__host__ __device__ inline uint64_t kmv_rec_size(Align al, uint64_t nv, uint32_t kb, uint64_t mvb)
+{
+  return round_up(kmv_val_off(al, nv, kb) + mvb, al.t);
+}
+
+// ---------------------------------------------------------------------------------------------
+// device helpers
+
+__device__ __forceinline__ unsigned lanemask_lt()
+{
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+// streaming 128-bit accesses: data that is read or written exactly once should not displace L1 lines
+__device__ __forceinline__ int4 ld_stream(const int4 *p)
+{
+  int4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream(int4 *p, int4 v)
+{
+  asm volatile("st.global.L1::no_allocate.v4.s32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+inline unsigned grid_for(uint64_t work_items, unsigned per_block, unsigned max_waves = 32)
+{
+  uint64_t b = (work_items + per_block - 1) / per_block;
+  uint64_t cap = (uint64_t) kSMs * max_waves;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (unsigned) b;
+}
+
+}  // namespace mrgpu

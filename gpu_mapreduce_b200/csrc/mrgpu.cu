@@ -1,0 +1,364 @@
+// C-ABI entry points (include/mrgpu.h) and the host orchestration of the sm_100a kernels.
+// One translation unit; kernels live in the .cuh files next to it.
+//
+// Reference map (paths relative to the reference tree):
+//   map emit / KV packing      src/keyvalue.cpp:343-428      -> ops_map.cuh
+//   convert (group by key)     src/keymultivalue.cpp:486-1209 -> ops_convert.cuh (radix.cuh, scan.cuh)
+//   reduce                     src/mapreduce.cpp:1769-1867   -> ops_reduce.cuh
+//   sort_keys                  src/mapreduce.cpp:2102-2633   -> ops_sort.cuh
+//   aggregate + Irregular      src/mapreduce.cpp:385-563, src/irregular.cpp:95-301 -> ops_aggregate.cuh
+#include "../../include/mrgpu.h"
+
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <exception>
+#include <vector>
+
+#include "common.cuh"
+#include "hash.cuh"
+#include "radix.cuh"
+#include "scan.cuh"
+#include "store.cuh"
+
+using namespace mrgpu;
+
+static thread_local std::string g_create_error;
+
+struct mrgpu_mr {
+  Pool pool;
+  int device = 0;
+  int64_t memsize = 64, keyalign = 4, valuealign = 4, verbosity = 0, timer = 0, all2all = 1, mapstyle = 0, minpage = 0,
+          maxpage = 0, freepage = 1, outofcore = 0, zeropage = 0;  // defaults(): src/mapreduce.cpp:196-262
+  Align al;
+  bool frozen = false;
+  uint64_t pagesize = 64ull << 20;
+  DevKV *kv = nullptr;
+  DevKMV *kmv = nullptr;
+  Staging stg;
+  int stg_addflag = 0;
+  std::string err;
+  int rank = 0, nranks = 1;
+  void *comm = nullptr;            // ncclComm_t
+  unsigned long long *d_small = nullptr;  // [64] device scalars (totals, flags)
+  unsigned long long *h_small = nullptr;  // pinned mirror
+};
+
+#define API_BEGIN(mr)                     \
+  if (!(mr)) return MRGPU_EINVAL;         \
+  try {                                   \
+    MR_CUDA(cudaSetDevice((mr)->device));
+
+#define API_END(mr)                       \
+  }                                       \
+  catch (const Error &e)                  \
+  {                                       \
+    (mr)->err = e.msg;                    \
+    return e.code;                        \
+  }                                       \
+  catch (const std::exception &e)         \
+  {                                       \
+    (mr)->err = e.what();                 \
+    return MRGPU_EINVAL;                  \
+  }                                       \
+  return MRGPU_OK;
+
+// freeze alignment + page size at first use, like MapReduce::allocate() src/mapreduce.cpp:3318-3357
+static void freeze(mrgpu_mr *mr)
+{
+  if (mr->frozen) return;
+  auto pow2 = [](int64_t a) { return a >= 1 && (a & (a - 1)) == 0; };
+  if (!pow2(mr->keyalign) || !pow2(mr->valuealign)) MR_FAIL(MRGPU_EINVAL, "Invalid alignment setting");
+  if (mr->memsize == 0) MR_FAIL(MRGPU_EINVAL, "Invalid memsize setting");
+  if (mr->minpage < 0) MR_FAIL(MRGPU_EINVAL, "Invalid minpage setting");
+  if (mr->maxpage && mr->maxpage < mr->minpage) MR_FAIL(MRGPU_EINVAL, "Invalid maxpage setting");
+  mr->al.k = (int) mr->keyalign;
+  mr->al.v = (int) mr->valuealign;
+  mr->al.t = std::max(std::max(mr->al.k, mr->al.v), 4);
+  mr->pagesize = mr->memsize > 0 ? (uint64_t) mr->memsize << 20 : (uint64_t) (-mr->memsize);
+  if (mr->pagesize < 512) MR_FAIL(MRGPU_EINVAL, "Page size smaller than ALIGNFILE");
+  mr->frozen = true;
+}
+
+static void sync(mrgpu_mr *mr) { MR_CUDA(cudaStreamSynchronize(mr->pool.stream)); }
+
+// read k device scalars d_small[0..k) to the host
+static void fetch_small(mrgpu_mr *mr, int k)
+{
+  MR_CUDA(cudaMemcpyAsync(mr->h_small, mr->d_small, 8 * k, cudaMemcpyDeviceToHost, mr->pool.stream));
+  sync(mr);
+}
+
+static bool is_device_ptr(const void *p)
+{
+  cudaPointerAttributes at;
+  cudaError_t e = cudaPointerGetAttributes(&at, p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+// global sum over ranks of a per-rank count (the MPI_Allreduce at the end of every reference op)
+static uint64_t allreduce_sum(mrgpu_mr *mr, uint64_t v);
+
+#include "ops_map.cuh"
+#include "ops_convert.cuh"
+#include "ops_text.cuh"
+#include "ops_reduce.cuh"
+#include "ops_sort.cuh"
+#include "ops_aggregate.cuh"
+#include "ops_pages.cuh"
+
+// ================================================================================================
+// lifetime, settings
+
+extern "C" int mrgpu_create(int device, void *stream, mrgpu_mr **out)
+{
+  if (!out) return MRGPU_EINVAL;
+  *out = nullptr;
+  mrgpu_mr *mr = nullptr;
+  try {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+      cudaGetLastError();
+      MR_FAIL(MRGPU_ECUDA, "no CUDA device: this library has no CPU path");
+    }
+    if (device < 0 || device >= ndev) MR_FAIL(MRGPU_EINVAL, "invalid device ordinal");
+    MR_CUDA(cudaSetDevice(device));
+    mr = new mrgpu_mr();
+    mr->device = device;
+    mr->pool.init(device, (cudaStream_t) stream);
+    MR_CUDA(cudaMalloc(&mr->d_small, 64 * 8));
+    MR_CUDA(cudaMallocHost(&mr->h_small, 64 * 8));
+    *out = mr;
+  } catch (const Error &e) {
+    g_create_error = e.msg;
+    delete mr;
+    return e.code;
+  }
+  return MRGPU_OK;
+}
+
+extern "C" int mrgpu_destroy(mrgpu_mr *mr)
+{
+  if (!mr) return MRGPU_EINVAL;
+  cudaSetDevice(mr->device);
+  delete mr->kv;
+  delete mr->kmv;
+  cudaStreamSynchronize(mr->pool.stream);
+  if (mr->comm) comm_destroy(mr);
+  cudaFree(mr->d_small);
+  cudaFreeHost(mr->h_small);
+  delete mr;
+  return MRGPU_OK;
+}
+
+extern "C" const char *mrgpu_last_error(const mrgpu_mr *mr) { return mr ? mr->err.c_str() : g_create_error.c_str(); }
+
+static int64_t *setting(mrgpu_mr *mr, const char *name)
+{
+  struct {
+    const char *n;
+    int64_t *p;
+  } tab[] = {{"memsize", &mr->memsize},     {"keyalign", &mr->keyalign},   {"valuealign", &mr->valuealign},
+             {"verbosity", &mr->verbosity}, {"timer", &mr->timer},         {"all2all", &mr->all2all},
+             {"mapstyle", &mr->mapstyle},   {"minpage", &mr->minpage},     {"maxpage", &mr->maxpage},
+             {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage}};
+  for (auto &t : tab)
+    if (!strcmp(t.n, name)) return t.p;
+  return nullptr;
+}
+
+extern "C" int mrgpu_set(mrgpu_mr *mr, const char *name, int64_t value)
+{
+  API_BEGIN(mr)
+  int64_t *p = setting(mr, name);
+  if (!p) MR_FAIL(MRGPU_EINVAL, std::string("unknown setting ") + name);
+  if (mr->frozen && (!strcmp(name, "keyalign") || !strcmp(name, "valuealign") || !strcmp(name, "memsize")) && *p != value)
+    MR_FAIL(MRGPU_EINVAL, "memsize/keyalign/valuealign are frozen after first use (src/mapreduce.cpp:3318)");
+  *p = value;
+  API_END(mr)
+}
+
+extern "C" int mrgpu_get(const mrgpu_mr *mr, const char *name, int64_t *value)
+{
+  if (!mr || !value) return MRGPU_EINVAL;
+  int64_t *p = setting(const_cast<mrgpu_mr *>(mr), name);
+  if (!p) return MRGPU_EINVAL;
+  *value = *p;
+  return MRGPU_OK;
+}
+
+extern "C" int mrgpu_comm_rank(const mrgpu_mr *mr, int *rank, int *nranks)
+{
+  if (!mr) return MRGPU_EINVAL;
+  if (rank) *rank = mr->rank;
+  if (nranks) *nranks = mr->nranks;
+  return MRGPU_OK;
+}
+
+// ================================================================================================
+// host staging: KeyValue::add from a host callback
+
+extern "C" int mrgpu_kv_open(mrgpu_mr *mr, int addflag)
+{
+  API_BEGIN(mr)
+  freeze(mr);
+  if (mr->stg.open) MR_FAIL(MRGPU_EINVAL, "KeyValue already open");
+  mr->stg.clear();
+  mr->stg.open = true;
+  mr->stg_addflag = addflag;
+  API_END(mr)
+}
+
+extern "C" int mrgpu_kv_add(mrgpu_mr *mr, uint64_t n, const void *keys, const int32_t *keybytes, int kfix, const void *values,
+                            const int32_t *valuebytes, int vfix)
+{
+  API_BEGIN(mr)
+  if (!mr->stg.open) MR_FAIL(MRGPU_EINVAL, "mrgpu_kv_add outside mrgpu_kv_open/close");
+  Staging &s = mr->stg;
+  const uint8_t *kp = (const uint8_t *) keys, *vp = (const uint8_t *) values;
+  const Align al = mr->al;
+  for (uint64_t i = 0; i < n; i++) {
+    int64_t kb = keybytes ? keybytes[i] : kfix, vb = valuebytes ? valuebytes[i] : vfix;
+    if (kb < 0 || vb < 0) MR_FAIL(MRGPU_EINVAL, "negative key/value length");
+    uint64_t rs = round_up(round_up(round_up(8, al.k) + kb, al.v) + vb, al.t);
+    if (rs > 0x7FFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "Single key/value pair exceeds int size");
+    if (rs > mr->pagesize) MR_FAIL(MRGPU_ELIMIT, "Single key/value pair exceeds page size");
+    if (s.nkv == 0) {
+      s.kb = (uint32_t) kb;
+      s.vb = (uint32_t) vb;
+    } else if (s.kb != (uint32_t) kb || s.vb != (uint32_t) vb) s.uniform = false;
+    uint64_t base = s.data.size();
+    s.offs.push_back(base);
+    s.data.resize(base + rs, 0);
+    uint8_t *r = &s.data[base];
+    int32_t k32 = (int32_t) kb, v32 = (int32_t) vb;
+    memcpy(r, &k32, 4);
+    memcpy(r + 4, &v32, 4);
+    if (kb) memcpy(r + kv_key_off(al), kp, kb);
+    if (vb) memcpy(r + kv_val_off(al, (uint32_t) kb), vp, vb);
+    kp += kb;
+    vp += vb;
+    s.nkv++;
+    s.ksize += kb;
+    s.vsize += vb;
+  }
+  API_END(mr)
+}
+
+extern "C" int mrgpu_kv_close(mrgpu_mr *mr, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!mr->stg.open) MR_FAIL(MRGPU_EINVAL, "KeyValue is not open");
+  Staging &s = mr->stg;
+  s.open = false;
+  kv_begin_map(mr, mr->stg_addflag);
+  DevKV *kv = mr->kv;
+  if (s.nkv) {
+    bool fits_uniform = s.uniform && (kv->nkv == 0 || (kv->uniform && kv->kb == s.kb && kv->vb == s.vb));
+    if (!fits_uniform) kv_make_general(mr, kv);
+    kv->reserve_bytes(kv->nbytes + s.data.size());
+    MR_CUDA(cudaMemcpyAsync(kv->data + kv->nbytes, s.data.data(), s.data.size(), cudaMemcpyHostToDevice, mr->pool.stream));
+    if (fits_uniform) {
+      kv->uniform = true;
+      kv->kb = s.kb;
+      kv->vb = s.vb;
+      kv->recsize = kv_rec_size(mr->al, s.kb, s.vb);
+    } else {
+      kv->reserve_offs(kv->nkv + s.nkv + 1);
+      std::vector<uint64_t> o(s.nkv + 1);
+      for (uint64_t i = 0; i < s.nkv; i++) o[i] = kv->nbytes + s.offs[i];
+      o[s.nkv] = kv->nbytes + s.data.size();
+      MR_CUDA(cudaMemcpyAsync(kv->offs + kv->nkv, o.data(), (s.nkv + 1) * 8, cudaMemcpyHostToDevice, mr->pool.stream));
+      sync(mr);  // o goes out of scope
+    }
+    kv->nbytes += s.data.size();
+    kv->nkv += s.nkv;
+    kv->ksize += s.ksize;
+    kv->vsize += s.vsize;
+    kv->h_offs_valid = false;
+  }
+  sync(mr);
+  s.clear();
+  if (nkv) *nkv = allreduce_sum(mr, kv->nkv);
+  API_END(mr)
+}
+
+// ================================================================================================
+// stand-alone kernels
+
+extern "C" int mrgpu_sort_pairs(int device, void *stream, void *keys, void *payload, uint64_t n, int key_bytes, int payload_bytes)
+{
+  try {
+    MR_CUDA(cudaSetDevice(device));
+    if ((key_bytes != 4 && key_bytes != 8) || (payload_bytes != 0 && payload_bytes != 4 && payload_bytes != 8)) return MRGPU_EINVAL;
+    if (n >= (1ull << 32)) return MRGPU_ELIMIT;
+    Pool pool;
+    pool.init(device, (cudaStream_t) stream);
+    Buf<uint8_t> k1(pool, n * key_bytes), p1(pool, n * (payload_bytes ? payload_bytes : 1));
+    Buf<unsigned long long> hist(pool, 8 * RADIX);
+    int cur = 0;
+#define SORT_CASE(K, P, HASP) \
+  cur = radix_sort_pairs<K, P, HASP>(pool, (K *) keys, (K *) k1.p, (P *) payload, (P *) p1.p, n, 0xFF, false, hist.p)
+    if (key_bytes == 4 && payload_bytes == 0) SORT_CASE(uint32_t, uint32_t, false);
+    else if (key_bytes == 4 && payload_bytes == 4) SORT_CASE(uint32_t, uint32_t, true);
+    else if (key_bytes == 4 && payload_bytes == 8) SORT_CASE(uint32_t, uint64_t, true);
+    else if (key_bytes == 8 && payload_bytes == 0) SORT_CASE(uint64_t, uint32_t, false);
+    else if (key_bytes == 8 && payload_bytes == 4) SORT_CASE(uint64_t, uint32_t, true);
+    else SORT_CASE(uint64_t, uint64_t, true);
+#undef SORT_CASE
+    if (cur) {
+      MR_CUDA(cudaMemcpyAsync(keys, k1.p, n * key_bytes, cudaMemcpyDeviceToDevice, pool.stream));
+      if (payload_bytes) MR_CUDA(cudaMemcpyAsync(payload, p1.p, n * payload_bytes, cudaMemcpyDeviceToDevice, pool.stream));
+    }
+    k1.release();
+    p1.release();
+    hist.release();
+    MR_CUDA(cudaStreamSynchronize(pool.stream));
+  } catch (const Error &e) {
+    g_create_error = e.msg;
+    return e.code;
+  }
+  return MRGPU_OK;
+}
+
+__global__ void hashlittle_kernel(const uint8_t *keys, const uint64_t *offs, uint64_t n, uint32_t initval, uint32_t *out)
+{
+  uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = hashlittle(keys + offs[i], (uint32_t) (offs[i + 1] - offs[i]), initval);
+}
+
+extern "C" int mrgpu_hashlittle(int device, const void *keys, const uint64_t *offsets, uint64_t n, uint32_t initval, uint32_t *out)
+{
+  try {
+    MR_CUDA(cudaSetDevice(device));
+    if (n == 0) return MRGPU_OK;
+    std::vector<uint64_t> ho(n + 1);
+    bool dev_in = is_device_ptr(keys);
+    uint8_t *dk = nullptr;
+    uint64_t *dofs = nullptr;
+    uint32_t *dout = nullptr;
+    uint64_t nbytes;
+    if (dev_in) MR_CUDA(cudaMemcpy(&nbytes, offsets + n, 8, cudaMemcpyDeviceToHost));
+    else nbytes = offsets[n];
+    MR_CUDA(cudaMalloc(&dk, nbytes ? nbytes : 1));
+    MR_CUDA(cudaMalloc(&dofs, (n + 1) * 8));
+    MR_CUDA(cudaMalloc(&dout, n * 4));
+    MR_CUDA(cudaMemcpy(dk, keys, nbytes, cudaMemcpyDefault));
+    MR_CUDA(cudaMemcpy(dofs, offsets, (n + 1) * 8, cudaMemcpyDefault));
+    hashlittle_kernel<<<(unsigned) ((n + 255) / 256), 256>>>(dk, dofs, n, initval, dout);
+    MR_CUDA(cudaGetLastError());
+    MR_CUDA(cudaMemcpy(out, dout, n * 4, cudaMemcpyDefault));
+    cudaFree(dk);
+    cudaFree(dofs);
+    cudaFree(dout);
+  } catch (const Error &e) {
+    g_create_error = e.msg;
+    return e.code;
+  }
+  return MRGPU_OK;
+}

@@ -1,0 +1,361 @@
+// aggregate(): hash-partition the KeyValue and exchange partitions between ranks (one rank = one GPU).
+//
+// Reference: MapReduce::aggregate src/mapreduce.cpp:385-563 computes, page by page,
+// proclist[i] = hashlittle(key,keybytes,nprocs) % nprocs (:469-472), then Irregular::setup/exchange
+// (src/irregular.cpp:95-301) packs pairs by destination and calls MPI_Alltoall (counts) + MPI_Alltoallv
+// (payload) under a flow-control loop that keeps every message under INTMAX bytes and every receive
+// under two pages.  Received pairs are ordered by source rank, original order within a source.
+//
+// Here: one kernel hashes every key (bit-exact lookup3), one stable single-digit radix pass groups record
+// indices by destination, one gather packs the send buffer, counts travel with an ncclAllGather, payload
+// with one ncclGroupStart/ncclSend/ncclRecv/ncclGroupEnd all-to-all over NVLink.  Receive buffers are
+// sized from the counts (HBM holds them whole), so the reference's INTMAX / two-page throttling and its
+// retry loop disappear; delivery order is the reference's.  Included by mrgpu.cu.
+#pragma once
+
+#include <nccl.h>  // types and prototypes only; the library is bound at run time with dlopen
+
+struct NcclApi {
+  void *lib = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *);
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int);
+  ncclResult_t (*CommDestroy)(ncclComm_t);
+  ncclResult_t (*GroupStart)();
+  ncclResult_t (*GroupEnd)();
+  ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t);
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
+  const char *(*GetErrorString)(ncclResult_t);
+};
+
+static NcclApi &nccl()
+{
+  static NcclApi api;
+  if (!api.lib) {
+    // if the host program already loaded an NCCL (torch does), dlopen returns that copy
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *nm : names) {
+      api.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+      if (api.lib) break;
+    }
+    if (!api.lib) MR_FAIL(MRGPU_ECOMM, std::string("cannot load libnccl.so.2: ") + dlerror());
+#define NCCL_SYM(field, name)                                      \
+  *(void **) (&api.field) = dlsym(api.lib, name);                  \
+  if (!api.field) MR_FAIL(MRGPU_ECOMM, "libnccl is missing symbol " name);
+    NCCL_SYM(GetUniqueId, "ncclGetUniqueId")
+    NCCL_SYM(CommInitRank, "ncclCommInitRank")
+    NCCL_SYM(CommDestroy, "ncclCommDestroy")
+    NCCL_SYM(GroupStart, "ncclGroupStart")
+    NCCL_SYM(GroupEnd, "ncclGroupEnd")
+    NCCL_SYM(Send, "ncclSend")
+    NCCL_SYM(Recv, "ncclRecv")
+    NCCL_SYM(AllGather, "ncclAllGather")
+    NCCL_SYM(AllReduce, "ncclAllReduce")
+    NCCL_SYM(GetErrorString, "ncclGetErrorString")
+#undef NCCL_SYM
+  }
+  return api;
+}
+
+#define MR_NCCL(expr)                                                                                     \
+  do {                                                                                                    \
+    ncclResult_t _r = (expr);                                                                             \
+    if (_r != ncclSuccess) throw ::mrgpu::Error{MRGPU_ECOMM, std::string(#expr " failed: ") + nccl().GetErrorString(_r)}; \
+  } while (0)
+
+static void comm_destroy(mrgpu_mr *mr)
+{
+  if (mr->comm) nccl().CommDestroy((ncclComm_t) mr->comm);
+  mr->comm = nullptr;
+}
+
+extern "C" int mrgpu_comm_unique_id(void *id128)
+{
+  if (!id128) return MRGPU_EINVAL;
+  try {
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    MR_NCCL(nccl().GetUniqueId(&id));
+    memcpy(id128, &id, 128);
+  } catch (const Error &e) {
+    g_create_error = e.msg;
+    return e.code;
+  }
+  return MRGPU_OK;
+}
+
+extern "C" int mrgpu_comm_init(mrgpu_mr *mr, int rank, int nranks, const void *id128)
+{
+  API_BEGIN(mr)
+  if (nranks < 1 || rank < 0 || rank >= nranks) MR_FAIL(MRGPU_EINVAL, "bad rank / nranks");
+  if (nranks > 256) MR_FAIL(MRGPU_ELIMIT, "more than 256 ranks is not supported");
+  if (mr->comm) comm_destroy(mr);
+  mr->rank = rank;
+  mr->nranks = nranks;
+  if (nranks > 1) {
+    if (!id128) MR_FAIL(MRGPU_EINVAL, "null unique id");
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    ncclComm_t c;
+    MR_NCCL(nccl().CommInitRank(&c, nranks, id, rank));
+    mr->comm = c;
+  }
+  API_END(mr)
+}
+
+static uint64_t allreduce_sum(mrgpu_mr *mr, uint64_t v)
+{
+  if (mr->nranks == 1) return v;
+  cudaStream_t s = mr->pool.stream;
+  unsigned long long *d = mr->d_small + 32;
+  MR_CUDA(cudaMemcpyAsync(d, &v, 8, cudaMemcpyHostToDevice, s));
+  MR_NCCL(nccl().AllReduce(d, d + 1, 1, ncclUint64, ncclSum, (ncclComm_t) mr->comm, s));
+  MR_CUDA(cudaMemcpyAsync(mr->h_small + 32, d + 1, 8, cudaMemcpyDeviceToHost, s));
+  sync(mr);
+  return mr->h_small[32];
+}
+
+// dest rank of every record, as a sort key whose only varying byte is the lowest one
+__global__ void __launch_bounds__(256)
+partition_dest_kernel(const uint8_t *__restrict__ data, const uint64_t *__restrict__ offs, uint64_t rs, uint64_t n, Align al, uint32_t nprocs,
+                      uint32_t *__restrict__ dest, uint32_t *__restrict__ idx, unsigned long long *hist)
+{
+  __shared__ unsigned sh[RADIX];
+  sh[threadIdx.x] = 0;
+  __syncthreads();
+  uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint8_t *r = data + rec_off(offs, rs, i);
+    uint32_t kb = *(const uint32_t *) r;
+    uint32_t d = hashlittle(r + kv_key_off(al), kb, nprocs) % nprocs;  // src/mapreduce.cpp:472
+    dest[i] = d;
+    idx[i] = (uint32_t) i;
+    atomicAdd(&sh[d], 1u);
+  }
+  __syncthreads();
+  if (sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], (unsigned long long) sh[threadIdx.x]);
+}
+
+__global__ void fill_u32_kernel(uint32_t *p, uint64_t n, uint32_t v)
+{
+  uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+__global__ void record_sizes_kernel(const uint64_t *__restrict__ offs, const uint32_t *__restrict__ perm, uint64_t n, uint32_t *__restrict__ sizes)
+{
+  uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) sizes[i] = (uint32_t) (offs[perm[i] + 1] - offs[perm[i]]);
+}
+
+__global__ void sum_kv_bytes_kernel(const uint8_t *__restrict__ data, const uint64_t *__restrict__ offs, uint64_t n, unsigned long long *ksum,
+                                    unsigned long long *vsum)
+{
+  unsigned long long k = 0, v = 0;
+  uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint32_t *r = (const uint32_t *) (data + offs[i]);
+    k += r[0];
+    v += r[1];
+  }
+  for (int o = 16; o; o >>= 1) {
+    k += __shfl_xor_sync(0xFFFFFFFFu, k, o);
+    v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (k) atomicAdd(ksum, k);
+    if (v) atomicAdd(vsum, v);
+  }
+}
+
+static void aggregate_impl(mrgpu_mr *mr)
+{
+  freeze(mr);
+  const int P = mr->nranks;
+  if (P == 1) return;  // src/mapreduce.cpp:403-406
+  DevKV *kv = mr->kv;
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const Align al = mr->al;
+  const uint64_t n = kv->nkv;
+  if (n >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "aggregate: more than 2^32-2 pairs on one GPU is not supported yet");
+  ncclComm_t comm = (ncclComm_t) mr->comm;
+
+  // 1. destinations, grouped stably
+  Buf<uint32_t> d0(pool, n), d1(pool, n), i0(pool, n), i1(pool, n);
+  Buf<unsigned long long> hist(pool, 8 * RADIX);
+  MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
+  if (n) {
+    partition_dest_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>(kv->data, kv->uniform ? nullptr : kv->offs, kv->recsize, n, al, (uint32_t) P, d0.p,
+                                                                i0.p, hist.p);
+    MR_CUDA(cudaGetLastError());
+  }
+  std::vector<unsigned long long> cnt(RADIX);
+  MR_CUDA(cudaMemcpyAsync(cnt.data(), hist.p, RADIX * 8, cudaMemcpyDeviceToHost, s));
+  sync(mr);
+  // bytes 1..3 of the dest "key" are all zero: mark them as known-constant
+  MR_CUDA(cudaMemsetAsync(hist.p + RADIX, 0, 3 * RADIX * 8, s));
+  int cur = radix_sort_pairs<uint32_t, uint32_t, true>(pool, d0.p, d1.p, i0.p, i1.p, n, 0x1, true, hist.p);
+  const uint32_t *perm = cur ? i1.p : i0.p;
+
+  // 2. pack the send buffer in destination order
+  Buf<uint8_t> sendbuf(pool, kv->nbytes);
+  Buf<uint32_t> ssizes;
+  Buf<uint64_t> soffs;
+  bool uni = kv->uniform;
+  std::vector<uint64_t> scount(P), sbytes(P), sdisp(P + 1, 0), srec(P + 1, 0);
+  for (int p = 0; p < P; p++) {
+    scount[p] = cnt[p];
+    srec[p + 1] = srec[p] + cnt[p];
+  }
+  if (n) {
+    if (uni) {
+      uint32_t words = kv->recsize / 4;
+      gather_uniform_kernel<<<(unsigned) ((n * words + 255) / 256), 256, 0, s>>>((const uint32_t *) kv->data, (uint32_t *) sendbuf.p, perm, n, words);
+      MR_CUDA(cudaGetLastError());
+      for (int p = 0; p < P; p++) sbytes[p] = scount[p] * kv->recsize;
+    } else {
+      ssizes.alloc(pool, n);
+      soffs.alloc(pool, n + 1);
+      record_sizes_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(kv->offs, perm, n, ssizes.p);
+      MR_CUDA(cudaGetLastError());
+      const uint32_t *sz = ssizes.p;
+      uint64_t *so = soffs.p;
+      scan_apply(
+          pool, n, [=] __device__(uint64_t i) -> unsigned long long { return sz[i]; },
+          [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { so[i] = e; }, mr->d_small);
+      MR_CUDA(cudaMemcpyAsync(so + n, mr->d_small, 8, cudaMemcpyDeviceToDevice, s));
+      gather_general_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(kv->data, kv->offs, sendbuf.p, soffs.p, perm, n);
+      MR_CUDA(cudaGetLastError());
+      std::vector<uint64_t> edge(P + 1);
+      for (int p = 0; p <= P; p++) MR_CUDA(cudaMemcpyAsync(&edge[p], soffs.p + srec[p], 8, cudaMemcpyDeviceToHost, s));
+      sync(mr);
+      for (int p = 0; p < P; p++) sbytes[p] = edge[p + 1] - edge[p];
+    }
+  }
+  for (int p = 0; p < P; p++) sdisp[p + 1] = sdisp[p] + sbytes[p];
+
+  // 3. counts: every rank learns the whole P x P table (records, bytes) and every rank's record shape
+  //    (replaces MPI_Alltoall + MPI_Reduce_scatter of src/irregular.cpp:144,178)
+  const int W = 2 * P + 2;
+  std::vector<unsigned long long> mine(W);
+  for (int p = 0; p < P; p++) {
+    mine[2 * p] = scount[p];
+    mine[2 * p + 1] = sbytes[p];
+  }
+  mine[2 * P] = n == 0 ? 0 : (uni ? 2 : 1);
+  mine[2 * P + 1] = uni ? (((unsigned long long) kv->kb << 32) | kv->vb) : 0;
+  Buf<unsigned long long> dmine(pool, W), dall(pool, (uint64_t) W * P);
+  MR_CUDA(cudaMemcpyAsync(dmine.p, mine.data(), W * 8, cudaMemcpyHostToDevice, s));
+  MR_NCCL(nccl().AllGather(dmine.p, dall.p, W, ncclUint64, comm, s));
+  std::vector<unsigned long long> all((size_t) W * P);
+  MR_CUDA(cudaMemcpyAsync(all.data(), dall.p, (size_t) W * P * 8, cudaMemcpyDeviceToHost, s));
+  sync(mr);
+  std::vector<uint64_t> rcount(P), rbytes(P), rdisp(P + 1, 0), rrec(P + 1, 0);
+  bool all_uniform = true;
+  unsigned long long shape = 0;
+  bool have_shape = false;
+  for (int q = 0; q < P; q++) {
+    rcount[q] = all[(size_t) q * W + 2 * mr->rank];
+    rbytes[q] = all[(size_t) q * W + 2 * mr->rank + 1];
+    rdisp[q + 1] = rdisp[q] + rbytes[q];
+    rrec[q + 1] = rrec[q] + rcount[q];
+    unsigned long long kind = all[(size_t) q * W + 2 * P], sh = all[(size_t) q * W + 2 * P + 1];
+    if (kind == 1) all_uniform = false;
+    if (kind == 2) {
+      if (have_shape && sh != shape) all_uniform = false;
+      shape = sh;
+      have_shape = true;
+    }
+  }
+  const uint64_t nrecv = rrec[P], brecv = rdisp[P];
+  if (nrecv >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "aggregate: a rank would receive more than 2^32-2 pairs");
+
+  // 4. payload all-to-all over NVLink (replaces MPI_Alltoallv, src/irregular.cpp:292-300)
+  DevKV *nk = new DevKV(&pool);
+  try {
+    nk->reserve_bytes(brecv);
+    Buf<uint32_t> rsizes;
+    bool need_sizes = !all_uniform;
+    if (need_sizes) {
+      rsizes.alloc(pool, nrecv);
+      if (uni && n) {  // peers need per-record sizes even if mine are all equal
+        ssizes.alloc(pool, n);
+        fill_u32_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(ssizes.p, n, kv->recsize);
+        MR_CUDA(cudaGetLastError());
+      }
+    }
+    MR_NCCL(nccl().GroupStart());
+    for (int p = 0; p < P; p++) {
+      if (p == mr->rank) continue;
+      if (sbytes[p]) MR_NCCL(nccl().Send(sendbuf.p + sdisp[p], sbytes[p], ncclInt8, p, comm, s));
+      if (rbytes[p]) MR_NCCL(nccl().Recv(nk->data + rdisp[p], rbytes[p], ncclInt8, p, comm, s));
+      if (need_sizes) {
+        if (scount[p]) MR_NCCL(nccl().Send(ssizes.p + srec[p], scount[p], ncclUint32, p, comm, s));
+        if (rcount[p]) MR_NCCL(nccl().Recv(rsizes.p + rrec[p], rcount[p], ncclUint32, p, comm, s));
+      }
+    }
+    MR_NCCL(nccl().GroupEnd());
+    int me = mr->rank;
+    if (sbytes[me])
+      MR_CUDA(cudaMemcpyAsync(nk->data + rdisp[me], sendbuf.p + sdisp[me], sbytes[me], cudaMemcpyDeviceToDevice, s));
+    if (need_sizes && scount[me])
+      MR_CUDA(cudaMemcpyAsync(rsizes.p + rrec[me], ssizes.p + srec[me], scount[me] * 4, cudaMemcpyDeviceToDevice, s));
+
+    nk->nbytes = brecv;
+    nk->nkv = nrecv;
+    if (all_uniform && have_shape) {
+      nk->uniform = true;
+      nk->kb = (uint32_t) (shape >> 32);
+      nk->vb = (uint32_t) shape;
+      nk->recsize = kv_rec_size(al, nk->kb, nk->vb);
+      nk->ksize = nrecv * nk->kb;
+      nk->vsize = nrecv * nk->vb;
+    } else if (nrecv) {
+      nk->uniform = false;
+      nk->reserve_offs(nrecv + 1);
+      const uint32_t *sz = rsizes.p;
+      uint64_t *oo = nk->offs;
+      scan_apply(
+          pool, nrecv, [=] __device__(uint64_t i) -> unsigned long long { return sz[i]; },
+          [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { oo[i] = e; }, mr->d_small);
+      MR_CUDA(cudaMemcpyAsync(oo + nrecv, mr->d_small, 8, cudaMemcpyDeviceToDevice, s));
+      MR_CUDA(cudaMemsetAsync(mr->d_small + 1, 0, 16, s));
+      sum_kv_bytes_kernel<<<grid_for(nrecv, 256 * 4, 8), 256, 0, s>>>(nk->data, nk->offs, nrecv, mr->d_small + 1, mr->d_small + 2);
+      MR_CUDA(cudaGetLastError());
+      fetch_small(mr, 3);
+      nk->ksize = mr->h_small[1];
+      nk->vsize = mr->h_small[2];
+    }
+    sync(mr);
+  } catch (...) {
+    delete nk;
+    throw;
+  }
+  delete mr->kv;
+  mr->kv = nk;
+}
+
+extern "C" int mrgpu_aggregate(mrgpu_mr *mr, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot aggregate without KeyValue");
+  if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  aggregate_impl(mr);
+  sync(mr);
+  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  API_END(mr)
+}
+
+extern "C" int mrgpu_collate(mrgpu_mr *mr, uint64_t *nkmv)
+{
+  API_BEGIN(mr)
+  if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot collate without KeyValue");
+  if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  aggregate_impl(mr);  // src/mapreduce.cpp:726-727: aggregate(hash); convert();
+  convert_impl(mr);
+  sync(mr);
+  if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
+  API_END(mr)
+}

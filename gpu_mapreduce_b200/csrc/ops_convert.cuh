@@ -1,0 +1,509 @@
+// convert(): KeyValue -> KeyMultiValue (group by key).
+//
+// Reference: KeyMultiValue::convert src/keymultivalue.cpp:486-638 = chained hash of Unique records
+// (kv2unique :645-789), page layout of the KMV pairs (unique2kmv_all :800-966), then a second full pass
+// re-hashing every pair to append its value (kv2kmv :1139-1209); overflow goes through Spool partitions.
+// Semantics kept: one KMV pair per distinct key; its values in ARRIVAL order (the stable sort below
+// preserves it -- reduce(cull) and the postings lists see the same value order as the reference).
+// Semantics not kept (none of the reference's callers can observe it after the canonical sort the spec
+// allows): KMV pairs come out in sort-key order instead of first-appearance order.
+//
+// GPU design: grouping = stable LSD radix sort on an exact, compact sort key, then run detection and a
+// coalesced scatter into KMV records.  Chained tables and the two re-hash passes are random HBM traffic;
+// the sort is streaming.
+//   uniform KV, <= 8 varying key bytes: sort key = those bytes (bijective), payload = the value itself
+//       (4/8-byte values), nothing (NULL values) or the record index (gathered afterwards);
+//   everything else: sort key = 64-bit fingerprint (hashlittle(key,kb,0) : second hash), payload = record
+//       index; runs are then VERIFIED key-by-key against their neighbour and the whole grouping is redone
+//       with a new seed if two different keys ever share a fingerprint, so the result is exact.
+// Included by mrgpu.cu.
+#pragma once
+
+struct CompactKey {
+  int nvb;               // number of varying key bytes (<= 8)
+  unsigned char pos[8];  // their positions inside the key
+};
+
+// ---- uniform records: extract sort key (+ payload) and histogram in one read of the KV -----------------
+
+template <typename K, int PMODE /*0 none, 1 val32, 2 val64, 3 idx*/, bool IDENT /*key bytes 0..kb-1, kb<=8, word loads*/>
+__global__ void __launch_bounds__(256)
+extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs, uint32_t koff, uint32_t voff, uint32_t kb, CompactKey ck,
+                       K *__restrict__ keys, void *__restrict__ pay, unsigned long long *hist)
+{
+  __shared__ unsigned sh[sizeof(K) * RADIX];
+  for (int i = threadIdx.x; i < (int) sizeof(K) * RADIX; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  unsigned prev[sizeof(K)], run[sizeof(K)];
+#pragma unroll
+  for (int b = 0; b < (int) sizeof(K); b++) prev[b] = 0, run[b] = 0;
+  uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint8_t *r = data + i * rs;
+    K key = 0;
+    if (IDENT) {
+      const uint32_t *w = (const uint32_t *) (r + koff);
+      unsigned long long k64 = 0;
+      if (kb > 0) k64 = w[0];
+      if (kb > 4) k64 |= (unsigned long long) w[1] << 32;
+      if (kb & 3) {  // partial last word: mask bytes beyond the key
+        unsigned long long m = kb >= 8 ? ~0ull : ((1ull << (8 * kb)) - 1);
+        k64 &= m;
+      }
+      key = (K) k64;
+    } else {
+      unsigned long long k64 = 0;
+      for (int q = 0; q < ck.nvb; q++) k64 |= (unsigned long long) r[koff + ck.pos[q]] << (8 * q);
+      key = (K) k64;
+    }
+    keys[i] = key;
+    if (PMODE == 1) ((uint32_t *) pay)[i] = *(const uint32_t *) (r + voff);
+    if (PMODE == 2) {
+      const uint32_t *v = (const uint32_t *) (r + voff);
+      ((uint64_t *) pay)[i] = (uint64_t) v[0] | ((uint64_t) v[1] << 32);
+    }
+    if (PMODE == 3) ((uint32_t *) pay)[i] = (uint32_t) i;
+    hist_accumulate<K>(key, prev, run, sh);
+  }
+  hist_flush<K>(prev, run, sh, hist);
+}
+
+// IntCount layout {kb=4, vb=4, key, value} in one 16-byte load per record
+__global__ void __launch_bounds__(256)
+extract16_kernel(const int4 *__restrict__ recs, uint64_t n, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, unsigned long long *hist)
+{
+  __shared__ unsigned sh[4 * RADIX];
+  for (int i = threadIdx.x; i < 4 * RADIX; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  unsigned prev[4] = {0, 0, 0, 0}, run[4] = {0, 0, 0, 0};
+  constexpr int U = 4;
+  uint64_t stride = (uint64_t) gridDim.x * blockDim.x * U;
+  for (uint64_t base = (uint64_t) blockIdx.x * blockDim.x * U + threadIdx.x; base < n; base += stride) {
+    int4 r[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      uint64_t i = base + (uint64_t) u * blockDim.x;
+      if (i < n) r[u] = ld_stream(recs + i);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      uint64_t i = base + (uint64_t) u * blockDim.x;
+      if (i < n) {
+        keys[i] = (uint32_t) r[u].z;
+        vals[i] = (uint32_t) r[u].w;
+        hist_accumulate<uint32_t>((uint32_t) r[u].z, prev, run, sh);
+      }
+    }
+  }
+  hist_flush<uint32_t>(prev, run, sh, hist);
+}
+
+// OR of (key XOR first key) over all records: which key bytes vary at all (uniform keys longer than 8 bytes)
+__global__ void key_diff_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs, uint32_t koff, uint32_t kb, unsigned *mask /*[kb]*/)
+{
+  extern __shared__ unsigned shm[];
+  for (uint32_t q = threadIdx.x; q < kb; q += blockDim.x) shm[q] = 0;
+  __syncthreads();
+  uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint8_t *r = data + i * rs + koff;
+    for (uint32_t q = 0; q < kb; q++) {
+      unsigned d = r[q] ^ data[koff + q];
+      if (d && !shm[q]) shm[q] = 1;  // benign race: any writer stores 1
+    }
+  }
+  __syncthreads();
+  for (uint32_t q = threadIdx.x; q < kb; q += blockDim.x)
+    if (shm[q]) mask[q] = 1;
+}
+
+// ---- general records: fingerprint + index ------------------------------------------------------------------
+
+__global__ void __launch_bounds__(256)
+extract_fp_kernel(const uint8_t *__restrict__ data, const uint64_t *__restrict__ offs, uint64_t recsize, uint64_t n, Align al, uint32_t seed,
+                  uint64_t *__restrict__ keys, uint32_t *__restrict__ idx, unsigned long long *hist)
+{
+  __shared__ unsigned sh[8 * RADIX];
+  for (int i = threadIdx.x; i < 8 * RADIX; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  unsigned prev[8], run[8];
+#pragma unroll
+  for (int b = 0; b < 8; b++) prev[b] = 0, run[b] = 0;
+  uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint8_t *r = data + rec_off(offs, recsize, i);
+    uint32_t kb = *(const uint32_t *) r;
+    const uint8_t *k = r + kv_key_off(al);
+    uint64_t fp = ((uint64_t) hashlittle(k, kb, seed) << 32) | fingerprint_lo(k, kb, seed * 0x9E3779B9u + 1);
+    keys[i] = fp;
+    idx[i] = (uint32_t) i;
+    hist_accumulate<uint64_t>(fp, prev, run, sh);
+  }
+  hist_flush<uint64_t>(prev, run, sh, hist);
+}
+
+__device__ __forceinline__ bool keys_equal(const uint8_t *data, const uint64_t *offs, uint64_t recsize, Align al, uint32_t i, uint32_t j)
+{
+  const uint8_t *a = data + rec_off(offs, recsize, i), *b = data + rec_off(offs, recsize, j);
+  uint32_t ka = *(const uint32_t *) a, kbb = *(const uint32_t *) b;
+  if (ka != kbb) return false;
+  a += kv_key_off(al);
+  b += kv_key_off(al);
+  for (uint32_t q = 0; q < ka; q++)
+    if (a[q] != b[q]) return false;
+  return true;
+}
+
+// warp-aggregated add of per-lane contributions to one global counter
+__device__ __forceinline__ void warp_add(unsigned long long *ctr, unsigned long long v)
+{
+  unsigned act = __activemask();
+  // sum over active lanes with shuffles restricted to the active set
+  for (int o = 16; o; o >>= 1) {
+    unsigned long long t = __shfl_down_sync(act, v, o);
+    int src = (threadIdx.x & 31) + o;
+    if (src < 32 && ((act >> src) & 1)) v += t;
+  }
+  if ((threadIdx.x & 31) == __ffs(act) - 1) atomicAdd(ctr, v);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+
+template <typename K, int PMODE>
+static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, const std::vector<uint8_t> &key0)
+{
+  DevKV *kv = mr->kv;
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const Align al = mr->al;
+  const uint64_t n = kv->nkv;
+  const uint32_t kb = kv->kb, vb = kv->vb, rs = kv->recsize, koff = kv_key_off(al), voff = kv_val_off(al, kb);
+  using P = typename std::conditional<PMODE == 2, uint64_t, uint32_t>::type;
+  constexpr bool HASP = PMODE != 0;
+
+  Buf<K> k0(pool, n), k1(pool, n);
+  Buf<P> p0(pool, HASP ? n : 1), p1(pool, HASP ? n : 1);
+  Buf<unsigned long long> hist(pool, 8 * RADIX);
+  MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
+
+  // 1. one read of the KV: sort keys, payload, byte histograms
+  if (ident && PMODE == 1 && sizeof(K) == 4 && kb == 4 && rs == 16 && koff == 8 && voff == 12 && ((uintptr_t) kv->data % 16) == 0)
+    extract16_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>((const int4 *) kv->data, n, (uint32_t *) k0.p, (uint32_t *) p0.p, hist.p);
+  else if (ident)
+    extract_uniform_kernel<K, PMODE, true><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p);
+  else
+    extract_uniform_kernel<K, PMODE, false><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p);
+  MR_CUDA(cudaGetLastError());
+
+  // 2. stable LSD radix sort on the varying bytes only
+  unsigned mask = ck.nvb >= 8 ? 0xFF : ((1u << ck.nvb) - 1);
+  int cur = radix_sort_pairs<K, P, HASP>(pool, k0.p, k1.p, p0.p, p1.p, n, mask, true, hist.p);
+  const K *sk = cur ? k1.p : k0.p;
+  const P *sp = cur ? p1.p : p0.p;
+  (cur ? k0 : k1).release();
+  (cur ? p0 : p1).release();
+
+  // 3. run heads -> number of unique keys U and start[u]
+  auto head = [=] __device__(uint64_t i) -> unsigned long long { return (i == 0 || sk[i] != sk[i - 1]) ? 1ull : 0ull; };
+  ScanTiles heads;
+  scan_tiles(pool, n, head, heads, mr->d_small);
+  fetch_small(mr, 1);
+  const uint64_t U = mr->h_small[0];
+  Buf<uint32_t> start(pool, U + 1);
+  {
+    uint32_t *st = start.p;
+    scan_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
+      if (h) st[e] = (uint32_t) i;
+    });
+    uint32_t n32 = (uint32_t) n;
+    MR_CUDA(cudaMemcpyAsync(start.p + U, &n32, 4, cudaMemcpyHostToDevice, s));
+  }
+
+  // 4. KMV record sizes -> offs[u]
+  DevKMV *kmv = new DevKMV(&pool);
+  try {
+    kmv->offs = (uint64_t *) pool.alloc((U + 1) * 8);
+    kmv->offs_cap = U + 1;
+    uint64_t *offs = kmv->offs;
+    const uint32_t *st = start.p;
+    scan_apply(
+        pool, U, [=] __device__(uint64_t u) -> unsigned long long {
+          uint64_t nv = st[u + 1] - st[u];
+          return kmv_rec_size(al, nv, kb, nv * vb);
+        },
+        [=] __device__(uint64_t u, unsigned long long e, unsigned long long) { offs[u] = e; }, mr->d_small);
+    fetch_small(mr, 1);
+    const uint64_t total = mr->h_small[0];
+    MR_CUDA(cudaMemcpyAsync(offs + U, &total, 8, cudaMemcpyHostToDevice, s));
+    kmv->data = (uint8_t *) pool.alloc(total);
+    kmv->cap = total;
+    kmv->nbytes = total;
+
+    // 5. scatter: element i of run u, rank r -> sizes[r], value r; the run head also writes header + key
+    uint8_t *out = kmv->data;
+    const uint8_t *kvdata = kv->data;
+    // first key's bytes (constant bytes of every key) for the compact mode
+    Buf<uint8_t> dkey0(pool, kb ? kb : 1);
+    if (!ident && kb) MR_CUDA(cudaMemcpyAsync(dkey0.p, key0.data(), kb, cudaMemcpyHostToDevice, s));
+    const uint8_t *k0b = dkey0.p;
+    scan_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
+      uint64_t u = e + h - 1;
+      uint32_t s0 = st[u];
+      uint64_t nv = st[u + 1] - s0, r = i - s0;
+      uint8_t *rec = out + offs[u];
+      uint64_t ko = kmv_key_off(al, nv), vo = kmv_val_off(al, nv, kb);
+      if (h) {
+        uint32_t *hd = (uint32_t *) rec;
+        hd[0] = (uint32_t) nv;
+        hd[1] = kb;
+        hd[2] = (uint32_t) (nv * vb);
+        for (uint64_t q = 12 + 4 * nv; q < ko; q++) rec[q] = 0;
+        K key = sk[i];
+        if (ident) {
+          for (uint32_t q = 0; q < kb; q++) rec[ko + q] = (uint8_t) ((unsigned long long) key >> (8 * q));
+        } else {
+          for (uint32_t q = 0; q < kb; q++) rec[ko + q] = k0b[q];
+          for (int q = 0; q < ck.nvb; q++) rec[ko + ck.pos[q]] = (uint8_t) ((unsigned long long) key >> (8 * q));
+        }
+        for (uint64_t q = ko + kb; q < vo; q++) rec[q] = 0;
+        uint64_t end = kmv_rec_size(al, nv, kb, nv * vb);
+        for (uint64_t q = vo + nv * vb; q < end; q++) rec[q] = 0;
+      }
+      ((uint32_t *) (rec + 12))[r] = vb;
+      if (PMODE == 1) *(uint32_t *) (rec + vo + r * 4) = (uint32_t) sp[i];
+      if (PMODE == 2) {
+        uint64_t v = sp[i];
+        uint32_t *d = (uint32_t *) (rec + vo + r * 8);
+        d[0] = (uint32_t) v;
+        d[1] = (uint32_t) (v >> 32);
+      }
+      if (PMODE == 3) {
+        const uint8_t *src = kvdata + (uint64_t) sp[i] * rs + voff;
+        uint8_t *d = rec + vo + r * vb;
+        for (uint32_t q = 0; q < vb; q++) d[q] = src[q];
+      }
+    });
+    kmv->nkmv = U;
+    kmv->nvalue = n;
+    kmv->ksize = U * (uint64_t) kb;
+    kmv->vsize = kv->vsize;
+    kmv->ukb = kb;
+    kmv->uvb = vb;
+    sync(mr);
+  } catch (...) {
+    delete kmv;
+    throw;
+  }
+  mr->kmv = kmv;
+}
+
+static void convert_general(mrgpu_mr *mr)
+{
+  DevKV *kv = mr->kv;
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const Align al = mr->al;
+  const uint64_t n = kv->nkv;
+  const uint8_t *data = kv->data;
+  const uint64_t *ko = kv->uniform ? nullptr : kv->offs;
+  const uint64_t rs = kv->recsize;
+
+  Buf<uint64_t> k0(pool, n), k1(pool, n);
+  Buf<uint32_t> p0(pool, n), p1(pool, n);
+  Buf<unsigned long long> hist(pool, 8 * RADIX);
+  const uint64_t *sk = nullptr;
+  const uint32_t *sp = nullptr;
+  ScanTiles heads;
+  uint64_t U = 0;
+  for (uint32_t attempt = 0;; attempt++) {
+    if (attempt == 8) MR_FAIL(MRGPU_EINVAL, "convert: fingerprint collisions persisted over 8 seeds");
+    MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
+    // seed 0 makes the high half exactly the reference's bucket hash hashlittle(key,kb,0) (keymultivalue.cpp:1428)
+    extract_fp_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>(data, ko, rs, n, al, attempt, k0.p, p0.p, hist.p);
+    MR_CUDA(cudaGetLastError());
+    int cur = radix_sort_pairs<uint64_t, uint32_t, true>(pool, k0.p, k1.p, p0.p, p1.p, n, 0xFF, true, hist.p);
+    sk = cur ? k1.p : k0.p;
+    sp = cur ? p1.p : p0.p;
+    const uint64_t *skc = sk;
+    const uint32_t *spc = sp;
+    unsigned long long *flag = mr->d_small + 1;
+    MR_CUDA(cudaMemsetAsync(flag, 0, 8, s));
+    // run heads by fingerprint; inside a run every element must equal its predecessor byte for byte
+    auto head = [=] __device__(uint64_t i) -> unsigned long long {
+      if (i == 0) return 1ull;
+      if (skc[i] != skc[i - 1]) return 1ull;
+      if (!keys_equal(data, ko, rs, al, spc[i], spc[i - 1])) *flag = 1;
+      return 0ull;
+    };
+    scan_tiles(pool, n, head, heads, mr->d_small);
+    fetch_small(mr, 2);
+    U = mr->h_small[0];
+    if (mr->h_small[1] == 0) break;
+  }
+  const uint64_t *skc = sk;
+  const uint32_t *spc = sp;
+  auto head = [=] __device__(uint64_t i) -> unsigned long long { return (i == 0 || skc[i] != skc[i - 1]) ? 1ull : 0ull; };
+
+  // start[u], and G[i] = value bytes before sorted element i
+  Buf<uint32_t> start(pool, U + 1);
+  Buf<uint64_t> G(pool, n + 1);
+  uint32_t *st = start.p;
+  uint64_t *g = G.p;
+  scan_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
+    if (h) st[e] = (uint32_t) i;
+  });
+  uint32_t n32 = (uint32_t) n;
+  MR_CUDA(cudaMemcpyAsync(st + U, &n32, 4, cudaMemcpyHostToDevice, s));
+  scan_apply(
+      pool, n, [=] __device__(uint64_t i) -> unsigned long long { return ((const uint32_t *) (data + rec_off(ko, rs, spc[i])))[1]; },
+      [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { g[i] = e; }, mr->d_small + 2);
+  MR_CUDA(cudaMemcpyAsync(g + n, mr->d_small + 2, 8, cudaMemcpyDeviceToDevice, s));
+
+  DevKMV *kmv = new DevKMV(&pool);
+  try {
+    kmv->offs = (uint64_t *) pool.alloc((U + 1) * 8);
+    kmv->offs_cap = U + 1;
+    uint64_t *offs = kmv->offs;
+    unsigned long long *ksum = mr->d_small + 3;
+    MR_CUDA(cudaMemsetAsync(ksum, 0, 8, s));
+    scan_apply(
+        pool, U,
+        [=] __device__(uint64_t u) -> unsigned long long {
+          uint32_t s0 = st[u], s1 = st[u + 1];
+          uint32_t kb = *(const uint32_t *) (data + rec_off(ko, rs, spc[s0]));
+          return kmv_rec_size(al, s1 - s0, kb, g[s1] - g[s0]);
+        },
+        [=] __device__(uint64_t u, unsigned long long e, unsigned long long) {
+          offs[u] = e;
+          warp_add(ksum, *(const uint32_t *) (data + rec_off(ko, rs, spc[st[u]])));
+        },
+        mr->d_small);
+    fetch_small(mr, 4);
+    const uint64_t total = mr->h_small[0];
+    MR_CUDA(cudaMemcpyAsync(offs + U, &total, 8, cudaMemcpyHostToDevice, s));
+    kmv->data = (uint8_t *) pool.alloc(total);
+    kmv->cap = total;
+    kmv->nbytes = total;
+    kmv->ksize = mr->h_small[3];
+    uint8_t *out = kmv->data;
+    scan_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
+      uint64_t u = e + h - 1;
+      uint32_t s0 = st[u], s1 = st[u + 1];
+      uint64_t nv = s1 - s0, r = i - s0;
+      const uint8_t *src = data + rec_off(ko, rs, spc[i]);
+      uint32_t kb = ((const uint32_t *) src)[0], vb = ((const uint32_t *) src)[1];
+      uint64_t mvb = g[s1] - g[s0];
+      uint8_t *rec = out + offs[u];
+      uint64_t koff = kmv_key_off(al, nv), vo = kmv_val_off(al, nv, kb);
+      if (h) {
+        uint32_t *hd = (uint32_t *) rec;
+        hd[0] = (uint32_t) nv;
+        hd[1] = kb;
+        hd[2] = (uint32_t) mvb;
+        for (uint64_t q = 12 + 4 * nv; q < koff; q++) rec[q] = 0;
+        const uint8_t *k = src + kv_key_off(al);
+        for (uint32_t q = 0; q < kb; q++) rec[koff + q] = k[q];
+        for (uint64_t q = koff + kb; q < vo; q++) rec[q] = 0;
+        uint64_t end = kmv_rec_size(al, nv, kb, mvb);
+        for (uint64_t q = vo + mvb; q < end; q++) rec[q] = 0;
+      }
+      ((uint32_t *) (rec + 12))[r] = vb;
+      const uint8_t *v = src + kv_val_off(al, kb);
+      uint8_t *d = rec + vo + (g[i] - g[s0]);
+      for (uint32_t q = 0; q < vb; q++) d[q] = v[q];
+    });
+    kmv->nkmv = U;
+    kmv->nvalue = n;
+    kmv->vsize = kv->vsize;
+    kmv->ukb = kv->uniform ? (int64_t) kv->kb : -1;
+    kmv->uvb = kv->uniform ? (int64_t) kv->vb : -1;
+    sync(mr);
+  } catch (...) {
+    delete kmv;
+    throw;
+  }
+  mr->kmv = kmv;
+}
+
+static void convert_impl(mrgpu_mr *mr)
+{
+  freeze(mr);
+  DevKV *kv = mr->kv;
+  if (kv->nkv >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "convert: more than 2^32-2 pairs on one GPU is not supported yet");
+  delete mr->kmv;
+  mr->kmv = nullptr;
+  const uint64_t n = kv->nkv;
+  if (n == 0) {
+    DevKMV *kmv = new DevKMV(&mr->pool);
+    kmv->offs = (uint64_t *) mr->pool.alloc(8);
+    kmv->offs_cap = 1;
+    MR_CUDA(cudaMemsetAsync(kmv->offs, 0, 8, mr->pool.stream));
+    mr->kmv = kmv;
+  } else {
+    bool done = false;
+    const Align al = mr->al;
+    // exact path needs word-aligned records/keys and a value that is empty, 4 or 8 bytes, or gatherable
+    if (kv->uniform && (al.k % 4) == 0 && (al.v % 4 == 0 || kv->vb == 0 || true)) {
+      CompactKey ck{};
+      bool ident = kv->kb <= 8;
+      std::vector<uint8_t> key0(kv->kb);
+      bool ok = true;
+      if (ident) {
+        ck.nvb = (int) kv->kb;
+        for (int q = 0; q < 8; q++) ck.pos[q] = (unsigned char) q;
+      } else if (kv->kb <= 1024) {
+        Buf<unsigned> mask(mr->pool, kv->kb);
+        MR_CUDA(cudaMemsetAsync(mask.p, 0, kv->kb * 4, mr->pool.stream));
+        key_diff_kernel<<<grid_for(n, 256 * 8, 4), 256, kv->kb * 4, mr->pool.stream>>>(kv->data, n, kv->recsize, kv_key_off(al), kv->kb, mask.p);
+        MR_CUDA(cudaGetLastError());
+        std::vector<unsigned> hm(kv->kb);
+        MR_CUDA(cudaMemcpyAsync(hm.data(), mask.p, kv->kb * 4, cudaMemcpyDeviceToHost, mr->pool.stream));
+        MR_CUDA(cudaMemcpyAsync(key0.data(), kv->data + kv_key_off(al), kv->kb, cudaMemcpyDeviceToHost, mr->pool.stream));
+        sync(mr);
+        int nv = 0;
+        for (uint32_t q = 0; q < kv->kb; q++)
+          if (hm[q]) {
+            if (nv < 8) ck.pos[nv] = (unsigned char) q;
+            nv++;
+          }
+        if (nv > 8 || kv->kb > 256) ok = false;
+        ck.nvb = nv;
+      } else
+        ok = false;
+      if (ok) {
+        bool small = ck.nvb <= 4;
+        bool v32 = kv->vb == 4 && (kv_val_off(al, kv->kb) % 4) == 0;
+        bool v64 = kv->vb == 8 && (kv_val_off(al, kv->kb) % 4) == 0;
+        int pm = kv->vb == 0 ? 0 : (v32 ? 1 : (v64 ? 2 : 3));
+#define CONV_CASE(K, PM) convert_uniform<K, PM>(mr, ck, ident, key0)
+        if (small) {
+          if (pm == 0) CONV_CASE(uint32_t, 0);
+          else if (pm == 1) CONV_CASE(uint32_t, 1);
+          else if (pm == 2) CONV_CASE(uint32_t, 2);
+          else CONV_CASE(uint32_t, 3);
+        } else {
+          if (pm == 0) CONV_CASE(uint64_t, 0);
+          else if (pm == 1) CONV_CASE(uint64_t, 1);
+          else if (pm == 2) CONV_CASE(uint64_t, 2);
+          else CONV_CASE(uint64_t, 3);
+        }
+#undef CONV_CASE
+        done = true;
+      }
+    }
+    if (!done) convert_general(mr);
+  }
+  // convert consumes the KV (src/mapreduce.cpp:876-878: "delete kv; kv = NULL")
+  delete mr->kv;
+  mr->kv = nullptr;
+}
+
+extern "C" int mrgpu_convert(mrgpu_mr *mr, uint64_t *nkmv)
+{
+  API_BEGIN(mr)
+  if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot convert without KeyValue");
+  convert_impl(mr);
+  sync(mr);
+  if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
+  API_END(mr)
+}

@@ -1,0 +1,469 @@
+// map(): emit into KV pages.  The reference calls a CPU callback per task which calls KeyValue::add per
+// pair (src/mapreduce.cpp:1102-1225, src/keyvalue.cpp:343-392).  Here the stock callbacks are device
+// functors and "add" is a coalesced store at a position known from the record index (uniform records) or
+// from a prefix sum of record sizes (variable records).  Included by mrgpu.cu.
+#pragma once
+
+// ---------------------------------------------------------------------------------------------
+// KV bookkeeping shared by all map flavours
+
+// map()'s preamble, src/mapreduce.cpp:1114-1131: an existing KMV is dropped; addflag = 0 starts a new KV,
+// addflag = 1 re-opens the current one for append (KeyValue::append, src/keyvalue.cpp:185-209).
+static void kv_begin_map(mrgpu_mr *mr, int addflag)
+{
+  freeze(mr);
+  delete mr->kmv;
+  mr->kmv = nullptr;
+  if (!addflag || !mr->kv) {
+    delete mr->kv;
+    mr->kv = new DevKV(&mr->pool);
+  }
+}
+
+__global__ void iota_offsets_kernel(uint64_t *offs, uint64_t n_plus_1, uint64_t recsize)
+{
+  uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_plus_1) offs[i] = i * recsize;
+}
+
+__global__ void affine_offsets_kernel(uint64_t *o, uint64_t cnt, uint64_t base, uint64_t rs)
+{
+  uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < cnt) o[j] = base + j * rs;
+}
+
+// give a uniform KV an explicit offset index so that records of another shape can be appended
+static void kv_make_general(mrgpu_mr *mr, DevKV *kv)
+{
+  if (!kv->uniform || kv->nkv == 0) {
+    if (kv->nkv == 0) {
+      kv->uniform = false;
+      kv->reserve_offs(1);
+      MR_CUDA(cudaMemsetAsync(kv->offs, 0, 8, mr->pool.stream));
+    }
+    return;
+  }
+  kv->reserve_offs(kv->nkv + 1);
+  iota_offsets_kernel<<<(unsigned) ((kv->nkv + 1 + 255) / 256), 256, 0, mr->pool.stream>>>(kv->offs, kv->nkv + 1, kv->recsize);
+  MR_CUDA(cudaGetLastError());
+  kv->uniform = false;
+  kv->h_offs_valid = false;
+}
+
+// Prepare `kv` to receive nnew uniform records (kb, vb); returns the byte offset where they go.
+// Keeps the KV uniform when possible, otherwise extends the offset index.
+static uint64_t kv_append_uniform(mrgpu_mr *mr, DevKV *kv, uint32_t kb, uint32_t vb, uint64_t nnew)
+{
+  uint32_t rs = kv_rec_size(mr->al, kb, vb);
+  if (rs > mr->pagesize) MR_FAIL(MRGPU_ELIMIT, "Single key/value pair exceeds page size");
+  uint64_t base = kv->nbytes;
+  bool fits = kv->nkv == 0 ? true : (kv->uniform && kv->kb == kb && kv->vb == vb);
+  if (kv->nkv == 0 && !kv->uniform && nnew) kv->uniform = true;  // empty general KV can become uniform again
+  if (fits) {
+    kv->uniform = true;
+    kv->kb = kb;
+    kv->vb = vb;
+    kv->recsize = rs;
+  } else {
+    kv_make_general(mr, kv);
+    kv->reserve_offs(kv->nkv + nnew + 1);
+    uint64_t *o = kv->offs + kv->nkv;
+    uint64_t cnt = nnew + 1;
+    affine_offsets_kernel<<<(unsigned) ((cnt + 255) / 256), 256, 0, mr->pool.stream>>>(o, cnt, base, rs);
+    MR_CUDA(cudaGetLastError());
+  }
+  kv->reserve_bytes(base + nnew * rs);
+  kv->h_offs_valid = false;
+  return base;
+}
+
+static void kv_commit_uniform(DevKV *kv, uint32_t kb, uint32_t vb, uint32_t rs, uint64_t nnew)
+{
+  kv->nbytes += nnew * rs;
+  kv->nkv += nnew;
+  kv->ksize += nnew * kb;
+  kv->vsize += nnew * vb;
+}
+
+// stage host input on the device (inside the call, so e2e timings include the copy)
+template <typename T>
+static const T *stage_input(mrgpu_mr *mr, const T *p, uint64_t n, Buf<T> &tmp)
+{
+  if (n == 0 || is_device_ptr(p)) return p;
+  tmp.alloc(mr->pool, n);
+  MR_CUDA(cudaMemcpyAsync(tmp.p, p, n * sizeof(T), cudaMemcpyHostToDevice, mr->pool.stream));
+  return tmp.p;
+}
+
+// ---------------------------------------------------------------------------------------------
+// IntCount emit: cpu/IntCount.cpp:177-180   kv->add(text+i*4, 4, (char*)&one, 4)
+
+// default alignment: the record is exactly one 16-byte vector {4, 4, key, 1}
+__global__ void __launch_bounds__(256) intcount_emit16_kernel(const uint32_t *__restrict__ keys, uint64_t n, int4 *__restrict__ out)
+{
+  constexpr int U = 4;
+  uint64_t stride = (uint64_t) gridDim.x * blockDim.x * U;
+  for (uint64_t base = (uint64_t) blockIdx.x * blockDim.x * U + threadIdx.x; base < n; base += stride) {
+    uint32_t k[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      uint64_t i = base + (uint64_t) u * blockDim.x;
+      k[u] = (i < n) ? __ldg(keys + i) : 0;
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      uint64_t i = base + (uint64_t) u * blockDim.x;
+      if (i < n) st_stream(out + i, make_int4(4, 4, (int) k[u], 1));
+    }
+  }
+}
+
+// any alignment: word-wise stores, padding zeroed
+__global__ void intcount_emit_generic_kernel(const uint32_t *__restrict__ keys, uint64_t n, uint8_t *out, Align al, uint32_t rs)
+{
+  uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t *r = (uint32_t *) (out + i * rs);
+  for (uint32_t w = 0; w < rs / 4; w++) r[w] = 0;
+  r[0] = 4;
+  r[1] = 4;
+  r[kv_key_off(al) / 4] = keys[i];
+  r[kv_val_off(al, 4) / 4] = 1;
+}
+
+extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n, int addflag, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (n && !keys) MR_FAIL(MRGPU_EINVAL, "null input");
+  kv_begin_map(mr, addflag);
+  DevKV *kv = mr->kv;
+  Buf<uint32_t> tmp;
+  const uint32_t *dk = stage_input(mr, keys, n, tmp);
+  uint64_t base = kv_append_uniform(mr, kv, 4, 4, n);
+  uint32_t rs = kv_rec_size(mr->al, 4, 4);
+  if (n) {
+    if (rs == 16 && kv_key_off(mr->al) == 8 && (base & 15) == 0)
+      intcount_emit16_kernel<<<grid_for(n, 256 * 4, 16), 256, 0, mr->pool.stream>>>(dk, n, (int4 *) (kv->data + base));
+    else
+      intcount_emit_generic_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, mr->pool.stream>>>(dk, n, kv->data + base, mr->al, rs);
+    MR_CUDA(cudaGetLastError());
+  }
+  kv_commit_uniform(kv, 4, 4, rs, n);
+  tmp.release();
+  if (nkv) {
+    sync(mr);
+    *nkv = allreduce_sum(mr, kv->nkv);
+  }
+  API_END(mr)
+}
+
+// ---------------------------------------------------------------------------------------------
+// map(mr, edge_to_vertices | edge_to_vertex | invert)   src/mapreduce.cpp:1560-1642
+
+__device__ __forceinline__ uint64_t rec_off(const uint64_t *offs, uint64_t recsize, uint64_t i) { return offs ? offs[i] : i * recsize; }
+
+// key = first (and second) u64 of the source key, value = NULL: oink/map_edge_to_vertices.cpp:14-20
+__global__ void __launch_bounds__(256)
+edge_to_vertices_kernel(const uint8_t *__restrict__ src, const uint64_t *__restrict__ offs, uint64_t recsize, uint32_t koff, uint64_t n,
+                        int both, uint8_t *__restrict__ dst, uint32_t out_rs, uint32_t out_koff)
+{
+  uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint8_t *r = src + rec_off(offs, recsize, i) + koff;
+  uint32_t w[4];
+  w[0] = ((const uint32_t *) r)[0];
+  w[1] = ((const uint32_t *) r)[1];
+  if (both) {
+    w[2] = ((const uint32_t *) r)[2];
+    w[3] = ((const uint32_t *) r)[3];
+  }
+  int nout = both ? 2 : 1;
+  for (int e = 0; e < nout; e++) {
+    uint32_t *o = (uint32_t *) (dst + (i * nout + e) * out_rs);
+    if (out_rs == 16 && out_koff == 8) {
+      *(int4 *) o = make_int4(8, 0, (int) w[2 * e], (int) w[2 * e + 1]);
+    } else {
+      for (uint32_t q = 0; q < out_rs / 4; q++) o[q] = 0;
+      o[0] = 8;
+      o[1] = 0;
+      o[out_koff / 4] = w[2 * e];
+      o[out_koff / 4 + 1] = w[2 * e + 1];
+    }
+  }
+}
+
+// invert: key <-> value, oink/map_invert.cpp:11-15; byte-wise copy, one thread per record
+__global__ void invert_kernel(const uint8_t *__restrict__ src, const uint64_t *__restrict__ soffs, uint64_t srs, uint64_t n,
+                              uint8_t *__restrict__ dst, const uint64_t *__restrict__ doffs, uint64_t drs, Align al)
+{
+  uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint8_t *r = src + rec_off(soffs, srs, i);
+  uint32_t kb = ((const uint32_t *) r)[0], vb = ((const uint32_t *) r)[1];
+  const uint8_t *k = r + kv_key_off(al), *v = r + kv_val_off(al, kb);
+  uint8_t *o = dst + rec_off(doffs, drs, i);
+  uint32_t sz = kv_rec_size(al, vb, kb);
+  for (uint32_t q = 0; q < sz / 4; q++) ((uint32_t *) o)[q] = 0;
+  ((uint32_t *) o)[0] = vb;
+  ((uint32_t *) o)[1] = kb;
+  uint8_t *ok = o + kv_key_off(al), *ov = o + kv_val_off(al, vb);
+  for (uint32_t q = 0; q < vb; q++) ok[q] = v[q];
+  for (uint32_t q = 0; q < kb; q++) ov[q] = k[q];
+}
+
+extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addflag, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!srcmr) MR_FAIL(MRGPU_EINVAL, "null source");
+  if (!srcmr->kv) MR_FAIL(MRGPU_ENOKV, "MapReduce passed to map() does not have KeyValue pairs");
+  if (srcmr->device != mr->device) MR_FAIL(MRGPU_EINVAL, "source and destination live on different devices");
+  freeze(mr);
+  freeze(srcmr);
+  // src == dst: the reference detaches the old KV, builds the new one, then deletes the old (:1584-1602, 1634)
+  DevKV *src = srcmr->kv;
+  bool self = (srcmr == mr);
+  if (self) mr->kv = nullptr;
+  try {
+    kv_begin_map(mr, self ? 0 : addflag);
+    DevKV *kv = mr->kv;
+    const Align al = mr->al;
+    const uint64_t n = src->nkv;
+    cudaStream_t s = mr->pool.stream;
+    if (functor == MRGPU_MAP_EDGE_TO_VERTICES || functor == MRGPU_MAP_EDGE_TO_VERTEX) {
+      int both = functor == MRGPU_MAP_EDGE_TO_VERTICES;
+      uint32_t need = both ? 16 : 8;
+      if (n && src->uniform && src->kb < need) MR_FAIL(MRGPU_EINVAL, "edge_to_vertices: source keys are shorter than an EDGE");
+      if (n && (srcmr->al.k % 4)) MR_FAIL(MRGPU_EINVAL, "edge_to_vertices needs keyalign >= 4");
+      uint64_t nout = n * (both ? 2 : 1);
+      uint64_t base = kv_append_uniform(mr, kv, 8, 0, nout);
+      uint32_t rs = kv_rec_size(al, 8, 0);
+      if (n) {
+        edge_to_vertices_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(src->data, src->uniform ? nullptr : src->offs, src->recsize,
+                                                                           kv_key_off(srcmr->al), n, both, kv->data + base, rs,
+                                                                           kv_key_off(al));
+        MR_CUDA(cudaGetLastError());
+      }
+      kv_commit_uniform(kv, 8, 0, rs, nout);
+    } else if (functor == MRGPU_MAP_INVERT) {
+      if (srcmr->al.k != al.k || srcmr->al.v != al.v) MR_FAIL(MRGPU_EINVAL, "invert: alignments differ");
+      if (src->uniform || n == 0) {
+        uint64_t base = kv_append_uniform(mr, kv, src->vb, src->kb, n);
+        uint32_t rs = kv_rec_size(al, src->vb, src->kb);
+        if (n) {
+          invert_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(src->data, nullptr, src->recsize, n, kv->data + base, nullptr, rs, al);
+          MR_CUDA(cudaGetLastError());
+        }
+        kv_commit_uniform(kv, src->vb, src->kb, rs, n);
+      } else {
+        // sizes -> scan -> write
+        kv_make_general(mr, kv);
+        kv->reserve_offs(kv->nkv + n + 1);
+        const uint8_t *sd = src->data;
+        const uint64_t *so = src->offs;
+        uint64_t *doffs = kv->offs + kv->nkv;
+        uint64_t base = kv->nbytes;
+        scan_apply(
+            mr->pool, n,
+            [=] __device__(uint64_t i) -> unsigned long long {
+              const uint32_t *r = (const uint32_t *) (sd + so[i]);
+              return kv_rec_size(al, r[1], r[0]);
+            },
+            [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { doffs[i] = base + e; }, mr->d_small);
+        fetch_small(mr, 1);
+        uint64_t total = mr->h_small[0];
+        uint64_t end = base + total;
+        MR_CUDA(cudaMemcpyAsync(doffs + n, &end, 8, cudaMemcpyHostToDevice, s));
+        kv->reserve_bytes(end);
+        invert_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(src->data, src->offs, 0, n, kv->data, doffs, 0, al);
+        MR_CUDA(cudaGetLastError());
+        sync(mr);
+        kv->nbytes = end;
+        kv->nkv += n;
+        kv->ksize += src->vsize;
+        kv->vsize += src->ksize;
+        kv->h_offs_valid = false;
+      }
+    } else
+      MR_FAIL(MRGPU_EINVAL, "unknown map functor");
+  } catch (...) {
+    if (self) delete src;
+    throw;
+  }
+  if (self) delete src;
+  if (nkv) {
+    sync(mr);
+    *nkv = allreduce_sum(mr, mr->kv->nkv);
+  }
+  API_END(mr)
+}
+
+// ---------------------------------------------------------------------------------------------
+// R-MAT edge generator: oink/map_rmat_generate.cpp:14-67 with glibc drand48 restated
+//   X' = (0x5DEECE66D X + 0xB) mod 2^48, value = X' / 2^48.
+// The reference draws sequentially from one per-rank stream; edge m consumes draws
+// [m*D, (m+1)*D) with D = nlevels (fraction == 0) or 5*nlevels, so thread m jumps the LCG ahead by m*D
+// steps in O(log) multiplications and then replays exactly the reference's arithmetic.  Double adds and
+// compares only when fraction == 0; for fraction > 0 every multiply/add goes through the round-to-nearest
+// intrinsics so that no FMA contraction changes a bit.
+
+constexpr unsigned long long LCG_A = 0x5DEECE66Dull, LCG_C = 0xBull, LCG_M = (1ull << 48) - 1;
+
+__host__ __device__ inline void lcg_jump(unsigned long long k, unsigned long long &x)
+{
+  unsigned long long ra = 1, rc = 0, ba = LCG_A, bc = LCG_C;
+  while (k) {
+    if (k & 1) {
+      ra = (ba * ra) & LCG_M;
+      rc = (ba * rc + bc) & LCG_M;
+    }
+    bc = (ba * bc + bc) & LCG_M;
+    ba = (ba * ba) & LCG_M;
+    k >>= 1;
+  }
+  x = (ra * x + rc) & LCG_M;
+}
+
+__device__ __forceinline__ double lcg_next(unsigned long long &x)
+{
+  x = (LCG_A * x + LCG_C) & LCG_M;
+  return (double) (long long) x * (1.0 / 281474976710656.0);
+}
+
+struct RmatParams {
+  unsigned long long order;
+  int nlevels;
+  double a, b, c, d, fraction;
+};
+
+__global__ void __launch_bounds__(256)
+rmat_generate_kernel(RmatParams p, unsigned long long state0, uint64_t ngenerate, uint8_t *out, uint32_t rs, uint32_t koff, bool fast)
+{
+  uint64_t m = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= ngenerate) return;
+  const int D = p.fraction > 0.0 ? 5 * p.nlevels : p.nlevels;
+  unsigned long long x = state0;
+  lcg_jump(m * (unsigned long long) D, x);
+  unsigned long long delta = p.order >> 1, i = 0, j = 0;
+  double a1 = p.a, b1 = p.b, c1 = p.c, d1 = p.d;
+  for (int l = 0; l < p.nlevels; l++) {
+    double rn = lcg_next(x);
+    double ab = __dadd_rn(a1, b1);
+    if (rn < a1) {
+    } else if (rn < ab) {
+      j += delta;
+    } else if (rn < __dadd_rn(ab, c1)) {
+      i += delta;
+    } else {
+      i += delta;
+      j += delta;
+    }
+    delta >>= 1;
+    if (p.fraction > 0.0) {
+      // a1 += a1*fraction * (drand48() - 0.5): ((a1*fraction) * (r-0.5)) then add, left to right as in C
+      a1 = __dadd_rn(a1, __dmul_rn(__dmul_rn(a1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
+      b1 = __dadd_rn(b1, __dmul_rn(__dmul_rn(b1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
+      c1 = __dadd_rn(c1, __dmul_rn(__dmul_rn(c1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
+      d1 = __dadd_rn(d1, __dmul_rn(__dmul_rn(d1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
+      double total = __dadd_rn(__dadd_rn(__dadd_rn(a1, b1), c1), d1);
+      a1 = __ddiv_rn(a1, total);
+      b1 = __ddiv_rn(b1, total);
+      c1 = __ddiv_rn(c1, total);
+      d1 = __ddiv_rn(d1, total);
+    }
+  }
+  uint32_t *r = (uint32_t *) (out + m * rs);
+  if (fast) {
+    // 24-byte record = three 8-byte stores (records are 8-byte aligned)
+    ((uint2 *) r)[0] = make_uint2(16, 0);
+    ((unsigned long long *) r)[1] = i;
+    ((unsigned long long *) r)[2] = j;
+  } else {
+    for (uint32_t q = 0; q < rs / 4; q++) r[q] = 0;
+    r[0] = 16;
+    r[1] = 0;
+    r[koff / 4] = (uint32_t) i;
+    r[koff / 4 + 1] = (uint32_t) (i >> 32);
+    r[koff / 4 + 2] = (uint32_t) j;
+    r[koff / 4 + 3] = (uint32_t) (j >> 32);
+  }
+}
+
+extern "C" int mrgpu_map_rmat(mrgpu_mr *mr, uint64_t ngenerate, int nlevels, double a, double b, double c, double d, double fraction,
+                              uint64_t *state48, int addflag, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!state48) MR_FAIL(MRGPU_EINVAL, "null state");
+  if (nlevels < 1 || nlevels > 62) MR_FAIL(MRGPU_EINVAL, "Illegal rmat command");
+  if (fraction >= 1.0) MR_FAIL(MRGPU_EINVAL, "RMAT fraction must be < 1");
+  kv_begin_map(mr, addflag);
+  DevKV *kv = mr->kv;
+  if (mr->al.k % 4) MR_FAIL(MRGPU_EINVAL, "rmat_generate needs keyalign >= 4");
+  uint64_t base = kv_append_uniform(mr, kv, 16, 0, ngenerate);
+  uint32_t rs = kv_rec_size(mr->al, 16, 0);
+  RmatParams p{1ull << nlevels, nlevels, a, b, c, d, fraction};
+  if (ngenerate) {
+    bool fast = rs == 24 && kv_key_off(mr->al) == 8 && (base % 8) == 0;
+    rmat_generate_kernel<<<(unsigned) ((ngenerate + 255) / 256), 256, 0, mr->pool.stream>>>(p, *state48 & LCG_M, ngenerate, kv->data + base,
+                                                                                         rs, kv_key_off(mr->al), fast);
+    MR_CUDA(cudaGetLastError());
+  }
+  kv_commit_uniform(kv, 16, 0, rs, ngenerate);
+  unsigned long long x = *state48 & LCG_M;
+  unsigned long long D = fraction > 0.0 ? 5ull * nlevels : (unsigned long long) nlevels;
+  lcg_jump(ngenerate * D, x);
+  *state48 = x;
+  if (nkv) {
+    sync(mr);
+    *nkv = allreduce_sum(mr, kv->nkv);
+  }
+  API_END(mr)
+}
+
+// ---------------------------------------------------------------------------------------------
+// MapReduce::add(MapReduce*) src/mapreduce.cpp:348-374: append the other object's KV to mine
+
+__global__ void shift_offsets_kernel(uint64_t *dst, const uint64_t *src, uint64_t n_plus_1, uint64_t delta)
+{
+  uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_plus_1) dst[i] = src[i] + delta;
+}
+
+extern "C" int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!other || !other->kv) MR_FAIL(MRGPU_ENOKV, "MapReduce passed to add() does not have KeyValue pairs");
+  if (mr == other) MR_FAIL(MRGPU_EINVAL, "Cannot add to self");
+  if (mr->kmv) MR_FAIL(MRGPU_EINVAL, "Cannot add to a MapReduce with KeyMultiValue pairs");  // :351-353
+  freeze(mr);
+  freeze(other);
+  if (mr->al.k != other->al.k || mr->al.v != other->al.v) MR_FAIL(MRGPU_EINVAL, "add: alignments differ");
+  if (!mr->kv) mr->kv = new DevKV(&mr->pool);
+  DevKV *kv = mr->kv, *o = other->kv;
+  cudaStream_t s = mr->pool.stream;
+  if (o->nkv) {
+    uint64_t base = kv->nbytes;
+    bool fits = o->uniform && (kv->nkv == 0 || (kv->uniform && kv->kb == o->kb && kv->vb == o->vb));
+    if (fits) {
+      kv_append_uniform(mr, kv, o->kb, o->vb, o->nkv);
+    } else {
+      kv_make_general(mr, kv);
+      kv->reserve_offs(kv->nkv + o->nkv + 1);
+      if (o->uniform) {
+        kv_append_uniform(mr, kv, o->kb, o->vb, o->nkv);  // general branch fills the offsets
+      } else {
+        shift_offsets_kernel<<<(unsigned) ((o->nkv + 1 + 255) / 256), 256, 0, s>>>(kv->offs + kv->nkv, o->offs, o->nkv + 1, base);
+        MR_CUDA(cudaGetLastError());
+        kv->reserve_bytes(base + o->nbytes);
+      }
+    }
+    MR_CUDA(cudaMemcpyAsync(kv->data + base, o->data, o->nbytes, cudaMemcpyDeviceToDevice, s));
+    kv->nbytes += o->nbytes;
+    kv->nkv += o->nkv;
+    kv->ksize += o->ksize;
+    kv->vsize += o->vsize;
+    kv->h_offs_valid = false;
+  }
+  sync(mr);
+  if (nkv) *nkv = allreduce_sum(mr, kv->nkv);
+  API_END(mr)
+}

@@ -1,0 +1,159 @@
+// reduce(): KeyMultiValue -> KeyValue with the stock callbacks as device functors.
+//
+// Reference: MapReduce::reduce src/mapreduce.cpp:1769-1867 walks the KMV pages, decodes each record and
+// calls myreduce(key,keybytes,multivalue,nvalues,valuebytes,kv,ptr); the callback emits with kv->add.
+//   count  oink/reduce_count.cpp:13-20   emit (key, int nvalues_total)      [multi-block aware]
+//   sum    examples/wordfreq.cpp:137-141 emit (key, int nvalues)
+//   cull   oink/reduce_cull.cpp:12-20    emit (key, first value)
+// Every one of them emits exactly one pair per KMV pair and needs only the KMV header (+ first value), so
+// the kernel is one thread per KMV pair reading the header through offs[u] and writing one KV record; the
+// multivalue bytes are never touched (less HBM traffic than the algorithmic KMV size).  Included by mrgpu.cu.
+#pragma once
+
+__device__ __forceinline__ void write_kv_record(uint8_t *dst, Align al, uint32_t kb, const uint8_t *key, uint32_t vb, const uint8_t *val)
+{
+  uint32_t ko = kv_key_off(al), vo = kv_val_off(al, kb), end = kv_rec_size(al, kb, vb);
+  ((uint32_t *) dst)[0] = kb;
+  ((uint32_t *) dst)[1] = vb;
+  for (uint32_t q = 8; q < ko; q++) dst[q] = 0;
+  for (uint32_t q = 0; q < kb; q++) dst[ko + q] = key[q];
+  for (uint32_t q = ko + kb; q < vo; q++) dst[q] = 0;
+  for (uint32_t q = 0; q < vb; q++) dst[vo + q] = val[q];
+  for (uint32_t q = vo + vb; q < end; q++) dst[q] = 0;
+}
+
+struct KmvHead {
+  uint32_t nv, kb, mvb;
+  const uint8_t *key, *sizes, *values;
+};
+
+__device__ __forceinline__ KmvHead kmv_head(const uint8_t *rec, Align al)
+{
+  KmvHead h;
+  const uint32_t *w = (const uint32_t *) rec;
+  h.nv = w[0];
+  h.kb = w[1];
+  h.mvb = w[2];
+  h.sizes = rec + 12;
+  h.key = rec + kmv_key_off(al, h.nv);
+  h.values = rec + kmv_val_off(al, h.nv, h.kb);
+  return h;
+}
+
+// output value of functor f for a KMV pair: count/sum -> the int nvalue; cull -> first value
+__device__ __forceinline__ uint32_t reduce_out_vb(int functor, const KmvHead &h)
+{
+  if (functor == MRGPU_REDUCE_CULL) return *(const uint32_t *) h.sizes;
+  return 4;
+}
+
+// fast path: 4-byte keys, default alignment, count/sum -> one 16-byte store per pair
+__global__ void __launch_bounds__(256)
+reduce_count16_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restrict__ offs, uint64_t U, int4 *__restrict__ out)
+{
+  uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= U) return;
+  const uint32_t *w = (const uint32_t *) (kmv + offs[u]);
+  uint32_t nv = w[0];
+  uint32_t key = w[3 + nv];  // key follows the nv value sizes (kalign 4)
+  st_stream(out + u, make_int4(4, 4, (int) key, (int) nv));
+}
+
+__global__ void __launch_bounds__(256)
+reduce_generic_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restrict__ offs, uint64_t U, int functor, Align al, uint8_t *out,
+                      const uint64_t *__restrict__ ooffs, uint64_t ors)
+{
+  uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= U) return;
+  KmvHead h = kmv_head(kmv + offs[u], al);
+  uint8_t *dst = out + (ooffs ? ooffs[u] : u * ors);
+  if (functor == MRGPU_REDUCE_CULL) {
+    write_kv_record(dst, al, h.kb, h.key, *(const uint32_t *) h.sizes, h.values);
+  } else {
+    uint32_t cnt = h.nv;
+    write_kv_record(dst, al, h.kb, h.key, 4, (const uint8_t *) &cnt);
+  }
+}
+
+static void reduce_impl(mrgpu_mr *mr, int functor)
+{
+  if (functor < 0 || functor > MRGPU_REDUCE_CULL) MR_FAIL(MRGPU_EINVAL, "unknown reduce functor");
+  DevKMV *kmv = mr->kmv;
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const Align al = mr->al;
+  const uint64_t U = kmv->nkmv;
+  DevKV *kv = new DevKV(&pool);
+  try {
+    const uint8_t *kd = kmv->data;
+    const uint64_t *ko = kmv->offs;
+    bool cull = functor == MRGPU_REDUCE_CULL;
+    bool uni = kmv->ukb >= 0 && (!cull || kmv->uvb >= 0);
+    if (U == 0) {
+      // empty KV
+    } else if (uni) {
+      uint32_t kb = (uint32_t) kmv->ukb, vb = cull ? (uint32_t) kmv->uvb : 4;
+      uint32_t rs = kv_rec_size(al, kb, vb);
+      kv->reserve_bytes(U * rs);
+      if (!cull && kb == 4 && rs == 16 && kv_key_off(al) == 8 && al.k == 4)
+        reduce_count16_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, (int4 *) kv->data);
+      else
+        reduce_generic_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, functor, al, kv->data, nullptr, rs);
+      MR_CUDA(cudaGetLastError());
+      kv->uniform = true;
+      kv->kb = kb;
+      kv->vb = vb;
+      kv->recsize = rs;
+      kv->nbytes = U * rs;
+      kv->nkv = U;
+      kv->ksize = U * kb;
+      kv->vsize = U * vb;
+    } else {
+      kv->uniform = false;
+      kv->reserve_offs(U + 1);
+      uint64_t *oo = kv->offs;
+      unsigned long long *vsum = mr->d_small + 1;
+      MR_CUDA(cudaMemsetAsync(vsum, 0, 8, s));
+      scan_apply(
+          pool, U,
+          [=] __device__(uint64_t u) -> unsigned long long {
+            KmvHead h = kmv_head(kd + ko[u], al);
+            return kv_rec_size(al, h.kb, reduce_out_vb(functor, h));
+          },
+          [=] __device__(uint64_t u, unsigned long long e, unsigned long long) {
+            oo[u] = e;
+            KmvHead h = kmv_head(kd + ko[u], al);
+            warp_add(vsum, reduce_out_vb(functor, h));
+          },
+          mr->d_small);
+      fetch_small(mr, 2);
+      uint64_t total = mr->h_small[0];
+      MR_CUDA(cudaMemcpyAsync(oo + U, &total, 8, cudaMemcpyHostToDevice, s));
+      kv->reserve_bytes(total);
+      reduce_generic_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, functor, al, kv->data, oo, 0);
+      MR_CUDA(cudaGetLastError());
+      kv->nbytes = total;
+      kv->nkv = U;
+      kv->ksize = kmv->ksize;
+      kv->vsize = mr->h_small[1];
+    }
+    sync(mr);
+  } catch (...) {
+    delete kv;
+    throw;
+  }
+  // reduce consumes the KMV (src/mapreduce.cpp:1853-1855)
+  delete mr->kmv;
+  mr->kmv = nullptr;
+  delete mr->kv;
+  mr->kv = kv;
+}
+
+extern "C" int mrgpu_reduce(mrgpu_mr *mr, int functor, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "Cannot reduce without KeyMultiValue");
+  reduce_impl(mr, functor);
+  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  API_END(mr)
+}

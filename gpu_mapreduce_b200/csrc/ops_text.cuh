@@ -1,0 +1,352 @@
+// Text map functors: the wordfreq tokenizer and the InvertedIndex href scanner.
+//
+// Both reference callbacks are sequential byte loops on the CPU (strtok in examples/wordfreq.cpp:104-130,
+// a 5-state switch with look-ahead in cpu/InvertedIndex.cpp:196-270) that call KeyValue::add per hit.  On
+// the GPU each becomes: classify bytes in parallel -> prefix sums give every hit its output slot ->
+// coalesced pack into KV records.  The fork's own GPU attempt (cuda/InvertedIndex.cu: `mark` +
+// thrust::copy_if + compute_url_length + a host kv->add loop) is NOT what is done here: it matches only the
+// literal `<a href="`, writes a 4-byte mask per input byte and packs records on the host.
+// Included by mrgpu.cu.
+#pragma once
+
+// ---------------------------------------------------------------------------------------------
+// shared: append variable-length records to a KV
+
+struct VarAppend {
+  uint64_t base;     // byte offset of the first new record
+  uint64_t *offs;    // device: offs for the new records (kv->offs + old nkv)
+};
+
+static VarAppend kv_append_var_begin(mrgpu_mr *mr, DevKV *kv, uint64_t nnew)
+{
+  kv_make_general(mr, kv);
+  kv->reserve_offs(kv->nkv + nnew + 1);
+  kv->h_offs_valid = false;
+  return VarAppend{kv->nbytes, kv->offs + kv->nkv};
+}
+
+// after offs[0..nnew) hold base + exclusive sizes and `total` bytes were computed
+static void kv_append_var_reserve(mrgpu_mr *mr, DevKV *kv, const VarAppend &va, uint64_t nnew, uint64_t total)
+{
+  uint64_t end = va.base + total;
+  MR_CUDA(cudaMemcpyAsync(va.offs + nnew, &end, 8, cudaMemcpyHostToDevice, mr->pool.stream));
+  kv->reserve_bytes(end);
+  sync(mr);  // `end` is a stack variable
+}
+
+// ---------------------------------------------------------------------------------------------
+// wordfreq tokenizer, examples/wordfreq.cpp:104-130
+//   text[nchar] = 0; strtok(text, " \t\n\f\r") ...  kv->add(word, strlen(word)+1, NULL, 0)
+// strtok stops at the first NUL, so the effective text is [0, first NUL).
+
+__device__ __forceinline__ bool tok_ws(uint8_t c) { return c == ' ' || c == '\t' || c == '\n' || c == '\f' || c == '\r'; }
+
+__global__ void first_nul_kernel(const uint8_t *__restrict__ t, uint64_t n, unsigned long long *pos)
+{
+  uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  unsigned long long best = ~0ull;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    if (t[i] == 0) {
+      best = i;
+      break;
+    }
+  for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+  if ((threadIdx.x & 31) == 0 && best != ~0ull) atomicMin(pos, best);
+}
+
+__global__ void __launch_bounds__(256)
+tokenize_write_kernel(const uint8_t *__restrict__ t, const uint32_t *__restrict__ starts, const uint32_t *__restrict__ ends, uint64_t nw,
+                      uint8_t *__restrict__ out, const uint64_t *__restrict__ offs, Align al)
+{
+  uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nw) return;
+  uint32_t s = starts[j], len = ends[j] - s, kb = len + 1;
+  uint8_t *r = out + offs[j];
+  uint32_t ko = kv_key_off(al), end = kv_rec_size(al, kb, 0);
+  ((uint32_t *) r)[0] = kb;
+  ((uint32_t *) r)[1] = 0;
+  for (uint32_t q = 8; q < ko; q++) r[q] = 0;
+  for (uint32_t q = 0; q < len; q++) r[ko + q] = t[s + q];
+  for (uint32_t q = ko + len; q < end; q++) r[q] = 0;  // the NUL and the padding
+}
+
+extern "C" int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbytes, int addflag, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (nbytes && !text) MR_FAIL(MRGPU_EINVAL, "null input");
+  if (nbytes >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "map_tokenize: one call handles a file below 4 GiB (the reference reads int filesize)");
+  kv_begin_map(mr, addflag);
+  DevKV *kv = mr->kv;
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const Align al = mr->al;
+  Buf<uint8_t> tmp;
+  const uint8_t *t = stage_input(mr, (const uint8_t *) text, nbytes, tmp);
+  uint64_t nwords = 0;
+  if (nbytes) {
+    unsigned long long *d = mr->d_small;
+    MR_CUDA(cudaMemsetAsync(d, 0xFF, 8, s));
+    first_nul_kernel<<<grid_for(nbytes, 256 * 16, 8), 256, 0, s>>>(t, nbytes, d);
+    MR_CUDA(cudaGetLastError());
+    fetch_small(mr, 1);
+    const uint64_t end = std::min<uint64_t>(mr->h_small[0], nbytes);
+    auto isstart = [=] __device__(uint64_t i) -> unsigned long long { return (!tok_ws(t[i]) && (i == 0 || tok_ws(t[i - 1]))) ? 1ull : 0ull; };
+    ScanTiles st;
+    scan_tiles(pool, end, isstart, st, mr->d_small);
+    fetch_small(mr, 1);
+    nwords = mr->h_small[0];
+    if (nwords) {
+      Buf<uint32_t> starts(pool, nwords), ends(pool, nwords);
+      uint32_t *ps = starts.p, *pe = ends.p;
+      scan_sink(pool, st, isstart, [=] __device__(uint64_t i, unsigned long long e, unsigned long long v) {
+        if (v) ps[e] = (uint32_t) i;
+        if (!tok_ws(t[i]) && (i + 1 == end || tok_ws(t[i + 1]))) pe[e + v - 1] = (uint32_t) (i + 1);
+      });
+      VarAppend va = kv_append_var_begin(mr, kv, nwords);
+      uint64_t *oo = va.offs;
+      uint64_t base = va.base;
+      unsigned long long *ksum = mr->d_small + 1;
+      MR_CUDA(cudaMemsetAsync(ksum, 0, 8, s));
+      scan_apply(
+          pool, nwords, [=] __device__(uint64_t j) -> unsigned long long { return kv_rec_size(al, pe[j] - ps[j] + 1, 0); },
+          [=] __device__(uint64_t j, unsigned long long e, unsigned long long) {
+            oo[j] = base + e;
+            warp_add(ksum, (unsigned long long) (pe[j] - ps[j] + 1));
+          },
+          mr->d_small);
+      fetch_small(mr, 2);
+      uint64_t total = mr->h_small[0], ksize = mr->h_small[1];
+      kv_append_var_reserve(mr, kv, va, nwords, total);
+      tokenize_write_kernel<<<(unsigned) ((nwords + 255) / 256), 256, 0, s>>>(t, ps, pe, nwords, kv->data, kv->offs + kv->nkv, al);
+      MR_CUDA(cudaGetLastError());
+      kv->nbytes = va.base + total;
+      kv->nkv += nwords;
+      kv->ksize += ksize;
+      sync(mr);
+    }
+  }
+  tmp.release();
+  sync(mr);
+  if (nkv) *nkv = allreduce_sum(mr, kv->nkv);
+  API_END(mr)
+}
+
+// ---------------------------------------------------------------------------------------------
+// InvertedIndex href scanner, cpu/InvertedIndex.cpp:196-270
+//
+// The reference's switch has 5 states plus a 4-byte look-ahead ("href" peeked at the 'h', then j += 3) and
+// an inner loop that runs to the closing quote.  Made explicit it is an 8-state DFA without look-ahead
+// (verified against the verbatim reference code): START, TAG, ATAG, H1, H2, H3, HREF, LINK.
+// A DFA over bytes parallelises as a prefix "sum" of per-byte transition functions under composition:
+// a function on 8 states packs into 24 bits.  Pass 1 composes each thread's chunk and each block; a tiny
+// sequential pass threads the state through the blocks; pass 2 re-walks every chunk from its now-known
+// start state and counts LINK entries / exits; a prefix sum places them; pass 3 writes their positions.
+// URL k = text[entry_k, exit_k): entries and exits alternate, so the k-th of each pair up.
+
+enum { HS_START, HS_TAG, HS_ATAG, HS_H1, HS_H2, HS_H3, HS_HREF, HS_LINK };
+
+static inline int href_start_on(int c) { return c == '<' ? HS_TAG : HS_START; }
+
+static inline int href_step(int st, int c)
+{
+  switch (st) {
+    case HS_START: return href_start_on(c);
+    case HS_TAG: return c == 'a' ? HS_ATAG : (c == ' ' ? HS_TAG : HS_START);     // cpu/InvertedIndex.cpp:211-221
+    case HS_ATAG: return c == 'h' ? HS_H1 : (c == ' ' ? HS_ATAG : HS_START);      // :222-243
+    case HS_H1: return c == 'r' ? HS_H2 : href_start_on(c);                       // failed peek: START at the 'h',
+    case HS_H2: return c == 'e' ? HS_H3 : href_start_on(c);                       // then these bytes are rescanned
+    case HS_H3: return c == 'f' ? HS_HREF : href_start_on(c);                     // from START
+    case HS_HREF: return (c == ' ' || c == '=') ? HS_HREF : (c == '"' ? HS_LINK : HS_START);  // :244-253
+    default: return c == '"' ? HS_START : HS_LINK;                                // :254-267
+  }
+}
+
+__constant__ uint32_t c_href_trans[256];  // packed transition function per byte value
+constexpr uint32_t HREF_IDENT = 0 | (1 << 3) | (2 << 6) | (3 << 9) | (4 << 12) | (5 << 15) | (6 << 18) | (7 << 21);
+constexpr int HREF_CHUNK = 32;  // bytes per thread
+
+static void href_upload_table()
+{
+  static bool done[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 64 && done[dev]) return;
+  uint32_t tab[256];
+  for (int c = 0; c < 256; c++) {
+    uint32_t f = 0;
+    for (int st = 0; st < 8; st++) f |= (uint32_t) href_step(st, c) << (3 * st);
+    tab[c] = f;
+  }
+  MR_CUDA(cudaMemcpyToSymbol(c_href_trans, tab, sizeof(tab)));
+  if (dev < 64) done[dev] = true;
+}
+
+// h = g after f
+__device__ __forceinline__ uint32_t href_compose(uint32_t f, uint32_t g)
+{
+  uint32_t h = 0;
+#pragma unroll
+  for (int st = 0; st < 8; st++) h |= ((g >> (3 * ((f >> (3 * st)) & 7))) & 7) << (3 * st);
+  return h;
+}
+
+__global__ void __launch_bounds__(256)
+href_compose_kernel(const uint8_t *__restrict__ t, uint64_t n, uint32_t *__restrict__ tfun /*exclusive prefix per thread-chunk*/,
+                    uint32_t *__restrict__ bfun /*per block*/)
+{
+  __shared__ uint32_t sh[256];
+  uint64_t c0 = ((uint64_t) blockIdx.x * 256 + threadIdx.x) * HREF_CHUNK;
+  uint32_t f = HREF_IDENT;
+  for (int q = 0; q < HREF_CHUNK; q++) {
+    uint64_t i = c0 + q;
+    if (i < n) f = href_compose(f, c_href_trans[t[i]]);
+  }
+  // inclusive scan under composition (Hillis-Steele in shared memory; order matters: earlier first)
+  sh[threadIdx.x] = f;
+  __syncthreads();
+  for (int o = 1; o < 256; o <<= 1) {
+    uint32_t mine = sh[threadIdx.x], prev = threadIdx.x >= o ? sh[threadIdx.x - o] : HREF_IDENT;
+    __syncthreads();
+    sh[threadIdx.x] = href_compose(prev, mine);
+    __syncthreads();
+  }
+  tfun[(uint64_t) blockIdx.x * 256 + threadIdx.x] = threadIdx.x ? sh[threadIdx.x - 1] : HREF_IDENT;
+  if (threadIdx.x == 255) bfun[blockIdx.x] = sh[255];
+}
+
+// thread the state through the blocks: bstate[b] = state at the first byte of block b
+__global__ void href_blockstate_kernel(const uint32_t *__restrict__ bfun, uint64_t nblocks, uint8_t *__restrict__ bstate)
+{
+  __shared__ uint32_t sh[1024];
+  int st = HS_START;
+  for (uint64_t base = 0; base < nblocks; base += 1024) {
+    uint64_t i = base + threadIdx.x;
+    sh[threadIdx.x] = i < nblocks ? bfun[i] : HREF_IDENT;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint64_t m = nblocks - base < 1024 ? nblocks - base : 1024;
+      for (uint64_t q = 0; q < m; q++) {
+        bstate[base + q] = (uint8_t) st;
+        st = (sh[q] >> (3 * st)) & 7;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// walk one chunk from state st; calls on_entry(pos of first URL byte) / on_exit(pos of closing quote)
+template <typename FE, typename FX>
+__device__ __forceinline__ void href_walk(const uint8_t *__restrict__ t, uint64_t n, uint64_t c0, int st, FE on_entry, FX on_exit)
+{
+  for (int q = 0; q < HREF_CHUNK; q++) {
+    uint64_t i = c0 + q;
+    if (i >= n) break;
+    int nx = (c_href_trans[t[i]] >> (3 * st)) & 7;
+    if (st == HS_HREF && nx == HS_LINK) on_entry(i + 1);
+    if (st == HS_LINK && nx == HS_START) on_exit(i);
+    st = nx;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+href_count_kernel(const uint8_t *__restrict__ t, uint64_t n, const uint32_t *__restrict__ tfun, const uint8_t *__restrict__ bstate,
+                  uint8_t *__restrict__ tstate, unsigned long long *__restrict__ cnt)
+{
+  uint64_t g = (uint64_t) blockIdx.x * 256 + threadIdx.x;
+  int st = (tfun[g] >> (3 * bstate[blockIdx.x])) & 7;
+  tstate[g] = (uint8_t) st;
+  unsigned ne = 0, nx = 0;
+  href_walk(t, n, g * HREF_CHUNK, st, [&](uint64_t) { ne++; }, [&](uint64_t) { nx++; });
+  cnt[g] = ((unsigned long long) ne << 32) | nx;
+}
+
+__global__ void __launch_bounds__(256)
+href_write_kernel(const uint8_t *__restrict__ t, const uint32_t *__restrict__ entry, const uint32_t *__restrict__ exitp, uint64_t nurl,
+                  const uint8_t *__restrict__ fname, uint32_t fnb, uint8_t *__restrict__ out, const uint64_t *__restrict__ offs, Align al)
+{
+  uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nurl) return;
+  uint32_t s = entry[j], kb = exitp[j] - s;
+  uint8_t *r = out + offs[j];
+  uint32_t ko = kv_key_off(al), vo = kv_val_off(al, kb), end = kv_rec_size(al, kb, fnb);
+  ((uint32_t *) r)[0] = kb;
+  ((uint32_t *) r)[1] = fnb;
+  for (uint32_t q = 8; q < ko; q++) r[q] = 0;
+  for (uint32_t q = 0; q < kb; q++) r[ko + q] = t[s + q];
+  for (uint32_t q = ko + kb; q < vo; q++) r[q] = 0;
+  for (uint32_t q = 0; q < fnb; q++) r[vo + q] = fname[q];
+  for (uint32_t q = vo + fnb; q < end; q++) r[q] = 0;
+}
+
+extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, const char *fname, int addflag, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (nbytes && !text) MR_FAIL(MRGPU_EINVAL, "null input");
+  if (!fname) MR_FAIL(MRGPU_EINVAL, "null file name");
+  if (nbytes >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "map_href: one call handles a file below 4 GiB (the reference reads int filesize)");
+  kv_begin_map(mr, addflag);
+  DevKV *kv = mr->kv;
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const Align al = mr->al;
+  href_upload_table();
+  Buf<uint8_t> tmp;
+  const uint8_t *t = stage_input(mr, (const uint8_t *) text, nbytes, tmp);
+  const uint32_t fnb = (uint32_t) strlen(fname) + 1;  // value = file name with its NUL, cpu/InvertedIndex.cpp:262
+  if (nbytes) {
+    const uint64_t n = nbytes;
+    const uint64_t nblk = (n + 256 * HREF_CHUNK - 1) / (256 * HREF_CHUNK), nthr = nblk * 256;
+    Buf<uint32_t> tfun(pool, nthr), bfun(pool, nblk);
+    Buf<uint8_t> bstate(pool, nblk), tstate(pool, nthr);
+    Buf<unsigned long long> cnt(pool, nthr);
+    href_compose_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, tfun.p, bfun.p);
+    MR_CUDA(cudaGetLastError());
+    href_blockstate_kernel<<<1, 1024, 0, s>>>(bfun.p, nblk, bstate.p);
+    MR_CUDA(cudaGetLastError());
+    href_count_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, tfun.p, bstate.p, tstate.p, cnt.p);
+    MR_CUDA(cudaGetLastError());
+    const unsigned long long *pc = cnt.p;
+    auto val = [=] __device__(uint64_t g) -> unsigned long long { return pc[g]; };
+    ScanTiles st;
+    scan_tiles(pool, nthr, val, st, mr->d_small);
+    fetch_small(mr, 1);
+    const uint64_t nentry = mr->h_small[0] >> 32, nurl = mr->h_small[0] & 0xFFFFFFFFull;
+    if (nurl) {
+      Buf<uint32_t> entry(pool, nentry), exitp(pool, nurl);
+      uint32_t *pe = entry.p, *px = exitp.p;
+      const uint8_t *pts = tstate.p;
+      scan_sink(pool, st, val, [=] __device__(uint64_t g, unsigned long long e, unsigned long long) {
+        uint32_t ie = (uint32_t) (e >> 32), ix = (uint32_t) e;
+        href_walk(t, n, g * HREF_CHUNK, pts[g], [&](uint64_t p) { pe[ie++] = (uint32_t) p; }, [&](uint64_t p) { px[ix++] = (uint32_t) p; });
+      });
+      VarAppend va = kv_append_var_begin(mr, kv, nurl);
+      uint64_t *oo = va.offs;
+      uint64_t base = va.base;
+      unsigned long long *ksum = mr->d_small + 1;
+      MR_CUDA(cudaMemsetAsync(ksum, 0, 8, s));
+      scan_apply(
+          pool, nurl, [=] __device__(uint64_t j) -> unsigned long long { return kv_rec_size(al, px[j] - pe[j], fnb); },
+          [=] __device__(uint64_t j, unsigned long long e, unsigned long long) {
+            oo[j] = base + e;
+            warp_add(ksum, (unsigned long long) (px[j] - pe[j]));
+          },
+          mr->d_small);
+      fetch_small(mr, 2);
+      uint64_t total = mr->h_small[0], ksize = mr->h_small[1];
+      kv_append_var_reserve(mr, kv, va, nurl, total);
+      Buf<uint8_t> dname(pool, fnb);
+      MR_CUDA(cudaMemcpyAsync(dname.p, fname, fnb, cudaMemcpyHostToDevice, s));
+      href_write_kernel<<<(unsigned) ((nurl + 255) / 256), 256, 0, s>>>(t, pe, px, nurl, dname.p, fnb, kv->data, kv->offs + kv->nkv, al);
+      MR_CUDA(cudaGetLastError());
+      kv->nbytes = va.base + total;
+      kv->nkv += nurl;
+      kv->ksize += ksize;
+      kv->vsize += nurl * fnb;
+      sync(mr);
+    }
+  }
+  tmp.release();
+  sync(mr);
+  if (nkv) *nkv = allreduce_sum(mr, kv->nkv);
+  API_END(mr)
+}

@@ -1,0 +1,103 @@
+// HBM-resident KeyValue / KeyMultiValue stores and the per-handle state.
+//
+// Layout in HBM.  A KeyValue is ONE contiguous stream of records in the reference's own record layout
+// (int keybytes | int valuebytes | pad | key | pad | value | pad, src/keyvalue.cpp:345-390), i.e. the
+// concatenation of the reference's pages without their unused tails.  The reference's page boundaries
+// (greedy fill to `memsize`, src/keyvalue.cpp:362-380) are metadata computed on demand for the page
+// accessors; kernels see one stream.  Two things make the stream random-accessible without parsing:
+//   - "uniform" KVs (every record has the same keybytes/valuebytes -- IntCount, R-MAT edges, vertices):
+//     record i starts at i * recsize, nothing else is stored;
+//   - otherwise a u64 offset index offs[nkv+1] is kept beside the data.
+// A KeyMultiValue is likewise one stream of records (int nvalue | int keybytes | int mvaluebytes |
+// int valuesizes[nvalue] | pad | key | pad | values | pad, src/keymultivalue.cpp:830-893) plus offs[nkmv+1].
+#pragma once
+
+#include <vector>
+
+#include "common.cuh"
+
+namespace mrgpu {
+
+struct DevKV {
+  Pool *pool = nullptr;
+  uint8_t *data = nullptr;
+  uint64_t cap = 0;      // bytes allocated
+  uint64_t nbytes = 0;   // bytes used (sum of the reference's per-page alignsize)
+  uint64_t nkv = 0, ksize = 0, vsize = 0;
+  bool uniform = true;   // meaningful when nkv > 0
+  uint32_t kb = 0, vb = 0, recsize = 0;
+  uint64_t *offs = nullptr;  // [nkv+1] when !uniform
+  uint64_t offs_cap = 0;     // entries allocated
+  std::vector<uint64_t> h_offs;  // host copy of offs (page table / page copies), filled on demand
+  bool h_offs_valid = false;
+
+  explicit DevKV(Pool *p) : pool(p) {}
+  ~DevKV()
+  {
+    pool->free(data, cap);
+    pool->free(offs, offs_cap * 8);
+  }
+  void reserve_bytes(uint64_t need)
+  {
+    if (need <= cap) return;
+    uint64_t ncap = cap ? cap : 0;
+    ncap = need > 2 * ncap ? need : 2 * ncap;
+    // growth beyond what was asked is only worth it for small stores; large ones are sized exactly
+    if (need > (1ull << 28)) ncap = need;
+    uint8_t *nd = (uint8_t *) pool->alloc(ncap);
+    if (nbytes) MR_CUDA(cudaMemcpyAsync(nd, data, nbytes, cudaMemcpyDeviceToDevice, pool->stream));
+    pool->free(data, cap);
+    data = nd;
+    cap = ncap;
+  }
+  void reserve_offs(uint64_t entries)
+  {
+    if (entries <= offs_cap) return;
+    uint64_t ncap = entries > 2 * offs_cap ? entries : 2 * offs_cap;
+    if (entries > (1ull << 25)) ncap = entries;
+    uint64_t *no = (uint64_t *) pool->alloc(ncap * 8);
+    if (offs && !uniform && nkv) MR_CUDA(cudaMemcpyAsync(no, offs, (nkv + 1) * 8, cudaMemcpyDeviceToDevice, pool->stream));
+    pool->free(offs, offs_cap * 8);
+    offs = no;
+    offs_cap = ncap;
+  }
+};
+
+struct DevKMV {
+  Pool *pool = nullptr;
+  uint8_t *data = nullptr;
+  uint64_t cap = 0, nbytes = 0;
+  uint64_t nkmv = 0, nvalue = 0, ksize = 0, vsize = 0;
+  uint64_t *offs = nullptr;  // [nkmv+1]
+  uint64_t offs_cap = 0;
+  int64_t ukb = -1, uvb = -1;  // keybytes / valuebytes shared by every pair, or -1
+  std::vector<uint64_t> h_offs;
+  bool h_offs_valid = false;
+
+  explicit DevKMV(Pool *p) : pool(p) {}
+  ~DevKMV()
+  {
+    pool->free(data, cap);
+    pool->free(offs, offs_cap * 8);
+  }
+};
+
+// host-side staging of pairs added one by one (KeyValue::add from a host callback)
+struct Staging {
+  bool open = false;
+  std::vector<uint8_t> data;
+  std::vector<uint64_t> offs;  // record starts, plus end
+  uint64_t nkv = 0, ksize = 0, vsize = 0;
+  bool uniform = true;
+  uint32_t kb = 0, vb = 0;
+  void clear()
+  {
+    data.clear();
+    offs.clear();
+    nkv = ksize = vsize = 0;
+    uniform = true;
+    kb = vb = 0;
+  }
+};
+
+}  // namespace mrgpu

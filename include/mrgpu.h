@@ -1,0 +1,192 @@
+/* mrgpu.h -- C ABI of the B200 (sm_100a) implementation of the MR-MPI data-parallel hot path:
+ *   map emit -> KeyValue pages in HBM -> aggregate (hash partition + all-to-all) -> convert/collate
+ *   (group by key -> KeyMultiValue) -> reduce / sort_keys / scan.
+ *
+ * This is the drop-in boundary: plain pointers, sizes and opaque handles; no
+ * C++, torch or CUDA types in any signature (a stream crosses as void*).  The C++ classes
+ * MAPREDUCE_NS::MapReduce / KeyValue in gpu_mapreduce_b200/cpp/ are a source-compatible mirror of the
+ * reference's src/mapreduce.h:22-131 and src/keyvalue.h:23-59 that forwards here; a host language with
+ * an FFI binds these symbols directly (INTEGRATION.md shows the stubs).
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the reference tree).
+ *
+ * Conventions
+ *  - Every function returns 0 on success, a negative MRGPU_E* code on failure; mrgpu_last_error()
+ *    returns the message.  The reference has no error codes: it prints "ERROR: msg" and exits
+ *    (src/error.cpp:33-67); the C++ mirror restores exactly that behaviour from these codes and keeps
+ *    the reference's message texts ("Cannot convert without KeyValue", ...).
+ *  - Like the reference (src/mapreduce.h:43-44) an MR handle owns at most one KeyValue (KV) or one
+ *    KeyMultiValue (KMV) at a time; operations consume one and produce the other.
+ *  - Counts returned through `uint64_t *n` are the GLOBAL pair counts the reference returns from every
+ *    call (MPI_Allreduce SUM, e.g. src/mapreduce.cpp:558), summed over the ranks of the communicator set
+ *    with mrgpu_comm_init() (one rank = one process = one GPU).
+ *  - Data pointers may be host or device pointers (detected with cudaPointerGetAttributes); host input is
+ *    copied to the GPU inside the call.
+ *  - All work is issued on the stream given at creation; calls that return counts synchronise it.
+ *  - Not thread-safe per handle, same as the reference (SURVEY.md 8b "Threading").
+ *  - There is no CPU implementation behind any of these calls: without a CUDA device every call fails
+ *    with MRGPU_ECUDA.
+ */
+#ifndef MRGPU_H
+#define MRGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mrgpu_mr mrgpu_mr;
+
+enum {
+  MRGPU_OK = 0,
+  MRGPU_EINVAL = -1,   /* bad argument / misuse (reference: Error::all) */
+  MRGPU_ECUDA = -2,    /* CUDA runtime failure, incl. no device */
+  MRGPU_ENOKV = -3,    /* "Cannot <op> without KeyValue" */
+  MRGPU_ENOKMV = -4,   /* "Cannot <op> without KeyMultiValue" */
+  MRGPU_ELIMIT = -5,   /* exceeds a documented limit (pair > page, > 2^32-1 pairs per sort, ...) */
+  MRGPU_ECOMM = -6     /* NCCL failure / communicator misuse */
+};
+
+/* device functors standing in for the reference's CPU callbacks (no CPU callback in the hot loop) */
+enum {
+  MRGPU_REDUCE_COUNT = 0, /* oink/reduce_count.cpp:13-20   value = int number of values            */
+  MRGPU_REDUCE_SUM = 1,   /* examples/wordfreq.cpp:137-141 value = int nvalues                     */
+  MRGPU_REDUCE_CULL = 2   /* oink/reduce_cull.cpp:12-20    value = first value                     */
+};
+enum {
+  MRGPU_MAP_EDGE_TO_VERTICES = 0, /* oink/map_edge_to_vertices.cpp:14-20  emit vi and vj           */
+  MRGPU_MAP_EDGE_TO_VERTEX = 1,   /* oink/map_edge_to_vertex.cpp          emit vi                  */
+  MRGPU_MAP_INVERT = 2            /* oink/map_invert.cpp:11-15            swap key and value       */
+};
+
+/* ---- lifetime and settings ------------------------------------------------------------------- */
+
+/* MapReduce::MapReduce(MPI_Comm) src/mapreduce.cpp:93 + defaults() :196-262.  device = CUDA ordinal,
+ * stream = cudaStream_t (NULL = the legacy default stream). */
+int mrgpu_create(int device, void *stream, mrgpu_mr **out);
+/* MapReduce::~MapReduce src/mapreduce.cpp:169 */
+int mrgpu_destroy(mrgpu_mr *mr);
+/* message of the last failure on this handle (or of the last failed mrgpu_create when mr == NULL) */
+const char *mrgpu_last_error(const mrgpu_mr *mr);
+
+/* Public settings of the reference object, src/mapreduce.h:28-39: "memsize" (MB per page if > 0, bytes if
+ * < 0, src/mapreduce.cpp:3351), "keyalign", "valuealign", "verbosity", "timer", "all2all", "mapstyle",
+ * "minpage", "maxpage", "freepage", "outofcore", "zeropage".  Alignments freeze at first use like the
+ * reference's allocate() (src/mapreduce.cpp:3318-3341). */
+int mrgpu_set(mrgpu_mr *mr, const char *name, int64_t value);
+int mrgpu_get(const mrgpu_mr *mr, const char *name, int64_t *value);
+
+/* ---- communicator (replaces the MPI_Comm of src/mapreduce.cpp:93 and src/irregular.cpp) ---------- */
+
+/* ncclGetUniqueId: fills 128 bytes; rank 0 calls it and the host program hands the bytes to all ranks. */
+int mrgpu_comm_unique_id(void *id128);
+/* ncclCommInitRank.  Without this call the handle is a single-rank communicator (like mpistubs). */
+int mrgpu_comm_init(mrgpu_mr *mr, int rank, int nranks, const void *id128);
+/* MapReduce::my_proc / num_procs src/mapreduce.h:125-126 */
+int mrgpu_comm_rank(const mrgpu_mr *mr, int *rank, int *nranks);
+
+/* ---- map: emit into KV pages ------------------------------------------------------------------- */
+
+/* KeyValue::add(int n, char *key, int *keybytes, char *value, int *valuebytes) src/keyvalue.cpp:419-428
+ * as called from a host map()/reduce() callback: appends n pairs given as packed key bytes / value bytes
+ * plus per-pair lengths.  keybytes_fixed / valuebytes_fixed >= 0 with NULL arrays is the fixed-length form
+ * src/keyvalue.cpp:399-412.  mrgpu_kv_open/close bracket a batch like MapReduce::open/close
+ * (src/mapreduce.cpp:1650-1669); addflag as in map(). */
+int mrgpu_kv_open(mrgpu_mr *mr, int addflag);
+int mrgpu_kv_add(mrgpu_mr *mr, uint64_t n, const void *keys, const int32_t *keybytes, int keybytes_fixed,
+                 const void *values, const int32_t *valuebytes, int valuebytes_fixed);
+int mrgpu_kv_close(mrgpu_mr *mr, uint64_t *nkv);
+
+/* map(nmap, mymap, ptr, addflag) src/mapreduce.cpp:1044 with the IntCount emitter cpu/IntCount.cpp:177-180
+ * as a device functor: for each of the n uint32 in `keys`, key = its 4 bytes, value = int 1. */
+int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n, int addflag, uint64_t *nkv);
+
+/* map(files..., fileread) src/mapreduce.cpp:1060 with examples/wordfreq.cpp:104-130 as a device functor:
+ * one call per file; text is cut at its first NUL, split on " \t\n\f\r"; key = word + NUL, no value. */
+int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbytes, int addflag, uint64_t *nkv);
+
+/* map with the InvertedIndex scanner cpu/InvertedIndex.cpp:196-270 as a device functor: one call per
+ * file; key = URL bytes (no NUL), value = fname including its NUL. */
+int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, const char *fname, int addflag,
+                   uint64_t *nkv);
+
+/* map(nprocs, rmat_generate, &rmat, addflag) oink/rmat.cpp:57 with oink/map_rmat_generate.cpp:14-67 as a
+ * device functor.  *state48 is this rank's drand48 state (srand48(seed+me): (seed+me)<<16 | 0x330E,
+ * oink/rmat.cpp:94); it is advanced past the draws consumed, as the reference's global stream is. */
+int mrgpu_map_rmat(mrgpu_mr *mr, uint64_t ngenerate, int nlevels, double a, double b, double c, double d,
+                   double fraction, uint64_t *state48, int addflag, uint64_t *nkv);
+
+/* map(MapReduce *mr2, mymap, ptr, addflag) src/mapreduce.cpp:1560-1642 with a stock OINK callback
+ * (MRGPU_MAP_*) as device functor.  src may equal dst (src/mapreduce.cpp:1584-1602). */
+int mrgpu_map_mr(mrgpu_mr *dst, mrgpu_mr *src, int functor, int addflag, uint64_t *nkv);
+
+/* ---- the hot path -------------------------------------------------------------------------------- */
+
+/* MapReduce::add(MapReduce *) src/mapreduce.cpp:348-374 */
+int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv);
+/* MapReduce::aggregate(NULL) src/mapreduce.cpp:385-563 + Irregular src/irregular.cpp:95-301: pairs move to
+ * rank hashlittle(key,keybytes,nprocs) % nprocs; arrival order = (source rank, original order). */
+int mrgpu_aggregate(mrgpu_mr *mr, uint64_t *nkv);
+/* MapReduce::convert src/mapreduce.cpp:861-886 -> KeyMultiValue::convert src/keymultivalue.cpp:486-638 */
+int mrgpu_convert(mrgpu_mr *mr, uint64_t *nkmv);
+/* MapReduce::collate(NULL) src/mapreduce.cpp:710-738 */
+int mrgpu_collate(mrgpu_mr *mr, uint64_t *nkmv);
+/* MapReduce::reduce(myreduce, ptr) src/mapreduce.cpp:1769-1867 with a stock callback (MRGPU_REDUCE_*) */
+int mrgpu_reduce(mrgpu_mr *mr, int functor, uint64_t *nkv);
+/* MapReduce::sort_keys(int flag) src/mapreduce.cpp:2102-2128; flags +-1..+-6 select the compare functions of
+ * src/mapreduce.cpp:2692-2802 */
+int mrgpu_sort_keys(mrgpu_mr *mr, int flag, uint64_t *nkv);
+
+/* ---- stats and page access (scan, host callbacks, printing) --------------------------------------- */
+
+typedef struct {
+  uint64_t npair;      /* nkv / nkmv on this rank (KeyValue::nkv src/keyvalue.h:27)                  */
+  uint64_t nvalue;     /* KMV only: total number of values                                           */
+  uint64_t keysize;    /* exact key bytes    (ksize)                                                  */
+  uint64_t valuesize;  /* exact value bytes  (vsize)                                                  */
+  uint64_t exactsize;  /* esize: KV 8n+k+v (src/keyvalue.cpp:671), KMV 12n+4nv+k+v (keymultivalue.cpp:1460) */
+  uint64_t alignsize;  /* bytes held in HBM in the reference page layout                              */
+  uint64_t npage;      /* pages of `memsize` the reference would split this into                      */
+} mrgpu_stats;
+
+/* MapReduce::kv_stats / kmv_stats src/mapreduce.cpp:2937-3010 (this rank's part) */
+int mrgpu_kv_stats(mrgpu_mr *mr, mrgpu_stats *out);
+int mrgpu_kmv_stats(mrgpu_mr *mr, mrgpu_stats *out);
+
+/* KeyValue::request_info / request_page src/keyvalue.cpp:277-308: page ipage of the KV in the reference's
+ * byte layout (int keybytes | int valuebytes | pad | key | pad | value | pad).  mrgpu_kv_page_info gives
+ * nkey and sizes; mrgpu_kv_page_copy writes alignsize bytes to host memory `dst` (padding zeroed). */
+int mrgpu_kv_page_info(mrgpu_mr *mr, uint64_t ipage, uint64_t *nkey, uint64_t *keysize, uint64_t *valuesize,
+                       uint64_t *alignsize);
+int mrgpu_kv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst);
+/* KeyMultiValue::request_info / request_page src/keymultivalue.cpp:223-260: layout int nvalue | int keybytes |
+ * int mvaluebytes | int valuesizes[nvalue] | pad | key | pad | values | pad.  A pair larger than a page
+ * occupies a page run of its own (is_extended = 1, nkey = 1) that the host mirror serves through the
+ * reference's multivalue_blocks()/multivalue_block() protocol (src/mapreduce.cpp:1874-1925). */
+int mrgpu_kmv_page_info(mrgpu_mr *mr, uint64_t ipage, uint64_t *nkey, uint64_t *alignsize, int *is_extended);
+int mrgpu_kmv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst);
+
+/* Device views for callers that stay on the GPU (device functors of their own, torch tensors, bench):
+ * base pointer of the packed record stream, its byte length, and the u64 record-offset index
+ * (NULL when all records have one size: then record i starts at i * record_bytes). */
+int mrgpu_kv_device_view(mrgpu_mr *mr, const void **data, uint64_t *nbytes, const uint64_t **offsets,
+                         uint64_t *record_bytes);
+int mrgpu_kmv_device_view(mrgpu_mr *mr, const void **data, uint64_t *nbytes, const uint64_t **offsets);
+
+/* ---- stand-alone kernels exposed for tests and profiling ---------------------------------------- */
+
+/* hashlittle src/hash.cpp:129 over n keys given as packed bytes + u64 offsets[n+1]; out[i] = hash. */
+int mrgpu_hashlittle(int device, const void *keys, const uint64_t *offsets, uint64_t n, uint32_t initval,
+                     uint32_t *out);
+/* Stable LSD radix sort of n (key, payload) pairs, the engine under convert and sort_keys (replaces the
+ * qsort + merge of src/mapreduce.cpp:2462-2633).  key_bytes 4 or 8, payload_bytes 0, 4 or 8; device
+ * pointers; sorted data is written back to keys/payload. */
+int mrgpu_sort_pairs(int device, void *stream, void *keys, void *payload, uint64_t n, int key_bytes,
+                     int payload_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

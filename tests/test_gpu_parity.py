@@ -1,0 +1,428 @@
+"""GPU parity tests (run on the B200 box with -m gpu): the CUDA path, called through the C-ABI of
+gpu_mapreduce_b200/libmrgpu.so, against the oracle and the fixtures recorded from the reference library.
+Integer / byte work: everything is compared bit-exact."""
+import ctypes
+import struct
+
+import numpy as np
+import pytest
+
+import mrhelpers as H
+from gpu_mapreduce_b200 import workloads as W
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def MR():
+    import gpu_mapreduce_b200 as g
+
+    made = []
+
+    def make(**settings):
+        mr = g.MapReduce(device=0)
+        for k, v in settings.items():
+            setattr(mr, k, v)
+        made.append(mr)
+        return mr
+
+    yield make
+    for mr in made:
+        mr.destroy()
+
+
+def _torch():
+    import torch
+
+    return torch
+
+
+# ------------------------------------------------------------------------------------------- primitives
+
+@pytest.mark.parametrize("n", [0, 1, 31, 4095, 4096, 4097, 100_003, 1_500_000])
+@pytest.mark.parametrize("kbytes,pbytes", [(4, 0), (4, 4), (4, 8), (8, 0), (8, 4), (8, 8)])
+def test_sort_pairs_matches_stable_argsort(n, kbytes, pbytes):
+    import gpu_mapreduce_b200 as g
+
+    torch = _torch()
+    r = np.random.RandomState(n % 1000 + kbytes + pbytes)
+    kd = np.uint32 if kbytes == 4 else np.uint64
+    # mixture: few distinct values (long runs), constant high bytes, some full-range keys
+    keys = r.randint(0, 1 << 20, size=n).astype(kd)
+    if n > 10:
+        keys[::7] = r.randint(0, 5, size=len(keys[::7]))
+        keys[::13] = np.iinfo(kd).max
+        keys[::11] = r.randint(0, 1 << 31, size=len(keys[::11])).astype(kd) << (kbytes * 8 - 31)
+    pay = None
+    if pbytes:
+        pd = np.uint32 if pbytes == 4 else np.uint64
+        pay = np.arange(n, dtype=pd) * 3 + 1
+    tk = torch.from_numpy(keys.view(np.int32 if kbytes == 4 else np.int64).copy()).cuda()
+    tp = torch.from_numpy(pay.view(np.int32 if pbytes == 4 else np.int64).copy()).cuda() if pbytes else None
+    rc = g.lib().mrgpu_sort_pairs(0, None, tk.data_ptr(), tp.data_ptr() if pbytes else None, n, kbytes, pbytes)
+    assert rc == 0
+    order = np.argsort(keys, kind="stable")
+    got_k = tk.cpu().numpy().view(kd)
+    assert np.array_equal(got_k, keys[order])
+    if pbytes:
+        assert np.array_equal(tp.cpu().numpy().view(pay.dtype), pay[order])
+
+
+def test_hashlittle_kernel_matches_reference_kat(golden, oracle):
+    import gpu_mapreduce_b200 as g
+
+    by_iv = {}
+    for iv, hexkey, h in golden.manifest["hash"]:
+        by_iv.setdefault(iv, []).append((bytes.fromhex(hexkey), h))
+    r = np.random.RandomState(5)
+    for iv, items in by_iv.items():
+        keys = [k for k, _ in items] + [bytes(r.randint(0, 256, size=r.randint(0, 90)).astype(np.uint8)) for _ in range(200)]
+        want = [h for _, h in items] + [oracle.hashlittle(k, iv) for k in keys[len(items):]]
+        offs = np.zeros(len(keys) + 1, dtype=np.uint64)
+        offs[1:] = np.cumsum([len(k) for k in keys])
+        blob = np.frombuffer(b"".join(keys) + b"\0", dtype=np.uint8)
+        out = np.zeros(len(keys), dtype=np.uint32)
+        rc = g.lib().mrgpu_hashlittle(0, blob.ctypes.data, offs.ctypes.data, len(keys), iv, out.ctypes.data)
+        assert rc == 0
+        assert out.tolist() == want
+
+
+# ------------------------------------------------------------------------------------------- IntCount
+
+def _intcount_gpu(mr, keys, device_input):
+    torch = _torch()
+    if device_input:
+        t = torch.from_numpy(keys.view(np.int32).copy()).cuda()
+        n = mr.map_intcount(t)
+    else:
+        n = mr.map_intcount(keys)
+    assert n == len(keys)
+    return n
+
+
+@pytest.mark.parametrize("device_input", [True, False])
+def test_intcount_golden_pipeline(MR, golden, device_input):
+    mr = MR()
+    keys = np.frombuffer(golden["intcount.in"], dtype=np.uint32)
+    _intcount_gpu(mr, keys, device_input)
+    # map output: byte-identical KV page vs the oracle's page image (records are fully specified, no padding)
+    pages = mr.kv_pages()
+    orc = H.Oracle()
+    assert pages == H.pages_decode(orc.kv_pages(orc.intcount_map(keys), 64 << 20))
+    assert mr.aggregate() == len(keys)
+    nu = mr.convert()
+    st = mr.kmv_stats()
+    assert st.npair == nu and st.nvalue == len(keys)
+    assert mr.reduce("count") == nu
+    assert mr.sort_keys(1) == nu
+    assert H.kv_encode(mr.scan_kv()) == golden["intcount.out"]
+
+
+@pytest.mark.parametrize("n,nd", [(1, 1), (2, 1), (5000, 1), (70_000, 3000), (300_000, 1 << 16)])
+def test_intcount_vs_oracle_sizes(MR, oracle, n, nd):
+    mr = MR()
+    keys = W.intcount_keys_np(0, n, ndistinct=nd, seed=n)
+    if n > 100:
+        keys = keys.copy()
+        keys[::97] = 0xFFFFFFF0 + (np.arange(len(keys[::97])) % 7).astype(np.uint32)  # keys with the sign bit set
+    _intcount_gpu(mr, keys, True)
+    mr.convert()
+    # KMV content: canonical key order, values in arrival order (all 1s here, sizes all 4)
+    kmv = mr.scan_kmv()
+    want = H.canon_kmv(H.kmv_decode(oracle.convert(oracle.intcount_map(keys))))
+    assert H.canon_kmv(kmv) == want
+    mr.reduce("count")
+    mr.sort_keys(1)
+    ref = oracle.sort_keys(oracle.reduce(oracle.convert(oracle.intcount_map(keys)), "count"), 1)
+    assert H.kv_encode(mr.scan_kv()) == ref
+
+
+def test_intcount_empty_and_errors(MR):
+    import gpu_mapreduce_b200 as g
+
+    mr = MR()
+    with pytest.raises(g.MRError, match="Cannot convert without KeyValue"):
+        mr.convert()
+    with pytest.raises(g.MRError, match="Cannot reduce without KeyMultiValue"):
+        mr.reduce("count")
+    with pytest.raises(g.MRError, match="Cannot aggregate without KeyValue"):
+        mr.aggregate()
+    assert mr.map_intcount(np.zeros(0, dtype=np.uint32)) == 0
+    assert mr.kv_stats().npage == 1
+    assert mr.convert() == 0
+    assert mr.reduce("count") == 0
+    assert mr.sort_keys(1) == 0
+    assert mr.scan_kv() == []
+    with pytest.raises(g.MRError, match="Invalid compare method"):
+        mr.sort_keys(9)
+
+
+def test_intcount_alignment8_and_pages(MR, oracle):
+    keys = W.intcount_keys_np(0, 5000, ndistinct=100)
+    mr = MR(keyalign=8, valuealign=8, memsize=-32768)
+    mr.map_intcount(keys)
+    got = mr.kv_pages()
+    want = H.pages_decode(oracle.kv_pages(oracle.intcount_map(keys), 32768, 8, 8))
+    assert len(want) > 1
+    assert got == want
+    mr.convert()
+    gk = []
+    for nkey, page, ext in mr.kmv_pages():
+        assert not ext
+        gk += H.kmv_page_records(page, nkey, 8, 8)
+    assert H.canon_kmv(gk) == H.canon_kmv(H.kmv_decode(oracle.convert(oracle.intcount_map(keys))))
+    mr.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(oracle.reduce(oracle.convert(oracle.intcount_map(keys)), "count")))
+
+
+def test_intcount_addflag_appends(MR, oracle):
+    a = W.intcount_keys_np(0, 3000, ndistinct=50, seed=1)
+    b = W.intcount_keys_np(0, 2000, ndistinct=50, seed=2)
+    mr = MR()
+    mr.map_intcount(a)
+    assert mr.map_intcount(b, addflag=1) == 5000
+    assert mr.scan_kv() == H.kv_decode(oracle.intcount_map(np.concatenate([a, b])))
+    assert mr.map_intcount(b, addflag=0) == 2000
+
+
+# ------------------------------------------------------------------------------------------- convert / reduce
+
+def _load(mr, kvfile):
+    recs = H.kv_decode(kvfile)
+    assert mr.kv_add(recs) == len(recs)
+    return recs
+
+
+def test_kv_add_pages_match_reference_layout(MR, golden, oracle):
+    mr = MR(memsize=-32768)
+    recs = _load(mr, golden["pages_multi.in"])
+    got = mr.kv_pages()
+    ref = H.pages_decode(golden["pages_multi.kv"])
+    assert [(n, len(b)) for n, b in got] == [(n, len(b)) for n, b in ref]
+    out = []
+    for n, pg in got:
+        out += H.kv_page_records(pg, n)
+    assert out == recs
+    st = mr.kv_stats()
+    assert st.npair == len(recs) and st.npage == len(ref)
+    assert st.exactsize == 8 * len(recs) + sum(len(k) + len(v) for k, v in recs)
+
+
+def test_convert_general_golden(MR, golden):
+    """variable-length keys and values: fingerprint path; key order canonical, value order = arrival"""
+    mr = MR()
+    _load(mr, golden["convert.in"])
+    ref = H.kmv_decode(golden["convert.kmv"])
+    assert mr.convert() == len(ref)
+    assert H.canon_kmv(mr.scan_kmv()) == H.canon_kmv(ref)
+    st = mr.kmv_stats()
+    assert st.keysize == sum(len(k) for k, _ in ref)
+    assert st.valuesize == sum(len(v) for _, vs in ref for v in vs)
+
+
+@pytest.mark.parametrize("cb", ["count", "sum", "cull"])
+def test_reduce_callbacks_golden(MR, golden, cb):
+    mr = MR()
+    _load(mr, golden["convert.in"])
+    mr.collate()
+    ref = H.kv_decode(golden[f"convert.reduce_{cb}"])
+    assert mr.reduce(cb) == len(ref)
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(ref)
+
+
+def test_b2_page_images(MR, golden):
+    mr = MR()
+    _load(mr, golden["pages_b2.in"])
+    assert mr.kv_pages() == H.pages_decode(golden["pages_b2.kv.a4"])
+    mr.convert()
+    (nkey, page, ext), = mr.kmv_pages()
+    ref_nkey, ref_page = H.pages_decode(golden["pages_b2.kmv.a4"])[0]
+    # same records; our key order is canonical, the reference's is first appearance ("a","bb","ccc" in both here)
+    assert H.canon_kmv(H.kmv_page_records(page, nkey)) == H.canon_kmv(H.kmv_page_records(ref_page, ref_nkey))
+    assert len(page) == len(ref_page)
+
+
+UNIFORM_CASES = [(4, 0), (4, 4), (4, 8), (8, 0), (8, 4), (3, 5), (16, 0), (16, 4), (12, 12), (1, 0), (24, 8)]
+
+
+@pytest.mark.parametrize("kb,vb", UNIFORM_CASES)
+def test_convert_uniform_shapes(MR, oracle, kb, vb):
+    """every uniform (keybytes, valuebytes) route: exact 32/64-bit keys, compacted long keys, gathered values"""
+    r = np.random.RandomState(kb * 100 + vb)
+    n = 6000
+    base = r.randint(0, 256, size=kb).astype(np.uint8)
+    recs = []
+    for i in range(n):
+        k = base.copy()
+        # vary at most 3 byte positions so long keys stay compactable; kb=24 case varies 10 -> general path
+        nvary = min(kb, 10 if kb == 24 else 3)
+        for q in range(nvary):
+            k[(q * 5) % kb] = r.randint(0, 6)
+        v = struct.pack("<I", i)[:vb] if vb <= 4 else (struct.pack("<I", i) * 3)[:vb]
+        recs.append((bytes(k), v))
+    mr = MR()
+    mr.kv_add(recs)
+    want = H.kmv_decode(oracle.convert(H.kv_encode(recs)))
+    assert mr.convert() == len(want)
+    assert H.canon_kmv(mr.scan_kmv()) == H.canon_kmv(want)
+    mr.reduce("cull" if vb else "count")
+    wantr = H.kv_decode(oracle.reduce(oracle.convert(H.kv_encode(recs)), "cull" if vb else "count"))
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(wantr)
+
+
+def test_convert_hot_key_bigger_than_page(MR, golden, oracle):
+    """one key with ~18000 values and 32 KiB pages -> the pair gets its own (extended) page"""
+    mr = MR(memsize=-32768)
+    _load(mr, golden["extended.in"])
+    mr.convert()
+    pages = mr.kmv_pages()
+    assert any(ext for _, _, ext in pages)
+    mr.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(golden["extended.count"]))
+
+
+# ------------------------------------------------------------------------------------------- sort_keys
+
+@pytest.mark.parametrize("flag", [1, 2, 3, 4, 5, 6])
+def test_sort_keys_flags_golden(MR, golden, flag):
+    for sgn, name in ((1, "outp"), (-1, "outm")):
+        mr = MR()
+        _load(mr, golden[f"sort{flag}.in"])
+        mr.sort_keys(sgn * flag)
+        assert H.kv_encode(mr.scan_kv()) == golden[f"sort{flag}.{name}"]
+
+
+# ------------------------------------------------------------------------------------------- text functors
+
+def test_wordfreq_golden(MR, golden):
+    mr = MR()
+    total = 0
+    for i in range(3):
+        total = mr.map_tokenize(golden[f"wordfreq.in{i}"], addflag=1 if i else 0)
+    ref_map = H.kv_decode(golden["wordfreq.mapout"])
+    assert total == len(ref_map)
+    assert mr.scan_kv() == ref_map          # same pairs in the same order as the reference's fileread
+    mr.collate()
+    mr.reduce("sum")
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(golden["wordfreq.final"]))
+
+
+def test_tokenize_edge_cases(MR, oracle):
+    for text in [b"", b" ", b"a", b" a", b"a ", b"\t\n\f\r", b"one\x00two three", b"\x00abc", b"x" * 5000, b"a b " * 3000 + b"z"]:
+        mr = MR()
+        n = mr.map_tokenize(text)
+        want = H.kv_decode(oracle.tokenize(text))
+        assert n == len(want)
+        assert mr.scan_kv() == want
+
+
+def test_invindex_golden(MR, golden):
+    mr = MR()
+    for i in range(4):
+        mr.map_href(golden[f"invindex.in{i}"], f"part-{i:05d}", addflag=1 if i else 0)
+    assert mr.scan_kv() == H.kv_decode(golden["invindex.mapout"])
+    mr.aggregate()
+    mr.convert()
+    assert H.canon_kmv(mr.scan_kmv()) == H.canon_kmv(H.kmv_decode(golden["invindex.kmv"]))
+
+
+def test_href_fsm_random_vs_oracle(MR, oracle):
+    r = np.random.RandomState(77)
+    toks = [b"<", b"a", b" ", b"h", b"r", b"e", b"f", b"=", b'"', b"x", b"href", b"<a href=\"", b"u", b">", b"\t"]
+    for trial in range(30):
+        text = b"".join(toks[r.randint(len(toks))] for _ in range(r.randint(1, 4000)))
+        mr = MR()
+        n = mr.map_href(text, "f.html")
+        want = H.kv_decode(oracle.href(text, "f.html"))
+        assert n == len(want)
+        assert mr.scan_kv() == want
+
+
+# ------------------------------------------------------------------------------------------- R-MAT + degree
+
+def _gpu_rmat(mr, N, ef, a, b, c, d, fr, seed, P):
+    states = [((seed + r) << 16) | 0x330E for r in range(P)]
+    ntotal, nremain, niter = (1 << N) * ef, (1 << N) * ef, 0
+    while nremain:
+        niter += 1
+        for r in range(P):
+            ng = nremain // P + (1 if r < nremain % P else 0)
+            _, states[r] = mr.map_rmat(ng, N, a, b, c, d, fr, states[r], addflag=1)
+        nunique = mr.collate()
+        mr.reduce("cull")
+        nremain = ntotal - nunique
+    return niter
+
+
+def test_rmat_degree_golden(MR, golden):
+    for ci, case in enumerate(golden.manifest["rmat"]):
+        N, ef, a, b, c, d, fr, seed, P, dup = case["args"]
+        mr = MR()
+        assert _gpu_rmat(mr, N, ef, a, b, c, d, fr, seed, P) == case["iterations"]
+        assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(golden[f"rmat{ci}.edges"]))
+        mrv = MR()
+        mrv.map_mr(mr, "edge_to_vertex" if dup == 1 else "edge_to_vertices")
+        mrv.collate()
+        mrv.reduce("count")
+        assert H.canon_kv(mrv.scan_kv()) == H.canon_kv(H.kv_decode(golden[f"rmat{ci}.degree"]))
+
+
+def test_rmat_generate_stream_matches_oracle(MR, oracle):
+    """one rmat_generate call = the reference's sequential drand48 stream, edge for edge, state included"""
+    for fr in (0.0, 0.2):
+        st0 = oracle.lib.orc_srand48(4242)
+        st1, edges = oracle.rmat_generate(st0, 5000, 14, .57, .19, .19, .05, fr)
+        mr = MR()
+        n, st = mr.map_rmat(5000, 14, .57, .19, .19, .05, fr, st0, addflag=0)
+        assert n == 5000 and st == st1
+        got = np.frombuffer(b"".join(k for k, _ in mr.scan_kv()), dtype=np.uint64).reshape(-1, 2)
+        assert np.array_equal(got, edges)
+
+
+def test_map_mr_self_and_invert(MR, oracle):
+    r = np.random.RandomState(3)
+    recs = [(struct.pack("<QQ", r.randint(0, 50), r.randint(0, 50)), b"") for _ in range(3000)]
+    mr = MR()
+    mr.kv_add(recs)
+    assert mr.map_mr(mr, "edge_to_vertices") == 6000      # src == dst, src/mapreduce.cpp:1584-1602
+    assert mr.scan_kv() == H.kv_decode(oracle.edge_to_vertices(H.kv_encode(recs), True))
+    recs2 = [(bytes(r.randint(0, 256, size=r.randint(1, 9)).astype(np.uint8)), bytes(r.randint(0, 256, size=r.randint(0, 5)).astype(np.uint8)))
+             for _ in range(500)]
+    m2, m3 = MR(), MR()
+    m2.kv_add(recs2)
+    m3.map_mr(m2, "invert")
+    assert m3.scan_kv() == [(v, k) for k, v in recs2]
+
+
+def test_add_appends_other_mr(MR):
+    a, b = MR(), MR()
+    ra = [(b"k%d" % i, b"v") for i in range(100)]
+    rb = [(struct.pack("<I", i), struct.pack("<I", 1)) for i in range(50)]
+    a.kv_add(ra)
+    b.kv_add(rb)
+    assert a.add(b) == 150
+    assert a.scan_kv() == ra + rb
+
+
+# ------------------------------------------------------------------------------------------- scale properties
+
+def test_intcount_16M_properties(MR):
+    """2^24 pairs (beyond what the oracle does in seconds): size-independent properties + numpy bincount"""
+    torch = _torch()
+    n, nd = 1 << 24, 1 << 20
+    keys = W.intcount_keys_torch(0, n, "cuda", ndistinct=nd)
+    mr = MR()
+    assert mr.map_intcount(keys) == n
+    nu = mr.convert()
+    st = mr.kmv_stats()
+    assert st.nvalue == n and st.exactsize == 12 * nu + 4 * n + 4 * nu + 4 * n
+    assert mr.reduce("count") == nu
+    assert mr.sort_keys(1) == nu
+    (nkey, page), = mr.kv_pages()
+    rec = np.frombuffer(page, dtype=np.int32).reshape(-1, 4)
+    assert nkey == nu and np.all(rec[:, 0] == 4) and np.all(rec[:, 1] == 4)
+    assert np.all(np.diff(rec[:, 2]) > 0)                       # sorted, unique
+    assert int(rec[:, 3].astype(np.int64).sum()) == n           # checksum of counts
+    bc = np.bincount(keys.cpu().numpy().astype(np.int64), minlength=nd)
+    nz = np.nonzero(bc)[0]
+    assert np.array_equal(rec[:, 2], nz) and np.array_equal(rec[:, 3], bc[nz])
