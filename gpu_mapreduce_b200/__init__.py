@@ -85,6 +85,8 @@ def lib():
         "mrgpu_kmv_page_copy": [vp, C.c_uint64, vp],
         "mrgpu_kv_device_view": [vp, C.POINTER(vp), u64p, C.POINTER(vp), u64p],
         "mrgpu_kmv_device_view": [vp, C.POINTER(vp), u64p, C.POINTER(vp)],
+        "mrgpu_prof": [vp, C.c_int],
+        "mrgpu_prof_report": [vp, C.c_char_p, C.c_uint64, u64p],
         "mrgpu_hashlittle": [C.c_int, vp, vp, C.c_uint64, C.c_uint32, vp],
         "mrgpu_sort_pairs": [C.c_int, vp, vp, vp, C.c_uint64, C.c_int, C.c_int],
     }
@@ -335,6 +337,19 @@ class MapReduce:
                     fn(page[k0:k0 + kb], kb, page[v0:v0 + mvb], nv, sizes)
                 p = (v0 + mvb + ta - 1) // ta * ta
         return out
+
+    def prof(self, enable=True):
+        """reset launch counters; with enable, time every tagged kernel (cf. the reference's `timer`)"""
+        self._ck(lib().mrgpu_prof(self._h, 1 if enable else 0))
+
+    def prof_report(self):
+        """(list of {tag, ms, bytes, launches, calls}, total kernel launches since prof())"""
+        import json
+
+        buf = C.create_string_buffer(1 << 16)
+        n = C.c_uint64()
+        self._ck(lib().mrgpu_prof_report(self._h, buf, len(buf), C.byref(n)))
+        return json.loads(buf.value.decode()), n.value
 
     def kv_device_view(self):
         d, n, o, r = C.c_void_p(), C.c_uint64(), C.c_void_p(), C.c_uint64()

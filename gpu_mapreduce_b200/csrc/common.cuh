@@ -8,6 +8,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <string>
+#include <vector>
 
 namespace mrgpu {
 
@@ -32,10 +33,51 @@ struct Error {
 // ones after every operation (src/mapreduce.cpp:3318-3517); here HBM is the page pool: allocations
 // come from the device's default cudaMallocAsync pool with an unlimited release threshold, so after
 // warm-up an operation's KV/KMV/scratch buffers are recycled without touching the driver.
+// Per-kernel timing, the analogue of the reference's `timer` setting (src/mapreduce.cpp:3112-3128 prints
+// "<Op> time (secs)").  When enabled every tagged launch is bracketed by CUDA events on the launching
+// stream; launches are always counted.
+struct ProfEntry {
+  const char *tag;
+  cudaEvent_t a, b;
+  double bytes;  // algorithmic bytes of this launch, 0 if not stated
+  int launches;
+};
+struct Prof {
+  bool on = false;
+  std::vector<ProfEntry> ev;
+  std::vector<cudaEvent_t> spare;
+  uint64_t launches = 0;
+  cudaEvent_t get()
+  {
+    cudaEvent_t e;
+    if (!spare.empty()) {
+      e = spare.back();
+      spare.pop_back();
+    } else
+      cudaEventCreate(&e);
+    return e;
+  }
+  void reset()
+  {
+    for (auto &x : ev) {
+      spare.push_back(x.a);
+      spare.push_back(x.b);
+    }
+    ev.clear();
+    launches = 0;
+  }
+  ~Prof()
+  {
+    reset();
+    for (auto e : spare) cudaEventDestroy(e);
+  }
+};
+
 struct Pool {
   cudaStream_t stream = nullptr;
   int device = 0;
   uint64_t live = 0, hiwater = 0;  // the reference's msize / msizemax (src/mapreduce.h:54)
+  Prof prof;
 
   void init(int dev, cudaStream_t s)
   {
@@ -61,6 +103,26 @@ struct Pool {
     if (bytes == 0) bytes = 256;
     cudaFreeAsync(p, stream);
     live -= bytes;
+  }
+};
+
+// brackets the kernel launches issued while it is alive
+struct ProfScope {
+  Pool &p;
+  int idx = -1;
+  ProfScope(Pool &pool, const char *tag, double bytes = 0, int nlaunch = 1) : p(pool)
+  {
+    p.prof.launches += nlaunch;
+    if (p.prof.on) {
+      ProfEntry e{tag, p.prof.get(), p.prof.get(), bytes, nlaunch};
+      cudaEventRecord(e.a, p.stream);
+      idx = (int) p.prof.ev.size();
+      p.prof.ev.push_back(e);
+    }
+  }
+  ~ProfScope()
+  {
+    if (idx >= 0) cudaEventRecord(p.prof.ev[idx].b, p.stream);
   }
 };
 

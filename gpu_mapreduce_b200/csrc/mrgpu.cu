@@ -201,6 +201,60 @@ extern "C" int mrgpu_comm_rank(const mrgpu_mr *mr, int *rank, int *nranks)
 }
 
 // ================================================================================================
+// per-kernel timing (the reference's `timer` setting prints per-op seconds, src/mapreduce.cpp:3112-3128)
+
+extern "C" int mrgpu_prof(mrgpu_mr *mr, int enable)
+{
+  API_BEGIN(mr)
+  sync(mr);
+  mr->pool.prof.reset();
+  mr->pool.prof.on = enable != 0;
+  API_END(mr)
+}
+
+extern "C" int mrgpu_prof_report(mrgpu_mr *mr, char *buf, uint64_t cap, uint64_t *launches)
+{
+  API_BEGIN(mr)
+  sync(mr);
+  if (launches) *launches = mr->pool.prof.launches;
+  struct Acc {
+    const char *tag;
+    double ms, bytes;
+    int launches, calls;
+  };
+  std::vector<Acc> acc;
+  for (auto &e : mr->pool.prof.ev) {
+    float ms = 0;
+    MR_CUDA(cudaEventElapsedTime(&ms, e.a, e.b));
+    Acc *a = nullptr;
+    for (auto &x : acc)
+      if (!strcmp(x.tag, e.tag)) a = &x;
+    if (!a) {
+      acc.push_back(Acc{e.tag, 0, 0, 0, 0});
+      a = &acc.back();
+    }
+    a->ms += ms;
+    a->bytes += e.bytes;
+    a->launches += e.launches;
+    a->calls++;
+  }
+  std::string js = "[";
+  for (size_t i = 0; i < acc.size(); i++) {
+    char line[256];
+    snprintf(line, sizeof(line), "%s{\"tag\": \"%s\", \"ms\": %.6f, \"bytes\": %.0f, \"launches\": %d, \"calls\": %d}", i ? ", " : "",
+             acc[i].tag, acc[i].ms, acc[i].bytes, acc[i].launches, acc[i].calls);
+    js += line;
+  }
+  js += "]";
+  if (buf && cap) {
+    size_t m = js.size() < cap - 1 ? js.size() : cap - 1;
+    memcpy(buf, js.data(), m);
+    buf[m] = 0;
+  }
+  API_END(mr)
+}
+
+// ================================================================================================
 // host staging: KeyValue::add from a host callback
 
 extern "C" int mrgpu_kv_open(mrgpu_mr *mr, int addflag)

@@ -187,6 +187,8 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
   MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
 
   // 1. one read of the KV: sort keys, payload, byte histograms
+  {
+  ProfScope ps(pool, "convert_extract", (double) n * (8 + kb + vb + sizeof(K) + (HASP ? sizeof(P) : 0)));
   if (ident && PMODE == 1 && sizeof(K) == 4 && kb == 4 && rs == 16 && koff == 8 && voff == 12 && ((uintptr_t) kv->data % 16) == 0)
     extract16_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>((const int4 *) kv->data, n, (uint32_t *) k0.p, (uint32_t *) p0.p, hist.p);
   else if (ident)
@@ -194,6 +196,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
   else
     extract_uniform_kernel<K, PMODE, false><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p);
   MR_CUDA(cudaGetLastError());
+  }
 
   // 2. stable LSD radix sort on the varying bytes only
   unsigned mask = ck.nvb >= 8 ? 0xFF : ((1u << ck.nvb) - 1);
@@ -206,7 +209,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
   // 3. run heads -> number of unique keys U and start[u]
   auto head = [=] __device__(uint64_t i) -> unsigned long long { return (i == 0 || sk[i] != sk[i - 1]) ? 1ull : 0ull; };
   ScanTiles heads;
-  scan_tiles(pool, n, head, heads, mr->d_small);
+  scan_tiles(pool, n, head, heads, mr->d_small, "convert_heads_count", (double) n * sizeof(K));
   fetch_small(mr, 1);
   const uint64_t U = mr->h_small[0];
   Buf<uint32_t> start(pool, U + 1);
@@ -214,7 +217,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
     uint32_t *st = start.p;
     scan_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
       if (h) st[e] = (uint32_t) i;
-    });
+    }, "convert_heads_compact", (double) n * sizeof(K) + 4.0 * U);
     uint32_t n32 = (uint32_t) n;
     MR_CUDA(cudaMemcpyAsync(start.p + U, &n32, 4, cudaMemcpyHostToDevice, s));
   }
@@ -231,7 +234,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
           uint64_t nv = st[u + 1] - st[u];
           return kmv_rec_size(al, nv, kb, nv * vb);
         },
-        [=] __device__(uint64_t u, unsigned long long e, unsigned long long) { offs[u] = e; }, mr->d_small);
+        [=] __device__(uint64_t u, unsigned long long e, unsigned long long) { offs[u] = e; }, mr->d_small, "convert_kmv_sizes", 16.0 * U);
     fetch_small(mr, 1);
     const uint64_t total = mr->h_small[0];
     MR_CUDA(cudaMemcpyAsync(offs + U, &total, 8, cudaMemcpyHostToDevice, s));
@@ -282,7 +285,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
         uint8_t *d = rec + vo + r * vb;
         for (uint32_t q = 0; q < vb; q++) d[q] = src[q];
       }
-    });
+    }, "convert_kmv_write", (double) n * (sizeof(K) + (HASP ? sizeof(P) : 0)) + (double) total);
     kmv->nkmv = U;
     kmv->nvalue = n;
     kmv->ksize = U * (uint64_t) kb;

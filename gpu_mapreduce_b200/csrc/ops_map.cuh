@@ -142,6 +142,7 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
   uint64_t base = kv_append_uniform(mr, kv, 4, 4, n);
   uint32_t rs = kv_rec_size(mr->al, 4, 4);
   if (n) {
+    ProfScope ps(mr->pool, "map_intcount_emit", (double) n * (4 + 8 + 4 + 4));
     if (rs == 16 && kv_key_off(mr->al) == 8 && (base & 15) == 0)
       intcount_emit16_kernel<<<grid_for(n, 256 * 4, 16), 256, 0, mr->pool.stream>>>(dk, n, (int4 *) (kv->data + base));
     else
@@ -238,6 +239,7 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
       uint64_t base = kv_append_uniform(mr, kv, 8, 0, nout);
       uint32_t rs = kv_rec_size(al, 8, 0);
       if (n) {
+        ProfScope ps(mr->pool, "map_edge_to_vertices", (double) n * (8 + src->kb + src->vb) + (double) nout * 16);
         edge_to_vertices_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(src->data, src->uniform ? nullptr : src->offs, src->recsize,
                                                                            kv_key_off(srcmr->al), n, both, kv->data + base, rs,
                                                                            kv_key_off(al));
@@ -403,6 +405,7 @@ extern "C" int mrgpu_map_rmat(mrgpu_mr *mr, uint64_t ngenerate, int nlevels, dou
   RmatParams p{1ull << nlevels, nlevels, a, b, c, d, fraction};
   if (ngenerate) {
     bool fast = rs == 24 && kv_key_off(mr->al) == 8 && (base % 8) == 0;
+    ProfScope ps(mr->pool, "map_rmat_generate", (double) ngenerate * 24);
     rmat_generate_kernel<<<(unsigned) ((ngenerate + 255) / 256), 256, 0, mr->pool.stream>>>(p, *state48 & LCG_M, ngenerate, kv->data + base,
                                                                                          rs, kv_key_off(mr->al), fast);
     MR_CUDA(cudaGetLastError());

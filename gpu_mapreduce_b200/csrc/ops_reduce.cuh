@@ -95,6 +95,7 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
       uint32_t kb = (uint32_t) kmv->ukb, vb = cull ? (uint32_t) kmv->uvb : 4;
       uint32_t rs = kv_rec_size(al, kb, vb);
       kv->reserve_bytes(U * rs);
+      ProfScope ps(pool, "reduce", (double) U * (12 + 4 + kb + rs));
       if (!cull && kb == 4 && rs == 16 && kv_key_off(al) == 8 && al.k == 4)
         reduce_count16_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, (int4 *) kv->data);
       else

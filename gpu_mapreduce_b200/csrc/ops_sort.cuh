@@ -138,9 +138,12 @@ static void sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nc
   const uint32_t *perm_in = nullptr;
   int w = 0;
   for (int c = (int) nchunks - 1; c >= 0; c--) {
+    {
+    ProfScope ps(pool, "sort_extract", (double) n * (8 + sizeof(K) + 4));
     sortkey_extract_kernel<K><<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(kv->data, kv->uniform ? nullptr : kv->offs, kv->recsize, n, mr->al,
                                                                          absflag, reverse, (uint32_t) c, perm_in, kb[w], pb[w], bad);
     MR_CUDA(cudaGetLastError());
+    }
     int r = radix_sort_pairs<K, uint32_t, true>(pool, kb[w], kb[w ^ 1], pb[w], pb[w ^ 1], n, 0xFF, false, hist.p);
     int res = w ^ r;
     perm_in = pb[res];
@@ -187,6 +190,7 @@ static void sort_keys_impl(mrgpu_mr *mr, int flag)
     if (kv->uniform) {
       uint32_t words = kv->recsize / 4;
       uint64_t total = n * words;
+      ProfScope ps(pool, "sort_gather", (double) n * (4 + 2.0 * kv->recsize));
       gather_uniform_kernel<<<(unsigned) ((total + 255) / 256), 256, 0, s>>>((const uint32_t *) kv->data, (uint32_t *) nk->data, perm.p, n, words);
       MR_CUDA(cudaGetLastError());
     } else {

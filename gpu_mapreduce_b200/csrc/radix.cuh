@@ -275,6 +275,7 @@ int radix_sort_pairs(Pool &pool, K *k0, K *k1, P *p0, P *p1, uint64_t n, unsigne
   if (n == 0) return 0;
   if (!hist_ready) {
     MR_CUDA(cudaMemsetAsync(d_hist, 0, sizeof(K) * RADIX * 8, s));
+    ProfScope ps(pool, "radix_hist", (double) n * sizeof(K));
     radix_hist_kernel<K><<<grid_for(n, 256 * 16, 8), 256, 0, s>>>(k0, n, d_hist);
     MR_CUDA(cudaGetLastError());
   }
@@ -290,7 +291,10 @@ int radix_sort_pairs(Pool &pool, K *k0, K *k1, P *p0, P *p1, uint64_t n, unsigne
     if (!single) need |= 1u << b;
   }
   if (!need) return 0;
-  radix_scan_hist_kernel<<<(unsigned) sizeof(K), RADIX, 0, s>>>(d_hist);
+  {
+    ProfScope ps(pool, "radix_scan_hist");
+    radix_scan_hist_kernel<<<(unsigned) sizeof(K), RADIX, 0, s>>>(d_hist);
+  }
   MR_CUDA(cudaGetLastError());
 
   uint64_t ntiles = sort_tiles(n, IPT);
@@ -305,6 +309,7 @@ int radix_sort_pairs(Pool &pool, K *k0, K *k1, P *p0, P *p1, uint64_t n, unsigne
     K *ko = cur ? k0 : k1;
     const P *pi = cur ? p1 : p0;
     P *po = cur ? p0 : p1;
+    ProfScope ps(pool, "onesweep_pass", 2.0 * n * (sizeof(K) + (HASP ? sizeof(P) : 0)));
     onesweep_kernel<K, P, HASP, IPT><<<(unsigned) ntiles, SORT_THREADS, 0, s>>>(ki, ko, pi, po, n, 8 * b, d_hist + b * RADIX,
                                                                               status.p, counter.p);
     MR_CUDA(cudaGetLastError());

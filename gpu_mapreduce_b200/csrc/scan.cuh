@@ -111,7 +111,7 @@ struct ScanTiles {
 };
 
 template <typename F>
-void scan_tiles(Pool &pool, uint64_t n, F value, ScanTiles &t, unsigned long long *d_total)
+void scan_tiles(Pool &pool, uint64_t n, F value, ScanTiles &t, unsigned long long *d_total, const char *tag = "scan_reduce", double bytes = 0)
 {
   cudaStream_t s = pool.stream;
   t.n = n;
@@ -121,6 +121,7 @@ void scan_tiles(Pool &pool, uint64_t n, F value, ScanTiles &t, unsigned long lon
     return;
   }
   t.sums.alloc(pool, t.ntiles);
+  ProfScope ps(pool, tag, bytes, 2);
   scan_reduce_kernel<<<(unsigned) t.ntiles, SCAN_THREADS, 0, s>>>(n, value, t.sums.p);
   MR_CUDA(cudaGetLastError());
   scan_tiles_kernel<<<1, 1024, 0, s>>>(t.sums.p, t.ntiles, d_total);
@@ -128,20 +129,21 @@ void scan_tiles(Pool &pool, uint64_t n, F value, ScanTiles &t, unsigned long lon
 }
 
 template <typename F, typename G>
-void scan_sink(Pool &pool, const ScanTiles &t, F value, G sink)
+void scan_sink(Pool &pool, const ScanTiles &t, F value, G sink, const char *tag = "scan_apply", double bytes = 0)
 {
   if (t.n == 0) return;
+  ProfScope ps(pool, tag, bytes, 1);
   scan_apply_kernel<<<(unsigned) t.ntiles, SCAN_THREADS, 0, pool.stream>>>(t.n, value, sink, t.sums.p);
   MR_CUDA(cudaGetLastError());
 }
 
 // One-shot exclusive scan.  d_total receives the sum (device u64).
 template <typename F, typename G>
-void scan_apply(Pool &pool, uint64_t n, F value, G sink, unsigned long long *d_total)
+void scan_apply(Pool &pool, uint64_t n, F value, G sink, unsigned long long *d_total, const char *tag = "scan", double bytes = 0)
 {
   ScanTiles t;
-  scan_tiles(pool, n, value, t, d_total);
-  scan_sink(pool, t, value, sink);
+  scan_tiles(pool, n, value, t, d_total, tag, 0);
+  scan_sink(pool, t, value, sink, tag, bytes);
 }
 
 }  // namespace mrgpu

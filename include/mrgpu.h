@@ -175,6 +175,16 @@ int mrgpu_kv_device_view(mrgpu_mr *mr, const void **data, uint64_t *nbytes, cons
                          uint64_t *record_bytes);
 int mrgpu_kmv_device_view(mrgpu_mr *mr, const void **data, uint64_t *nbytes, const uint64_t **offsets);
 
+/* ---- per-kernel timing ---------------------------------------------------------------------------- */
+
+/* The reference's `timer` setting makes every op print "<Op> time (secs)" (src/mapreduce.cpp:3112-3128,
+ * 3230-3234).  mrgpu_prof(mr, 1) resets the counters and brackets every tagged kernel launch with CUDA events
+ * on the handle's stream; mrgpu_prof_report() synchronises and writes a JSON array
+ * [{"tag", "ms", "bytes" (algorithmic bytes), "launches", "calls"}] into buf and the number of
+ * kernel launches since the last mrgpu_prof() call into *launches (counted whether or not timing is on). */
+int mrgpu_prof(mrgpu_mr *mr, int enable);
+int mrgpu_prof_report(mrgpu_mr *mr, char *buf, uint64_t cap, uint64_t *launches);
+
 /* ---- stand-alone kernels exposed for tests and profiling ---------------------------------------- */
 
 /* hashlittle src/hash.cpp:129 over n keys given as packed bytes + u64 offsets[n+1]; out[i] = hash. */
