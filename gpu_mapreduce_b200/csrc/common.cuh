@@ -7,6 +7,8 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -29,10 +31,6 @@ struct Error {
 #define MR_FAIL(code, text) throw ::mrgpu::Error{(code), std::string(text)}
 
 // ---------------------------------------------------------------------------------------------
-// Stream-ordered HBM pool.  The reference keeps a tagged pool of `memsize` pages and frees unused
-// ones after every operation (src/mapreduce.cpp:3318-3517); here HBM is the page pool: allocations
-// come from the device's default cudaMallocAsync pool with an unlimited release threshold, so after
-// warm-up an operation's KV/KMV/scratch buffers are recycled without touching the driver.
 // Per-kernel timing, the analogue of the reference's `timer` setting (src/mapreduce.cpp:3112-3128 prints
 // "<Op> time (secs)").  When enabled every tagged launch is bracketed by CUDA events on the launching
 // stream; launches are always counted.
@@ -73,36 +71,139 @@ struct Prof {
   }
 };
 
+// HBM page pool.  The reference keeps a tagged pool of `memsize` pages and frees unused ones after every
+// operation (src/mapreduce.cpp:3318-3517); here HBM is the page pool and KV/KMV/scratch buffers of any size
+// are carved from cached chunks, so that after warm-up an operation never calls the driver allocator.
 struct Pool {
   cudaStream_t stream = nullptr;
   int device = 0;
   uint64_t live = 0, hiwater = 0;  // the reference's msize / msizemax (src/mapreduce.h:54)
+  uint64_t reserved = 0;           // bytes obtained from cudaMalloc
   Prof prof;
+
+  // Caching sub-allocator over big cudaMalloc'ed chunks.  The driver's own stream-ordered pool
+  // (cudaMallocAsync) re-maps physical pages whenever a request does not match a cached block, which
+  // measured ~6 ms per GiB on every operation; an operation here allocates tens of GiB of KV/KMV/sort
+  // buffers, so blocks are cached and split/coalesced in user space instead.  All work of a handle is issued
+  // on one stream, so a block freed after its last kernel was enqueued can be handed out again at once:
+  // the next user is ordered behind it on the same stream.
+  struct Block {
+    uint64_t size;
+    int chunk;
+  };
+  std::map<uint8_t *, Block> freeb;                 // free blocks by address (for coalescing)
+  std::multimap<uint64_t, uint8_t *> by_size;       // free blocks by size (best fit)
+  std::map<uint8_t *, Block> used;                  // live blocks
+  std::vector<std::pair<uint8_t *, uint64_t>> chunks;
+  static constexpr uint64_t kGran = 512;
 
   void init(int dev, cudaStream_t s)
   {
     device = dev;
     stream = s;
-    cudaMemPool_t mp;
-    MR_CUDA(cudaDeviceGetDefaultMemPool(&mp, dev));
-    uint64_t thresh = UINT64_MAX;
-    MR_CUDA(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &thresh));
+  }
+  void erase_free(std::map<uint8_t *, Block>::iterator it)
+  {
+    auto r = by_size.equal_range(it->second.size);
+    for (auto j = r.first; j != r.second; ++j)
+      if (j->second == it->first) {
+        by_size.erase(j);
+        break;
+      }
+    freeb.erase(it);
+  }
+  void add_free(uint8_t *p, Block b)
+  {
+    freeb[p] = b;
+    by_size.emplace(b.size, p);
+  }
+  // give wholly-free chunks back to the driver (called when cudaMalloc fails, and at destruction)
+  void trim()
+  {
+    for (size_t c = 0; c < chunks.size(); c++) {
+      if (!chunks[c].first) continue;
+      auto it = freeb.find(chunks[c].first);
+      if (it != freeb.end() && it->second.size == chunks[c].second) {
+        erase_free(it);
+        cudaStreamSynchronize(stream);
+        cudaFree(chunks[c].first);
+        reserved -= chunks[c].second;
+        chunks[c].first = nullptr;
+      }
+    }
   }
   void *alloc(uint64_t bytes)
   {
-    void *p = nullptr;
-    if (bytes == 0) bytes = 256;
-    MR_CUDA(cudaMallocAsync(&p, bytes, stream));
-    live += bytes;
+    if (bytes == 0) bytes = kGran;
+    bytes = (bytes + kGran - 1) / kGran * kGran;
+    auto it = by_size.lower_bound(bytes);
+    uint8_t *p;
+    Block b;
+    if (it != by_size.end()) {
+      p = it->second;
+      auto f = freeb.find(p);
+      b = f->second;
+      erase_free(f);
+    } else {
+      uint64_t csize = (bytes + (2ull << 20) - 1) / (2ull << 20) * (2ull << 20);
+      void *q = nullptr;
+      cudaError_t e = cudaMalloc(&q, csize);
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        trim();
+        e = cudaMalloc(&q, csize);
+      }
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        throw ::mrgpu::Error{-2, "out of GPU memory: cudaMalloc(" + std::to_string(csize) + " bytes) failed with " +
+                                     std::to_string(reserved) + " bytes already reserved by this handle"};
+      }
+      p = (uint8_t *) q;
+      chunks.emplace_back(p, csize);
+      reserved += csize;
+      b = Block{csize, (int) chunks.size() - 1};
+    }
+    if (b.size - bytes >= (1ull << 16)) {  // split, keep the tail free
+      add_free(p + bytes, Block{b.size - bytes, b.chunk});
+      b.size = bytes;
+    }
+    used[p] = b;
+    live += b.size;
     if (live > hiwater) hiwater = live;
     return p;
   }
-  void free(void *p, uint64_t bytes)
+  void free(void *ptr, uint64_t)
   {
-    if (!p) return;
-    if (bytes == 0) bytes = 256;
-    cudaFreeAsync(p, stream);
-    live -= bytes;
+    if (!ptr) return;
+    uint8_t *p = (uint8_t *) ptr;
+    auto u = used.find(p);
+    if (u == used.end()) return;
+    Block b = u->second;
+    used.erase(u);
+    live -= b.size;
+    // coalesce with free neighbours of the same chunk
+    auto nx = freeb.find(p + b.size);
+    if (nx != freeb.end() && nx->second.chunk == b.chunk) {
+      b.size += nx->second.size;
+      erase_free(nx);
+    }
+    auto pv = freeb.lower_bound(p);
+    if (pv != freeb.begin()) {
+      --pv;
+      if (pv->first + pv->second.size == p && pv->second.chunk == b.chunk) {
+        p = pv->first;
+        b.size += pv->second.size;
+        erase_free(pv);
+      }
+    }
+    add_free(p, b);
+  }
+  ~Pool()
+  {
+    if (chunks.empty()) return;
+    cudaStreamSynchronize(stream);
+    for (auto &c : chunks)
+      if (c.first) cudaFree(c.first);
   }
 };
 
