@@ -19,6 +19,7 @@
 #include "hash.cuh"
 #include "radix.cuh"
 #include "scan.cuh"
+#include "flagscan.cuh"
 #include "store.cuh"
 
 using namespace mrgpu;

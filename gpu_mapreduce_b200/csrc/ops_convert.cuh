@@ -207,15 +207,15 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
   (cur ? p0 : p1).release();
 
   // 3. run heads -> number of unique keys U and start[u]
-  auto head = [=] __device__(uint64_t i) -> unsigned long long { return (i == 0 || sk[i] != sk[i - 1]) ? 1ull : 0ull; };
-  ScanTiles heads;
-  scan_tiles(pool, n, head, heads, mr->d_small, "convert_heads_count", (double) n * sizeof(K));
+  auto head = [=] __device__(uint64_t i) -> bool { return i == 0 || sk[i] != sk[i - 1]; };
+  FlagTiles heads;
+  flag_tiles(pool, n, head, heads, mr->d_small, "convert_heads_count", (double) n * sizeof(K));
   fetch_small(mr, 1);
   const uint64_t U = mr->h_small[0];
   Buf<uint32_t> start(pool, U + 1);
   {
     uint32_t *st = start.p;
-    scan_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
+    flag_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
       if (h) st[e] = (uint32_t) i;
     }, "convert_heads_compact", (double) n * sizeof(K) + 4.0 * U);
     uint32_t n32 = (uint32_t) n;
@@ -249,7 +249,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
     Buf<uint8_t> dkey0(pool, kb ? kb : 1);
     if (!ident && kb) MR_CUDA(cudaMemcpyAsync(dkey0.p, key0.data(), kb, cudaMemcpyHostToDevice, s));
     const uint8_t *k0b = dkey0.p;
-    scan_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
+    flag_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
       uint64_t u = e + h - 1;
       uint32_t s0 = st[u];
       uint64_t nv = st[u + 1] - s0, r = i - s0;

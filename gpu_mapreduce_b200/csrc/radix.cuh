@@ -75,7 +75,22 @@ constexpr unsigned long long LB_AGG = 1ull << 62;   // tile-local count publishe
 constexpr unsigned long long LB_INC = 2ull << 62;   // inclusive prefix published
 constexpr unsigned long long LB_VAL = (1ull << 62) - 1;
 
-struct NoPayload {};
+// lanes of the warp holding the same 8-bit digit.  Eight ballots + eight logic ops: measured far cheaper
+// on sm_100a than one MATCH.ANY per key (ncu showed ~half of all stall samples waiting on MATCH results
+// and a pass bound at ~10k cycles per 4096-key tile by the match unit).
+// `sh` = 31 - (bit position of the digit's lowest bit): bit b of the digit is moved to the sign position
+// and smeared, so the per-bit work is shift, shift, setp, vote, one 3-input logic op.
+__device__ __forceinline__ unsigned match_digit(unsigned key_lo32, int sh)
+{
+  unsigned m = 0xFFFFFFFFu;
+#pragma unroll
+  for (int b = 0; b < RADIX_BITS; b++) {
+    int sx = ((int) (key_lo32 << (sh - b))) >> 31;  // 0 or -1
+    unsigned bal = __ballot_sync(0xFFFFFFFFu, sx < 0);
+    m &= ~(bal ^ (unsigned) sx);                      // keep lanes whose bit equals mine
+  }
+  return m;
+}
 
 template <typename K, typename P, int IPT>
 struct SortSmem {
@@ -83,70 +98,65 @@ struct SortSmem {
   static constexpr int XBYTES = (sizeof(K) > sizeof(P) ? sizeof(K) : sizeof(P)) * TILE;
 };
 
-template <typename K, typename P, bool HASP, int IPT>
-__global__ void __launch_bounds__(SORT_THREADS)
-onesweep_kernel(const K *__restrict__ kin, K *__restrict__ kout, const P *__restrict__ pin, P *__restrict__ pout, uint64_t n,
-                int shift, const unsigned long long *__restrict__ gexcl /*[256] exclusive global digit offsets*/,
-                unsigned long long *status /*[ntiles*256]*/, unsigned *tile_counter)
+// The tile body.  FULL = every slot of the tile holds a key (all tiles but the last): no bounds checks.
+// Global positions fit 32 bits (callers cap n below 2^32), so scatter indices are u32 in shared memory and
+// registers.  Instruction count per key matters here: at 148 SMs x 4 issue slots x 1.965 GHz against
+// ~6.5 TB/s a pass that moves 16 B per key has a budget of ~90 thread-instructions per key before it turns
+// issue-bound instead of HBM-bound.
+template <typename K, typename P, bool HASP, int IPT, bool FULL>
+__device__ __forceinline__ void onesweep_tile(const K *__restrict__ kin, K *__restrict__ kout, const P *__restrict__ pin, P *__restrict__ pout,
+                                              uint64_t n, int shift, const unsigned long long *__restrict__ gexcl, unsigned long long *status,
+                                              uint64_t tile, unsigned (*wc)[RADIX], unsigned char *xbuf, unsigned *gbase, unsigned *warp_tot)
 {
   constexpr int TILE = SORT_THREADS * IPT;
-  __shared__ unsigned wc[SORT_WARPS][RADIX];
-  __shared__ __align__(16) unsigned char xbuf[SortSmem<K, P, IPT>::XBYTES];
-  __shared__ unsigned long long gbase[RADIX];
-  __shared__ unsigned dstart[RADIX];
-  __shared__ unsigned warp_tot[SORT_WARPS];
-  __shared__ unsigned s_tile;
-
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
-  // tiles are claimed in launch order so that every tile a look-back waits on is already running
-  if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
-#pragma unroll
-  for (int w = 0; w < SORT_WARPS; w++) wc[w][tid] = 0;
-  __syncthreads();
-  const uint64_t tile = s_tile;
   const uint64_t tbase = tile * TILE;
-  const unsigned nvalid = (unsigned) ((n - tbase) < (uint64_t) TILE ? (n - tbase) : (uint64_t) TILE);
+  const unsigned nvalid = FULL ? (unsigned) TILE : (unsigned) (n - tbase);
+  const unsigned woff0 = warp * (32 * IPT) + lane;  // this lane's first slot in the tile
 
   // ---- load: warp-striped, coalesced; out-of-range slots hold the maximum key
   K key[IPT];
-  const uint64_t wbase = tbase + (uint64_t) warp * (32 * IPT);
+  const K *kp = kin + tbase + woff0;
 #pragma unroll
-  for (int j = 0; j < IPT; j++) {
-    uint64_t i = wbase + j * 32 + lane;
-    key[j] = (i < n) ? kin[i] : (K) ~(K) 0;
-  }
+  for (int j = 0; j < IPT; j++) key[j] = (FULL || woff0 + j * 32 < nvalid) ? kp[j * 32] : (K) ~(K) 0;
 
-  // ---- rank inside the warp, digit by digit, in memory order (stable)
-  unsigned short rank[IPT];
+  // ---- rank inside the warp, digit by digit, in memory order (stable).
+  // (1) all match masks, independent of each other; (2) each group's lowest lane bumps the warp's digit
+  // counter (plain load + store; __syncwarp() orders successive rounds across lanes) and remembers the
+  // old value = the group's base; (3) the base is broadcast from that lane.
+  unsigned peers[IPT], wbase_r[IPT];
+#pragma unroll
+  for (int j = 0; j < IPT; j++) peers[j] = match_digit((unsigned) (key[j] >> (shift & 32)), 31 - (shift & 31));
+  const unsigned lt_mask = lanemask_lt();
 #pragma unroll
   for (int j = 0; j < IPT; j++) {
-    unsigned d = (unsigned) (key[j] >> shift) & 0xFF;
-    unsigned peers = __match_any_sync(0xFFFFFFFFu, d);
-    unsigned lt = __popc(peers & lanemask_lt());
-    unsigned base = 0;
-    if (lt == 0) {
-      base = wc[warp][d];
-      wc[warp][d] = base + __popc(peers);
+    wbase_r[j] = 0;
+    if ((peers[j] & lt_mask) == 0) {
+      unsigned *c = &wc[warp][(unsigned) (key[j] >> shift) & 0xFF];
+      unsigned b = *c;
+      *c = b + __popc(peers[j]);
+      wbase_r[j] = b;
     }
-    base = __shfl_sync(0xFFFFFFFFu, base, __ffs(peers) - 1);
-    rank[j] = (unsigned short) (base + lt);
     __syncwarp();
+  }
+  unsigned rank[IPT];
+#pragma unroll
+  for (int j = 0; j < IPT; j++) {
+    unsigned b = __shfl_sync(0xFFFFFFFFu, wbase_r[j], __ffs(peers[j]) - 1);
+    rank[j] = b + __popc(peers[j] & lt_mask);
   }
   __syncthreads();
 
   // ---- thread d: digit d's count in this tile, and each warp's exclusive offset for it
-  unsigned cnt = 0;
+  unsigned cnt = 0, wex[SORT_WARPS];
 #pragma unroll
   for (int w = 0; w < SORT_WARPS; w++) {
-    unsigned c = wc[w][tid];
-    wc[w][tid] = cnt;
-    cnt += c;
+    wex[w] = cnt;
+    cnt += wc[w][tid];
   }
   // publish for the tiles behind us as early as possible
   unsigned long long *st = status + tile * RADIX + tid;
-  if (tile == 0) atomicExch(st, LB_INC | cnt);
-  else atomicExch(st, LB_AGG | cnt);
+  atomicExch(st, (tile == 0 ? LB_INC : LB_AGG) | cnt);
 
   // exclusive scan of cnt over the 256 digits -> start of each digit's run inside the tile
   unsigned incl = cnt;
@@ -162,56 +172,66 @@ onesweep_kernel(const K *__restrict__ kin, K *__restrict__ kout, const P *__rest
   for (int w = 0; w < SORT_WARPS; w++)
     if (w < warp) woff += warp_tot[w];
   const unsigned my_start = woff + incl - cnt;
-  dstart[tid] = my_start;
+  // wc[w][d] becomes the tile slot where warp w's keys of digit d start
+#pragma unroll
+  for (int w = 0; w < SORT_WARPS; w++) wc[w][tid] = my_start + wex[w];
 
-  // ---- decoupled look-back for digit d
+  // ---- decoupled look-back for digit d.  Predecessor states are read four at a time (independent loads in
+  // flight) and consumed in order; an entry that is not published yet is polled again.
   unsigned long long excl = 0;
   if (tile > 0) {
     long long t = (long long) tile - 1;
-    while (true) {
-      unsigned long long v;
-      const volatile unsigned long long *pv = status + (uint64_t) t * RADIX + tid;
-      do {
-        v = *pv;
-      } while ((v >> 62) == 0);
-      excl += v & LB_VAL;
-      if ((v >> 62) == 2) break;
-      t--;
+    bool done = false;
+    while (!done) {
+      constexpr int W = 4;
+      unsigned long long v[W];
+#pragma unroll
+      for (int q = 0; q < W; q++) {
+        long long tt = t - q;
+        v[q] = tt >= 0 ? *(const volatile unsigned long long *) (status + (uint64_t) tt * RADIX + tid) : LB_INC;
+      }
+#pragma unroll
+      for (int q = 0; q < W; q++) {
+        if (done) break;
+        unsigned f = (unsigned) (v[q] >> 62);
+        if (f == 0) break;  // not there yet: re-read from this entry
+        excl += v[q] & LB_VAL;
+        t--;
+        if (f == 2) done = true;
+      }
     }
     atomicExch(st, LB_INC | (excl + cnt));
   }
-  gbase[tid] = gexcl[tid] + excl - my_start;
+  gbase[tid] = (unsigned) (gexcl[tid] + excl) - my_start;
   __syncthreads();
 
   // ---- stage keys in tile-sorted order
   K *xk = reinterpret_cast<K *>(xbuf);
-  unsigned short pos[IPT];
+  unsigned (&pos)[IPT] = rank;  // same registers: rank -> slot in the tile
 #pragma unroll
   for (int j = 0; j < IPT; j++) {
-    unsigned d = (unsigned) (key[j] >> shift) & 0xFF;
-    pos[j] = (unsigned short) (dstart[d] + wc[warp][d] + rank[j]);
+    pos[j] = wc[warp][(unsigned) (key[j] >> shift) & 0xFF] + rank[j];
     xk[pos[j]] = key[j];
   }
   __syncthreads();
 
   // ---- scatter: consecutive threads write consecutive slots of a digit's run
-  K okey[IPT];
+  unsigned gidx[IPT];
 #pragma unroll
   for (int k = 0; k < IPT; k++) {
     unsigned s = k * SORT_THREADS + tid;
-    if (s < nvalid) {
-      okey[k] = xk[s];
-      unsigned d = (unsigned) (okey[k] >> shift) & 0xFF;
-      kout[gbase[d] + s] = okey[k];
+    if (FULL || s < nvalid) {
+      K kk = xk[s];
+      gidx[k] = gbase[(unsigned) (kk >> shift) & 0xFF] + s;
+      kout[gidx[k]] = kk;
     }
   }
   if constexpr (HASP) {
     P pay[IPT];
+    const P *pp = pin + tbase + woff0;
 #pragma unroll
-    for (int j = 0; j < IPT; j++) {
-      uint64_t i = wbase + j * 32 + lane;
-      if (i < n) pay[j] = pin[i];
-    }
+    for (int j = 0; j < IPT; j++)
+      if (FULL || woff0 + j * 32 < nvalid) pay[j] = pp[j * 32];
     __syncthreads();
     P *xp = reinterpret_cast<P *>(xbuf);
 #pragma unroll
@@ -220,12 +240,34 @@ onesweep_kernel(const K *__restrict__ kin, K *__restrict__ kout, const P *__rest
 #pragma unroll
     for (int k = 0; k < IPT; k++) {
       unsigned s = k * SORT_THREADS + tid;
-      if (s < nvalid) {
-        unsigned d = (unsigned) (okey[k] >> shift) & 0xFF;
-        pout[gbase[d] + s] = xp[s];
-      }
+      if (FULL || s < nvalid) pout[gidx[k]] = xp[s];
     }
   }
+}
+
+template <typename K, typename P, bool HASP, int IPT>
+__global__ void __launch_bounds__(SORT_THREADS, (sizeof(K) == 4 ? 3 : 2))
+onesweep_kernel(const K *__restrict__ kin, K *__restrict__ kout, const P *__restrict__ pin, P *__restrict__ pout, uint64_t n,
+                int shift, const unsigned long long *__restrict__ gexcl /*[256] exclusive global digit offsets*/,
+                unsigned long long *status /*[ntiles*256]*/, unsigned *tile_counter)
+{
+  constexpr int TILE = SORT_THREADS * IPT;
+  __shared__ unsigned wc[SORT_WARPS][RADIX];
+  __shared__ __align__(16) unsigned char xbuf[SortSmem<K, P, IPT>::XBYTES];
+  __shared__ unsigned gbase[RADIX];
+  __shared__ unsigned warp_tot[SORT_WARPS];
+  __shared__ unsigned s_tile;
+  const int tid = threadIdx.x;
+  // tiles are claimed in launch order so that every tile a look-back waits on is already running
+  if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
+#pragma unroll
+  for (int w = 0; w < SORT_WARPS; w++) wc[w][tid] = 0;
+  __syncthreads();
+  const uint64_t tile = s_tile;
+  if ((tile + 1) * TILE <= n)
+    onesweep_tile<K, P, HASP, IPT, true>(kin, kout, pin, pout, n, shift, gexcl, status, tile, wc, xbuf, gbase, warp_tot);
+  else
+    onesweep_tile<K, P, HASP, IPT, false>(kin, kout, pin, pout, n, shift, gexcl, status, tile, wc, xbuf, gbase, warp_tot);
 }
 
 // exclusive scan of each byte's 256-bin histogram, in place; one block per byte
