@@ -89,6 +89,7 @@ def lib():
         "mrgpu_prof_report": [vp, C.c_char_p, C.c_uint64, u64p],
         "mrgpu_hashlittle": [C.c_int, vp, vp, C.c_uint64, C.c_uint32, vp],
         "mrgpu_sort_pairs": [C.c_int, vp, vp, vp, C.c_uint64, C.c_int, C.c_int],
+        "mrgpu_sort_pairs_noalloc": [C.c_int, vp, vp, vp, C.c_uint64, C.c_int, C.c_int],
     }
     for name, args in sig.items():
         f = getattr(L, name)

@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <exception>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -411,6 +412,106 @@ extern "C" int mrgpu_hashlittle(int device, const void *keys, const uint64_t *of
     cudaFree(dk);
     cudaFree(dofs);
     cudaFree(dout);
+  } catch (const Error &e) {
+    g_create_error = e.msg;
+    return e.code;
+  }
+  return MRGPU_OK;
+}
+
+// ================================================================================================
+// Sorting without allocating
+//
+// mrgpu_sort_pairs() takes its ping-pong buffers, histograms and look-back state from the heap of the GPU
+// (cudaMalloc).  Some programs that want this sort are not in a position to do that:
+//   - a host application (a database engine, an inference server, a solver) that grabbed practically all of
+//     the GPU's memory for its own arena at start-up -- a driver allocation made on its behalf later can fail
+//     at a moment nobody can predict, and succeeds only by fragmenting what is left;
+//   - code on a latency-critical path: cudaMalloc and cudaFree synchronise the whole device, so an allocation
+//     in the middle of a request stalls every other stream of the process.
+// For them the scratch lives in the image of this library instead: one file-scope __device__ array, present
+// on every GPU that loads libmrgpu.so from the moment the module is loaded until the process exits (about
+// 16.5 MiB per GPU), big enough for kNoAllocMaxPairs pairs.  The caller still owns the inputs/outputs.
+
+constexpr uint64_t kNoAllocMaxPairs = 1ull << 20;
+constexpr int kNoAllocIpt = 16;
+constexpr uint64_t kNaTiles = kNoAllocMaxPairs / ((uint64_t) SORT_THREADS * kNoAllocIpt);
+constexpr uint64_t kNaOffKeys = 0;                                              // second key buffer, 8 B per pair
+constexpr uint64_t kNaOffPay = kNaOffKeys + 8 * kNoAllocMaxPairs;               // second payload buffer, 8 B per pair
+constexpr uint64_t kNaOffStatus = kNaOffPay + 8 * kNoAllocMaxPairs;             // look-back state, one pass at a time
+constexpr uint64_t kNaOffHist = kNaOffStatus + kNaTiles * RADIX * 8;            // byte histograms / digit offsets
+constexpr uint64_t kNaOffCounter = kNaOffHist + 8 * RADIX * 8;                  // tile ticket
+constexpr uint64_t kNaBytes = kNaOffCounter + 256;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaBytes];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not an address a kernel can use; the
+// device address is looked up once per device and kept here.
+static unsigned char *g_noalloc_dev[64];
+static std::mutex g_noalloc_mu;
+
+static unsigned char *noalloc_scratch(int device)
+{
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (device < 0 || device >= 64) MR_FAIL(MRGPU_EINVAL, "invalid device ordinal");
+  if (!g_noalloc_dev[device]) {
+    unsigned char *p = nullptr;
+    MR_CUDA(cudaGetSymbolAddress((void **) &p, g_noalloc_scratch));  // the current device's copy
+    g_noalloc_dev[device] = p;
+  }
+  return g_noalloc_dev[device];
+}
+
+template <typename K, typename P, bool HASP>
+static void sort_pairs_static(cudaStream_t s, K *k0, P *p0, uint64_t n, unsigned char *scr)
+{
+  K *k1 = (K *) (scr + kNaOffKeys);
+  P *p1 = (P *) (scr + kNaOffPay);
+  unsigned long long *status = (unsigned long long *) (scr + kNaOffStatus);
+  unsigned long long *hist = (unsigned long long *) (scr + kNaOffHist);
+  unsigned *counter = (unsigned *) (scr + kNaOffCounter);
+  const uint64_t ntiles = sort_tiles(n, kNoAllocIpt);
+  // the array still holds whatever the previous call left: everything that is accumulated into starts at zero
+  MR_CUDA(cudaMemsetAsync(hist, 0, sizeof(K) * RADIX * 8, s));
+  radix_hist_kernel<K><<<grid_for(n, 256 * 16, 8), 256, 0, s>>>(k0, n, hist);
+  MR_CUDA(cudaGetLastError());
+  radix_scan_hist_kernel<<<(unsigned) sizeof(K), RADIX, 0, s>>>(hist);
+  MR_CUDA(cudaGetLastError());
+  // every key byte is sorted (no host round trip to find constant bytes): sizeof(K) passes, an even number,
+  // so the sorted pairs end up back in the caller's arrays
+  for (int b = 0; b < (int) sizeof(K); b++) {
+    MR_CUDA(cudaMemsetAsync(status, 0, ntiles * RADIX * 8, s));
+    MR_CUDA(cudaMemsetAsync(counter, 0, 4, s));
+    const K *ki = (b & 1) ? k1 : k0;
+    K *ko = (b & 1) ? k0 : k1;
+    const P *pi = (b & 1) ? p1 : p0;
+    P *po = (b & 1) ? p0 : p1;
+    onesweep_kernel<K, P, HASP, kNoAllocIpt><<<(unsigned) ntiles, SORT_THREADS, 0, s>>>(ki, ko, pi, po, n, 8 * b, hist + b * RADIX, status, counter);
+    MR_CUDA(cudaGetLastError());
+  }
+}
+
+extern "C" int mrgpu_sort_pairs_noalloc(int device, void *stream, void *keys, void *payload, uint64_t n, int key_bytes, int payload_bytes)
+{
+  try {
+    if ((key_bytes != 4 && key_bytes != 8) || (payload_bytes != 0 && payload_bytes != 4 && payload_bytes != 8))
+      MR_FAIL(MRGPU_EINVAL, "mrgpu_sort_pairs_noalloc: key_bytes must be 4 or 8, payload_bytes 0, 4 or 8");
+    if (n > kNoAllocMaxPairs)
+      MR_FAIL(MRGPU_ELIMIT, "mrgpu_sort_pairs_noalloc: " + std::to_string(n) + " pairs exceed the built-in scratch, which holds at most " +
+                                std::to_string(kNoAllocMaxPairs) + " pairs; use mrgpu_sort_pairs (it allocates) for more");
+    if (n && (!keys || (payload_bytes && !payload))) MR_FAIL(MRGPU_EINVAL, "mrgpu_sort_pairs_noalloc: null pointer");
+    MR_CUDA(cudaSetDevice(device));
+    unsigned char *scr = noalloc_scratch(device);
+    cudaStream_t s = (cudaStream_t) stream;
+    if (n) {
+      if (key_bytes == 4 && payload_bytes == 0) sort_pairs_static<uint32_t, uint32_t, false>(s, (uint32_t *) keys, (uint32_t *) nullptr, n, scr);
+      else if (key_bytes == 4 && payload_bytes == 4) sort_pairs_static<uint32_t, uint32_t, true>(s, (uint32_t *) keys, (uint32_t *) payload, n, scr);
+      else if (key_bytes == 4 && payload_bytes == 8) sort_pairs_static<uint32_t, uint64_t, true>(s, (uint32_t *) keys, (uint64_t *) payload, n, scr);
+      else if (key_bytes == 8 && payload_bytes == 0) sort_pairs_static<uint64_t, uint32_t, false>(s, (uint64_t *) keys, (uint32_t *) nullptr, n, scr);
+      else if (key_bytes == 8 && payload_bytes == 4) sort_pairs_static<uint64_t, uint32_t, true>(s, (uint64_t *) keys, (uint32_t *) payload, n, scr);
+      else sort_pairs_static<uint64_t, uint64_t, true>(s, (uint64_t *) keys, (uint64_t *) payload, n, scr);
+    }
+    MR_CUDA(cudaStreamSynchronize(s));
   } catch (const Error &e) {
     g_create_error = e.msg;
     return e.code;

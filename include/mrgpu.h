@@ -196,6 +196,25 @@ int mrgpu_hashlittle(int device, const void *keys, const uint64_t *offsets, uint
 int mrgpu_sort_pairs(int device, void *stream, void *keys, void *payload, uint64_t n, int key_bytes,
                      int payload_bytes);
 
+/* No counterpart in the reference (its sort is a host qsort, nothing there distinguishes callers by whether
+ * they may allocate GPU memory).
+ *
+ * Same result as mrgpu_sort_pairs(), for callers that must not allocate on the GPU: a host application
+ * whose own arena already owns nearly all device memory (a later driver allocation may fail at any time), or a
+ * latency-critical path that cannot take the device-wide synchronisation of cudaMalloc/cudaFree.  This call
+ * makes no cudaMalloc/cudaFree and uses no allocating library routine: the second key/payload buffers, the
+ * digit histograms and the look-back state live in one static __device__ array inside libmrgpu.so (about
+ * 16.5 MiB, resident on every GPU that loads the library until the process exits).  keys/payload stay yours.
+ *  - Limit: n <= 1 048 576 pairs; a larger n fails with MRGPU_ELIMIT and a message that states the limit.
+ *  - The first call on a device looks up the array's device address (one cudaGetSymbolAddress, cached
+ *    afterwards).  Make that first call during start-up, before you begin any stream capture.
+ *  - All calls share the one array per GPU and it keeps the previous call's contents; the call clears what it
+ *    needs cleared.  Two calls whose GPU work overlaps on the same device (different streams or threads) race
+ *    on the scratch and corrupt each other: serialise them.
+ *  - Returns after the stream has drained, like mrgpu_sort_pairs(). */
+int mrgpu_sort_pairs_noalloc(int device, void *stream, void *keys, void *payload, uint64_t n, int key_bytes,
+                             int payload_bytes);
+
 #ifdef __cplusplus
 }
 #endif
