@@ -73,6 +73,7 @@ def lib():
         "mrgpu_map_mr": [vp, vp, C.c_int, C.c_int, u64p],
         "mrgpu_add": [vp, vp, u64p],
         "mrgpu_aggregate": [vp, u64p],
+        "mrgpu_plan_exchange": [C.c_int, C.c_int, u64p, u64p, u64p, u64p, u64p, u64p, C.POINTER(C.c_int)],
         "mrgpu_convert": [vp, u64p],
         "mrgpu_collate": [vp, u64p],
         "mrgpu_reduce": [vp, C.c_int, u64p],

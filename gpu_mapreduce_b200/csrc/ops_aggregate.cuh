@@ -64,9 +64,24 @@ static NcclApi &nccl()
     if (_r != ncclSuccess) throw ::mrgpu::Error{MRGPU_ECOMM, std::string(#expr " failed: ") + nccl().GetErrorString(_r)}; \
   } while (0)
 
+// One NCCL communicator per unique id per process, shared by every handle initialised with that id -- the
+// reference creates any number of MapReduce objects on one MPI communicator (oink/degree.cpp:45-46 uses two),
+// while an NCCL unique id can be turned into a communicator only once.
+struct CommRef {
+  ncclComm_t comm;
+  int refs;
+};
+static std::map<std::string, CommRef> g_comms;
+static std::mutex g_comms_mu;
+
+// A handle only drops its reference; the communicator itself stays cached for the life of the process, because
+// the same unique id may be presented again by a later handle and NCCL accepts an id once.
 static void comm_destroy(mrgpu_mr *mr)
 {
-  if (mr->comm) nccl().CommDestroy((ncclComm_t) mr->comm);
+  if (!mr->comm) return;
+  std::lock_guard<std::mutex> lk(g_comms_mu);
+  for (auto &kvp : g_comms)
+    if (kvp.second.comm == (ncclComm_t) mr->comm && kvp.second.refs > 0) kvp.second.refs--;
   mr->comm = nullptr;
 }
 
@@ -95,11 +110,21 @@ extern "C" int mrgpu_comm_init(mrgpu_mr *mr, int rank, int nranks, const void *i
   mr->nranks = nranks;
   if (nranks > 1) {
     if (!id128) MR_FAIL(MRGPU_EINVAL, "null unique id");
-    ncclUniqueId id;
-    memcpy(&id, id128, 128);
-    ncclComm_t c;
-    MR_NCCL(nccl().CommInitRank(&c, nranks, id, rank));
-    mr->comm = c;
+    std::lock_guard<std::mutex> lk(g_comms_mu);
+    std::string key((const char *) id128, 128);
+    key += std::to_string(mr->device);
+    auto it = g_comms.find(key);
+    if (it != g_comms.end()) {
+      it->second.refs++;
+      mr->comm = it->second.comm;
+    } else {
+      ncclUniqueId id;
+      memcpy(&id, id128, 128);
+      ncclComm_t c;
+      MR_NCCL(nccl().CommInitRank(&c, nranks, id, rank));
+      g_comms[key] = CommRef{c, 1};
+      mr->comm = c;
+    }
   }
   API_END(mr)
 }
@@ -169,6 +194,46 @@ __global__ void sum_kv_bytes_kernel(const uint8_t *__restrict__ data, const uint
   }
 }
 
+// Host-side exchange plan (the part of Irregular::setup src/irregular.cpp:95-242 that survives): from the
+// all-gathered table -- row q = rank q's {records, bytes} for every destination, then its record shape
+// {kind 0 empty / 1 variable / 2 uniform, keybytes<<32|valuebytes} -- rank `me` derives what it receives from
+// each source, the displacements in source-rank order (= the reference's delivery order) and whether the
+// result is still a uniform KV.  Returns 0 = nothing anywhere, 1 = variable records, 2 = uniform (shape set).
+static int plan_exchange(int P, int me, const unsigned long long *table, uint64_t *rcount, uint64_t *rbytes, uint64_t *rdisp /*[P+1]*/,
+                         uint64_t *rrec /*[P+1]*/, uint64_t *shape)
+{
+  const int W = 2 * P + 2;
+  bool all_uniform = true, have_shape = false;
+  unsigned long long sh0 = 0;
+  rdisp[0] = rrec[0] = 0;
+  for (int q = 0; q < P; q++) {
+    rcount[q] = table[(size_t) q * W + 2 * me];
+    rbytes[q] = table[(size_t) q * W + 2 * me + 1];
+    rdisp[q + 1] = rdisp[q] + rbytes[q];
+    rrec[q + 1] = rrec[q] + rcount[q];
+    unsigned long long kind = table[(size_t) q * W + 2 * P], sh = table[(size_t) q * W + 2 * P + 1];
+    if (kind == 1) all_uniform = false;
+    if (kind == 2) {
+      if (have_shape && sh != sh0) all_uniform = false;
+      sh0 = sh;
+      have_shape = true;
+    }
+  }
+  if (shape) *shape = sh0;
+  if (!all_uniform) return 1;
+  return have_shape ? 2 : 0;
+}
+
+// the plan as a C entry point: pure host arithmetic, usable (and tested) without a GPU
+extern "C" int mrgpu_plan_exchange(int nranks, int rank, const uint64_t *table, uint64_t *rcount, uint64_t *rbytes, uint64_t *rdisp,
+                                   uint64_t *rrec, uint64_t *shape, int *kind)
+{
+  if (nranks < 1 || rank < 0 || rank >= nranks || !table || !rcount || !rbytes || !rdisp || !rrec) return MRGPU_EINVAL;
+  int k = plan_exchange(nranks, rank, (const unsigned long long *) table, rcount, rbytes, rdisp, rrec, shape);
+  if (kind) *kind = k;
+  return MRGPU_OK;
+}
+
 static void aggregate_impl(mrgpu_mr *mr)
 {
   freeze(mr);
@@ -187,6 +252,7 @@ static void aggregate_impl(mrgpu_mr *mr)
   Buf<unsigned long long> hist(pool, 8 * RADIX);
   MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
   if (n) {
+    ProfScope ps(pool, "aggregate_partition", (double) kv->nbytes + 8.0 * n);
     partition_dest_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>(kv->data, kv->uniform ? nullptr : kv->offs, kv->recsize, n, al, (uint32_t) P, d0.p,
                                                                 i0.p, hist.p);
     MR_CUDA(cudaGetLastError());
@@ -212,6 +278,7 @@ static void aggregate_impl(mrgpu_mr *mr)
   if (n) {
     if (uni) {
       uint32_t words = kv->recsize / 4;
+      ProfScope ps(pool, "aggregate_pack", 2.0 * kv->nbytes + 4.0 * n);
       gather_uniform_kernel<<<(unsigned) ((n * words + 255) / 256), 256, 0, s>>>((const uint32_t *) kv->data, (uint32_t *) sendbuf.p, perm, n, words);
       MR_CUDA(cudaGetLastError());
       for (int p = 0; p < P; p++) sbytes[p] = scount[p] * kv->recsize;
@@ -253,22 +320,9 @@ static void aggregate_impl(mrgpu_mr *mr)
   MR_CUDA(cudaMemcpyAsync(all.data(), dall.p, (size_t) W * P * 8, cudaMemcpyDeviceToHost, s));
   sync(mr);
   std::vector<uint64_t> rcount(P), rbytes(P), rdisp(P + 1, 0), rrec(P + 1, 0);
-  bool all_uniform = true;
-  unsigned long long shape = 0;
-  bool have_shape = false;
-  for (int q = 0; q < P; q++) {
-    rcount[q] = all[(size_t) q * W + 2 * mr->rank];
-    rbytes[q] = all[(size_t) q * W + 2 * mr->rank + 1];
-    rdisp[q + 1] = rdisp[q] + rbytes[q];
-    rrec[q + 1] = rrec[q] + rcount[q];
-    unsigned long long kind = all[(size_t) q * W + 2 * P], sh = all[(size_t) q * W + 2 * P + 1];
-    if (kind == 1) all_uniform = false;
-    if (kind == 2) {
-      if (have_shape && sh != shape) all_uniform = false;
-      shape = sh;
-      have_shape = true;
-    }
-  }
+  uint64_t shape = 0;
+  int kind = plan_exchange(P, mr->rank, all.data(), rcount.data(), rbytes.data(), rdisp.data(), rrec.data(), &shape);
+  const bool all_uniform = kind != 1, have_shape = kind == 2;
   const uint64_t nrecv = rrec[P], brecv = rdisp[P];
   if (nrecv >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "aggregate: a rank would receive more than 2^32-2 pairs");
 
@@ -286,6 +340,10 @@ static void aggregate_impl(mrgpu_mr *mr)
         MR_CUDA(cudaGetLastError());
       }
     }
+    uint64_t wire = 0;
+    for (int p = 0; p < P; p++)
+      if (p != mr->rank) wire += sbytes[p] > rbytes[p] ? sbytes[p] : rbytes[p];
+    ProfScope psx(pool, "aggregate_exchange_nvlink", (double) wire);
     MR_NCCL(nccl().GroupStart());
     for (int p = 0; p < P; p++) {
       if (p == mr->rank) continue;
@@ -305,7 +363,7 @@ static void aggregate_impl(mrgpu_mr *mr)
 
     nk->nbytes = brecv;
     nk->nkv = nrecv;
-    if (all_uniform && have_shape) {
+    if (have_shape) {
       nk->uniform = true;
       nk->kb = (uint32_t) (shape >> 32);
       nk->vb = (uint32_t) shape;

@@ -129,6 +129,13 @@ int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv);
 /* MapReduce::aggregate(NULL) src/mapreduce.cpp:385-563 + Irregular src/irregular.cpp:95-301: pairs move to
  * rank hashlittle(key,keybytes,nprocs) % nprocs; arrival order = (source rank, original order). */
 int mrgpu_aggregate(mrgpu_mr *mr, uint64_t *nkv);
+/* The host half of Irregular::setup (src/irregular.cpp:95-242): given the all-gathered table of what every
+ * rank sends -- row q (2*nranks+2 u64): {records, bytes} per destination, then {kind 0 empty / 1 variable / 2
+ * uniform, keybytes<<32|valuebytes} -- compute what `rank` receives from each source (rcount, rbytes),
+ * displacements in source-rank order (rdisp, rrec: nranks+1 entries) and the record kind/shape of the result.
+ * Pure host arithmetic; mrgpu_aggregate uses it internally. */
+int mrgpu_plan_exchange(int nranks, int rank, const uint64_t *table, uint64_t *rcount, uint64_t *rbytes,
+                        uint64_t *rdisp, uint64_t *rrec, uint64_t *shape, int *kind);
 /* MapReduce::convert src/mapreduce.cpp:861-886 -> KeyMultiValue::convert src/keymultivalue.cpp:486-638 */
 int mrgpu_convert(mrgpu_mr *mr, uint64_t *nkmv);
 /* MapReduce::collate(NULL) src/mapreduce.cpp:710-738 */

@@ -1,0 +1,38 @@
+"""N > 1 path.  CPU: two gloo ranks exercise the host-side exchange plan of aggregate() (mrgpu_plan_exchange)
+against the reference's delivery rule.  GPU (needs >= 2 devices): the real aggregate/collate over NCCL."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+WORKER = os.path.join(ROOT, "tests", "multi_rank_worker.py")
+
+
+def _launch(nproc, backend, port, timeout=600):
+    env = dict(os.environ, MR_WORKER_BACKEND=backend, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), WORKER]
+    p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
+    assert p.returncode == 0 and "MULTI_OK" in p.stdout, (p.stdout[-2000:], p.stderr[-4000:])
+
+
+def test_exchange_plan_two_gloo_ranks():
+    _launch(2, "gloo", 29611)
+
+
+def test_exchange_plan_three_gloo_ranks():
+    _launch(3, "gloo", 29612)
+
+
+@pytest.mark.gpu
+def test_aggregate_collate_over_nccl():
+    import torch
+
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs (run with gpurun --gpus 2)")
+    _launch(2, "nccl", 29613)
+    if n >= 3:
+        _launch(3, "nccl", 29614)
