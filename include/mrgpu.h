@@ -175,7 +175,8 @@ int mrgpu_kv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst);
 int mrgpu_kmv_page_info(mrgpu_mr *mr, uint64_t ipage, uint64_t *nkey, uint64_t *alignsize, int *is_extended);
 int mrgpu_kmv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst);
 
-/* Device views for callers that stay on the GPU (device functors of their own, torch tensors, bench):
+/* No counterpart in the reference (its pages live in host memory: KeyValue::request_page src/keyvalue.cpp:288).
+ * Device views for callers that stay on the GPU (device functors of their own, torch tensors, bench):
  * base pointer of the packed record stream, its byte length, and the u64 record-offset index
  * (NULL when all records have one size: then record i starts at i * record_bytes). */
 int mrgpu_kv_device_view(mrgpu_mr *mr, const void **data, uint64_t *nbytes, const uint64_t **offsets,
