@@ -1,0 +1,880 @@
+// MapReduce / KeyValue: host-side mirror of the reference's class surface (src/mapreduce.h:22-131,
+// src/keyvalue.h:23-59) over the C-ABI CUDA library.  See mapreduce.h for what runs where.
+// Written from scratch against the reference's documented behaviour (doc/Interface_c++.txt and the
+// file:line sites cited per method); no reference code is reused.
+#include "mapreduce.h"
+
+#include <dirent.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/stat.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/mrgpu.h"
+#include "keyvalue.h"
+#include "mrgpu_functors.h"
+
+#ifndef MRMPI_MEMSIZE
+#define MRMPI_MEMSIZE 64  // src/mapreduce.cpp:80
+#endif
+
+namespace MAPREDUCE_NS {
+
+class KeyMultiValue {};  // opaque: callers only test MapReduce::kmv for NULL
+static KeyMultiValue g_kmv_marker;
+
+MapReduce *MapReduce::mrptr = NULL;
+int MapReduce::instances_now = 0;
+int MapReduce::instances_ever = 0;
+int MapReduce::mpi_finalize_flag = 0;
+uint64_t MapReduce::msize = 0, MapReduce::msizemax = 0;
+uint64_t MapReduce::rsize = 0, MapReduce::wsize = 0;
+uint64_t MapReduce::cssize = 0, MapReduce::crsize = 0;
+double MapReduce::commtime = 0.0;
+
+// ---------------------------------------------------------------------------------------------- stock functors
+// These bodies are never executed: their ADDRESSES select device functors.
+namespace gpu {
+void count(char *, int, char *, int, int *, KeyValue *, void *) {}
+void sum(char *, int, char *, int, int *, KeyValue *, void *) {}
+void cull(char *, int, char *, int, int *, KeyValue *, void *) {}
+void edge_to_vertices(uint64_t, char *, int, char *, int, KeyValue *, void *) {}
+void edge_to_vertex(uint64_t, char *, int, char *, int, KeyValue *, void *) {}
+void invert(uint64_t, char *, int, char *, int, KeyValue *, void *) {}
+}  // namespace gpu
+
+typedef void (*ReduceFn)(char *, int, char *, int, int *, KeyValue *, void *);
+typedef void (*MapMrFn)(uint64_t, char *, int, char *, int, KeyValue *, void *);
+
+static int stock_reduce(ReduceFn f)
+{
+  if (f == gpu::count) return MRGPU_REDUCE_COUNT;
+  if (f == gpu::sum) return MRGPU_REDUCE_SUM;
+  if (f == gpu::cull) return MRGPU_REDUCE_CULL;
+  return -1;
+}
+static int stock_mapmr(MapMrFn f)
+{
+  if (f == gpu::edge_to_vertices) return MRGPU_MAP_EDGE_TO_VERTICES;
+  if (f == gpu::edge_to_vertex) return MRGPU_MAP_EDGE_TO_VERTEX;
+  if (f == gpu::invert) return MRGPU_MAP_INVERT;
+  return -1;
+}
+
+// ---------------------------------------------------------------------------------------------- KeyValue
+
+static const size_t kFlushBytes = 32u << 20;
+
+KeyValue::KeyValue(mrgpu_mr *h) : nkv(0), ksize(0), vsize(0), esize(0), fsize(0), msize(0), page(NULL), memtag(0), npage(0), handle(h) {}
+
+void KeyValue::flush()
+{
+  if (klen.empty()) return;
+  int rc = mrgpu_kv_add(handle, klen.size(), kbuf.data(), klen.data(), -1, vbuf.data(), vlen.data(), -1);
+  if (rc != MRGPU_OK) {
+    printf("ERROR: %s\n", mrgpu_last_error(handle));  // Error::one text from the library, e.g. pair exceeds page
+    fflush(stdout);
+    exit(1);
+  }
+  kbuf.clear();
+  vbuf.clear();
+  klen.clear();
+  vlen.clear();
+}
+
+void KeyValue::add(char *key, int keybytes, char *value, int valuebytes)
+{
+  kbuf.insert(kbuf.end(), key, key + keybytes);
+  if (valuebytes) vbuf.insert(vbuf.end(), value, value + valuebytes);
+  klen.push_back(keybytes);
+  vlen.push_back(valuebytes);
+  if (kbuf.size() + vbuf.size() > kFlushBytes) flush();
+}
+
+void KeyValue::add(int n, char *key, int keybytes, char *value, int valuebytes)
+{
+  for (int i = 0; i < n; i++) add(key + (size_t) i * keybytes, keybytes, value + (size_t) i * valuebytes, valuebytes);
+}
+
+void KeyValue::add(int n, char *key, int *keybytes, char *value, int *valuebytes)
+{
+  for (int i = 0; i < n; i++) {
+    add(key, keybytes[i], value, valuebytes[i]);
+    key += keybytes[i];
+    value += valuebytes[i];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- life cycle
+
+void MapReduce::init(MPI_Comm caller)
+{
+  comm = caller;
+  MPI_Comm_rank(comm, &me);
+  MPI_Comm_size(comm, &nprocs);
+  instances_now++;
+  instances_ever++;
+  // defaults(): src/mapreduce.cpp:196-262
+  mapstyle = 0;
+  all2all = 1;
+  verbosity = 0;
+  timer = 0;
+  memsize = MRMPI_MEMSIZE;
+  minpage = 0;
+  maxpage = 0;
+  freepage = 1;
+  outofcore = 0;
+  zeropage = 0;
+  keyalign = valuealign = 4;
+  fpath = strdup(".");
+  mapfilecount = 0;
+  kv = NULL;
+  kmv = NULL;
+  settings_pushed = 0;
+  kmv_block_valid = 0;
+  blk_buf = NULL;
+  time_start = 0;
+  int device = 0;
+  if (getenv("MRGPU_DEVICE")) device = atoi(getenv("MRGPU_DEVICE"));
+  else if (getenv("LOCAL_RANK")) device = atoi(getenv("LOCAL_RANK"));
+  gpu = NULL;
+  if (mrgpu_create(device, NULL, &gpu) != MRGPU_OK) {
+    printf("ERROR: %s\n", mrgpu_last_error(NULL));
+    fflush(stdout);
+    exit(1);
+  }
+#ifndef MRGPU_MPI_STUB
+  if (nprocs > 1) {  // real MPI: NCCL bootstrap = one broadcast of 128 bytes
+    char id[128];
+    if (me == 0 && mrgpu_comm_unique_id(id) != MRGPU_OK) all(mrgpu_last_error(NULL));
+    MPI_Bcast(id, 128, MPI_BYTE, 0, comm);
+    if (mrgpu_comm_init(gpu, me, nprocs, id) != MRGPU_OK) all(mrgpu_last_error(gpu));
+  }
+#endif
+}
+
+MapReduce::MapReduce(MPI_Comm caller) { init(caller); }
+MapReduce::MapReduce()
+{
+  int flag;
+  MPI_Initialized(&flag);
+  if (!flag) {
+    int argc = 0;
+    char **argv = NULL;
+    MPI_Init(&argc, &argv);
+  }
+  init(MPI_COMM_WORLD);
+}
+MapReduce::MapReduce(double)
+{
+  int flag;
+  MPI_Initialized(&flag);
+  if (!flag) {
+    int argc = 0;
+    char **argv = NULL;
+    MPI_Init(&argc, &argv);
+  }
+  init(MPI_COMM_WORLD);
+  mpi_finalize_flag = 1;
+}
+
+MapReduce::~MapReduce()
+{
+  delete kv;
+  free(fpath);
+  free(blk_buf);
+  if (gpu) mrgpu_destroy(gpu);
+  instances_now--;
+  if (mpi_finalize_flag && instances_now == 0) MPI_Finalize();
+}
+
+void MapReduce::all(const char *str)
+{
+  if (me == 0) {
+    printf("ERROR: %s\n", str);
+    fflush(stdout);
+  }
+  MPI_Finalize();
+  exit(1);
+}
+
+void MapReduce::one(const char *str)
+{
+  char name[MPI_MAX_PROCESSOR_NAME + 1];
+  int len;
+  MPI_Get_processor_name(name, &len);
+  name[len] = '\0';
+  printf("ERROR on proc %d (%s): %s\n", me, name, str);
+  fflush(stdout);
+  MPI_Abort(comm, 1);
+}
+
+uint64_t MapReduce::ck(int rc, uint64_t n)
+{
+  if (rc != MRGPU_OK) all(mrgpu_last_error(gpu));
+  return n;
+}
+
+// settings are public ints the caller may change until first use (src/mapreduce.cpp:3318-3357)
+void MapReduce::push_settings()
+{
+  if (settings_pushed) return;
+  settings_pushed = 1;
+  ck(mrgpu_set(gpu, "memsize", memsize), 0);
+  ck(mrgpu_set(gpu, "keyalign", keyalign), 0);
+  ck(mrgpu_set(gpu, "valuealign", valuealign), 0);
+}
+
+void MapReduce::set_fpath(const char *str)
+{
+  free(fpath);
+  fpath = strdup(str);  // kept for compatibility; nothing is spilled to files
+}
+
+void MapReduce::start_timer()
+{
+  if (timer) MPI_Barrier(comm);
+  time_start = MPI_Wtime();
+}
+
+// src/mapreduce.cpp:3112-3165: "<Op> time (secs) = t" then, with verbosity, the size line of the result
+void MapReduce::stats(const char *heading, int which)
+{
+  if (timer) {
+    MPI_Barrier(comm);
+    if (me == 0) printf("%s time (secs) = %g\n", heading, MPI_Wtime() - time_start);
+  }
+  if (verbosity == 0) return;
+  if (me == 0) printf("%s: ", heading);
+  if (which == 0) kv_stats(1);
+  else kmv_stats(1);
+}
+
+void MapReduce::sync_kv_fields()
+{
+  if (!kv) return;
+  mrgpu_stats s;
+  if (mrgpu_kv_stats(gpu, &s) != MRGPU_OK) return;
+  kv->nkv = s.npair;
+  kv->ksize = s.keysize;
+  kv->vsize = s.valuesize;
+  kv->esize = s.exactsize;
+  kv->npage = (int) s.npage;
+}
+
+uint64_t MapReduce::kv_stats(int level)
+{
+  if (kv == NULL) all("Cannot print stats without KeyValue");
+  mrgpu_stats s;
+  ck(mrgpu_kv_stats(gpu, &s), 0);
+  const double mbyte = 1024.0 * 1024.0;
+  // single rank or counts already global through the op return values; sizes are this rank's
+  if (level >= 1 && me == 0)
+    printf("%lu pairs, %.3g Mb keys, %.3g Mb values, %.3g Mb, %d pages\n", (unsigned long) s.npair, s.keysize / mbyte, s.valuesize / mbyte,
+           s.exactsize / mbyte, (int) s.npage);
+  return s.npair;
+}
+
+uint64_t MapReduce::kmv_stats(int level)
+{
+  if (kmv == NULL) all("Cannot print stats without KeyMultiValue");
+  mrgpu_stats s;
+  ck(mrgpu_kmv_stats(gpu, &s), 0);
+  const double mbyte = 1024.0 * 1024.0;
+  if (level >= 1 && me == 0)
+    printf("%lu pairs, %.3g Mb keys, %.3g Mb values, %.3g Mb, %d pages\n", (unsigned long) s.npair, s.keysize / mbyte, s.valuesize / mbyte,
+           s.exactsize / mbyte, (int) s.npage);
+  return s.npair;
+}
+
+void MapReduce::cummulative_stats(int, int) {}
+
+// ---------------------------------------------------------------------------------------------- page walks
+
+static inline uint64_t ru(uint64_t x, int a) { return (x + a - 1) / a * a; }
+
+// calls f(key, keybytes, value, valuebytes) for every pair of handle h, page by page (src/mapreduce.cpp:1949-1967)
+template <typename F>
+void MapReduce::walk_kv(mrgpu_mr *h, F f)
+{
+  mrgpu_stats s;
+  ck(mrgpu_kv_stats(h, &s), 0);
+  const int ka = keyalign, va = valuealign, ta = std::max(std::max(ka, va), 4);
+  std::vector<char> page;
+  for (uint64_t ip = 0; ip < s.npage; ip++) {
+    uint64_t nkey, asz;
+    ck(mrgpu_kv_page_info(h, ip, &nkey, NULL, NULL, &asz), 0);
+    page.resize(asz ? asz : 1);
+    ck(mrgpu_kv_page_copy(h, ip, page.data()), 0);
+    uint64_t p = 0;
+    for (uint64_t i = 0; i < nkey; i++) {
+      int kb = *(int *) &page[p], vb = *(int *) &page[p + 4];
+      uint64_t k0 = ru(p + 8, ka), v0 = ru(k0 + kb, va);
+      f(&page[k0], kb, &page[v0], vb);
+      p = ru(v0 + vb, ta);
+    }
+  }
+}
+
+// calls f(key, keybytes, multivalue, nvalues, valuesizes) for every KMV pair; a pair bigger than a page is
+// presented through the reference's block protocol (multivalue == NULL, nvalues == 0, valuesizes == (int*)this;
+// src/mapreduce.cpp:1828-1848)
+template <typename F>
+void MapReduce::walk_kmv(mrgpu_mr *h, F f)
+{
+  mrgpu_stats s;
+  ck(mrgpu_kmv_stats(h, &s), 0);
+  const int ka = keyalign, va = valuealign, ta = std::max(std::max(ka, va), 4);
+  int64_t ms = memsize;
+  const uint64_t pagesize = ms > 0 ? (uint64_t) ms << 20 : (uint64_t) (-ms);
+  std::vector<char> page;
+  for (uint64_t ip = 0; ip < s.npage; ip++) {
+    uint64_t nkey, asz;
+    int ext;
+    ck(mrgpu_kmv_page_info(h, ip, &nkey, &asz, &ext), 0);
+    page.resize(asz ? asz : 1);
+    ck(mrgpu_kmv_page_copy(h, ip, page.data()), 0);
+    uint64_t p = 0;
+    for (uint64_t i = 0; i < nkey; i++) {
+      int nv = *(int *) &page[p], kb = *(int *) &page[p + 4], mvb = *(int *) &page[p + 8];
+      int *sizes = (int *) &page[p + 12];
+      uint64_t k0 = ru(p + 12 + 4 * (uint64_t) nv, ka), v0 = ru(k0 + kb, va);
+      if (!ext) {
+        f(&page[k0], kb, &page[v0], nv, sizes);
+      } else {
+        kmv_block_valid = 1;
+        kmv_nvalue_total = (uint64_t) nv;
+        blk_capacity = std::max<uint64_t>(1, pagesize / 2 / sizeof(int) - 1);  // src/keymultivalue.cpp:1241-1242
+        kmv_nblock = (int) ((kmv_nvalue_total + blk_capacity - 1) / blk_capacity);
+        blk_sizes_base = (const char *) sizes;
+        blk_values_base = &page[v0];
+        f(&page[k0], kb, (char *) NULL, 0, (int *) this);
+        kmv_block_valid = 0;
+      }
+      p = ru(v0 + (uint64_t) mvb, ta);
+    }
+  }
+}
+
+uint64_t MapReduce::multivalue_blocks(int &nblock)
+{
+  if (!kmv_block_valid) one("Invalid call to multivalue_blocks()");
+  nblock = kmv_nblock;
+  return kmv_nvalue_total;
+}
+
+void MapReduce::multivalue_block_select(int which)
+{
+  if (!kmv_block_valid) one("Invalid call to multivalue_block_select()");
+  if (which != 1 && which != 2) one("Invalid arg to multivalue_block_select()");
+}
+
+int MapReduce::multivalue_block(int iblock, char **pmultivalue, int **pvaluesizes)
+{
+  if (!kmv_block_valid) one("Invalid call to multivalue_block()");
+  if (iblock < 0 || iblock >= kmv_nblock) one("Invalid page request to multivalue_block()");
+  const int *sizes = (const int *) blk_sizes_base;
+  uint64_t first = (uint64_t) iblock * blk_capacity;
+  uint64_t n = std::min<uint64_t>(blk_capacity, kmv_nvalue_total - first);
+  uint64_t off = 0;
+  for (uint64_t i = 0; i < first; i++) off += sizes[i];
+  *pvaluesizes = (int *) (sizes + first);
+  *pmultivalue = (char *) blk_values_base + off;
+  return (int) n;
+}
+
+// ---------------------------------------------------------------------------------------------- emit helpers
+
+KeyValue *MapReduce::begin_emit(mrgpu_mr *target, int addflag)
+{
+  if (mrgpu_kv_open(target, addflag) != MRGPU_OK) all(mrgpu_last_error(target));
+  return new KeyValue(target);
+}
+
+uint64_t MapReduce::end_emit(mrgpu_mr *target, KeyValue *k)
+{
+  k->flush();
+  delete k;
+  uint64_t n = 0;
+  if (mrgpu_kv_close(target, &n) != MRGPU_OK) all(mrgpu_last_error(target));
+  return n;
+}
+
+// a second handle on the same device with the same layout settings: host callbacks that consume this
+// object's KV/KMV emit into it, then the result is moved over (the reference builds a new KV beside the old
+// one in the same way, e.g. src/mapreduce.cpp:1584-1602)
+static mrgpu_mr *make_side_handle(MapReduce *mr, int memsize, int keyalign, int valuealign)
+{
+  mrgpu_mr *t = NULL;
+  int device = 0;
+  if (getenv("MRGPU_DEVICE")) device = atoi(getenv("MRGPU_DEVICE"));
+  else if (getenv("LOCAL_RANK")) device = atoi(getenv("LOCAL_RANK"));
+  if (mrgpu_create(device, NULL, &t) != MRGPU_OK) return NULL;
+  mrgpu_set(t, "memsize", memsize);
+  mrgpu_set(t, "keyalign", keyalign);
+  mrgpu_set(t, "valuealign", valuealign);
+  (void) mr;
+  return t;
+}
+
+// ---------------------------------------------------------------------------------------------- map
+
+// task ids of this rank: mapstyle 0 = contiguous chunk, 1 = strided (src/mapreduce.cpp:1136-1170);
+// 2 (master/slave) degenerates to chunks -- tasks are independent, only their placement differs
+static void my_tasks(int nmap, int me, int nprocs, int mapstyle, std::vector<int> &out)
+{
+  if (mapstyle == 1) {
+    for (int i = me; i < nmap; i += nprocs) out.push_back(i);
+  } else {
+    uint64_t lo = (uint64_t) me * nmap / nprocs, hi = (uint64_t) (me + 1) * nmap / nprocs;
+    for (uint64_t i = lo; i < hi; i++) out.push_back((int) i);
+  }
+}
+
+uint64_t MapReduce::map(int nmap, void (*appmap)(int, KeyValue *, void *), void *ptr, int addflag)
+{
+  push_settings();
+  start_timer();
+  KeyValue *out = begin_emit(gpu, addflag);
+  std::vector<int> tasks;
+  my_tasks(nmap, me, nprocs, mapstyle, tasks);
+  for (size_t i = 0; i < tasks.size(); i++) appmap(tasks[i], out, ptr);
+  uint64_t n = end_emit(gpu, out);
+  delete kv;
+  kv = new KeyValue(gpu);
+  kmv = NULL;
+  sync_kv_fields();
+  stats("Map", 0);
+  return n;
+}
+
+static void list_files(const std::string &path, int recurse, std::vector<std::string> &out)
+{
+  struct stat st;
+  if (stat(path.c_str(), &st) != 0) return;
+  if (S_ISDIR(st.st_mode)) {
+    DIR *d = opendir(path.c_str());
+    if (!d) return;
+    std::vector<std::string> names;
+    while (struct dirent *e = readdir(d)) {
+      if (e->d_name[0] == '.') continue;
+      names.push_back(e->d_name);
+    }
+    closedir(d);
+    std::sort(names.begin(), names.end());
+    for (size_t i = 0; i < names.size(); i++) {
+      std::string child = path + "/" + names[i];
+      struct stat cs;
+      if (stat(child.c_str(), &cs) != 0) continue;
+      if (S_ISDIR(cs.st_mode)) {
+        if (recurse) list_files(child, recurse, out);
+      } else
+        out.push_back(child);
+    }
+  } else
+    out.push_back(path);
+}
+
+// map(nstr, strings, self, recurse, readfile, mymap, ptr, addflag): src/mapreduce.cpp:1060-1092.  Each string
+// is a file, a directory (expanded, recursively if asked) or, with readfile, a file listing one name per line.
+uint64_t MapReduce::map(int nstr, char **strings, int self, int recurse, int readfile, void (*appmap)(int, char *, KeyValue *, void *), void *ptr,
+                        int addflag)
+{
+  push_settings();
+  start_timer();
+  std::vector<std::string> files;
+  for (int i = 0; i < nstr; i++) {
+    if (readfile) {
+      FILE *fp = fopen(strings[i], "r");
+      if (!fp) one("Could not open file of file names");
+      char line[4096];
+      while (fgets(line, sizeof(line), fp)) {
+        char *w = strtok(line, " \t\n\f\r");
+        if (w) list_files(w, recurse, files);
+      }
+      fclose(fp);
+    } else
+      list_files(strings[i], recurse, files);
+  }
+  (void) self;
+  mapfilecount = (int) files.size();
+  KeyValue *out = begin_emit(gpu, addflag);
+  std::vector<int> tasks;
+  my_tasks((int) files.size(), me, nprocs, mapstyle, tasks);
+  for (size_t i = 0; i < tasks.size(); i++) appmap(tasks[i], (char *) files[tasks[i]].c_str(), out, ptr);
+  uint64_t n = end_emit(gpu, out);
+  delete kv;
+  kv = new KeyValue(gpu);
+  kmv = NULL;
+  sync_kv_fields();
+  stats("Map", 0);
+  return n;
+}
+
+uint64_t MapReduce::map(int, int, char **, int, int, char, int, void (*)(int, char *, int, KeyValue *, void *), void *, int)
+{
+  all("map() of file chunks is not built in the GPU library (SURVEY.md 8f)");
+  return 0;
+}
+uint64_t MapReduce::map(int, int, char **, int, int, char *, int, void (*)(int, char *, int, KeyValue *, void *), void *, int)
+{
+  all("map() of file chunks is not built in the GPU library (SURVEY.md 8f)");
+  return 0;
+}
+
+// map(mr2, mymap, ptr, addflag): src/mapreduce.cpp:1560-1642
+uint64_t MapReduce::map(MapReduce *mr, MapMrFn appmap, void *ptr, int addflag)
+{
+  if (mr->kv == NULL) all("MapReduce passed to map() does not have KeyValue pairs");
+  push_settings();
+  mr->push_settings();
+  start_timer();
+  uint64_t n = 0;
+  int f = stock_mapmr(appmap);
+  if (f >= 0) {
+    ck(mrgpu_map_mr(gpu, mr->gpu, f, addflag, &n), 0);
+  } else if (mr == this) {
+    mrgpu_mr *side = make_side_handle(this, memsize, keyalign, valuealign);
+    if (!side) all(mrgpu_last_error(NULL));
+    KeyValue *out = begin_emit(side, 0);
+    uint64_t itask = 0;
+    walk_kv(gpu, [&](char *k, int kb, char *v, int vb) { appmap(itask++, k, kb, v, vb, out, ptr); });
+    end_emit(side, out);
+    ck(mrgpu_kv_open(gpu, 0), 0);  // drops the old KV
+    ck(mrgpu_kv_close(gpu, &n), 0);
+    ck(mrgpu_add(gpu, side, &n), 0);
+    mrgpu_destroy(side);
+  } else {
+    KeyValue *out = begin_emit(gpu, addflag);
+    uint64_t itask = 0;
+    walk_kv(mr->gpu, [&](char *k, int kb, char *v, int vb) { appmap(itask++, k, kb, v, vb, out, ptr); });
+    n = end_emit(gpu, out);
+  }
+  delete kv;
+  kv = new KeyValue(gpu);
+  kmv = NULL;
+  sync_kv_fields();
+  stats("Map", 0);
+  return n;
+}
+
+// open()/close(): src/mapreduce.cpp:1650-1669 -- pairs added to mr->kv between the two calls
+void MapReduce::open(int addflag)
+{
+  push_settings();
+  ck(mrgpu_kv_open(gpu, addflag), 0);
+  delete kv;
+  kv = new KeyValue(gpu);
+  kmv = NULL;
+}
+
+uint64_t MapReduce::close()
+{
+  if (!kv) all("Cannot close without KeyValue");
+  kv->flush();
+  uint64_t n = 0;
+  ck(mrgpu_kv_close(gpu, &n), 0);
+  sync_kv_fields();
+  return n;
+}
+
+// ---------------------------------------------------------------------------------------------- the hot path
+
+uint64_t MapReduce::add(MapReduce *mr)
+{
+  if (mr->kv == NULL) all("MapReduce passed to add() does not have KeyValue pairs");
+  if (mr == this) all("Cannot add to self");
+  if (kmv) all("Cannot add to a MapReduce with KeyMultiValue pairs");
+  push_settings();
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_add(gpu, mr->gpu, &n), 0);
+  if (!kv) kv = new KeyValue(gpu);
+  sync_kv_fields();
+  stats("Add", 0);
+  return n;
+}
+
+uint64_t MapReduce::aggregate(int (*hash)(char *, int))
+{
+  if (kv == NULL) all("Cannot aggregate without KeyValue");
+  if (hash && nprocs > 1) all("aggregate() with a user hash function runs on the host and is not built for more than one rank");
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_aggregate(gpu, &n), 0);
+  sync_kv_fields();
+  stats("Aggregate", 0);
+  return n;
+}
+
+uint64_t MapReduce::convert()
+{
+  if (kv == NULL) all("Cannot convert without KeyValue");
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_convert(gpu, &n), 0);
+  delete kv;
+  kv = NULL;
+  kmv = &g_kmv_marker;
+  stats("Convert", 1);
+  return n;
+}
+
+uint64_t MapReduce::collate(int (*hash)(char *, int))
+{
+  if (kv == NULL) all("Cannot collate without KeyValue");
+  if (hash && nprocs > 1) all("collate() with a user hash function runs on the host and is not built for more than one rank");
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_collate(gpu, &n), 0);
+  delete kv;
+  kv = NULL;
+  kmv = &g_kmv_marker;
+  stats("Collate", 1);
+  return n;
+}
+
+uint64_t MapReduce::reduce_impl(ReduceFn appreduce, void *ptr, const char *heading)
+{
+  uint64_t n = 0;
+  int f = stock_reduce(appreduce);
+  if (f >= 0) {
+    ck(mrgpu_reduce(gpu, f, &n), 0);
+  } else {
+    mrgpu_mr *side = make_side_handle(this, memsize, keyalign, valuealign);
+    if (!side) all(mrgpu_last_error(NULL));
+    KeyValue *out = begin_emit(side, 0);
+    walk_kmv(gpu, [&](char *k, int kb, char *mv, int nv, int *sizes) { appreduce(k, kb, mv, nv, sizes, out, ptr); });
+    end_emit(side, out);
+    ck(mrgpu_kv_open(gpu, 0), 0);  // drops the KMV, leaves an empty KV
+    ck(mrgpu_kv_close(gpu, &n), 0);
+    ck(mrgpu_add(gpu, side, &n), 0);
+    mrgpu_destroy(side);
+  }
+  kmv = NULL;
+  delete kv;
+  kv = new KeyValue(gpu);
+  sync_kv_fields();
+  stats(heading, 0);
+  return n;
+}
+
+uint64_t MapReduce::reduce(ReduceFn appreduce, void *ptr)
+{
+  if (kmv == NULL) all("Cannot reduce without KeyMultiValue");
+  start_timer();
+  return reduce_impl(appreduce, ptr, "Reduce");
+}
+
+// compress(): convert + reduce on this rank's pairs only, no communication (src/mapreduce.cpp:749-851)
+uint64_t MapReduce::compress(ReduceFn appcompress, void *ptr)
+{
+  if (kv == NULL) all("Cannot compress without KeyValue");
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_convert(gpu, &n), 0);
+  delete kv;
+  kv = NULL;
+  kmv = &g_kmv_marker;
+  return reduce_impl(appcompress, ptr, "Compress");
+}
+
+uint64_t MapReduce::scan(void (*appscan)(char *, int, char *, int, void *), void *ptr)
+{
+  if (kv == NULL) all("Cannot scan without KeyValue");
+  start_timer();
+  walk_kv(gpu, [&](char *k, int kb, char *v, int vb) { appscan(k, kb, v, vb, ptr); });
+  stats("Scan", 0);
+  return kv_stats(0);
+}
+
+uint64_t MapReduce::scan(void (*appscan)(char *, int, char *, int, int *, void *), void *ptr)
+{
+  if (kmv == NULL) all("Cannot scan without KeyMultiValue");
+  start_timer();
+  walk_kmv(gpu, [&](char *k, int kb, char *mv, int nv, int *sizes) { appscan(k, kb, mv, nv, sizes, ptr); });
+  stats("Scan", 1);
+  return kmv_stats(0);
+}
+
+// ---------------------------------------------------------------------------------------------- sorting
+
+uint64_t MapReduce::sort_keys(int flag)
+{
+  if (kv == NULL) all("Cannot sort_keys without KeyValue");
+  int a = flag < 0 ? -flag : flag;
+  if (a < 1 || a > 6) all("Invalid compare method for sort keys");
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_sort_keys(gpu, flag, &n), 0);
+  sync_kv_fields();
+  stats("Sort_keys", 0);
+  return n;
+}
+
+// the built-in comparisons of src/mapreduce.cpp:2692-2802, restated, for sort_values(flag)
+static int cmp_builtin(int flag, char *p1, int l1, char *p2, int l2)
+{
+  int a = flag < 0 ? -flag : flag, c = 0;
+  if (a == 1) {
+    int x, y;
+    memcpy(&x, p1, 4);
+    memcpy(&y, p2, 4);
+    c = x < y ? -1 : (x > y);
+  } else if (a == 2) {
+    uint64_t x, y;
+    memcpy(&x, p1, 8);
+    memcpy(&y, p2, 8);
+    c = x < y ? -1 : (x > y);
+  } else if (a == 3) {
+    float x, y;
+    memcpy(&x, p1, 4);
+    memcpy(&y, p2, 4);
+    c = x < y ? -1 : (x > y);
+  } else if (a == 4) {
+    double x, y;
+    memcpy(&x, p1, 8);
+    memcpy(&y, p2, 8);
+    c = x < y ? -1 : (x > y);
+  } else if (a == 5)
+    c = strcmp(p1, p2);
+  else
+    c = strncmp(p1, p2, l1 < l2 ? l1 : l2);
+  return flag < 0 ? -c : c;
+}
+
+// A user compare function is host code: the pairs come to the host, are stably sorted (the reference's
+// qsort is a merge sort here) and go back.  by_value = 0 sorts by key, 1 by value.
+static int g_sort_flag = 0;
+static int cmp_flag_tramp(char *a, int la, char *b, int lb) { return cmp_builtin(g_sort_flag, a, la, b, lb); }
+
+uint64_t MapReduce::host_sort(int (*appcompare)(char *, int, char *, int), int by_value)
+{
+  struct Rec {
+    size_t koff, voff;
+    int kb, vb;
+  };
+  std::vector<char> pool;
+  std::vector<Rec> recs;
+  walk_kv(gpu, [&](char *k, int kb, char *v, int vb) {
+    Rec r;
+    r.koff = pool.size();
+    pool.insert(pool.end(), k, k + kb);
+    pool.push_back(0);  // callers' compare functions may read a terminating NUL that sits in the padding
+    r.voff = pool.size();
+    pool.insert(pool.end(), v, v + vb);
+    pool.push_back(0);
+    r.kb = kb;
+    r.vb = vb;
+    recs.push_back(r);
+  });
+  std::stable_sort(recs.begin(), recs.end(), [&](const Rec &x, const Rec &y) {
+    if (by_value) return appcompare(&pool[x.voff], x.vb, &pool[y.voff], y.vb) < 0;
+    return appcompare(&pool[x.koff], x.kb, &pool[y.koff], y.kb) < 0;
+  });
+  KeyValue *out = begin_emit(gpu, 0);
+  for (size_t i = 0; i < recs.size(); i++) out->add(&pool[recs[i].koff], recs[i].kb, &pool[recs[i].voff], recs[i].vb);
+  uint64_t n = end_emit(gpu, out);
+  sync_kv_fields();
+  return n;
+}
+
+uint64_t MapReduce::sort_keys(int (*appcompare)(char *, int, char *, int))
+{
+  if (kv == NULL) all("Cannot sort_keys without KeyValue");
+  start_timer();
+  uint64_t n = host_sort(appcompare, 0);
+  stats("Sort_keys", 0);
+  return n;
+}
+
+uint64_t MapReduce::sort_values(int (*appcompare)(char *, int, char *, int))
+{
+  if (kv == NULL) all("Cannot sort_values without KeyValue");
+  start_timer();
+  uint64_t n = host_sort(appcompare, 1);
+  stats("Sort_values", 0);
+  return n;
+}
+
+uint64_t MapReduce::sort_values(int flag)
+{
+  if (kv == NULL) all("Cannot sort_values without KeyValue");
+  int a = flag < 0 ? -flag : flag;
+  if (a < 1 || a > 6) all("Invalid compare method for sort values");
+  g_sort_flag = flag;
+  start_timer();
+  uint64_t n = host_sort(cmp_flag_tramp, 1);
+  stats("Sort_values", 0);
+  return n;
+}
+
+uint64_t MapReduce::sort_multivalues(int)
+{
+  all("sort_multivalues() is not built in the GPU library (SURVEY.md 8f)");
+  return 0;
+}
+uint64_t MapReduce::sort_multivalues(int (*)(char *, int, char *, int))
+{
+  all("sort_multivalues() is not built in the GPU library (SURVEY.md 8f)");
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- the rest
+
+// gather(n): with one rank every pair already lives on rank 0 (src/mapreduce.cpp:893-905 returns early)
+uint64_t MapReduce::gather(int numprocs)
+{
+  if (kv == NULL) all("Cannot gather without KeyValue");
+  if (numprocs < 1 || numprocs > nprocs) all("Invalid processor count for gather");
+  if (nprocs == 1 || numprocs == nprocs) return kv_stats(0);
+  all("gather() across ranks is not built in the GPU library (SURVEY.md 8f)");
+  return 0;
+}
+
+MapReduce *MapReduce::copy()
+{
+  MapReduce *m = new MapReduce(comm);
+  m->mapstyle = mapstyle;
+  m->all2all = all2all;
+  m->verbosity = verbosity;
+  m->timer = timer;
+  m->memsize = memsize;
+  m->minpage = minpage;
+  m->maxpage = maxpage;
+  m->keyalign = keyalign;
+  m->valuealign = valuealign;
+  if (kmv) all("copy() of a MapReduce holding KeyMultiValue pairs is not built in the GPU library");
+  if (kv) m->add(this);
+  return m;
+}
+
+uint64_t MapReduce::broadcast(int)
+{
+  if (nprocs == 1) return kv ? kv_stats(0) : 0;
+  all("broadcast() is not built in the GPU library (SURVEY.md 8f)");
+  return 0;
+}
+uint64_t MapReduce::clone()
+{
+  all("clone() is not built in the GPU library (SURVEY.md 8f)");
+  return 0;
+}
+uint64_t MapReduce::collapse(char *, int)
+{
+  all("collapse() is not built in the GPU library (SURVEY.md 8f)");
+  return 0;
+}
+uint64_t MapReduce::scrunch(int, char *, int)
+{
+  all("scrunch() is not built in the GPU library (SURVEY.md 8f)");
+  return 0;
+}
+void MapReduce::print(int, int, int, int) { all("print() is not built in the GPU library (SURVEY.md 8f)"); }
+void MapReduce::print(char *, int, int, int, int, int) { all("print() is not built in the GPU library (SURVEY.md 8f)"); }
+
+}  // namespace MAPREDUCE_NS

@@ -1,0 +1,55 @@
+/* Minimal single-process stand-in for <mpi.h>, for building reference callers (examples/wordfreq.cpp,
+ * examples/rmat.cpp, cpu/IntCount.cpp ...) against this library on a box without MPI -- the role the
+ * reference's own mpistubs/ plays (mpistubs/mpi.h:19-125).  Written from scratch; only what those callers
+ * use.  One process = rank 0 of 1.  With a real MPI, use its mpi.h instead: MapReduce(MPI_Comm) then
+ * bootstraps NCCL with one MPI_Bcast of 128 bytes. */
+#ifndef MRGPU_MPI_STUB_H
+#define MRGPU_MPI_STUB_H
+
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/time.h>
+
+typedef int MPI_Comm;
+#define MPI_COMM_WORLD 0
+#define MPI_MAX_PROCESSOR_NAME 128
+#define MRGPU_MPI_STUB 1
+
+static inline int MPI_Init(int *, char ***) { return 0; }
+static inline int MPI_Initialized(int *flag)
+{
+  *flag = 1;
+  return 0;
+}
+static inline int MPI_Finalize() { return 0; }
+static inline int MPI_Comm_rank(MPI_Comm, int *me)
+{
+  *me = 0;
+  return 0;
+}
+static inline int MPI_Comm_size(MPI_Comm, int *n)
+{
+  *n = 1;
+  return 0;
+}
+static inline int MPI_Barrier(MPI_Comm) { return 0; }
+static inline int MPI_Abort(MPI_Comm, int code)
+{
+  exit(code);
+  return 0;
+}
+static inline double MPI_Wtime()
+{
+  struct timeval tv;
+  gettimeofday(&tv, NULL);
+  return tv.tv_sec + 1.0e-6 * tv.tv_usec;
+}
+static inline int MPI_Get_processor_name(char *name, int *len)
+{
+  strcpy(name, "gpu");
+  *len = 3;
+  return 0;
+}
+
+#endif

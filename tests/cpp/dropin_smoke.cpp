@@ -1,0 +1,192 @@
+// One caller, two libraries.  This program is written against the MR-MPI class API only
+// (MapReduce / KeyValue, function-pointer callbacks); oracle/Makefile links it with the unmodified reference
+// library, __graft_entry__.build() links the very same source with the GPU library's mirror classes.
+// tests/test_cpp_dropin.py runs both and requires identical output.
+#include "mpi.h"
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stdint.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+#include "mapreduce.h"
+#include "keyvalue.h"
+
+using namespace MAPREDUCE_NS;
+
+static uint64_t rng_state = 12345;
+static uint32_t rnd()
+{
+  rng_state = rng_state * 6364136223846793005ULL + 1442695040888963407ULL;
+  return (uint32_t) (rng_state >> 33);
+}
+
+// map task: emit words with a small-int value
+static void gen(int itask, KeyValue *kv, void *ptr)
+{
+  int n = *(int *) ptr;
+  for (int i = 0; i < n; i++) {
+    char word[32];
+    int w = rnd() % 300;
+    int len = sprintf(word, "w%d_%d", w % 7, w);
+    int val = itask * 1000 + i;
+    kv->add(word, len + 1, (char *) &val, sizeof(int));
+  }
+}
+
+// hot key: one key with very many values -> multi-block KMV with small pages
+static void gen_hot(int itask, KeyValue *kv, void *ptr)
+{
+  int n = *(int *) ptr;
+  for (int i = 0; i < n; i++) {
+    int key = (i % 10 == 3) ? 100 + (i / 10) % 7 : 7;
+    int one = 1;
+    kv->add((char *) &key, sizeof(int), (char *) &one, sizeof(int));
+  }
+}
+
+// reduce: emit (key, nvalues, sum of values), walking blocks when the pair is multi-block
+static void sumvals(char *key, int keybytes, char *multivalue, int nvalues, int *valuebytes, KeyValue *kv, void *ptr)
+{
+  MapReduce *mr = (MapReduce *) ptr;
+  int64_t out[2] = {0, 0};
+  if (multivalue) {
+    for (int i = 0; i < nvalues; i++) {
+      int v;
+      memcpy(&v, multivalue, sizeof(int));
+      out[1] += v;
+      multivalue += valuebytes[i];
+    }
+    out[0] = nvalues;
+  } else {
+    int nblocks;
+    uint64_t total = mr->multivalue_blocks(nblocks);
+    out[0] = (int64_t) total;
+    for (int b = 0; b < nblocks; b++) {
+      int nv = mr->multivalue_block(b, &multivalue, &valuebytes);
+      for (int i = 0; i < nv; i++) {
+        int v;
+        memcpy(&v, multivalue, sizeof(int));
+        out[1] += v;
+        multivalue += valuebytes[i];
+      }
+    }
+  }
+  kv->add(key, keybytes, (char *) out, sizeof(out));
+}
+
+static std::vector<std::string> lines;
+
+static void collect_str(char *key, int keybytes, char *value, int valuebytes, void *)
+{
+  int64_t v[2];
+  memcpy(v, value, sizeof(v));
+  char buf[128];
+  sprintf(buf, "%s %d %lld %lld", key, keybytes, (long long) v[0], (long long) v[1]);
+  lines.push_back(buf);
+}
+
+static void collect_int(char *key, int keybytes, char *value, int valuebytes, void *)
+{
+  int k;
+  memcpy(&k, key, 4);
+  int64_t v[2];
+  memcpy(v, value, sizeof(v));
+  char buf[128];
+  sprintf(buf, "%d %lld %lld", k, (long long) v[0], (long long) v[1]);
+  lines.push_back(buf);
+}
+
+static void collect_kmv(char *key, int keybytes, char *mv, int nv, int *sizes, void *)
+{
+  // values of one key in arrival order are part of the contract
+  std::string s = std::string(key) + ":";
+  for (int i = 0; i < nv; i++) {
+    int v;
+    memcpy(&v, mv, 4);
+    s += " " + std::to_string(v);
+    mv += sizes[i];
+  }
+  lines.push_back(s);
+}
+
+static void dump(const char *title, bool sort_lines)
+{
+  if (sort_lines) std::sort(lines.begin(), lines.end());
+  printf("== %s (%zu)\n", title, lines.size());
+  for (size_t i = 0; i < lines.size(); i++) printf("%s\n", lines[i].c_str());
+  lines.clear();
+}
+
+static int by_count_desc(char *p1, int, char *p2, int)
+{
+  int64_t a, b;
+  memcpy(&a, p1, 8);
+  memcpy(&b, p2, 8);
+  if (a > b) return -1;
+  if (a < b) return 1;
+  return 0;
+}
+
+static void emit_swapped(uint64_t, char *key, int keybytes, char *value, int valuebytes, KeyValue *kv, void *)
+{
+  kv->add(value, 8, key, keybytes);  // key = count (first int64 of the value), value = word
+}
+
+static void collect_swapped(char *key, int, char *value, int, void *)
+{
+  int64_t c;
+  memcpy(&c, key, 8);
+  char buf[128];
+  sprintf(buf, "%lld %s", (long long) c, value);
+  lines.push_back(buf);
+}
+
+int main(int narg, char **args)
+{
+  MPI_Init(&narg, &args);
+  int n = 4000;
+
+  // 1. words: map -> collate -> scan KMV -> reduce (host callback) -> scan KV
+  MapReduce *mr = new MapReduce(MPI_COMM_WORLD);
+  uint64_t npairs = mr->map(3, gen, &n);
+  uint64_t nuniq = mr->collate(NULL);
+  printf("pairs %lu unique %lu\n", (unsigned long) npairs, (unsigned long) nuniq);
+  mr->scan(collect_kmv, NULL);
+  dump("kmv, values in arrival order", true);
+  uint64_t nred = mr->reduce(sumvals, mr);
+  printf("reduced %lu\n", (unsigned long) nred);
+  mr->scan(collect_str, NULL);
+  dump("key count sum", true);
+
+  // 2. sort_keys(5) (strcmp order) is deterministic: print in order
+  mr->sort_keys(5);
+  mr->scan(collect_str, NULL);
+  dump("sorted by key", false);
+
+  // 3. map(mr, callback) + sort_keys(user compare): top counts (ties broken by the sorted key order above)
+  MapReduce *mr2 = new MapReduce(MPI_COMM_WORLD);
+  mr2->map(mr, emit_swapped, NULL);
+  mr2->sort_keys(by_count_desc);
+  mr2->scan(collect_swapped, NULL);
+  lines.resize(10);
+  dump("top 10 by count", false);
+  delete mr2;
+  delete mr;
+
+  // 4. hot key with 32 KiB pages: the reduce callback must see it through the multi-block protocol
+  MapReduce *mh = new MapReduce(MPI_COMM_WORLD);
+  mh->memsize = -32768;
+  int nh = 20000;
+  mh->map(1, gen_hot, &nh);
+  mh->convert();
+  mh->reduce(sumvals, mh);
+  mh->sort_keys(1);
+  mh->scan(collect_int, NULL);
+  dump("hot key", false);
+  delete mh;
+
+  MPI_Finalize();
+  return 0;
+}
