@@ -207,7 +207,9 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
   (cur ? p0 : p1).release();
 
   // 3. run heads -> number of unique keys U and start[u]
-  auto head = [=] __device__(uint64_t i) -> bool { return i == 0 || sk[i] != sk[i - 1]; };
+  // read-only arrays go through the non-coherent path so that loads of later rounds may be hoisted above the
+  // KMV stores of earlier rounds (the compiler must otherwise assume the stores alias them)
+  auto head = [=] __device__(uint64_t i) -> bool { return i == 0 || __ldg(sk + i) != __ldg(sk + i - 1); };
   FlagTiles heads;
   flag_tiles(pool, n, head, heads, mr->d_small, "convert_heads_count", (double) n * sizeof(K));
   fetch_small(mr, 1);
@@ -251,9 +253,9 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
     const uint8_t *k0b = dkey0.p;
     flag_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
       uint64_t u = e + h - 1;
-      uint32_t s0 = st[u];
-      uint64_t nv = st[u + 1] - s0, r = i - s0;
-      uint8_t *rec = out + offs[u];
+      uint32_t s0 = __ldg(st + u);
+      uint64_t nv = __ldg(st + u + 1) - s0, r = i - s0;
+      uint8_t *rec = out + __ldg((const unsigned long long *) offs + u);
       uint64_t ko = kmv_key_off(al, nv), vo = kmv_val_off(al, nv, kb);
       if (h) {
         uint32_t *hd = (uint32_t *) rec;
@@ -261,7 +263,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
         hd[1] = kb;
         hd[2] = (uint32_t) (nv * vb);
         for (uint64_t q = 12 + 4 * nv; q < ko; q++) rec[q] = 0;
-        K key = sk[i];
+        K key = __ldg(sk + i);
         if (ident) {
           for (uint32_t q = 0; q < kb; q++) rec[ko + q] = (uint8_t) ((unsigned long long) key >> (8 * q));
         } else {
@@ -273,15 +275,15 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
         for (uint64_t q = vo + nv * vb; q < end; q++) rec[q] = 0;
       }
       ((uint32_t *) (rec + 12))[r] = vb;
-      if (PMODE == 1) *(uint32_t *) (rec + vo + r * 4) = (uint32_t) sp[i];
+      if (PMODE == 1) *(uint32_t *) (rec + vo + r * 4) = (uint32_t) __ldg(sp + i);
       if (PMODE == 2) {
-        uint64_t v = sp[i];
+        uint64_t v = __ldg(sp + i);
         uint32_t *d = (uint32_t *) (rec + vo + r * 8);
         d[0] = (uint32_t) v;
         d[1] = (uint32_t) (v >> 32);
       }
       if (PMODE == 3) {
-        const uint8_t *src = kvdata + (uint64_t) sp[i] * rs + voff;
+        const uint8_t *src = kvdata + (uint64_t) __ldg(sp + i) * rs + voff;
         uint8_t *d = rec + vo + r * vb;
         for (uint32_t q = 0; q < vb; q++) d[q] = src[q];
       }

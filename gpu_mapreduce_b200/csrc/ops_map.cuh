@@ -85,11 +85,18 @@ static void kv_commit_uniform(DevKV *kv, uint32_t kb, uint32_t vb, uint32_t rs, 
   kv->vsize += nnew * vb;
 }
 
-// stage host input on the device (inside the call, so e2e timings include the copy)
+// Host input.  Pinned (page-locked) host memory is read by the kernel directly over PCIe through its device
+// alias: the transfer and the emit are one pass and no staging buffer exists.  Pageable memory has no device
+// alias and is staged with one cudaMemcpyAsync.  Either way the transfer happens inside the call.
 template <typename T>
-static const T *stage_input(mrgpu_mr *mr, const T *p, uint64_t n, Buf<T> &tmp)
+static const T *stage_input(mrgpu_mr *mr, const T *p, uint64_t n, Buf<T> &tmp, bool allow_zero_copy = true)
 {
-  if (n == 0 || is_device_ptr(p)) return p;
+  if (n == 0) return p;
+  cudaPointerAttributes at;
+  cudaError_t e = cudaPointerGetAttributes(&at, p);
+  if (e != cudaSuccess) cudaGetLastError();
+  if (e == cudaSuccess && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged)) return p;
+  if (e == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer && allow_zero_copy) return (const T *) at.devicePointer;
   tmp.alloc(mr->pool, n);
   MR_CUDA(cudaMemcpyAsync(tmp.p, p, n * sizeof(T), cudaMemcpyHostToDevice, mr->pool.stream));
   return tmp.p;

@@ -81,7 +81,7 @@ extern "C" int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbyte
   cudaStream_t s = pool.stream;
   const Align al = mr->al;
   Buf<uint8_t> tmp;
-  const uint8_t *t = stage_input(mr, (const uint8_t *) text, nbytes, tmp);
+  const uint8_t *t = stage_input(mr, (const uint8_t *) text, nbytes, tmp, false);  // read several times: stage it
   uint64_t nwords = 0;
   if (nbytes) {
     unsigned long long *d = mr->d_small;
@@ -291,7 +291,7 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
   const Align al = mr->al;
   href_upload_table();
   Buf<uint8_t> tmp;
-  const uint8_t *t = stage_input(mr, (const uint8_t *) text, nbytes, tmp);
+  const uint8_t *t = stage_input(mr, (const uint8_t *) text, nbytes, tmp, false);  // read several times: stage it
   const uint32_t fnb = (uint32_t) strlen(fname) + 1;  // value = file name with its NUL, cpu/InvertedIndex.cpp:262
   if (nbytes) {
     const uint64_t n = nbytes;
