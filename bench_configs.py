@@ -1,0 +1,207 @@
+#!/usr/bin/env python
+"""The other BASELINE.json configs at full size on one B200 (bench.py is the contract benchmark for configs[1]).
+
+  python bench_configs.py [wordfreq] [invindex] [rmat24] [rmat26]      (default: wordfreq invindex rmat24)
+
+Each config runs its reference pipeline through the C-ABI with device functors, is checked against a ground truth
+that does not depend on size (the generator's own index counts, pair-count identities), and prints one JSON line
+{config, pairs, seconds per phase, pairs_per_s}.  Synthetic inputs are generated on the GPU with torch and the time
+to generate them is not counted; inputs are device resident (the e2e figure belongs to bench.py)."""
+import json
+import sys
+import time
+
+import numpy as np
+import torch
+
+from gpu_mapreduce_b200 import MapReduce, workloads as W
+
+DEV = torch.device("cuda", 0)
+
+
+def sync():
+    torch.cuda.synchronize()
+
+
+class Timer:
+    def __init__(self):
+        self.t = {}
+
+    def run(self, name, fn):
+        sync()
+        t0 = time.perf_counter()
+        r = fn()
+        sync()
+        self.t[name] = self.t.get(name, 0.0) + time.perf_counter() - t0
+        return r
+
+
+# ------------------------------------------------------------------------------------------ config 1: wordfreq
+
+def wordfreq(total_bytes=1 << 30, nfiles=8, nvocab=1 << 17):
+    """examples/wordfreq.cpp:64-66: map(files, fileread) -> collate -> reduce(sum).  1 GiB of Zipf(1.0) words over a
+    2^17 vocabulary in 8 files (the reference's own corpus is a missing blob)."""
+    vocab = W.vocabulary(nvocab)
+    maxlen = max(len(w) for w in vocab)
+    table = np.zeros((nvocab, maxlen + 1), dtype=np.uint8)
+    lens = np.zeros(nvocab, dtype=np.int64)
+    for i, w in enumerate(vocab):
+        table[i, :len(w)] = np.frombuffer(w, dtype=np.uint8)
+        lens[i] = len(w)
+    table_t, lens_t = torch.from_numpy(table).to(DEV), torch.from_numpy(lens).to(DEV)
+    cdf_t = torch.from_numpy(W.zipf_cdf(nvocab, 1.0)).to(DEV)
+    mr = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
+    T = Timer()
+    truth = torch.zeros(nvocab, dtype=torch.int64, device=DEV)
+    nwords_total, nbytes_total, start = 0, 0, 0
+    per_file = total_bytes // nfiles
+    avg = float((lens + 1).astype(np.float64) @ np.diff(np.concatenate([[0.0], W.zipf_cdf(nvocab, 1.0)])))
+    for f in range(nfiles):
+        nw = int(per_file / avg)
+        idx = torch.arange(start, start + nw, dtype=torch.int64, device=DEV)
+        z = W.splitmix64_torch(idx, W.WORDS_SEED)
+        u = W._lsr_t(z, 11).to(torch.float64) * (1.0 / 9007199254740992.0)
+        k = torch.clamp(torch.searchsorted(cdf_t, u, right=True), max=nvocab - 1)
+        start += nw
+        truth += torch.bincount(k, minlength=nvocab)
+        rows = table_t[k]                                     # [nw, maxlen+1]
+        ln = lens_t[k]
+        sep = torch.where((torch.arange(nw, device=DEV) % 16) == 15, 10, 32).to(torch.uint8)
+        rows.scatter_(1, ln.unsqueeze(1), sep.unsqueeze(1))   # separator right after the word
+        mask = torch.arange(maxlen + 1, device=DEV).unsqueeze(0) <= ln.unsqueeze(1)
+        text = rows[mask].contiguous()
+        del rows, mask, idx, z, u
+        nwords_total += nw
+        nbytes_total += text.numel()
+        got = T.run("map", lambda: mr.map_tokenize(text, addflag=1 if f else 0))
+        assert got == nwords_total
+        del text
+    nuniq = T.run("collate", mr.collate)
+    assert nuniq == int((truth > 0).sum().item())
+    assert T.run("reduce", lambda: mr.reduce("sum")) == nuniq
+    # ground truth: the count of vocabulary word i is the number of times index i was drawn
+    recs = mr.scan_kv() if nuniq <= 300000 else None
+    if recs is not None:
+        want = {vocab[i] + b"\0": int(c) for i, c in enumerate(truth.cpu().numpy()) if c}
+        got = {k: int(np.frombuffer(v, dtype=np.int32)[0]) for k, v in recs}
+        assert got == want, "wordfreq counts differ from the generator's index counts"
+    mr.destroy()
+    secs = sum(T.t.values())
+    return {"config": "wordfreq: 1 GiB synthetic text, 8 files, map(tokenize)->collate->reduce(sum)", "pairs": nwords_total, "text_bytes": nbytes_total,
+            "unique": nuniq, "secs": T.t, "pairs_per_s": nwords_total / secs, "text_gbs": nbytes_total / 1e9 / T.t["map"],
+            "check": "every (word,count) equals the generator's bincount"}
+
+
+# ------------------------------------------------------------------------------------------ config 3: InvertedIndex
+
+_ROW = (b'<a href="http://h0000.example/p/0000000">link</a><p>lorem ipsum dolor sit amet, consectetur adipiscing elit</p>'
+        b'<div class="x">sed do eiusmod tempor incididunt ut labore et dolore magna aliqua</div><br/><span>ut enim ad minim</span> '
+        b'<img src="i.png"> plain words here &amp; there, with <b>bold</b> and <i>italic</i> filler\n')
+
+
+def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
+    """cpu/InvertedIndex.cpp: map(href FSM) -> aggregate -> convert (-> postings).  128 files x 128 MiB of synthetic HTML,
+    one <a href> per ~256-byte row, URLs Zipf(1.0) over 2^22."""
+    row = np.frombuffer(_ROW, dtype=np.uint8)
+    rowlen = len(row)
+    host_pos, path_pos = _ROW.index(b"h0000") + 1, _ROW.index(b"/p/") + 3
+    row_t = torch.from_numpy(row.copy()).to(DEV)
+    cdf_t = torch.from_numpy(W.zipf_cdf(nurls, 1.0)).to(DEV)
+    mr = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
+    T = Timer()
+    truth = torch.zeros(nurls, dtype=torch.int64, device=DEV)
+    per_file = total_bytes // nfiles
+    rows_per_file = per_file // rowlen
+    nlinks, nbytes, start = 0, 0, 0
+    for f in range(nfiles):
+        idx = torch.arange(start, start + rows_per_file, dtype=torch.int64, device=DEV)
+        start += rows_per_file
+        z = W.splitmix64_torch(idx, W.HTML_SEED)
+        u = W._lsr_t(z, 11).to(torch.float64) * (1.0 / 9007199254740992.0)
+        k = torch.clamp(torch.searchsorted(cdf_t, u, right=True), max=nurls - 1)
+        truth += torch.bincount(k, minlength=nurls)
+        text = row_t.repeat(rows_per_file, 1)
+        h = k % 10000
+        for j in range(4):
+            text[:, host_pos + 3 - j] = (48 + (h // 10 ** j) % 10).to(torch.uint8)
+        for j in range(7):
+            text[:, path_pos + 6 - j] = (48 + (k // 10 ** j) % 10).to(torch.uint8)
+        text = text.reshape(-1)
+        nlinks += rows_per_file
+        nbytes += text.numel()
+        got = T.run("map", lambda: mr.map_href(text, f"part-{f:05d}", addflag=1 if f else 0))
+        assert got == nlinks, (got, nlinks)
+        del text, idx, z, u, h
+    T.run("aggregate", mr.aggregate)
+    nuniq = T.run("convert", mr.convert)
+    assert nuniq == int((truth > 0).sum().item())
+    st = mr.kmv_stats()
+    assert st.nvalue == nlinks and st.valuesize == nlinks * len("part-00000\0")
+    # postings -> per-URL posting counts, against the generator
+    assert T.run("reduce", lambda: mr.reduce("count")) == nuniq
+    mr.sort_keys(5)
+    counts = []
+    for nkey, page in mr.kv_pages():
+        counts.append(np.frombuffer(page, dtype=np.uint8).reshape(nkey, -1)[:, -4:].copy().view(np.int32).reshape(-1))
+    counts = np.concatenate(counts)
+    want = truth.cpu().numpy()
+    # URL strings sort like (host, path) strings; compare as multisets of counts plus the total
+    assert int(counts.sum()) == nlinks and np.array_equal(np.sort(counts), np.sort(want[want > 0]))
+    mr.destroy()
+    secs = T.t["map"] + T.t["aggregate"] + T.t["convert"] + T.t["reduce"]
+    return {"config": "InvertedIndex: 16 GiB synthetic HTML in 128 files, map(href FSM)->aggregate->convert->reduce", "pairs": nlinks,
+            "text_bytes": nbytes, "unique": nuniq, "secs": T.t, "pairs_per_s": nlinks / secs, "text_gbs": nbytes / 1e9 / T.t["map"],
+            "check": "posting counts per URL equal the generator's bincount (as multiset) and sum to the number of links"}
+
+
+# ------------------------------------------------------------------------------------------ configs 4/5: R-MAT + degree
+
+def rmat(nlevels=24, ef=16, a=.57, b=.19, c=.19, d=.05, fraction=0.0, seed=12345):
+    """oink: rmat N 16 .57 .19 .19 .05 0.0 12345 ; degree 2 (oink/rmat.cpp:37-61, oink/degree.cpp:43-50)."""
+    mr = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
+    T = Timer()
+    state = (seed << 16) | 0x330E
+    ntotal = nremain = (1 << nlevels) * ef
+    niter, generated = 0, 0
+    while nremain:
+        niter += 1
+        generated += nremain
+        _, state = T.run("generate", lambda: mr.map_rmat(nremain, nlevels, a, b, c, d, fraction, state, addflag=1))
+        nunique = T.run("collate", mr.collate)
+        T.run("cull", lambda: mr.reduce("cull"))
+        nremain = ntotal - nunique
+    assert mr.kv_stats().npair == ntotal
+    mrv = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
+    assert T.run("degree_map", lambda: mrv.map_mr(mr, "edge_to_vertices")) == 2 * ntotal
+    nvert = T.run("degree_collate", mrv.collate)
+    assert T.run("degree_reduce", lambda: mrv.reduce("count")) == nvert
+    deg_sum = 0
+    for nkey, page in mrv.kv_pages():
+        deg_sum += int(np.frombuffer(page, dtype=np.int32).reshape(nkey, -1)[:, -1].astype(np.int64).sum())
+    assert deg_sum == 2 * ntotal and nvert <= (1 << nlevels)
+    mr.destroy()
+    mrv.destroy()
+    secs = sum(T.t.values())
+    return {"config": f"oink rmat {nlevels} {ef} {a} {b} {c} {d} {fraction} {seed} + degree 2", "edges": ntotal, "iterations": niter,
+            "pairs": generated + 2 * ntotal, "vertices": nvert, "secs": T.t, "pairs_per_s": (generated + 2 * ntotal) / secs,
+            "check": "unique edges == order*ef, sum of degrees == 2*edges (small scales are compared edge for edge in tests/)"}
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["wordfreq", "invindex", "rmat24"]
+    for w in which:
+        if w == "wordfreq":
+            r = wordfreq()
+        elif w == "invindex":
+            r = invindex()
+        elif w.startswith("rmat"):
+            r = rmat(int(w[4:]))
+        elif w == "wordfreq_small":
+            r = wordfreq(total_bytes=1 << 24, nfiles=2, nvocab=1 << 10)
+        elif w == "invindex_small":
+            r = invindex(total_bytes=1 << 24, nfiles=2, nurls=1 << 12)
+        else:
+            raise SystemExit(f"unknown config {w}")
+        r["secs"] = {k: round(v, 4) for k, v in r["secs"].items()}
+        print(json.dumps(r), flush=True)
+        torch.cuda.empty_cache()
