@@ -29,11 +29,16 @@ struct CompactKey {
 template <typename K, int PMODE /*0 none, 1 val32, 2 val64, 3 idx*/, bool IDENT /*key bytes 0..kb-1, kb<=8, word loads*/>
 __global__ void __launch_bounds__(256)
 extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs, uint32_t koff, uint32_t voff, uint32_t kb, CompactKey ck,
-                       K *__restrict__ keys, void *__restrict__ pay, unsigned long long *hist)
+                       K *__restrict__ keys, void *__restrict__ pay, unsigned long long *hist, unsigned long long *vdiff)
 {
   __shared__ unsigned sh[sizeof(K) * RADIX];
   for (int i = threadIdx.x; i < (int) sizeof(K) * RADIX; i += blockDim.x) sh[i] = 0;
   __syncthreads();
+  // value of record 0: if every record carries the same value bytes the sort need not move them at all
+  uint64_t v0 = 0;
+  bool vd = false;
+  if (PMODE == 1) v0 = *(const uint32_t *) (data + voff);
+  if (PMODE == 2) v0 = (uint64_t) ((const uint32_t *) (data + voff))[0] | ((uint64_t) ((const uint32_t *) (data + voff))[1] << 32);
   unsigned prev[sizeof(K)], run[sizeof(K)];
 #pragma unroll
   for (int b = 0; b < (int) sizeof(K); b++) prev[b] = 0, run[b] = 0;
@@ -57,24 +62,34 @@ extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs
       key = (K) k64;
     }
     keys[i] = key;
-    if (PMODE == 1) ((uint32_t *) pay)[i] = *(const uint32_t *) (r + voff);
+    if (PMODE == 1) {
+      uint32_t v = *(const uint32_t *) (r + voff);
+      ((uint32_t *) pay)[i] = v;
+      vd |= v != (uint32_t) v0;
+    }
     if (PMODE == 2) {
       const uint32_t *v = (const uint32_t *) (r + voff);
-      ((uint64_t *) pay)[i] = (uint64_t) v[0] | ((uint64_t) v[1] << 32);
+      uint64_t vv = (uint64_t) v[0] | ((uint64_t) v[1] << 32);
+      ((uint64_t *) pay)[i] = vv;
+      vd |= vv != v0;
     }
     if (PMODE == 3) ((uint32_t *) pay)[i] = (uint32_t) i;
     hist_accumulate<K>(key, prev, run, sh);
   }
   hist_flush<K>(prev, run, sh, hist);
+  if (__syncthreads_or(vd) && threadIdx.x == 0) *vdiff = 1;
 }
 
 // IntCount layout {kb=4, vb=4, key, value} in one 16-byte load per record
 __global__ void __launch_bounds__(256)
-extract16_kernel(const int4 *__restrict__ recs, uint64_t n, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, unsigned long long *hist)
+extract16_kernel(const int4 *__restrict__ recs, uint64_t n, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, unsigned long long *hist,
+                 unsigned long long *vdiff)
 {
   __shared__ unsigned sh[4 * RADIX];
   for (int i = threadIdx.x; i < 4 * RADIX; i += blockDim.x) sh[i] = 0;
   __syncthreads();
+  const uint32_t v0 = (uint32_t) __ldg((const int *) recs + 3);
+  bool vd = false;
   unsigned prev[4] = {0, 0, 0, 0}, run[4] = {0, 0, 0, 0};
   constexpr int U = 4;
   uint64_t stride = (uint64_t) gridDim.x * blockDim.x * U;
@@ -91,11 +106,13 @@ extract16_kernel(const int4 *__restrict__ recs, uint64_t n, uint32_t *__restrict
       if (i < n) {
         keys[i] = (uint32_t) r[u].z;
         vals[i] = (uint32_t) r[u].w;
+        vd |= (uint32_t) r[u].w != v0;
         hist_accumulate<uint32_t>((uint32_t) r[u].z, prev, run, sh);
       }
     }
   }
   hist_flush<uint32_t>(prev, run, sh, hist);
+  if (__syncthreads_or(vd) && threadIdx.x == 0) *vdiff = 1;
 }
 
 // OR of (key XOR first key) over all records: which key bytes vary at all (uniform keys longer than 8 bytes)
@@ -183,28 +200,46 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
 
   Buf<K> k0(pool, n), k1(pool, n);
   Buf<P> p0(pool, HASP ? n : 1), p1(pool, HASP ? n : 1);
-  Buf<unsigned long long> hist(pool, 8 * RADIX);
-  MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
+  Buf<unsigned long long> hist(pool, 8 * RADIX + 8);
+  MR_CUDA(cudaMemsetAsync(hist.p, 0, (8 * RADIX + 8) * 8, s));
+  unsigned long long *vdiff = hist.p + 8 * RADIX;
 
   // 1. one read of the KV: sort keys, payload, byte histograms
   {
   ProfScope ps(pool, "convert_extract", (double) n * (8 + kb + vb + sizeof(K) + (HASP ? sizeof(P) : 0)));
   if (ident && PMODE == 1 && sizeof(K) == 4 && kb == 4 && rs == 16 && koff == 8 && voff == 12 && ((uintptr_t) kv->data % 16) == 0)
-    extract16_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>((const int4 *) kv->data, n, (uint32_t *) k0.p, (uint32_t *) p0.p, hist.p);
+    extract16_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>((const int4 *) kv->data, n, (uint32_t *) k0.p, (uint32_t *) p0.p, hist.p, vdiff);
   else if (ident)
-    extract_uniform_kernel<K, PMODE, true><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p);
+    extract_uniform_kernel<K, PMODE, true><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p, vdiff);
   else
-    extract_uniform_kernel<K, PMODE, false><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p);
+    extract_uniform_kernel<K, PMODE, false><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p, vdiff);
   MR_CUDA(cudaGetLastError());
   }
 
   // 2. stable LSD radix sort on the varying bytes only
+  //    The same economy applies to values: when every pair carries identical value bytes (IntCount's int 1) the
+  //    values are not moved through the sort; the KMV writer fills them in.
   unsigned mask = ck.nvb >= 8 ? 0xFF : ((1u << ck.nvb) - 1);
-  int cur = radix_sort_pairs<K, P, HASP>(pool, k0.p, k1.p, p0.p, p1.p, n, mask, true, hist.p);
+  bool constval = false;
+  uint64_t cval = 0;
+  if (PMODE == 1 || PMODE == 2) {
+    unsigned long long flag = 1;
+    MR_CUDA(cudaMemcpyAsync(&flag, vdiff, 8, cudaMemcpyDeviceToHost, s));
+    MR_CUDA(cudaMemcpyAsync(&cval, kv->data + voff, vb, cudaMemcpyDeviceToHost, s));
+    sync(mr);
+    constval = flag == 0;
+  }
+  int cur;
+  if (constval) {
+    p0.release();
+    p1.release();
+    cur = radix_sort_pairs<K, P, false>(pool, k0.p, k1.p, (P *) nullptr, (P *) nullptr, n, mask, true, hist.p);
+  } else
+    cur = radix_sort_pairs<K, P, HASP>(pool, k0.p, k1.p, p0.p, p1.p, n, mask, true, hist.p);
   const K *sk = cur ? k1.p : k0.p;
-  const P *sp = cur ? p1.p : p0.p;
+  const P *sp = constval ? (const P *) nullptr : (cur ? p1.p : p0.p);
   (cur ? k0 : k1).release();
-  (cur ? p0 : p1).release();
+  if (!constval) (cur ? p0 : p1).release();
 
   // 3. run heads -> number of unique keys U and start[u]
   // read-only arrays go through the non-coherent path so that loads of later rounds may be hoisted above the
@@ -275,9 +310,9 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
         for (uint64_t q = vo + nv * vb; q < end; q++) rec[q] = 0;
       }
       ((uint32_t *) (rec + 12))[r] = vb;
-      if (PMODE == 1) *(uint32_t *) (rec + vo + r * 4) = (uint32_t) __ldg(sp + i);
+      if (PMODE == 1) *(uint32_t *) (rec + vo + r * 4) = constval ? (uint32_t) cval : (uint32_t) __ldg(sp + i);
       if (PMODE == 2) {
-        uint64_t v = __ldg(sp + i);
+        uint64_t v = constval ? cval : (uint64_t) __ldg(sp + i);
         uint32_t *d = (uint32_t *) (rec + vo + r * 8);
         d[0] = (uint32_t) v;
         d[1] = (uint32_t) (v >> 32);
@@ -287,7 +322,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
         uint8_t *d = rec + vo + r * vb;
         for (uint32_t q = 0; q < vb; q++) d[q] = src[q];
       }
-    }, "convert_kmv_write", (double) n * (sizeof(K) + (HASP ? sizeof(P) : 0)) + (double) total);
+    }, "convert_kmv_write", (double) n * (sizeof(K) + ((HASP && !constval) ? sizeof(P) : 0)) + (double) total);
     kmv->nkmv = U;
     kmv->nvalue = n;
     kmv->ksize = U * (uint64_t) kb;

@@ -270,6 +270,25 @@ def test_convert_uniform_shapes(MR, oracle, kb, vb):
     assert H.canon_kv(mr.scan_kv()) == H.canon_kv(wantr)
 
 
+@pytest.mark.parametrize("kb,vb", [(4, 4), (8, 8), (4, 8), (16, 4)])
+def test_convert_constant_values_are_not_sorted_but_still_written(MR, oracle, kb, vb):
+    """every pair carries the same value bytes: the sort skips the payload, the KMV must still hold every value"""
+    r = np.random.RandomState(kb + vb)
+    val = bytes(r.randint(1, 255, size=vb).astype(np.uint8))
+    recs = [(bytes(r.randint(0, 3, size=kb).astype(np.uint8)), val) for _ in range(9000)]
+    mr = MR()
+    mr.kv_add(recs)
+    want = H.kmv_decode(oracle.convert(H.kv_encode(recs)))
+    assert mr.convert() == len(want)
+    assert H.canon_kmv(mr.scan_kmv()) == H.canon_kmv(want)
+    # one differing value at the very end must switch the payload back on
+    recs[-1] = (recs[-1][0], bytes(vb))
+    mr2 = MR()
+    mr2.kv_add(recs)
+    mr2.convert()
+    assert H.canon_kmv(mr2.scan_kmv()) == H.canon_kmv(H.kmv_decode(oracle.convert(H.kv_encode(recs))))
+
+
 def test_convert_hot_key_bigger_than_page(MR, golden, oracle):
     """one key with ~18000 values and 32 KiB pages -> the pair gets its own (extended) page"""
     mr = MR(memsize=-32768)
