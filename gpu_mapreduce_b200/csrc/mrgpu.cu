@@ -108,6 +108,7 @@ static uint64_t allreduce_sum(mrgpu_mr *mr, uint64_t v);
 
 #include "ops_map.cuh"
 #include "ops_convert.cuh"
+#include "ops_convert_dense.cuh"
 #include "ops_text.cuh"
 #include "ops_reduce.cuh"
 #include "ops_sort.cuh"

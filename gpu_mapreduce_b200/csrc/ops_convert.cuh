@@ -465,6 +465,8 @@ static void convert_general(mrgpu_mr *mr)
   mr->kmv = kmv;
 }
 
+static bool convert_dense(mrgpu_mr *mr);
+
 static void convert_impl(mrgpu_mr *mr)
 {
   freeze(mr);
@@ -480,10 +482,10 @@ static void convert_impl(mrgpu_mr *mr)
     MR_CUDA(cudaMemsetAsync(kmv->offs, 0, 8, mr->pool.stream));
     mr->kmv = kmv;
   } else {
-    bool done = false;
+    bool done = convert_dense(mr);  // small integer keys + indistinguishable pairs: count, do not sort
     const Align al = mr->al;
     // exact path needs word-aligned records/keys and a value that is empty, 4 or 8 bytes, or gatherable
-    if (kv->uniform && (al.k % 4) == 0 && (al.v % 4 == 0 || kv->vb == 0 || true)) {
+    if (!done && kv->uniform && (al.k % 4) == 0) {
       CompactKey ck{};
       bool ident = kv->kb <= 8;
       std::vector<uint8_t> key0(kv->kb);

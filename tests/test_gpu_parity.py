@@ -289,6 +289,48 @@ def test_convert_constant_values_are_not_sorted_but_still_written(MR, oracle, kb
     assert H.canon_kmv(mr2.scan_kmv()) == H.canon_kmv(H.kmv_decode(oracle.convert(H.kv_encode(recs))))
 
 
+@pytest.mark.parametrize("kb,vb", [(4, 4), (4, 0), (8, 0), (8, 8), (4, 8)])
+def test_convert_dense_integer_keys(MR, oracle, kb, vb):
+    """small integer keys + identical values: grouping by counting (no sort); result must equal the general path's"""
+    r = np.random.RandomState(100 + kb + vb)
+    n = 150_000
+    kd = "<I" if kb == 4 else "<Q"
+    keys = (r.zipf(1.2, size=n) % 5000).astype(np.int64)
+    keys[:10] = [0, 1, (1 << 26) - 1, 7, 7, 7, 12345, 0, 4999, 2]
+    val = bytes(r.randint(1, 255, size=vb).astype(np.uint8))
+    recs = [(struct.pack(kd, int(k)), val) for k in keys]
+    mr = MR()
+    mr.kv_add(recs)
+    want = H.kmv_decode(oracle.convert(H.kv_encode(recs)))
+    assert mr.convert() == len(want)
+    st = mr.kmv_stats()
+    assert st.nvalue == n and st.keysize == kb * len(want) and st.valuesize == vb * n
+    assert H.canon_kmv(mr.scan_kmv()) == H.canon_kmv(want)
+    mr.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(oracle.reduce(oracle.convert(H.kv_encode(recs)), "count")))
+
+
+@pytest.mark.parametrize("spoil", ["bigkey", "value", "highword"])
+def test_convert_dense_falls_back_to_the_sort(MR, oracle, spoil):
+    """one key outside the table / one differing value anywhere: the counting path must hand over to the sort"""
+    r = np.random.RandomState(7)
+    n = 120_000
+    kb = 8 if spoil == "highword" else 4
+    kd = "<I" if kb == 4 else "<Q"
+    recs = [(struct.pack(kd, int(k)), struct.pack("<i", 1)) for k in r.randint(0, 3000, size=n)]
+    if spoil == "bigkey":
+        recs[n // 2] = (struct.pack("<I", 1 << 26), recs[0][1])
+    elif spoil == "value":
+        recs[n - 1] = (recs[n - 1][0], struct.pack("<i", 2))
+    else:
+        recs[17] = (struct.pack("<Q", 5 | (1 << 40)), recs[0][1])
+    mr = MR()
+    mr.kv_add(recs)
+    want = H.kmv_decode(oracle.convert(H.kv_encode(recs)))
+    assert mr.convert() == len(want)
+    assert H.canon_kmv(mr.scan_kmv()) == H.canon_kmv(want)
+
+
 def test_convert_hot_key_bigger_than_page(MR, golden, oracle):
     """one key with ~18000 values and 32 KiB pages -> the pair gets its own (extended) page"""
     mr = MR(memsize=-32768)
