@@ -46,29 +46,47 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
   bool bad = false;
   const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
   const bool rec16 = a.rs == 16 && ((uintptr_t) a.data % 16) == 0;
-  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
-    uint32_t key, khi = 0, va = v0a, vb2 = v0b;
-    if (rec16) {  // one 16-byte load per record: {kb, vb, w2, w3}
-      int4 r = ld_stream((const int4 *) a.data + i);
-      key = (uint32_t) r.z;
-      if (a.kb == 8) khi = (uint32_t) r.w;
-      else if (a.vb == 4) va = (uint32_t) r.w;
-    } else {
-      const uint8_t *r = a.data + i * a.rs;
-      key = *(const uint32_t *) (r + a.koff);
-      if (a.kb == 8) khi = *(const uint32_t *) (r + a.koff + 4);
-      if (a.vb >= 4) va = *(const uint32_t *) (r + a.voff);
-      if (a.vb == 8) vb2 = *(const uint32_t *) (r + a.voff + 4);
-    }
+  auto count_one = [&](uint32_t key, uint32_t khi, uint32_t va, uint32_t vb2) {
     if (khi != 0 || key >= DENSE_SLOTS || va != v0a || vb2 != v0b) {
       bad = true;
-      break;
+      return;
     }
     unsigned slot = (key * 0x9E3779B1u) >> (32 - 13);  // 8192 slots
     unsigned old = ckey[slot];
     if (old == DENSE_EMPTY) old = atomicCAS(&ckey[slot], DENSE_EMPTY, key);
     if (old == DENSE_EMPTY || old == key) atomicAdd(&ccnt[slot], 1u);
     else atomicAdd(&table[key], 1u);
+  };
+  if (rec16) {
+    // one 16-byte load per record {kb, vb, w2, w3}; eight independent loads in flight per thread -- with a
+    // single load per iteration the kernel sat at 18 % issue utilisation waiting on HBM latency (ncu)
+    constexpr int U = 8;
+    const int4 *recs = (const int4 *) a.data;
+    for (uint64_t base = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; base < a.n && !bad; base += stride * U) {
+      int4 r[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        uint64_t i = base + (uint64_t) u * stride;
+        if (i < a.n) r[u] = ld_stream(recs + i);
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        uint64_t i = base + (uint64_t) u * stride;
+        if (i < a.n) {
+          if (a.kb == 8) count_one((uint32_t) r[u].z, (uint32_t) r[u].w, v0a, v0b);
+          else count_one((uint32_t) r[u].z, 0, a.vb == 4 ? (uint32_t) r[u].w : v0a, v0b);
+        }
+      }
+    }
+  } else {
+    for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < a.n && !bad; i += stride) {
+      const uint8_t *r = a.data + i * a.rs;
+      uint32_t key = *(const uint32_t *) (r + a.koff), khi = 0, va = v0a, vb2 = v0b;
+      if (a.kb == 8) khi = *(const uint32_t *) (r + a.koff + 4);
+      if (a.vb >= 4) va = *(const uint32_t *) (r + a.voff);
+      if (a.vb == 8) vb2 = *(const uint32_t *) (r + a.voff + 4);
+      count_one(key, khi, va, vb2);
+    }
   }
   if (__syncthreads_or(bad)) {
     if (threadIdx.x == 0) *abort_flag = 1;
@@ -88,17 +106,22 @@ constexpr int FILL_MAX_PAIRS = FILL_CHUNK_WORDS / 4 + 2;               // a KMV 
 
 __global__ void __launch_bounds__(FILL_THREADS)
 dense_fill_kernel(uint32_t *__restrict__ out, uint64_t total_words, const uint64_t *__restrict__ offs, const uint32_t *__restrict__ ukey,
-                  const uint32_t *__restrict__ ucnt, uint64_t U, Align al, uint32_t kb, uint32_t vb, uint32_t cv0, uint32_t cv1)
+                  const uint32_t *__restrict__ ucnt, uint64_t U, Align al, uint32_t kb, uint32_t vb, uint32_t cv0, uint32_t cv1,
+                  uint64_t chunks_per_block)
 {
   __shared__ uint64_t s_off[FILL_MAX_PAIRS + 1];
   __shared__ uint32_t s_key[FILL_MAX_PAIRS], s_cnt[FILL_MAX_PAIRS];
   __shared__ uint64_t s_u0;
   __shared__ int s_np;
-  const uint64_t w0 = (uint64_t) blockIdx.x * FILL_CHUNK_WORDS;
-  const uint64_t b0 = w0 * 4, b1 = min((w0 + FILL_CHUNK_WORDS) * 4, total_words * 4);
+  const uint64_t nchunks = (total_words + FILL_CHUNK_WORDS - 1) / FILL_CHUNK_WORDS;
+  const uint64_t c_begin = (uint64_t) blockIdx.x * chunks_per_block;
+  const uint64_t c_end = min(c_begin + chunks_per_block, nchunks);
+  if (c_begin >= c_end) return;
+  // a block walks consecutive chunks, so only its first chunk needs a search in global memory for the pair
+  // that contains the chunk start; afterwards the position carries over
   if (threadIdx.x == 0) {
-    // first pair whose end lies beyond the chunk start: upper_bound(offs[1..U], b0)
-    uint64_t lo = 0, hi = U;
+    const uint64_t b0 = c_begin * FILL_CHUNK_WORDS * 4;
+    uint64_t lo = 0, hi = U;  // first pair whose end lies beyond b0
     while (lo < hi) {
       uint64_t mid = (lo + hi) >> 1;
       if (offs[mid + 1] > b0) hi = mid;
@@ -106,48 +129,96 @@ dense_fill_kernel(uint32_t *__restrict__ out, uint64_t total_words, const uint64
     }
     s_u0 = lo;
   }
-  __syncthreads();
-  const uint64_t u0 = s_u0;
-  // pairs u0 .. while offs[u] < b1
-  for (int q = threadIdx.x; q <= FILL_MAX_PAIRS; q += FILL_THREADS) {
-    uint64_t u = u0 + q;
-    s_off[q] = u <= U ? offs[u] : ~0ull;
-    if (q < FILL_MAX_PAIRS && u < U) {
-      s_key[q] = ukey[u];
-      s_cnt[q] = ucnt[u];
+  for (uint64_t c = c_begin; c < c_end; c++) {
+    __syncthreads();
+    const uint64_t w0 = c * FILL_CHUNK_WORDS;
+    const uint64_t b1 = min((w0 + FILL_CHUNK_WORDS) * 4, total_words * 4);
+    const uint64_t u0 = s_u0;
+    // load the pairs that start before the chunk end, a batch of FILL_THREADS at a time (usually one batch)
+    int np_acc = 0;
+    for (int base = 0; base <= FILL_MAX_PAIRS; base += FILL_THREADS) {
+      const int q = base + threadIdx.x;
+      const uint64_t u = u0 + q;
+      const uint64_t o = (q <= FILL_MAX_PAIRS && u <= U) ? offs[u] : ~0ull;
+      if (q <= FILL_MAX_PAIRS) {
+        s_off[q] = o;
+        if (q < FILL_MAX_PAIRS && u < U) {
+          s_key[q] = ukey[u];
+          s_cnt[q] = ucnt[u];
+        }
+      }
+      const int c = __syncthreads_count(o < b1);
+      np_acc += c;
+      if (c < FILL_THREADS) break;  // block-uniform: the first pair starting at or after b1 is loaded too
     }
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int np = 0;
-    while (np < FILL_MAX_PAIRS && s_off[np] < b1) np++;
-    s_np = np;  // pairs 0..np-1 start before the chunk end
-  }
-  __syncthreads();
-  const int np = s_np;
-#pragma unroll 4
-  for (int k = 0; k < FILL_WORDS_PER_THREAD; k++) {
-    uint64_t w = w0 + (uint64_t) k * FILL_THREADS + threadIdx.x;
-    if (w >= total_words) break;
-    uint64_t b = w * 4;
-    // last pair with s_off <= b
-    int lo = 0, hi = np - 1;
-    while (lo < hi) {
-      int mid = (lo + hi + 1) >> 1;
-      if (s_off[mid] <= b) lo = mid;
-      else hi = mid - 1;
+    if (threadIdx.x == 0) s_np = np_acc;
+    __syncthreads();
+    const int np = s_np;
+    // each thread produces 16 consecutive words (four 16-byte stores): one binary search in shared memory
+    // for its first word, then it walks forward through the pairs
+    const uint64_t wfirst = w0 + (uint64_t) threadIdx.x * FILL_WORDS_PER_THREAD;
+    if (wfirst < total_words) {
+      int lo = 0, hi = np - 1;
+      {
+        const uint64_t b = wfirst * 4;
+        while (lo < hi) {
+          int mid = (lo + hi + 1) >> 1;
+          if (s_off[mid] <= b) lo = mid;
+          else hi = mid - 1;
+        }
+      }
+      uint64_t pbase = s_off[lo], pnext = s_off[lo + 1];
+      uint64_t nv = s_cnt[lo], ko = kmv_key_off(al, nv), vo = kmv_val_off(al, nv, kb);
+      uint32_t pkey = s_key[lo];
+      uint32_t wbuf[FILL_WORDS_PER_THREAD];
+      // most of the stream is the inside of a long pair's size array or value array: 64 bytes of one constant
+      const uint64_t sb = wfirst * 4, se = sb + 4 * FILL_WORDS_PER_THREAD, r0 = sb - pbase;
+      const bool in_sizes = se <= pnext && r0 >= 12 && r0 + 4 * FILL_WORDS_PER_THREAD <= 12 + 4 * nv;
+      const bool in_values = se <= pnext && r0 >= vo && r0 + 4 * FILL_WORDS_PER_THREAD <= vo + nv * vb;
+      if (in_sizes || in_values) {
+        const bool odd = in_values && vb == 8 && ((r0 - vo) & 4);
+        const uint32_t e = in_sizes ? vb : (odd ? cv1 : cv0), o = in_sizes ? vb : (vb == 8 ? (odd ? cv0 : cv1) : cv0);
+#pragma unroll
+        for (int k = 0; k < FILL_WORDS_PER_THREAD; k += 2) {
+          wbuf[k] = e;
+          wbuf[k + 1] = o;
+        }
+      } else
+#pragma unroll
+      for (int k = 0; k < FILL_WORDS_PER_THREAD; k++) {
+        const uint64_t b = (wfirst + k) * 4;
+        if (b >= pnext && lo + 1 < np) {  // next pair
+          lo++;
+          pbase = pnext;
+          pnext = s_off[lo + 1];
+          nv = s_cnt[lo];
+          ko = kmv_key_off(al, nv);
+          vo = kmv_val_off(al, nv, kb);
+          pkey = s_key[lo];
+        }
+        const uint64_t r = b - pbase;
+        uint32_t word = 0;
+        if (r >= 12 && r < 12 + 4 * nv) word = vb;
+        else if (r >= vo && r < vo + nv * vb) word = (vb == 8 && ((r - vo) & 4)) ? cv1 : cv0;
+        else if (r == 0) word = (uint32_t) nv;
+        else if (r == 4) word = kb;
+        else if (r == 8) word = (uint32_t) (nv * vb);
+        else if (r == ko) word = pkey;  // 8-byte keys: the high word is 0 on this path
+        wbuf[k] = word;
+      }
+      if (wfirst + FILL_WORDS_PER_THREAD <= total_words && (((uintptr_t) (out + wfirst)) & 15) == 0) {
+#pragma unroll
+        for (int k = 0; k < FILL_WORDS_PER_THREAD; k += 4)
+          st_stream((int4 *) (out + wfirst + k), make_int4((int) wbuf[k], (int) wbuf[k + 1], (int) wbuf[k + 2], (int) wbuf[k + 3]));
+      } else {
+#pragma unroll
+        for (int k = 0; k < FILL_WORDS_PER_THREAD; k++)
+          if (wfirst + k < total_words) out[wfirst + k] = wbuf[k];
+      }
     }
-    const uint64_t r = b - s_off[lo];
-    const uint64_t nv = s_cnt[lo];
-    const uint64_t ko = kmv_key_off(al, nv), vo = kmv_val_off(al, nv, kb);
-    uint32_t word = 0;
-    if (r == 0) word = (uint32_t) nv;
-    else if (r == 4) word = kb;
-    else if (r == 8) word = (uint32_t) (nv * vb);
-    else if (r < 12 + 4 * nv) word = vb;
-    else if (r >= ko && r < ko + kb) word = (r - ko) == 0 ? s_key[lo] : 0u;  // 8-byte keys: high word is 0 here
-    else if (r >= vo && r < vo + nv * vb) word = (vb == 8 && ((r - vo) & 4)) ? cv1 : cv0;
-    out[w] = word;
+    __syncthreads();
+    // the pair that contains the next chunk's first byte: the last one seen if it runs past b1, else the next
+    if (threadIdx.x == 0) s_u0 = u0 + (uint64_t) np - (s_off[np] > b1 ? 1 : 0);
   }
 }
 
@@ -226,8 +297,11 @@ static bool convert_dense(mrgpu_mr *mr)
     {
       ProfScope ps(pool, "convert_dense_fill", (double) total + 16.0 * U);
       const uint64_t words = total / 4;
-      dense_fill_kernel<<<(unsigned) ((words + FILL_CHUNK_WORDS - 1) / FILL_CHUNK_WORDS), FILL_THREADS, 0, s>>>(
-          (uint32_t *) kmv->data, words, offs, ukey.p, ucnt.p, U, al, kb, vb, cv[0], cv[1]);
+      const uint64_t nchunks = (words + FILL_CHUNK_WORDS - 1) / FILL_CHUNK_WORDS;
+      const uint64_t nblk = std::min<uint64_t>(nchunks, (uint64_t) kSMs * 16);
+      const uint64_t cpb = (nchunks + nblk - 1) / nblk;
+      dense_fill_kernel<<<(unsigned) ((nchunks + cpb - 1) / cpb), FILL_THREADS, 0, s>>>((uint32_t *) kmv->data, words, offs, ukey.p, ucnt.p, U, al, kb,
+                                                                                       vb, cv[0], cv[1], cpb);
       MR_CUDA(cudaGetLastError());
     }
     kmv->nkmv = U;
