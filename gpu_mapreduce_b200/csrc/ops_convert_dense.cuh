@@ -20,8 +20,17 @@
 
 constexpr uint32_t DENSE_BITS = 26;                 // table of 2^26 u32 counts = 256 MB (touched part stays in L2)
 constexpr uint32_t DENSE_SLOTS = 1u << DENSE_BITS;
-constexpr int DENSE_CACHE = 8192;                   // per-block cache entries (64 KB of shared memory)
-constexpr uint32_t DENSE_EMPTY = 0xFFFFFFFFu;
+#ifndef MRGPU_DENSE_CACHE_BITS
+#define MRGPU_DENSE_CACHE_BITS 15
+#endif
+// Per-block cache: 2^15 entries = a u32 tag (key+1, 0 = empty; 128 KB) and a 15-bit count packed two per word
+// (64 KB): 192 KB of shared memory, one 1024-thread block per SM.  A hit is one shared atomic add.  Bit 15 of
+// each half-word is a guard: the add that takes a count from 0x7FFF to 0x8000 cannot carry into the neighbour;
+// the thread that did it subtracts the 0x8000 again and forwards 32768 to the table in L2.  Measured on the
+// IntCount workload (ncu + A/B runs): the L2 atomics of cache MISSES bound this kernel (64-entry cache 125 ms,
+// 512: 50 ms, 8192: 7.7 ms, 16384: 5.4 ms) and L2 atomics on one address are slow (forwarding the hottest key
+// every 32 hits cost 20 ms), hence the largest cache that fits and counts that rarely overflow.
+constexpr int DENSE_CACHE = 1 << MRGPU_DENSE_CACHE_BITS;
 
 struct DenseArgs {
   const uint8_t *data;
@@ -29,15 +38,19 @@ struct DenseArgs {
   uint32_t rs, koff, voff, kb, vb;
 };
 
-__global__ void __launch_bounds__(512)
+#ifndef MRGPU_DENSE_THREADS
+#define MRGPU_DENSE_THREADS 1024
+#endif
+#ifndef MRGPU_DENSE_BPS
+#define MRGPU_DENSE_BPS 1
+#endif
+__global__ void __launch_bounds__(MRGPU_DENSE_THREADS)
 dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long *abort_flag)
 {
   extern __shared__ unsigned dsm[];
-  unsigned *ckey = dsm, *ccnt = dsm + DENSE_CACHE;
-  for (int i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x) {
-    ckey[i] = DENSE_EMPTY;
-    ccnt[i] = 0;
-  }
+  unsigned *tags = dsm, *cnts = dsm + DENSE_CACHE;  // cnts: DENSE_CACHE / 2 words
+  for (int i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x) tags[i] = 0;
+  for (int i = threadIdx.x; i < DENSE_CACHE / 2; i += blockDim.x) cnts[i] = 0;
   __syncthreads();
   // value of record 0 (compared word-wise; vb is 0, 4 or 8 here)
   uint32_t v0a = 0, v0b = 0;
@@ -51,11 +64,22 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
       bad = true;
       return;
     }
-    unsigned slot = (key * 0x9E3779B1u) >> (32 - 13);  // 8192 slots
-    unsigned old = ckey[slot];
-    if (old == DENSE_EMPTY) old = atomicCAS(&ckey[slot], DENSE_EMPTY, key);
-    if (old == DENSE_EMPTY || old == key) atomicAdd(&ccnt[slot], 1u);
-    else atomicAdd(&table[key], 1u);
+    const unsigned slot = (key * 0x9E3779B1u) >> (32 - MRGPU_DENSE_CACHE_BITS);
+    const unsigned tag = key + 1;
+    unsigned t = tags[slot];
+    if (t == 0) {
+      t = atomicCAS(&tags[slot], 0u, tag);
+      if (t == 0) t = tag;
+    }
+    if (t == tag) {
+      const unsigned sh = (slot & 1) * 16;
+      unsigned old = atomicAdd(&cnts[slot >> 1], 1u << sh);
+      if (((old >> sh) & 0xFFFF) == 0x7FFF) {  // this add set the guard bit: take the 32768 out again
+        atomicSub(&cnts[slot >> 1], 0x8000u << sh);
+        atomicAdd(&table[key], 32768u);
+      }
+    } else
+      atomicAdd(&table[key], 1u);
   };
   if (rec16) {
     // one 16-byte load per record {kb, vb, w2, w3}; eight independent loads in flight per thread -- with a
@@ -92,8 +116,10 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
     if (threadIdx.x == 0) *abort_flag = 1;
     return;  // the table is abandoned; the caller falls back to the sort path
   }
-  for (int i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x)
-    if (ccnt[i]) atomicAdd(&table[ckey[i]], ccnt[i]);
+  for (int i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x) {
+    unsigned c = (cnts[i >> 1] >> ((i & 1) * 16)) & 0xFFFF;
+    if (c) atomicAdd(&table[tags[i] - 1], c);
+  }
 }
 
 // One thread per 4-byte word of the KMV stream: coalesced stores, no reads of pair data at all.
@@ -241,13 +267,13 @@ static bool convert_dense(mrgpu_mr *mr)
   MR_CUDA(cudaMemsetAsync(flag, 0, 8, s));
   static bool attr_set[64] = {false};
   if (mr->device < 64 && !attr_set[mr->device]) {
-    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 8));
+    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 6));
     attr_set[mr->device] = true;
   }
   {
     ProfScope ps(pool, "convert_dense_count", (double) kv->nbytes);
     DenseArgs a{kv->data, n, rs, koff, voff, kb, vb};
-    dense_count_kernel<<<kSMs * 3, 512, DENSE_CACHE * 8, s>>>(a, table.p, flag);
+    dense_count_kernel<<<kSMs * MRGPU_DENSE_BPS, MRGPU_DENSE_THREADS, DENSE_CACHE * 6, s>>>(a, table.p, flag);
     MR_CUDA(cudaGetLastError());
   }
   unsigned long long h_flag = 1;
