@@ -74,6 +74,7 @@ def lib():
         "mrgpu_add": [vp, vp, u64p],
         "mrgpu_aggregate": [vp, u64p],
         "mrgpu_plan_exchange": [C.c_int, C.c_int, u64p, u64p, u64p, u64p, u64p, u64p, C.POINTER(C.c_int)],
+        "mrgpu_debug_partition": [vp, C.c_int, u64p],
         "mrgpu_convert": [vp, u64p],
         "mrgpu_collate": [vp, u64p],
         "mrgpu_reduce": [vp, C.c_int, u64p],
@@ -247,6 +248,12 @@ class MapReduce:
         if hash is not None:
             raise MRError(-1, "user hash callbacks run on the host; only the default hashlittle partition is built")
         return self._count(lib().mrgpu_aggregate)
+
+    def debug_partition(self, nprocs):
+        """local half of aggregate() for a virtual rank count (test / profiling hook); returns per-destination counts"""
+        c = (C.c_uint64 * nprocs)()
+        self._ck(lib().mrgpu_debug_partition(self._h, nprocs, c))
+        return list(c)
 
     def convert(self):
         return self._count(lib().mrgpu_convert)

@@ -234,6 +234,8 @@ extern "C" int mrgpu_plan_exchange(int nranks, int rank, const uint64_t *table, 
   return MRGPU_OK;
 }
 
+static bool partition_uniform(mrgpu_mr *mr, DevKV *kv, uint8_t *sendbuf, std::vector<uint64_t> &scount);
+
 static void aggregate_impl(mrgpu_mr *mr)
 {
   freeze(mr);
@@ -247,58 +249,66 @@ static void aggregate_impl(mrgpu_mr *mr)
   if (n >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "aggregate: more than 2^32-2 pairs on one GPU is not supported yet");
   ncclComm_t comm = (ncclComm_t) mr->comm;
 
-  // 1. destinations, grouped stably
-  Buf<uint32_t> d0(pool, n), d1(pool, n), i0(pool, n), i1(pool, n);
-  Buf<unsigned long long> hist(pool, 8 * RADIX);
-  MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
-  if (n) {
-    ProfScope ps(pool, "aggregate_partition", (double) kv->nbytes + 8.0 * n);
-    partition_dest_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>(kv->data, kv->uniform ? nullptr : kv->offs, kv->recsize, n, al, (uint32_t) P, d0.p,
-                                                                i0.p, hist.p);
-    MR_CUDA(cudaGetLastError());
-  }
-  std::vector<unsigned long long> cnt(RADIX);
-  MR_CUDA(cudaMemcpyAsync(cnt.data(), hist.p, RADIX * 8, cudaMemcpyDeviceToHost, s));
-  sync(mr);
-  // bytes 1..3 of the dest "key" are all zero: mark them as known-constant
-  MR_CUDA(cudaMemsetAsync(hist.p + RADIX, 0, 3 * RADIX * 8, s));
-  int cur = radix_sort_pairs<uint32_t, uint32_t, true>(pool, d0.p, d1.p, i0.p, i1.p, n, 0x1, true, hist.p);
-  const uint32_t *perm = cur ? i1.p : i0.p;
-
-  // 2. pack the send buffer in destination order
   Buf<uint8_t> sendbuf(pool, kv->nbytes);
   Buf<uint32_t> ssizes;
   Buf<uint64_t> soffs;
-  bool uni = kv->uniform;
+  const bool uni = kv->uniform;
   std::vector<uint64_t> scount(P), sbytes(P), sdisp(P + 1, 0), srec(P + 1, 0);
-  for (int p = 0; p < P; p++) {
-    scount[p] = cnt[p];
-    srec[p + 1] = srec[p] + cnt[p];
-  }
-  if (n) {
-    if (uni) {
-      uint32_t words = kv->recsize / 4;
-      ProfScope ps(pool, "aggregate_pack", 2.0 * kv->nbytes + 4.0 * n);
-      gather_uniform_kernel<<<(unsigned) ((n * words + 255) / 256), 256, 0, s>>>((const uint32_t *) kv->data, (uint32_t *) sendbuf.p, perm, n, words);
+  if (n && partition_uniform(mr, kv, sendbuf.p, scount)) {
+    // single pass: records hashed, ranked and packed by destination (ops_partition.cuh)
+    for (int p = 0; p < P; p++) {
+      srec[p + 1] = srec[p] + scount[p];
+      sbytes[p] = scount[p] * kv->recsize;
+    }
+  } else {
+    // 1. destinations, grouped stably
+    Buf<uint32_t> d0(pool, n), d1(pool, n), i0(pool, n), i1(pool, n);
+    Buf<unsigned long long> hist(pool, 8 * RADIX);
+    MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
+    if (n) {
+      ProfScope ps(pool, "aggregate_partition", (double) kv->nbytes + 8.0 * n);
+      partition_dest_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>(kv->data, kv->uniform ? nullptr : kv->offs, kv->recsize, n, al, (uint32_t) P, d0.p,
+                                                                  i0.p, hist.p);
       MR_CUDA(cudaGetLastError());
-      for (int p = 0; p < P; p++) sbytes[p] = scount[p] * kv->recsize;
-    } else {
-      ssizes.alloc(pool, n);
-      soffs.alloc(pool, n + 1);
-      record_sizes_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(kv->offs, perm, n, ssizes.p);
-      MR_CUDA(cudaGetLastError());
-      const uint32_t *sz = ssizes.p;
-      uint64_t *so = soffs.p;
-      scan_apply(
-          pool, n, [=] __device__(uint64_t i) -> unsigned long long { return sz[i]; },
-          [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { so[i] = e; }, mr->d_small);
-      MR_CUDA(cudaMemcpyAsync(so + n, mr->d_small, 8, cudaMemcpyDeviceToDevice, s));
-      gather_general_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(kv->data, kv->offs, sendbuf.p, soffs.p, perm, n);
-      MR_CUDA(cudaGetLastError());
-      std::vector<uint64_t> edge(P + 1);
-      for (int p = 0; p <= P; p++) MR_CUDA(cudaMemcpyAsync(&edge[p], soffs.p + srec[p], 8, cudaMemcpyDeviceToHost, s));
-      sync(mr);
-      for (int p = 0; p < P; p++) sbytes[p] = edge[p + 1] - edge[p];
+    }
+    std::vector<unsigned long long> cnt(RADIX);
+    MR_CUDA(cudaMemcpyAsync(cnt.data(), hist.p, RADIX * 8, cudaMemcpyDeviceToHost, s));
+    sync(mr);
+    // bytes 1..3 of the dest "key" are all zero: mark them as known-constant
+    MR_CUDA(cudaMemsetAsync(hist.p + RADIX, 0, 3 * RADIX * 8, s));
+    int cur = radix_sort_pairs<uint32_t, uint32_t, true>(pool, d0.p, d1.p, i0.p, i1.p, n, 0x1, true, hist.p);
+    const uint32_t *perm = cur ? i1.p : i0.p;
+
+    // 2. pack the send buffer in destination order
+    for (int p = 0; p < P; p++) {
+      scount[p] = cnt[p];
+      srec[p + 1] = srec[p] + cnt[p];
+    }
+    if (n) {
+      if (uni) {
+        uint32_t words = kv->recsize / 4;
+        ProfScope ps(pool, "aggregate_pack", 2.0 * kv->nbytes + 4.0 * n);
+        gather_uniform_kernel<<<(unsigned) ((n * words + 255) / 256), 256, 0, s>>>((const uint32_t *) kv->data, (uint32_t *) sendbuf.p, perm, n, words);
+        MR_CUDA(cudaGetLastError());
+        for (int p = 0; p < P; p++) sbytes[p] = scount[p] * kv->recsize;
+      } else {
+        ssizes.alloc(pool, n);
+        soffs.alloc(pool, n + 1);
+        record_sizes_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(kv->offs, perm, n, ssizes.p);
+        MR_CUDA(cudaGetLastError());
+        const uint32_t *sz = ssizes.p;
+        uint64_t *so = soffs.p;
+        scan_apply(
+            pool, n, [=] __device__(uint64_t i) -> unsigned long long { return sz[i]; },
+            [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { so[i] = e; }, mr->d_small);
+        MR_CUDA(cudaMemcpyAsync(so + n, mr->d_small, 8, cudaMemcpyDeviceToDevice, s));
+        gather_general_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(kv->data, kv->offs, sendbuf.p, soffs.p, perm, n);
+        MR_CUDA(cudaGetLastError());
+        std::vector<uint64_t> edge(P + 1);
+        for (int p = 0; p <= P; p++) MR_CUDA(cudaMemcpyAsync(&edge[p], soffs.p + srec[p], 8, cudaMemcpyDeviceToHost, s));
+        sync(mr);
+        for (int p = 0; p < P; p++) sbytes[p] = edge[p + 1] - edge[p];
+      }
     }
   }
   for (int p = 0; p < P; p++) sdisp[p + 1] = sdisp[p] + sbytes[p];

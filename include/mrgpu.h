@@ -136,6 +136,10 @@ int mrgpu_aggregate(mrgpu_mr *mr, uint64_t *nkv);
  * Pure host arithmetic; mrgpu_aggregate uses it internally. */
 int mrgpu_plan_exchange(int nranks, int rank, const uint64_t *table, uint64_t *rcount, uint64_t *rbytes,
                         uint64_t *rdisp, uint64_t *rrec, uint64_t *shape, int *kind);
+/* Test / profiling hook for the local half of aggregate() (hash src/mapreduce.cpp:469-472 + pack
+ * src/irregular.cpp:279-288) with a virtual rank count on one GPU: the KV is replaced by the same pairs grouped
+ * stably by destination hashlittle(key,keybytes,nprocs) % nprocs; counts[d] = pairs for destination d. */
+int mrgpu_debug_partition(mrgpu_mr *mr, int nprocs, uint64_t *counts);
 /* MapReduce::convert src/mapreduce.cpp:861-886 -> KeyMultiValue::convert src/keymultivalue.cpp:486-638 */
 int mrgpu_convert(mrgpu_mr *mr, uint64_t *nkmv);
 /* MapReduce::collate(NULL) src/mapreduce.cpp:710-738 */

@@ -342,6 +342,23 @@ def test_convert_hot_key_bigger_than_page(MR, golden, oracle):
     assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(golden["extended.count"]))
 
 
+@pytest.mark.parametrize("kb,vb", [(4, 4), (4, 0), (8, 0), (8, 4), (8, 8), (16, 0)])
+@pytest.mark.parametrize("P", [2, 3, 8, 33])
+def test_single_pass_partition_matches_reference_placement(MR, oracle, kb, vb, P):
+    """local half of aggregate(): every pair in the slice of rank hashlittle(key,kb,P) % P, original order kept"""
+    r = np.random.RandomState(kb * 7 + vb + P)
+    n = 5000 if P == 33 else 21000
+    recs = [(bytes(r.randint(0, 256, size=kb).astype(np.uint8)) if i % 3 else struct.pack("<I", 7) * (kb // 4),
+             struct.pack("<I", i)[:vb] if vb <= 4 else struct.pack("<II", i, ~i & 0xFFFFFFFF)) for i in range(n)]
+    mr = MR()
+    mr.kv_add(recs)
+    counts = mr.debug_partition(P)
+    dest = oracle.partition(H.kv_encode(recs), P)
+    want = [rec for p in range(P) for rec, d in zip(recs, dest) if d == p]
+    assert counts == [dest.count(p) for p in range(P)]
+    assert mr.scan_kv() == want
+
+
 # ------------------------------------------------------------------------------------------- sort_keys
 
 @pytest.mark.parametrize("flag", [1, 2, 3, 4, 5, 6])
