@@ -9,6 +9,7 @@
 #include <string.h>
 #include <stdlib.h>
 #include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -121,7 +122,7 @@ struct Pool {
   void trim()
   {
     for (size_t c = 0; c < chunks.size(); c++) {
-      if (!chunks[c].first) continue;
+      if (!chunks[c].first || exported.count((int) c)) continue;  // a peer process may hold a mapping of an exported chunk
       auto it = freeb.find(chunks[c].first);
       if (it != freeb.end() && it->second.size == chunks[c].second) {
         erase_free(it);
@@ -197,6 +198,17 @@ struct Pool {
       }
     }
     add_free(p, b);
+  }
+  // the cudaMalloc allocation a live block belongs to (for CUDA IPC, which shares whole allocations)
+  std::set<int> exported;  // chunks whose CUDA IPC handle went to peer ranks: kept until the pool dies
+  bool chunk_of(const void *ptr, uint8_t **base, uint64_t *size)
+  {
+    auto u = used.find((uint8_t *) ptr);
+    if (u == used.end()) return false;
+    exported.insert(u->second.chunk);
+    *base = chunks[u->second.chunk].first;
+    *size = chunks[u->second.chunk].second;
+    return true;
   }
   ~Pool()
   {

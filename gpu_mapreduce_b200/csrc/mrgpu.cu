@@ -45,6 +45,8 @@ struct mrgpu_mr {
   void *comm = nullptr;            // ncclComm_t
   unsigned long long *d_small = nullptr;  // [64] device scalars (totals, flags)
   unsigned long long *h_small = nullptr;  // pinned mirror
+  bool p2p_used = false;  // set identically on every rank
+  std::map<std::string, void *> ipc_open;  // peers' receive chunks mapped by the peer-store exchange (CUDA IPC handle -> base)
 };
 
 #define API_BEGIN(mr)                     \
@@ -112,8 +114,8 @@ static uint64_t allreduce_sum(mrgpu_mr *mr, uint64_t v);
 #include "ops_text.cuh"
 #include "ops_reduce.cuh"
 #include "ops_sort.cuh"
-#include "ops_aggregate.cuh"
 #include "ops_partition.cuh"
+#include "ops_aggregate.cuh"
 #include "ops_pages.cuh"
 
 // ================================================================================================
@@ -154,7 +156,12 @@ extern "C" int mrgpu_destroy(mrgpu_mr *mr)
   delete mr->kv;
   delete mr->kmv;
   cudaStreamSynchronize(mr->pool.stream);
-  if (mr->comm) comm_destroy(mr);
+  if (mr->comm) {
+    // like MapReduce::~MapReduce's MPI_Comm_free (src/mapreduce.cpp:283), collective once ranks share memory:
+    // unmap the peers' buffers, then wait until every peer has unmapped mine before the pool frees it
+    if (mr->p2p_used) peer_store_teardown(mr);
+    comm_destroy(mr);
+  }
   cudaFree(mr->d_small);
   cudaFreeHost(mr->h_small);
   delete mr;

@@ -234,7 +234,107 @@ extern "C" int mrgpu_plan_exchange(int nranks, int rank, const uint64_t *table, 
   return MRGPU_OK;
 }
 
-static bool partition_uniform(mrgpu_mr *mr, DevKV *kv, uint8_t *sendbuf, std::vector<uint64_t> &scount);
+// ---------------------------------------------------------------------------------------------------------
+// Peer-store exchange: partition pass 2 writes every pair straight into its destination rank's receive buffer
+// over NVLink -- the compute step (hash partition) and the collective (all-to-all) are one kernel; no local
+// send buffer, no separate transfer.  Needs: every rank holds uniform records of one shape (so slices are
+// record-count arithmetic), and the receive buffers are mapped into every peer with CUDA IPC (one rank = one
+// process).  Protocol, all on the handle's stream:
+//   1. every rank allocates its receive buffer (size known from the gathered count table);
+//   2. all-gather of {ok flag, IPC handle of the cudaMalloc chunk holding it, offset} -- which is also the barrier
+//      that guarantees every buffer exists and its previous users have drained;
+//   3. each rank maps its peers' chunks (cached per handle), agrees by all-reduce that everyone succeeded;
+//   4. scatter kernel: destination d's slice = peer d's buffer + (bytes rank d receives from lower ranks);
+//   5. all-reduce = barrier: when it completes every scatter kernel has finished, so the buffer is complete.
+// Returns false (nothing written) when any rank cannot take part; the caller then uses ncclSend/ncclRecv.
+
+static bool exchange_peer_store(mrgpu_mr *mr, DevKV *kv, DevKV *nk, PartPlan *pl, uint64_t n, const std::vector<unsigned long long> &table, int W,
+                                const std::vector<uint64_t> &scount, const std::vector<uint64_t> &rdisp, uint64_t brecv)
+{
+  static const bool enabled = !(getenv("MRGPU_P2P") && atoi(getenv("MRGPU_P2P")) == 0);
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const int P = mr->nranks, me = mr->rank;
+  ncclComm_t comm = (ncclComm_t) mr->comm;
+  // row: [0] ok, [1..8] handle, [9] offset of my receive buffer inside the chunk
+  constexpr int RW64 = 10;
+  std::vector<unsigned long long> row(RW64, 0), rows((size_t) RW64 * P, 0);
+  uint8_t *cbase = nullptr;
+  uint64_t csize = 0;
+  bool ok = enabled && (n == 0 || pl != nullptr) && pool.chunk_of(nk->data, &cbase, &csize);
+  if (ok) {
+    cudaIpcMemHandle_t h;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+    if (cudaIpcGetMemHandle(&h, cbase) != cudaSuccess) {
+      cudaGetLastError();
+      ok = false;
+    } else {
+      memcpy(&row[1], &h, 64);
+      row[9] = (unsigned long long) (nk->data - cbase);
+    }
+  }
+  row[0] = ok ? 1 : 0;
+  Buf<unsigned long long> drow(pool, RW64), drows(pool, (uint64_t) RW64 * P);
+  MR_CUDA(cudaMemcpyAsync(drow.p, row.data(), RW64 * 8, cudaMemcpyHostToDevice, s));
+  MR_NCCL(nccl().AllGather(drow.p, drows.p, RW64, ncclUint64, comm, s));
+  MR_CUDA(cudaMemcpyAsync(rows.data(), drows.p, (size_t) RW64 * P * 8, cudaMemcpyDeviceToHost, s));
+  sync(mr);
+  for (int q = 0; q < P; q++)
+    if (!rows[(size_t) q * RW64]) return false;  // same answer on every rank
+  mr->p2p_used = true;
+  // map the peers' chunks
+  DestPtrs dp;
+  bool opened = true;
+  for (int q = 0; q < P && opened; q++) {
+    uint8_t *base = nullptr;
+    if (q == me) base = cbase;
+    else {
+      std::string key((const char *) &rows[(size_t) q * RW64 + 1], 64);
+      auto it = mr->ipc_open.find(key);
+      if (it != mr->ipc_open.end()) base = (uint8_t *) it->second;
+      else {
+        cudaIpcMemHandle_t h;
+        memcpy(&h, &rows[(size_t) q * RW64 + 1], 64);
+        void *ptr = nullptr;
+        if (cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+          cudaGetLastError();
+          opened = false;
+        } else {
+          mr->ipc_open[key] = ptr;
+          base = (uint8_t *) ptr;
+        }
+      }
+    }
+    if (!opened) break;
+    // rank q receives my pairs after those of the ranks below me: sum over sources < me of bytes sent to q
+    uint64_t disp = 0;
+    for (int src = 0; src < me; src++) disp += table[(size_t) src * W + 2 * q + 1];
+    dp.base[q] = base + rows[(size_t) q * RW64 + 9] + disp;
+  }
+  if (allreduce_sum(mr, opened ? 0 : 1) != 0) return false;  // somebody could not map a peer: everyone falls back
+  (void) rdisp;
+  (void) brecv;
+  uint64_t wire = 0;
+  for (int q = 0; q < P; q++)
+    if (q != me) wire += scount[q] * kv->recsize;
+  {
+    ProfScope ps(pool, "aggregate_exchange_nvlink", (double) wire, 0);  // brackets the scatter + the completion barrier
+    if (n) partition_scatter(mr, kv, *pl, dp, "aggregate_partition_peer_store", true);
+    allreduce_sum(mr, 1);  // barrier: every rank's stores have landed
+  }
+  return true;
+}
+
+static void peer_store_teardown(mrgpu_mr *mr)
+{
+  for (auto &kvp : mr->ipc_open) cudaIpcCloseMemHandle(kvp.second);
+  mr->ipc_open.clear();
+  cudaGetLastError();
+  try {
+    allreduce_sum(mr, 1);
+  } catch (...) {
+  }
+}
 
 static void aggregate_impl(mrgpu_mr *mr)
 {
@@ -249,18 +349,24 @@ static void aggregate_impl(mrgpu_mr *mr)
   if (n >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "aggregate: more than 2^32-2 pairs on one GPU is not supported yet");
   ncclComm_t comm = (ncclComm_t) mr->comm;
 
-  Buf<uint8_t> sendbuf(pool, kv->nbytes);
+  Buf<uint8_t> sendbuf;
   Buf<uint32_t> ssizes;
   Buf<uint64_t> soffs;
   const bool uni = kv->uniform;
   std::vector<uint64_t> scount(P), sbytes(P), sdisp(P + 1, 0), srec(P + 1, 0);
-  if (n && partition_uniform(mr, kv, sendbuf.p, scount)) {
-    // single pass: records hashed, ranked and packed by destination (ops_partition.cuh)
+  // uniform records: pass 1 of the single-pass partition (ops_partition.cuh) gives the per-destination counts now;
+  // pass 2 writes the pairs later -- straight into the peers' receive buffers when the peer-store exchange is
+  // possible, else into a local send buffer for NCCL
+  const bool fast = n && partition_eligible(mr, kv);
+  PartPlan pl;
+  if (fast) {
+    partition_counts(mr, kv, pl, scount);
     for (int p = 0; p < P; p++) {
       srec[p + 1] = srec[p] + scount[p];
       sbytes[p] = scount[p] * kv->recsize;
     }
   } else {
+    sendbuf.alloc(pool, kv->nbytes);
     // 1. destinations, grouped stably
     Buf<uint32_t> d0(pool, n), d1(pool, n), i0(pool, n), i1(pool, n);
     Buf<unsigned long long> hist(pool, 8 * RADIX);
@@ -339,7 +445,15 @@ static void aggregate_impl(mrgpu_mr *mr)
   // 4. payload all-to-all over NVLink (replaces MPI_Alltoallv, src/irregular.cpp:292-300)
   DevKV *nk = new DevKV(&pool);
   try {
-    nk->reserve_bytes(brecv);
+    nk->reserve_bytes(brecv > 512 ? brecv : 512);
+    bool delivered = false;
+    if (kind == 2) delivered = exchange_peer_store(mr, kv, nk, fast ? &pl : nullptr, n, all, W, scount, rdisp, brecv);
+    if (!delivered && fast) {  // NCCL path needs the pairs packed locally
+      sendbuf.alloc(pool, kv->nbytes);
+      DestPtrs dp;
+      for (int p = 0; p < P; p++) dp.base[p] = sendbuf.p + srec[p] * kv->recsize;
+      partition_scatter(mr, kv, pl, dp, "aggregate_partition_scatter");
+    }
     Buf<uint32_t> rsizes;
     bool need_sizes = !all_uniform;
     if (need_sizes) {
@@ -353,6 +467,7 @@ static void aggregate_impl(mrgpu_mr *mr)
     uint64_t wire = 0;
     for (int p = 0; p < P; p++)
       if (p != mr->rank) wire += sbytes[p] > rbytes[p] ? sbytes[p] : rbytes[p];
+    if (!delivered) {
     ProfScope psx(pool, "aggregate_exchange_nvlink", (double) wire);
     MR_NCCL(nccl().GroupStart());
     for (int p = 0; p < P; p++) {
@@ -370,6 +485,7 @@ static void aggregate_impl(mrgpu_mr *mr)
       MR_CUDA(cudaMemcpyAsync(nk->data + rdisp[me], sendbuf.p + sdisp[me], sbytes[me], cudaMemcpyDeviceToDevice, s));
     if (need_sizes && scount[me])
       MR_CUDA(cudaMemcpyAsync(rsizes.p + rrec[me], ssizes.p + srec[me], scount[me] * 4, cudaMemcpyDeviceToDevice, s));
+    }
 
     nk->nbytes = brecv;
     nk->nkv = nrecv;

@@ -137,12 +137,19 @@ __device__ __forceinline__ unsigned match_dest(uint32_t d, int nbits)
   return m;
 }
 
-// Pass 2: records -> destination-ordered send buffer.  toffs[d * ntiles + tile] = output slot of this tile's
-// first pair for destination d (exclusive scan of pass 1's counts).
+// where each destination's pairs go: a slice of the local send buffer, or -- peer-store exchange -- the
+// slice of that rank's receive buffer reserved for this source, mapped through CUDA IPC (NVLink stores)
+struct DestPtrs {
+  uint8_t *base[PART_MAXP];
+};
+
+// Pass 2: records -> destination slices.  toffs[d * ntiles + tile] = slot (counted over the whole destination-major
+// order) of this tile's first pair for destination d; slots inside a destination's slice are relative to
+// toffs[d * ntiles].
 template <int RW, int KW>
 __global__ void __launch_bounds__(PART_THREADS)
-partition_scatter_kernel(const uint32_t *__restrict__ data, uint32_t *__restrict__ out, uint64_t n, uint32_t nprocs, int nbits, uint64_t ntiles,
-                         const unsigned *__restrict__ toffs)
+partition_scatter_kernel(const uint32_t *__restrict__ data, DestPtrs dp, uint64_t n, uint32_t nprocs, int nbits, uint64_t ntiles,
+                         const unsigned *__restrict__ toffs, bool direct)
 {
   extern __shared__ __align__(16) unsigned char psm[];
   uint32_t *xrec = (uint32_t *) psm;                                // [PART_TILE * RW] records in destination order
@@ -235,7 +242,7 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, uint32_t *__restrict
 #pragma unroll
   for (int w = 0; w < PART_WARPS; w++) wc[w][tid] = my_start + wex[w];
 
-  if (tid < (int) nprocs) gbase[tid] = toffs[(uint64_t) tid * ntiles + tile] - my_start;
+  if (tid < (int) nprocs) gbase[tid] = toffs[(uint64_t) tid * ntiles + tile] - toffs[(uint64_t) tid * ntiles] - my_start;
   __syncthreads();
 
   // stage records in destination order, then write contiguous runs -- in the widest vectors the record size
@@ -243,8 +250,7 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, uint32_t *__restrict
   constexpr int VW = (RW % 4 == 0) ? 4 : ((RW % 2 == 0) ? 2 : 1);
   constexpr int NV = RW / VW;
   using V = typename std::conditional<VW == 4, uint4, typename std::conditional<VW == 2, uint2, uint32_t>::type>::type;
-  V *ov = reinterpret_cast<V *>(out);
-  if (nprocs <= PART_DIRECT_MAXP) {
+  if (direct) {
     // few destinations: each lane writes its record straight to its slot.  Lanes of a warp round that share a
     // destination hold consecutive slots, so a round produces at most nprocs contiguous pieces (>= 64 bytes
     // each on average for 16-byte records and 8 ranks) and successive rounds extend the same runs; no
@@ -259,7 +265,7 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, uint32_t *__restrict
           if constexpr (VW == 4) v = make_uint4(rec[j][4 * q], rec[j][4 * q + 1], rec[j][4 * q + 2], rec[j][4 * q + 3]);
           else if constexpr (VW == 2) v = make_uint2(rec[j][2 * q], rec[j][2 * q + 1]);
           else v = rec[j][q];
-          ov[slot + q] = v;
+          reinterpret_cast<V *>(dp.base[dest[j]])[slot + q] = v;
         }
       }
     }
@@ -285,39 +291,60 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, uint32_t *__restrict
   const unsigned nvec = nvalid * NV;
   for (unsigned v = tid; v < nvec; v += PART_THREADS) {
     const unsigned s = v / NV, q = v - s * NV;
-    ov[(uint64_t) (gbase[xdst[s]] + s) * NV + q] = xv[v];
+    reinterpret_cast<V *>(dp.base[xdst[s]])[(uint64_t) (gbase[xdst[s]] + s) * NV + q] = xv[v];
   }
 }
 
+// state between the two passes
+struct PartPlan {
+  int rw = 0, kw = 0;
+  uint64_t ntiles = 0;
+  Buf<unsigned> toffs;
+};
+
 template <int RW, int KW>
-static void partition_launch(mrgpu_mr *mr, DevKV *kv, uint8_t *sendbuf, std::vector<uint64_t> &scount)
+static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount)
 {
   Pool &pool = mr->pool;
   cudaStream_t s = pool.stream;
   const int P = mr->nranks;
   const uint64_t n = kv->nkv;
   const uint64_t ntiles = (n + PART_TILE - 1) / PART_TILE;
-  Buf<unsigned> tcount(pool, ntiles * P), toffs(pool, ntiles * P);
+  pl.rw = RW;
+  pl.kw = KW;
+  pl.ntiles = ntiles;
+  Buf<unsigned> tcount(pool, ntiles * P);
+  pl.toffs.alloc(pool, ntiles * P);
   {
     ProfScope ps(pool, "aggregate_count", (double) kv->nbytes);
     partition_count_kernel<RW, KW><<<(unsigned) std::min<uint64_t>(ntiles, (uint64_t) kSMs * 16), PART_THREADS, 0, s>>>((const uint32_t *) kv->data, n,
                                                                                                                       (uint32_t) P, ntiles, tcount.p);
     MR_CUDA(cudaGetLastError());
   }
-  // exclusive scan in destination-major order = slot of every (destination, tile) in the send buffer
-  {
-    const unsigned *tc = tcount.p;
-    unsigned *to = toffs.p;
-    scan_apply(
-        pool, ntiles * P, [=] __device__(uint64_t i) -> unsigned long long { return tc[i]; },
-        [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { to[i] = (unsigned) e; }, mr->d_small, "aggregate_tile_scan",
-        8.0 * ntiles * P);
-  }
-  // per-destination totals = differences of the scanned array at the destination boundaries
+  // exclusive scan in destination-major order = slot of every (destination, tile)
+  const unsigned *tc = tcount.p;
+  unsigned *to = pl.toffs.p;
+  scan_apply(
+      pool, ntiles * P, [=] __device__(uint64_t i) -> unsigned long long { return tc[i]; },
+      [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { to[i] = (unsigned) e; }, mr->d_small, "aggregate_tile_scan",
+      8.0 * ntiles * P);
   std::vector<unsigned> first(P);
-  for (int p = 0; p < P; p++) MR_CUDA(cudaMemcpyAsync(&first[p], toffs.p + (uint64_t) p * ntiles, 4, cudaMemcpyDeviceToHost, s));
+  for (int p = 0; p < P; p++) MR_CUDA(cudaMemcpyAsync(&first[p], pl.toffs.p + (uint64_t) p * ntiles, 4, cudaMemcpyDeviceToHost, s));
   sync(mr);
   for (int p = 0; p < P; p++) scount[p] = (p + 1 < P ? first[p + 1] : n) - first[p];
+}
+
+template <int RW, int KW>
+static void partition_scatter_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, const DestPtrs &dp, const char *tag, bool remote)
+{
+  // MRGPU_PART_DIRECT / MRGPU_PEER_DIRECT (0/1) override the choice between per-lane stores and staged runs
+  static const char *e_loc = getenv("MRGPU_PART_DIRECT"), *e_rem = getenv("MRGPU_PEER_DIRECT");
+  const char *e = remote ? e_rem : e_loc;
+  // stores that cross NVLink go out as staged runs (full 128-byte lines): 654 vs 556 GB/s at 2 ranks, 302 vs 228 at 8
+  const bool direct = e ? atoi(e) != 0 : (!remote && mr->nranks <= PART_DIRECT_MAXP);
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const int P = mr->nranks;
   int nbits = 0;
   while ((1 << nbits) < P) nbits++;
   const size_t smem = (size_t) PART_TILE * RW * 4 + PART_TILE;
@@ -326,36 +353,54 @@ static void partition_launch(mrgpu_mr *mr, DevKV *kv, uint8_t *sendbuf, std::vec
     MR_CUDA(cudaFuncSetAttribute(partition_scatter_kernel<RW, KW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     attr[mr->device] = true;
   }
-  {
-    ProfScope ps(pool, "aggregate_partition_scatter", 2.0 * kv->nbytes);
-    partition_scatter_kernel<RW, KW><<<(unsigned) ntiles, PART_THREADS, smem, s>>>((const uint32_t *) kv->data, (uint32_t *) sendbuf, n, (uint32_t) P, nbits,
-                                                                                ntiles, toffs.p);
-    MR_CUDA(cudaGetLastError());
-  }
-  sync(mr);
+  ProfScope ps(pool, tag, 2.0 * kv->nbytes);
+  partition_scatter_kernel<RW, KW><<<(unsigned) pl.ntiles, PART_THREADS, direct ? 0 : smem, s>>>((const uint32_t *) kv->data, dp, kv->nkv, (uint32_t) P, nbits, pl.ntiles,
+                                                                                  pl.toffs.p, direct);
+  MR_CUDA(cudaGetLastError());
 }
 
-// true = the send buffer holds this rank's records grouped by destination and scount[] their counts
-static bool partition_uniform(mrgpu_mr *mr, DevKV *kv, uint8_t *sendbuf, std::vector<uint64_t> &scount)
+#define PART_DISPATCH(FN, ...)                                   \
+  do {                                                           \
+    const int _rw = (int) (kv->recsize / 4), _kw = (int) (kv->kb / 4); \
+    if (_rw == 3 && _kw == 1) FN<3, 1>(__VA_ARGS__);             \
+    else if (_rw == 4 && _kw == 1) FN<4, 1>(__VA_ARGS__);        \
+    else if (_rw == 4 && _kw == 2) FN<4, 2>(__VA_ARGS__);        \
+    else if (_rw == 5 && _kw == 2) FN<5, 2>(__VA_ARGS__);        \
+    else if (_rw == 6 && _kw == 2) FN<6, 2>(__VA_ARGS__);        \
+    else if (_rw == 6 && _kw == 4) FN<6, 4>(__VA_ARGS__);        \
+  } while (0)
+
+// record shapes the single-pass partition handles: 4-byte-aligned uniform records, key right after the header
+static bool partition_eligible(mrgpu_mr *mr, DevKV *kv)
 {
   const Align al = mr->al;
-  if (!kv->uniform || mr->nranks > PART_MAXP || (al.k % 4) || (kv->kb % 4) || kv->kb == 0 || (kv->recsize % 4)) return false;
-  if (((uintptr_t) kv->data % 16) || ((uintptr_t) sendbuf % 16)) return false;
-  const int RW = kv->recsize / 4, KW = kv->kb / 4;
-  if (kv_key_off(al) != 8) return false;
-#define PART_CASE(rw, kw)                                      \
-  if (RW == rw && KW == kw) {                                  \
-    partition_launch<rw, kw>(mr, kv, sendbuf, scount);         \
-    return true;                                               \
+  if (!kv->uniform || kv->nkv == 0 || mr->nranks > PART_MAXP || (al.k % 4) || (kv->kb % 4) || kv->kb == 0 || (kv->recsize % 4)) return false;
+  if (((uintptr_t) kv->data % 16) || kv_key_off(al) != 8) return false;
+  const int rw = kv->recsize / 4, kw = kv->kb / 4;
+  return (rw == 3 && kw == 1) || (rw == 4 && kw == 1) || (rw == 4 && kw == 2) || (rw == 5 && kw == 2) || (rw == 6 && kw == 2) || (rw == 6 && kw == 4);
+}
+
+static void partition_counts(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount) { PART_DISPATCH(partition_counts_t, mr, kv, pl, scount); }
+static void partition_scatter(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, const DestPtrs &dp, const char *tag, bool remote = false)
+{
+  PART_DISPATCH(partition_scatter_t, mr, kv, pl, dp, tag, remote);
+}
+
+// both passes into one local buffer: destination d's slice starts at record slot sum(scount[0..d))
+static bool partition_uniform(mrgpu_mr *mr, DevKV *kv, uint8_t *sendbuf, std::vector<uint64_t> &scount)
+{
+  if (!partition_eligible(mr, kv) || ((uintptr_t) sendbuf % 16)) return false;
+  PartPlan pl;
+  partition_counts(mr, kv, pl, scount);
+  DestPtrs dp;
+  uint64_t off = 0;
+  for (int p = 0; p < mr->nranks; p++) {
+    dp.base[p] = sendbuf + off;
+    off += scount[p] * kv->recsize;
   }
-  PART_CASE(3, 1)   // 4-byte key, no value
-  PART_CASE(4, 1)   // IntCount: 4-byte key, 4-byte value
-  PART_CASE(4, 2)   // vertices: 8-byte key, no value
-  PART_CASE(5, 2)   // 8-byte key, 4-byte value
-  PART_CASE(6, 2)   // 8-byte key, 8-byte value
-  PART_CASE(6, 4)   // R-MAT edges: 16-byte key, no value
-#undef PART_CASE
-  return false;
+  partition_scatter(mr, kv, pl, dp, "aggregate_partition_scatter");
+  sync(mr);
+  return true;
 }
 
 // Test / profiling hook: the local half of aggregate() for a VIRTUAL rank count on one GPU -- the KV is

@@ -10,8 +10,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WORKER = os.path.join(ROOT, "tests", "multi_rank_worker.py")
 
 
-def _launch(nproc, backend, port, timeout=600):
-    env = dict(os.environ, MR_WORKER_BACKEND=backend, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="1")
+def _launch(nproc, backend, port, timeout=600, **extra):
+    env = dict(os.environ, MR_WORKER_BACKEND=backend, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="1", **extra)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), WORKER]
     p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
@@ -33,6 +33,8 @@ def test_aggregate_collate_over_nccl():
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs at least 2 GPUs (run with gpurun --gpus 2)")
-    _launch(2, "nccl", 29613)
+    _launch(2, "nccl", 29613)                   # exchange by peer stores (CUDA IPC) where the pairs are uniform
+    _launch(2, "nccl", 29615, MRGPU_P2P="0")    # the same through ncclSend/ncclRecv
+    _launch(2, "nccl", 29616, MRGPU_PEER_DIRECT="1")
     if n >= 3:
         _launch(3, "nccl", 29614)
