@@ -296,6 +296,7 @@ def main():
     for k in kern:
         k["ms_per_launch"] = k["ms"] / max(k["calls"], 1)
         k["gbs"] = (k["bytes"] / 1e9) / (k["ms"] / 1e3) if k["ms"] > 0 and k["bytes"] > 0 else None
+        k["moved_gbs"] = (k.get("moved", 0) / 1e9) / (k["ms"] / 1e3) if k["ms"] > 0 and k.get("moved", 0) > 0 else None
     shuffle = None
     for k in kern:
         if k["tag"] == "aggregate_exchange_nvlink" and k["ms"] > 0:
@@ -311,8 +312,14 @@ def main():
                     "peak_source": peak_src, "launches_per_step": dom["calls"], "ms_per_launch": dom["ms_per_launch"],
                     "share_of_step": dom["ms"] / step_ms,
                     "algorithmic_bytes_per_launch": dom["bytes"] / max(dom["calls"], 1),
+                    # compact stores: the kernel moves fewer bytes than the reference layout's
+                    # algorithmic figure, so `achieved` can exceed the HBM peak; these two use the bytes it really has to move
+                    "moved_bytes_per_launch": dom.get("moved", 0) / max(dom["calls"], 1),
+                    "achieved_moved": dom["moved_gbs"], "frac_moved": (dom["moved_gbs"] / peak) if dom["moved_gbs"] else None,
                     "kernels": [{"tag": k["tag"], "ms": round(k["ms"], 4), "calls": k["calls"],
-                                 "gbs": None if k["gbs"] is None else round(k["gbs"], 1)} for k in sorted(kern, key=lambda k: -k["ms"])]}
+                                 "gbs": None if k["gbs"] is None else round(k["gbs"], 1),
+                                 "moved_gbs": None if k["moved_gbs"] is None else round(k["moved_gbs"], 1)}
+                                for k in sorted(kern, key=lambda k: -k["ms"])]}
 
     # ---- end to end: pinned host input, H2D + D2H inside the timed region
     e2e = None

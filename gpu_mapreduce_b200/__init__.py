@@ -125,7 +125,8 @@ class MapReduce:
     """One MR object = one rank's KeyValue or KeyMultiValue in HBM (src/mapreduce.h:43-44)."""
 
     _SETTINGS = ("mapstyle", "all2all", "verbosity", "timer", "memsize", "minpage", "maxpage", "freepage",
-                 "outofcore", "zeropage", "keyalign", "valuealign")
+                 "outofcore", "zeropage", "keyalign", "valuealign",
+                 "compact")  # not a reference member: 0 = stores always hold the reference's record streams (see mrgpu.h)
 
     def __init__(self, device: int = 0, stream: int | None = None, rank: int = 0, nranks: int = 1,
                  unique_id: bytes | None = None):

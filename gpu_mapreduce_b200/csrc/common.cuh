@@ -38,8 +38,9 @@ struct Error {
 struct ProfEntry {
   const char *tag;
   cudaEvent_t a, b;
-  double bytes;  // algorithmic bytes of this launch, 0 if not stated
+  double bytes;  // algorithmic bytes of this launch: the reference's exact sizes, 0 if not stated
   int launches;
+  double moved;  // bytes this launch has to move given the layout actually in HBM (= bytes unless a compact store is involved)
 };
 struct Prof {
   bool on = false;
@@ -223,11 +224,11 @@ struct Pool {
 struct ProfScope {
   Pool &p;
   int idx = -1;
-  ProfScope(Pool &pool, const char *tag, double bytes = 0, int nlaunch = 1) : p(pool)
+  ProfScope(Pool &pool, const char *tag, double bytes = 0, int nlaunch = 1, double moved = -1) : p(pool)
   {
     p.prof.launches += nlaunch;
     if (p.prof.on) {
-      ProfEntry e{tag, p.prof.get(), p.prof.get(), bytes, nlaunch};
+      ProfEntry e{tag, p.prof.get(), p.prof.get(), bytes, nlaunch, moved < 0 ? bytes : moved};
       cudaEventRecord(e.a, p.stream);
       idx = (int) p.prof.ev.size();
       p.prof.ev.push_back(e);

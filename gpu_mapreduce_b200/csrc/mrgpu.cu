@@ -33,6 +33,9 @@ struct mrgpu_mr {
   int device = 0;
   int64_t memsize = 64, keyalign = 4, valuealign = 4, verbosity = 0, timer = 0, all2all = 1, mapstyle = 0, minpage = 0,
           maxpage = 0, freepage = 1, outofcore = 0, zeropage = 0;  // defaults(): src/mapreduce.cpp:196-262
+  // compact = 1 (default): stores may keep a lossless compact form (factored KMV, header-less uniform KV) and
+  // write the reference's record stream only when its bytes are asked for; 0: always the record stream
+  int64_t compact = 1;
   Align al;
   bool frozen = false;
   uint64_t pagesize = 64ull << 20;
@@ -178,7 +181,7 @@ static int64_t *setting(mrgpu_mr *mr, const char *name)
   } tab[] = {{"memsize", &mr->memsize},     {"keyalign", &mr->keyalign},   {"valuealign", &mr->valuealign},
              {"verbosity", &mr->verbosity}, {"timer", &mr->timer},         {"all2all", &mr->all2all},
              {"mapstyle", &mr->mapstyle},   {"minpage", &mr->minpage},     {"maxpage", &mr->maxpage},
-             {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage}};
+             {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage},   {"compact", &mr->compact}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) return t.p;
   return nullptr;
@@ -233,6 +236,7 @@ extern "C" int mrgpu_prof_report(mrgpu_mr *mr, char *buf, uint64_t cap, uint64_t
     const char *tag;
     double ms, bytes;
     int launches, calls;
+    double moved;
   };
   std::vector<Acc> acc;
   for (auto &e : mr->pool.prof.ev) {
@@ -242,19 +246,20 @@ extern "C" int mrgpu_prof_report(mrgpu_mr *mr, char *buf, uint64_t cap, uint64_t
     for (auto &x : acc)
       if (!strcmp(x.tag, e.tag)) a = &x;
     if (!a) {
-      acc.push_back(Acc{e.tag, 0, 0, 0, 0});
+      acc.push_back(Acc{e.tag, 0, 0, 0, 0, 0});
       a = &acc.back();
     }
     a->ms += ms;
     a->bytes += e.bytes;
+    a->moved += e.moved;
     a->launches += e.launches;
     a->calls++;
   }
   std::string js = "[";
   for (size_t i = 0; i < acc.size(); i++) {
     char line[256];
-    snprintf(line, sizeof(line), "%s{\"tag\": \"%s\", \"ms\": %.6f, \"bytes\": %.0f, \"launches\": %d, \"calls\": %d}", i ? ", " : "",
-             acc[i].tag, acc[i].ms, acc[i].bytes, acc[i].launches, acc[i].calls);
+    snprintf(line, sizeof(line), "%s{\"tag\": \"%s\", \"ms\": %.6f, \"bytes\": %.0f, \"moved\": %.0f, \"launches\": %d, \"calls\": %d}",
+             i ? ", " : "", acc[i].tag, acc[i].ms, acc[i].bytes, acc[i].moved, acc[i].launches, acc[i].calls);
     js += line;
   }
   js += "]";

@@ -316,13 +316,45 @@ static bool exchange_peer_store(mrgpu_mr *mr, DevKV *kv, DevKV *nk, PartPlan *pl
   (void) brecv;
   uint64_t wire = 0;
   for (int q = 0; q < P; q++)
-    if (q != me) wire += scount[q] * kv->recsize;
+    if (q != me) wire += scount[q] * (kv->packed ? kv->prow() : kv->recsize);
   {
     ProfScope ps(pool, "aggregate_exchange_nvlink", (double) wire, 0);  // brackets the scatter + the completion barrier
     if (n) partition_scatter(mr, kv, *pl, dp, "aggregate_partition_peer_store", true);
     allreduce_sum(mr, 1);  // barrier: every rank's stores have landed
   }
   return true;
+}
+
+// Do all ranks that hold pairs hold them header-less, in the same shape, with the same shared value?
+// desc = {has pairs, packed | cval_on << 1 | kb << 8 | vb << 32, cval}; on true, desc is that of the agreeing ranks.
+static bool agree_packed(mrgpu_mr *mr, DevKV *kv, unsigned long long desc[3])
+{
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const int P = mr->nranks;
+  unsigned long long mine[3] = {kv->nkv ? 1ull : 0ull, 0, 0};
+  if (kv->nkv && kv->packed) {
+    mine[1] = 1ull | ((unsigned long long) kv->cval_on << 1) | ((unsigned long long) kv->kb << 8) | ((unsigned long long) kv->vb << 32);
+    mine[2] = kv->cval_on ? ((unsigned long long) kv->cval[1] << 32) | kv->cval[0] : 0;
+  }
+  Buf<unsigned long long> dm(pool, 3), da(pool, 3ull * P);
+  std::vector<unsigned long long> all(3 * (size_t) P);
+  MR_CUDA(cudaMemcpyAsync(dm.p, mine, 24, cudaMemcpyHostToDevice, s));
+  MR_NCCL(nccl().AllGather(dm.p, da.p, 3, ncclUint64, (ncclComm_t) mr->comm, s));
+  MR_CUDA(cudaMemcpyAsync(all.data(), da.p, 24 * (size_t) P, cudaMemcpyDeviceToHost, s));
+  sync(mr);
+  bool have = false, ok = true;
+  for (int q = 0; q < P && ok; q++) {
+    const unsigned long long *r = &all[3 * (size_t) q];
+    if (!r[0]) continue;
+    if (!(r[1] & 1)) ok = false;
+    else if (!have) {
+      desc[0] = 1, desc[1] = r[1], desc[2] = r[2];
+      have = true;
+    } else if (r[1] != desc[1] || r[2] != desc[2])
+      ok = false;
+  }
+  return ok && have;
 }
 
 static void peer_store_teardown(mrgpu_mr *mr)
@@ -349,6 +381,14 @@ static void aggregate_impl(mrgpu_mr *mr)
   if (n >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "aggregate: more than 2^32-2 pairs on one GPU is not supported yet");
   ncclComm_t comm = (ncclComm_t) mr->comm;
 
+  // header-less rows travel as they are when every rank that holds pairs holds the same header-less shape;
+  // otherwise they are written out as records first
+  if (kv->packed && !partition_eligible(mr, kv)) kv_unpack(mr, kv);
+  unsigned long long wire_desc[3];
+  const bool packed_wire = agree_packed(mr, kv, wire_desc);
+  if (kv->packed && !packed_wire) kv_unpack(mr, kv);
+  const uint64_t row = kv->packed ? kv->prow() : kv->recsize;  // bytes per pair of a uniform KV as stored and sent
+
   Buf<uint8_t> sendbuf;
   Buf<uint32_t> ssizes;
   Buf<uint64_t> soffs;
@@ -363,7 +403,7 @@ static void aggregate_impl(mrgpu_mr *mr)
     partition_counts(mr, kv, pl, scount);
     for (int p = 0; p < P; p++) {
       srec[p + 1] = srec[p] + scount[p];
-      sbytes[p] = scount[p] * kv->recsize;
+      sbytes[p] = scount[p] * row;
     }
   } else {
     sendbuf.alloc(pool, kv->nbytes);
@@ -449,9 +489,9 @@ static void aggregate_impl(mrgpu_mr *mr)
     bool delivered = false;
     if (kind == 2) delivered = exchange_peer_store(mr, kv, nk, fast ? &pl : nullptr, n, all, W, scount, rdisp, brecv);
     if (!delivered && fast) {  // NCCL path needs the pairs packed locally
-      sendbuf.alloc(pool, kv->nbytes);
+      sendbuf.alloc(pool, kv->phys_bytes());
       DestPtrs dp;
-      for (int p = 0; p < P; p++) dp.base[p] = sendbuf.p + srec[p] * kv->recsize;
+      for (int p = 0; p < P; p++) dp.base[p] = sendbuf.p + srec[p] * row;
       partition_scatter(mr, kv, pl, dp, "aggregate_partition_scatter");
     }
     Buf<uint32_t> rsizes;
@@ -494,6 +534,13 @@ static void aggregate_impl(mrgpu_mr *mr)
       nk->kb = (uint32_t) (shape >> 32);
       nk->vb = (uint32_t) shape;
       nk->recsize = kv_rec_size(al, nk->kb, nk->vb);
+      if (packed_wire) {
+        nk->packed = true;
+        nk->cval_on = (wire_desc[1] >> 1) & 1;
+        nk->cval[0] = (uint32_t) wire_desc[2];
+        nk->cval[1] = (uint32_t) (wire_desc[2] >> 32);
+        nk->nbytes = nrecv * nk->recsize;
+      }
       nk->ksize = nrecv * nk->kb;
       nk->vsize = nrecv * nk->vb;
     } else if (nrecv) {

@@ -483,6 +483,7 @@ static void convert_impl(mrgpu_mr *mr)
     mr->kmv = kmv;
   } else {
     bool done = convert_dense(mr);  // small integer keys + indistinguishable pairs: count, do not sort
+    if (!done) kv_unpack(mr, kv);   // the sort paths read records
     const Align al = mr->al;
     // exact path needs word-aligned records/keys and a value that is empty, 4 or 8 bytes, or gatherable
     if (!done && kv->uniform && (al.k % 4) == 0) {

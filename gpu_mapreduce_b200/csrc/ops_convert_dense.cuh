@@ -58,7 +58,7 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
   if (a.vb == 8) v0b = *(const uint32_t *) (a.data + a.voff + 4);
   bool bad = false;
   const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
-  const bool rec16 = a.rs == 16 && ((uintptr_t) a.data % 16) == 0;
+  const bool rec16 = a.rs == 16 && a.koff == 8 && ((uintptr_t) a.data % 16) == 0;
   auto count_one = [&](uint32_t key, uint32_t khi, uint32_t va, uint32_t vb2) {
     if (khi != 0 || key >= DENSE_SLOTS || va != v0a || vb2 != v0b) {
       bad = true;
@@ -81,7 +81,32 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
     } else
       atomicAdd(&table[key], 1u);
   };
-  if (rec16) {
+  if (a.rs == 4 && a.koff == 0 && ((uintptr_t) a.data % 16) == 0) {
+    // header-less rows that are just a 4-byte key (the value is shared): a 16-byte load brings four pairs
+    constexpr int U = 4;
+    const int4 *q4 = (const int4 *) a.data;
+    const uint64_t n4 = a.n / 4;
+    for (uint64_t base = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; base < n4 && !bad; base += stride * U) {
+      int4 r[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        uint64_t i = base + (uint64_t) u * stride;
+        if (i < n4) r[u] = ld_stream(q4 + i);
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        uint64_t i = base + (uint64_t) u * stride;
+        if (i < n4) {
+          count_one((uint32_t) r[u].x, 0, v0a, v0b);
+          count_one((uint32_t) r[u].y, 0, v0a, v0b);
+          count_one((uint32_t) r[u].z, 0, v0a, v0b);
+          count_one((uint32_t) r[u].w, 0, v0a, v0b);
+        }
+      }
+    }
+    for (uint64_t i = n4 * 4 + (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride)
+      count_one(((const uint32_t *) a.data)[i], 0, v0a, v0b);
+  } else if (rec16) {
     // one 16-byte load per record {kb, vb, w2, w3}; eight independent loads in flight per thread -- with a
     // single load per iteration the kernel sat at 18 % issue utilisation waiting on HBM latency (ncu)
     constexpr int U = 8;
@@ -248,6 +273,50 @@ dense_fill_kernel(uint32_t *__restrict__ out, uint64_t total_words, const uint64
   }
 }
 
+// factored KMV -> the reference's record stream (kmv->data, kmv->offs); no-op for any other KMV
+static void kmv_expand(mrgpu_mr *mr, DevKMV *kmv)
+{
+  if (!kmv || !kmv->factored) return;
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const Align al = mr->al;
+  const uint64_t U = kmv->nkmv;
+  const uint32_t kb = (uint32_t) kmv->ukb, vb = (uint32_t) kmv->uvb;
+  kmv->offs = (uint64_t *) pool.alloc((U + 1) * 8);
+  kmv->offs_cap = U + 1;
+  uint64_t *offs = kmv->offs;
+  const uint32_t *pc = kmv->fcnt;
+  scan_apply(
+      pool, U, [=] __device__(uint64_t u) -> unsigned long long {
+        uint64_t nv = pc[u];
+        return kmv_rec_size(al, nv, kb, nv * vb);
+      },
+      [=] __device__(uint64_t u, unsigned long long e, unsigned long long) { offs[u] = e; }, mr->d_small, "convert_kmv_sizes", 12.0 * U);
+  fetch_small(mr, 1);
+  const uint64_t total = mr->h_small[0];
+  MR_CUDA(cudaMemcpyAsync(offs + U, &total, 8, cudaMemcpyHostToDevice, s));
+  kmv->data = (uint8_t *) pool.alloc(total);
+  kmv->cap = total;
+  kmv->nbytes = total;
+  if (total) {
+    ProfScope ps(pool, "convert_dense_fill", (double) total + 16.0 * U);
+    const uint64_t words = total / 4;
+    const uint64_t nchunks = (words + FILL_CHUNK_WORDS - 1) / FILL_CHUNK_WORDS;
+    const uint64_t nblk = std::min<uint64_t>(nchunks, (uint64_t) kSMs * 16);
+    const uint64_t cpb = (nchunks + nblk - 1) / nblk;
+    dense_fill_kernel<<<(unsigned) ((nchunks + cpb - 1) / cpb), FILL_THREADS, 0, s>>>((uint32_t *) kmv->data, words, offs, kmv->fkey, kmv->fcnt, U, al, kb, vb,
+                                                                                     kmv->fval[0], kmv->fval[1], cpb);
+    MR_CUDA(cudaGetLastError());
+  }
+  sync(mr);
+  pool.free(kmv->fkey, kmv->fcap * 4);
+  pool.free(kmv->fcnt, kmv->fcap * 4);
+  kmv->fkey = kmv->fcnt = nullptr;
+  kmv->fcap = 0;
+  kmv->factored = false;
+  kmv->h_offs_valid = false;
+}
+
 // returns true if the dense path produced mr->kmv; false = not applicable, nothing changed
 static bool convert_dense(mrgpu_mr *mr)
 {
@@ -259,7 +328,10 @@ static bool convert_dense(mrgpu_mr *mr)
   const uint32_t kb = kv->kb, vb = kv->vb;
   if (!kv->uniform || (kb != 4 && kb != 8) || (vb != 0 && vb != 4 && vb != 8)) return false;
   if ((al.k % 4) || (al.v % 4) || n < (1u << 16)) return false;  // small inputs: the table scan would dominate
-  const uint32_t rs = kv->recsize, koff = kv_key_off(al), voff = kv_val_off(al, kb);
+  // header-less rows (store.cuh): key at 0, value (if stored per pair) right after it
+  const bool shared_val = kv->packed && kv->cval_on;
+  const uint32_t rs = kv->packed ? kv->prow() : kv->recsize, koff = kv->packed ? 0 : kv_key_off(al), voff = kv->packed ? kb : kv_val_off(al, kb);
+  const uint32_t svb = shared_val ? 0 : vb;  // value bytes the count kernel has to compare per pair
 
   Buf<unsigned> table(pool, DENSE_SLOTS);
   unsigned long long *flag = mr->d_small + 8;
@@ -271,15 +343,16 @@ static bool convert_dense(mrgpu_mr *mr)
     attr_set[mr->device] = true;
   }
   {
-    ProfScope ps(pool, "convert_dense_count", (double) kv->nbytes);
-    DenseArgs a{kv->data, n, rs, koff, voff, kb, vb};
+    ProfScope ps(pool, "convert_dense_count", (double) kv->nbytes, 1, (double) kv->phys_bytes());
+    DenseArgs a{kv->data, n, rs, koff, voff, kb, svb};
     dense_count_kernel<<<kSMs * MRGPU_DENSE_BPS, MRGPU_DENSE_THREADS, DENSE_CACHE * 6, s>>>(a, table.p, flag);
     MR_CUDA(cudaGetLastError());
   }
   unsigned long long h_flag = 1;
   uint32_t cv[2] = {0, 0};
   MR_CUDA(cudaMemcpyAsync(&h_flag, flag, 8, cudaMemcpyDeviceToHost, s));
-  if (vb) MR_CUDA(cudaMemcpyAsync(cv, kv->data + voff, vb, cudaMemcpyDeviceToHost, s));
+  if (shared_val) cv[0] = kv->cval[0], cv[1] = kv->cval[1];
+  else if (vb) MR_CUDA(cudaMemcpyAsync(cv, kv->data + voff, vb, cudaMemcpyDeviceToHost, s));
   sync(mr);
   if (h_flag) return false;
 
@@ -290,52 +363,29 @@ static bool convert_dense(mrgpu_mr *mr)
   flag_tiles(pool, DENSE_SLOTS, nonzero, bins, mr->d_small, "convert_dense_bins", (double) DENSE_SLOTS * 4);
   fetch_small(mr, 1);
   const uint64_t U = mr->h_small[0];
-  Buf<uint32_t> ukey(pool, U), ucnt(pool, U);
-  {
-    uint32_t *pk = ukey.p, *pc = ucnt.p;
+  DevKMV *kmv = new DevKMV(&pool);
+  try {
+    kmv->fkey = (uint32_t *) pool.alloc((U ? U : 1) * 4);
+    kmv->fcnt = (uint32_t *) pool.alloc((U ? U : 1) * 4);
+    kmv->fcap = U ? U : 1;
+    uint32_t *pk = kmv->fkey, *pc = kmv->fcnt;
     flag_sink(pool, bins, nonzero, [=] __device__(uint64_t k, unsigned long long e, unsigned long long h) {
       if (h) {
         pk[e] = (uint32_t) k;
         pc[e] = __ldg(tb + k);
       }
     }, "convert_dense_bins", (double) DENSE_SLOTS * 4 + 8.0 * U);
-  }
-  table.release();
-
-  DevKMV *kmv = new DevKMV(&pool);
-  try {
-    kmv->offs = (uint64_t *) pool.alloc((U + 1) * 8);
-    kmv->offs_cap = U + 1;
-    uint64_t *offs = kmv->offs;
-    const uint32_t *pc = ucnt.p;
-    scan_apply(
-        pool, U, [=] __device__(uint64_t u) -> unsigned long long {
-          uint64_t nv = pc[u];
-          return kmv_rec_size(al, nv, kb, nv * vb);
-        },
-        [=] __device__(uint64_t u, unsigned long long e, unsigned long long) { offs[u] = e; }, mr->d_small, "convert_kmv_sizes", 12.0 * U);
-    fetch_small(mr, 1);
-    const uint64_t total = mr->h_small[0];
-    MR_CUDA(cudaMemcpyAsync(offs + U, &total, 8, cudaMemcpyHostToDevice, s));
-    kmv->data = (uint8_t *) pool.alloc(total);
-    kmv->cap = total;
-    kmv->nbytes = total;
-    {
-      ProfScope ps(pool, "convert_dense_fill", (double) total + 16.0 * U);
-      const uint64_t words = total / 4;
-      const uint64_t nchunks = (words + FILL_CHUNK_WORDS - 1) / FILL_CHUNK_WORDS;
-      const uint64_t nblk = std::min<uint64_t>(nchunks, (uint64_t) kSMs * 16);
-      const uint64_t cpb = (nchunks + nblk - 1) / nblk;
-      dense_fill_kernel<<<(unsigned) ((nchunks + cpb - 1) / cpb), FILL_THREADS, 0, s>>>((uint32_t *) kmv->data, words, offs, ukey.p, ucnt.p, U, al, kb,
-                                                                                       vb, cv[0], cv[1], cpb);
-      MR_CUDA(cudaGetLastError());
-    }
+    table.release();
+    kmv->factored = true;
+    kmv->fval[0] = cv[0];
+    kmv->fval[1] = cv[1];
     kmv->nkmv = U;
     kmv->nvalue = n;
     kmv->ksize = U * (uint64_t) kb;
     kmv->vsize = kv->vsize;
     kmv->ukb = kb;
     kmv->uvb = vb;
+    if (!mr->compact) kmv_expand(mr, kmv);
     sync(mr);
   } catch (...) {
     delete kmv;

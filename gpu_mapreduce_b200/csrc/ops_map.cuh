@@ -9,7 +9,9 @@
 
 // map()'s preamble, src/mapreduce.cpp:1114-1131: an existing KMV is dropped; addflag = 0 starts a new KV,
 // addflag = 1 re-opens the current one for append (KeyValue::append, src/keyvalue.cpp:185-209).
-static void kv_begin_map(mrgpu_mr *mr, int addflag)
+static void kv_unpack(mrgpu_mr *mr, DevKV *kv);
+
+static void kv_begin_map(mrgpu_mr *mr, int addflag, bool keep_packed = false)
 {
   freeze(mr);
   delete mr->kmv;
@@ -17,7 +19,80 @@ static void kv_begin_map(mrgpu_mr *mr, int addflag)
   if (!addflag || !mr->kv) {
     delete mr->kv;
     mr->kv = new DevKV(&mr->pool);
+  } else if (!keep_packed)
+    kv_unpack(mr, mr->kv);
+}
+
+// ---------------------------------------------------------------------------------------------
+// header-less uniform KV (store.cuh) <-> the reference's record stream
+
+// shapes that may be kept header-less: default alignment (record = 8 + kb + vb, no padding), word-sized fields
+static bool kv_can_pack(const mrgpu_mr *mr, uint32_t kb, uint32_t vb)
+{
+  return mr->compact && mr->al.k == 4 && mr->al.v == 4 && kb > 0 && kb % 4 == 0 && vb % 4 == 0;
+}
+
+// 4-byte key + 4-byte value (stored or shared): one 16-byte record per thread
+__global__ void __launch_bounds__(256) kv_unpack16_kernel(const uint32_t *__restrict__ rows, uint64_t n, bool cval_on, uint32_t c0, int4 *__restrict__ out)
+{
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint32_t k, v;
+    if (cval_on) k = __ldg(rows + i), v = c0;
+    else {
+      uint2 r = __ldg((const uint2 *) rows + i);
+      k = r.x, v = r.y;
+    }
+    st_stream(out + i, make_int4(4, 4, (int) k, (int) v));
   }
+}
+
+// any word-sized shape: one thread per output word
+__global__ void __launch_bounds__(256)
+kv_unpack_kernel(const uint32_t *__restrict__ rows, uint64_t n, uint32_t kw, uint32_t vw, bool cval_on, uint32_t c0, uint32_t c1, uint32_t *__restrict__ out)
+{
+  const uint32_t rw = 2 + kw + vw, roww = kw + (cval_on ? 0 : vw);
+  const uint64_t total = n * rw, stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t w = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; w < total; w += stride) {
+    const uint64_t i = w / rw;
+    const uint32_t q = (uint32_t) (w - i * rw);
+    uint32_t x;
+    if (q == 0) x = kw * 4;
+    else if (q == 1) x = vw * 4;
+    else if (q < 2 + kw || !cval_on) x = rows[i * roww + (q - 2)];
+    else x = (q - 2 - kw) ? c1 : c0;
+    out[w] = x;
+  }
+}
+
+// records [first, first + count) of a header-less KV written to out (count * recsize bytes, 16-byte aligned)
+static void kv_unpack_rows(mrgpu_mr *mr, const DevKV *kv, uint64_t first, uint64_t count, uint8_t *out)
+{
+  if (!count) return;
+  Pool &pool = mr->pool;
+  const uint32_t *rows = (const uint32_t *) (kv->data + first * kv->prow());
+  ProfScope ps(pool, "kv_unpack", (double) count * (kv->prow() + kv->recsize));
+  if (kv->kb == 4 && kv->vb == 4 && (!kv->cval_on ? ((uintptr_t) rows % 8) == 0 : true))
+    kv_unpack16_kernel<<<grid_for(count, 256, 16), 256, 0, pool.stream>>>(rows, count, kv->cval_on, kv->cval[0], (int4 *) out);
+  else
+    kv_unpack_kernel<<<grid_for(count * (kv->recsize / 4), 256, 16), 256, 0, pool.stream>>>(rows, count, kv->kb / 4, kv->vb / 4, kv->cval_on, kv->cval[0],
+                                                                                           kv->cval[1], (uint32_t *) out);
+  MR_CUDA(cudaGetLastError());
+}
+
+static void kv_unpack(mrgpu_mr *mr, DevKV *kv)
+{
+  if (!kv || !kv->packed) return;
+  if (kv->nkv) {
+    Pool &pool = mr->pool;
+    uint8_t *nd = (uint8_t *) pool.alloc(kv->nbytes);
+    kv_unpack_rows(mr, kv, 0, kv->nkv, nd);
+    pool.free(kv->data, kv->cap);
+    kv->data = nd;
+    kv->cap = kv->nbytes;
+  }
+  kv->packed = kv->cval_on = false;
+  kv->cval[0] = kv->cval[1] = 0;
 }
 
 __global__ void iota_offsets_kernel(uint64_t *offs, uint64_t n_plus_1, uint64_t recsize)
@@ -125,6 +200,25 @@ __global__ void __launch_bounds__(256) intcount_emit16_kernel(const uint32_t *__
   }
 }
 
+// header-less KV: the emit is a copy of the key column (16 bytes per thread per step, four steps in flight)
+__global__ void __launch_bounds__(256) copy_words_kernel(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst, uint64_t n)
+{
+  constexpr int U = 4;
+  const bool vec = (((uintptr_t) src | (uintptr_t) dst) & 15) == 0;
+  const uint64_t nv = vec ? n / 4 : 0;
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t base = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; base < nv; base += stride * U) {
+    int4 r[U];
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if (base + u * stride < nv) r[u] = ld_stream((const int4 *) src + base + u * stride);
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if (base + u * stride < nv) st_stream((int4 *) dst + base + u * stride, r[u]);
+  }
+  for (uint64_t i = nv * 4 + (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = src[i];
+}
+
 // any alignment: word-wise stores, padding zeroed
 __global__ void intcount_emit_generic_kernel(const uint32_t *__restrict__ keys, uint64_t n, uint8_t *out, Align al, uint32_t rs)
 {
@@ -142,10 +236,37 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
 {
   API_BEGIN(mr)
   if (n && !keys) MR_FAIL(MRGPU_EINVAL, "null input");
-  kv_begin_map(mr, addflag);
+  kv_begin_map(mr, addflag, true);
   DevKV *kv = mr->kv;
   Buf<uint32_t> tmp;
   const uint32_t *dk = stage_input(mr, keys, n, tmp);
+  // header-less: every pair is {4, 4, key, 1}, so the KV is the key column plus one shared value
+  const bool pack = kv_can_pack(mr, 4, 4) &&
+                    (kv->nkv == 0 || (kv->packed && kv->cval_on && kv->kb == 4 && kv->vb == 4 && kv->cval[0] == 1));
+  if (pack) {
+    if (kv->nkv == 0) {
+      kv->uniform = kv->packed = kv->cval_on = true;
+      kv->kb = kv->vb = 4;
+      kv->recsize = 16;
+      kv->cval[0] = 1;
+      kv->cval[1] = 0;
+    }
+    kv->reserve_bytes((kv->nkv + n) * 4);
+    if (n) {
+      ProfScope ps(mr->pool, "map_intcount_emit", (double) n * (4 + 8 + 4 + 4), 1, (double) n * 8);
+      copy_words_kernel<<<grid_for(n, 256 * 16, 16), 256, 0, mr->pool.stream>>>(dk, (uint32_t *) kv->data + kv->nkv, n);
+      MR_CUDA(cudaGetLastError());
+    }
+    kv_commit_uniform(kv, 4, 4, 16, n);
+    kv->h_offs_valid = false;
+    tmp.release();
+    if (nkv) {
+      sync(mr);
+      *nkv = allreduce_sum(mr, kv->nkv);
+    }
+    return MRGPU_OK;
+  }
+  kv_unpack(mr, kv);
   uint64_t base = kv_append_uniform(mr, kv, 4, 4, n);
   uint32_t rs = kv_rec_size(mr->al, 4, 4);
   if (n) {
@@ -229,6 +350,7 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
   freeze(srcmr);
   // src == dst: the reference detaches the old KV, builds the new one, then deletes the old (:1584-1602, 1634)
   DevKV *src = srcmr->kv;
+  kv_unpack(srcmr, src);  // the functors read records
   bool self = (srcmr == mr);
   if (self) mr->kv = nullptr;
   try {
@@ -449,6 +571,8 @@ extern "C" int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv)
   if (mr->al.k != other->al.k || mr->al.v != other->al.v) MR_FAIL(MRGPU_EINVAL, "add: alignments differ");
   if (!mr->kv) mr->kv = new DevKV(&mr->pool);
   DevKV *kv = mr->kv, *o = other->kv;
+  kv_unpack(mr, kv);
+  kv_unpack(other, o);
   cudaStream_t s = mr->pool.stream;
   if (o->nkv) {
     uint64_t base = kv->nbytes;

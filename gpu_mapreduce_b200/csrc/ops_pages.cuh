@@ -73,6 +73,7 @@ static PageSlice kv_page(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
 static PageSlice kmv_page(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
 {
   DevKMV *kmv = mr->kmv;
+  kmv_expand(mr, kmv);  // page boundaries and bytes are those of the record stream
   const uint64_t ps = mr->pagesize;
   PageSlice sl{0, 0, 0, 0, 0};
   if (kmv->nkmv == 0) {
@@ -134,6 +135,7 @@ extern "C" int mrgpu_kmv_stats(mrgpu_mr *mr, mrgpu_stats *out)
   if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "Cannot print stats without KeyMultiValue");
   freeze(mr);
   DevKMV *kmv = mr->kmv;
+  kmv_expand(mr, kmv);
   out->npair = kmv->nkmv;
   out->nvalue = kmv->nvalue;
   out->keysize = kmv->ksize;
@@ -185,7 +187,13 @@ extern "C" int mrgpu_kv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst)
   if (ipage >= np) MR_FAIL(MRGPU_EINVAL, "page index out of range");
   if (sl.end > sl.begin) {
     if (!dst) MR_FAIL(MRGPU_EINVAL, "null destination");
-    MR_CUDA(cudaMemcpyAsync(dst, mr->kv->data + sl.begin, sl.end - sl.begin, cudaMemcpyDeviceToHost, mr->pool.stream));
+    if (mr->kv->packed) {  // header-less rows: write this page's records out, the KV itself stays as it is
+      Buf<uint8_t> tmp(mr->pool, sl.end - sl.begin);
+      kv_unpack_rows(mr, mr->kv, sl.first, sl.nkey, tmp.p);
+      MR_CUDA(cudaMemcpyAsync(dst, tmp.p, sl.end - sl.begin, cudaMemcpyDeviceToHost, mr->pool.stream));
+      sync(mr);
+    } else
+      MR_CUDA(cudaMemcpyAsync(dst, mr->kv->data + sl.begin, sl.end - sl.begin, cudaMemcpyDeviceToHost, mr->pool.stream));
   }
   sync(mr);
   API_END(mr)
@@ -226,6 +234,7 @@ extern "C" int mrgpu_kv_device_view(mrgpu_mr *mr, const void **data, uint64_t *n
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "no KeyValue");
   DevKV *kv = mr->kv;
+  kv_unpack(mr, kv);  // the view is of the record stream
   if (data) *data = kv->data;
   if (nbytes) *nbytes = kv->nbytes;
   if (offsets) *offsets = (kv->uniform || kv->nkv == 0) ? nullptr : kv->offs;
@@ -237,6 +246,7 @@ extern "C" int mrgpu_kmv_device_view(mrgpu_mr *mr, const void **data, uint64_t *
 {
   API_BEGIN(mr)
   if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "no KeyMultiValue");
+  kmv_expand(mr, mr->kmv);
   if (data) *data = mr->kmv->data;
   if (nbytes) *nbytes = mr->kmv->nbytes;
   if (offsets) *offsets = mr->kmv->offs;

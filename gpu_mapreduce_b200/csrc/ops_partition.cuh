@@ -45,14 +45,13 @@ __device__ __forceinline__ uint32_t hashlittle_regs(const uint32_t (&w)[KW], uin
 // the key starts at word 2 of the record (after the two length ints; keyalign 4 or 8 with 8-byte header):
 // a compile-time index keeps the record in registers (a run-time index sent it to local memory -- ncu showed
 // STL.128 spills as the top stall of the first version)
-constexpr int PART_KWORD = 2;
-
-template <int RW, int KW>
+// (KOFF = 2); a header-less row (store.cuh) starts with its key (KOFF = 0)
+template <int RW, int KW, int KOFF>
 __device__ __forceinline__ uint32_t record_dest(const uint32_t (&rec)[RW], uint32_t nprocs)
 {
   uint32_t k[KW];
 #pragma unroll
-  for (int q = 0; q < KW; q++) k[q] = rec[PART_KWORD + q];
+  for (int q = 0; q < KW; q++) k[q] = rec[KOFF + q];
   return hashlittle_regs<KW>(k, nprocs) % nprocs;
 }
 
@@ -82,7 +81,7 @@ __device__ __forceinline__ void load_record(const uint32_t *__restrict__ p, uint
 // output slot of its first pair for each destination -- the scatter pass needs no look-back between tiles
 // (the first version used a decoupled look-back; ncu showed the tiles waiting on it: 5.3 barrier + 7.5
 // long-scoreboard stall cycles per issue, 2.3 TB/s).
-template <int RW, int KW>
+template <int RW, int KW, int KOFF>
 __global__ void __launch_bounds__(PART_THREADS)
 partition_count_kernel(const uint32_t *__restrict__ data, uint64_t n, uint32_t nprocs, uint64_t ntiles, unsigned *__restrict__ tcount)
 {
@@ -102,7 +101,7 @@ partition_count_kernel(const uint32_t *__restrict__ data, uint64_t n, uint32_t n
       if (sidx < nvalid) {
         uint32_t rec[RW];
         load_record<RW>(data + (tbase + sidx) * RW, rec);
-        dest[j] = record_dest<RW, KW>(rec, nprocs);
+        dest[j] = record_dest<RW, KW, KOFF>(rec, nprocs);
       }
     }
     if (nprocs <= 32) {
@@ -146,7 +145,7 @@ struct DestPtrs {
 // Pass 2: records -> destination slices.  toffs[d * ntiles + tile] = slot (counted over the whole destination-major
 // order) of this tile's first pair for destination d; slots inside a destination's slice are relative to
 // toffs[d * ntiles].
-template <int RW, int KW>
+template <int RW, int KW, int KOFF>
 __global__ void __launch_bounds__(PART_THREADS)
 partition_scatter_kernel(const uint32_t *__restrict__ data, DestPtrs dp, uint64_t n, uint32_t nprocs, int nbits, uint64_t ntiles,
                          const unsigned *__restrict__ toffs, bool direct)
@@ -178,7 +177,7 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, DestPtrs dp, uint64_
   for (int j = 0; j < PART_IPT; j++) {
     const unsigned sidx = woff0 + j * 32;
     dest[j] = nprocs;  // sentinel for empty slots: ranks after every real destination
-    if (sidx < nvalid) dest[j] = record_dest<RW, KW>(rec[j], nprocs);
+    if (sidx < nvalid) dest[j] = record_dest<RW, KW, KOFF>(rec[j], nprocs);
   }
   // rank inside the warp by destination, in memory order
   const unsigned lt_mask = lanemask_lt();
@@ -302,7 +301,7 @@ struct PartPlan {
   Buf<unsigned> toffs;
 };
 
-template <int RW, int KW>
+template <int RW, int KW, int KOFF>
 static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount)
 {
   Pool &pool = mr->pool;
@@ -316,8 +315,8 @@ static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vecto
   Buf<unsigned> tcount(pool, ntiles * P);
   pl.toffs.alloc(pool, ntiles * P);
   {
-    ProfScope ps(pool, "aggregate_count", (double) kv->nbytes);
-    partition_count_kernel<RW, KW><<<(unsigned) std::min<uint64_t>(ntiles, (uint64_t) kSMs * 16), PART_THREADS, 0, s>>>((const uint32_t *) kv->data, n,
+    ProfScope ps(pool, "aggregate_count", (double) kv->nbytes, 1, (double) kv->phys_bytes());
+    partition_count_kernel<RW, KW, KOFF><<<(unsigned) std::min<uint64_t>(ntiles, (uint64_t) kSMs * 16), PART_THREADS, 0, s>>>((const uint32_t *) kv->data, n,
                                                                                                                       (uint32_t) P, ntiles, tcount.p);
     MR_CUDA(cudaGetLastError());
   }
@@ -334,7 +333,7 @@ static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vecto
   for (int p = 0; p < P; p++) scount[p] = (p + 1 < P ? first[p + 1] : n) - first[p];
 }
 
-template <int RW, int KW>
+template <int RW, int KW, int KOFF>
 static void partition_scatter_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, const DestPtrs &dp, const char *tag, bool remote)
 {
   // MRGPU_PART_DIRECT / MRGPU_PEER_DIRECT (0/1) override the choice between per-lane stores and staged runs
@@ -350,33 +349,47 @@ static void partition_scatter_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, const Des
   const size_t smem = (size_t) PART_TILE * RW * 4 + PART_TILE;
   static bool attr[64] = {false};
   if (mr->device < 64 && !attr[mr->device]) {
-    MR_CUDA(cudaFuncSetAttribute(partition_scatter_kernel<RW, KW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    MR_CUDA(cudaFuncSetAttribute(partition_scatter_kernel<RW, KW, KOFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     attr[mr->device] = true;
   }
-  ProfScope ps(pool, tag, 2.0 * kv->nbytes);
-  partition_scatter_kernel<RW, KW><<<(unsigned) pl.ntiles, PART_THREADS, direct ? 0 : smem, s>>>((const uint32_t *) kv->data, dp, kv->nkv, (uint32_t) P, nbits, pl.ntiles,
+  ProfScope ps(pool, tag, 2.0 * kv->nbytes, 1, 2.0 * kv->phys_bytes());
+  partition_scatter_kernel<RW, KW, KOFF><<<(unsigned) pl.ntiles, PART_THREADS, direct ? 0 : smem, s>>>((const uint32_t *) kv->data, dp, kv->nkv, (uint32_t) P, nbits, pl.ntiles,
                                                                                   pl.toffs.p, direct);
   MR_CUDA(cudaGetLastError());
 }
 
-#define PART_DISPATCH(FN, ...)                                   \
-  do {                                                           \
-    const int _rw = (int) (kv->recsize / 4), _kw = (int) (kv->kb / 4); \
-    if (_rw == 3 && _kw == 1) FN<3, 1>(__VA_ARGS__);             \
-    else if (_rw == 4 && _kw == 1) FN<4, 1>(__VA_ARGS__);        \
-    else if (_rw == 4 && _kw == 2) FN<4, 2>(__VA_ARGS__);        \
-    else if (_rw == 5 && _kw == 2) FN<5, 2>(__VA_ARGS__);        \
-    else if (_rw == 6 && _kw == 2) FN<6, 2>(__VA_ARGS__);        \
-    else if (_rw == 6 && _kw == 4) FN<6, 4>(__VA_ARGS__);        \
+// rows the kernels are instantiated for: {words per row, key words, key offset}
+#define PART_DISPATCH(FN, ...)                                                                  \
+  do {                                                                                          \
+    const int _kw = (int) (kv->kb / 4), _ko = kv->packed ? 0 : 2;                               \
+    const int _rw = (int) ((kv->packed ? kv->prow() : kv->recsize) / 4);                        \
+    if (_ko == 2 && _rw == 3 && _kw == 1) FN<3, 1, 2>(__VA_ARGS__);                             \
+    else if (_ko == 2 && _rw == 4 && _kw == 1) FN<4, 1, 2>(__VA_ARGS__);                        \
+    else if (_ko == 2 && _rw == 4 && _kw == 2) FN<4, 2, 2>(__VA_ARGS__);                        \
+    else if (_ko == 2 && _rw == 5 && _kw == 2) FN<5, 2, 2>(__VA_ARGS__);                        \
+    else if (_ko == 2 && _rw == 6 && _kw == 2) FN<6, 2, 2>(__VA_ARGS__);                        \
+    else if (_ko == 2 && _rw == 6 && _kw == 4) FN<6, 4, 2>(__VA_ARGS__);                        \
+    else if (_ko == 0 && _rw == 1 && _kw == 1) FN<1, 1, 0>(__VA_ARGS__);                        \
+    else if (_ko == 0 && _rw == 2 && _kw == 1) FN<2, 1, 0>(__VA_ARGS__);                        \
+    else if (_ko == 0 && _rw == 2 && _kw == 2) FN<2, 2, 0>(__VA_ARGS__);                        \
+    else if (_ko == 0 && _rw == 4 && _kw == 4) FN<4, 4, 0>(__VA_ARGS__);                        \
+    else MR_FAIL(MRGPU_EINVAL, "internal: partition kernel not instantiated for this row");    \
   } while (0)
 
 // record shapes the single-pass partition handles: 4-byte-aligned uniform records, key right after the header
+// (or header-less rows)
 static bool partition_eligible(mrgpu_mr *mr, DevKV *kv)
 {
   const Align al = mr->al;
   if (!kv->uniform || kv->nkv == 0 || mr->nranks > PART_MAXP || (al.k % 4) || (kv->kb % 4) || kv->kb == 0 || (kv->recsize % 4)) return false;
-  if (((uintptr_t) kv->data % 16) || kv_key_off(al) != 8) return false;
-  const int rw = kv->recsize / 4, kw = kv->kb / 4;
+  if ((uintptr_t) kv->data % 16) return false;
+  const int kw = kv->kb / 4;
+  if (kv->packed) {
+    const int rw = kv->prow() / 4;
+    return (rw == 1 && kw == 1) || (rw == 2 && kw == 1) || (rw == 2 && kw == 2) || (rw == 4 && kw == 4);
+  }
+  if (kv_key_off(al) != 8) return false;
+  const int rw = kv->recsize / 4;
   return (rw == 3 && kw == 1) || (rw == 4 && kw == 1) || (rw == 4 && kw == 2) || (rw == 5 && kw == 2) || (rw == 6 && kw == 2) || (rw == 6 && kw == 4);
 }
 
@@ -396,7 +409,7 @@ static bool partition_uniform(mrgpu_mr *mr, DevKV *kv, uint8_t *sendbuf, std::ve
   uint64_t off = 0;
   for (int p = 0; p < mr->nranks; p++) {
     dp.base[p] = sendbuf + off;
-    off += scount[p] * kv->recsize;
+    off += scount[p] * (kv->packed ? kv->prow() : kv->recsize);
   }
   partition_scatter(mr, kv, pl, dp, "aggregate_partition_scatter");
   sync(mr);
@@ -416,7 +429,7 @@ extern "C" int mrgpu_debug_partition(mrgpu_mr *mr, int nprocs, uint64_t *counts)
   DevKV *nk = new DevKV(&mr->pool);
   int saved = mr->nranks;
   try {
-    nk->reserve_bytes(kv->nbytes);
+    nk->reserve_bytes(kv->phys_bytes());
     std::vector<uint64_t> sc(nprocs, 0);
     mr->nranks = nprocs;
     bool ok = kv->nkv && partition_uniform(mr, kv, nk->data, sc);
@@ -428,6 +441,10 @@ extern "C" int mrgpu_debug_partition(mrgpu_mr *mr, int nprocs, uint64_t *counts)
     nk->kb = kv->kb;
     nk->vb = kv->vb;
     nk->recsize = kv->recsize;
+    nk->packed = kv->packed;
+    nk->cval_on = kv->cval_on;
+    nk->cval[0] = kv->cval[0];
+    nk->cval[1] = kv->cval[1];
     nk->nbytes = kv->nbytes;
     nk->nkv = kv->nkv;
     nk->ksize = kv->ksize;

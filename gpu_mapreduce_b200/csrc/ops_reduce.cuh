@@ -59,6 +59,26 @@ reduce_count16_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restric
   st_stream(out + u, make_int4(4, 4, (int) key, (int) nv));
 }
 
+// factored KMV (store.cuh): pair u is (fkey[u], fcnt[u] values, all equal to the shared value)
+__global__ void __launch_bounds__(256)
+reduce_factored16_kernel(const uint32_t *__restrict__ fkey, const uint32_t *__restrict__ fcnt, uint64_t U, int4 *__restrict__ out)
+{
+  uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= U) return;
+  st_stream(out + u, make_int4(4, 4, (int) __ldg(fkey + u), (int) __ldg(fcnt + u)));
+}
+
+__global__ void __launch_bounds__(256)
+reduce_factored_kernel(const uint32_t *__restrict__ fkey, const uint32_t *__restrict__ fcnt, uint64_t U, int functor, Align al, uint32_t kb,
+                       uint32_t vb, uint32_t cv0, uint32_t cv1, uint8_t *out, uint64_t ors)
+{
+  uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= U) return;
+  const uint32_t key[2] = {fkey[u], 0}, cnt = fcnt[u], cv[2] = {cv0, cv1};
+  if (functor == MRGPU_REDUCE_CULL) write_kv_record(out + u * ors, al, kb, (const uint8_t *) key, vb, (const uint8_t *) cv);
+  else write_kv_record(out + u * ors, al, kb, (const uint8_t *) key, 4, (const uint8_t *) &cnt);
+}
+
 __global__ void __launch_bounds__(256)
 reduce_generic_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restrict__ offs, uint64_t U, int functor, Align al, uint8_t *out,
                       const uint64_t *__restrict__ ooffs, uint64_t ors)
@@ -96,7 +116,13 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
       uint32_t rs = kv_rec_size(al, kb, vb);
       kv->reserve_bytes(U * rs);
       ProfScope ps(pool, "reduce", (double) U * (12 + 4 + kb + rs));
-      if (!cull && kb == 4 && rs == 16 && kv_key_off(al) == 8 && al.k == 4)
+      if (kmv->factored) {
+        if (!cull && kb == 4 && rs == 16 && kv_key_off(al) == 8 && al.k == 4)
+          reduce_factored16_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kmv->fkey, kmv->fcnt, U, (int4 *) kv->data);
+        else
+          reduce_factored_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kmv->fkey, kmv->fcnt, U, functor, al, kb, (uint32_t) kmv->uvb,
+                                                                              kmv->fval[0], kmv->fval[1], kv->data, rs);
+      } else if (!cull && kb == 4 && rs == 16 && kv_key_off(al) == 8 && al.k == 4)
         reduce_count16_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, (int4 *) kv->data);
       else
         reduce_generic_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, functor, al, kv->data, nullptr, rs);

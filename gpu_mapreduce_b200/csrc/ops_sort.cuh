@@ -227,6 +227,7 @@ extern "C" int mrgpu_sort_keys(mrgpu_mr *mr, int flag, uint64_t *nkv)
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot sort_keys without KeyValue");
   freeze(mr);
+  kv_unpack(mr, mr->kv);
   sort_keys_impl(mr, flag);
   sync(mr);
   if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);

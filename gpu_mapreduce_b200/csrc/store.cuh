@@ -30,6 +30,16 @@ struct DevKV {
   uint64_t offs_cap = 0;     // entries allocated
   std::vector<uint64_t> h_offs;  // host copy of offs (page table / page copies), filled on demand
   bool h_offs_valid = false;
+  // Header-less form of a uniform KV (default alignment, key and value multiples of 4 bytes): the two length
+  // ints of every record are the same and are not stored; data holds nkv rows of [key | value], and when every
+  // pair carries the same value (IntCount's int 1) that value is kept once in cval and rows are just the key.
+  // nbytes/recsize keep describing the reference's record stream, which kv_unpack() writes out whenever its
+  // bytes are needed (pages, device views, ops without a header-less kernel).
+  bool packed = false;
+  bool cval_on = false;
+  uint32_t cval[2] = {0, 0};
+  uint32_t prow() const { return kb + (cval_on ? 0 : vb); }                  // bytes per stored row
+  uint64_t phys_bytes() const { return packed ? nkv * prow() : nbytes; }    // bytes of data in use
 
   explicit DevKV(Pool *p) : pool(p) {}
   ~DevKV()
@@ -45,7 +55,7 @@ struct DevKV {
     // growth beyond what was asked is only worth it for small stores; large ones are sized exactly
     if (need > (1ull << 28)) ncap = need;
     uint8_t *nd = (uint8_t *) pool->alloc(ncap);
-    if (nbytes) MR_CUDA(cudaMemcpyAsync(nd, data, nbytes, cudaMemcpyDeviceToDevice, pool->stream));
+    if (phys_bytes()) MR_CUDA(cudaMemcpyAsync(nd, data, phys_bytes(), cudaMemcpyDeviceToDevice, pool->stream));
     pool->free(data, cap);
     data = nd;
     cap = ncap;
@@ -73,12 +83,22 @@ struct DevKMV {
   int64_t ukb = -1, uvb = -1;  // keybytes / valuebytes shared by every pair, or -1
   std::vector<uint64_t> h_offs;
   bool h_offs_valid = false;
+  // Factored form (convert's dense path): when all pairs of a key are indistinguishable the KMV is fully
+  // described by (key, number of values) per distinct key plus the one shared value.  The record stream
+  // (data/offs above) is then written only when somebody needs its bytes (kmv_expand: pages, device views, a
+  // functor that reads multivalues); reduce's stock functors read this form directly.
+  bool factored = false;
+  uint32_t *fkey = nullptr, *fcnt = nullptr;  // [nkmv]
+  uint64_t fcap = 0;
+  uint32_t fval[2] = {0, 0};  // the shared value (uvb bytes)
 
   explicit DevKMV(Pool *p) : pool(p) {}
   ~DevKMV()
   {
     pool->free(data, cap);
     pool->free(offs, offs_cap * 8);
+    pool->free(fkey, fcap * 4);
+    pool->free(fcnt, fcap * 4);
   }
 };
 

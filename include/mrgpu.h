@@ -74,7 +74,14 @@ const char *mrgpu_last_error(const mrgpu_mr *mr);
 /* Public settings of the reference object, src/mapreduce.h:28-39: "memsize" (MB per page if > 0, bytes if
  * < 0, src/mapreduce.cpp:3351), "keyalign", "valuealign", "verbosity", "timer", "all2all", "mapstyle",
  * "minpage", "maxpage", "freepage", "outofcore", "zeropage".  Alignments freeze at first use like the
- * reference's allocate() (src/mapreduce.cpp:3318-3341). */
+ * reference's allocate() (src/mapreduce.cpp:3318-3341).
+ * One setting of this library's own: "compact" (default 1).  With 1 a store may be held in HBM in a lossless
+ * compact form -- a uniform KeyValue without its per-record length ints (and with a value shared by all
+ * pairs kept once), a KeyMultiValue of indistinguishable pairs as (key, count) -- and the reference's record
+ * stream is written when its bytes are asked for (page copies, device views, ops that read records).  With 0
+ * every store always holds the record stream.  Results and page images are identical either way.
+ * mrgpu_destroy is collective over the communicator once aggregate() has exchanged pairs by peer stores
+ * (like MapReduce::~MapReduce's MPI_Comm_free, src/mapreduce.cpp:283). */
 int mrgpu_set(mrgpu_mr *mr, const char *name, int64_t value);
 int mrgpu_get(const mrgpu_mr *mr, const char *name, int64_t *value);
 

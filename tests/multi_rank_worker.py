@@ -87,6 +87,38 @@ def main_nccl():
                     assert orc.hashlittle(k, world) % world == q
         mr.destroy()
 
+    # IntCount through map_intcount: header-less rows cross the wire when every rank holds them; with one rank
+    # set to compact=0 (or one rank empty / holding another shape) the ranks must agree on records instead
+    def ic_keys(q, variant):
+        return W.intcount_keys_np(q * 80000, (q + 1) * 80000, ndistinct=2000) if not (variant == 2 and q == 0) else np.zeros(0, np.uint32)
+
+    for variant in range(4):
+        mr = g.MapReduce(device=local, rank=rank, nranks=world, unique_id=uid)
+        if variant == 1 and rank == 1:
+            mr.compact = 0
+        keys = ic_keys(rank, variant)
+        shards = [[(struct.pack("<I", int(k)), struct.pack("<i", 1)) for k in ic_keys(q, variant)] for q in range(world)]
+        total = sum(len(x) for x in shards)
+        assert mr.map_intcount(keys) == total
+        if variant == 3 and rank == world - 1:      # another shape appended on one rank
+            extra = [(b"wide-key", b"")]
+            assert mr.kv_add(extra, addflag=1) == total + 1
+        if variant == 3:
+            shards[world - 1] = shards[world - 1] + [(b"wide-key", b"")]
+            total += 1
+        assert mr.aggregate() == total
+        want = []
+        for q in range(world):
+            dest = orc.partition(H.kv_encode(shards[q]), world) if shards[q] else []
+            want += [rec for rec, d in zip(shards[q], dest) if d == rank]
+        assert mr.scan_kv() == want, f"intcount variant {variant}: wrong pairs/order on rank {rank}"
+        nuniq = mr.convert()
+        assert mr.reduce("count") == nuniq
+        counts = [None] * world
+        dist.all_gather_object(counts, sum(struct.unpack("<i", v)[0] for _, v in mr.scan_kv()))
+        assert sum(counts) == total
+        mr.destroy()
+
     # R-MAT with one drand48 stream per rank (oink/rmat.cpp:94 srand48(seed+me)) + degree, vs the reference run with P virtual ranks
     import json
 

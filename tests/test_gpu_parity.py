@@ -359,6 +359,64 @@ def test_single_pass_partition_matches_reference_placement(MR, oracle, kb, vb, P
     assert mr.scan_kv() == want
 
 
+# ------------------------------------------------------------------------------------------- compact stores
+
+@pytest.mark.parametrize("compact", [0, 1])
+@pytest.mark.parametrize("cb", ["count", "sum", "cull"])
+def test_compact_stores_give_the_same_pairs_and_pages(MR, oracle, compact, cb):
+    """header-less KV + factored KMV (compact=1) vs record streams everywhere (compact=0): same pages, same results"""
+    n = 200_000
+    keys = W.intcount_keys_np(0, n, ndistinct=3000, seed=5)
+    kv_ref = oracle.intcount_map(keys)
+    mr = MR(compact=compact, memsize=-(1 << 20))
+    assert mr.map_intcount(keys[:120_000]) == 120_000
+    assert mr.map_intcount(keys[120_000:], addflag=1) == n          # append keeps the form
+    st = mr.kv_stats()
+    assert (st.npair, st.keysize, st.valuesize, st.alignsize) == (n, 4 * n, 4 * n, 16 * n)
+    assert mr.kv_pages() == H.pages_decode(oracle.kv_pages(kv_ref, 1 << 20))   # page copies write the records out
+    assert mr.convert() == len(np.unique(keys))                     # counting path, straight from the rows
+    kmv_ref = oracle.convert(kv_ref)
+    if cb == "count":                                               # reading the KMV writes its record stream out
+        st = mr.kmv_stats()
+        assert (st.npair, st.nvalue, st.valuesize) == (len(np.unique(keys)), n, 4 * n)
+        assert H.canon_kmv(mr.scan_kmv()) == H.canon_kmv(H.kmv_decode(kmv_ref))
+    mr.reduce(cb)                                                   # ... or the functor reads the factored form
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(oracle.reduce(kmv_ref, cb)))
+
+
+@pytest.mark.parametrize("P", [2, 8, 33])
+def test_partition_of_headerless_rows(MR, oracle, P):
+    keys = W.intcount_keys_np(0, 70_001, ndistinct=5000, seed=P)
+    mr = MR()
+    mr.map_intcount(keys)
+    counts = mr.debug_partition(P)
+    recs = H.kv_decode(oracle.intcount_map(keys))
+    dest = oracle.partition(H.kv_encode(recs), P)
+    assert counts == [dest.count(p) for p in range(P)]
+    assert mr.scan_kv() == [rec for p in range(P) for rec, d in zip(recs, dest) if d == p]
+
+
+def test_headerless_kv_meets_other_shapes(MR, oracle):
+    """ops without a header-less kernel (add, map(mr), sort_keys, appending another shape) see the records"""
+    keys = W.intcount_keys_np(0, 3000, ndistinct=40, seed=9)
+    recs = H.kv_decode(oracle.intcount_map(keys))
+    mr = MR()
+    mr.map_intcount(keys)
+    extra = [(b"abc", b"z"), (b"", b"")]
+    mr.kv_add(extra, addflag=1)
+    assert mr.scan_kv() == recs + extra
+    a, b = MR(), MR()
+    a.map_intcount(keys)
+    b.map_intcount(keys[:100])
+    assert b.add(a) == 3100
+    assert b.scan_kv() == recs[:100] + recs
+    c = MR()
+    c.map_mr(a, "invert")
+    assert c.scan_kv() == [(v, k) for k, v in recs]
+    assert a.sort_keys(1) == 3000
+    assert H.kv_encode(a.scan_kv()) == oracle.sort_keys(oracle.intcount_map(keys), 1)
+
+
 # ------------------------------------------------------------------------------------------- sort_keys
 
 @pytest.mark.parametrize("flag", [1, 2, 3, 4, 5, 6])
