@@ -44,17 +44,72 @@ def measured_peak_gbs():
 # ------------------------------------------------------------------------------------------ clocks
 
 class ClockSampler:
-    """nvidia-smi sampled every 200 ms while the timed region runs (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons sampled while the timed region runs (B200_PROFILING.md recipe).  A step is a
+    few milliseconds, so the sampler reads NVML in-process every 2 ms (nvidia-smi -lms cannot start that fast);
+    nvidia-smi at 100 ms is the fallback when pynvml is not usable."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    BITS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
 
     def __init__(self, gpu_index: int):
         self.idx = gpu_index
         self.proc = None
         self.path = None
+        self.thread = None
+        self.samples = []
+        self.stop_flag = False
+
+    def _nvml_loop(self, nv, h):
+        import time
+
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((sm, r))
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def start_nvml(self):
+        import threading
+
+        import pynvml as nv
+        import torch
+
+        nv.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(self.idx).uuid)
+            h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            h = nv.nvmlDeviceGetHandleByIndex(self.idx)
+        self.sm_max = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        self.thread = threading.Thread(target=self._nvml_loop, args=(nv, h), daemon=True)
+        self.thread.start()
+
+    def stop_nvml(self):
+        self.stop_flag = True
+        self.thread.join(timeout=2)
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.samples:
+            sm = sorted(x for x, _ in self.samples)
+            bits = 0
+            for _, r in self.samples:
+                bits |= int(r)
+            out.update(sm_mhz=float(sm[len(sm) // 2]), sm_max_mhz=float(self.sm_max), reasons=[n for b, n in self.BITS if bits & b],
+                       samples=len(sm), source="nvml, 2 ms period")
+        return out
 
     def start(self):
+        try:
+            self.start_nvml()
+            return
+        except Exception:
+            self.thread = None
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
@@ -65,6 +120,8 @@ class ClockSampler:
             self.proc = None
 
     def stop(self):
+        if self.thread:
+            return self.stop_nvml()
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if not self.proc:
             return out

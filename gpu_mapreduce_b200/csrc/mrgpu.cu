@@ -48,6 +48,7 @@ struct mrgpu_mr {
   void *comm = nullptr;            // ncclComm_t
   unsigned long long *d_small = nullptr;  // [64] device scalars (totals, flags)
   unsigned long long *h_small = nullptr;  // pinned mirror
+  unsigned *dense_table = nullptr;  // convert's 2^26-slot count table: allocated at first use, all zero between calls
   bool p2p_used = false;  // set identically on every rank
   std::map<std::string, void *> ipc_open;  // peers' receive chunks mapped by the peer-store exchange (CUDA IPC handle -> base)
 };

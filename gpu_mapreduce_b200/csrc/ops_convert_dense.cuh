@@ -20,17 +20,31 @@
 
 constexpr uint32_t DENSE_BITS = 26;                 // table of 2^26 u32 counts = 256 MB (touched part stays in L2)
 constexpr uint32_t DENSE_SLOTS = 1u << DENSE_BITS;
-#ifndef MRGPU_DENSE_CACHE_BITS
-#define MRGPU_DENSE_CACHE_BITS 15
-#endif
-// Per-block cache: 2^15 entries = a u32 tag (key+1, 0 = empty; 128 KB) and a 15-bit count packed two per word
-// (64 KB): 192 KB of shared memory, one 1024-thread block per SM.  A hit is one shared atomic add.  Bit 15 of
-// each half-word is a guard: the add that takes a count from 0x7FFF to 0x8000 cannot carry into the neighbour;
-// the thread that did it subtracts the 0x8000 again and forwards 32768 to the table in L2.  Measured on the
-// IntCount workload (ncu + A/B runs): the L2 atomics of cache MISSES bound this kernel (64-entry cache 125 ms,
-// 512: 50 ms, 8192: 7.7 ms, 16384: 5.4 ms) and L2 atomics on one address are slow (forwarding the hottest key
-// every 32 hits cost 20 ms), hence the largest cache that fits and counts that rarely overflow.
-constexpr int DENSE_CACHE = 1 << MRGPU_DENSE_CACHE_BITS;
+constexpr uint32_t DENSE_MASK = DENSE_SLOTS - 1;
+// Per-block cache: DENSE_CACHE 4-byte entries = 224 KB of shared memory, one 1024-thread block per SM.
+// An entry is {count : 20 | tag : 12}.  Keys are < 2^26; h = key * odd mod 2^26 is a bijection, the slot is
+// floor(h * DENSE_CACHE / 2^26), and the at most 1171 values of h that share a slot differ in their low 11
+// bits, so tag = (h & 2047) + 1 identifies the key exactly (0 = empty) and the key can be recovered from
+// (slot, tag) when the entry is flushed.  A hit is one shared load + one shared atomic add whose result is not
+// needed (the count sits in the high bits: it cannot carry into the tag, and a block flushes its cache to the
+// table in L2 every DENSE_ROUND < 2^20 keys, so it cannot wrap either).
+// History (ncu + A/B runs on the IntCount workload): the L2 atomics of cache MISSES bound the first versions
+// (64-entry cache 125 ms, 512: 50 ms, 8192: 7.7 ms, 16384: 5.4 ms, 32768 entries of tag + 15-bit count: 4.4 ms on
+// 16-byte records, 2.95 ms on header-less keys); L2 atomics on one address are slow (forwarding the hottest
+// key every 32 hits cost 20 ms).  That version issued at 1.6 IPC with every pipe under 60 %: latency-bound on
+// the load -> compare -> atomic -> check chain of one key at a time, hence the batches of four below.
+constexpr uint32_t DENSE_CACHE = 57344;
+constexpr uint32_t DENSE_MULT = 0x278DC01u;         // odd; spreads consecutive integers over the 26-bit range
+constexpr uint32_t DENSE_ROUND_LIMIT = (1u << 20) - 1;
+constexpr uint32_t dense_inv26(uint32_t a)
+{
+  uint32_t x = a;  // Newton: each step doubles the number of correct low bits
+  for (int i = 0; i < 6; i++) x *= 2u - a * x;
+  return x & DENSE_MASK;
+}
+constexpr uint32_t DENSE_MULT_INV = dense_inv26(DENSE_MULT);
+static_assert(((DENSE_MULT * DENSE_MULT_INV) & DENSE_MASK) == 1u, "inverse of the hash multiplier");
+static_assert((DENSE_SLOTS + DENSE_CACHE - 1) / DENSE_CACHE <= 2048, "an 11-bit tag must separate the keys of a slot");
 
 struct DenseArgs {
   const uint8_t *data;
@@ -38,113 +52,174 @@ struct DenseArgs {
   uint32_t rs, koff, voff, kb, vb;
 };
 
+#ifndef MRGPU_DENSE_EXPERIMENT
+#define MRGPU_DENSE_EXPERIMENT 0
+#endif
 #ifndef MRGPU_DENSE_THREADS
 #define MRGPU_DENSE_THREADS 1024
 #endif
-#ifndef MRGPU_DENSE_BPS
-#define MRGPU_DENSE_BPS 1
-#endif
-__global__ void __launch_bounds__(MRGPU_DENSE_THREADS)
-dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long *abort_flag)
+
+__device__ __forceinline__ void dense_slot(uint32_t key, uint32_t &slot, uint32_t &tag)
 {
-  extern __shared__ unsigned dsm[];
-  unsigned *tags = dsm, *cnts = dsm + DENSE_CACHE;  // cnts: DENSE_CACHE / 2 words
-  for (int i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x) tags[i] = 0;
-  for (int i = threadIdx.x; i < DENSE_CACHE / 2; i += blockDim.x) cnts[i] = 0;
-  __syncthreads();
+  const uint32_t h = (key * DENSE_MULT) & DENSE_MASK;
+  slot = __umulhi(h << (32 - DENSE_BITS), DENSE_CACHE);
+  tag = (h & 2047u) + 1u;
+}
+
+// four keys at a time: the four tag loads are independent, then the four updates
+__device__ __forceinline__ void dense_count4(const uint32_t (&key)[4], unsigned valid_mask, unsigned *__restrict__ cache, unsigned *__restrict__ table)
+{
+  uint32_t slot[4], tag[4], e[4];
+#pragma unroll
+  for (int q = 0; q < 4; q++) dense_slot(key[q], slot[q], tag[q]);
+#pragma unroll
+  for (int q = 0; q < 4; q++) e[q] = cache[slot[q]];
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    if (!(valid_mask >> q & 1)) continue;
+    uint32_t t = e[q] & 0xFFFu;
+    if (t == 0) {  // empty: claim it (first come; the hot keys come first more often than not)
+      const uint32_t old = atomicCAS(&cache[slot[q]], 0u, tag[q]);
+      t = old ? (old & 0xFFFu) : tag[q];
+    }
+#if MRGPU_DENSE_EXPERIMENT == 1   // timing experiment: misses are dropped
+    if (t == tag[q]) atomicAdd(&cache[slot[q]], 0x1000u);
+#elif MRGPU_DENSE_EXPERIMENT == 2  // timing experiment: hits are dropped
+    if (t != tag[q]) atomicAdd(&table[key[q]], 1u);
+#elif MRGPU_DENSE_EXPERIMENT == 3  // timing experiment: only the tag loads
+    if (t == 0xFFFu) atomicAdd(&table[key[q]], 1u);
+#else
+    if (t == tag[q]) atomicAdd(&cache[slot[q]], 0x1000u);
+    else atomicAdd(&table[key[q]], 1u);
+#endif
+  }
+}
+
+// cache -> table; counts back to zero, tags stay
+__device__ __forceinline__ void dense_flush(unsigned *__restrict__ cache, unsigned *__restrict__ table)
+{
+  for (uint32_t i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x) {
+    const uint32_t e = cache[i], c = e >> 12;
+    if (c) {
+      // h lies in [lo, lo + 1171) where lo = ceil(i * 2^26 / DENSE_CACHE), and its low 11 bits are tag - 1
+      const uint32_t lo = (uint32_t) ((((uint64_t) i << DENSE_BITS) + DENSE_CACHE - 1) / DENSE_CACHE);
+      const uint32_t h = lo + (((e & 0xFFFu) - 1u - lo) & 2047u);
+      atomicAdd(&table[(h * DENSE_MULT_INV) & DENSE_MASK], c);
+      cache[i] = e & 0xFFFu;
+    }
+  }
+}
+
+// MODE 0: header-less rows that are just a 4-byte key (a 16-byte load brings four pairs)
+// MODE 1: 16-byte records {kb, vb, w2, w3} (one load per pair)      MODE 2: any other word-aligned layout
+template <int MODE>
+__global__ void __launch_bounds__(MRGPU_DENSE_THREADS)
+dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long *abort_flag, unsigned long long *key_bits)
+{
+  extern __shared__ unsigned cache[];
+  uint32_t kor = 0;  // OR of this thread's keys: bounds the part of the table that has to be scanned afterwards
+  for (uint32_t i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x) cache[i] = 0;
   // value of record 0 (compared word-wise; vb is 0, 4 or 8 here)
   uint32_t v0a = 0, v0b = 0;
   if (a.vb >= 4) v0a = *(const uint32_t *) (a.data + a.voff);
   if (a.vb == 8) v0b = *(const uint32_t *) (a.data + a.voff + 4);
   bool bad = false;
   const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
-  const bool rec16 = a.rs == 16 && a.koff == 8 && ((uintptr_t) a.data % 16) == 0;
-  auto count_one = [&](uint32_t key, uint32_t khi, uint32_t va, uint32_t vb2) {
-    if (khi != 0 || key >= DENSE_SLOTS || va != v0a || vb2 != v0b) {
-      bad = true;
-      return;
-    }
-    const unsigned slot = (key * 0x9E3779B1u) >> (32 - MRGPU_DENSE_CACHE_BITS);
-    const unsigned tag = key + 1;
-    unsigned t = tags[slot];
-    if (t == 0) {
-      t = atomicCAS(&tags[slot], 0u, tag);
-      if (t == 0) t = tag;
-    }
-    if (t == tag) {
-      const unsigned sh = (slot & 1) * 16;
-      unsigned old = atomicAdd(&cnts[slot >> 1], 1u << sh);
-      if (((old >> sh) & 0xFFFF) == 0x7FFF) {  // this add set the guard bit: take the 32768 out again
-        atomicSub(&cnts[slot >> 1], 0x8000u << sh);
-        atomicAdd(&table[key], 32768u);
-      }
-    } else
-      atomicAdd(&table[key], 1u);
-  };
-  if (a.rs == 4 && a.koff == 0 && ((uintptr_t) a.data % 16) == 0) {
-    // header-less rows that are just a 4-byte key (the value is shared): a 16-byte load brings four pairs
-    constexpr int U = 4;
-    const int4 *q4 = (const int4 *) a.data;
-    const uint64_t n4 = a.n / 4;
-    for (uint64_t base = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; base < n4 && !bad; base += stride * U) {
-      int4 r[U];
+  const uint64_t tid0 = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  // keys a block takes per loop iteration; a round ends before any cache count can reach 2^20
+  constexpr uint32_t KPI = MODE == 0 ? 16 : (MODE == 1 ? 8 : 4);
+  const uint32_t iters_per_round = DENSE_ROUND_LIMIT / (KPI * blockDim.x);
+  const uint64_t units = MODE == 0 ? a.n / 4 : a.n;                 // loop units: 16-byte vectors or pairs
+  constexpr int U = MODE == 0 ? 4 : (MODE == 1 ? 8 : 4);            // units in flight per thread
+  const uint64_t iters = (units + stride * U - 1) / (stride * U);   // same for every thread of the grid
+  __syncthreads();
+  for (uint64_t it0 = 0; it0 < iters; it0 += iters_per_round) {
+    const uint64_t it1 = min(it0 + iters_per_round, iters);
+    for (uint64_t it = it0; it < it1 && !bad; it++) {
+      const uint64_t base = it * stride * U + tid0;
+      if (MODE == 0) {
+        int4 r[U];
 #pragma unroll
-      for (int u = 0; u < U; u++) {
-        uint64_t i = base + (uint64_t) u * stride;
-        if (i < n4) r[u] = ld_stream(q4 + i);
-      }
-#pragma unroll
-      for (int u = 0; u < U; u++) {
-        uint64_t i = base + (uint64_t) u * stride;
-        if (i < n4) {
-          count_one((uint32_t) r[u].x, 0, v0a, v0b);
-          count_one((uint32_t) r[u].y, 0, v0a, v0b);
-          count_one((uint32_t) r[u].z, 0, v0a, v0b);
-          count_one((uint32_t) r[u].w, 0, v0a, v0b);
+        for (int u = 0; u < U; u++) {
+          const uint64_t i = base + (uint64_t) u * stride;
+          if (i < units) r[u] = ld_stream((const int4 *) a.data + i);
         }
-      }
-    }
-    for (uint64_t i = n4 * 4 + (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride)
-      count_one(((const uint32_t *) a.data)[i], 0, v0a, v0b);
-  } else if (rec16) {
-    // one 16-byte load per record {kb, vb, w2, w3}; eight independent loads in flight per thread -- with a
-    // single load per iteration the kernel sat at 18 % issue utilisation waiting on HBM latency (ncu)
-    constexpr int U = 8;
-    const int4 *recs = (const int4 *) a.data;
-    for (uint64_t base = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; base < a.n && !bad; base += stride * U) {
-      int4 r[U];
 #pragma unroll
-      for (int u = 0; u < U; u++) {
-        uint64_t i = base + (uint64_t) u * stride;
-        if (i < a.n) r[u] = ld_stream(recs + i);
-      }
-#pragma unroll
-      for (int u = 0; u < U; u++) {
-        uint64_t i = base + (uint64_t) u * stride;
-        if (i < a.n) {
-          if (a.kb == 8) count_one((uint32_t) r[u].z, (uint32_t) r[u].w, v0a, v0b);
-          else count_one((uint32_t) r[u].z, 0, a.vb == 4 ? (uint32_t) r[u].w : v0a, v0b);
+        for (int u = 0; u < U; u++) {
+          const uint64_t i = base + (uint64_t) u * stride;
+          if (i < units) {
+            const uint32_t k[4] = {(uint32_t) r[u].x, (uint32_t) r[u].y, (uint32_t) r[u].z, (uint32_t) r[u].w};
+            kor |= k[0] | k[1] | k[2] | k[3];
+            if ((k[0] | k[1] | k[2] | k[3]) >= DENSE_SLOTS) bad = true;
+            else dense_count4(k, 0xFu, cache, table);
+          }
         }
+      } else if (MODE == 1) {
+        int4 r[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+          const uint64_t i = base + (uint64_t) u * stride;
+          if (i < units) r[u] = ld_stream((const int4 *) a.data + i);
+        }
+#pragma unroll
+        for (int g = 0; g < U; g += 4) {
+          uint32_t k[4];
+          unsigned vm = 0;
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const uint64_t i = base + (uint64_t) (g + q) * stride;
+            k[q] = 0;
+            if (i < units) {
+              k[q] = (uint32_t) r[g + q].z;
+              const uint32_t w3 = (uint32_t) r[g + q].w;
+              // kb 8: w3 is the key's high word (must be 0); kb 4, vb 4: w3 is the value
+              if (k[q] >= DENSE_SLOTS || (a.kb == 8 ? w3 != 0 : (a.vb == 4 && w3 != v0a))) bad = true;
+              else vm |= 1u << q;
+              kor |= k[q];
+            }
+          }
+          if (!bad) dense_count4(k, vm, cache, table);
+        }
+      } else {
+        uint32_t k[4];
+        unsigned vm = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          const uint64_t i = base + (uint64_t) q * stride;
+          k[q] = 0;
+          if (i < units) {
+            const uint8_t *r = a.data + i * a.rs;
+            k[q] = *(const uint32_t *) (r + a.koff);
+            uint32_t khi = 0, va = v0a, vb2 = v0b;
+            if (a.kb == 8) khi = *(const uint32_t *) (r + a.koff + 4);
+            if (a.vb >= 4) va = *(const uint32_t *) (r + a.voff);
+            if (a.vb == 8) vb2 = *(const uint32_t *) (r + a.voff + 4);
+            if (khi != 0 || k[q] >= DENSE_SLOTS || va != v0a || vb2 != v0b) bad = true;
+            else vm |= 1u << q;
+            kor |= k[q];
+          }
+        }
+        if (!bad) dense_count4(k, vm, cache, table);
       }
     }
-  } else {
-    for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < a.n && !bad; i += stride) {
-      const uint8_t *r = a.data + i * a.rs;
-      uint32_t key = *(const uint32_t *) (r + a.koff), khi = 0, va = v0a, vb2 = v0b;
-      if (a.kb == 8) khi = *(const uint32_t *) (r + a.koff + 4);
-      if (a.vb >= 4) va = *(const uint32_t *) (r + a.voff);
-      if (a.vb == 8) vb2 = *(const uint32_t *) (r + a.voff + 4);
-      count_one(key, khi, va, vb2);
+    if (__syncthreads_or(bad)) {
+      if (threadIdx.x == 0) *abort_flag = 1;
+      return;  // the table is abandoned; the caller falls back to the sort path
+    }
+    dense_flush(cache, table);
+    __syncthreads();
+  }
+  if (MODE == 0) {  // the up to three keys after the last full vector
+    const uint64_t i = units * 4 + tid0;
+    if (i < a.n) {
+      const uint32_t k = ((const uint32_t *) a.data)[i];
+      kor |= k;
+      if (k >= DENSE_SLOTS) *abort_flag = 1;
+      else atomicAdd(&table[k], 1u);
     }
   }
-  if (__syncthreads_or(bad)) {
-    if (threadIdx.x == 0) *abort_flag = 1;
-    return;  // the table is abandoned; the caller falls back to the sort path
-  }
-  for (int i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x) {
-    unsigned c = (cnts[i >> 1] >> ((i & 1) * 16)) & 0xFFFF;
-    if (c) atomicAdd(&table[tags[i] - 1], c);
-  }
+  kor = __reduce_or_sync(0xFFFFFFFFu, kor);
+  if ((threadIdx.x & 31) == 0 && kor) atomicOr(key_bits, (unsigned long long) kor);
 }
 
 // One thread per 4-byte word of the KMV stream: coalesced stores, no reads of pair data at all.
@@ -333,34 +408,50 @@ static bool convert_dense(mrgpu_mr *mr)
   const uint32_t rs = kv->packed ? kv->prow() : kv->recsize, koff = kv->packed ? 0 : kv_key_off(al), voff = kv->packed ? kb : kv_val_off(al, kb);
   const uint32_t svb = shared_val ? 0 : vb;  // value bytes the count kernel has to compare per pair
 
-  Buf<unsigned> table(pool, DENSE_SLOTS);
-  unsigned long long *flag = mr->d_small + 8;
-  MR_CUDA(cudaMemsetAsync(table.p, 0, (uint64_t) DENSE_SLOTS * 4, s));
-  MR_CUDA(cudaMemsetAsync(flag, 0, 8, s));
+  // the table lives as long as the handle and is all zero between calls: the compaction below puts back a
+  // zero wherever it finds a count, so no 256 MB memset per convert
+  if (!mr->dense_table) {
+    mr->dense_table = (unsigned *) pool.alloc((uint64_t) DENSE_SLOTS * 4);
+    MR_CUDA(cudaMemsetAsync(mr->dense_table, 0, (uint64_t) DENSE_SLOTS * 4, s));
+  }
+  unsigned *table = mr->dense_table;
+  unsigned long long *flag = mr->d_small + 8, *key_bits = mr->d_small + 9;
+  MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
   static bool attr_set[64] = {false};
   if (mr->device < 64 && !attr_set[mr->device]) {
-    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 6));
+    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
+    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
+    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
     attr_set[mr->device] = true;
   }
   {
     ProfScope ps(pool, "convert_dense_count", (double) kv->nbytes, 1, (double) kv->phys_bytes());
     DenseArgs a{kv->data, n, rs, koff, voff, kb, svb};
-    dense_count_kernel<<<kSMs * MRGPU_DENSE_BPS, MRGPU_DENSE_THREADS, DENSE_CACHE * 6, s>>>(a, table.p, flag);
+    const bool a16 = ((uintptr_t) kv->data % 16) == 0;
+    if (rs == 4 && koff == 0 && a16) dense_count_kernel<0><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, table, flag, key_bits);
+    else if (rs == 16 && koff == 8 && a16 && svb != 8) dense_count_kernel<1><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, table, flag, key_bits);
+    else dense_count_kernel<2><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, table, flag, key_bits);
     MR_CUDA(cudaGetLastError());
   }
-  unsigned long long h_flag = 1;
+  unsigned long long h_flag[2] = {1, 0};
   uint32_t cv[2] = {0, 0};
-  MR_CUDA(cudaMemcpyAsync(&h_flag, flag, 8, cudaMemcpyDeviceToHost, s));
+  MR_CUDA(cudaMemcpyAsync(h_flag, flag, 16, cudaMemcpyDeviceToHost, s));
   if (shared_val) cv[0] = kv->cval[0], cv[1] = kv->cval[1];
   else if (vb) MR_CUDA(cudaMemcpyAsync(cv, kv->data + voff, vb, cudaMemcpyDeviceToHost, s));
   sync(mr);
-  if (h_flag) return false;
+  if (h_flag[0]) {  // a key or value the table cannot take: clean up, the sort path runs
+    MR_CUDA(cudaMemsetAsync(table, 0, (uint64_t) DENSE_SLOTS * 4, s));
+    return false;
+  }
+  // every key is <= the OR of all keys: only that much of the table can hold counts
+  uint64_t span = 1;
+  while (span <= h_flag[1]) span <<= 1;
 
   // non-empty bins -> U, ukey[u], ucnt[u]
-  const unsigned *tb = table.p;
-  auto nonzero = [=] __device__(uint64_t k) -> bool { return __ldg(tb + k) != 0; };
+  unsigned *tb = table;
+  auto nonzero = [=] __device__(uint64_t k) -> bool { return tb[k] != 0; };
   FlagTiles bins;
-  flag_tiles(pool, DENSE_SLOTS, nonzero, bins, mr->d_small, "convert_dense_bins", (double) DENSE_SLOTS * 4);
+  flag_tiles(pool, span, nonzero, bins, mr->d_small, "convert_dense_bins", (double) span * 4);
   fetch_small(mr, 1);
   const uint64_t U = mr->h_small[0];
   DevKMV *kmv = new DevKMV(&pool);
@@ -372,10 +463,10 @@ static bool convert_dense(mrgpu_mr *mr)
     flag_sink(pool, bins, nonzero, [=] __device__(uint64_t k, unsigned long long e, unsigned long long h) {
       if (h) {
         pk[e] = (uint32_t) k;
-        pc[e] = __ldg(tb + k);
+        pc[e] = tb[k];
+        tb[k] = 0;
       }
-    }, "convert_dense_bins", (double) DENSE_SLOTS * 4 + 8.0 * U);
-    table.release();
+    }, "convert_dense_bins", (double) span * 4 + 12.0 * U);
     kmv->factored = true;
     kmv->fval[0] = cv[0];
     kmv->fval[1] = cv[1];

@@ -118,8 +118,20 @@ __global__ void max_keybytes_kernel(const uint8_t *__restrict__ data, const uint
   if ((threadIdx.x & 31) == 0 && m) atomicMax(mx, m);
 }
 
+// number of adjacent pairs out of order (0 = the stable sort would move nothing)
 template <typename K>
-static void sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nchunks, Buf<uint32_t> &perm_out)
+__global__ void __launch_bounds__(256) sortkey_descents_kernel(const K *__restrict__ k, uint64_t n, unsigned long long *out)
+{
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  unsigned c = 0;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i + 1 < n; i += stride) c += k[i] > k[i + 1];
+  c = __syncthreads_count(c != 0);
+  if (threadIdx.x == 0 && c) atomicAdd(out, (unsigned long long) c);
+}
+
+// returns false when the pairs already are in sorted order (perm_out untouched)
+template <typename K>
+static bool sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nchunks, Buf<uint32_t> &perm_out)
 {
   DevKV *kv = mr->kv;
   Pool &pool = mr->pool;
@@ -144,6 +156,20 @@ static void sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nc
                                                                          absflag, reverse, (uint32_t) c, perm_in, kb[w], pb[w], bad);
     MR_CUDA(cudaGetLastError());
     }
+    if (nchunks == 1) {
+      // adaptive: keys that are already in order (the output of the counting convert + reduce is) need no sort;
+      // one read of the extracted keys decides
+      unsigned long long *desc = mr->d_small + 2;
+      MR_CUDA(cudaMemsetAsync(desc, 0, 8, s));
+      {
+        ProfScope ps(pool, "sort_check", (double) n * sizeof(K));
+        sortkey_descents_kernel<K><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kb[w], n, desc);
+        MR_CUDA(cudaGetLastError());
+      }
+      fetch_small(mr, 3);
+      if (mr->h_small[1] & 0xFFFFFFFFull) MR_FAIL(MRGPU_EINVAL, "sort_keys: key shorter than the compared type");
+      if (mr->h_small[2] == 0) return false;
+    }
     int r = radix_sort_pairs<K, uint32_t, true>(pool, kb[w], kb[w ^ 1], pb[w], pb[w ^ 1], n, 0xFF, false, hist.p);
     int res = w ^ r;
     perm_in = pb[res];
@@ -154,6 +180,7 @@ static void sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nc
   // hand the permutation buffer to the caller
   if (perm_in == p0.p) perm_out = static_cast<Buf<uint32_t> &&>(p0);
   else perm_out = static_cast<Buf<uint32_t> &&>(p1);
+  return true;
 }
 
 static void sort_keys_impl(mrgpu_mr *mr, int flag)
@@ -180,8 +207,10 @@ static void sort_keys_impl(mrgpu_mr *mr, int flag)
     nchunks = (uint32_t) std::max<uint64_t>(1, (maxkb + 7) / 8);
   }
   Buf<uint32_t> perm;
-  if (absflag == 1 || absflag == 3) sort_keys_typed<uint32_t>(mr, absflag, flag < 0, 1, perm);
-  else sort_keys_typed<uint64_t>(mr, absflag, flag < 0, nchunks, perm);
+  bool moved;
+  if (absflag == 1 || absflag == 3) moved = sort_keys_typed<uint32_t>(mr, absflag, flag < 0, 1, perm);
+  else moved = sort_keys_typed<uint64_t>(mr, absflag, flag < 0, nchunks, perm);
+  if (!moved) return;
 
   // gather the records in sorted order into a new KV
   DevKV *nk = new DevKV(&pool);

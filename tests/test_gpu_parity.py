@@ -359,6 +359,36 @@ def test_single_pass_partition_matches_reference_placement(MR, oracle, kb, vb, P
     assert mr.scan_kv() == want
 
 
+def test_convert_dense_table_is_clean_between_calls(MR, oracle):
+    """the 2^26-slot count table belongs to the handle: a success, an abandoned attempt and another success in a row"""
+    mr = MR()
+    r = np.random.RandomState(3)
+    for rnd, hi in enumerate([5000, 1 << 27, 70000]):
+        keys = r.randint(0, 4000 + 1000 * rnd, size=100_000).astype(np.uint32)
+        keys[12345] = hi                                   # round 1: a key the table cannot take
+        mr.map_intcount(keys)
+        want = H.kv_decode(oracle.reduce(oracle.convert(oracle.intcount_map(keys)), "count"))
+        assert mr.convert() == len(want)
+        mr.reduce("count")
+        assert H.canon_kv(mr.scan_kv()) == H.canon_kv(want)
+
+
+def test_sort_keys_leaves_sorted_pairs_alone_and_still_sorts_the_rest(MR, oracle):
+    recs = [(struct.pack("<i", k // 3 - 20), struct.pack("<I", k)) for k in range(30_000)]   # ascending, with ties
+    mr = MR()
+    mr.kv_add(recs)
+    assert mr.sort_keys(1) == len(recs)
+    assert mr.scan_kv() == recs                                                              # stable: nothing moves
+    assert mr.sort_keys(-1) == len(recs)
+    assert H.kv_encode(mr.scan_kv()) == oracle.sort_keys(H.kv_encode(recs), -1)
+    swapped = recs[:]
+    swapped[-1], swapped[-2] = (struct.pack("<i", -99), b"abcd"), swapped[-1]                  # one pair out of place
+    mr2 = MR()
+    mr2.kv_add(swapped)
+    mr2.sort_keys(1)
+    assert H.kv_encode(mr2.scan_kv()) == oracle.sort_keys(H.kv_encode(swapped), 1)
+
+
 # ------------------------------------------------------------------------------------------- compact stores
 
 @pytest.mark.parametrize("compact", [0, 1])
