@@ -100,10 +100,9 @@ def main_nccl():
         shards = [[(struct.pack("<I", int(k)), struct.pack("<i", 1)) for k in ic_keys(q, variant)] for q in range(world)]
         total = sum(len(x) for x in shards)
         assert mr.map_intcount(keys) == total
-        if variant == 3 and rank == world - 1:      # another shape appended on one rank
-            extra = [(b"wide-key", b"")]
+        if variant == 3:                            # another shape appended on one rank (kv_add is collective: close() sums)
+            extra = [(b"wide-key", b"")] if rank == world - 1 else []
             assert mr.kv_add(extra, addflag=1) == total + 1
-        if variant == 3:
             shards[world - 1] = shards[world - 1] + [(b"wide-key", b"")]
             total += 1
         assert mr.aggregate() == total

@@ -1,6 +1,7 @@
 """N > 1 path.  CPU: two gloo ranks exercise the host-side exchange plan of aggregate() (mrgpu_plan_exchange)
 against the reference's delivery rule.  GPU (needs >= 2 devices): the real aggregate/collate over NCCL."""
 import os
+import signal
 import subprocess
 import sys
 
@@ -10,12 +11,19 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WORKER = os.path.join(ROOT, "tests", "multi_rank_worker.py")
 
 
-def _launch(nproc, backend, port, timeout=600, **extra):
+def _launch(nproc, backend, port, timeout=240, **extra):
     env = dict(os.environ, MR_WORKER_BACKEND=backend, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="1", **extra)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), WORKER]
-    p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
-    assert p.returncode == 0 and "MULTI_OK" in p.stdout, (p.stdout[-2000:], p.stderr[-4000:])
+    # own process group: a rank stuck in a collective must not outlive the test
+    p = subprocess.Popen(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, start_new_session=True)
+    try:
+        out, err = p.communicate(timeout=timeout)
+    except subprocess.TimeoutExpired:
+        os.killpg(p.pid, signal.SIGKILL)
+        out, err = p.communicate()
+        raise AssertionError(("timed out", out[-2000:], err[-4000:]))
+    assert p.returncode == 0 and "MULTI_OK" in out, (out[-2000:], err[-4000:])
 
 
 def test_exchange_plan_two_gloo_ranks():
