@@ -126,7 +126,7 @@ class MapReduce:
 
     _SETTINGS = ("mapstyle", "all2all", "verbosity", "timer", "memsize", "minpage", "maxpage", "freepage",
                  "outofcore", "zeropage", "keyalign", "valuealign",
-                 "compact")  # not a reference member: 0 = stores always hold the reference's record streams (see mrgpu.h)
+                 "compact", "ahead")  # not reference members: 0 = stores always hold the reference's record streams (see mrgpu.h)
 
     def __init__(self, device: int = 0, stream: int | None = None, rank: int = 0, nranks: int = 1,
                  unique_id: bytes | None = None):

@@ -49,6 +49,8 @@ struct mrgpu_mr {
   unsigned long long *d_small = nullptr;  // [64] device scalars (totals, flags)
   unsigned long long *h_small = nullptr;  // pinned mirror
   unsigned *dense_table = nullptr;  // convert's 2^26-slot count table: allocated at first use, all zero between calls
+  uint64_t dense_owner = 0;         // uid of the KV whose counts map_intcount already put in the table (0 = none)
+  int64_t ahead = 1;                // setting: map_intcount may do the next op's first pass while it writes the keys
   bool p2p_used = false;  // set identically on every rank
   std::map<std::string, void *> ipc_open;  // peers' receive chunks mapped by the peer-store exchange (CUDA IPC handle -> base)
 };
@@ -182,7 +184,7 @@ static int64_t *setting(mrgpu_mr *mr, const char *name)
   } tab[] = {{"memsize", &mr->memsize},     {"keyalign", &mr->keyalign},   {"valuealign", &mr->valuealign},
              {"verbosity", &mr->verbosity}, {"timer", &mr->timer},         {"all2all", &mr->all2all},
              {"mapstyle", &mr->mapstyle},   {"minpage", &mr->minpage},     {"maxpage", &mr->maxpage},
-             {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage},   {"compact", &mr->compact}};
+             {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage},   {"compact", &mr->compact},     {"ahead", &mr->ahead}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) return t.p;
   return nullptr;

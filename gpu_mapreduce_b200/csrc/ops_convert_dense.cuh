@@ -114,7 +114,7 @@ __device__ __forceinline__ void dense_flush(unsigned *__restrict__ cache, unsign
 // MODE 1: 16-byte records {kb, vb, w2, w3} (one load per pair)      MODE 2: any other word-aligned layout
 template <int MODE>
 __global__ void __launch_bounds__(MRGPU_DENSE_THREADS)
-dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long *abort_flag, unsigned long long *key_bits)
+dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long *abort_flag, unsigned long long *key_bits, int4 *__restrict__ copy_out)
 {
   extern __shared__ unsigned cache[];
   uint32_t kor = 0;  // OR of this thread's keys: bounds the part of the table that has to be scanned afterwards
@@ -135,7 +135,7 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
   __syncthreads();
   for (uint64_t it0 = 0; it0 < iters; it0 += iters_per_round) {
     const uint64_t it1 = min(it0 + iters_per_round, iters);
-    for (uint64_t it = it0; it < it1 && !bad; it++) {
+    for (uint64_t it = it0; it < it1 && (!bad || copy_out); it++) {  // a copy goes on after the count is given up
       const uint64_t base = it * stride * U + tid0;
       if (MODE == 0) {
         int4 r[U];
@@ -148,10 +148,11 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
         for (int u = 0; u < U; u++) {
           const uint64_t i = base + (uint64_t) u * stride;
           if (i < units) {
+            if (copy_out) st_stream(copy_out + i, r[u]);  // emit + count in one pass (map_intcount)
             const uint32_t k[4] = {(uint32_t) r[u].x, (uint32_t) r[u].y, (uint32_t) r[u].z, (uint32_t) r[u].w};
             kor |= k[0] | k[1] | k[2] | k[3];
             if ((k[0] | k[1] | k[2] | k[3]) >= DENSE_SLOTS) bad = true;
-            else dense_count4(k, 0xFu, cache, table);
+            else if (!bad) dense_count4(k, 0xFu, cache, table);
           }
         }
       } else if (MODE == 1) {
@@ -204,7 +205,9 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
     }
     if (__syncthreads_or(bad)) {
       if (threadIdx.x == 0) *abort_flag = 1;
-      return;  // the table is abandoned; the caller falls back to the sort path
+      if (!copy_out) return;  // the table is abandoned; the caller falls back to the sort path
+      bad = true;
+      continue;
     }
     dense_flush(cache, table);
     __syncthreads();
@@ -213,6 +216,7 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
     const uint64_t i = units * 4 + tid0;
     if (i < a.n) {
       const uint32_t k = ((const uint32_t *) a.data)[i];
+      if (copy_out) ((uint32_t *) copy_out)[i] = k;
       kor |= k;
       if (k >= DENSE_SLOTS) *abort_flag = 1;
       else atomicAdd(&table[k], 1u);
@@ -392,6 +396,54 @@ static void kmv_expand(mrgpu_mr *mr, DevKMV *kmv)
   kmv->h_offs_valid = false;
 }
 
+static void dense_prepare(mrgpu_mr *mr)
+{
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  // the table lives as long as the handle and is all zero between calls: the compaction in convert_dense puts
+  // back a zero wherever it finds a count, so no 256 MB memset per convert
+  if (!mr->dense_table) {
+    mr->dense_table = (unsigned *) pool.alloc((uint64_t) DENSE_SLOTS * 4);
+    MR_CUDA(cudaMemsetAsync(mr->dense_table, 0, (uint64_t) DENSE_SLOTS * 4, s));
+  } else if (mr->dense_owner) {  // counts made ahead for a KV that never reached convert()
+    MR_CUDA(cudaMemsetAsync(mr->dense_table, 0, (uint64_t) DENSE_SLOTS * 4, s));
+  }
+  mr->dense_owner = 0;
+  static bool attr_set[64] = {false};
+  if (mr->device < 64 && !attr_set[mr->device]) {
+    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
+    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
+    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
+    attr_set[mr->device] = true;
+  }
+}
+
+// map_intcount on one rank (ops_map.cuh): write the key column AND count it -- convert() then starts at the
+// compaction.  If the KV changes before convert() (append, add, ...) the counts are dropped.
+static void emit_and_count(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64_t n)
+{
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  dense_prepare(mr);
+  unsigned long long *flag = mr->d_small + 8, *key_bits = mr->d_small + 9;
+  MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
+  {
+    // algorithmic bytes: map (input + KV out, 20 B/pair) + convert's read of the KV (16 B/pair); moved: 4 in, 4 out
+    ProfScope ps(pool, "map_intcount_emit_count", (double) n * 36, 1, (double) n * 8);
+    DenseArgs a{(const uint8_t *) keys, n, 4, 0, 4, 4, 0};
+    dense_count_kernel<0><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, (int4 *) kv->data);
+    MR_CUDA(cudaGetLastError());
+  }
+  unsigned long long h[2] = {1, 0};
+  MR_CUDA(cudaMemcpyAsync(h, flag, 16, cudaMemcpyDeviceToHost, s));
+  sync(mr);
+  kv->counted = true;
+  kv->counted_bad = h[0] != 0;
+  kv->counted_bits = h[1];
+  kv->ahead_n = n;
+  mr->dense_owner = kv->uid;
+}
+
 // returns true if the dense path produced mr->kmv; false = not applicable, nothing changed
 static bool convert_dense(mrgpu_mr *mr)
 {
@@ -408,34 +460,25 @@ static bool convert_dense(mrgpu_mr *mr)
   const uint32_t rs = kv->packed ? kv->prow() : kv->recsize, koff = kv->packed ? 0 : kv_key_off(al), voff = kv->packed ? kb : kv_val_off(al, kb);
   const uint32_t svb = shared_val ? 0 : vb;  // value bytes the count kernel has to compare per pair
 
-  // the table lives as long as the handle and is all zero between calls: the compaction below puts back a
-  // zero wherever it finds a count, so no 256 MB memset per convert
-  if (!mr->dense_table) {
-    mr->dense_table = (unsigned *) pool.alloc((uint64_t) DENSE_SLOTS * 4);
-    MR_CUDA(cudaMemsetAsync(mr->dense_table, 0, (uint64_t) DENSE_SLOTS * 4, s));
-  }
-  unsigned *table = mr->dense_table;
+  // counts made by map_intcount while it wrote this very KV?
+  const bool ahead = kv->counted && kv->ahead_n == n && mr->dense_owner == kv->uid && shared_val && kb == 4;
   unsigned long long *flag = mr->d_small + 8, *key_bits = mr->d_small + 9;
-  MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
-  static bool attr_set[64] = {false};
-  if (mr->device < 64 && !attr_set[mr->device]) {
-    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
-    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
-    MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
-    attr_set[mr->device] = true;
-  }
-  {
+  if (!ahead) {
+    dense_prepare(mr);
+    MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
     ProfScope ps(pool, "convert_dense_count", (double) kv->nbytes, 1, (double) kv->phys_bytes());
     DenseArgs a{kv->data, n, rs, koff, voff, kb, svb};
     const bool a16 = ((uintptr_t) kv->data % 16) == 0;
-    if (rs == 4 && koff == 0 && a16) dense_count_kernel<0><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, table, flag, key_bits);
-    else if (rs == 16 && koff == 8 && a16 && svb != 8) dense_count_kernel<1><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, table, flag, key_bits);
-    else dense_count_kernel<2><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, table, flag, key_bits);
+    if (rs == 4 && koff == 0 && a16) dense_count_kernel<0><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, nullptr);
+    else if (rs == 16 && koff == 8 && a16 && svb != 8) dense_count_kernel<1><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, nullptr);
+    else dense_count_kernel<2><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, nullptr);
     MR_CUDA(cudaGetLastError());
   }
-  unsigned long long h_flag[2] = {1, 0};
+  mr->dense_owner = 0;  // the counts in the table are consumed (or wiped) below
+  unsigned *table = mr->dense_table;
+  unsigned long long h_flag[2] = {kv->counted_bad ? 1ull : 0ull, kv->counted_bits};
   uint32_t cv[2] = {0, 0};
-  MR_CUDA(cudaMemcpyAsync(h_flag, flag, 16, cudaMemcpyDeviceToHost, s));
+  if (!ahead) MR_CUDA(cudaMemcpyAsync(h_flag, flag, 16, cudaMemcpyDeviceToHost, s));
   if (shared_val) cv[0] = kv->cval[0], cv[1] = kv->cval[1];
   else if (vb) MR_CUDA(cudaMemcpyAsync(cv, kv->data + voff, vb, cudaMemcpyDeviceToHost, s));
   sync(mr);

@@ -85,7 +85,8 @@ __device__ __forceinline__ void load_record(const uint32_t *__restrict__ p, uint
 // long-scoreboard stall cycles per issue, 2.3 TB/s).
 template <int RW, int KW, int KOFF>
 __global__ void __launch_bounds__(PART_THREADS)
-partition_count_kernel(const uint32_t *__restrict__ data, uint64_t n, uint32_t nprocs, uint64_t ntiles, unsigned *__restrict__ tcount)
+partition_count_kernel(const uint32_t *__restrict__ data, uint64_t n, uint32_t nprocs, uint64_t ntiles, unsigned *__restrict__ tcount,
+                       uint8_t *__restrict__ dest_out, uint32_t *__restrict__ copy_out)
 {
   __shared__ unsigned sh[PART_MAXP];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -104,6 +105,11 @@ partition_count_kernel(const uint32_t *__restrict__ data, uint64_t n, uint32_t n
         uint32_t rec[RW];
         load_record<RW>(data + (tbase + sidx) * RW, rec);
         dest[j] = record_dest<RW, KW, KOFF>(rec, nprocs);
+        dest_out[tbase + sidx] = (uint8_t) dest[j];  // pass 2 does not hash again
+        if (copy_out) {  // map_intcount: this pass also writes the rows into the KV
+#pragma unroll
+          for (int q = 0; q < RW; q++) copy_out[(tbase + sidx) * RW + q] = rec[q];
+        }
       }
     }
     if (nprocs <= 32) {
@@ -150,7 +156,7 @@ struct DestPtrs {
 template <int RW, int KW, int KOFF>
 __global__ void __launch_bounds__(PART_THREADS)
 partition_scatter_kernel(const uint32_t *__restrict__ data, DestPtrs dp, uint64_t n, uint32_t nprocs, int nbits, uint64_t ntiles,
-                         const unsigned *__restrict__ toffs, bool direct)
+                         const unsigned *__restrict__ toffs, bool direct, const uint8_t *__restrict__ dest_in)
 {
   extern __shared__ __align__(16) unsigned char psm[];
   uint32_t *xrec = (uint32_t *) psm;                                // [PART_TILE * RW] records in destination order
@@ -179,7 +185,7 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, DestPtrs dp, uint64_
   for (int j = 0; j < PART_IPT; j++) {
     const unsigned sidx = woff0 + j * 32;
     dest[j] = nprocs;  // sentinel for empty slots: ranks after every real destination
-    if (sidx < nvalid) dest[j] = record_dest<RW, KW, KOFF>(rec[j], nprocs);
+    if (sidx < nvalid) dest[j] = dest_in[tbase + sidx];
   }
   // rank inside the warp by destination, in memory order
   const unsigned lt_mask = lanemask_lt();
@@ -296,30 +302,29 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, DestPtrs dp, uint64_
   }
 }
 
-// state between the two passes
-struct PartPlan {
-  int rw = 0, kw = 0;
-  uint64_t ntiles = 0;
-  Buf<unsigned> toffs;
-};
+// state between the two passes: struct PartPlan, store.cuh
 
 template <int RW, int KW, int KOFF>
-static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount)
+static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount, const uint32_t *src = nullptr, uint64_t nsrc = 0)
 {
+  // src != nullptr: the rows come from src (nsrc of them) and are written to kv->data by the same pass
   Pool &pool = mr->pool;
   cudaStream_t s = pool.stream;
   const int P = mr->nranks;
-  const uint64_t n = kv->nkv;
+  const uint64_t n = src ? nsrc : kv->nkv;
   const uint64_t ntiles = (n + PART_TILE - 1) / PART_TILE;
   pl.rw = RW;
   pl.kw = KW;
   pl.ntiles = ntiles;
   Buf<unsigned> tcount(pool, ntiles * P);
   pl.toffs.alloc(pool, ntiles * P);
+  pl.dest.alloc(pool, n);
   {
-    ProfScope ps(pool, "aggregate_count", (double) kv->nbytes, 1, (double) kv->phys_bytes());
-    partition_count_kernel<RW, KW, KOFF><<<(unsigned) std::min<uint64_t>(ntiles, (uint64_t) kSMs * 16), PART_THREADS, 0, s>>>((const uint32_t *) kv->data, n,
-                                                                                                                      (uint32_t) P, ntiles, tcount.p);
+    // emit + count: map's 20 B/pair plus aggregate's read of the KV (16 B/pair) in the reference layout; moved: rows in, rows + 1 byte out
+    ProfScope ps(pool, src ? "map_intcount_emit_plan" : "aggregate_count", src ? (double) n * 36 : (double) kv->nbytes, 1,
+                 src ? (double) n * (RW * 8 + 1) : (double) kv->phys_bytes() + (double) n);
+    partition_count_kernel<RW, KW, KOFF><<<(unsigned) std::min<uint64_t>(ntiles, (uint64_t) kSMs * 16), PART_THREADS, 0, s>>>(
+        src ? src : (const uint32_t *) kv->data, n, (uint32_t) P, ntiles, tcount.p, pl.dest.p, src ? (uint32_t *) kv->data : nullptr);
     MR_CUDA(cudaGetLastError());
   }
   // exclusive scan in destination-major order = slot of every (destination, tile)
@@ -356,7 +361,7 @@ static void partition_scatter_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, const Des
   }
   ProfScope ps(pool, tag, 2.0 * kv->nbytes, 1, 2.0 * kv->phys_bytes());
   partition_scatter_kernel<RW, KW, KOFF><<<(unsigned) pl.ntiles, PART_THREADS, direct ? 0 : smem, s>>>((const uint32_t *) kv->data, dp, kv->nkv, (uint32_t) P, nbits, pl.ntiles,
-                                                                                  pl.toffs.p, direct);
+                                                                                  pl.toffs.p, direct, pl.dest.p);
   MR_CUDA(cudaGetLastError());
 }
 
@@ -396,6 +401,18 @@ static bool partition_eligible(mrgpu_mr *mr, DevKV *kv)
 }
 
 static void partition_counts(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount) { PART_DISPATCH(partition_counts_t, mr, kv, pl, scount); }
+// map_intcount on several ranks (ops_map.cuh): the pass that writes the key column also does aggregate()'s
+// pass 1 (destination of every pair, per-tile counts).  aggregate() uses the plan if the KV is still the same.
+static void emit_and_plan(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64_t n)
+{
+  delete kv->plan;
+  kv->plan = new PartPlan();
+  kv->plan_scount.assign(mr->nranks, 0);
+  partition_counts_t<1, 1, 0>(mr, kv, *kv->plan, kv->plan_scount, keys, n);
+  kv->plan_nranks = mr->nranks;
+  kv->ahead_n = n;
+}
+
 static void partition_scatter(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, const DestPtrs &dp, const char *tag, bool remote = false)
 {
   PART_DISPATCH(partition_scatter_t, mr, kv, pl, dp, tag, remote);

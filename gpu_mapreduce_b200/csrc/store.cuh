@@ -18,6 +18,14 @@
 
 namespace mrgpu {
 
+// aggregate()'s partition, state between its two passes (ops_partition.cuh)
+struct PartPlan {
+  int rw = 0, kw = 0;
+  uint64_t ntiles = 0;
+  Buf<unsigned> toffs;  // [nranks * ntiles] slot of each tile's first pair per destination, destination-major
+  Buf<uint8_t> dest;    // destination rank of every pair (nranks <= 256), written by pass 1 for pass 2
+};
+
 struct DevKV {
   Pool *pool = nullptr;
   uint8_t *data = nullptr;
@@ -38,15 +46,25 @@ struct DevKV {
   bool packed = false;
   bool cval_on = false;
   uint32_t cval[2] = {0, 0};
+  // Work done ahead at emit time (map_intcount, ops_map.cuh): the pass that writes the key column also did the
+  // first pass of whatever comes next -- one rank: convert's count into the handle's table (counted*); several
+  // ranks: aggregate's destination counts (plan, ops_partition.cuh).  Valid only while nkv == ahead_n.
+  uint64_t uid = 0;            // identity of this KV among the handle's stores
+  uint64_t ahead_n = 0;
+  bool counted = false, counted_bad = false;
+  uint64_t counted_bits = 0;
+  PartPlan *plan = nullptr;
+  int plan_nranks = 0;
+  std::vector<uint64_t> plan_scount;
   uint32_t prow() const { return kb + (cval_on ? 0 : vb); }                  // bytes per stored row
   uint64_t phys_bytes() const { return packed ? nkv * prow() : nbytes; }    // bytes of data in use
 
-  explicit DevKV(Pool *p) : pool(p) {}
-  ~DevKV()
+  explicit DevKV(Pool *p) : pool(p)
   {
-    pool->free(data, cap);
-    pool->free(offs, offs_cap * 8);
+    static uint64_t next_uid = 0;
+    uid = ++next_uid;
   }
+  ~DevKV();
   void reserve_bytes(uint64_t need)
   {
     if (need <= cap) return;
@@ -72,6 +90,13 @@ struct DevKV {
     offs_cap = ncap;
   }
 };
+
+inline DevKV::~DevKV()
+{
+  delete plan;
+  pool->free(data, cap);
+  pool->free(offs, offs_cap * 8);
+}
 
 struct DevKMV {
   Pool *pool = nullptr;

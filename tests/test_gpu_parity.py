@@ -414,6 +414,41 @@ def test_compact_stores_give_the_same_pairs_and_pages(MR, oracle, compact, cb):
     assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(oracle.reduce(kmv_ref, cb)))
 
 
+@pytest.mark.parametrize("ahead", [0, 1])
+def test_counts_made_at_emit_time_follow_the_kv(MR, oracle, ahead):
+    """map_intcount counts while it writes (ahead=1); the counts must be used only for that very KV, unchanged"""
+    a = W.intcount_keys_np(0, 150_000, ndistinct=2000, seed=11)
+    b = W.intcount_keys_np(0, 90_000, ndistinct=500, seed=12)
+    want = lambda keys: H.canon_kv(H.kv_decode(oracle.reduce(oracle.convert(oracle.intcount_map(keys)), "count")))
+    mr = MR(ahead=ahead)
+    mr.map_intcount(a)                                   # straight to convert: the counts are the ones made ahead
+    mr.convert(), mr.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == want(a)
+    mr.map_intcount(a)
+    mr.map_intcount(b)                                   # a's counts are stale now
+    mr.convert(), mr.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == want(b)
+    mr.map_intcount(a)
+    mr.map_intcount(b, addflag=1)                        # appended: recount
+    mr.convert(), mr.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == want(np.concatenate([a, b]))
+    bad = a.copy()
+    bad[77_777] = 1 << 30                                # emit-time count gives up, the copy must still be complete
+    mr.map_intcount(bad)
+    assert mr.scan_kv() == H.kv_decode(oracle.intcount_map(bad))
+    mr.convert(), mr.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == want(bad)
+    mr.map_intcount(a)                                   # and the table is clean again afterwards
+    mr.convert(), mr.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == want(a)
+    mr2 = MR(ahead=ahead)                                # two handles do not share counts
+    mr.map_intcount(a)
+    mr2.map_intcount(b)
+    mr2.convert(), mr.convert()
+    mr.reduce("count"), mr2.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == want(a) and H.canon_kv(mr2.scan_kv()) == want(b)
+
+
 @pytest.mark.parametrize("P", [2, 8, 33])
 def test_partition_of_headerless_rows(MR, oracle, P):
     keys = W.intcount_keys_np(0, 70_001, ndistinct=5000, seed=P)
