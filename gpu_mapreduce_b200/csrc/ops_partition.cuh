@@ -86,7 +86,7 @@ __device__ __forceinline__ void load_record(const uint32_t *__restrict__ p, uint
 template <int RW, int KW, int KOFF>
 __global__ void __launch_bounds__(PART_THREADS)
 partition_count_kernel(const uint32_t *__restrict__ data, uint64_t n, uint32_t nprocs, uint64_t ntiles, unsigned *__restrict__ tcount,
-                       uint8_t *__restrict__ dest_out, uint32_t *__restrict__ copy_out)
+                       uint8_t *__restrict__ dest_out)
 {
   __shared__ unsigned sh[PART_MAXP];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -106,10 +106,6 @@ partition_count_kernel(const uint32_t *__restrict__ data, uint64_t n, uint32_t n
         load_record<RW>(data + (tbase + sidx) * RW, rec);
         dest[j] = record_dest<RW, KW, KOFF>(rec, nprocs);
         dest_out[tbase + sidx] = (uint8_t) dest[j];  // pass 2 does not hash again
-        if (copy_out) {  // map_intcount: this pass also writes the rows into the KV
-#pragma unroll
-          for (int q = 0; q < RW; q++) copy_out[(tbase + sidx) * RW + q] = rec[q];
-        }
       }
     }
     if (nprocs <= 32) {
@@ -295,6 +291,25 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, DestPtrs dp, uint64_
     }
   }
   __syncthreads();
+  if (VW < 4 && nprocs <= PART_DIRECT_MAXP) {
+    // narrow rows, few destinations: each destination's run leaves as 16-byte stores (4-byte keys over NVLink:
+    // 476 GB/s with one word per lane against 654 GB/s measured for 16-byte records)
+    for (uint32_t d = 0; d < nprocs; d++) {
+      const unsigned rs = wc[0][d], re = (d + 1 < nprocs) ? wc[0][d + 1] : nvalid;
+      const unsigned w0 = rs * RW, len = (re - rs) * RW;  // words in shared memory
+      uint32_t *G = (uint32_t *) dp.base[d] + (uint64_t) (gbase[d] + rs) * RW;
+      unsigned head = (unsigned) ((16 - ((uintptr_t) G & 15)) & 15) / 4;
+      if (head > len) head = len;
+      const unsigned nv4 = (len - head) / 4, tail0 = head + nv4 * 4;
+      if (tid < (int) head) G[tid] = xrec[w0 + tid];
+      for (unsigned v = tid; v < nv4; v += PART_THREADS) {
+        const uint32_t *x = xrec + w0 + head + 4 * v;
+        *reinterpret_cast<int4 *>(G + head + 4 * v) = make_int4((int) x[0], (int) x[1], (int) x[2], (int) x[3]);
+      }
+      if (tid < (int) (len - tail0)) G[tail0 + tid] = xrec[w0 + tail0 + tid];
+    }
+    return;
+  }
   const unsigned nvec = nvalid * NV;
   for (unsigned v = tid; v < nvec; v += PART_THREADS) {
     const unsigned s = v / NV, q = v - s * NV;
@@ -305,13 +320,12 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, DestPtrs dp, uint64_
 // state between the two passes: struct PartPlan, store.cuh
 
 template <int RW, int KW, int KOFF>
-static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount, const uint32_t *src = nullptr, uint64_t nsrc = 0)
+static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount)
 {
-  // src != nullptr: the rows come from src (nsrc of them) and are written to kv->data by the same pass
   Pool &pool = mr->pool;
   cudaStream_t s = pool.stream;
   const int P = mr->nranks;
-  const uint64_t n = src ? nsrc : kv->nkv;
+  const uint64_t n = kv->nkv;
   const uint64_t ntiles = (n + PART_TILE - 1) / PART_TILE;
   pl.rw = RW;
   pl.kw = KW;
@@ -320,11 +334,9 @@ static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vecto
   pl.toffs.alloc(pool, ntiles * P);
   pl.dest.alloc(pool, n);
   {
-    // emit + count: map's 20 B/pair plus aggregate's read of the KV (16 B/pair) in the reference layout; moved: rows in, rows + 1 byte out
-    ProfScope ps(pool, src ? "map_intcount_emit_plan" : "aggregate_count", src ? (double) n * 36 : (double) kv->nbytes, 1,
-                 src ? (double) n * (RW * 8 + 1) : (double) kv->phys_bytes() + (double) n);
+    ProfScope ps(pool, "aggregate_count", (double) kv->nbytes, 1, (double) kv->phys_bytes() + (double) n);
     partition_count_kernel<RW, KW, KOFF><<<(unsigned) std::min<uint64_t>(ntiles, (uint64_t) kSMs * 16), PART_THREADS, 0, s>>>(
-        src ? src : (const uint32_t *) kv->data, n, (uint32_t) P, ntiles, tcount.p, pl.dest.p, src ? (uint32_t *) kv->data : nullptr);
+        (const uint32_t *) kv->data, n, (uint32_t) P, ntiles, tcount.p, pl.dest.p);
     MR_CUDA(cudaGetLastError());
   }
   // exclusive scan in destination-major order = slot of every (destination, tile)
@@ -401,18 +413,6 @@ static bool partition_eligible(mrgpu_mr *mr, DevKV *kv)
 }
 
 static void partition_counts(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount) { PART_DISPATCH(partition_counts_t, mr, kv, pl, scount); }
-// map_intcount on several ranks (ops_map.cuh): the pass that writes the key column also does aggregate()'s
-// pass 1 (destination of every pair, per-tile counts).  aggregate() uses the plan if the KV is still the same.
-static void emit_and_plan(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64_t n)
-{
-  delete kv->plan;
-  kv->plan = new PartPlan();
-  kv->plan_scount.assign(mr->nranks, 0);
-  partition_counts_t<1, 1, 0>(mr, kv, *kv->plan, kv->plan_scount, keys, n);
-  kv->plan_nranks = mr->nranks;
-  kv->ahead_n = n;
-}
-
 static void partition_scatter(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, const DestPtrs &dp, const char *tag, bool remote = false)
 {
   PART_DISPATCH(partition_scatter_t, mr, kv, pl, dp, tag, remote);

@@ -46,16 +46,12 @@ struct DevKV {
   bool packed = false;
   bool cval_on = false;
   uint32_t cval[2] = {0, 0};
-  // Work done ahead at emit time (map_intcount, ops_map.cuh): the pass that writes the key column also did the
-  // first pass of whatever comes next -- one rank: convert's count into the handle's table (counted*); several
-  // ranks: aggregate's destination counts (plan, ops_partition.cuh).  Valid only while nkv == ahead_n.
+  // Work done ahead at emit time (map_intcount on one rank, ops_map.cuh): the pass that wrote the key column
+  // also counted the keys into the handle's table, which is convert's first pass.  Valid only while nkv == ahead_n.
   uint64_t uid = 0;            // identity of this KV among the handle's stores
   uint64_t ahead_n = 0;
   bool counted = false, counted_bad = false;
   uint64_t counted_bits = 0;
-  PartPlan *plan = nullptr;
-  int plan_nranks = 0;
-  std::vector<uint64_t> plan_scount;
   uint32_t prow() const { return kb + (cval_on ? 0 : vb); }                  // bytes per stored row
   uint64_t phys_bytes() const { return packed ? nkv * prow() : nbytes; }    // bytes of data in use
 
@@ -93,7 +89,6 @@ struct DevKV {
 
 inline DevKV::~DevKV()
 {
-  delete plan;
   pool->free(data, cap);
   pool->free(offs, offs_cap * 8);
 }

@@ -81,7 +81,7 @@ const char *mrgpu_last_error(const mrgpu_mr *mr);
  * stream is written when its bytes are asked for (page copies, device views, ops that read records).  With 0
  * every store always holds the record stream.  Results and page images are identical either way.
  * "ahead" (default 1): mrgpu_map_intcount's pass over the keys also does the first pass of the op that follows
- * it in every pipeline (one rank: convert's key count; several ranks: aggregate's destination count); the work
+ * it in every pipeline on one rank (convert's key count); the work
  * is dropped if the KeyValue changes before that op runs.  0 turns this off.
  * mrgpu_destroy is collective over the communicator once aggregate() has exchanged pairs by peer stores
  * (like MapReduce::~MapReduce's MPI_Comm_free, src/mapreduce.cpp:283). */

@@ -461,6 +461,23 @@ def test_partition_of_headerless_rows(MR, oracle, P):
     assert mr.scan_kv() == [rec for p in range(P) for rec, d in zip(recs, dest) if d == p]
 
 
+def test_partition_staged_runs_variant():
+    """the staged (shared-memory runs, 16-byte stores) form of pass 2 is what crosses NVLink; on one GPU it is
+    chosen by MRGPU_PART_DIRECT=0, which is read once per process: rerun the placement tests in a child"""
+    import os
+    import subprocess
+    import sys
+
+    if os.environ.get("MRGPU_PART_DIRECT") == "0":
+        pytest.skip("already inside the child run")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_parity.py"), "-q", "-x", "-m", "gpu", "-k",
+                        "single_pass_partition or partition_of_headerless_rows"], env=dict(os.environ, MRGPU_PART_DIRECT="0"),
+                       capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-3000:]
+    assert "passed" in p.stdout and "failed" not in p.stdout
+
+
 def test_headerless_kv_meets_other_shapes(MR, oracle):
     """ops without a header-less kernel (add, map(mr), sort_keys, appending another shape) see the records"""
     keys = W.intcount_keys_np(0, 3000, ndistinct=40, seed=9)
