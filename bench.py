@@ -363,9 +363,16 @@ def main():
     dom = max([k for k in kern if k["tag"] != "aggregate_exchange_nvlink"], key=lambda k: k["ms"]) if kern else None
     step_ms = ms / args.steps
     roofline = None
+    traffic = None
+    try:  # measured DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture
+        tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_ncu_traffic.json")))
+        if dom and dom["tag"] in tj and tj[dom["tag"]]["pairs"] == n:
+            traffic = tj[dom["tag"]]["dram_bytes"]
+    except Exception:
+        traffic = None
     if dom:
         roofline = {"bound": "hbm", "kernel": dom["tag"], "achieved": dom["gbs"], "peak": peak, "unit": "GB/s",
-                    "frac": (dom["gbs"] / peak) if dom["gbs"] else None, "traffic": None,
+                    "frac": (dom["gbs"] / peak) if dom["gbs"] else None, "traffic": traffic,
                     "peak_source": peak_src, "launches_per_step": dom["calls"], "ms_per_launch": dom["ms_per_launch"],
                     "share_of_step": dom["ms"] / step_ms,
                     "algorithmic_bytes_per_launch": dom["bytes"] / max(dom["calls"], 1),
