@@ -49,6 +49,8 @@ struct mrgpu_mr {
   unsigned long long *d_small = nullptr;  // [64] device scalars (totals, flags)
   unsigned long long *h_small = nullptr;  // pinned mirror
   unsigned *dense_table = nullptr;  // convert's 2^26-slot count table: allocated at first use, all zero between calls
+  cudaStream_t copy_stream = nullptr;  // host input: DMA on this stream overlaps the kernels that consume the chunks
+  cudaEvent_t copy_ev[2] = {nullptr, nullptr};
   uint64_t dense_owner = 0;         // uid of the KV whose counts map_intcount already put in the table (0 = none)
   int64_t ahead = 1;                // setting: map_intcount may do the next op's first pass while it writes the keys
   bool p2p_used = false;  // set identically on every rank
@@ -168,6 +170,9 @@ extern "C" int mrgpu_destroy(mrgpu_mr *mr)
     if (mr->p2p_used) peer_store_teardown(mr);
     comm_destroy(mr);
   }
+  if (mr->copy_stream) cudaStreamDestroy(mr->copy_stream);
+  for (auto e : mr->copy_ev)
+    if (e) cudaEventDestroy(e);
   cudaFree(mr->d_small);
   cudaFreeHost(mr->h_small);
   delete mr;

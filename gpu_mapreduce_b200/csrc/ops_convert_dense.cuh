@@ -444,6 +444,63 @@ static void emit_and_count(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64
   mr->dense_owner = kv->uid;
 }
 
+// map_intcount with the keys in host memory: chunked DMA into the key column on a second stream; when `count`,
+// each chunk is counted as soon as it has landed, so only the last chunk's count is not hidden behind PCIe.
+static void emit_from_host(mrgpu_mr *mr, DevKV *kv, const uint32_t *hkeys, uint64_t n, bool count)
+{
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  uint32_t *dst = (uint32_t *) kv->data + kv->nkv;
+  if (!mr->copy_stream) {
+    MR_CUDA(cudaStreamCreateWithFlags(&mr->copy_stream, cudaStreamNonBlocking));
+    for (auto &e : mr->copy_ev) MR_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  unsigned long long *flag = mr->d_small + 8, *key_bits = mr->d_small + 9;
+  if (count) {
+    dense_prepare(mr);
+    MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
+  }
+  // the copy stream starts after everything already queued on the handle's stream (allocation reuse)
+  MR_CUDA(cudaEventRecord(mr->copy_ev[0], s));
+  MR_CUDA(cudaStreamWaitEvent(mr->copy_stream, mr->copy_ev[0], 0));
+  // 64 M keys per chunk: the cache flush at the end of every count launch is 148 x 57 344 REDs, small against
+  // the 16 M misses a chunk of this workload has anyway
+  const uint64_t chunk = 1ull << 26;
+  std::vector<cudaEvent_t> landed;
+  bool counted_any = false;
+  for (uint64_t o = 0; o < n; o += chunk) {
+    const uint64_t m = std::min(chunk, n - o);
+    MR_CUDA(cudaMemcpyAsync(dst + o, hkeys + o, m * 4, cudaMemcpyHostToDevice, mr->copy_stream));
+    cudaEvent_t e;
+    MR_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    landed.push_back(e);
+    MR_CUDA(cudaEventRecord(e, mr->copy_stream));
+    MR_CUDA(cudaStreamWaitEvent(s, e, 0));
+    if (count && (((uintptr_t) (dst + o)) & 15) == 0) {
+      ProfScope ps(pool, "map_intcount_count_chunk", (double) m * 16, 1, (double) m * 4);
+      DenseArgs a{(const uint8_t *) (dst + o), m, 4, 0, 4, 4, 0};
+      dense_count_kernel<0><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, nullptr);
+      MR_CUDA(cudaGetLastError());
+      counted_any = true;
+    } else
+      count = false;  // an unaligned destination: convert() will count the whole KV itself
+  }
+  unsigned long long h[2] = {1, 0};
+  if (count) MR_CUDA(cudaMemcpyAsync(h, flag, 16, cudaMemcpyDeviceToHost, s));
+  sync(mr);
+  for (auto e : landed) cudaEventDestroy(e);
+  if (count) {
+    kv->counted = true;
+    kv->counted_bad = h[0] != 0;
+    kv->counted_bits = h[1];
+    kv->ahead_n = n;
+    mr->dense_owner = kv->uid;
+  } else if (counted_any) {
+    // counting was abandoned half way: the table holds counts of the first chunks
+    mr->dense_owner = ~0ull;  // "dirty, owned by nobody": dense_prepare wipes it before the next use
+  }
+}
+
 // returns true if the dense path produced mr->kmv; false = not applicable, nothing changed
 static bool convert_dense(mrgpu_mr *mr)
 {

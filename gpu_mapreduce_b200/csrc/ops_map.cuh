@@ -11,6 +11,7 @@
 // addflag = 1 re-opens the current one for append (KeyValue::append, src/keyvalue.cpp:185-209).
 static void kv_unpack(mrgpu_mr *mr, DevKV *kv);
 static void emit_and_count(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64_t n);  // ops_convert_dense.cuh
+static void emit_from_host(mrgpu_mr *mr, DevKV *kv, const uint32_t *hkeys, uint64_t n, bool count);  // ops_convert_dense.cuh
 
 static void kv_begin_map(mrgpu_mr *mr, int addflag, bool keep_packed = false)
 {
@@ -240,6 +241,28 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
   kv_begin_map(mr, addflag, true);
   DevKV *kv = mr->kv;
   Buf<uint32_t> tmp;
+  // header-less KV from host memory: the key column is filled by DMA (55.6 GB/s measured against 51.7 GB/s for a
+  // kernel reading pinned memory through its device alias), in chunks so that counting overlaps the transfer
+  if (n && !is_device_ptr(keys) && kv_can_pack(mr, 4, 4) &&
+      (kv->nkv == 0 || (kv->packed && kv->cval_on && kv->kb == 4 && kv->vb == 4 && kv->cval[0] == 1))) {
+    if (kv->nkv == 0) {
+      kv->uniform = kv->packed = kv->cval_on = true;
+      kv->kb = kv->vb = 4;
+      kv->recsize = 16;
+      kv->cval[0] = 1;
+      kv->cval[1] = 0;
+    }
+    kv->reserve_bytes((kv->nkv + n) * 4);
+    const bool count = kv->nkv == 0 && mr->ahead && mr->nranks == 1 && n >= (1u << 16);
+    emit_from_host(mr, kv, keys, n, count);
+    kv_commit_uniform(kv, 4, 4, 16, n);
+    kv->h_offs_valid = false;
+    if (nkv) {
+      sync(mr);
+      *nkv = allreduce_sum(mr, kv->nkv);
+    }
+    return MRGPU_OK;
+  }
   const uint32_t *dk = stage_input(mr, keys, n, tmp);
   // header-less: every pair is {4, 4, key, 1}, so the KV is the key column plus one shared value
   const bool pack = kv_can_pack(mr, 4, 4) &&

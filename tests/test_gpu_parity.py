@@ -415,11 +415,32 @@ def test_compact_stores_give_the_same_pairs_and_pages(MR, oracle, compact, cb):
 
 
 @pytest.mark.parametrize("ahead", [0, 1])
-def test_counts_made_at_emit_time_follow_the_kv(MR, oracle, ahead):
-    """map_intcount counts while it writes (ahead=1); the counts must be used only for that very KV, unchanged"""
+@pytest.mark.parametrize("where", ["device", "pinned", "pageable"])
+def test_counts_made_at_emit_time_follow_the_kv(MR, oracle, ahead, where):
+    """map_intcount counts while it writes (ahead=1; host input: chunked DMA with the count overlapped); the counts
+    must be used only for that very KV, unchanged"""
+    torch = _torch()
     a = W.intcount_keys_np(0, 150_000, ndistinct=2000, seed=11)
     b = W.intcount_keys_np(0, 90_000, ndistinct=500, seed=12)
     want = lambda keys: H.canon_kv(H.kv_decode(oracle.reduce(oracle.convert(oracle.intcount_map(keys)), "count")))
+
+    class _Loc:  # hands map_intcount the keys where the test wants them
+        def __init__(self, mr):
+            self.mr, self.keep = mr, []
+
+        def map_intcount(self, keys, addflag=0):
+            if where == "pageable":
+                return self.mr.map_intcount(keys, addflag=addflag)
+            t = torch.from_numpy(keys.view(np.int32).copy())
+            t = t.cuda() if where == "device" else t.pin_memory()
+            self.keep.append(t)
+            return self.mr.map_intcount(t, addflag=addflag)
+
+        def __getattr__(self, name):
+            return getattr(self.mr, name)
+
+    _MR = MR
+    MR = lambda **kw: _Loc(_MR(**kw))
     mr = MR(ahead=ahead)
     mr.map_intcount(a)                                   # straight to convert: the counts are the ones made ahead
     mr.convert(), mr.reduce("count")
