@@ -79,6 +79,9 @@ def lib():
         "mrgpu_collate": [vp, u64p],
         "mrgpu_reduce": [vp, C.c_int, u64p],
         "mrgpu_sort_keys": [vp, C.c_int, u64p],
+        "mrgpu_sort_values": [vp, C.c_int, u64p],
+        "mrgpu_compress": [vp, C.c_int, u64p],
+        "mrgpu_gather": [vp, C.c_int, u64p],
         "mrgpu_kv_stats": [vp, C.POINTER(Stats)],
         "mrgpu_kmv_stats": [vp, C.POINTER(Stats)],
         "mrgpu_kv_page_info": [vp, C.c_uint64, u64p, u64p, u64p, u64p],
@@ -269,6 +272,18 @@ class MapReduce:
 
     def sort_keys(self, flag: int):
         return self._count(lib().mrgpu_sort_keys, int(flag))
+
+    def sort_values(self, flag: int):
+        """sort_values(flag) src/mapreduce.cpp:2156: per-rank stable sort of the pairs by value."""
+        return self._count(lib().mrgpu_sort_values, int(flag))
+
+    def compress(self, functor: str):
+        """compress(mycompress) src/mapreduce.cpp:749 with a stock callback: local convert + reduce, no exchange."""
+        return self._count(lib().mrgpu_compress, REDUCE[functor])
+
+    def gather(self, numprocs: int):
+        """gather(numprocs) src/mapreduce.cpp:893: pairs of ranks >= numprocs move to rank me % numprocs."""
+        return self._count(lib().mrgpu_gather, int(numprocs))
 
     # -- stats, pages, scan
     def kv_stats(self, level=0):

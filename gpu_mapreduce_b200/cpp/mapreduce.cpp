@@ -716,42 +716,8 @@ uint64_t MapReduce::sort_keys(int flag)
   return n;
 }
 
-// the built-in comparisons of src/mapreduce.cpp:2692-2802, restated, for sort_values(flag)
-static int cmp_builtin(int flag, char *p1, int l1, char *p2, int l2)
-{
-  int a = flag < 0 ? -flag : flag, c = 0;
-  if (a == 1) {
-    int x, y;
-    memcpy(&x, p1, 4);
-    memcpy(&y, p2, 4);
-    c = x < y ? -1 : (x > y);
-  } else if (a == 2) {
-    uint64_t x, y;
-    memcpy(&x, p1, 8);
-    memcpy(&y, p2, 8);
-    c = x < y ? -1 : (x > y);
-  } else if (a == 3) {
-    float x, y;
-    memcpy(&x, p1, 4);
-    memcpy(&y, p2, 4);
-    c = x < y ? -1 : (x > y);
-  } else if (a == 4) {
-    double x, y;
-    memcpy(&x, p1, 8);
-    memcpy(&y, p2, 8);
-    c = x < y ? -1 : (x > y);
-  } else if (a == 5)
-    c = strcmp(p1, p2);
-  else
-    c = strncmp(p1, p2, l1 < l2 ? l1 : l2);
-  return flag < 0 ? -c : c;
-}
-
 // A user compare function is host code: the pairs come to the host, are stably sorted (the reference's
 // qsort is a merge sort here) and go back.  by_value = 0 sorts by key, 1 by value.
-static int g_sort_flag = 0;
-static int cmp_flag_tramp(char *a, int la, char *b, int lb) { return cmp_builtin(g_sort_flag, a, la, b, lb); }
-
 uint64_t MapReduce::host_sort(int (*appcompare)(char *, int, char *, int), int by_value)
 {
   struct Rec {
@@ -806,9 +772,10 @@ uint64_t MapReduce::sort_values(int flag)
   if (kv == NULL) all("Cannot sort_values without KeyValue");
   int a = flag < 0 ? -flag : flag;
   if (a < 1 || a > 6) all("Invalid compare method for sort values");
-  g_sort_flag = flag;
   start_timer();
-  uint64_t n = host_sort(cmp_flag_tramp, 1);
+  uint64_t n = 0;
+  ck(mrgpu_sort_values(gpu, flag, &n), 0);
+  sync_kv_fields();
   stats("Sort_values", 0);
   return n;
 }
@@ -831,9 +798,12 @@ uint64_t MapReduce::gather(int numprocs)
 {
   if (kv == NULL) all("Cannot gather without KeyValue");
   if (numprocs < 1 || numprocs > nprocs) all("Invalid processor count for gather");
-  if (nprocs == 1 || numprocs == nprocs) return kv_stats(0);
-  all("gather() across ranks is not built in the GPU library (SURVEY.md 8f)");
-  return 0;
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_gather(gpu, numprocs, &n), 0);
+  sync_kv_fields();
+  stats("Gather", 0);
+  return n;
 }
 
 MapReduce *MapReduce::copy()

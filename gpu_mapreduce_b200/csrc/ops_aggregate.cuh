@@ -590,3 +590,118 @@ extern "C" int mrgpu_collate(mrgpu_mr *mr, uint64_t *nkmv)
   if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
   API_END(mr)
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// gather(numprocs)   src/mapreduce.cpp:893-1036
+// Ranks >= numprocs hand their whole KV to rank (me % numprocs) and end up with an empty one; a receiver appends
+// what it gets to its own pairs, senders in ascending rank order (me+numprocs, me+2*numprocs, ...), each
+// sender's pairs in their order.  The reference moves page by page with a handshake per INTMAX chunk; here
+// every rank learns all sizes from one all-gather and the payload moves in one grouped send/recv.
+static void gather_impl(mrgpu_mr *mr, int numprocs)
+{
+  freeze(mr);
+  const int P = mr->nranks, me = mr->rank;
+  if (P == 1 || numprocs == P) return;  // :905-910
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  ncclComm_t comm = (ncclComm_t) mr->comm;
+  DevKV *kv = mr->kv;
+  kv_unpack(mr, kv);
+  // every rank's {pairs, bytes, kind 0 empty / 1 variable / 2 uniform, keybytes<<32|valuebytes, keysize, valuesize}
+  constexpr int W = 6;
+  unsigned long long mine[W] = {kv->nkv, kv->nbytes, kv->nkv == 0 ? 0ull : (kv->uniform ? 2ull : 1ull),
+                                kv->uniform ? (((unsigned long long) kv->kb << 32) | kv->vb) : 0ull, kv->ksize, kv->vsize};
+  std::vector<unsigned long long> all((size_t) W * P);
+  {
+    Buf<unsigned long long> dm(pool, W), da(pool, (uint64_t) W * P);
+    MR_CUDA(cudaMemcpyAsync(dm.p, mine, W * 8, cudaMemcpyHostToDevice, s));
+    MR_NCCL(nccl().AllGather(dm.p, da.p, W, ncclUint64, comm, s));
+    MR_CUDA(cudaMemcpyAsync(all.data(), da.p, (size_t) W * P * 8, cudaMemcpyDeviceToHost, s));
+    sync(mr);
+  }
+  auto row = [&](int q) { return &all[(size_t) q * W]; };
+  if (me >= numprocs) {
+    const int dest = me % numprocs;
+    if (kv->nkv) {
+      MR_NCCL(nccl().GroupStart());
+      MR_NCCL(nccl().Send(kv->data, kv->nbytes, ncclInt8, dest, comm, s));
+      if (!kv->uniform) MR_NCCL(nccl().Send(kv->offs, kv->nkv + 1, ncclUint64, dest, comm, s));
+      MR_NCCL(nccl().GroupEnd());
+      sync(mr);
+    }
+    delete mr->kv;  // :1021-1022: the sender starts over with an empty KV
+    mr->kv = new DevKV(&pool);
+    return;
+  }
+  // receiver: what arrives, and whether the result can stay a uniform KV
+  uint64_t add_n = 0, add_b = 0, add_k = 0, add_v = 0;
+  bool uniform = kv->nkv == 0 || kv->uniform;
+  unsigned long long shape = kv->nkv ? mine[3] : 0;
+  bool have_shape = kv->nkv != 0;
+  for (int q = me + numprocs; q < P; q += numprocs) {
+    const unsigned long long *r = row(q);
+    if (!r[0]) continue;
+    add_n += r[0], add_b += r[1], add_k += r[4], add_v += r[5];
+    if (r[2] != 2) uniform = false;
+    else if (have_shape && r[3] != shape) uniform = false;
+    else shape = r[3], have_shape = true;
+  }
+  if (!add_n) return;
+  if (kv->nkv + add_n >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "gather: a rank would hold more than 2^32-2 pairs");
+  if (uniform) {
+    kv->uniform = true;
+    kv->kb = (uint32_t) (shape >> 32);
+    kv->vb = (uint32_t) shape;
+    kv->recsize = kv_rec_size(mr->al, kv->kb, kv->vb);
+  } else {
+    kv_make_general(mr, kv);
+    kv->reserve_offs(kv->nkv + add_n + 1);
+  }
+  kv->reserve_bytes(kv->nbytes + add_b);
+  std::vector<Buf<uint64_t>> roffs;  // offsets of the variable-length senders, as they index their own stream
+  MR_NCCL(nccl().GroupStart());
+  uint64_t at_b = kv->nbytes;
+  for (int q = me + numprocs; q < P; q += numprocs) {
+    const unsigned long long *r = row(q);
+    if (!r[0]) continue;
+    MR_NCCL(nccl().Recv(kv->data + at_b, r[1], ncclInt8, q, comm, s));
+    if (r[2] == 1) {
+      roffs.emplace_back(pool, r[0] + 1);
+      MR_NCCL(nccl().Recv(roffs.back().p, r[0] + 1, ncclUint64, q, comm, s));
+    }
+    at_b += r[1];
+  }
+  MR_NCCL(nccl().GroupEnd());
+  if (!uniform) {
+    uint64_t at_n = kv->nkv;
+    at_b = kv->nbytes;
+    size_t vi = 0;
+    for (int q = me + numprocs; q < P; q += numprocs) {
+      const unsigned long long *r = row(q);
+      if (!r[0]) continue;
+      const uint64_t cnt = r[0] + 1;
+      if (r[2] == 1) shift_offsets_kernel<<<(unsigned) ((cnt + 255) / 256), 256, 0, s>>>(kv->offs + at_n, roffs[vi++].p, cnt, at_b);
+      else affine_offsets_kernel<<<(unsigned) ((cnt + 255) / 256), 256, 0, s>>>(kv->offs + at_n, cnt, at_b, kv_rec_size(mr->al, (uint32_t) (r[3] >> 32), (uint32_t) r[3]));
+      MR_CUDA(cudaGetLastError());
+      at_n += r[0];
+      at_b += r[1];
+    }
+  }
+  kv->nkv += add_n;
+  kv->nbytes += add_b;
+  kv->ksize += add_k;
+  kv->vsize += add_v;
+  kv->h_offs_valid = false;
+  sync(mr);
+}
+
+extern "C" int mrgpu_gather(mrgpu_mr *mr, int numprocs, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot gather without KeyValue");
+  if (numprocs < 1 || numprocs > mr->nranks) MR_FAIL(MRGPU_EINVAL, "Invalid processor count for gather");
+  if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  gather_impl(mr, numprocs);
+  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  API_END(mr)
+}

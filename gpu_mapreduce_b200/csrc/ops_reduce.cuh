@@ -184,3 +184,16 @@ extern "C" int mrgpu_reduce(mrgpu_mr *mr, int functor, uint64_t *nkv)
   if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
   API_END(mr)
 }
+
+// compress(): convert + reduce on this rank's own pairs, no exchange (src/mapreduce.cpp:749-851) -- the local
+// combiner a caller runs before aggregate() to shrink what crosses the fabric
+extern "C" int mrgpu_compress(mrgpu_mr *mr, int functor, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot compress without KeyValue");
+  if (functor < 0 || functor > MRGPU_REDUCE_CULL) MR_FAIL(MRGPU_EINVAL, "unknown reduce functor");
+  convert_impl(mr);
+  reduce_impl(mr, functor);
+  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  API_END(mr)
+}

@@ -57,14 +57,19 @@ template <typename K>
 __global__ void __launch_bounds__(256)
 sortkey_extract_kernel(const uint8_t *__restrict__ data, const uint64_t *__restrict__ offs, uint64_t rs, uint64_t n, Align al, int absflag,
                        bool reverse, uint32_t chunk, const uint32_t *__restrict__ perm_in, K *__restrict__ keys, uint32_t *__restrict__ perm,
-                       unsigned *bad)
+                       unsigned *bad, bool by_value)
 {
   uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint32_t rec = perm_in ? perm_in[i] : (uint32_t) i;
   const uint8_t *r = data + rec_off(offs, rs, rec);
+  // the compared field: the key, or (sort_values) the value -- from here on "k, kb" is that field
   uint32_t kb = *(const uint32_t *) r;
   const uint8_t *k = r + kv_key_off(al);
+  if (by_value) {
+    k = r + kv_val_off(al, kb);
+    kb = ((const uint32_t *) r)[1];
+  }
   uint64_t v = 0;
   uint32_t need = (absflag == 1 || absflag == 3) ? 4 : ((absflag == 2 || absflag == 4) ? 8 : 0);
   if (kb < need) {
@@ -108,12 +113,12 @@ gather_general_kernel(const uint8_t *__restrict__ src, const uint64_t *__restric
   for (uint64_t q = 0; q < sz / 4; q++) d[q] = s[q];
 }
 
-__global__ void max_keybytes_kernel(const uint8_t *__restrict__ data, const uint64_t *__restrict__ offs, uint64_t n, unsigned long long *mx)
+__global__ void max_keybytes_kernel(const uint8_t *__restrict__ data, const uint64_t *__restrict__ offs, uint64_t n, unsigned long long *mx, int word)
 {
   unsigned long long m = 0;
   uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
   for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-    m = max(m, (unsigned long long) *(const uint32_t *) (data + offs[i]));
+    m = max(m, (unsigned long long) ((const uint32_t *) (data + offs[i]))[word]);  // word 0: keybytes, 1: valuebytes
   for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
   if ((threadIdx.x & 31) == 0 && m) atomicMax(mx, m);
 }
@@ -131,7 +136,7 @@ __global__ void __launch_bounds__(256) sortkey_descents_kernel(const K *__restri
 
 // returns false when the pairs already are in sorted order (perm_out untouched)
 template <typename K>
-static bool sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nchunks, Buf<uint32_t> &perm_out)
+static bool sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nchunks, Buf<uint32_t> &perm_out, bool by_value)
 {
   DevKV *kv = mr->kv;
   Pool &pool = mr->pool;
@@ -153,7 +158,7 @@ static bool sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nc
     {
     ProfScope ps(pool, "sort_extract", (double) n * (8 + sizeof(K) + 4));
     sortkey_extract_kernel<K><<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(kv->data, kv->uniform ? nullptr : kv->offs, kv->recsize, n, mr->al,
-                                                                         absflag, reverse, (uint32_t) c, perm_in, kb[w], pb[w], bad);
+                                                                         absflag, reverse, (uint32_t) c, perm_in, kb[w], pb[w], bad, by_value);
     MR_CUDA(cudaGetLastError());
     }
     if (nchunks == 1) {
@@ -167,7 +172,7 @@ static bool sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nc
         MR_CUDA(cudaGetLastError());
       }
       fetch_small(mr, 3);
-      if (mr->h_small[1] & 0xFFFFFFFFull) MR_FAIL(MRGPU_EINVAL, "sort_keys: key shorter than the compared type");
+      if (mr->h_small[1] & 0xFFFFFFFFull) MR_FAIL(MRGPU_EINVAL, by_value ? "sort_values: value shorter than the compared type" : "sort_keys: key shorter than the compared type");
       if (mr->h_small[2] == 0) return false;
     }
     int r = radix_sort_pairs<K, uint32_t, true>(pool, kb[w], kb[w ^ 1], pb[w], pb[w ^ 1], n, 0xFF, false, hist.p);
@@ -176,17 +181,17 @@ static bool sort_keys_typed(mrgpu_mr *mr, int absflag, bool reverse, uint32_t nc
     w = res ^ 1;
   }
   fetch_small(mr, 2);
-  if (mr->h_small[1] & 0xFFFFFFFFull) MR_FAIL(MRGPU_EINVAL, "sort_keys: key shorter than the compared type");
+  if (mr->h_small[1] & 0xFFFFFFFFull) MR_FAIL(MRGPU_EINVAL, by_value ? "sort_values: value shorter than the compared type" : "sort_keys: key shorter than the compared type");
   // hand the permutation buffer to the caller
   if (perm_in == p0.p) perm_out = static_cast<Buf<uint32_t> &&>(p0);
   else perm_out = static_cast<Buf<uint32_t> &&>(p1);
   return true;
 }
 
-static void sort_keys_impl(mrgpu_mr *mr, int flag)
+static void sort_keys_impl(mrgpu_mr *mr, int flag, bool by_value = false)
 {
   int absflag = flag < 0 ? -flag : flag;
-  if (absflag < 1 || absflag > 6) MR_FAIL(MRGPU_EINVAL, "Invalid compare method for sort keys");
+  if (absflag < 1 || absflag > 6) MR_FAIL(MRGPU_EINVAL, by_value ? "Invalid compare method for sort values" : "Invalid compare method for sort keys");
   DevKV *kv = mr->kv;
   Pool &pool = mr->pool;
   cudaStream_t s = pool.stream;
@@ -195,11 +200,11 @@ static void sort_keys_impl(mrgpu_mr *mr, int flag)
   if (n < 2) return;
   uint32_t nchunks = 1;
   if (absflag >= 5) {
-    uint64_t maxkb = kv->kb;
+    uint64_t maxkb = by_value ? kv->vb : kv->kb;
     if (!kv->uniform) {
       unsigned long long *mx = mr->d_small;
       MR_CUDA(cudaMemsetAsync(mx, 0, 8, s));
-      max_keybytes_kernel<<<grid_for(n, 256, 8), 256, 0, s>>>(kv->data, kv->offs, n, mx);
+      max_keybytes_kernel<<<grid_for(n, 256, 8), 256, 0, s>>>(kv->data, kv->offs, n, mx, by_value ? 1 : 0);
       MR_CUDA(cudaGetLastError());
       fetch_small(mr, 1);
       maxkb = mr->h_small[0];
@@ -208,8 +213,8 @@ static void sort_keys_impl(mrgpu_mr *mr, int flag)
   }
   Buf<uint32_t> perm;
   bool moved;
-  if (absflag == 1 || absflag == 3) moved = sort_keys_typed<uint32_t>(mr, absflag, flag < 0, 1, perm);
-  else moved = sort_keys_typed<uint64_t>(mr, absflag, flag < 0, nchunks, perm);
+  if (absflag == 1 || absflag == 3) moved = sort_keys_typed<uint32_t>(mr, absflag, flag < 0, 1, perm, by_value);
+  else moved = sort_keys_typed<uint64_t>(mr, absflag, flag < 0, nchunks, perm, by_value);
   if (!moved) return;
 
   // gather the records in sorted order into a new KV
@@ -258,6 +263,18 @@ extern "C" int mrgpu_sort_keys(mrgpu_mr *mr, int flag, uint64_t *nkv)
   freeze(mr);
   kv_unpack(mr, mr->kv);
   sort_keys_impl(mr, flag);
+  sync(mr);
+  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  API_END(mr)
+}
+
+extern "C" int mrgpu_sort_values(mrgpu_mr *mr, int flag, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot sort_values without KeyValue");
+  freeze(mr);
+  kv_unpack(mr, mr->kv);
+  sort_keys_impl(mr, flag, true);
   sync(mr);
   if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
   API_END(mr)

@@ -159,6 +159,14 @@ int mrgpu_reduce(mrgpu_mr *mr, int functor, uint64_t *nkv);
 /* MapReduce::sort_keys(int flag) src/mapreduce.cpp:2102-2128; flags +-1..+-6 select the compare functions of
  * src/mapreduce.cpp:2692-2802 */
 int mrgpu_sort_keys(mrgpu_mr *mr, int flag, uint64_t *nkv);
+/* MapReduce::sort_values(int flag) src/mapreduce.cpp:2156-2182: the same compare functions applied to the values */
+int mrgpu_sort_values(mrgpu_mr *mr, int flag, uint64_t *nkv);
+/* MapReduce::compress(mycompress, ptr) src/mapreduce.cpp:749-851 with a stock callback (MRGPU_REDUCE_*): convert +
+ * reduce on this rank's own pairs, no exchange; the KeyValue is replaced by one pair per distinct local key */
+int mrgpu_compress(mrgpu_mr *mr, int functor, uint64_t *nkv);
+/* MapReduce::gather(int numprocs) src/mapreduce.cpp:893-1036: ranks >= numprocs send their KeyValue to rank
+ * (me % numprocs), which appends the senders' pairs in ascending rank order; senders are left with an empty KeyValue */
+int mrgpu_gather(mrgpu_mr *mr, int numprocs, uint64_t *nkv);
 
 /* ---- stats and page access (scan, host callbacks, printing) --------------------------------------- */
 

@@ -172,6 +172,19 @@ int main(int narg, char **args)
   mr2->scan(collect_swapped, NULL);
   lines.resize(10);
   dump("top 10 by count", false);
+  // 3b. sort_values(flag) + gather: back to word order through the values (strcmp), everything on rank 0
+  mr2->sort_values(5);
+  mr2->gather(1);
+  mr2->scan(collect_swapped, NULL);
+  dump("sorted by value", false);
+  // 3c. compress with a host callback: local convert + reduce in one call
+  MapReduce *mr3 = new MapReduce(MPI_COMM_WORLD);
+  mr3->map(3, gen, &n);
+  uint64_t ncomp = mr3->compress(sumvals, mr3);
+  printf("compressed %lu\n", (unsigned long) ncomp);
+  mr3->scan(collect_str, NULL);
+  dump("compress: key count sum", true);
+  delete mr3;
   delete mr2;
   delete mr;
 

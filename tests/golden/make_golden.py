@@ -184,6 +184,18 @@ def main():
         for sgn in (1, -1):
             G[f"sort{fl}.out{'p' if sgn > 0 else 'm'}"] = b2a(H.ref_ops(kv, [f"sort_keys:{sgn * fl}", "dumpkv"]))
 
+    # 11. sort_values flags +-1..+-6 (src/mapreduce.cpp:2156-2182): the records of 10 with key and value swapped
+    for fl, recs in srt.items():
+        kv = H.kv_encode([(v, k) for k, v in recs])
+        G[f"sortv{fl}.in"] = b2a(kv)
+        for sgn in (1, -1):
+            G[f"sortv{fl}.out{'p' if sgn > 0 else 'm'}"] = b2a(H.ref_ops(kv, [f"sort_values:{sgn * fl}", "dumpkv"]))
+
+    # 12. compress = local convert + reduce in one call (src/mapreduce.cpp:749-851), on the data of 4
+    kv4 = G["convert.in"].tobytes()
+    for cb in ("count", "sum", "cull"):
+        G[f"compress.{cb}"] = b2a(H.ref_ops(kv4, [f"compress_{cb}", "dumpkv"]))
+
     np.savez_compressed(os.path.join(HERE, "golden.npz"), **G)
     with open(os.path.join(HERE, "manifest.json"), "w") as f:
         json.dump(M, f, indent=0)

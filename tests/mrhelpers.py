@@ -166,6 +166,16 @@ class Oracle:
     def sort_keys(self, kv: bytes, flag: int) -> bytes:
         return _call_out(self.lib.orc_sort_keys, kv, flag)
 
+    def sort_values(self, kv: bytes, flag: int) -> bytes:
+        """src/mapreduce.cpp:2156-2182: the compare functions of sort_keys applied to the value; the sort is the same
+        stable one, so it is sort_keys on the pairs with key and value swapped, swapped back"""
+        swapped = self.sort_keys(kv_encode([(v, k) for k, v in kv_decode(kv)]), flag)
+        return kv_encode([(k, v) for v, k in kv_decode(swapped)])
+
+    def compress(self, kv: bytes, which: str) -> bytes:
+        """src/mapreduce.cpp:749-851: KeyMultiValue::convert of the local pairs, then the callback per distinct key"""
+        return self.reduce(self.convert(kv), which)
+
     def edge_to_vertices(self, kv: bytes, both=True) -> bytes:
         return _call_out(self.lib.orc_map_edge_to_vertices, kv, 1 if both else 0)
 

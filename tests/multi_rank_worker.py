@@ -87,6 +87,22 @@ def main_nccl():
                     assert orc.hashlittle(k, world) % world == q
         mr.destroy()
 
+    # gather(numprocs), src/mapreduce.cpp:893-1036: rank r < numprocs ends with its own pairs followed by those of
+    # ranks r+numprocs, r+2*numprocs, ... ; the others end empty
+    for case in range(4):
+        for numprocs in sorted({1, max(1, world - 1), world}):
+            mr = g.MapReduce(device=local, rank=rank, nranks=world, unique_id=uid)
+            total = sum(len(shard_records(case, q)) for q in range(world))
+            assert mr.kv_add(shard_records(case, rank)) == total
+            assert mr.gather(numprocs) == total
+            want = [rec for q in range(rank, world, numprocs) for rec in shard_records(case, q)] if rank < numprocs else []
+            assert mr.scan_kv() == want, f"gather({numprocs}) case {case}: wrong pairs on rank {rank}"
+            st = mr.kv_stats()
+            assert st.npair == len(want) and st.keysize == sum(len(k) for k, _ in want)
+            mr.sort_keys(5)                    # the gathered KV is a working KV (collective: every rank calls)
+            assert H.canon_kv(mr.scan_kv()) == H.canon_kv(want)
+            mr.destroy()
+
     # IntCount through map_intcount: header-less rows cross the wire when every rank holds them; with one rank
     # set to compact=0 (or one rank empty / holding another shape) the ranks must agree on records instead
     def ic_keys(q, variant):

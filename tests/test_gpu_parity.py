@@ -523,6 +523,37 @@ def test_headerless_kv_meets_other_shapes(MR, oracle):
 # ------------------------------------------------------------------------------------------- sort_keys
 
 @pytest.mark.parametrize("flag", [1, 2, 3, 4, 5, 6])
+def test_sort_values_flags_golden(MR, golden, flag):
+    """sort_values(flag) against pages recorded from the reference (tests/golden section 11)"""
+    for sgn, tag in ((1, "p"), (-1, "m")):
+        mr = MR()
+        _load(mr, golden[f"sortv{flag}.in"])
+        n = mr.sort_values(sgn * flag)
+        assert n == len(H.kv_decode(golden[f"sortv{flag}.in"]))
+        assert H.kv_encode(mr.scan_kv()) == golden[f"sortv{flag}.out{tag}"]
+
+
+@pytest.mark.parametrize("cb", ["count", "sum", "cull"])
+def test_compress_golden(MR, golden, cb):
+    """compress = local convert + reduce (src/mapreduce.cpp:749-851), against the reference's output"""
+    mr = MR()
+    _load(mr, golden["convert.in"])
+    want = H.kv_decode(golden[f"compress.{cb}"])
+    assert mr.compress(cb) == len(want)
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(want)
+    with pytest.raises(Exception, match="Cannot compress without KeyValue"):
+        mr2 = MR()
+        mr2.compress(cb)
+    big = MR()                                         # the counting path under compress
+    keys = W.intcount_keys_np(0, 100_000, ndistinct=700, seed=3)
+    big.map_intcount(keys)
+    assert big.compress("count") == len(np.unique(keys))
+    u, c = np.unique(keys, return_counts=True)
+    assert sorted((struct.unpack("<I", k)[0], struct.unpack("<i", v)[0]) for k, v in big.scan_kv()) == list(zip(u.tolist(), c.tolist()))
+    assert big.gather(1) == len(u)                     # one rank: nothing moves (src/mapreduce.cpp:905-910)
+
+
+@pytest.mark.parametrize("flag", [1, 2, 3, 4, 5, 6])
 def test_sort_keys_flags_golden(MR, golden, flag):
     for sgn, name in ((1, "outp"), (-1, "outm")):
         mr = MR()

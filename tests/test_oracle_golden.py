@@ -147,3 +147,15 @@ def test_sort_keys_flags(golden, oracle, flag):
     kv = golden[f"sort{flag}.in"]
     assert oracle.sort_keys(kv, flag) == golden[f"sort{flag}.outp"]
     assert oracle.sort_keys(kv, -flag) == golden[f"sort{flag}.outm"]
+
+
+@pytest.mark.parametrize("flag", [1, 2, 3, 4, 5, 6])
+def test_sort_values_flags(golden, oracle, flag):
+    kv = golden[f"sortv{flag}.in"]
+    assert oracle.sort_values(kv, flag) == golden[f"sortv{flag}.outp"]
+    assert oracle.sort_values(kv, -flag) == golden[f"sortv{flag}.outm"]
+
+
+@pytest.mark.parametrize("cb", ["count", "sum", "cull"])
+def test_compress(golden, oracle, cb):
+    assert oracle.compress(golden["convert.in"], cb) == golden[f"compress.{cb}"]
