@@ -1,5 +1,5 @@
 """Microbenchmark (not a test): time convert()'s counting kernel on the IntCount key stream.
-   python tests/_densebench.py <log2n>   [MRGPU_LIB=<variant .so> for A/B runs]"""
+   python tools/densebench.py <log2n>   [MRGPU_LIB=<variant .so> for A/B runs]"""
 import sys, torch
 sys.path.insert(0, "/root/repo")
 from gpu_mapreduce_b200 import MapReduce, workloads
