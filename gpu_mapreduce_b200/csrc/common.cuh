@@ -335,6 +335,21 @@ __device__ __forceinline__ void st_stream(int4 *p, int4 v)
                : "memory");
 }
 
+// 32-byte streaming accesses (sm_100 has 256-bit global loads/stores) marked evict-first in L2: a stream that is
+// read or written once should not push out what the kernel keeps coming back to (convert's count table)
+__device__ __forceinline__ void ld_stream256(const void *p, uint32_t (&q)[8])
+{
+  asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3]), "=r"(q[4]), "=r"(q[5]), "=r"(q[6]), "=r"(q[7])
+               : "l"(p));
+}
+__device__ __forceinline__ void st_stream256(void *p, const uint32_t (&q)[8])
+{
+  asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(q[0]), "r"(q[1]), "r"(q[2]),
+               "r"(q[3]), "r"(q[4]), "r"(q[5]), "r"(q[6]), "r"(q[7])
+               : "memory");
+}
+
 inline unsigned grid_for(uint64_t work_items, unsigned per_block, unsigned max_waves = 32)
 {
   uint64_t b = (work_items + per_block - 1) / per_block;
