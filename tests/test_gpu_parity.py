@@ -533,6 +533,26 @@ def test_sort_values_flags_golden(MR, golden, flag):
         assert H.kv_encode(mr.scan_kv()) == golden[f"sortv{flag}.out{tag}"]
 
 
+def test_widened_ops_error_paths(MR):
+    import gpu_mapreduce_b200 as g
+
+    mr = MR()
+    for call, msg in ((lambda: mr.sort_values(1), "Cannot sort_values without KeyValue"),
+                      (lambda: mr.gather(1), "Cannot gather without KeyValue"),
+                      (lambda: mr.compress("count"), "Cannot compress without KeyValue")):
+        with pytest.raises(g.MRError, match=msg):
+            call()
+    mr.kv_add([(b"k", b"ab")])
+    with pytest.raises(g.MRError, match="Invalid compare method for sort values"):
+        mr.sort_values(7)
+    with pytest.raises(g.MRError, match="value shorter than the compared type"):
+        mr.sort_values(1)                                  # 2-byte values compared as int
+    with pytest.raises(g.MRError, match="Invalid processor count for gather"):
+        mr.gather(2)
+    assert mr.gather(1) == 1 and mr.scan_kv() == [(b"k", b"ab")]
+    assert mr.sort_values(5) == 1
+
+
 @pytest.mark.parametrize("cb", ["count", "sum", "cull"])
 def test_compress_golden(MR, golden, cb):
     """compress = local convert + reduce (src/mapreduce.cpp:749-851), against the reference's output"""
