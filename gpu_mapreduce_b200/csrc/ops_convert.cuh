@@ -19,6 +19,14 @@
 // Included by mrgpu.cu.
 #pragma once
 
+// f(i) for i in [0, n)
+template <typename F>
+__global__ void __launch_bounds__(256) for_each_kernel(uint64_t n, F f)
+{
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
+}
+
 struct CompactKey {
   int nvb;               // number of varying key bytes (<= 8)
   unsigned char pos[8];  // their positions inside the key
@@ -257,6 +265,58 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
     }, "convert_heads_compact", (double) n * sizeof(K) + 4.0 * U);
     uint32_t n32 = (uint32_t) n;
     MR_CUDA(cudaMemcpyAsync(start.p + U, &n32, 4, cudaMemcpyHostToDevice, s));
+  }
+
+  // 4'. pairs that cannot be told apart (no value, or the same value everywhere): the KMV is (key, count) per
+  //     distinct key -- the factored form (store.cuh); its record stream is written only if somebody reads it
+  if (mr->compact && (PMODE == 0 || constval) && kb % 4 == 0 && kb > 0 && (vb == 0 || vb == 4 || vb == 8) && al.k % 4 == 0 && al.v % 4 == 0) {
+    DevKMV *kmv = new DevKMV(&pool);
+    try {
+      const uint32_t kw = kb / 4;
+      kmv->fkw = kw;
+      kmv->fkey = (uint32_t *) pool.alloc((U ? U : 1) * 4 * kw);
+      kmv->fcnt = (uint32_t *) pool.alloc((U ? U : 1) * 4);
+      kmv->fcap = U ? U : 1;
+      Buf<uint32_t> dkey0(pool, kw);
+      if (!ident) MR_CUDA(cudaMemcpyAsync(dkey0.p, key0.data(), kb, cudaMemcpyHostToDevice, s));
+      const uint8_t *k0b = (const uint8_t *) dkey0.p;
+      uint8_t *fk = (uint8_t *) kmv->fkey;
+      uint32_t *fc = kmv->fcnt;
+      const uint32_t *st = start.p;
+      {
+        ProfScope ps(pool, "convert_factored", (double) U * (sizeof(K) + 8 + kb));
+        const CompactKey ckc = ck;
+        auto mk = [=] __device__(uint64_t u) {
+          const uint32_t s0 = st[u];
+          fc[u] = st[u + 1] - s0;
+          const unsigned long long key = (unsigned long long) sk[s0];
+          uint8_t *d = fk + u * kb;
+          if (ident) {
+            for (uint32_t q = 0; q < kb; q++) d[q] = (uint8_t) (key >> (8 * q));
+          } else {
+            for (uint32_t q = 0; q < kb; q++) d[q] = k0b[q];
+            for (int q = 0; q < ckc.nvb; q++) d[ckc.pos[q]] = (uint8_t) (key >> (8 * q));
+          }
+        };
+        for_each_kernel<<<grid_for(U, 256, 64), 256, 0, s>>>(U, mk);
+        MR_CUDA(cudaGetLastError());
+      }
+      kmv->factored = true;
+      kmv->fval[0] = (uint32_t) cval;
+      kmv->fval[1] = (uint32_t) (cval >> 32);
+      kmv->nkmv = U;
+      kmv->nvalue = n;
+      kmv->ksize = U * (uint64_t) kb;
+      kmv->vsize = kv->vsize;
+      kmv->ukb = kb;
+      kmv->uvb = vb;
+      sync(mr);
+    } catch (...) {
+      delete kmv;
+      throw;
+    }
+    mr->kmv = kmv;
+    return;
   }
 
   // 4. KMV record sizes -> offs[u]

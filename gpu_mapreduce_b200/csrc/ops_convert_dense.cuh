@@ -265,11 +265,11 @@ constexpr int FILL_MAX_PAIRS = FILL_CHUNK_WORDS / 4 + 2;               // a KMV 
 
 __global__ void __launch_bounds__(FILL_THREADS)
 dense_fill_kernel(uint32_t *__restrict__ out, uint64_t total_words, const uint64_t *__restrict__ offs, const uint32_t *__restrict__ ukey,
-                  const uint32_t *__restrict__ ucnt, uint64_t U, Align al, uint32_t kb, uint32_t vb, uint32_t cv0, uint32_t cv1,
+                  uint32_t kw, const uint32_t *__restrict__ ucnt, uint64_t U, Align al, uint32_t kb, uint32_t vb, uint32_t cv0, uint32_t cv1,
                   uint64_t chunks_per_block)
 {
   __shared__ uint64_t s_off[FILL_MAX_PAIRS + 1];
-  __shared__ uint32_t s_key[FILL_MAX_PAIRS], s_cnt[FILL_MAX_PAIRS];
+  __shared__ uint32_t s_cnt[FILL_MAX_PAIRS];
   __shared__ uint64_t s_u0;
   __shared__ int s_np;
   const uint64_t nchunks = (total_words + FILL_CHUNK_WORDS - 1) / FILL_CHUNK_WORDS;
@@ -301,10 +301,7 @@ dense_fill_kernel(uint32_t *__restrict__ out, uint64_t total_words, const uint64
       const uint64_t o = (q <= FILL_MAX_PAIRS && u <= U) ? offs[u] : ~0ull;
       if (q <= FILL_MAX_PAIRS) {
         s_off[q] = o;
-        if (q < FILL_MAX_PAIRS && u < U) {
-          s_key[q] = ukey[u];
-          s_cnt[q] = ucnt[u];
-        }
+        if (q < FILL_MAX_PAIRS && u < U) s_cnt[q] = ucnt[u];
       }
       const int c = __syncthreads_count(o < b1);
       np_acc += c;
@@ -328,7 +325,6 @@ dense_fill_kernel(uint32_t *__restrict__ out, uint64_t total_words, const uint64
       }
       uint64_t pbase = s_off[lo], pnext = s_off[lo + 1];
       uint64_t nv = s_cnt[lo], ko = kmv_key_off(al, nv), vo = kmv_val_off(al, nv, kb);
-      uint32_t pkey = s_key[lo];
       uint32_t wbuf[FILL_WORDS_PER_THREAD];
       // most of the stream is the inside of a long pair's size array or value array: 64 bytes of one constant
       const uint64_t sb = wfirst * 4, se = sb + 4 * FILL_WORDS_PER_THREAD, r0 = sb - pbase;
@@ -353,7 +349,6 @@ dense_fill_kernel(uint32_t *__restrict__ out, uint64_t total_words, const uint64
           nv = s_cnt[lo];
           ko = kmv_key_off(al, nv);
           vo = kmv_val_off(al, nv, kb);
-          pkey = s_key[lo];
         }
         const uint64_t r = b - pbase;
         uint32_t word = 0;
@@ -362,7 +357,7 @@ dense_fill_kernel(uint32_t *__restrict__ out, uint64_t total_words, const uint64
         else if (r == 0) word = (uint32_t) nv;
         else if (r == 4) word = kb;
         else if (r == 8) word = (uint32_t) (nv * vb);
-        else if (r == ko) word = pkey;  // 8-byte keys: the high word is 0 on this path
+        else if (r >= ko && r < ko + kb) word = __ldg(ukey + (u0 + lo) * kw + (uint32_t) ((r - ko) >> 2));
         wbuf[k] = word;
       }
       if (wfirst + FILL_WORDS_PER_THREAD <= total_words && (((uintptr_t) (out + wfirst)) & 15) == 0) {
@@ -412,12 +407,12 @@ static void kmv_expand(mrgpu_mr *mr, DevKMV *kmv)
     const uint64_t nchunks = (words + FILL_CHUNK_WORDS - 1) / FILL_CHUNK_WORDS;
     const uint64_t nblk = std::min<uint64_t>(nchunks, (uint64_t) kSMs * 16);
     const uint64_t cpb = (nchunks + nblk - 1) / nblk;
-    dense_fill_kernel<<<(unsigned) ((nchunks + cpb - 1) / cpb), FILL_THREADS, 0, s>>>((uint32_t *) kmv->data, words, offs, kmv->fkey, kmv->fcnt, U, al, kb, vb,
+    dense_fill_kernel<<<(unsigned) ((nchunks + cpb - 1) / cpb), FILL_THREADS, 0, s>>>((uint32_t *) kmv->data, words, offs, kmv->fkey, kmv->fkw, kmv->fcnt, U, al, kb, vb,
                                                                                      kmv->fval[0], kmv->fval[1], cpb);
     MR_CUDA(cudaGetLastError());
   }
   sync(mr);
-  pool.free(kmv->fkey, kmv->fcap * 4);
+  pool.free(kmv->fkey, kmv->fcap * 4 * kmv->fkw);
   pool.free(kmv->fcnt, kmv->fcap * 4);
   kmv->fkey = kmv->fcnt = nullptr;
   kmv->fcap = 0;
@@ -634,13 +629,16 @@ static bool convert_dense(mrgpu_mr *mr)
   const uint64_t U = mr->h_small[0];
   DevKMV *kmv = new DevKMV(&pool);
   try {
-    kmv->fkey = (uint32_t *) pool.alloc((U ? U : 1) * 4);
+    const uint32_t kw = kb / 4;
+    kmv->fkw = kw;
+    kmv->fkey = (uint32_t *) pool.alloc((U ? U : 1) * 4 * kw);
     kmv->fcnt = (uint32_t *) pool.alloc((U ? U : 1) * 4);
     kmv->fcap = U ? U : 1;
     uint32_t *pk = kmv->fkey, *pc = kmv->fcnt;
     flag_sink(pool, bins, nonzero, [=] __device__(uint64_t k, unsigned long long e, unsigned long long h) {
       if (h) {
-        pk[e] = (uint32_t) k;
+        pk[e * kw] = (uint32_t) k;
+        if (kw == 2) pk[e * 2 + 1] = 0;  // 8-byte keys on this path have a zero high word
         pc[e] = tb[k];
         tb[k] = 0;
       }

@@ -68,15 +68,37 @@ reduce_factored16_kernel(const uint32_t *__restrict__ fkey, const uint32_t *__re
   st_stream(out + u, make_int4(4, 4, (int) __ldg(fkey + u), (int) __ldg(fcnt + u)));
 }
 
+// default alignment (record = 8 + kb + vb, all words): one thread per output word, coalesced both ways
+__global__ void __launch_bounds__(256)
+reduce_factored_words_kernel(const uint32_t *__restrict__ fkey, const uint32_t *__restrict__ fcnt, uint64_t U, int functor, uint32_t kw, uint32_t vw,
+                             uint32_t cv0, uint32_t cv1, uint32_t *__restrict__ out)
+{
+  // count / sum emit (key, int count); cull emits (key, the shared value)
+  const uint32_t ow = functor == MRGPU_REDUCE_CULL ? vw : 1, rw = 2 + kw + ow;
+  const uint64_t total = U * rw, stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t t = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
+    const uint64_t u = t / rw;
+    const uint32_t w = (uint32_t) (t - u * rw);
+    uint32_t x;
+    if (w == 0) x = kw * 4;
+    else if (w == 1) x = ow * 4;
+    else if (w < 2 + kw) x = __ldg(fkey + u * kw + (w - 2));
+    else if (functor == MRGPU_REDUCE_CULL) x = (w - 2 - kw) ? cv1 : cv0;
+    else x = __ldg(fcnt + u);
+    out[t] = x;
+  }
+}
+
 __global__ void __launch_bounds__(256)
 reduce_factored_kernel(const uint32_t *__restrict__ fkey, const uint32_t *__restrict__ fcnt, uint64_t U, int functor, Align al, uint32_t kb,
                        uint32_t vb, uint32_t cv0, uint32_t cv1, uint8_t *out, uint64_t ors)
 {
   uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= U) return;
-  const uint32_t key[2] = {fkey[u], 0}, cnt = fcnt[u], cv[2] = {cv0, cv1};
-  if (functor == MRGPU_REDUCE_CULL) write_kv_record(out + u * ors, al, kb, (const uint8_t *) key, vb, (const uint8_t *) cv);
-  else write_kv_record(out + u * ors, al, kb, (const uint8_t *) key, 4, (const uint8_t *) &cnt);
+  const uint8_t *key = (const uint8_t *) (fkey + u * (kb / 4));
+  const uint32_t cnt = fcnt[u], cv[2] = {cv0, cv1};
+  if (functor == MRGPU_REDUCE_CULL) write_kv_record(out + u * ors, al, kb, key, vb, (const uint8_t *) cv);
+  else write_kv_record(out + u * ors, al, kb, key, 4, (const uint8_t *) &cnt);
 }
 
 __global__ void __launch_bounds__(256)
@@ -119,6 +141,9 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
       if (kmv->factored) {
         if (!cull && kb == 4 && rs == 16 && kv_key_off(al) == 8 && al.k == 4)
           reduce_factored16_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kmv->fkey, kmv->fcnt, U, (int4 *) kv->data);
+        else if (al.k == 4 && al.v == 4 && rs == 8 + kb + vb)
+          reduce_factored_words_kernel<<<grid_for(U * (rs / 4), 256, 64), 256, 0, s>>>(kmv->fkey, kmv->fcnt, U, functor, kb / 4, (uint32_t) kmv->uvb / 4,
+                                                                                      kmv->fval[0], kmv->fval[1], (uint32_t *) kv->data);
         else
           reduce_factored_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kmv->fkey, kmv->fcnt, U, functor, al, kb, (uint32_t) kmv->uvb,
                                                                               kmv->fval[0], kmv->fval[1], kv->data, rs);

@@ -41,11 +41,11 @@ static void kv_append_var_reserve(mrgpu_mr *mr, DevKV *kv, const VarAppend &va, 
 
 __device__ __forceinline__ bool tok_ws(uint8_t c) { return c == ' ' || c == '\t' || c == '\n' || c == '\f' || c == '\r'; }
 
-__global__ void first_nul_kernel(const uint8_t *__restrict__ t, uint64_t n, unsigned long long *pos)
+__global__ void first_nul_kernel(const uint8_t *__restrict__ t, uint64_t first, uint64_t n, unsigned long long *pos)
 {
   uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
   unsigned long long best = ~0ull;
-  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+  for (uint64_t i = first + (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
     if (t[i] == 0) {
       best = i;
       break;
@@ -70,6 +70,201 @@ tokenize_write_kernel(const uint8_t *__restrict__ t, const uint32_t *__restrict_
   for (uint32_t q = ko + len; q < end; q++) r[q] = 0;  // the NUL and the padding
 }
 
+// ---- vectorised form (16 bytes of text per thread) ------------------------------------------------------
+// The per-byte scans above read one byte per scan element (25.6 GB/s of text on a B200).  Here a thread takes
+// 16 bytes, turns them into a 16-bit whitespace mask with SWAR compares, and word starts / ends are bit
+// operations on the masks:  start = ~ws & (ws << 1 | previous byte is ws),  end = ~ws & (ws >> 1 | next byte is ws).
+// A 4 KB chunk (one block iteration) reports how many words start in it and where its last start is; a small
+// scan turns that into each chunk's first word index and the start position carried in from the left (a word
+// may begin chunks earlier); a second pass pairs every END with its start and writes both positions.
+constexpr int TOKV_THREADS = 256;
+constexpr uint32_t TOKV_CHUNK = TOKV_THREADS * 16;
+
+// bit i set iff byte i of the 16 is one of " \t\n\f\r"; bytes at or after `end` count as whitespace
+__device__ __forceinline__ uint32_t tok_ws_mask16(const uint8_t *__restrict__ t, uint64_t p, uint64_t end)
+{
+  if (p >= end) return 0xFFFFu;
+  uint32_t w[4] = {0, 0, 0, 0};
+  if (end - p >= 16) {
+    const uint4 v = *reinterpret_cast<const uint4 *>(t + p);
+    w[0] = v.x, w[1] = v.y, w[2] = v.z, w[3] = v.w;
+  } else  // the last, partial vector: byte loads, never past the text
+    for (uint32_t i = 0; i < (uint32_t) (end - p); i++) w[i >> 2] |= (uint32_t) t[p + i] << (8 * (i & 3));
+  uint32_t m = 0;
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    // zero-byte tests on x ^ c for the five delimiters (exact form: the 7 low bits are tested without borrow,
+    // then the high bit)
+    uint32_t hit = 0;
+    const uint32_t delim[5] = {0x20202020u, 0x09090909u, 0x0A0A0A0Au, 0x0C0C0C0Cu, 0x0D0D0D0Du};
+#pragma unroll
+    for (int d = 0; d < 5; d++) {
+      const uint32_t x = w[q] ^ delim[d];
+      hit |= ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;  // 0x80 in every byte of x that is zero
+    }
+    // gather the four flag bits (bit 7 of each byte) into a nibble
+    m |= (((hit >> 7) * 0x00204081u) >> 21 & 0xFu) << (4 * q);
+  }
+  if (end - p < 16) m |= 0xFFFFu << (uint32_t) (end - p);
+  return m & 0xFFFFu;
+}
+
+__device__ __forceinline__ void tokv_masks(const uint8_t *__restrict__ t, uint64_t p, uint64_t end, uint32_t &S, uint32_t &E)
+{
+  const uint32_t m = tok_ws_mask16(t, p, end);
+  const uint32_t prev = (p == 0 || p > end) ? 1u : (tok_ws(t[p - 1]) ? 1u : 0u);
+  const uint32_t next = (p + 16 >= end) ? 1u : (tok_ws(t[p + 16]) ? 1u : 0u);
+  const uint32_t nm = ~m & 0xFFFFu;
+  S = nm & ((m << 1) | prev);
+  E = nm & ((m >> 1) | (next << 15));
+}
+
+// per chunk: words starting in it, and (position + 1) of its last start (0 = none)
+__global__ void __launch_bounds__(TOKV_THREADS)
+tokv_count_kernel(const uint8_t *__restrict__ t, uint64_t end, uint64_t nchunks, uint32_t *__restrict__ cnt, uint32_t *__restrict__ last)
+{
+  __shared__ uint32_t s_cnt[TOKV_THREADS / 32], s_last[TOKV_THREADS / 32];
+  for (uint64_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const uint64_t p = c * TOKV_CHUNK + (uint64_t) threadIdx.x * 16;
+    uint32_t S, E;
+    tokv_masks(t, p, end, S, E);
+    uint32_t n = __popc(S), l = S ? (uint32_t) p + (31 - __clz(S)) + 1 : 0;
+    n = __reduce_add_sync(0xFFFFFFFFu, n);
+    l = __reduce_max_sync(0xFFFFFFFFu, l);
+    if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = n, s_last[threadIdx.x >> 5] = l;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t a = 0, b = 0;
+      for (int w = 0; w < TOKV_THREADS / 32; w++) a += s_cnt[w], b = max(b, s_last[w]);
+      cnt[c] = a;
+      last[c] = b;
+    }
+    __syncthreads();
+  }
+}
+
+// one block: base[c] = words before chunk c, carry[c] = (position + 1) of the last start before chunk c
+__global__ void __launch_bounds__(1024)
+tokv_scan_kernel(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ last, uint64_t nchunks, uint32_t *__restrict__ base,
+                 uint32_t *__restrict__ carry, unsigned long long *total)
+{
+  __shared__ uint32_t ws[32], wm[32];
+  __shared__ uint32_t run_sum, run_max;
+  if (threadIdx.x == 0) run_sum = 0, run_max = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (uint64_t c0 = 0; c0 < nchunks; c0 += 1024) {
+    const uint64_t c = c0 + threadIdx.x;
+    const uint32_t v = c < nchunks ? cnt[c] : 0, l = c < nchunks ? last[c] : 0;
+    uint32_t is = v, im = l;  // inclusive scans inside the warp
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t a = __shfl_up_sync(0xFFFFFFFFu, is, o), b = __shfl_up_sync(0xFFFFFFFFu, im, o);
+      if (lane >= o) is += a, im = max(im, b);
+    }
+    if (lane == 31) ws[warp] = is, wm[warp] = im;
+    __syncthreads();
+    uint32_t ps = run_sum, pm = run_max;
+    for (int w = 0; w < warp; w++) ps += ws[w], pm = max(pm, wm[w]);
+    uint32_t em = __shfl_up_sync(0xFFFFFFFFu, im, 1);  // exclusive max inside the warp
+    if (lane == 0) em = 0;
+    if (c < nchunks) {
+      base[c] = ps + is - v;
+      carry[c] = max(pm, em);  // everything before this chunk
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) run_sum = ps + is, run_max = max(pm, im);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = run_sum;
+}
+
+// every END finds its word's index and start and writes (start, end) of that word
+__global__ void __launch_bounds__(TOKV_THREADS)
+tokv_pairs_kernel(const uint8_t *__restrict__ t, uint64_t end, uint64_t nchunks, const uint32_t *__restrict__ base,
+                  const uint32_t *__restrict__ carry, uint32_t *__restrict__ starts, uint32_t *__restrict__ ends)
+{
+  __shared__ uint32_t s_cnt[TOKV_THREADS / 32], s_last[TOKV_THREADS / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (uint64_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const uint64_t p = c * TOKV_CHUNK + (uint64_t) threadIdx.x * 16;
+    uint32_t S, E;
+    tokv_masks(t, p, end, S, E);
+    const uint32_t n = __popc(S), l = S ? (uint32_t) p + (31 - __clz(S)) + 1 : 0;
+    uint32_t is = n, im = l;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t a = __shfl_up_sync(0xFFFFFFFFu, is, o), b = __shfl_up_sync(0xFFFFFFFFu, im, o);
+      if (lane >= o) is += a, im = max(im, b);
+    }
+    if (lane == 31) s_cnt[warp] = is, s_last[warp] = im;
+    uint32_t em = __shfl_up_sync(0xFFFFFFFFu, im, 1);
+    if (lane == 0) em = 0;
+    __syncthreads();
+    uint32_t before = base[c], lastb = carry[c];  // starts / last start before this thread's 16 bytes
+    for (int w = 0; w < warp; w++) before += s_cnt[w], lastb = max(lastb, s_last[w]);
+    before += is - n;
+    lastb = max(lastb, em);
+    uint32_t e = E;
+    while (e) {
+      const int bit = __ffs(e) - 1;
+      e &= e - 1;
+      const uint32_t sle = S & ((2u << bit) - 1);  // starts at or before this end, inside the 16 bytes
+      const uint32_t w = before + __popc(sle) - 1;
+      starts[w] = sle ? (uint32_t) p + (31 - __clz(sle)) : lastb - 1;
+      ends[w] = (uint32_t) p + bit + 1;
+    }
+    __syncthreads();
+  }
+}
+
+// one thread per word, 4-byte stores; the key bytes come from two aligned 32-bit loads and a funnel shift
+__global__ void __launch_bounds__(256)
+tokv_write_kernel(const uint8_t *__restrict__ t, uint64_t tbytes, const uint32_t *__restrict__ starts, const uint32_t *__restrict__ ends, uint64_t nw,
+                  uint8_t *__restrict__ out, const uint64_t *__restrict__ offs, Align al)
+{
+  const uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nw) return;
+  const uint32_t s = starts[j], len = ends[j] - s, kb = len + 1;
+  uint32_t *r = reinterpret_cast<uint32_t *>(out + offs[j]);
+  const uint32_t ko = kv_key_off(al) / 4, nwords = kv_rec_size(al, kb, 0) / 4;
+  r[0] = kb;
+  r[1] = 0;
+  for (uint32_t q = 2; q < ko; q++) r[q] = 0;
+  const uint32_t *t32 = reinterpret_cast<const uint32_t *>(t);
+  const uint32_t sh = (s & 3) * 8;
+  const uint64_t safe = tbytes / 4;  // aligned words wholly inside the text buffer
+  for (uint32_t q = ko, b = 0; q < nwords; q++, b += 4) {
+    uint32_t word = 0;
+    if (b < len) {
+      const uint64_t a = ((uint64_t) s + b) >> 2;
+      if (a + 1 < safe) word = __funnelshift_r(t32[a], t32[a + 1], sh);
+      else  // the last bytes of the buffer: byte loads, never past the end
+        for (uint32_t i = 0; i < 4 && b + i < len; i++) word |= (uint32_t) t[(uint64_t) s + b + i] << (8 * i);
+      if (len - b < 4) word &= (1u << (8 * (len - b))) - 1;  // the NUL and the padding
+    }
+    r[q] = word;
+  }
+}
+
+// position of the first NUL, 16 bytes per load (t 16-byte aligned); the tail is left to first_nul_kernel
+__global__ void __launch_bounds__(256) first_nul16_kernel(const uint8_t *__restrict__ t, uint64_t nvec, unsigned long long *pos)
+{
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  unsigned long long best = ~0ull;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < nvec && best == ~0ull; i += stride) {
+    const uint4 v = *reinterpret_cast<const uint4 *>(t + i * 16);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int q = 3; q >= 0; q--) {
+      const uint32_t z = ~(((w[q] & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | w[q]) & 0x80808080u;  // 0x80 where a byte is zero
+      if (z) best = i * 16 + q * 4 + ((__ffs(z) - 1) >> 3);
+    }
+  }
+  for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+  if ((threadIdx.x & 31) == 0 && best != ~0ull) atomicMin(pos, best);
+}
+
 extern "C" int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbytes, int addflag, uint64_t *nkv)
 {
   API_BEGIN(mr)
@@ -86,22 +281,59 @@ extern "C" int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbyte
   if (nbytes) {
     unsigned long long *d = mr->d_small;
     MR_CUDA(cudaMemsetAsync(d, 0xFF, 8, s));
-    first_nul_kernel<<<grid_for(nbytes, 256 * 16, 8), 256, 0, s>>>(t, nbytes, d);
-    MR_CUDA(cudaGetLastError());
+    {
+      ProfScope ps(pool, "tok_first_nul", (double) nbytes, 2);
+      const uint64_t nvec = ((uintptr_t) t % 16) == 0 ? nbytes / 16 : 0;
+      if (nvec) first_nul16_kernel<<<grid_for(nvec, 256 * 4, 8), 256, 0, s>>>(t, nvec, d);
+      if (nbytes > nvec * 16) first_nul_kernel<<<grid_for(nbytes - nvec * 16, 256 * 16, 8), 256, 0, s>>>(t, nvec * 16, nbytes, d);
+      MR_CUDA(cudaGetLastError());
+    }
     fetch_small(mr, 1);
     const uint64_t end = std::min<uint64_t>(mr->h_small[0], nbytes);
+    // 16 bytes per thread when the text is 16-byte aligned (MRGPU_TOK_BYTEWISE=1 forces the per-byte form)
+    static const bool force_bytewise = getenv("MRGPU_TOK_BYTEWISE") && atoi(getenv("MRGPU_TOK_BYTEWISE"));
+    const bool vec = ((uintptr_t) t % 16) == 0 && !force_bytewise;
+    Buf<uint32_t> starts, ends;
     auto isstart = [=] __device__(uint64_t i) -> unsigned long long { return (!tok_ws(t[i]) && (i == 0 || tok_ws(t[i - 1]))) ? 1ull : 0ull; };
-    ScanTiles st;
-    scan_tiles(pool, end, isstart, st, mr->d_small);
-    fetch_small(mr, 1);
-    nwords = mr->h_small[0];
+    if (vec) {
+      const uint64_t nchunks = (end + TOKV_CHUNK - 1) / TOKV_CHUNK;
+      Buf<uint32_t> cnt(pool, nchunks), last(pool, nchunks), cbase(pool, nchunks), carry(pool, nchunks);
+      MR_CUDA(cudaMemsetAsync(mr->d_small, 0, 8, s));
+      if (nchunks) {
+        {
+          ProfScope ps(pool, "tok_count", (double) end, 2);
+          tokv_count_kernel<<<grid_for(nchunks, 1, 16), TOKV_THREADS, 0, s>>>(t, end, nchunks, cnt.p, last.p);
+          MR_CUDA(cudaGetLastError());
+          tokv_scan_kernel<<<1, 1024, 0, s>>>(cnt.p, last.p, nchunks, cbase.p, carry.p, mr->d_small);
+          MR_CUDA(cudaGetLastError());
+        }
+        fetch_small(mr, 1);
+        nwords = mr->h_small[0];
+        if (nwords) {
+          starts.alloc(pool, nwords);
+          ends.alloc(pool, nwords);
+          ProfScope ps(pool, "tok_pairs", (double) end + 8.0 * nwords);
+          tokv_pairs_kernel<<<grid_for(nchunks, 1, 16), TOKV_THREADS, 0, s>>>(t, end, nchunks, cbase.p, carry.p, starts.p, ends.p);
+          MR_CUDA(cudaGetLastError());
+        }
+      }
+    } else {
+      ScanTiles st;
+      scan_tiles(pool, end, isstart, st, mr->d_small);
+      fetch_small(mr, 1);
+      nwords = mr->h_small[0];
+      if (nwords) {
+        starts.alloc(pool, nwords);
+        ends.alloc(pool, nwords);
+        uint32_t *ps = starts.p, *pe = ends.p;
+        scan_sink(pool, st, isstart, [=] __device__(uint64_t i, unsigned long long e, unsigned long long v) {
+          if (v) ps[e] = (uint32_t) i;
+          if (!tok_ws(t[i]) && (i + 1 == end || tok_ws(t[i + 1]))) pe[e + v - 1] = (uint32_t) (i + 1);
+        });
+      }
+    }
     if (nwords) {
-      Buf<uint32_t> starts(pool, nwords), ends(pool, nwords);
       uint32_t *ps = starts.p, *pe = ends.p;
-      scan_sink(pool, st, isstart, [=] __device__(uint64_t i, unsigned long long e, unsigned long long v) {
-        if (v) ps[e] = (uint32_t) i;
-        if (!tok_ws(t[i]) && (i + 1 == end || tok_ws(t[i + 1]))) pe[e + v - 1] = (uint32_t) (i + 1);
-      });
       VarAppend va = kv_append_var_begin(mr, kv, nwords);
       uint64_t *oo = va.offs;
       uint64_t base = va.base;
@@ -113,12 +345,16 @@ extern "C" int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbyte
             oo[j] = base + e;
             warp_add(ksum, (unsigned long long) (pe[j] - ps[j] + 1));
           },
-          mr->d_small);
+          mr->d_small, "tok_sizes", 16.0 * nwords);
       fetch_small(mr, 2);
       uint64_t total = mr->h_small[0], ksize = mr->h_small[1];
       kv_append_var_reserve(mr, kv, va, nwords, total);
-      tokenize_write_kernel<<<(unsigned) ((nwords + 255) / 256), 256, 0, s>>>(t, ps, pe, nwords, kv->data, kv->offs + kv->nkv, al);
-      MR_CUDA(cudaGetLastError());
+      {
+        ProfScope psw(pool, "tok_write", (double) end + 16.0 * nwords + (double) total);
+        if (vec) tokv_write_kernel<<<(unsigned) ((nwords + 255) / 256), 256, 0, s>>>(t, nbytes, ps, pe, nwords, kv->data, kv->offs + kv->nkv, al);
+        else tokenize_write_kernel<<<(unsigned) ((nwords + 255) / 256), 256, 0, s>>>(t, ps, pe, nwords, kv->data, kv->offs + kv->nkv, al);
+        MR_CUDA(cudaGetLastError());
+      }
       kv->nbytes = va.base + total;
       kv->nkv += nwords;
       kv->ksize += ksize;

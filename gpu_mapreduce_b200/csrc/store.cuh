@@ -12,6 +12,7 @@
 // int valuesizes[nvalue] | pad | key | pad | values | pad, src/keymultivalue.cpp:830-893) plus offs[nkmv+1].
 #pragma once
 
+#include <algorithm>
 #include <vector>
 
 #include "common.cuh"
@@ -66,8 +67,9 @@ struct DevKV {
     if (need <= cap) return;
     uint64_t ncap = cap ? cap : 0;
     ncap = need > 2 * ncap ? need : 2 * ncap;
-    // growth beyond what was asked is only worth it for small stores; large ones are sized exactly
-    if (need > (1ull << 28)) ncap = need;
+    // large stores are sized exactly when first filled; one that is being appended to (map with addflag, add,
+    // gather) grows by half again so that a run of appends does not copy the whole store every time
+    if (need > (1ull << 28)) ncap = (cap && nbytes) ? std::max<uint64_t>(need, cap + cap / 2) : need;
     uint8_t *nd = (uint8_t *) pool->alloc(ncap);
     if (phys_bytes()) MR_CUDA(cudaMemcpyAsync(nd, data, phys_bytes(), cudaMemcpyDeviceToDevice, pool->stream));
     pool->free(data, cap);
@@ -78,7 +80,7 @@ struct DevKV {
   {
     if (entries <= offs_cap) return;
     uint64_t ncap = entries > 2 * offs_cap ? entries : 2 * offs_cap;
-    if (entries > (1ull << 25)) ncap = entries;
+    if (entries > (1ull << 25)) ncap = (offs_cap && nkv) ? std::max<uint64_t>(entries, offs_cap + offs_cap / 2) : entries;
     uint64_t *no = (uint64_t *) pool->alloc(ncap * 8);
     if (offs && !uniform && nkv) MR_CUDA(cudaMemcpyAsync(no, offs, (nkv + 1) * 8, cudaMemcpyDeviceToDevice, pool->stream));
     pool->free(offs, offs_cap * 8);
@@ -108,8 +110,9 @@ struct DevKMV {
   // (data/offs above) is then written only when somebody needs its bytes (kmv_expand: pages, device views, a
   // functor that reads multivalues); reduce's stock functors read this form directly.
   bool factored = false;
-  uint32_t *fkey = nullptr, *fcnt = nullptr;  // [nkmv]
-  uint64_t fcap = 0;
+  uint32_t *fkey = nullptr, *fcnt = nullptr;  // keys: [nkmv * fkw] words (ukb = 4 * fkw bytes each); counts: [nkmv]
+  uint32_t fkw = 1;
+  uint64_t fcap = 0;                          // pairs allocated
   uint32_t fval[2] = {0, 0};  // the shared value (uvb bytes)
 
   explicit DevKMV(Pool *p) : pool(p) {}
@@ -117,7 +120,7 @@ struct DevKMV {
   {
     pool->free(data, cap);
     pool->free(offs, offs_cap * 8);
-    pool->free(fkey, fcap * 4);
+    pool->free(fkey, fcap * 4 * fkw);
     pool->free(fcnt, fcap * 4);
   }
 };

@@ -542,15 +542,15 @@ def test_widened_ops_error_paths(MR):
                       (lambda: mr.compress("count"), "Cannot compress without KeyValue")):
         with pytest.raises(g.MRError, match=msg):
             call()
-    mr.kv_add([(b"k", b"ab")])
+    mr.kv_add([(b"k", b"ab"), (b"j", b"a")])
     with pytest.raises(g.MRError, match="Invalid compare method for sort values"):
         mr.sort_values(7)
     with pytest.raises(g.MRError, match="value shorter than the compared type"):
         mr.sort_values(1)                                  # 2-byte values compared as int
     with pytest.raises(g.MRError, match="Invalid processor count for gather"):
         mr.gather(2)
-    assert mr.gather(1) == 1 and mr.scan_kv() == [(b"k", b"ab")]
-    assert mr.sort_values(5) == 1
+    assert mr.gather(1) == 2 and mr.scan_kv() == [(b"k", b"ab"), (b"j", b"a")]
+    assert mr.sort_values(6) == 2 and mr.scan_kv() == [(b"j", b"a"), (b"k", b"ab")]
 
 
 @pytest.mark.parametrize("cb", ["count", "sum", "cull"])
@@ -604,6 +604,45 @@ def test_tokenize_edge_cases(MR, oracle):
         want = H.kv_decode(oracle.tokenize(text))
         assert n == len(want)
         assert mr.scan_kv() == want
+
+
+def test_tokenize_chunk_boundaries_vs_oracle(MR, oracle):
+    """the 16-bytes-per-thread tokenizer: words that straddle 16-byte vectors, warps and 4 KB chunks, a word longer than
+    several chunks, every delimiter and \\v (not a delimiter), text cut at a NUL, lengths around the vector size"""
+    r = np.random.RandomState(42)
+    texts = []
+    for ln in (15, 16, 17, 31, 32, 33, 4095, 4096, 4097, 8191, 8193, 70_001):
+        a = r.choice(np.frombuffer(b"ab \t\n\f\r\x0bz", dtype=np.uint8), size=ln, p=[.3, .2, .2, .04, .04, .04, .04, .04, .1])
+        texts.append(bytes(a))
+    texts.append(b"w" * 13_000 + b" " + b"q" * 9_000)                     # words spanning three chunks
+    texts.append(b" " * 4096 + b"x" * 4096 + b" " * 4096 + b"y")          # a word that is exactly one chunk
+    texts.append(b"ab cd" * 1000 + b"\x00" + b" tail words" * 100)         # strtok stops at the first NUL
+    texts.append(bytes(r.randint(1, 256, size=50_000).astype(np.uint8)))   # arbitrary bytes, no NUL
+    for al in (4, 8):
+        for text in texts:
+            mr = MR(keyalign=al, valuealign=al)
+            want = H.kv_decode(oracle.tokenize(text))
+            assert mr.map_tokenize(text) == len(want)
+            assert mr.scan_kv() == want
+            assert mr.map_tokenize(text, addflag=1) == 2 * len(want)       # append keeps the earlier records
+            assert mr.scan_kv() == want + want
+
+
+def test_tokenize_bytewise_variant():
+    """the per-byte form of the tokenizer (used for text that is not 16-byte aligned) is chosen by
+    MRGPU_TOK_BYTEWISE=1, read once per process: rerun the tokenizer tests in a child"""
+    import os
+    import subprocess
+    import sys
+
+    if os.environ.get("MRGPU_TOK_BYTEWISE") == "1":
+        pytest.skip("already inside the child run")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_parity.py"), "-q", "-x", "-m", "gpu", "-k",
+                        "wordfreq_golden or tokenize_edge or tokenize_chunk"], env=dict(os.environ, MRGPU_TOK_BYTEWISE="1"),
+                       capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-3000:]
+    assert "passed" in p.stdout and "failed" not in p.stdout
 
 
 def test_invindex_golden(MR, golden):
