@@ -54,6 +54,7 @@ def wordfreq(total_bytes=1 << 30, nfiles=8, nvocab=1 << 17):
     T = Timer()
     truth = torch.zeros(nvocab, dtype=torch.int64, device=DEV)
     nwords_total, nbytes_total, start = 0, 0, 0
+    texts = []
     per_file = total_bytes // nfiles
     avg = float((lens + 1).astype(np.float64) @ np.diff(np.concatenate([[0.0], W.zipf_cdf(nvocab, 1.0)])))
     for f in range(nfiles):
@@ -73,12 +74,17 @@ def wordfreq(total_bytes=1 << 30, nfiles=8, nvocab=1 << 17):
         del rows, mask, idx, z, u
         nwords_total += nw
         nbytes_total += text.numel()
-        got = T.run("map", lambda: mr.map_tokenize(text, addflag=1 if f else 0))
-        assert got == nwords_total
-        del text
-    nuniq = T.run("collate", mr.collate)
-    assert nuniq == int((truth > 0).sum().item())
-    assert T.run("reduce", lambda: mr.reduce("sum")) == nuniq
+        texts.append((text, nwords_total))
+    # the pipeline runs twice on the same handle; the second pass (allocator warm, as in a long-running job) is reported
+    for rep in range(2):
+        T = Timer()
+        for f, (text, upto) in enumerate(texts):
+            got = T.run("map", lambda: mr.map_tokenize(text, addflag=1 if f else 0))
+            assert got == upto
+        nuniq = T.run("collate", mr.collate)
+        assert nuniq == int((truth > 0).sum().item())
+        assert T.run("reduce", lambda: mr.reduce("sum")) == nuniq
+    del texts
     # ground truth: the count of vocabulary word i is the number of times index i was drawn
     recs = mr.scan_kv() if nuniq <= 300000 else None
     if recs is not None:
@@ -159,22 +165,24 @@ def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
 def rmat(nlevels=24, ef=16, a=.57, b=.19, c=.19, d=.05, fraction=0.0, seed=12345):
     """oink: rmat N 16 .57 .19 .19 .05 0.0 12345 ; degree 2 (oink/rmat.cpp:37-61, oink/degree.cpp:43-50)."""
     mr = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
-    T = Timer()
-    state = (seed << 16) | 0x330E
-    ntotal = nremain = (1 << nlevels) * ef
-    niter, generated = 0, 0
-    while nremain:
-        niter += 1
-        generated += nremain
-        _, state = T.run("generate", lambda: mr.map_rmat(nremain, nlevels, a, b, c, d, fraction, state, addflag=1))
-        nunique = T.run("collate", mr.collate)
-        T.run("cull", lambda: mr.reduce("cull"))
-        nremain = ntotal - nunique
-    assert mr.kv_stats().npair == ntotal
     mrv = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
-    assert T.run("degree_map", lambda: mrv.map_mr(mr, "edge_to_vertices")) == 2 * ntotal
-    nvert = T.run("degree_collate", mrv.collate)
-    assert T.run("degree_reduce", lambda: mrv.reduce("count")) == nvert
+    # the whole job runs twice on the same handles; the second pass (allocator warm) is reported
+    for rep in range(2):
+        T = Timer()
+        state = (seed << 16) | 0x330E
+        ntotal = nremain = (1 << nlevels) * ef
+        niter, generated = 0, 0
+        while nremain:
+            niter += 1
+            generated += nremain
+            _, state = T.run("generate", lambda: mr.map_rmat(nremain, nlevels, a, b, c, d, fraction, state, addflag=1 if niter > 1 else 0))
+            nunique = T.run("collate", mr.collate)
+            T.run("cull", lambda: mr.reduce("cull"))
+            nremain = ntotal - nunique
+        assert mr.kv_stats().npair == ntotal
+        assert T.run("degree_map", lambda: mrv.map_mr(mr, "edge_to_vertices")) == 2 * ntotal
+        nvert = T.run("degree_collate", mrv.collate)
+        assert T.run("degree_reduce", lambda: mrv.reduce("count")) == nvert
     deg_sum = 0
     for nkey, page in mrv.kv_pages():
         deg_sum += int(np.frombuffer(page, dtype=np.int32).reshape(nkey, -1)[:, -1].astype(np.int64).sum())

@@ -142,6 +142,27 @@ __global__ void key_diff_kernel(const uint8_t *__restrict__ data, uint64_t n, ui
     if (shm[q]) mask[q] = 1;
 }
 
+// the same for word-aligned keys of at most 8 words: OR of (word XOR first key's word), reduced per warp
+__global__ void __launch_bounds__(256)
+key_diff_words_kernel(const uint32_t *__restrict__ data, uint64_t n, uint32_t rw, uint32_t kow, uint32_t kw, unsigned *wmask /*[kw]*/)
+{
+  uint32_t first[8], acc[8];
+#pragma unroll
+  for (int w = 0; w < 8; w++) first[w] = w < (int) kw ? data[kow + w] : 0, acc[w] = 0;
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint32_t *r = data + i * rw + kow;
+#pragma unroll
+    for (int w = 0; w < 8; w++)
+      if (w < (int) kw) acc[w] |= r[w] ^ first[w];
+  }
+#pragma unroll
+  for (int w = 0; w < 8; w++) {
+    const uint32_t a = __reduce_or_sync(0xFFFFFFFFu, acc[w]);
+    if ((threadIdx.x & 31) == 0 && a && w < (int) kw) atomicOr(&wmask[w], a);
+  }
+}
+
 // ---- general records: fingerprint + index ------------------------------------------------------------------
 
 __global__ void __launch_bounds__(256)
@@ -285,20 +306,29 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
       const uint32_t *st = start.p;
       {
         ProfScope ps(pool, "convert_factored", (double) U * (sizeof(K) + 8 + kb));
+        // one thread per key WORD: the word of the first key with the varying bytes that fall into it replaced
         const CompactKey ckc = ck;
-        auto mk = [=] __device__(uint64_t u) {
-          const uint32_t s0 = st[u];
-          fc[u] = st[u + 1] - s0;
-          const unsigned long long key = (unsigned long long) sk[s0];
-          uint8_t *d = fk + u * kb;
-          if (ident) {
-            for (uint32_t q = 0; q < kb; q++) d[q] = (uint8_t) (key >> (8 * q));
-          } else {
-            for (uint32_t q = 0; q < kb; q++) d[q] = k0b[q];
-            for (int q = 0; q < ckc.nvb; q++) d[ckc.pos[q]] = (uint8_t) (key >> (8 * q));
+        const uint32_t *k0w = (const uint32_t *) k0b;
+        uint32_t *fkw32 = (uint32_t *) fk;
+        auto mk = [=] __device__(uint64_t t) {
+          const uint64_t u = t / kw;
+          const uint32_t w = (uint32_t) (t - u * kw);
+          const uint32_t s0 = __ldg(st + u);
+          if (w == 0) fc[u] = __ldg(st + u + 1) - s0;
+          const unsigned long long key = (unsigned long long) __ldg(sk + s0);
+          uint32_t x;
+          if (ident) x = (uint32_t) (key >> (32 * w));
+          else {
+            x = k0w[w];
+            for (int q = 0; q < ckc.nvb; q++)
+              if ((uint32_t) (ckc.pos[q] >> 2) == w) {
+                const uint32_t sh = (ckc.pos[q] & 3) * 8;
+                x = (x & ~(0xFFu << sh)) | ((uint32_t) ((key >> (8 * q)) & 0xFF) << sh);
+              }
           }
+          fkw32[t] = x;
         };
-        for_each_kernel<<<grid_for(U, 256, 64), 256, 0, s>>>(U, mk);
+        for_each_kernel<<<grid_for(U * kw, 256, 64), 256, 0, s>>>(U * kw, mk);
         MR_CUDA(cudaGetLastError());
       }
       kmv->factored = true;
@@ -557,12 +587,25 @@ static void convert_impl(mrgpu_mr *mr)
       } else if (kv->kb <= 1024) {
         Buf<unsigned> mask(mr->pool, kv->kb);
         MR_CUDA(cudaMemsetAsync(mask.p, 0, kv->kb * 4, mr->pool.stream));
-        key_diff_kernel<<<grid_for(n, 256 * 8, 4), 256, kv->kb * 4, mr->pool.stream>>>(kv->data, n, kv->recsize, kv_key_off(al), kv->kb, mask.p);
-        MR_CUDA(cudaGetLastError());
+        const bool words = kv->kb % 4 == 0 && kv->kb <= 32 && kv->recsize % 4 == 0 && kv_key_off(al) % 4 == 0;
+        {
+          ProfScope ps(mr->pool, "convert_key_diff", (double) kv->nbytes);
+          if (words)
+            key_diff_words_kernel<<<grid_for(n, 256 * 8, 8), 256, 0, mr->pool.stream>>>((const uint32_t *) kv->data, n, kv->recsize / 4, kv_key_off(al) / 4,
+                                                                                         kv->kb / 4, mask.p);
+          else
+            key_diff_kernel<<<grid_for(n, 256 * 8, 4), 256, kv->kb * 4, mr->pool.stream>>>(kv->data, n, kv->recsize, kv_key_off(al), kv->kb, mask.p);
+          MR_CUDA(cudaGetLastError());
+        }
         std::vector<unsigned> hm(kv->kb);
         MR_CUDA(cudaMemcpyAsync(hm.data(), mask.p, kv->kb * 4, cudaMemcpyDeviceToHost, mr->pool.stream));
         MR_CUDA(cudaMemcpyAsync(key0.data(), kv->data + kv_key_off(al), kv->kb, cudaMemcpyDeviceToHost, mr->pool.stream));
         sync(mr);
+        if (words) {  // word ORs -> one flag per key byte
+          std::vector<unsigned> bytes(kv->kb);
+          for (uint32_t q = 0; q < kv->kb; q++) bytes[q] = (hm[q / 4] >> (8 * (q % 4))) & 0xFF;
+          hm = bytes;
+        }
         int nv = 0;
         for (uint32_t q = 0; q < kv->kb; q++)
           if (hm[q]) {
