@@ -82,6 +82,10 @@ def lib():
         "mrgpu_sort_values": [vp, C.c_int, u64p],
         "mrgpu_compress": [vp, C.c_int, u64p],
         "mrgpu_gather": [vp, C.c_int, u64p],
+        "mrgpu_broadcast": [vp, C.c_int, u64p],
+        "mrgpu_clone": [vp, u64p],
+        "mrgpu_collapse": [vp, C.c_char_p, C.c_int, u64p],
+        "mrgpu_scrunch": [vp, C.c_int, C.c_char_p, C.c_int, u64p],
         "mrgpu_kv_stats": [vp, C.POINTER(Stats)],
         "mrgpu_kmv_stats": [vp, C.POINTER(Stats)],
         "mrgpu_kv_page_info": [vp, C.c_uint64, u64p, u64p, u64p, u64p],
@@ -280,6 +284,22 @@ class MapReduce:
     def compress(self, functor: str):
         """compress(mycompress) src/mapreduce.cpp:749 with a stock callback: local convert + reduce, no exchange."""
         return self._count(lib().mrgpu_compress, REDUCE[functor])
+
+    def broadcast(self, root: int):
+        """broadcast(root) src/mapreduce.cpp:569: every rank gets a copy of root's KeyValue."""
+        return self._count(lib().mrgpu_broadcast, int(root))
+
+    def clone(self):
+        """clone() src/mapreduce.cpp:631: KV -> KMV, one value per pair."""
+        return self._count(lib().mrgpu_clone)
+
+    def collapse(self, key: bytes):
+        """collapse(key) src/mapreduce.cpp:681: all pairs -> one KMV pair (key_1, value_1, key_2, ...)."""
+        return self._count(lib().mrgpu_collapse, key, len(key))
+
+    def scrunch(self, numprocs: int, key: bytes):
+        """scrunch(numprocs, key) src/mapreduce.cpp:2075: gather then collapse."""
+        return self._count(lib().mrgpu_scrunch, int(numprocs), key, len(key))
 
     def gather(self, numprocs: int):
         """gather(numprocs) src/mapreduce.cpp:893: pairs of ranks >= numprocs move to rank me % numprocs."""

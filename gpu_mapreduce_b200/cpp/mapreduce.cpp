@@ -823,26 +823,57 @@ MapReduce *MapReduce::copy()
   return m;
 }
 
-uint64_t MapReduce::broadcast(int)
+uint64_t MapReduce::broadcast(int root)
 {
-  if (nprocs == 1) return kv ? kv_stats(0) : 0;
-  all("broadcast() is not built in the GPU library (SURVEY.md 8f)");
-  return 0;
+  if (kv == NULL) all("Cannot broadcast without KeyValue");
+  if (root < 0 || root >= nprocs) all("Invalid root for broadcast");
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_broadcast(gpu, root, &n), 0);
+  sync_kv_fields();
+  stats("Broadcast", 0);
+  return n;
 }
+
+// KV -> KMV on the GPU; the host-side objects follow as in convert()
 uint64_t MapReduce::clone()
 {
-  all("clone() is not built in the GPU library (SURVEY.md 8f)");
-  return 0;
+  if (kv == NULL) all("Cannot clone without KeyValue");
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_clone(gpu, &n), 0);
+  delete kv;
+  kv = NULL;
+  kmv = &g_kmv_marker;
+  stats("Clone", 1);
+  return n;
 }
-uint64_t MapReduce::collapse(char *, int)
+
+uint64_t MapReduce::collapse(char *key, int keybytes)
 {
-  all("collapse() is not built in the GPU library (SURVEY.md 8f)");
-  return 0;
+  if (kv == NULL) all("Cannot collapse without KeyValue");
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_collapse(gpu, key, keybytes, &n), 0);
+  delete kv;
+  kv = NULL;
+  kmv = &g_kmv_marker;
+  stats("Collapse", 1);
+  return n;
 }
-uint64_t MapReduce::scrunch(int, char *, int)
+
+uint64_t MapReduce::scrunch(int numprocs, char *key, int keybytes)
 {
-  all("scrunch() is not built in the GPU library (SURVEY.md 8f)");
-  return 0;
+  if (kv == NULL) all("Cannot scrunch without KeyValue");
+  if (numprocs < 1 || numprocs > nprocs) all("Invalid processor count for gather");
+  start_timer();
+  uint64_t n = 0;
+  ck(mrgpu_scrunch(gpu, numprocs, key, keybytes, &n), 0);
+  delete kv;
+  kv = NULL;
+  kmv = &g_kmv_marker;
+  stats("Scrunch", 1);
+  return n;
 }
 void MapReduce::print(int, int, int, int) { all("print() is not built in the GPU library (SURVEY.md 8f)"); }
 void MapReduce::print(char *, int, int, int, int, int) { all("print() is not built in the GPU library (SURVEY.md 8f)"); }

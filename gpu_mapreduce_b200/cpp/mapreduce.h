@@ -4,15 +4,16 @@
  * written for MR-MPI compile unchanged.  Written from scratch; nothing here is the reference's code.
  *
  * Where the work runs:
- *   aggregate / convert / collate / gather / sort_keys(flag) / sort_values(flag) / add / kv_stats / kmv_stats
+ *   aggregate / convert / collate / gather / broadcast / clone / collapse / scrunch / sort_keys(flag) /
+ *   sort_values(flag) / add / kv_stats / kmv_stats
  *                                                                                    always on the GPU
  *   map / reduce / compress / scan with one of the STOCK callbacks declared in
  *   mrgpu_functors.h (count, sum, cull, edge_to_vertices, ...)                       on the GPU (device functor)
  *   map / reduce / compress / scan / sort_*(compare fn) with any other function ptr  the callback runs on the
  *     host, one page at a time, exactly as in the reference; pages are staged D2H, emitted pairs H2D
  *
- * Not built (out of this round's scope): broadcast, clone, collapse, scrunch, print,
- * sort_multivalues, the two file-chunk map() variants.  They fail with
+ * Not built (out of this round's scope): print, sort_multivalues, the two file-chunk map()
+ * variants.  They fail with
  * the reference's error convention instead of silently doing something else. */
 #ifndef MAP_REDUCE_H
 #define MAP_REDUCE_H

@@ -122,6 +122,7 @@ static uint64_t allreduce_sum(mrgpu_mr *mr, uint64_t v);
 #include "ops_text.cuh"
 #include "ops_reduce.cuh"
 #include "ops_sort.cuh"
+#include "ops_shape.cuh"
 #include "ops_partition.cuh"
 #include "ops_aggregate.cuh"
 #include "ops_pages.cuh"

@@ -705,3 +705,94 @@ extern "C" int mrgpu_gather(mrgpu_mr *mr, int numprocs, uint64_t *nkv)
   if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
   API_END(mr)
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// broadcast(root)   src/mapreduce.cpp:569-625: every rank ends with a copy of root's KeyValue (its own is dropped).
+// The reference broadcasts page by page; here root's sizes travel in one all-gather-sized message and the
+// payload in one grouped send per peer.
+static void broadcast_impl(mrgpu_mr *mr, int root)
+{
+  freeze(mr);
+  const int P = mr->nranks, me = mr->rank;
+  if (P == 1) return;  // :582-587
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  ncclComm_t comm = (ncclComm_t) mr->comm;
+  if (me == root) kv_unpack(mr, mr->kv);
+  DevKV *kv = mr->kv;
+  constexpr int W = 6;  // {pairs, bytes, uniform, keybytes<<32|valuebytes, keysize, valuesize} of root
+  unsigned long long h[W] = {0, 0, 0, 0, 0, 0};
+  if (me == root) {
+    h[0] = kv->nkv, h[1] = kv->nbytes, h[2] = (kv->nkv == 0 || kv->uniform) ? 1 : 0;
+    h[3] = ((unsigned long long) kv->kb << 32) | kv->vb, h[4] = kv->ksize, h[5] = kv->vsize;
+  }
+  Buf<unsigned long long> d(pool, W);
+  MR_CUDA(cudaMemcpyAsync(d.p, h, W * 8, cudaMemcpyHostToDevice, s));
+  MR_NCCL(nccl().GroupStart());
+  if (me == root) {
+    for (int q = 0; q < P; q++)
+      if (q != root) MR_NCCL(nccl().Send(d.p, W, ncclUint64, q, comm, s));
+  } else
+    MR_NCCL(nccl().Recv(d.p, W, ncclUint64, root, comm, s));
+  MR_NCCL(nccl().GroupEnd());
+  MR_CUDA(cudaMemcpyAsync(h, d.p, W * 8, cudaMemcpyDeviceToHost, s));
+  sync(mr);
+  if (me != root) {
+    delete mr->kv;  // :590-592
+    kv = mr->kv = new DevKV(&pool);
+    kv->uniform = h[2] != 0;
+    kv->kb = (uint32_t) (h[3] >> 32);
+    kv->vb = (uint32_t) h[3];
+    kv->recsize = kv->uniform ? kv_rec_size(mr->al, kv->kb, kv->vb) : 0;
+    kv->reserve_bytes(h[1] > 512 ? h[1] : 512);
+    if (!kv->uniform) kv->reserve_offs(h[0] + 1);
+  }
+  if (h[0]) {
+    MR_NCCL(nccl().GroupStart());
+    if (me == root) {
+      for (int q = 0; q < P; q++) {
+        if (q == root) continue;
+        MR_NCCL(nccl().Send(kv->data, h[1], ncclInt8, q, comm, s));
+        if (!kv->uniform) MR_NCCL(nccl().Send(kv->offs, h[0] + 1, ncclUint64, q, comm, s));
+      }
+    } else {
+      MR_NCCL(nccl().Recv(kv->data, h[1], ncclInt8, root, comm, s));
+      if (!kv->uniform) MR_NCCL(nccl().Recv(kv->offs, h[0] + 1, ncclUint64, root, comm, s));
+    }
+    MR_NCCL(nccl().GroupEnd());
+  } else if (me != root && !kv->uniform)
+    MR_CUDA(cudaMemsetAsync(kv->offs, 0, 8, s));
+  if (me != root) {
+    kv->nkv = h[0];
+    kv->nbytes = h[1];
+    kv->ksize = h[4];
+    kv->vsize = h[5];
+    kv->h_offs_valid = false;
+  }
+  sync(mr);
+}
+
+extern "C" int mrgpu_broadcast(mrgpu_mr *mr, int root, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot broadcast without KeyValue");
+  if (root < 0 || root >= mr->nranks) MR_FAIL(MRGPU_EINVAL, "Invalid root for broadcast");
+  if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  broadcast_impl(mr, root);
+  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  API_END(mr)
+}
+
+// scrunch(numprocs, key, keybytes) = gather(numprocs) then collapse(key)   src/mapreduce.cpp:2075-2093
+extern "C" int mrgpu_scrunch(mrgpu_mr *mr, int numprocs, const void *key, int keybytes, uint64_t *nkmv)
+{
+  API_BEGIN(mr)
+  if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot scrunch without KeyValue");
+  if (numprocs < 1 || numprocs > mr->nranks) MR_FAIL(MRGPU_EINVAL, "Invalid processor count for gather");
+  if (keybytes < 0 || (keybytes && !key)) MR_FAIL(MRGPU_EINVAL, "bad key");
+  if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  gather_impl(mr, numprocs);
+  collapse_impl(mr, key, keybytes);
+  if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
+  API_END(mr)
+}

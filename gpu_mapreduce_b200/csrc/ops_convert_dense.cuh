@@ -454,17 +454,24 @@ static void dense_l2_window(mrgpu_mr *mr, bool on)
   static const char *e = getenv("MRGPU_DENSE_L2PIN");  // MiB of table to pin (0 = no window); default 56
   static const long mib = e ? atol(e) : 56;
   if (mib <= 0) return;
+  // handles on other host threads may be inside their own window on the same device: the set-aside is saved by
+  // the first one in and restored by the last one out
+  static std::mutex mu;
   static size_t saved_limit[64] = {0};
+  static int depth[64] = {0};
   const int dev = mr->device < 64 ? mr->device : 0;
   size_t bytes = (size_t) mib << 20;
+  std::lock_guard<std::mutex> lk(mu);
   if (on) {
     int maxp = 0, maxw = 0;
     cudaDeviceGetAttribute(&maxp, cudaDevAttrMaxPersistingL2CacheSize, mr->device);
     cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, mr->device);
     bytes = std::min(bytes, std::min((size_t) maxp, (size_t) maxw));
     if (bytes == 0) return;
-    cudaDeviceGetLimit(&saved_limit[dev], cudaLimitPersistingL2CacheSize);
-    cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes);
+    if (depth[dev]++ == 0) {
+      cudaDeviceGetLimit(&saved_limit[dev], cudaLimitPersistingL2CacheSize);
+      cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes);
+    }
   }
   cudaStreamAttrValue av;
   memset(&av, 0, sizeof(av));
@@ -476,8 +483,10 @@ static void dense_l2_window(mrgpu_mr *mr, bool on)
   cudaStreamSetAttribute(mr->pool.stream, cudaStreamAttributeAccessPolicyWindow, &av);
   if (!on) {
     cudaStreamSynchronize(mr->pool.stream);  // the kernel that used the window is done before the set-aside goes
-    cudaCtxResetPersistingL2Cache();
-    cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, saved_limit[dev]);
+    if (depth[dev] > 0 && --depth[dev] == 0) {
+      cudaCtxResetPersistingL2Cache();
+      cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, saved_limit[dev]);
+    }
   }
   cudaGetLastError();  // a device without the feature: run without it
 }

@@ -13,6 +13,7 @@
 #pragma once
 
 #include <algorithm>
+#include <atomic>
 #include <vector>
 
 #include "common.cuh"
@@ -58,7 +59,7 @@ struct DevKV {
 
   explicit DevKV(Pool *p) : pool(p)
   {
-    static uint64_t next_uid = 0;
+    static std::atomic<uint64_t> next_uid{0};
     uid = ++next_uid;
   }
   ~DevKV();

@@ -167,6 +167,16 @@ int mrgpu_compress(mrgpu_mr *mr, int functor, uint64_t *nkv);
 /* MapReduce::gather(int numprocs) src/mapreduce.cpp:893-1036: ranks >= numprocs send their KeyValue to rank
  * (me % numprocs), which appends the senders' pairs in ascending rank order; senders are left with an empty KeyValue */
 int mrgpu_gather(mrgpu_mr *mr, int numprocs, uint64_t *nkv);
+/* MapReduce::broadcast(int root) src/mapreduce.cpp:569-625: every rank's KeyValue is replaced by a copy of root's */
+int mrgpu_broadcast(mrgpu_mr *mr, int root, uint64_t *nkv);
+/* MapReduce::clone() src/mapreduce.cpp:631-672: every KeyValue pair becomes a KeyMultiValue pair with one value */
+int mrgpu_clone(mrgpu_mr *mr, uint64_t *nkmv);
+/* MapReduce::collapse(key, keybytes) src/mapreduce.cpp:681-702: this rank's pairs become ONE KeyMultiValue pair whose
+ * values are key_1, value_1, key_2, value_2, ...; like the reference (src/keymultivalue.cpp:475-478) it refuses a
+ * result that does not fit one page */
+int mrgpu_collapse(mrgpu_mr *mr, const void *key, int keybytes, uint64_t *nkmv);
+/* MapReduce::scrunch(numprocs, key, keybytes) src/mapreduce.cpp:2075-2093: gather(numprocs) then collapse(key) */
+int mrgpu_scrunch(mrgpu_mr *mr, int numprocs, const void *key, int keybytes, uint64_t *nkmv);
 
 /* ---- stats and page access (scan, host callbacks, printing) --------------------------------------- */
 

@@ -305,6 +305,8 @@ static void run_ops(MapReduce *mr, int narg, char **arg, const char *out)
     else if (!strcmp(op, "reduce_cull")) n = mr->reduce(cull, NULL);
     else if (!strncmp(op, "sort_keys:", 10)) n = mr->sort_keys(atoi(op + 10));
     else if (!strncmp(op, "sort_values:", 12)) n = mr->sort_values(atoi(op + 12));
+    else if (!strcmp(op, "clone")) n = mr->clone();
+    else if (!strncmp(op, "collapse:", 9)) n = mr->collapse((char *) op + 9, (int) strlen(op + 9) + 1);  // key = text + NUL
     else if (!strcmp(op, "compress_count")) n = mr->compress(count, NULL);
     else if (!strcmp(op, "compress_sum")) n = mr->compress(sum, NULL);
     else if (!strcmp(op, "compress_cull")) n = mr->compress(cull, NULL);
@@ -325,7 +327,7 @@ static void usage()
           "refdrv hash                                  (stdin: '<initval> <hexkey>' per line)\n"
           "refdrv run <in.kv> <out> <memsize> [align] ops...   ops: aggregate convert collate reduce_count\n"
           "        reduce_sum reduce_cull sort_keys:<flag> sort_values:<flag> compress_count compress_sum compress_cull\n"
-          "        map_e2v map_e2v1 dumpkv dumpkmv pagekv pagekmv\n"
+          "        clone collapse:<key text> map_e2v map_e2v1 dumpkv dumpkmv pagekv pagekmv\n"
           "refdrv intcount <in.u32> <out.kv> <memsize>  map emit, aggregate, convert, reduce count, sort_keys 1\n"
           "refdrv wordfreq <out> <memsize> <mapout|final> files...\n"
           "refdrv invindex <out> <memsize> <mapout|kmv> files...\n"

@@ -184,6 +184,18 @@ int main(int narg, char **args)
   printf("compressed %lu\n", (unsigned long) ncomp);
   mr3->scan(collect_str, NULL);
   dump("compress: key count sum", true);
+  // 3d. clone: one KMV pair per KV pair, in order; collapse: everything under one key (sorted first: the order of
+  //     compress's output is not part of the contract)
+  mr3->sort_keys(5);
+  mr3->clone();
+  mr3->scan(collect_kmv, NULL);
+  dump("clone", false);
+  mr3->reduce(sumvals, mr3);
+  char allkey[] = "all";
+  uint64_t ncol = mr3->collapse(allkey, 4);
+  printf("collapsed %lu\n", (unsigned long) ncol);
+  mr3->scan(collect_kmv, NULL);
+  dump("collapse", false);
   delete mr3;
   delete mr2;
   delete mr;

@@ -196,6 +196,14 @@ def main():
     for cb in ("count", "sum", "cull"):
         G[f"compress.{cb}"] = b2a(H.ref_ops(kv4, [f"compress_{cb}", "dumpkv"]))
 
+    # 13. clone (src/mapreduce.cpp:631) and collapse (:681) on the data of 4 and of 2; collapse's key is "all\0"
+    for name, kvb in (("convert", kv4), ("pages_b2", G["pages_b2.in"].tobytes())):
+        G[f"clone.{name}"] = b2a(H.ref_ops(kvb, ["clone", "dumpkmv"]))
+        G[f"collapse.{name}"] = b2a(H.ref_ops(kvb, ["collapse:all", "dumpkmv"]))
+    for al in (4, 8):
+        G[f"collapse.pages_b2.page.a{al}"] = b2a(H.ref_ops(G["pages_b2.in"].tobytes(), ["collapse:all", "pagekmv"], align=al))
+        G[f"clone.pages_b2.page.a{al}"] = b2a(H.ref_ops(G["pages_b2.in"].tobytes(), ["clone", "pagekmv"], align=al))
+
     np.savez_compressed(os.path.join(HERE, "golden.npz"), **G)
     with open(os.path.join(HERE, "manifest.json"), "w") as f:
         json.dump(M, f, indent=0)

@@ -172,6 +172,14 @@ class Oracle:
         swapped = self.sort_keys(kv_encode([(v, k) for k, v in kv_decode(kv)]), flag)
         return kv_encode([(k, v) for v, k in kv_decode(swapped)])
 
+    def clone(self, kv: bytes) -> bytes:
+        """src/keymultivalue.cpp:344-374: every pair becomes a KMV pair holding its one value, in KV order"""
+        return kmv_encode([(k, [v]) for k, v in kv_decode(kv)])
+
+    def collapse(self, kv: bytes, key: bytes) -> bytes:
+        """src/keymultivalue.cpp:384-468: ONE KMV pair, values = key_1, value_1, key_2, value_2, ... in KV order"""
+        return kmv_encode([(key, [x for k, v in kv_decode(kv) for x in (k, v)])])
+
     def compress(self, kv: bytes, which: str) -> bytes:
         """src/mapreduce.cpp:749-851: KeyMultiValue::convert of the local pairs, then the callback per distinct key"""
         return self.reduce(self.convert(kv), which)

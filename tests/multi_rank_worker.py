@@ -103,6 +103,22 @@ def main_nccl():
             assert H.canon_kv(mr.scan_kv()) == H.canon_kv(want)
             mr.destroy()
 
+    # broadcast(root), src/mapreduce.cpp:569-625: every rank ends with root's pairs; scrunch = gather + collapse (:2075)
+    for case in range(4):
+        for root in (0, world - 1):
+            mr = g.MapReduce(device=local, rank=rank, nranks=world, unique_id=uid)
+            mr.kv_add(shard_records(case, rank))
+            want = shard_records(case, root)
+            assert mr.broadcast(root) == world * len(want)
+            assert mr.scan_kv() == want, f"broadcast({root}) case {case}: wrong pairs on rank {rank}"
+            mr.destroy()
+        mr = g.MapReduce(device=local, rank=rank, nranks=world, unique_id=uid)
+        mr.kv_add(shard_records(case, rank))
+        assert mr.scrunch(1, b"all\0") == world            # one KMV pair per rank, only rank 0's has values
+        flat = [x for q in range(world) for k, v in shard_records(case, q) for x in (k, v)] if rank == 0 else []
+        assert mr.scan_kmv() == [(b"all\0", flat)]
+        mr.destroy()
+
     # IntCount through map_intcount: header-less rows cross the wire when every rank holds them; with one rank
     # set to compact=0 (or one rank empty / holding another shape) the ranks must agree on records instead
     def ic_keys(q, variant):

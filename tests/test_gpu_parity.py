@@ -533,6 +533,62 @@ def test_sort_values_flags_golden(MR, golden, flag):
         assert H.kv_encode(mr.scan_kv()) == golden[f"sortv{flag}.out{tag}"]
 
 
+@pytest.mark.parametrize("name", ["convert", "pages_b2"])
+def test_clone_and_collapse_golden(MR, golden, oracle, name):
+    """clone (src/mapreduce.cpp:631) and collapse (:681) against KMVs dumped by the reference (tests/golden section 13)"""
+    kvb = golden["convert.in"] if name == "convert" else golden["pages_b2.in"]
+    recs = H.kv_decode(kvb)
+    mr = MR()
+    _load(mr, kvb)
+    assert mr.clone() == len(recs)
+    assert mr.scan_kmv() == H.kmv_decode(golden[f"clone.{name}"])            # same pairs, same order
+    assert mr.reduce("count") == len(recs)
+    assert mr.scan_kv() == [(k, struct.pack("<i", 1)) for k, _ in recs]
+    mr = MR()
+    _load(mr, kvb)
+    assert mr.collapse(b"all\0") == 1
+    st = mr.kmv_stats()
+    assert (st.npair, st.nvalue, st.keysize, st.valuesize) == (1, 2 * len(recs), 4, sum(len(k) + len(v) for k, v in recs))
+    assert mr.scan_kmv() == H.kmv_decode(golden[f"collapse.{name}"])
+    assert mr.reduce("count") == 1 and mr.scan_kv() == [(b"all\0", struct.pack("<i", 2 * len(recs)))]
+
+
+@pytest.mark.parametrize("al", [4, 8])
+def test_clone_and_collapse_page_images(MR, golden, al):
+    for op in ("clone", "collapse"):
+        mr = MR(keyalign=al, valuealign=al)
+        _load(mr, golden["pages_b2.in"])
+        mr.clone() if op == "clone" else mr.collapse(b"all\0")
+        want = H.pages_decode(golden[f"{op}.pages_b2.page.a{al}"])
+        got = [(nkey, page) for nkey, page, ext in mr.kmv_pages()]
+        assert len(got) == len(want) == 1 and got[0][0] == want[0][0]
+        kal = (al, al)
+        assert H.kmv_page_records(got[0][1], got[0][0], *kal) == H.kmv_page_records(want[0][1], want[0][0], *kal)
+
+
+def test_collapse_limits_and_empty(MR):
+    import gpu_mapreduce_b200 as g
+
+    mr = MR(memsize=-4096)
+    mr.kv_add([(struct.pack("<I", i), b"payload!") for i in range(400)])     # 400 * (8 + 12) bytes of values > one 4 KiB page
+    with pytest.raises(g.MRError, match="Collapse of multi-block KMV not yet supported"):
+        mr.collapse(b"k")
+    with pytest.raises(g.MRError, match="Cannot clone without KeyValue"):
+        MR().clone()
+    with pytest.raises(g.MRError, match="Cannot collapse without KeyValue"):
+        MR().collapse(b"k")
+    e = MR()
+    e.kv_add([])
+    assert e.clone() == 0 and e.scan_kmv() == []
+    e2 = MR()
+    e2.kv_add([])
+    assert e2.collapse(b"kk") == 1 and e2.scan_kmv() == [(b"kk", [])]
+    b = MR()
+    b.kv_add([(b"a", b"b")])
+    assert b.broadcast(0) == 1 and b.scan_kv() == [(b"a", b"b")]           # one rank: nothing moves
+    assert b.scrunch(1, b"s\0") == 1 and b.scan_kmv() == [(b"s\0", [b"a", b"b"])]
+
+
 def test_widened_ops_error_paths(MR):
     import gpu_mapreduce_b200 as g
 

@@ -159,3 +159,17 @@ def test_sort_values_flags(golden, oracle, flag):
 @pytest.mark.parametrize("cb", ["count", "sum", "cull"])
 def test_compress(golden, oracle, cb):
     assert oracle.compress(golden["convert.in"], cb) == golden[f"compress.{cb}"]
+
+
+@pytest.mark.parametrize("name", ["convert", "pages_b2"])
+def test_clone_and_collapse(golden, oracle, name):
+    kv = golden["convert.in"] if name == "convert" else golden["pages_b2.in"]
+    assert oracle.clone(kv) == golden[f"clone.{name}"]
+    assert oracle.collapse(kv, b"all\0") == golden[f"collapse.{name}"]
+
+
+@pytest.mark.parametrize("al", [4, 8])
+def test_clone_and_collapse_page_images(golden, oracle, al):
+    kv = golden["pages_b2.in"]
+    assert oracle.kmv_pages(oracle.clone(kv), 64 << 20, al, al) == golden[f"clone.pages_b2.page.a{al}"]
+    assert oracle.kmv_pages(oracle.collapse(kv, b"all\0"), 64 << 20, al, al) == golden[f"collapse.pages_b2.page.a{al}"]

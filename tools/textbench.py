@@ -16,3 +16,14 @@ tot = 0
 for k in mr.prof_report()[0]:
     print(k["tag"], round(k["ms"], 4)); tot += k["ms"]
 print("words", nw, "kernel ms", round(tot, 3), "text GB/s", round(n / tot / 1e6, 1))
+
+# collate + reduce(sum) on the words just emitted (general path: variable-length keys)
+for it in range(2):
+    mr.map_tokenize(t)
+    mr.prof(it == 1)
+    nu = mr.collate()
+    mr.reduce("sum")
+tot = 0
+for k in sorted(mr.prof_report()[0], key=lambda k: -k["ms"]):
+    print("   ", k["tag"], round(k["ms"], 3), k["calls"]); tot += k["ms"]
+print("unique", nu, "collate+reduce kernel ms", round(tot, 2))
