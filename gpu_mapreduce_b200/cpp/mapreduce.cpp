@@ -875,7 +875,107 @@ uint64_t MapReduce::scrunch(int numprocs, char *key, int keybytes)
   stats("Scrunch", 1);
   return n;
 }
-void MapReduce::print(int, int, int, int) { all("print() is not built in the GPU library (SURVEY.md 8f)"); }
-void MapReduce::print(char *, int, int, int, int, int) { all("print() is not built in the GPU library (SURVEY.md 8f)"); }
+// ---- print(): the reference's text form of the pairs (KeyValue::print src/keyvalue.cpp:773-830,
+// KeyMultiValue::print src/keymultivalue.cpp:1646-1760), produced on the host from the page walks
+
+// one field in the format selected by flag 0..7 (NULL, int, uint64, float, double, string, 2 ints, 2 uint64)
+static void print_field(FILE *fp, int flag, const char *p)
+{
+  int i2[2];
+  uint64_t u2[2];
+  float f;
+  double d;
+  switch (flag) {
+    case 0: fputs("NULL", fp); break;
+    case 1: memcpy(i2, p, 4); fprintf(fp, "%d", i2[0]); break;
+    case 2: memcpy(u2, p, 8); fprintf(fp, "%lu", (unsigned long) u2[0]); break;
+    case 3: memcpy(&f, p, 4); fprintf(fp, "%g", f); break;
+    case 4: memcpy(&d, p, 8); fprintf(fp, "%g", d); break;
+    case 5: fprintf(fp, "%s", p); break;
+    case 6: memcpy(i2, p, 8); fprintf(fp, "%d %d", i2[0], i2[1]); break;
+    default: memcpy(u2, p, 16); fprintf(fp, "%lu %lu", (unsigned long) u2[0], (unsigned long) u2[1]); break;
+  }
+}
+
+void MapReduce::print_pairs(FILE *fp, int nstride, int kflag, int vflag)
+{
+  int istride = 0;
+  if (kv) {
+    walk_kv(gpu, [&](char *k, int kb, char *v, int vb) {
+      if (++istride != nstride) return;
+      istride = 0;
+      fprintf(fp, "KV pair: proc %d, sizes %d %d, key ", me, kb, vb);
+      print_field(fp, kflag, k);
+      fputs(", value ", fp);
+      print_field(fp, vflag, v);
+      fputc('\n', fp);
+    });
+  }
+  if (kmv) {
+    walk_kmv(gpu, [&](char *k, int kb, char *mv, int nv, int *sizes) {
+      if (mv == NULL && nv == 0 && (void *) sizes == (void *) this) {  // a multi-block pair: never strided, never listed
+        fprintf(fp, "KMV pair: proc %d, nvalues %lu, size %d, key ", me, (unsigned long) kmv_nvalue_total, kb);
+        print_field(fp, kflag, k);
+        fputs(", too many values to print\n", fp);
+        return;
+      }
+      if (++istride != nstride) return;
+      istride = 0;
+      int mvb = 0;
+      for (int j = 0; j < nv; j++) mvb += sizes[j];
+      fprintf(fp, "KMV pair: proc %d, nvalues %d, sizes %d %d, key ", me, nv, kb, mvb);
+      print_field(fp, kflag, k);
+      fputs(", values ", fp);
+      for (int j = 0; j < nv; j++) {
+        print_field(fp, vflag, mv);
+        fputc(' ', fp);
+        mv += sizes[j];
+      }
+      fputc('\n', fp);
+    });
+  }
+}
+
+// print to the screen (src/mapreduce.cpp:1671-1711): proc >= 0 only that rank prints, proc < 0 every rank in turn
+void MapReduce::print(int proc, int nstride, int kflag, int vflag)
+{
+  if (kv == NULL && kmv == NULL) all("Cannot print without KeyValue or KeyMultiValue");
+  if (kflag < 0 || vflag < 0 || kflag > 7 || vflag > 7) all("Invalid print args");
+  if (proc == me) print_pairs(stdout, nstride, kflag, vflag);
+  if (proc >= 0) return;
+  for (int r = 0; r < nprocs; r++) {
+    MPI_Barrier(comm);
+    if (r == me) {
+      print_pairs(stdout, nstride, kflag, vflag);
+      fflush(stdout);
+    }
+  }
+  MPI_Barrier(comm);
+}
+
+// print to file(s) (src/mapreduce.cpp:1719-1762): one rank -> `file`; all ranks -> `file` appended in rank order
+// (fflag 0) or `file.<rank>` each (fflag 1)
+void MapReduce::print(char *file, int fflag, int proc, int nstride, int kflag, int vflag)
+{
+  if (kv == NULL && kmv == NULL) all("Cannot print without KeyValue or KeyMultiValue");
+  if (kflag < 0 || vflag < 0 || kflag > 7 || vflag > 7) all("Invalid print args");
+  auto to_file = [&](const std::string &name, const char *mode) {
+    FILE *fp = fopen(name.c_str(), mode);
+    if (fp == NULL) one("Could not open print file");
+    print_pairs(fp, nstride, kflag, vflag);
+    fclose(fp);
+  };
+  if (proc == me) to_file(file, "w");
+  if (proc >= 0) return;
+  if (fflag == 1) {
+    to_file(std::string(file) + "." + std::to_string(me), "w");
+    return;
+  }
+  for (int r = 0; r < nprocs; r++) {
+    MPI_Barrier(comm);
+    if (r == me) to_file(file, "a");
+  }
+  MPI_Barrier(comm);
+}
 
 }  // namespace MAPREDUCE_NS

@@ -12,14 +12,15 @@
  *   map / reduce / compress / scan / sort_*(compare fn) with any other function ptr  the callback runs on the
  *     host, one page at a time, exactly as in the reference; pages are staged D2H, emitted pairs H2D
  *
- * Not built (out of this round's scope): print, sort_multivalues, the two file-chunk map()
- * variants.  They fail with
+ * Not built (out of this round's scope): sort_multivalues, the two file-chunk map() variants.
+ * They fail with
  * the reference's error convention instead of silently doing something else. */
 #ifndef MAP_REDUCE_H
 #define MAP_REDUCE_H
 
 #include "mpi.h"
 #include "stdint.h"
+#include <stdio.h>
 
 struct mrgpu_mr;
 
@@ -141,6 +142,7 @@ class MapReduce {
   uint64_t end_emit(mrgpu_mr *target, KeyValue *k);
   template <typename F> void walk_kv(mrgpu_mr *h, F f);
   template <typename F> void walk_kmv(mrgpu_mr *h, F f);
+  void print_pairs(FILE *fp, int nstride, int kflag, int vflag);
   uint64_t host_sort(int (*)(char *, int, char *, int), int by_value);
   uint64_t reduce_impl(void (*)(char *, int, char *, int, int *, class KeyValue *, void *), void *, const char *heading);
 };

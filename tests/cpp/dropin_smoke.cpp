@@ -184,12 +184,20 @@ int main(int narg, char **args)
   printf("compressed %lu\n", (unsigned long) ncomp);
   mr3->scan(collect_str, NULL);
   dump("compress: key count sum", true);
+  // 3c'. print(): every 50th KV pair as (string, 2 x uint64)... the values are two int64, printed as "%lu %lu"
+  mr3->sort_keys(5);
+  fflush(stdout);
+  mr3->print(0, 50, 5, 7);
+  fflush(stdout);
   // 3d. clone: one KMV pair per KV pair, in order; collapse: everything under one key (sorted first: the order of
   //     compress's output is not part of the contract)
   mr3->sort_keys(5);
   mr3->clone();
   mr3->scan(collect_kmv, NULL);
   dump("clone", false);
+  fflush(stdout);
+  mr3->print(0, 100, 5, 1);
+  fflush(stdout);
   mr3->reduce(sumvals, mr3);
   char allkey[] = "all";
   uint64_t ncol = mr3->collapse(allkey, 4);
