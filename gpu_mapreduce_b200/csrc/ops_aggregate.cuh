@@ -398,9 +398,13 @@ static void aggregate_impl(mrgpu_mr *mr)
   // pass 2 writes the pairs later -- straight into the peers' receive buffers when the peer-store exchange is
   // possible, else into a local send buffer for NCCL
   const bool fast = n && partition_eligible(mr, kv);
-  PartPlan pl;
+  PartPlan pl_local;
+  // pass 1 may have been done by map_intcount while it wrote this KV (emit_and_plan)
+  const bool planned = fast && kv->plan && kv->ahead_n == n && kv->plan_nranks == P;
+  PartPlan &pl = planned ? *kv->plan : pl_local;
   if (fast) {
-    partition_counts(mr, kv, pl, scount);
+    if (planned) scount = kv->plan_scount;
+    else partition_counts(mr, kv, pl, scount);
     for (int p = 0; p < P; p++) {
       srec[p + 1] = srec[p] + scount[p];
       sbytes[p] = scount[p] * row;

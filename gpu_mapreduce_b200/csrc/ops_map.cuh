@@ -11,6 +11,7 @@
 // addflag = 1 re-opens the current one for append (KeyValue::append, src/keyvalue.cpp:185-209).
 static void kv_unpack(mrgpu_mr *mr, DevKV *kv);
 static void emit_and_count(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64_t n);  // ops_convert_dense.cuh
+static void emit_and_plan(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64_t n);   // ops_partition.cuh
 static void emit_from_host(mrgpu_mr *mr, DevKV *kv, const uint32_t *hkeys, uint64_t n, bool count);  // ops_convert_dense.cuh
 
 static void kv_begin_map(mrgpu_mr *mr, int addflag, bool keep_packed = false)
@@ -277,11 +278,14 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
     }
     kv->reserve_bytes((kv->nkv + n) * 4);
     // The pass that writes the key column can do the first pass of the op that follows in every pipeline: with
-    // one rank aggregate() is a no-op and convert() counts keys.  (With several ranks the same was tried for
-    // aggregate()'s destination count: the fused pass took 4.19 ms against 1.38 + 2.49 apart, so it is not done.)
+    // one rank aggregate() is a no-op and convert() counts keys; with several, aggregate() needs every pair's
+    // destination and the per-tile counts (1.89 ms fused against 1.38 + 1.82 apart at two ranks; a first, word-
+    // per-lane version of the fused pass had been slower than the two apart: 4.19 against 3.87 ms).
     const bool fresh = kv->nkv == 0 && mr->ahead && n >= (1u << 16) && ((((uintptr_t) dk) | ((uintptr_t) kv->data)) & 15) == 0;
     if (fresh && mr->nranks == 1) {
       emit_and_count(mr, kv, dk, n);
+    } else if (fresh && mr->nranks > 1 && mr->nranks <= 256 && !getenv("MRGPU_NO_EMIT_PLAN")) {
+      emit_and_plan(mr, kv, dk, n);
     } else if (n) {
       ProfScope ps(mr->pool, "map_intcount_emit", (double) n * (4 + 8 + 4 + 4), 1, (double) n * 8);
       copy_words_kernel<<<grid_for(n, 256 * 16, 16), 256, 0, mr->pool.stream>>>(dk, (uint32_t *) kv->data + kv->nkv, n);

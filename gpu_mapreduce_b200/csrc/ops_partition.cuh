@@ -128,6 +128,75 @@ partition_count_kernel(const uint32_t *__restrict__ data, uint64_t n, uint32_t n
   }
 }
 
+// Pass 1 for header-less 4-byte rows (IntCount's key column): a thread takes four consecutive keys with one 16-byte
+// load, writes their four destination bytes with one 4-byte store and -- when map_intcount runs this pass while
+// it emits (emit_and_plan) -- copies the keys into the KV with one 16-byte store.  Counting does not care which
+// thread holds which pair, so nothing here has to be warp-striped like pass 2.
+__global__ void __launch_bounds__(PART_THREADS)
+partition_count4_kernel(const uint32_t *__restrict__ keys, uint64_t n, uint32_t nprocs, uint64_t ntiles, unsigned *__restrict__ tcount,
+                        uint8_t *__restrict__ dest_out, uint32_t *__restrict__ copy_out)
+{
+  __shared__ unsigned sh[PART_MAXP];
+  const int tid = threadIdx.x, lane = tid & 31;
+  constexpr int VPT = PART_IPT / 4;  // 16-byte vectors per thread per tile
+  const bool pow2 = (nprocs & (nprocs - 1)) == 0;
+  for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    sh[tid] = 0;
+    __syncthreads();
+    const uint64_t tbase = tile * PART_TILE;
+    uint32_t dest[PART_IPT];
+    int4 v[VPT];
+#pragma unroll
+    for (int j = 0; j < VPT; j++) {
+      const uint64_t i = tbase + (uint64_t) (j * PART_THREADS + tid) * 4;
+      v[j] = make_int4(0, 0, 0, 0);
+      if (i + 4 <= n) v[j] = ld_stream((const int4 *) (keys + i));
+      else
+        for (int q = 0; q < 4; q++)
+          if (i + q < n) (&v[j].x)[q] = (int) keys[i + q];
+    }
+#pragma unroll
+    for (int j = 0; j < VPT; j++) {
+      const uint64_t i = tbase + (uint64_t) (j * PART_THREADS + tid) * 4;
+      uint32_t packed = 0;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const uint32_t k[1] = {(uint32_t) (&v[j].x)[q]};
+        const uint32_t h = hashlittle_regs<1>(k, nprocs);
+        const uint32_t d = pow2 ? (h & (nprocs - 1)) : (h % nprocs);
+        dest[j * 4 + q] = i + q < n ? d : 0xFFFFFFFFu;
+        packed |= d << (8 * q);
+      }
+      if (i + 4 <= n) {
+        *(uint32_t *) (dest_out + i) = packed;
+        if (copy_out) st_stream((int4 *) (copy_out + i), v[j]);
+      } else
+        for (int q = 0; q < 4; q++)
+          if (i + q < n) {
+            dest_out[i + q] = (uint8_t) (packed >> (8 * q));
+            if (copy_out) copy_out[i + q] = (uint32_t) (&v[j].x)[q];
+          }
+    }
+    if (nprocs <= 32) {
+      unsigned mine = 0;  // lane d accumulates destination d
+      for (uint32_t q = 0; q < nprocs; q++) {
+        unsigned c = 0;
+#pragma unroll
+        for (int j = 0; j < PART_IPT; j++) c += __popc(__ballot_sync(0xFFFFFFFFu, dest[j] == q));
+        if (lane == (int) q) mine = c;
+      }
+      if (lane < (int) nprocs && mine) atomicAdd(&sh[lane], mine);
+    } else {
+#pragma unroll
+      for (int j = 0; j < PART_IPT; j++)
+        if (dest[j] != 0xFFFFFFFFu) atomicAdd(&sh[dest[j]], 1u);
+    }
+    __syncthreads();
+    if (tid < (int) nprocs) tcount[(uint64_t) tid * ntiles + tile] = sh[tid];
+    __syncthreads();
+  }
+}
+
 // lanes of the warp with the same destination: one ballot per destination bit
 __device__ __forceinline__ unsigned match_dest(uint32_t d, int nbits)
 {
@@ -320,12 +389,13 @@ partition_scatter_kernel(const uint32_t *__restrict__ data, DestPtrs dp, uint64_
 // state between the two passes: struct PartPlan, store.cuh
 
 template <int RW, int KW, int KOFF>
-static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount)
+static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount, const uint32_t *src = nullptr, uint64_t nsrc = 0)
 {
+  // src != nullptr (header-less 4-byte rows only): the rows come from src and the same pass writes them to kv->data
   Pool &pool = mr->pool;
   cudaStream_t s = pool.stream;
   const int P = mr->nranks;
-  const uint64_t n = kv->nkv;
+  const uint64_t n = src ? nsrc : kv->nkv;
   const uint64_t ntiles = (n + PART_TILE - 1) / PART_TILE;
   pl.rw = RW;
   pl.kw = KW;
@@ -334,9 +404,15 @@ static void partition_counts_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vecto
   pl.toffs.alloc(pool, ntiles * P);
   pl.dest.alloc(pool, n);
   {
-    ProfScope ps(pool, "aggregate_count", (double) kv->nbytes, 1, (double) kv->phys_bytes() + (double) n);
-    partition_count_kernel<RW, KW, KOFF><<<(unsigned) std::min<uint64_t>(ntiles, (uint64_t) kSMs * 16), PART_THREADS, 0, s>>>(
-        (const uint32_t *) kv->data, n, (uint32_t) P, ntiles, tcount.p, pl.dest.p);
+    // emit + count: map's 20 B/pair plus aggregate's read of the KV (16 B/pair) in the reference layout
+    ProfScope ps(pool, src ? "map_intcount_emit_plan" : "aggregate_count", src ? (double) n * 36 : (double) kv->nbytes, 1,
+                 src ? (double) n * 9 : (double) kv->phys_bytes() + (double) n);
+    const unsigned grid = (unsigned) std::min<uint64_t>(ntiles, (uint64_t) kSMs * 16);
+    const uint32_t *in = src ? src : (const uint32_t *) kv->data;
+    if (RW == 1 && KW == 1 && KOFF == 0 && ((uintptr_t) in % 16) == 0 && ((uintptr_t) kv->data % 16) == 0)
+      partition_count4_kernel<<<grid, PART_THREADS, 0, s>>>(in, n, (uint32_t) P, ntiles, tcount.p, pl.dest.p, src ? (uint32_t *) kv->data : nullptr);
+    else if (src) MR_FAIL(MRGPU_EINVAL, "internal: emit_and_plan needs 16-byte aligned header-less rows");
+    else partition_count_kernel<RW, KW, KOFF><<<grid, PART_THREADS, 0, s>>>(in, n, (uint32_t) P, ntiles, tcount.p, pl.dest.p);
     MR_CUDA(cudaGetLastError());
   }
   // exclusive scan in destination-major order = slot of every (destination, tile)
@@ -413,6 +489,18 @@ static bool partition_eligible(mrgpu_mr *mr, DevKV *kv)
 }
 
 static void partition_counts(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, std::vector<uint64_t> &scount) { PART_DISPATCH(partition_counts_t, mr, kv, pl, scount); }
+// map_intcount on several ranks (ops_map.cuh): the pass that writes the key column also does aggregate()'s
+// pass 1 (destination of every pair, per-tile counts).  aggregate() uses the plan if the KV is still the same.
+static void emit_and_plan(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64_t n)
+{
+  delete kv->plan;
+  kv->plan = new PartPlan();
+  kv->plan_scount.assign(mr->nranks, 0);
+  partition_counts_t<1, 1, 0>(mr, kv, *kv->plan, kv->plan_scount, keys, n);
+  kv->plan_nranks = mr->nranks;
+  kv->ahead_n = n;
+}
+
 static void partition_scatter(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, const DestPtrs &dp, const char *tag, bool remote = false)
 {
   PART_DISPATCH(partition_scatter_t, mr, kv, pl, dp, tag, remote);

@@ -54,6 +54,10 @@ struct DevKV {
   uint64_t ahead_n = 0;
   bool counted = false, counted_bad = false;
   uint64_t counted_bits = 0;
+  // ... or, with several ranks, aggregate()'s first pass (destination of every pair, per-tile counts)
+  PartPlan *plan = nullptr;
+  int plan_nranks = 0;
+  std::vector<uint64_t> plan_scount;
   uint32_t prow() const { return kb + (cval_on ? 0 : vb); }                  // bytes per stored row
   uint64_t phys_bytes() const { return packed ? nkv * prow() : nbytes; }    // bytes of data in use
 
@@ -92,6 +96,7 @@ struct DevKV {
 
 inline DevKV::~DevKV()
 {
+  delete plan;
   pool->free(data, cap);
   pool->free(offs, offs_cap * 8);
 }
