@@ -371,15 +371,18 @@ def main():
     except Exception:
         traffic = None
     if dom:
-        roofline = {"bound": "hbm", "kernel": dom["tag"], "achieved": dom["gbs"], "peak": peak, "unit": "GB/s",
-                    "frac": (dom["gbs"] / peak) if dom["gbs"] else None, "traffic": traffic,
+        # achieved = the bytes the kernel has to move with the layout that is in HBM (header-less KV,
+        # 8 B/pair for the dominant kernel) / its time.  The reference record layout's figure for the same work
+        # (SURVEY.md 8d exact sizes, 36 B/pair) is kept beside it: against that one the rate exceeds the HBM peak,
+        # which is the point of the layout, not a measurement of the memory system.
+        mgbs = dom["moved_gbs"] or dom["gbs"]
+        roofline = {"bound": "hbm", "kernel": dom["tag"], "achieved": mgbs, "peak": peak, "unit": "GB/s",
+                    "frac": (mgbs / peak) if mgbs else None, "traffic": traffic,
                     "peak_source": peak_src, "launches_per_step": dom["calls"], "ms_per_launch": dom["ms_per_launch"],
                     "share_of_step": dom["ms"] / step_ms,
-                    "algorithmic_bytes_per_launch": dom["bytes"] / max(dom["calls"], 1),
-                    # compact stores: the kernel moves fewer bytes than the reference layout's
-                    # algorithmic figure, so `achieved` can exceed the HBM peak; these two use the bytes it really has to move
-                    "moved_bytes_per_launch": dom.get("moved", 0) / max(dom["calls"], 1),
-                    "achieved_moved": dom["moved_gbs"], "frac_moved": (dom["moved_gbs"] / peak) if dom["moved_gbs"] else None,
+                    "algorithmic_bytes_per_launch": (dom.get("moved", 0) or dom["bytes"]) / max(dom["calls"], 1),
+                    "reference_layout": {"algorithmic_bytes_per_launch": dom["bytes"] / max(dom["calls"], 1), "achieved": dom["gbs"],
+                                         "frac": (dom["gbs"] / peak) if dom["gbs"] else None},
                     "kernels": [{"tag": k["tag"], "ms": round(k["ms"], 4), "calls": k["calls"],
                                  "gbs": None if k["gbs"] is None else round(k["gbs"], 1),
                                  "moved_gbs": None if k["moved_gbs"] is None else round(k["moved_gbs"], 1)}
@@ -424,8 +427,10 @@ def main():
                        "parallelism": f"hash-partitioned ranks x{world}" if world > 1 else "1 rank"},
             "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu_baseline,
             "shuffle": shuffle,
-            "pipeline_algorithmic_bytes_per_step_per_gpu": alg,
-            "pipeline_gbs_per_gpu": alg / 1e9 / (step_ms / 1e3), "pipeline_frac_of_peak": alg / 1e9 / (step_ms / 1e3) / peak,
+            # what the whole step would have to move in the reference's record layout and the rate that
+            # corresponds to; with the compact stores the step moves a fraction of it, so this is not a utilisation
+            "pipeline_reference_layout_bytes_per_step_per_gpu": alg,
+            "pipeline_reference_layout_gbs_per_gpu": alg / 1e9 / (step_ms / 1e3),
         }
         real_stdout.write(json.dumps(line) + "\n")
         real_stdout.flush()
