@@ -78,3 +78,32 @@ def test_rmat_more_params(oracle):
         assert H.canon_kv(H.kv_decode(kv)) == H.canon_kv(H.kv_decode(ref_e))
         verts = oracle.edge_to_vertices(ref_e, both=(dup != 1))
         assert oracle.reduce(oracle.convert(verts), "count") == ref_d
+
+
+@pytest.mark.parametrize("seed,n,nkeys", [(51, 1, 1), (52, 3000, 40), (53, 2500, 2500)])
+def test_clone_collapse_compress_random(oracle, seed, n, nkeys):
+    """the ops widened in round 1: the Python restatements against the live reference on random pairs"""
+    kv = H.kv_encode(_random_kv(seed, n, nkeys))
+    assert oracle.clone(kv) == H.ref_ops(kv, ["clone", "dumpkmv"])
+    assert oracle.collapse(kv, b"all\0") == H.ref_ops(kv, ["collapse:all", "dumpkmv"])
+    for cb in ("count", "cull"):
+        assert oracle.compress(kv, cb) == H.ref_ops(kv, [f"compress_{cb}", "dumpkv"])
+
+
+@pytest.mark.parametrize("flag", [1, -1, 2, -2, 3, -3, 4, -4, 5, -5, 6, -6])
+def test_sort_values_random(oracle, flag):
+    r = np.random.RandomState(60 + abs(flag))
+    a = abs(flag)
+    n = 900
+    if a == 1:
+        vals = [struct.pack("<i", int(x)) for x in r.randint(-40, 40, size=n)]
+    elif a == 2:
+        vals = [struct.pack("<Q", int(x)) for x in r.randint(0, 30, size=n)]
+    elif a == 3:
+        vals = [struct.pack("<f", float(x) * 0.5) for x in r.randint(-20, 20, size=n)]
+    elif a == 4:
+        vals = [struct.pack("<d", float(x) * 0.25) for x in r.randint(-20, 20, size=n)]
+    else:
+        vals = [bytes(r.randint(97, 100, size=r.randint(0, 5)).astype(np.uint8)) + b"\0" for _ in range(n)]
+    kv = H.kv_encode([(struct.pack("<I", i), v) for i, v in enumerate(vals)])   # keys record the input order: ties must keep it
+    assert oracle.sort_values(kv, flag) == H.ref_ops(kv, [f"sort_values:{flag}", "dumpkv"])
