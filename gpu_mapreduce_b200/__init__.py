@@ -57,6 +57,7 @@ def lib():
     sig = {
         "mrgpu_create": [C.c_int, vp, C.POINTER(vp)],
         "mrgpu_destroy": [vp],
+        "mrgpu_abandon": [vp],
         "mrgpu_set": [vp, C.c_char_p, C.c_int64],
         "mrgpu_get": [vp, C.c_char_p, C.POINTER(C.c_int64)],
         "mrgpu_comm_unique_id": [vp],
@@ -133,7 +134,7 @@ class MapReduce:
 
     _SETTINGS = ("mapstyle", "all2all", "verbosity", "timer", "memsize", "minpage", "maxpage", "freepage",
                  "outofcore", "zeropage", "keyalign", "valuealign",
-                 "compact", "ahead")  # not reference members: 0 = stores always hold the reference's record streams (see mrgpu.h)
+                 "compact", "ahead", "l2pin", "debug_fail_alloc")  # not reference members: 0 = stores always hold the reference's record streams (see mrgpu.h)
 
     def __init__(self, device: int = 0, stream: int | None = None, rank: int = 0, nranks: int = 1,
                  unique_id: bytes | None = None):
@@ -167,13 +168,19 @@ class MapReduce:
         raise AttributeError(name)
 
     def destroy(self):
+        """~MapReduce (src/mapreduce.cpp:169).  COLLECTIVE once aggregate() has exchanged pairs between ranks, like the
+        reference's destructor (MPI_Comm_free): call it explicitly, on every rank, in the same order."""
         if self._h:
             lib().mrgpu_destroy(self._h)
             object.__setattr__(self, "_h", None)
 
     def __del__(self):
+        # The garbage collector runs finalisers in no particular order across ranks, so it must not enter a
+        # collective: mrgpu_abandon releases this rank's side without a barrier (see include/mrgpu.h).
         try:
-            self.destroy()
+            if self._h:
+                lib().mrgpu_abandon(self._h)
+                object.__setattr__(self, "_h", None)
         except Exception:
             pass
 

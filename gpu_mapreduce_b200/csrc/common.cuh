@@ -81,6 +81,8 @@ struct Pool {
   int device = 0;
   uint64_t live = 0, hiwater = 0;  // the reference's msize / msizemax (src/mapreduce.h:54)
   uint64_t reserved = 0;           // bytes obtained from cudaMalloc
+  int64_t fail_after = -1;         // test hook ("debug_fail_alloc" setting): the fail_after-th next alloc() throws
+  bool abandon = false;            // mrgpu_abandon(): peers may still map exported chunks, so those are never freed
   Prof prof;
 
   // Caching sub-allocator over big cudaMalloc'ed chunks.  The driver's own stream-ordered pool
@@ -136,6 +138,8 @@ struct Pool {
   }
   void *alloc(uint64_t bytes)
   {
+    if (fail_after >= 0 && fail_after-- == 0)
+      throw ::mrgpu::Error{-2, "out of GPU memory: allocation failure injected by the debug_fail_alloc setting"};
     if (bytes == 0) bytes = kGran;
     bytes = (bytes + kGran - 1) / kGran * kGran;
     auto it = by_size.lower_bound(bytes);
@@ -215,8 +219,8 @@ struct Pool {
   {
     if (chunks.empty()) return;
     cudaStreamSynchronize(stream);
-    for (auto &c : chunks)
-      if (c.first) cudaFree(c.first);
+    for (size_t c = 0; c < chunks.size(); c++)
+      if (chunks[c].first && !(abandon && exported.count((int) c))) cudaFree(chunks[c].first);
   }
 };
 

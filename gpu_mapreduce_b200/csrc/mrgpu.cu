@@ -53,9 +53,20 @@ struct mrgpu_mr {
   cudaEvent_t copy_ev[2] = {nullptr, nullptr};
   uint64_t dense_owner = 0;         // uid of the KV whose counts map_intcount already put in the table (0 = none)
   int64_t ahead = 1;                // setting: map_intcount may do the next op's first pass while it writes the keys
+  // setting "l2pin": MiB of convert's count table pinned in L2 (persisting access-policy window on the handle's stream
+  // + device-wide persisting set-aside) for the duration of one count launch; 0 = never touch that device state
+  int64_t l2pin = getenv("MRGPU_DENSE_L2PIN") ? atol(getenv("MRGPU_DENSE_L2PIN")) : 56;
+  int64_t debug_fail_alloc = -1;    // test hook: the n-th next pool allocation fails (-1 = off); mirrors pool.fail_after
+  cudaEvent_t order_ev = nullptr;   // orders this handle's stream behind another handle's (add, map(mr))
   bool p2p_used = false;  // set identically on every rank
   std::map<std::string, void *> ipc_open;  // peers' receive chunks mapped by the peer-store exchange (CUDA IPC handle -> base)
 };
+
+// A failed NCCL call leaves the communicator unusable and the peers inside a collective.  The reference ends the
+// job there (Error::one -> MPI_Abort, src/error.cpp:47-57); the library's part of that is ncclCommAbort, which
+// releases this rank's side so that nothing of it keeps the peers' kernels spinning; the caller (the C++ mirror's
+// Error::one, or the launcher when the process exits non-zero) ends the job.
+static void comm_abort_on_error(mrgpu_mr *mr);
 
 #define API_BEGIN(mr)                     \
   if (!(mr)) return MRGPU_EINVAL;         \
@@ -67,6 +78,7 @@ struct mrgpu_mr {
   catch (const Error &e)                  \
   {                                       \
     (mr)->err = e.msg;                    \
+    if (e.code == MRGPU_ECOMM) comm_abort_on_error(mr); \
     return e.code;                        \
   }                                       \
   catch (const std::exception &e)         \
@@ -116,6 +128,16 @@ static bool is_device_ptr(const void *p)
 // global sum over ranks of a per-rank count (the MPI_Allreduce at the end of every reference op)
 static uint64_t allreduce_sum(mrgpu_mr *mr, uint64_t v);
 
+// Two handles may have been created on different streams.  Work that `mr` is about to enqueue and that reads
+// memory written by work already enqueued on `other`'s stream is ordered behind it with an event (no host wait).
+static void order_after(mrgpu_mr *mr, mrgpu_mr *other)
+{
+  if (mr == other || mr->pool.stream == other->pool.stream) return;
+  if (!mr->order_ev) MR_CUDA(cudaEventCreateWithFlags(&mr->order_ev, cudaEventDisableTiming));
+  MR_CUDA(cudaEventRecord(mr->order_ev, other->pool.stream));
+  MR_CUDA(cudaStreamWaitEvent(mr->pool.stream, mr->order_ev, 0));
+}
+
 #include "ops_map.cuh"
 #include "ops_convert.cuh"
 #include "ops_convert_dense.cuh"
@@ -158,7 +180,7 @@ extern "C" int mrgpu_create(int device, void *stream, mrgpu_mr **out)
   return MRGPU_OK;
 }
 
-extern "C" int mrgpu_destroy(mrgpu_mr *mr)
+static int destroy_impl(mrgpu_mr *mr, bool collective)
 {
   if (!mr) return MRGPU_EINVAL;
   cudaSetDevice(mr->device);
@@ -167,10 +189,18 @@ extern "C" int mrgpu_destroy(mrgpu_mr *mr)
   cudaStreamSynchronize(mr->pool.stream);
   if (mr->comm) {
     // like MapReduce::~MapReduce's MPI_Comm_free (src/mapreduce.cpp:283), collective once ranks share memory:
-    // unmap the peers' buffers, then wait until every peer has unmapped mine before the pool frees it
-    if (mr->p2p_used) peer_store_teardown(mr);
+    // unmap the peers' buffers, then wait until every peer has unmapped mine before the pool frees it.
+    // mrgpu_abandon skips the barrier: my mappings are closed, and the chunks peers may still map are never freed.
+    if (mr->p2p_used) {
+      if (collective) peer_store_teardown(mr);
+      else {
+        peer_store_unmap(mr);
+        mr->pool.abandon = true;
+      }
+    }
     comm_destroy(mr);
   }
+  if (mr->order_ev) cudaEventDestroy(mr->order_ev);
   if (mr->copy_stream) cudaStreamDestroy(mr->copy_stream);
   for (auto e : mr->copy_ev)
     if (e) cudaEventDestroy(e);
@@ -179,6 +209,9 @@ extern "C" int mrgpu_destroy(mrgpu_mr *mr)
   delete mr;
   return MRGPU_OK;
 }
+
+extern "C" int mrgpu_destroy(mrgpu_mr *mr) { return destroy_impl(mr, true); }
+extern "C" int mrgpu_abandon(mrgpu_mr *mr) { return destroy_impl(mr, false); }
 
 extern "C" const char *mrgpu_last_error(const mrgpu_mr *mr) { return mr ? mr->err.c_str() : g_create_error.c_str(); }
 
@@ -190,7 +223,8 @@ static int64_t *setting(mrgpu_mr *mr, const char *name)
   } tab[] = {{"memsize", &mr->memsize},     {"keyalign", &mr->keyalign},   {"valuealign", &mr->valuealign},
              {"verbosity", &mr->verbosity}, {"timer", &mr->timer},         {"all2all", &mr->all2all},
              {"mapstyle", &mr->mapstyle},   {"minpage", &mr->minpage},     {"maxpage", &mr->maxpage},
-             {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage},   {"compact", &mr->compact},     {"ahead", &mr->ahead}};
+             {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage},   {"compact", &mr->compact},     {"ahead", &mr->ahead},
+             {"l2pin", &mr->l2pin},         {"debug_fail_alloc", &mr->debug_fail_alloc}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) return t.p;
   return nullptr;
@@ -203,7 +237,9 @@ extern "C" int mrgpu_set(mrgpu_mr *mr, const char *name, int64_t value)
   if (!p) MR_FAIL(MRGPU_EINVAL, std::string("unknown setting ") + name);
   if (mr->frozen && (!strcmp(name, "keyalign") || !strcmp(name, "valuealign") || !strcmp(name, "memsize")) && *p != value)
     MR_FAIL(MRGPU_EINVAL, "memsize/keyalign/valuealign are frozen after first use (src/mapreduce.cpp:3318)");
+  if (!strcmp(name, "l2pin") && (value < 0 || value > 1024)) MR_FAIL(MRGPU_EINVAL, "l2pin is a size in MiB between 0 and 1024");
   *p = value;
+  if (p == &mr->debug_fail_alloc) mr->pool.fail_after = value;
   API_END(mr)
 }
 

@@ -20,6 +20,7 @@ struct NcclApi {
   ncclResult_t (*GetUniqueId)(ncclUniqueId *);
   ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int);
   ncclResult_t (*CommDestroy)(ncclComm_t);
+  ncclResult_t (*CommAbort)(ncclComm_t);
   ncclResult_t (*GroupStart)();
   ncclResult_t (*GroupEnd)();
   ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
@@ -46,6 +47,7 @@ static NcclApi &nccl()
     NCCL_SYM(GetUniqueId, "ncclGetUniqueId")
     NCCL_SYM(CommInitRank, "ncclCommInitRank")
     NCCL_SYM(CommDestroy, "ncclCommDestroy")
+    NCCL_SYM(CommAbort, "ncclCommAbort")
     NCCL_SYM(GroupStart, "ncclGroupStart")
     NCCL_SYM(GroupEnd, "ncclGroupEnd")
     NCCL_SYM(Send, "ncclSend")
@@ -83,6 +85,22 @@ static void comm_destroy(mrgpu_mr *mr)
   for (auto &kvp : g_comms)
     if (kvp.second.comm == (ncclComm_t) mr->comm && kvp.second.refs > 0) kvp.second.refs--;
   mr->comm = nullptr;
+}
+
+static void comm_abort_on_error(mrgpu_mr *mr)
+{
+  if (!mr->comm) return;
+  std::lock_guard<std::mutex> lk(g_comms_mu);
+  ncclComm_t c = (ncclComm_t) mr->comm;
+  for (auto it = g_comms.begin(); it != g_comms.end();)
+    if (it->second.comm == c) it = g_comms.erase(it);
+    else ++it;
+  try {
+    nccl().CommAbort(c);
+  } catch (...) {
+  }
+  mr->comm = nullptr;  // every later collective on this handle fails with "communicator not initialised"
+  mr->err += " -- communicator aborted; the job cannot continue (the reference calls MPI_Abort here, src/error.cpp:47-57)";
 }
 
 extern "C" int mrgpu_comm_unique_id(void *id128)
@@ -132,6 +150,7 @@ extern "C" int mrgpu_comm_init(mrgpu_mr *mr, int rank, int nranks, const void *i
 static uint64_t allreduce_sum(mrgpu_mr *mr, uint64_t v)
 {
   if (mr->nranks == 1) return v;
+  if (!mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
   cudaStream_t s = mr->pool.stream;
   unsigned long long *d = mr->d_small + 32;
   MR_CUDA(cudaMemcpyAsync(d, &v, 8, cudaMemcpyHostToDevice, s));
@@ -357,11 +376,16 @@ static bool agree_packed(mrgpu_mr *mr, DevKV *kv, unsigned long long desc[3])
   return ok && have;
 }
 
-static void peer_store_teardown(mrgpu_mr *mr)
+static void peer_store_unmap(mrgpu_mr *mr)
 {
   for (auto &kvp : mr->ipc_open) cudaIpcCloseMemHandle(kvp.second);
   mr->ipc_open.clear();
   cudaGetLastError();
+}
+
+static void peer_store_teardown(mrgpu_mr *mr)
+{
+  peer_store_unmap(mr);
   try {
     allreduce_sum(mr, 1);
   } catch (...) {

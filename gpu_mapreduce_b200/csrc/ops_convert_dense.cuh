@@ -432,14 +432,17 @@ static void dense_prepare(mrgpu_mr *mr)
   } else if (mr->dense_owner) {  // counts made ahead for a KV that never reached convert()
     MR_CUDA(cudaMemsetAsync(mr->dense_table, 0, (uint64_t) DENSE_SLOTS * 4, s));
   }
-  mr->dense_owner = 0;
-  static bool attr_set[64] = {false};
-  if (mr->device < 64 && !attr_set[mr->device]) {
+  // from here on the caller counts into the table: it is "dirty, owned by nobody" until the caller hands it to a KV
+  // (emit_and_count) or the compaction in convert_dense has put the zeros back -- an error in between must not leave
+  // stale counts behind a clean flag
+  mr->dense_owner = ~0ull;
+  static std::atomic<bool> attr_set[64];
+  if (mr->device < 64 && !attr_set[mr->device].load()) {
     MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
     MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
     MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
     MR_CUDA(cudaFuncSetAttribute(dense_count_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, DENSE_CACHE * 4));
-    attr_set[mr->device] = true;
+    attr_set[mr->device].store(true);
   }
 }
 
@@ -447,49 +450,75 @@ static void dense_prepare(mrgpu_mr *mr)
 // policy window on the launching stream (persisting for the table, streaming for everything else) over an L2
 // set-aside of the same size.  Measured on IntCount (fused emit + count, 2^30 keys): no window 3.27 ms, 32 MiB
 // 3.01, 40 MiB 2.88, 48 MiB 2.72, 56 MiB 2.56, 60 MiB 2.57, 64 MiB 3.25, 96 MiB 3.59 -- the table's touched part is
-// 64 MiB there, but a set-aside beyond half of the 126 MiB L2 starves the streams.  `on = false` removes window and set-aside again:
-// the caller's stream and the device are left as they were found.
-static void dense_l2_window(mrgpu_mr *mr, bool on)
-{
-  static const char *e = getenv("MRGPU_DENSE_L2PIN");  // MiB of table to pin (0 = no window); default 56
-  static const long mib = e ? atol(e) : 56;
-  if (mib <= 0) return;
-  // handles on other host threads may be inside their own window on the same device: the set-aside is saved by
-  // the first one in and restored by the last one out
-  static std::mutex mu;
-  static size_t saved_limit[64] = {0};
-  static int depth[64] = {0};
-  const int dev = mr->device < 64 ? mr->device : 0;
-  size_t bytes = (size_t) mib << 20;
-  std::lock_guard<std::mutex> lk(mu);
-  if (on) {
+// 64 MiB there, but a set-aside beyond half of the 126 MiB L2 starves the streams.
+// This touches DEVICE-WIDE state (cudaLimitPersistingL2CacheSize) for the duration of one count launch, so it is a
+// setting ("l2pin", MiB, default 56, 0 = leave the device alone; include/mrgpu.h) and it is scoped: the guard's
+// destructor removes the stream's window and puts the set-aside back however the scope is left (error included).
+// A host application that runs its own persisting lines (a non-zero limit found on entry) keeps them: the limit is
+// only ever raised, the persisting lines are not reset, and the limit it had is restored.
+struct L2Window {
+  mrgpu_mr *mr;
+  bool active = false;
+  static std::mutex &mu()
+  {
+    static std::mutex m;
+    return m;
+  }
+  static size_t *saved() { static size_t v[64] = {0}; return v; }
+  static int *depth() { static int v[64] = {0}; return v; }
+  explicit L2Window(mrgpu_mr *m) : mr(m)
+  {
+    if (mr->l2pin <= 0 || !mr->dense_table) return;
+    const int dev = mr->device < 64 ? mr->device : 0;
+    size_t bytes = (size_t) mr->l2pin << 20;
     int maxp = 0, maxw = 0;
     cudaDeviceGetAttribute(&maxp, cudaDevAttrMaxPersistingL2CacheSize, mr->device);
     cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, mr->device);
     bytes = std::min(bytes, std::min((size_t) maxp, (size_t) maxw));
-    if (bytes == 0) return;
-    if (depth[dev]++ == 0) {
-      cudaDeviceGetLimit(&saved_limit[dev], cudaLimitPersistingL2CacheSize);
-      cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes);
+    if (bytes == 0) {
+      cudaGetLastError();
+      return;
     }
+    {
+      // handles on other host threads may be inside their own window on the same device: the set-aside is saved
+      // by the first one in and restored by the last one out
+      std::lock_guard<std::mutex> lk(mu());
+      if (depth()[dev]++ == 0) {
+        cudaDeviceGetLimit(&saved()[dev], cudaLimitPersistingL2CacheSize);
+        if (saved()[dev] < bytes) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes);
+      }
+    }
+    set_window(bytes);
+    active = true;
+    cudaGetLastError();  // a device without the feature: run without it
   }
-  cudaStreamAttrValue av;
-  memset(&av, 0, sizeof(av));
-  av.accessPolicyWindow.base_ptr = mr->dense_table;
-  av.accessPolicyWindow.num_bytes = on ? bytes : 0;
-  av.accessPolicyWindow.hitRatio = 1.0f;
-  av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-  av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-  cudaStreamSetAttribute(mr->pool.stream, cudaStreamAttributeAccessPolicyWindow, &av);
-  if (!on) {
+  void set_window(size_t bytes)
+  {
+    cudaStreamAttrValue av;
+    memset(&av, 0, sizeof(av));
+    av.accessPolicyWindow.base_ptr = mr->dense_table;
+    av.accessPolicyWindow.num_bytes = bytes;
+    av.accessPolicyWindow.hitRatio = 1.0f;
+    av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    cudaStreamSetAttribute(mr->pool.stream, cudaStreamAttributeAccessPolicyWindow, &av);
+  }
+  L2Window(const L2Window &) = delete;
+  L2Window &operator=(const L2Window &) = delete;
+  ~L2Window()
+  {
+    if (!active) return;
+    const int dev = mr->device < 64 ? mr->device : 0;
+    set_window(0);
     cudaStreamSynchronize(mr->pool.stream);  // the kernel that used the window is done before the set-aside goes
-    if (depth[dev] > 0 && --depth[dev] == 0) {
-      cudaCtxResetPersistingL2Cache();
-      cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, saved_limit[dev]);
+    std::lock_guard<std::mutex> lk(mu());
+    if (depth()[dev] > 0 && --depth()[dev] == 0) {
+      if (saved()[dev] == 0) cudaCtxResetPersistingL2Cache();  // nobody else's persisting lines can exist
+      cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, saved()[dev]);
     }
+    cudaGetLastError();
   }
-  cudaGetLastError();  // a device without the feature: run without it
-}
+};
 
 // map_intcount on one rank (ops_map.cuh): write the key column AND count it -- convert() then starts at the
 // compaction.  If the KV changes before convert() (append, add, ...) the counts are dropped.
@@ -500,9 +529,11 @@ static void emit_and_count(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64
   dense_prepare(mr);
   unsigned long long *flag = mr->d_small + 8, *key_bits = mr->d_small + 9;
   MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
-  dense_l2_window(mr, true);
+  unsigned long long h[2] = {1, 0};
   {
+    L2Window win(mr);
     // algorithmic bytes: map (input + KV out, 20 B/pair) + convert's read of the KV (16 B/pair); moved: 4 in, 4 out
+    {
     ProfScope ps(pool, "map_intcount_emit_count", (double) n * 36, 1, (double) n * 8);
     DenseArgs a{(const uint8_t *) keys, n, 4, 0, 4, 4, 0};
     if (((((uintptr_t) keys) | ((uintptr_t) kv->data)) & 31) == 0 && !getenv("MRGPU_DENSE_NO256"))
@@ -510,11 +541,10 @@ static void emit_and_count(mrgpu_mr *mr, DevKV *kv, const uint32_t *keys, uint64
     else
       dense_count_kernel<0><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, (int4 *) kv->data);
     MR_CUDA(cudaGetLastError());
+    }
+    MR_CUDA(cudaMemcpyAsync(h, flag, 16, cudaMemcpyDeviceToHost, s));
+    sync(mr);
   }
-  unsigned long long h[2] = {1, 0};
-  MR_CUDA(cudaMemcpyAsync(h, flag, 16, cudaMemcpyDeviceToHost, s));
-  sync(mr);
-  dense_l2_window(mr, false);
   kv->counted = true;
   kv->counted_bad = h[0] != 0;
   kv->counted_bits = h[1];
@@ -534,6 +564,7 @@ static void emit_from_host(mrgpu_mr *mr, DevKV *kv, const uint32_t *hkeys, uint6
     for (auto &e : mr->copy_ev) MR_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
   unsigned long long *flag = mr->d_small + 8, *key_bits = mr->d_small + 9;
+  const bool prepared = count;
   if (count) {
     dense_prepare(mr);
     MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
@@ -576,7 +607,8 @@ static void emit_from_host(mrgpu_mr *mr, DevKV *kv, const uint32_t *hkeys, uint6
   } else if (counted_any) {
     // counting was abandoned half way: the table holds counts of the first chunks
     mr->dense_owner = ~0ull;  // "dirty, owned by nobody": dense_prepare wipes it before the next use
-  }
+  } else if (prepared)
+    mr->dense_owner = 0;  // prepared, but no chunk was ever counted: the table is still all zero
 }
 
 // returns true if the dense path produced mr->kmv; false = not applicable, nothing changed
@@ -601,7 +633,7 @@ static bool convert_dense(mrgpu_mr *mr)
   if (!ahead) {
     dense_prepare(mr);
     MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
-    dense_l2_window(mr, true);
+    L2Window win(mr);
     ProfScope ps(pool, "convert_dense_count", (double) kv->nbytes, 1, (double) kv->phys_bytes());
     DenseArgs a{kv->data, n, rs, koff, voff, kb, svb};
     const bool a16 = ((uintptr_t) kv->data % 16) == 0;
@@ -612,8 +644,10 @@ static bool convert_dense(mrgpu_mr *mr)
     else dense_count_kernel<2><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, nullptr);
     MR_CUDA(cudaGetLastError());
   }
-  if (!ahead) dense_l2_window(mr, false);
-  mr->dense_owner = 0;  // the counts in the table are consumed (or wiped) below
+  // The table holds counts from here until the compaction below has put the zeros back (or the abort path has wiped
+  // it).  Anything that throws in between (pool.alloc out of memory at 2^30 keys, a CUDA error) leaves the handle
+  // usable, so the table must read "dirty": the next dense_prepare() then wipes it instead of trusting it.
+  mr->dense_owner = ~0ull;
   unsigned *table = mr->dense_table;
   unsigned long long h_flag[2] = {kv->counted_bad ? 1ull : 0ull, kv->counted_bits};
   uint32_t cv[2] = {0, 0};
@@ -623,6 +657,7 @@ static bool convert_dense(mrgpu_mr *mr)
   sync(mr);
   if (h_flag[0]) {  // a key or value the table cannot take: clean up, the sort path runs
     MR_CUDA(cudaMemsetAsync(table, 0, (uint64_t) DENSE_SLOTS * 4, s));
+    mr->dense_owner = 0;
     return false;
   }
   // every key is <= the OR of all keys: only that much of the table can hold counts
@@ -652,6 +687,7 @@ static bool convert_dense(mrgpu_mr *mr)
         tb[k] = 0;
       }
     }, "convert_dense_bins", (double) span * 4 + 12.0 * U);
+    mr->dense_owner = 0;  // the sink that re-zeroes every counted slot is enqueued: clean again
     kmv->factored = true;
     kmv->fval[0] = cv[0];
     kmv->fval[1] = cv[1];

@@ -385,6 +385,7 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
   // src == dst: the reference detaches the old KV, builds the new one, then deletes the old (:1584-1602, 1634)
   DevKV *src = srcmr->kv;
   kv_unpack(srcmr, src);  // the functors read records
+  order_after(mr, srcmr);  // the kernels below run on mr's stream and read what srcmr's stream wrote
   bool self = (srcmr == mr);
   if (self) mr->kv = nullptr;
   try {
@@ -455,10 +456,10 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
     throw;
   }
   if (self) delete src;
-  if (nkv) {
-    sync(mr);
-    *nkv = allreduce_sum(mr, mr->kv->nkv);
-  }
+  // another stream read srcmr's store: it must be done before srcmr (whose pool reuses memory in ITS stream's order)
+  // is used again
+  if (nkv || mr->pool.stream != srcmr->pool.stream) sync(mr);
+  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
   API_END(mr)
 }
 
@@ -603,10 +604,12 @@ extern "C" int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv)
   freeze(mr);
   freeze(other);
   if (mr->al.k != other->al.k || mr->al.v != other->al.v) MR_FAIL(MRGPU_EINVAL, "add: alignments differ");
+  if (mr->device != other->device) MR_FAIL(MRGPU_EINVAL, "add: the two MapReduce objects live on different devices");
   if (!mr->kv) mr->kv = new DevKV(&mr->pool);
   DevKV *kv = mr->kv, *o = other->kv;
   kv_unpack(mr, kv);
-  kv_unpack(other, o);
+  kv_unpack(other, o);   // enqueued on other's stream ...
+  order_after(mr, other);  // ... and read below on mine
   cudaStream_t s = mr->pool.stream;
   if (o->nkv) {
     uint64_t base = kv->nbytes;

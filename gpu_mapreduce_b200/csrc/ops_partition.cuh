@@ -442,10 +442,10 @@ static void partition_scatter_t(mrgpu_mr *mr, DevKV *kv, PartPlan &pl, const Des
   int nbits = 0;
   while ((1 << nbits) < P) nbits++;
   const size_t smem = (size_t) PART_TILE * RW * 4 + PART_TILE;
-  static bool attr[64] = {false};
-  if (mr->device < 64 && !attr[mr->device]) {
+  static std::atomic<bool> attr[64];  // per instantiation and device; the attribute call itself is idempotent
+  if (mr->device < 64 && !attr[mr->device].load()) {
     MR_CUDA(cudaFuncSetAttribute(partition_scatter_kernel<RW, KW, KOFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    attr[mr->device] = true;
+    attr[mr->device].store(true);
   }
   ProfScope ps(pool, tag, 2.0 * kv->nbytes, 1, 2.0 * kv->phys_bytes());
   partition_scatter_kernel<RW, KW, KOFF><<<(unsigned) pl.ntiles, PART_THREADS, direct ? 0 : smem, s>>>((const uint32_t *) kv->data, dp, kv->nkv, (uint32_t) P, nbits, pl.ntiles,

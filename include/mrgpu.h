@@ -66,8 +66,16 @@ enum {
 /* MapReduce::MapReduce(MPI_Comm) src/mapreduce.cpp:93 + defaults() :196-262.  device = CUDA ordinal,
  * stream = cudaStream_t (NULL = the legacy default stream). */
 int mrgpu_create(int device, void *stream, mrgpu_mr **out);
-/* MapReduce::~MapReduce src/mapreduce.cpp:169 */
+/* MapReduce::~MapReduce src/mapreduce.cpp:169.  Collective over the communicator once aggregate() has exchanged
+ * pairs by peer stores (the ranks unmap each other's receive buffers, then meet in a barrier before any is freed),
+ * like the reference destructor's MPI_Comm_free (src/mapreduce.cpp:283): every rank must call it, in the same
+ * order relative to its other collective calls on that communicator. */
 int mrgpu_destroy(mrgpu_mr *mr);
+/* No counterpart in the reference.  Non-collective teardown for places that cannot promise the above -- a garbage
+ * collector's finaliser, an error path on one rank: closes this rank's mappings of its peers' buffers, takes no
+ * barrier, and leaves the buffers its peers may still have mapped allocated until the process exits (freeing a
+ * buffer another process still maps is undefined in CUDA IPC).  Everything else is released. */
+int mrgpu_abandon(mrgpu_mr *mr);
 /* message of the last failure on this handle (or of the last failed mrgpu_create when mr == NULL) */
 const char *mrgpu_last_error(const mrgpu_mr *mr);
 
@@ -83,8 +91,16 @@ const char *mrgpu_last_error(const mrgpu_mr *mr);
  * "ahead" (default 1): mrgpu_map_intcount's pass over the keys also does the first pass of the op that follows
  * it in every pipeline on one rank (convert's key count); the work
  * is dropped if the KeyValue changes before that op runs.  0 turns this off.
- * mrgpu_destroy is collective over the communicator once aggregate() has exchanged pairs by peer stores
- * (like MapReduce::~MapReduce's MPI_Comm_free, src/mapreduce.cpp:283). */
+ * "l2pin" (MiB, default 56; 0 = off): convert()'s counting path keeps the busy part of its count table resident in
+ * L2 while it streams the keys past it.  For the duration of that ONE kernel launch it (a) puts a persisting
+ * access-policy window on the handle's stream and (b) raises the DEVICE-WIDE limit cudaLimitPersistingL2CacheSize
+ * to this many MiB if it is lower; when the launch has finished the window is removed and the limit restored, also
+ * on an error.  If the limit was 0 on entry the persisting lines are reset (cudaCtxResetPersistingL2Cache); if the
+ * host application had a limit of its own, its persisting lines are left alone.  A host that manages L2 persistence
+ * itself and does not want it touched sets l2pin = 0 (the count then runs about 25 % slower on the IntCount workload).
+ * "debug_fail_alloc" (test hook, default -1 = off): the n-th next allocation from the handle's HBM pool fails.
+ * A failed NCCL call aborts the handle's communicator (ncclCommAbort) before the call returns MRGPU_ECOMM: the job
+ * cannot continue, as after the reference's Error::one -> MPI_Abort (src/error.cpp:47-57). */
 int mrgpu_set(mrgpu_mr *mr, const char *name, int64_t value);
 int mrgpu_get(const mrgpu_mr *mr, const char *name, int64_t *value);
 
@@ -247,11 +263,14 @@ int mrgpu_sort_pairs(int device, void *stream, void *keys, void *payload, uint64
  * 16.5 MiB, resident on every GPU that loads the library until the process exits).  keys/payload stay yours.
  *  - Limit: n <= 1 048 576 pairs; a larger n fails with MRGPU_ELIMIT and a message that states the limit.
  *  - The first call on a device looks up the array's device address (one cudaGetSymbolAddress, cached
- *    afterwards).  Make that first call during start-up, before you begin any stream capture.
+ *    afterwards).  With lazy module loading that first call is also where the driver loads this library's GPU
+ *    module and gives the array its 16.5 MiB, so make it during start-up, while memory is still available.
+ *  - Every call takes a host mutex and ends in cudaStreamSynchronize: it must not be made while a stream capture
+ *    is in progress, the first call or any later one.
  *  - All calls share the one array per GPU and it keeps the previous call's contents; the call clears what it
  *    needs cleared.  Two calls whose GPU work overlaps on the same device (different streams or threads) race
  *    on the scratch and corrupt each other: serialise them.
- *  - Returns after the stream has drained, like mrgpu_sort_pairs(). */
+ *  - Returns after the stream has drained, like mrgpu_sort_pairs() (see the capture note above). */
 int mrgpu_sort_pairs_noalloc(int device, void *stream, void *keys, void *payload, uint64_t n, int key_bytes,
                              int payload_bytes);
 

@@ -373,6 +373,29 @@ def test_convert_dense_table_is_clean_between_calls(MR, oracle):
         assert H.canon_kv(mr.scan_kv()) == H.canon_kv(want)
 
 
+@pytest.mark.parametrize("ahead", [0, 1])
+@pytest.mark.parametrize("nth", [0, 1, 2])
+def test_convert_dense_survives_an_allocation_failure(MR, oracle, ahead, nth):
+    """an out-of-memory between the count and the compaction that re-zeroes the table (injected: the nth next pool
+    allocation fails) must not leave stale counts behind: the handle stays usable and the next convert is exact"""
+    import gpu_mapreduce_b200 as g
+
+    mr = MR(ahead=ahead)
+    r = np.random.RandomState(11 + nth)
+    keys = r.randint(0, 9000, size=120_000).astype(np.uint32)
+    mr.map_intcount(_torch().from_numpy(keys.view(np.int32)).cuda())
+    mr.debug_fail_alloc = nth + (0 if ahead else 0)
+    with pytest.raises(g.MRError, match="out of GPU memory"):
+        mr.convert()
+    mr.debug_fail_alloc = -1
+    keys2 = r.randint(3000, 12000, size=150_000).astype(np.uint32)    # overlaps the first key range
+    mr.map_intcount(_torch().from_numpy(keys2.view(np.int32)).cuda())
+    want = H.kv_decode(oracle.reduce(oracle.convert(oracle.intcount_map(keys2)), "count"))
+    assert mr.convert() == len(want)
+    mr.reduce("count")
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(want)
+
+
 def test_sort_keys_leaves_sorted_pairs_alone_and_still_sorts_the_rest(MR, oracle):
     recs = [(struct.pack("<i", k // 3 - 20), struct.pack("<I", k)) for k in range(30_000)]   # ascending, with ties
     mr = MR()
@@ -787,6 +810,41 @@ def test_add_appends_other_mr(MR):
     b.kv_add(rb)
     assert a.add(b) == 150
     assert a.scan_kv() == ra + rb
+
+
+def test_add_and_map_mr_across_streams():
+    """two handles on distinct non-blocking streams: add() / map(mr) write the other handle's header-less KV out as
+    records on ITS stream and read them on mine -- the result must not depend on which stream runs first"""
+    import gpu_mapreduce_b200 as g
+
+    torch = _torch()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    n = 1 << 22
+    keys = torch.randint(0, 1 << 20, (n,), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    a = g.MapReduce(device=0, stream=s1.cuda_stream)
+    b = g.MapReduce(device=0, stream=s2.cuda_stream)
+    c = g.MapReduce(device=0, stream=s1.cuda_stream)
+    hk = keys.cpu().numpy()
+
+    def records(mr):
+        return np.concatenate([np.frombuffer(page, dtype=np.int32) for _, page in mr.kv_pages()]).reshape(-1, 4)
+
+    try:
+        for rep in range(3):
+            assert b.map_intcount(keys) == n           # header-less (packed) KV on stream 2
+            a.kv_add([(struct.pack("<I", 7), struct.pack("<i", 1))])
+            assert a.add(b) == n + 1                   # unpack on stream 2, copy on stream 1
+            rec = records(a)
+            assert rec.shape[0] == n + 1 and rec[0, 2] == 7
+            assert np.array_equal(rec[1:, 2], hk) and np.all(rec[:, 3] == 1) and np.all(rec[:, :2] == 4)
+            b.map_intcount(keys)
+            assert c.map_mr(b, "invert") == n           # map(mr) from a header-less source on the other stream
+            rec = records(c)
+            assert np.array_equal(rec[:, 3], hk) and np.all(rec[:, 2] == 1)
+    finally:
+        for h in (a, b, c):
+            h.destroy()
 
 
 # ------------------------------------------------------------------------------------------- scale properties
