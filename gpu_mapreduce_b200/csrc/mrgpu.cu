@@ -56,6 +56,9 @@ struct mrgpu_mr {
   // setting "l2pin": MiB of convert's count table pinned in L2 (persisting access-policy window on the handle's stream
   // + device-wide persisting set-aside) for the duration of one count launch; 0 = never touch that device state
   int64_t l2pin = getenv("MRGPU_DENSE_L2PIN") ? atol(getenv("MRGPU_DENSE_L2PIN")) : 56;
+  // setting "combine": aggregate() ships one row [key | count] per distinct key instead of every pair when the pairs
+  // cannot be told apart (ops_aggregate.cuh); 0 = always the plain exchange in the reference's delivery order
+  int64_t combine = 1;
   int64_t debug_fail_alloc = -1;    // test hook: the n-th next pool allocation fails (-1 = off); mirrors pool.fail_after
   cudaEvent_t order_ev = nullptr;   // orders this handle's stream behind another handle's (add, map(mr))
   bool p2p_used = false;  // set identically on every rank
@@ -224,7 +227,8 @@ static int64_t *setting(mrgpu_mr *mr, const char *name)
              {"verbosity", &mr->verbosity}, {"timer", &mr->timer},         {"all2all", &mr->all2all},
              {"mapstyle", &mr->mapstyle},   {"minpage", &mr->minpage},     {"maxpage", &mr->maxpage},
              {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage},   {"compact", &mr->compact},     {"ahead", &mr->ahead},
-             {"l2pin", &mr->l2pin},         {"debug_fail_alloc", &mr->debug_fail_alloc}};
+             {"l2pin", &mr->l2pin},         {"combine", &mr->combine},
+                    {"debug_fail_alloc", &mr->debug_fail_alloc}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) return t.p;
   return nullptr;

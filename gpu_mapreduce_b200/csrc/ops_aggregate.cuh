@@ -333,11 +333,15 @@ static bool exchange_peer_store(mrgpu_mr *mr, DevKV *kv, DevKV *nk, PartPlan *pl
   if (allreduce_sum(mr, opened ? 0 : 1) != 0) return false;  // somebody could not map a peer: everyone falls back
   (void) rdisp;
   (void) brecv;
-  uint64_t wire = 0;
+  // bytes this rank puts on / takes off NVLink (its own share stays local): the report carries both
+  uint64_t wire = 0, wire_in = 0;
   for (int q = 0; q < P; q++)
-    if (q != me) wire += scount[q] * (kv->packed ? kv->prow() : kv->recsize);
+    if (q != me) {
+      wire += scount[q] * (kv->packed ? kv->prow() : kv->recsize);
+      wire_in += table[(size_t) q * W + 2 * me + 1];
+    }
   {
-    ProfScope ps(pool, "aggregate_exchange_nvlink", (double) wire, 0);  // brackets the scatter + the completion barrier
+    ProfScope ps(pool, "aggregate_exchange_nvlink", (double) wire, 0, (double) wire_in);  // brackets the scatter + the completion barrier
     if (n) partition_scatter(mr, kv, *pl, dp, "aggregate_partition_peer_store", true);
     allreduce_sum(mr, 1);  // barrier: every rank's stores have landed
   }
@@ -345,15 +349,17 @@ static bool exchange_peer_store(mrgpu_mr *mr, DevKV *kv, DevKV *nk, PartPlan *pl
 }
 
 // Do all ranks that hold pairs hold them header-less, in the same shape, with the same shared value?
-// desc = {has pairs, packed | cval_on << 1 | kb << 8 | vb << 32, cval}; on true, desc is that of the agreeing ranks.
-static bool agree_packed(mrgpu_mr *mr, DevKV *kv, unsigned long long desc[3])
+// desc = {has pairs, packed | cval_on << 1 | can_combine << 2 | kb << 8 | vb << 32, cval}; on true, desc is that of the
+// agreeing ranks.  *combine (in: this rank could run the combiner; out: every rank that holds pairs can).
+static bool agree_packed(mrgpu_mr *mr, DevKV *kv, unsigned long long desc[3], bool *combine)
 {
   Pool &pool = mr->pool;
   cudaStream_t s = pool.stream;
   const int P = mr->nranks;
   unsigned long long mine[3] = {kv->nkv ? 1ull : 0ull, 0, 0};
   if (kv->nkv && kv->packed) {
-    mine[1] = 1ull | ((unsigned long long) kv->cval_on << 1) | ((unsigned long long) kv->kb << 8) | ((unsigned long long) kv->vb << 32);
+    mine[1] = 1ull | ((unsigned long long) kv->cval_on << 1) | ((unsigned long long) (*combine ? 1 : 0) << 2) | ((unsigned long long) kv->kb << 8) |
+              ((unsigned long long) kv->vb << 32);
     mine[2] = kv->cval_on ? ((unsigned long long) kv->cval[1] << 32) | kv->cval[0] : 0;
   }
   Buf<unsigned long long> dm(pool, 3), da(pool, 3ull * P);
@@ -362,10 +368,11 @@ static bool agree_packed(mrgpu_mr *mr, DevKV *kv, unsigned long long desc[3])
   MR_NCCL(nccl().AllGather(dm.p, da.p, 3, ncclUint64, (ncclComm_t) mr->comm, s));
   MR_CUDA(cudaMemcpyAsync(all.data(), da.p, 24 * (size_t) P, cudaMemcpyDeviceToHost, s));
   sync(mr);
-  bool have = false, ok = true;
+  bool have = false, ok = true, all_can = true;
   for (int q = 0; q < P && ok; q++) {
     const unsigned long long *r = &all[3 * (size_t) q];
     if (!r[0]) continue;
+    if (!(r[1] & 4)) all_can = false;
     if (!(r[1] & 1)) ok = false;
     else if (!have) {
       desc[0] = 1, desc[1] = r[1], desc[2] = r[2];
@@ -373,6 +380,7 @@ static bool agree_packed(mrgpu_mr *mr, DevKV *kv, unsigned long long desc[3])
     } else if (r[1] != desc[1] || r[2] != desc[2])
       ok = false;
   }
+  *combine = ok && have && all_can;  // decided from the gathered rows only: the same answer on every rank
   return ok && have;
 }
 
@@ -401,16 +409,56 @@ static void aggregate_impl(mrgpu_mr *mr)
   Pool &pool = mr->pool;
   cudaStream_t s = pool.stream;
   const Align al = mr->al;
-  const uint64_t n = kv->nkv;
-  if (n >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "aggregate: more than 2^32-2 pairs on one GPU is not supported yet");
+  if (kv->nkv >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "aggregate: more than 2^32-2 pairs on one GPU is not supported yet");
   ncclComm_t comm = (ncclComm_t) mr->comm;
 
   // header-less rows travel as they are when every rank that holds pairs holds the same header-less shape;
   // otherwise they are written out as records first
+  if (kv->weighted) kv_unpack(mr, kv);  // a second aggregate() in a row: start from the records again
   if (kv->packed && !partition_eligible(mr, kv)) kv_unpack(mr, kv);
+
+  // The combiner.  Pairs that share one value (IntCount's int 1, OINK's NULL values) cannot be told apart once their
+  // keys are equal, so what the destination needs from this rank is, per distinct key, how many it had.  When every
+  // rank that holds pairs holds them as 4-byte integer keys below 2^26 with one shared value, each rank counts its
+  // own keys (convert's counting kernel -- or nothing at all when map_intcount already counted them while it wrote
+  // them), turns the non-empty table slots into rows [key | count] and THOSE are partitioned and exchanged: Zipf's
+  // hottest key crosses NVLink once per rank instead of 10^8 times, so neither the busiest port nor the rank that
+  // owns the key sees the skew.  It is the reference's own remedy -- compress() before aggregate()
+  // (src/mapreduce.cpp:749-851; cpu/IntCount.cpp:78 has it commented out) -- applied where it cannot change any
+  // result.  The receiver holds the rows as a weighted KV (store.cuh): same pair count, statistics and page table
+  // as the plain exchange; the pairs of one source come out grouped by key instead of in arrival order.
+  // Setting "combine" = 0 keeps the plain exchange (exact delivery order of the reference).
+  bool combine = mr->combine && kv->nkv && kv->packed && kv->cval_on && kv->kb == 4 && (kv->vb == 0 || kv->vb == 4 || kv->vb == 8) &&
+                 ((uintptr_t) kv->data % 16) == 0;
+  if (combine) {
+    if (!(kv->counted && kv->ahead_n == kv->nkv && mr->dense_owner == kv->uid)) dense_count_shared4(mr, kv);
+    if (kv->counted_bad) combine = false;  // a key the table cannot take
+  }
   unsigned long long wire_desc[3];
-  const bool packed_wire = agree_packed(mr, kv, wire_desc);
+  const bool packed_wire = agree_packed(mr, kv, wire_desc, &combine);
   if (kv->packed && !packed_wire) kv_unpack(mr, kv);
+  DevKV *const orig = kv;
+  DevKV *ck = nullptr;  // the rows [key | count] that stand in for this rank's pairs
+  struct CkGuard {
+    DevKV *&p;
+    ~CkGuard() { delete p; }
+  } ck_guard{ck};
+  if (combine && kv->nkv) {
+    Buf<uint2> rows;
+    const uint64_t U = dense_table_to_rows(mr, kv->counted_bits, rows);
+    ck = new DevKV(&pool);
+    ck->data = (uint8_t *) rows.detach();
+    ck->cap = (U ? U : 1) * 8;
+    ck->uniform = ck->packed = true;
+    ck->cval_on = false;
+    ck->kb = ck->vb = 4;
+    ck->recsize = kv_rec_size(al, 4, 4);
+    ck->nkv = U;
+    ck->nbytes = U * ck->recsize;
+    ck->ksize = ck->vsize = 4 * U;
+    kv = ck;
+  }
+  const uint64_t n = kv->nkv;
   const uint64_t row = kv->packed ? kv->prow() : kv->recsize;  // bytes per pair of a uniform KV as stored and sent
 
   Buf<uint8_t> sendbuf;
@@ -532,11 +580,11 @@ static void aggregate_impl(mrgpu_mr *mr)
         MR_CUDA(cudaGetLastError());
       }
     }
-    uint64_t wire = 0;
+    uint64_t wire = 0, wire_in = 0;  // sent / received over NVLink
     for (int p = 0; p < P; p++)
-      if (p != mr->rank) wire += sbytes[p] > rbytes[p] ? sbytes[p] : rbytes[p];
+      if (p != mr->rank) wire += sbytes[p], wire_in += rbytes[p];
     if (!delivered) {
-    ProfScope psx(pool, "aggregate_exchange_nvlink", (double) wire);
+    ProfScope psx(pool, "aggregate_exchange_nvlink", (double) wire, 1, (double) wire_in);
     MR_NCCL(nccl().GroupStart());
     for (int p = 0; p < P; p++) {
       if (p == mr->rank) continue;
@@ -571,6 +619,25 @@ static void aggregate_impl(mrgpu_mr *mr)
       }
       nk->ksize = nrecv * nk->kb;
       nk->vsize = nrecv * nk->vb;
+      if (combine) {
+        // what arrived are rows [key | count]: the KV they stand for has the senders' shape and shared value
+        nk->weighted = true;
+        nk->nrows = nrecv;
+        nk->kb = (uint32_t) ((wire_desc[1] >> 8) & 0xFFFFFF);
+        nk->vb = (uint32_t) (wire_desc[1] >> 32);
+        nk->recsize = kv_rec_size(al, nk->kb, nk->vb);
+        MR_CUDA(cudaMemsetAsync(mr->d_small, 0, 8, s));
+        if (nrecv) {
+          sum_multiplicities_kernel<<<grid_for(nrecv, 256 * 8, 8), 256, 0, s>>>((const uint2 *) nk->data, nrecv, mr->d_small);
+          MR_CUDA(cudaGetLastError());
+        }
+        fetch_small(mr, 1);
+        nk->nkv = mr->h_small[0];
+        if (nk->nkv >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "aggregate: a rank would receive more than 2^32-2 pairs");
+        nk->nbytes = nk->nkv * nk->recsize;
+        nk->ksize = nk->nkv * nk->kb;
+        nk->vsize = nk->nkv * nk->vb;
+      }
     } else if (nrecv) {
       nk->uniform = false;
       nk->reserve_offs(nrecv + 1);
@@ -592,6 +659,7 @@ static void aggregate_impl(mrgpu_mr *mr)
     delete nk;
     throw;
   }
+  (void) orig;
   delete mr->kv;
   mr->kv = nk;
 }

@@ -611,6 +611,96 @@ static void emit_from_host(mrgpu_mr *mr, DevKV *kv, const uint32_t *hkeys, uint6
     mr->dense_owner = 0;  // prepared, but no chunk was ever counted: the table is still all zero
 }
 
+// Weighted rows [key | multiplicity] (store.cuh) into the table: one RED per row.  Rows arrive from every source rank
+// with each key at most once per source, so no address is hit more than nranks times: no cache needed.
+__global__ void __launch_bounds__(256)
+dense_add_rows_kernel(const uint2 *__restrict__ rows, uint64_t nrows, unsigned *__restrict__ table, unsigned long long *abort_flag,
+                      unsigned long long *key_bits)
+{
+  uint32_t kor = 0;
+  bool bad = false;
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < nrows; i += stride) {
+    const uint2 r = __ldg(rows + i);
+    kor |= r.x;
+    if (r.x >= DENSE_SLOTS) bad = true;
+    else atomicAdd(&table[r.x], r.y);
+  }
+  kor = __reduce_or_sync(0xFFFFFFFFu, kor);
+  if ((threadIdx.x & 31) == 0 && kor) atomicOr(key_bits, (unsigned long long) kor);
+  if (bad) *abort_flag = 1;
+}
+
+__global__ void __launch_bounds__(256) sum_multiplicities_kernel(const uint2 *__restrict__ rows, uint64_t nrows, unsigned long long *out)
+{
+  unsigned long long s = 0;
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < nrows; i += stride) s += __ldg(&rows[i].y);
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+  if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+
+// Count the keys of a header-less KV of 4-byte keys that share one value into the handle's table (the first pass of
+// convert's counting path, also what aggregate()'s combiner starts from).  Afterwards the counts belong to that KV
+// (kv->counted ...) exactly as if map_intcount had made them while it wrote the keys.
+static void dense_count_shared4(mrgpu_mr *mr, DevKV *kv)
+{
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const uint64_t n = kv->nkv;
+  dense_prepare(mr);
+  unsigned long long *flag = mr->d_small + 8, *key_bits = mr->d_small + 9;
+  MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
+  unsigned long long h[2] = {1, 0};
+  {
+    L2Window win(mr);
+    {
+      ProfScope ps(pool, "convert_dense_count", (double) kv->nbytes, 1, (double) kv->phys_bytes());
+      DenseArgs a{kv->data, n, 4, 0, 4, 4, 0};
+      if (((uintptr_t) kv->data % 32) == 0 && !getenv("MRGPU_DENSE_NO256"))
+        dense_count_kernel<3><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, nullptr);
+      else if (((uintptr_t) kv->data % 16) == 0)
+        dense_count_kernel<0><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, nullptr);
+      else
+        dense_count_kernel<2><<<kSMs, MRGPU_DENSE_THREADS, DENSE_CACHE * 4, s>>>(a, mr->dense_table, flag, key_bits, nullptr);
+      MR_CUDA(cudaGetLastError());
+    }
+    MR_CUDA(cudaMemcpyAsync(h, flag, 16, cudaMemcpyDeviceToHost, s));
+    sync(mr);
+  }
+  kv->counted = true;
+  kv->counted_bad = h[0] != 0;
+  kv->counted_bits = h[1];
+  kv->ahead_n = n;
+  mr->dense_owner = kv->uid;
+}
+
+// The table's non-empty slots as rows [key | count] (ascending keys); every slot read is put back to zero, so the
+// table is clean afterwards.  key_bits = OR of all counted keys (bounds the scan).  Returns the number of rows.
+static uint64_t dense_table_to_rows(mrgpu_mr *mr, uint64_t key_bits, Buf<uint2> &rows)
+{
+  Pool &pool = mr->pool;
+  uint64_t span = 1;
+  while (span <= key_bits) span <<= 1;
+  mr->dense_owner = ~0ull;  // dirty until the sink below is enqueued
+  unsigned *tb = mr->dense_table;
+  auto nonzero = [=] __device__(uint64_t k) -> bool { return tb[k] != 0; };
+  FlagTiles bins;
+  flag_tiles(pool, span, nonzero, bins, mr->d_small, "aggregate_combine_bins", (double) span * 4);
+  fetch_small(mr, 1);
+  const uint64_t U = mr->h_small[0];
+  rows.alloc(pool, U ? U : 1);
+  uint2 *pr = rows.p;
+  flag_sink(pool, bins, nonzero, [=] __device__(uint64_t k, unsigned long long e, unsigned long long h) {
+    if (h) {
+      pr[e] = make_uint2((uint32_t) k, tb[k]);
+      tb[k] = 0;
+    }
+  }, "aggregate_combine_bins", (double) span * 4 + 8.0 * U);
+  mr->dense_owner = 0;
+  return U;
+}
+
 // returns true if the dense path produced mr->kmv; false = not applicable, nothing changed
 static bool convert_dense(mrgpu_mr *mr)
 {
@@ -621,16 +711,25 @@ static bool convert_dense(mrgpu_mr *mr)
   const uint64_t n = kv->nkv;
   const uint32_t kb = kv->kb, vb = kv->vb;
   if (!kv->uniform || (kb != 4 && kb != 8) || (vb != 0 && vb != 4 && vb != 8)) return false;
-  if ((al.k % 4) || (al.v % 4) || n < (1u << 16)) return false;  // small inputs: the table scan would dominate
+  const bool weighted = kv->weighted;
+  if ((al.k % 4) || (al.v % 4) || (n < (1u << 16) && !weighted)) return false;  // small inputs: the table scan would dominate
   // header-less rows (store.cuh): key at 0, value (if stored per pair) right after it
   const bool shared_val = kv->packed && kv->cval_on;
   const uint32_t rs = kv->packed ? kv->prow() : kv->recsize, koff = kv->packed ? 0 : kv_key_off(al), voff = kv->packed ? kb : kv_val_off(al, kb);
   const uint32_t svb = shared_val ? 0 : vb;  // value bytes the count kernel has to compare per pair
 
   // counts made by map_intcount while it wrote this very KV?
-  const bool ahead = kv->counted && kv->ahead_n == n && mr->dense_owner == kv->uid && shared_val && kb == 4;
+  const bool ahead = !weighted && kv->counted && kv->ahead_n == n && mr->dense_owner == kv->uid && shared_val && kb == 4;
   unsigned long long *flag = mr->d_small + 8, *key_bits = mr->d_small + 9;
-  if (!ahead) {
+  if (weighted) {  // rows [key | multiplicity] delivered by aggregate()'s combiner: add the multiplicities
+    dense_prepare(mr);
+    MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
+    if (kv->nrows) {
+      ProfScope ps(pool, "convert_dense_add_rows", (double) kv->nbytes, 1, (double) kv->phys_bytes());
+      dense_add_rows_kernel<<<grid_for(kv->nrows, 256 * 4, 16), 256, 0, s>>>((const uint2 *) kv->data, kv->nrows, mr->dense_table, flag, key_bits);
+      MR_CUDA(cudaGetLastError());
+    }
+  } else if (!ahead) {
     dense_prepare(mr);
     MR_CUDA(cudaMemsetAsync(flag, 0, 16, s));
     L2Window win(mr);
@@ -651,7 +750,7 @@ static bool convert_dense(mrgpu_mr *mr)
   unsigned *table = mr->dense_table;
   unsigned long long h_flag[2] = {kv->counted_bad ? 1ull : 0ull, kv->counted_bits};
   uint32_t cv[2] = {0, 0};
-  if (!ahead) MR_CUDA(cudaMemcpyAsync(h_flag, flag, 16, cudaMemcpyDeviceToHost, s));
+  if (!ahead || weighted) MR_CUDA(cudaMemcpyAsync(h_flag, flag, 16, cudaMemcpyDeviceToHost, s));
   if (shared_val) cv[0] = kv->cval[0], cv[1] = kv->cval[1];
   else if (vb) MR_CUDA(cudaMemcpyAsync(cv, kv->data + voff, vb, cudaMemcpyDeviceToHost, s));
   sync(mr);

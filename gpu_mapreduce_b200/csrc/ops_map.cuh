@@ -83,9 +83,67 @@ static void kv_unpack_rows(mrgpu_mr *mr, const DevKV *kv, uint64_t first, uint64
   MR_CUDA(cudaGetLastError());
 }
 
+// weighted rows [key | multiplicity] -> records: output record i belongs to the row r with start[r] <= i < start[r+1]
+// (start = exclusive prefix sum of the multiplicities); one thread per record, binary search over start[].
+// Not on any hot path: a weighted KV is expanded only when somebody asks for its bytes.
+__global__ void __launch_bounds__(256)
+kv_expand_weighted_kernel(const uint2 *__restrict__ rows, const uint64_t *__restrict__ start, uint64_t nrows, uint64_t total, uint32_t vw, uint32_t c0,
+                          uint32_t c1, uint32_t *__restrict__ out)
+{
+  const uint32_t rw = 3 + vw;
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    uint64_t lo = 0, hi = nrows - 1;
+    while (lo < hi) {
+      const uint64_t mid = (lo + hi + 1) >> 1;
+      if (__ldg(start + mid) <= i) lo = mid;
+      else hi = mid - 1;
+    }
+    const uint32_t key = __ldg(&rows[lo].x);
+    uint32_t *o = out + i * rw;
+    if (vw == 1) *(int4 *) o = make_int4(4, 4, (int) key, (int) c0);
+    else {
+      o[0] = 4;
+      o[1] = vw * 4;
+      o[2] = key;
+      if (vw == 2) o[3] = c0, o[4] = c1;
+    }
+  }
+}
+
+static void kv_unpack_weighted(mrgpu_mr *mr, DevKV *kv)
+{
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const uint64_t R = kv->nrows, total = kv->nkv;
+  uint8_t *nd = (uint8_t *) pool.alloc(kv->nbytes ? kv->nbytes : 16);
+  if (R && total) {
+    Buf<uint64_t> start(pool, R + 1);
+    const uint2 *rows = (const uint2 *) kv->data;
+    uint64_t *st = start.p;
+    scan_apply(
+        pool, R, [=] __device__(uint64_t r) -> unsigned long long { return rows[r].y; },
+        [=] __device__(uint64_t r, unsigned long long e, unsigned long long) { st[r] = e; }, mr->d_small, "kv_unpack_weighted_scan", 8.0 * R);
+    ProfScope ps(pool, "kv_unpack_weighted", (double) R * 8 + (double) kv->nbytes);
+    kv_expand_weighted_kernel<<<grid_for(total, 256, 32), 256, 0, s>>>(rows, st, R, total, kv->vb / 4, kv->cval[0], kv->cval[1], (uint32_t *) nd);
+    MR_CUDA(cudaGetLastError());
+    MR_CUDA(cudaStreamSynchronize(s));  // start[] is released on return; same stream, but keep the expansion simple to reason about
+  }
+  pool.free(kv->data, kv->cap);
+  kv->data = nd;
+  kv->cap = kv->nbytes ? kv->nbytes : 16;
+  kv->packed = kv->cval_on = kv->weighted = false;
+  kv->nrows = 0;
+  kv->cval[0] = kv->cval[1] = 0;
+}
+
 static void kv_unpack(mrgpu_mr *mr, DevKV *kv)
 {
   if (!kv || !kv->packed) return;
+  if (kv->weighted) {
+    kv_unpack_weighted(mr, kv);
+    return;
+  }
   if (kv->nkv) {
     Pool &pool = mr->pool;
     uint8_t *nd = (uint8_t *) pool.alloc(kv->nbytes);
@@ -245,7 +303,7 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
   // header-less KV from host memory: the key column is filled by DMA (55.6 GB/s measured against 51.7 GB/s for a
   // kernel reading pinned memory through its device alias), in chunks so that counting overlaps the transfer
   if (n && !is_device_ptr(keys) && kv_can_pack(mr, 4, 4) &&
-      (kv->nkv == 0 || (kv->packed && kv->cval_on && kv->kb == 4 && kv->vb == 4 && kv->cval[0] == 1))) {
+      (kv->nkv == 0 || (kv->packed && !kv->weighted && kv->cval_on && kv->kb == 4 && kv->vb == 4 && kv->cval[0] == 1))) {
     if (kv->nkv == 0) {
       kv->uniform = kv->packed = kv->cval_on = true;
       kv->kb = kv->vb = 4;
@@ -254,7 +312,7 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
       kv->cval[1] = 0;
     }
     kv->reserve_bytes((kv->nkv + n) * 4);
-    const bool count = kv->nkv == 0 && mr->ahead && mr->nranks == 1 && n >= (1u << 16);
+    const bool count = kv->nkv == 0 && mr->ahead && (mr->nranks == 1 || mr->combine) && n >= (1u << 16);
     emit_from_host(mr, kv, keys, n, count);
     kv_commit_uniform(kv, 4, 4, 16, n);
     kv->h_offs_valid = false;
@@ -267,7 +325,7 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
   const uint32_t *dk = stage_input(mr, keys, n, tmp);
   // header-less: every pair is {4, 4, key, 1}, so the KV is the key column plus one shared value
   const bool pack = kv_can_pack(mr, 4, 4) &&
-                    (kv->nkv == 0 || (kv->packed && kv->cval_on && kv->kb == 4 && kv->vb == 4 && kv->cval[0] == 1));
+                    (kv->nkv == 0 || (kv->packed && !kv->weighted && kv->cval_on && kv->kb == 4 && kv->vb == 4 && kv->cval[0] == 1));
   if (pack) {
     if (kv->nkv == 0) {
       kv->uniform = kv->packed = kv->cval_on = true;
@@ -282,7 +340,8 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
     // destination and the per-tile counts (1.89 ms fused against 1.38 + 1.82 apart at two ranks; a first, word-
     // per-lane version of the fused pass had been slower than the two apart: 4.19 against 3.87 ms).
     const bool fresh = kv->nkv == 0 && mr->ahead && n >= (1u << 16) && ((((uintptr_t) dk) | ((uintptr_t) kv->data)) & 15) == 0;
-    if (fresh && mr->nranks == 1) {
+    // (with several ranks and the combiner on, aggregate() starts from the same key counts: ops_aggregate.cuh)
+    if (fresh && (mr->nranks == 1 || mr->combine)) {
       emit_and_count(mr, kv, dk, n);
     } else if (fresh && mr->nranks > 1 && mr->nranks <= 256 && !getenv("MRGPU_NO_EMIT_PLAN")) {
       emit_and_plan(mr, kv, dk, n);

@@ -187,6 +187,7 @@ extern "C" int mrgpu_kv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst)
   if (ipage >= np) MR_FAIL(MRGPU_EINVAL, "page index out of range");
   if (sl.end > sl.begin) {
     if (!dst) MR_FAIL(MRGPU_EINVAL, "null destination");
+    if (mr->kv->weighted) kv_unpack(mr, mr->kv);  // rows [key | count] -> records, once; pages are then plain slices
     if (mr->kv->packed) {  // header-less rows: write this page's records out, the KV itself stays as it is
       Buf<uint8_t> tmp(mr->pool, sl.end - sl.begin);
       kv_unpack_rows(mr, mr->kv, sl.first, sl.nkey, tmp.p);

@@ -48,6 +48,13 @@ struct DevKV {
   bool packed = false;
   bool cval_on = false;
   uint32_t cval[2] = {0, 0};
+  // Weighted form (what aggregate()'s combiner delivers, ops_aggregate.cuh): pairs that share one value cannot be
+  // told apart once their keys are equal, so a run of m equal pairs is kept as ONE row [key | m].  packed and
+  // cval_on are set; data holds nrows rows of kb + 4 bytes; nkv = sum of the multiplicities, and nbytes / ksize /
+  // vsize / the page table describe the nkv records of the reference's stream, which kv_unpack() writes out when
+  // its bytes are needed.  Rows are grouped by source rank; within a source they are in ascending key order.
+  bool weighted = false;
+  uint64_t nrows = 0;
   // Work done ahead at emit time (map_intcount on one rank, ops_map.cuh): the pass that wrote the key column
   // also counted the keys into the handle's table, which is convert's first pass.  Valid only while nkv == ahead_n.
   uint64_t uid = 0;            // identity of this KV among the handle's stores
@@ -58,8 +65,8 @@ struct DevKV {
   PartPlan *plan = nullptr;
   int plan_nranks = 0;
   std::vector<uint64_t> plan_scount;
-  uint32_t prow() const { return kb + (cval_on ? 0 : vb); }                  // bytes per stored row
-  uint64_t phys_bytes() const { return packed ? nkv * prow() : nbytes; }    // bytes of data in use
+  uint32_t prow() const { return weighted ? kb + 4 : kb + (cval_on ? 0 : vb); }                  // bytes per stored row
+  uint64_t phys_bytes() const { return packed ? (weighted ? nrows : nkv) * prow() : nbytes; }   // bytes of data in use
 
   explicit DevKV(Pool *p) : pool(p)
   {

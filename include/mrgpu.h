@@ -91,6 +91,14 @@ const char *mrgpu_last_error(const mrgpu_mr *mr);
  * "ahead" (default 1): mrgpu_map_intcount's pass over the keys also does the first pass of the op that follows
  * it in every pipeline on one rank (convert's key count); the work
  * is dropped if the KeyValue changes before that op runs.  0 turns this off.
+ * "combine" (default 1): aggregate() on several ranks, when every rank's pairs are 4-byte integer keys below 2^26
+ * that all carry the same value (what mrgpu_map_intcount emits): such pairs cannot be told apart once their keys are
+ * equal, so each rank sends one row (key, how many) per distinct key instead of every pair -- the reference's own
+ * remedy for skewed keys, compress() before aggregate() (src/mapreduce.cpp:749-851, cpu/IntCount.cpp:78), applied
+ * where it cannot change a result.  Pair counts, statistics, page table and every later result are those of the
+ * plain exchange; the one observable difference is the ORDER of the pairs inside the KeyValue after aggregate():
+ * still by source rank, but within a source by ascending key instead of arrival order.  0 = always the plain
+ * exchange, in the reference's delivery order.  Must be the same on every rank.
  * "l2pin" (MiB, default 56; 0 = off): convert()'s counting path keeps the busy part of its count table resident in
  * L2 while it streams the keys past it.  For the duration of that ONE kernel launch it (a) puts a persisting
  * access-policy window on the handle's stream and (b) raises the DEVICE-WIDE limit cudaLimitPersistingL2CacheSize

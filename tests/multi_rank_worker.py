@@ -124,8 +124,11 @@ def main_nccl():
     def ic_keys(q, variant):
         return W.intcount_keys_np(q * 80000, (q + 1) * 80000, ndistinct=2000) if not (variant == 2 and q == 0) else np.zeros(0, np.uint32)
 
-    for variant in range(4):
+    # With the combiner on (default) and every rank holding such rows, what crosses the wire is one row (key, count) per
+    # distinct key: same pairs on the same ranks, grouped by key inside each source's segment (include/mrgpu.h "combine").
+    for variant, combine in [(v, c) for v in range(4) for c in (1, 0)]:
         mr = g.MapReduce(device=local, rank=rank, nranks=world, unique_id=uid)
+        mr.combine = combine
         if variant == 1 and rank == 1:
             mr.compact = 0
         keys = ic_keys(rank, variant)
@@ -138,15 +141,31 @@ def main_nccl():
             shards[world - 1] = shards[world - 1] + [(b"wide-key", b"")]
             total += 1
         assert mr.aggregate() == total
+        combined = combine == 1 and variant in (0, 2)
         want = []
         for q in range(world):
             dest = orc.partition(H.kv_encode(shards[q]), world) if shards[q] else []
-            want += [rec for rec, d in zip(shards[q], dest) if d == rank]
-        assert mr.scan_kv() == want, f"intcount variant {variant}: wrong pairs/order on rank {rank}"
+            seg = [rec for rec, d in zip(shards[q], dest) if d == rank]
+            if combined:
+                seg.sort(key=lambda kv_: struct.unpack("<I", kv_[0])[0])
+            want += seg
+        st = mr.kv_stats()                           # statistics describe the full record stream either way
+        assert st.npair == len(want) and st.keysize == 4 * len(want) and st.alignsize == 16 * len(want)
+        assert mr.scan_kv() == want, f"intcount variant {variant} combine {combine}: wrong pairs/order on rank {rank}"
+        if variant == 0:                             # once from the expanded records (scan above), once from the rows as delivered
+            mr.map_intcount(keys)
+            mr.aggregate()
         nuniq = mr.convert()
         assert mr.reduce("count") == nuniq
+        got = mr.scan_kv()
+        bc = {}
+        for q in range(world):
+            for k, _ in shards[q]:
+                bc[k] = bc.get(k, 0) + 1
+        mine = {k: c for k, c in bc.items() if orc.hashlittle(k, world) % world == rank}
+        assert {k: struct.unpack("<i", v)[0] for k, v in got} == mine, f"intcount variant {variant} combine {combine}: counts differ on rank {rank}"
         counts = [None] * world
-        dist.all_gather_object(counts, sum(struct.unpack("<i", v)[0] for _, v in mr.scan_kv()))
+        dist.all_gather_object(counts, sum(struct.unpack("<i", v)[0] for _, v in got))
         assert sum(counts) == total
         mr.destroy()
 
