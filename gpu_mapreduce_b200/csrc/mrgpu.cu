@@ -61,6 +61,12 @@ struct mrgpu_mr {
   int64_t combine = 1;
   int64_t debug_fail_alloc = -1;    // test hook: the n-th next pool allocation fails (-1 = off); mirrors pool.fail_after
   cudaEvent_t order_ev = nullptr;   // orders this handle's stream behind another handle's (add, map(mr))
+  // The global pair count of the current store when the last collective call computed it (1 = of the KV, 2 = of the
+  // KMV, 0 = unknown).  Ops that cannot change it (aggregate: pairs only move; sort; reduce with a stock functor: one
+  // pair per KMV pair) return it without another all-reduce.  Evolves identically on every rank because every rank
+  // makes the same calls in the same order (SURVEY.md 8b "Threading").
+  int g_what = 0;
+  uint64_t g_count = 0;
   bool p2p_used = false;  // set identically on every rank
   std::map<std::string, void *> ipc_open;  // peers' receive chunks mapped by the peer-store exchange (CUDA IPC handle -> base)
 };
@@ -81,6 +87,7 @@ static void comm_abort_on_error(mrgpu_mr *mr);
   catch (const Error &e)                  \
   {                                       \
     (mr)->err = e.msg;                    \
+    (mr)->g_what = 0;                     \
     if (e.code == MRGPU_ECOMM) comm_abort_on_error(mr); \
     return e.code;                        \
   }                                       \
@@ -130,6 +137,15 @@ static bool is_device_ptr(const void *p)
 
 // global sum over ranks of a per-rank count (the MPI_Allreduce at the end of every reference op)
 static uint64_t allreduce_sum(mrgpu_mr *mr, uint64_t v);
+enum { G_NONE = 0, G_KV = 1, G_KMV = 2 };
+static uint64_t global_count(mrgpu_mr *mr, uint64_t local, int what, bool reuse)
+{
+  if (reuse && mr->g_what == what) return mr->g_count;
+  mr->g_what = G_NONE;
+  mr->g_count = allreduce_sum(mr, local);
+  mr->g_what = what;
+  return mr->g_count;
+}
 
 // Two handles may have been created on different streams.  Work that `mr` is about to enqueue and that reads
 // memory written by work already enqueued on `other`'s stream is ordered behind it with an event (no host wait).

@@ -671,7 +671,7 @@ extern "C" int mrgpu_aggregate(mrgpu_mr *mr, uint64_t *nkv)
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
   aggregate_impl(mr);
   sync(mr);
-  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);  // pairs only moved: the global count is the one before
   API_END(mr)
 }
 
@@ -681,9 +681,10 @@ extern "C" int mrgpu_collate(mrgpu_mr *mr, uint64_t *nkmv)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot collate without KeyValue");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
   aggregate_impl(mr);  // src/mapreduce.cpp:726-727: aggregate(hash); convert();
+  mr->g_what = G_NONE;
   convert_impl(mr);
   sync(mr);
-  if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
+  if (nkmv) *nkmv = global_count(mr, mr->kmv->nkmv, G_KMV, false);
   API_END(mr)
 }
 
@@ -797,6 +798,7 @@ extern "C" int mrgpu_gather(mrgpu_mr *mr, int numprocs, uint64_t *nkv)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot gather without KeyValue");
   if (numprocs < 1 || numprocs > mr->nranks) MR_FAIL(MRGPU_EINVAL, "Invalid processor count for gather");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  mr->g_what = G_NONE;
   gather_impl(mr, numprocs);
   if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
   API_END(mr)
@@ -874,6 +876,7 @@ extern "C" int mrgpu_broadcast(mrgpu_mr *mr, int root, uint64_t *nkv)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot broadcast without KeyValue");
   if (root < 0 || root >= mr->nranks) MR_FAIL(MRGPU_EINVAL, "Invalid root for broadcast");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  mr->g_what = G_NONE;
   broadcast_impl(mr, root);
   if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
   API_END(mr)
@@ -887,6 +890,7 @@ extern "C" int mrgpu_scrunch(mrgpu_mr *mr, int numprocs, const void *key, int ke
   if (numprocs < 1 || numprocs > mr->nranks) MR_FAIL(MRGPU_EINVAL, "Invalid processor count for gather");
   if (keybytes < 0 || (keybytes && !key)) MR_FAIL(MRGPU_EINVAL, "bad key");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  mr->g_what = G_NONE;
   gather_impl(mr, numprocs);
   collapse_impl(mr, key, keybytes);
   if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);

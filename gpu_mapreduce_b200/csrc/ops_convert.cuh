@@ -648,8 +648,9 @@ extern "C" int mrgpu_convert(mrgpu_mr *mr, uint64_t *nkmv)
 {
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot convert without KeyValue");
+  mr->g_what = G_NONE;
   convert_impl(mr);
   sync(mr);
-  if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
+  if (nkmv) *nkmv = global_count(mr, mr->kmv->nkmv, G_KMV, false);
   API_END(mr)
 }

@@ -17,6 +17,7 @@ static void emit_from_host(mrgpu_mr *mr, DevKV *kv, const uint32_t *hkeys, uint6
 static void kv_begin_map(mrgpu_mr *mr, int addflag, bool keep_packed = false)
 {
   freeze(mr);
+  mr->g_what = G_NONE;
   delete mr->kmv;
   mr->kmv = nullptr;
   if (!addflag || !mr->kv) {
@@ -318,7 +319,7 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
     kv->h_offs_valid = false;
     if (nkv) {
       sync(mr);
-      *nkv = allreduce_sum(mr, kv->nkv);
+      *nkv = global_count(mr, kv->nkv, G_KV, false);
     }
     return MRGPU_OK;
   }
@@ -355,7 +356,7 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
     tmp.release();
     if (nkv) {
       sync(mr);
-      *nkv = allreduce_sum(mr, kv->nkv);
+      *nkv = global_count(mr, kv->nkv, G_KV, false);
     }
     return MRGPU_OK;
   }
@@ -374,7 +375,7 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
   tmp.release();
   if (nkv) {
     sync(mr);
-    *nkv = allreduce_sum(mr, kv->nkv);
+    *nkv = global_count(mr, kv->nkv, G_KV, false);
   }
   API_END(mr)
 }
@@ -518,7 +519,7 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
   // another stream read srcmr's store: it must be done before srcmr (whose pool reuses memory in ITS stream's order)
   // is used again
   if (nkv || mr->pool.stream != srcmr->pool.stream) sync(mr);
-  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, false);
   API_END(mr)
 }
 
@@ -640,7 +641,7 @@ extern "C" int mrgpu_map_rmat(mrgpu_mr *mr, uint64_t ngenerate, int nlevels, dou
   *state48 = x;
   if (nkv) {
     sync(mr);
-    *nkv = allreduce_sum(mr, kv->nkv);
+    *nkv = global_count(mr, kv->nkv, G_KV, false);
   }
   API_END(mr)
 }
@@ -660,6 +661,7 @@ extern "C" int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv)
   if (!other || !other->kv) MR_FAIL(MRGPU_ENOKV, "MapReduce passed to add() does not have KeyValue pairs");
   if (mr == other) MR_FAIL(MRGPU_EINVAL, "Cannot add to self");
   if (mr->kmv) MR_FAIL(MRGPU_EINVAL, "Cannot add to a MapReduce with KeyMultiValue pairs");  // :351-353
+  mr->g_what = G_NONE;
   freeze(mr);
   freeze(other);
   if (mr->al.k != other->al.k || mr->al.v != other->al.v) MR_FAIL(MRGPU_EINVAL, "add: alignments differ");
@@ -694,6 +696,6 @@ extern "C" int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv)
     kv->h_offs_valid = false;
   }
   sync(mr);
-  if (nkv) *nkv = allreduce_sum(mr, kv->nkv);
+  if (nkv) *nkv = global_count(mr, kv->nkv, G_KV, false);
   API_END(mr)
 }

@@ -205,8 +205,11 @@ extern "C" int mrgpu_reduce(mrgpu_mr *mr, int functor, uint64_t *nkv)
 {
   API_BEGIN(mr)
   if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "Cannot reduce without KeyMultiValue");
+  const bool had = mr->g_what == G_KMV;  // every stock functor emits exactly one pair per KMV pair
+  mr->g_what = G_NONE;
   reduce_impl(mr, functor);
-  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  if (had) mr->g_what = G_KV;
+  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);
   API_END(mr)
 }
 
@@ -217,6 +220,7 @@ extern "C" int mrgpu_compress(mrgpu_mr *mr, int functor, uint64_t *nkv)
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot compress without KeyValue");
   if (functor < 0 || functor > MRGPU_REDUCE_CULL) MR_FAIL(MRGPU_EINVAL, "unknown reduce functor");
+  mr->g_what = G_NONE;
   convert_impl(mr);
   reduce_impl(mr, functor);
   if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);

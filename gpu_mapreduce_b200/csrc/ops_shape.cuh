@@ -180,6 +180,7 @@ extern "C" int mrgpu_clone(mrgpu_mr *mr, uint64_t *nkmv)
 {
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot clone without KeyValue");
+  mr->g_what = G_NONE;
   clone_impl(mr);
   if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
   API_END(mr)
@@ -190,6 +191,7 @@ extern "C" int mrgpu_collapse(mrgpu_mr *mr, const void *key, int keybytes, uint6
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot collapse without KeyValue");
   if (keybytes < 0 || (keybytes && !key)) MR_FAIL(MRGPU_EINVAL, "bad key");
+  mr->g_what = G_NONE;
   collapse_impl(mr, key, keybytes);
   if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
   API_END(mr)

@@ -264,7 +264,7 @@ extern "C" int mrgpu_sort_keys(mrgpu_mr *mr, int flag, uint64_t *nkv)
   kv_unpack(mr, mr->kv);
   sort_keys_impl(mr, flag);
   sync(mr);
-  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);
   API_END(mr)
 }
 
@@ -276,6 +276,6 @@ extern "C" int mrgpu_sort_values(mrgpu_mr *mr, int flag, uint64_t *nkv)
   kv_unpack(mr, mr->kv);
   sort_keys_impl(mr, flag, true);
   sync(mr);
-  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);
   API_END(mr)
 }

@@ -150,11 +150,12 @@ def main_nccl():
                 seg.sort(key=lambda kv_: struct.unpack("<I", kv_[0])[0])
             want += seg
         st = mr.kv_stats()                           # statistics describe the full record stream either way
-        assert st.npair == len(want) and st.keysize == 4 * len(want) and st.alignsize == 16 * len(want)
+        assert st.npair == len(want) and st.keysize == sum(len(k) for k, _ in want) and st.alignsize == 16 * len(want)
         assert mr.scan_kv() == want, f"intcount variant {variant} combine {combine}: wrong pairs/order on rank {rank}"
-        if variant == 0:                             # once from the expanded records (scan above), once from the rows as delivered
-            mr.map_intcount(keys)
-            mr.aggregate()
+        if variant == 0:                             # once from the expanded records (scan above), once from the rows as delivered,
+            mr.ahead = 0                             # device input and no counts made at emit time: aggregate() counts itself
+            assert mr.map_intcount(torch.from_numpy(keys.view(np.int32)).cuda()) == total
+            assert mr.aggregate() == total
         nuniq = mr.convert()
         assert mr.reduce("count") == nuniq
         got = mr.scan_kv()

@@ -23,6 +23,12 @@ def _launch(nproc, backend, port, timeout=240, **extra):
         os.killpg(p.pid, signal.SIGKILL)
         out, err = p.communicate()
         raise AssertionError(("timed out", out[-2000:], err[-4000:]))
+    if not (p.returncode == 0 and "MULTI_OK" in out):
+        # pytest shortens long assertion messages: keep the whole output where a gpurun call brings it back
+        d = os.path.join(ROOT, "gpurun_out")
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, f"multirank_fail_{backend}_{nproc}_{port}.log"), "w") as f:
+            f.write(out + "\n---- stderr ----\n" + err)
     assert p.returncode == 0 and "MULTI_OK" in out, (out[-2000:], err[-4000:])
 
 
