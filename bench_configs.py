@@ -8,6 +8,7 @@ that does not depend on size (the generator's own index counts, pair-count ident
 {config, pairs, seconds per phase, pairs_per_s}.  Synthetic inputs are generated on the GPU with torch and the time
 to generate them is not counted; inputs are device resident (the e2e figure belongs to bench.py)."""
 import json
+import os
 import sys
 import time
 
@@ -16,7 +17,7 @@ import torch
 
 from gpu_mapreduce_b200 import MapReduce, workloads as W
 
-DEV = torch.device("cuda", 0)
+DEV = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
 
 
 def sync():
@@ -162,37 +163,138 @@ def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
 
 # ------------------------------------------------------------------------------------------ configs 4/5: R-MAT + degree
 
-def rmat(nlevels=24, ef=16, a=.57, b=.19, c=.19, d=.05, fraction=0.0, seed=12345):
-    """oink: rmat N 16 .57 .19 .19 .05 0.0 12345 ; degree 2 (oink/rmat.cpp:37-61, oink/degree.cpp:43-50)."""
-    mr = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
-    mrv = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
-    # the whole job runs twice on the same handles; the second pass (allocator warm) is reported
-    for rep in range(2):
+_DIST = {"init": False, "uid": None}
+
+
+def _ranks():
+    """(rank, world, local, unique id): one process per GPU under torch.distributed.run; 0, 1 without it"""
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not _DIST["init"]:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        t = torch.zeros(128, dtype=torch.uint8, device=torch.device("cuda", local))
+        if rank == 0:
+            t.copy_(torch.frombuffer(bytearray(MapReduce.unique_id()), dtype=torch.uint8))
+        dist.broadcast(t, 0)
+        _DIST["uid"] = bytes(t.cpu().numpy().tobytes())
+        _DIST["init"] = True
+    return rank, world, local, _DIST["uid"]
+
+
+def _allmax(x, local):
+    import torch.distributed as dist
+
+    t = torch.tensor([float(x)], dtype=torch.float64, device=torch.device("cuda", local))
+    if dist.is_initialized():
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _golden_kv(name):
+    """records of a fixture recorded from the reference (tests/golden/make_golden.py): u64 n, then (int kb, int vb, key, value)"""
+    import struct
+
+    buf = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "golden.npz"))[name].tobytes()
+    (n,) = struct.unpack_from("<Q", buf, 0)
+    p, out = 8, []
+    for _ in range(n):
+        kb, vb = struct.unpack_from("<ii", buf, p)
+        out.append((bytes(buf[p + 8:p + 8 + kb]), bytes(buf[p + 8 + kb:p + 8 + kb + vb])))
+        p += 8 + kb + vb
+    return out
+
+
+def rmat(nlevels=24, ef=16, a=.57, b=.19, c=.19, d=.05, fraction=0.0, seed=12345, reps=2, fixture=None):
+    """oink: rmat N 16 .57 .19 .19 .05 0.0 12345 ; degree 2 (oink/rmat.cpp:37-61, oink/degree.cpp:43-50), on 1 rank or --
+    under torch.distributed.run -- on one rank per GPU: rank r draws from its own drand48 stream srand48(seed + r) and
+    generates nremain / P (+1 for r < nremain % P) edges per iteration (oink/rmat.cpp:53-56, 94); collate() moves every
+    edge to rank hashlittle(edge,16,P) % P over NVLink.  Phase times are the max over ranks.  fixture = index of the
+    tests/golden rmat case recorded from the reference with the same parameters and P virtual ranks: edges and degrees
+    are then compared with it pair for pair."""
+    rank, world, local, uid = _ranks()
+    torch.cuda.set_device(local)
+    stream = torch.cuda.current_stream().cuda_stream
+    mr = MapReduce(device=local, stream=stream, rank=rank, nranks=world, unique_id=uid)
+    mrv = MapReduce(device=local, stream=stream, rank=rank, nranks=world, unique_id=uid)
+
+    def exchange(h):
+        """(max over ranks of max(sent, received) bytes, max over ranks of ms) of the exchanges since prof(True)"""
+        kern, _ = h.prof_report()
+        x = [k for k in kern if k["tag"] == "aggregate_exchange_nvlink"]
+        return (_allmax(max(sum(k["bytes"] for k in x), sum(k.get("moved", 0) for k in x)), local), _allmax(sum(k["ms"] for k in x), local),
+                {k["tag"]: round(k["ms"], 3) for k in kern if k["ms"] > 0.5})
+
+    # the whole job runs `reps` times on the same handles; the last pass (allocator warm) is reported
+    for rep in range(reps):
         T = Timer()
-        state = (seed << 16) | 0x330E
+        state = ((seed + rank) << 16) | 0x330E
         ntotal = nremain = (1 << nlevels) * ef
         niter, generated = 0, 0
+        per_iter = []
+        mr.prof(True)
         while nremain:
             niter += 1
             generated += nremain
-            _, state = T.run("generate", lambda: mr.map_rmat(nremain, nlevels, a, b, c, d, fraction, state, addflag=1 if niter > 1 else 0))
+            ng = nremain // world + (1 if rank < nremain % world else 0)
+            t0 = dict(T.t)
+            _, state = T.run("generate", lambda: mr.map_rmat(ng, nlevels, a, b, c, d, fraction, state, addflag=1 if niter > 1 else 0))
             nunique = T.run("collate", mr.collate)
             T.run("cull", lambda: mr.reduce("cull"))
+            per_iter.append({k: round((T.t[k] - t0.get(k, 0.0)) * 1e3, 2) for k in ("generate", "collate", "cull")})
             nremain = ntotal - nunique
-        assert mr.kv_stats().npair == ntotal
+        xb, xms, kern_rmat = exchange(mr)
+        mr.prof(False)
+        mrv.prof(True)
         assert T.run("degree_map", lambda: mrv.map_mr(mr, "edge_to_vertices")) == 2 * ntotal
         nvert = T.run("degree_collate", mrv.collate)
         assert T.run("degree_reduce", lambda: mrv.reduce("count")) == nvert
+        db, dms, kern_deg = exchange(mrv)
+        mrv.prof(False)
+    edges_here = mr.kv_stats().npair
+    tot = torch.tensor([edges_here], dtype=torch.int64, device=torch.device("cuda", local))
     deg_sum = 0
     for nkey, page in mrv.kv_pages():
         deg_sum += int(np.frombuffer(page, dtype=np.int32).reshape(nkey, -1)[:, -1].astype(np.int64).sum())
-    assert deg_sum == 2 * ntotal and nvert <= (1 << nlevels)
+    tot2 = torch.tensor([deg_sum], dtype=torch.int64, device=torch.device("cuda", local))
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.all_reduce(tot)
+        dist.all_reduce(tot2)
+    assert int(tot.item()) == ntotal and int(tot2.item()) == 2 * ntotal and nvert <= (1 << nlevels)
+    check = "unique edges == order*ef, sum of degrees == 2*edges"
+    if fixture is not None:
+        ge, gd = mr.scan_kv(), mrv.scan_kv()
+        if world > 1:
+            import torch.distributed as dist
+
+            le, ld = [None] * world, [None] * world
+            dist.all_gather_object(le, ge)
+            dist.all_gather_object(ld, gd)
+            ge, gd = [r for p in le for r in p], [r for p in ld for r in p]
+        assert sorted(ge) == sorted(_golden_kv(f"rmat{fixture}.edges")), "edges differ from the reference's"
+        assert sorted(gd) == sorted(_golden_kv(f"rmat{fixture}.degree")), "degrees differ from the reference's"
+        check = f"edges and (vertex, degree) pairs equal the reference's run with {world} ranks, pair for pair (tests/golden rmat{fixture})"
+    hi = _allmax(max(mr.pool_hiwater(), mrv.pool_hiwater()) if hasattr(mr, "pool_hiwater") else 0, local)
     mr.destroy()
     mrv.destroy()
-    secs = sum(T.t.values())
-    return {"config": f"oink rmat {nlevels} {ef} {a} {b} {c} {d} {fraction} {seed} + degree 2", "edges": ntotal, "iterations": niter,
-            "pairs": generated + 2 * ntotal, "vertices": nvert, "secs": T.t, "pairs_per_s": (generated + 2 * ntotal) / secs,
-            "check": "unique edges == order*ef, sum of degrees == 2*edges (small scales are compared edge for edge in tests/)"}
+    secs = {k: _allmax(v, local) for k, v in sorted(T.t.items())}
+    total = sum(secs.values())
+    out = {"config": f"oink rmat {nlevels} {ef} {a} {b} {c} {d} {fraction} {seed} + degree 2", "n_gpus": world, "edges": ntotal, "iterations": niter,
+           "pairs": generated + 2 * ntotal, "vertices": nvert, "secs": secs, "pairs_per_s": (generated + 2 * ntotal) / total,
+           "per_iteration_ms_rank0": per_iter, "check": check}
+    if world > 1:
+        # SURVEY.md 8d: shuffle bus = max over GPUs of max(sent, received) / exchange time; 900 GB/s per direction nominal
+        out["shuffle_rmat_collates"] = {"bytes_max_over_ranks": xb, "ms": xms, "bus_gbs": xb / 1e9 / (xms / 1e3) if xms else None,
+                                        "frac_of_900": xb / 1e9 / (xms / 1e3) / 900 if xms else None}
+        out["shuffle_degree_collate"] = {"bytes_max_over_ranks": db, "ms": dms, "bus_gbs": db / 1e9 / (dms / 1e3) if dms else None,
+                                         "frac_of_900": db / 1e9 / (dms / 1e3) / 900 if dms else None}
+    out["kernels_ms_rank0"] = {"rmat": kern_rmat, "degree": kern_deg}
+    if hi:
+        out["pool_hiwater_bytes_max_over_ranks"] = hi
+    return out if rank == 0 else None
 
 
 if __name__ == "__main__":
@@ -202,6 +304,17 @@ if __name__ == "__main__":
             r = wordfreq()
         elif w == "invindex":
             r = invindex()
+        elif w == "rmatcheck":
+            # parity of the multi-rank R-MAT + degree against the reference's run with as many (virtual) ranks
+            world = int(os.environ.get("WORLD_SIZE", "1"))
+            man = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "manifest.json")))["rmat"]
+            fx = [i for i, cse in enumerate(man) if cse["args"][8] == world and cse["args"][9] == 2]
+            if not fx:
+                raise SystemExit(f"no reference fixture for {world} ranks")
+            N, ef, a, b, c, d, fr, seed, P, dup = man[fx[0]]["args"]
+            r = rmat(N, ef, a, b, c, d, fr, seed, reps=1, fixture=fx[0])
+            if r is not None:
+                assert r["iterations"] == man[fx[0]]["iterations"], (r["iterations"], man[fx[0]]["iterations"])
         elif w.startswith("rmat"):
             r = rmat(int(w[4:]))
         elif w == "wordfreq_small":
@@ -210,6 +323,8 @@ if __name__ == "__main__":
             r = invindex(total_bytes=1 << 24, nfiles=2, nurls=1 << 12)
         else:
             raise SystemExit(f"unknown config {w}")
+        if r is None:   # ranks other than 0 of a multi-rank config
+            continue
         r["secs"] = {k: round(v, 4) for k, v in r["secs"].items()}
         print(json.dumps(r), flush=True)
         torch.cuda.empty_cache()

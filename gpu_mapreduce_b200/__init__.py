@@ -192,6 +192,12 @@ class MapReduce:
             raise MRError(rc, lib().mrgpu_last_error(None).decode())
         return buf.raw
 
+    def pool_hiwater(self):
+        """msizemax (src/mapreduce.h:54): high-water mark, in bytes, of the HBM this handle's page pool had in use"""
+        v = C.c_int64()
+        self._ck(lib().mrgpu_get(self._h, b"msizemax", C.byref(v)))
+        return v.value
+
     def my_proc(self):
         r, n = C.c_int(), C.c_int()
         lib().mrgpu_comm_rank(self._h, C.byref(r), C.byref(n))

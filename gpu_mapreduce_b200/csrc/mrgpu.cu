@@ -265,7 +265,11 @@ extern "C" int mrgpu_set(mrgpu_mr *mr, const char *name, int64_t value)
 
 extern "C" int mrgpu_get(const mrgpu_mr *mr, const char *name, int64_t *value)
 {
-  if (!mr || !value) return MRGPU_EINVAL;
+  if (!mr || !value || !name) return MRGPU_EINVAL;
+  // read-only: the reference's msize / msizemax (src/mapreduce.h:54), in bytes of HBM held by the handle's page pool
+  if (!strcmp(name, "msize")) return *value = (int64_t) mr->pool.live, MRGPU_OK;
+  if (!strcmp(name, "msizemax")) return *value = (int64_t) mr->pool.hiwater, MRGPU_OK;
+  if (!strcmp(name, "reserved")) return *value = (int64_t) mr->pool.reserved, MRGPU_OK;
   int64_t *p = setting(const_cast<mrgpu_mr *>(mr), name);
   if (!p) return MRGPU_EINVAL;
   *value = *p;

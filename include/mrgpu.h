@@ -109,6 +109,8 @@ const char *mrgpu_last_error(const mrgpu_mr *mr);
  * "debug_fail_alloc" (test hook, default -1 = off): the n-th next allocation from the handle's HBM pool fails.
  * A failed NCCL call aborts the handle's communicator (ncclCommAbort) before the call returns MRGPU_ECOMM: the job
  * cannot continue, as after the reference's Error::one -> MPI_Abort (src/error.cpp:47-57). */
+/* mrgpu_get also answers three read-only names, in bytes: "msize" / "msizemax" (HBM in use by the handle's page pool now /
+ * at its high-water mark: the reference's msize, msizemax of src/mapreduce.h:54) and "reserved" (obtained from cudaMalloc). */
 int mrgpu_set(mrgpu_mr *mr, const char *name, int64_t value);
 int mrgpu_get(const mrgpu_mr *mr, const char *name, int64_t *value);
 

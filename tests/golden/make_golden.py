@@ -146,7 +146,9 @@ def main():
     # 9. R-MAT + degree through the unmodified oink callbacks
     M["rmat"] = []
     cases = [(8, 4, .57, .19, .19, .05, 0.0, 12345, 1, 2), (8, 4, .57, .19, .19, .05, 0.0, 12345, 2, 2),
-             (7, 3, .25, .25, .25, .25, 0.0, 7, 3, 1), (6, 4, .45, .15, .15, .25, 0.1, 99, 2, 2)]
+             (7, 3, .25, .25, .25, .25, 0.0, 7, 3, 1), (6, 4, .45, .15, .15, .25, 0.1, 99, 2, 2),
+             # 4 and 8 virtual ranks (SCALE runs: the same ranks on real GPUs, bench_configs.py rmat parity)
+             (10, 8, .57, .19, .19, .05, 0.0, 12345, 4, 2), (10, 8, .57, .19, .19, .05, 0.0, 12345, 8, 2)]
     with tempfile.TemporaryDirectory() as td:
         for ci, c in enumerate(cases):
             fe, fd = os.path.join(td, "e"), os.path.join(td, "d")

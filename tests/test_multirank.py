@@ -52,3 +52,5 @@ def test_aggregate_collate_over_nccl():
     _launch(2, "nccl", 29616, MRGPU_PEER_DIRECT="1")
     if n >= 3:
         _launch(3, "nccl", 29614)
+    if n >= 8:
+        _launch(8, "nccl", 29617, timeout=600)
