@@ -232,9 +232,9 @@ def rmat(nlevels=24, ef=16, a=.57, b=.19, c=.19, d=.05, fraction=0.0, seed=12345
         state = ((seed + rank) << 16) | 0x330E
         ntotal = nremain = (1 << nlevels) * ef
         niter, generated = 0, 0
-        per_iter = []
-        mr.prof(True)
+        per_iter, xchg = [], []
         while nremain:
+            mr.prof(True)
             niter += 1
             generated += nremain
             ng = nremain // world + (1 if rank < nremain % world else 0)
@@ -244,8 +244,10 @@ def rmat(nlevels=24, ef=16, a=.57, b=.19, c=.19, d=.05, fraction=0.0, seed=12345
             T.run("cull", lambda: mr.reduce("cull"))
             per_iter.append({k: round((T.t[k] - t0.get(k, 0.0)) * 1e3, 2) for k in ("generate", "collate", "cull")})
             nremain = ntotal - nunique
-        xb, xms, kern_rmat = exchange(mr)
+            xchg.append(exchange(mr))   # an aggregate() re-hashes every pair; after the first one only the new edges change rank
         mr.prof(False)
+        xb, xms, kern_rmat = max(xchg, key=lambda x: x[0])
+        per_iter = [dict(p, exchange_ms=round(x[1], 3), exchange_gb=round(x[0] / 1e9, 3)) for p, x in zip(per_iter, xchg)]
         mrv.prof(True)
         assert T.run("degree_map", lambda: mrv.map_mr(mr, "edge_to_vertices")) == 2 * ntotal
         nvert = T.run("degree_collate", mrv.collate)
@@ -287,7 +289,7 @@ def rmat(nlevels=24, ef=16, a=.57, b=.19, c=.19, d=.05, fraction=0.0, seed=12345
            "per_iteration_ms_rank0": per_iter, "check": check}
     if world > 1:
         # shuffle bus = max over GPUs of max(sent, received) / exchange time; 900 GB/s per direction nominal
-        out["shuffle_rmat_collates"] = {"bytes_max_over_ranks": xb, "ms": xms, "bus_gbs": xb / 1e9 / (xms / 1e3) if xms else None,
+        out["shuffle_rmat_collate_largest"] = {"bytes_max_over_ranks": xb, "ms": xms, "bus_gbs": xb / 1e9 / (xms / 1e3) if xms else None,
                                         "frac_of_900": xb / 1e9 / (xms / 1e3) / 900 if xms else None}
         out["shuffle_degree_collate"] = {"bytes_max_over_ranks": db, "ms": dms, "bus_gbs": db / 1e9 / (dms / 1e3) if dms else None,
                                          "frac_of_900": db / 1e9 / (dms / 1e3) / 900 if dms else None}

@@ -68,6 +68,7 @@ struct mrgpu_mr {
   int g_what = 0;
   uint64_t g_count = 0;
   bool p2p_used = false;  // set identically on every rank
+  std::set<std::string> ipc_agreed;        // chunks (by IPC handle) that every rank is known to have mapped
   std::map<std::string, void *> ipc_open;  // peers' receive chunks mapped by the peer-store exchange (CUDA IPC handle -> base)
 };
 

@@ -47,6 +47,11 @@ def test_aggregate_collate_over_nccl():
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs at least 2 GPUs (run with gpurun --gpus 2)")
+    only = os.environ.get("MR_RANKS")            # e.g. MR_RANKS=8: just that rank count (a large box is charged per GPU)
+    if only:
+        _launch(int(only), "nccl", 29618, timeout=600)
+        _launch(int(only), "nccl", 29619, timeout=600, MRGPU_P2P="0")
+        return
     _launch(2, "nccl", 29613)                   # exchange by peer stores (CUDA IPC) where the pairs are uniform
     _launch(2, "nccl", 29615, MRGPU_P2P="0")    # the same through ncclSend/ncclRecv
     _launch(2, "nccl", 29616, MRGPU_PEER_DIRECT="1")
