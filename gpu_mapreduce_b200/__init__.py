@@ -41,6 +41,10 @@ class Stats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+# host callbacks of scan() (src/mapreduce.h:103-105): (key, keybytes, value, valuebytes, ptr) / (key, keybytes, multivalue, nvalues, valuesizes, ptr)
+SCAN_KV_FN = C.CFUNCTYPE(None, C.POINTER(C.c_char), C.c_int, C.POINTER(C.c_char), C.c_int, C.c_void_p)
+SCAN_KMV_FN = C.CFUNCTYPE(None, C.POINTER(C.c_char), C.c_int, C.POINTER(C.c_char), C.c_int, C.POINTER(C.c_int), C.c_void_p)
+
 _lib = None
 
 
@@ -74,6 +78,12 @@ def lib():
         "mrgpu_map_mr": [vp, vp, C.c_int, C.c_int, u64p],
         "mrgpu_add": [vp, vp, u64p],
         "mrgpu_aggregate": [vp, u64p],
+        "mrgpu_aggregate_dest": [vp, vp, C.c_uint64, u64p],
+        "mrgpu_scan_kv": [vp, SCAN_KV_FN, vp, u64p],
+        "mrgpu_scan_kmv": [vp, SCAN_KMV_FN, vp, u64p],
+        "mrgpu_multivalue_blocks": [vp, C.POINTER(C.c_int), u64p],
+        "mrgpu_multivalue_block_select": [vp, C.c_int],
+        "mrgpu_multivalue_block": [vp, C.c_int, C.POINTER(C.POINTER(C.c_char)), C.POINTER(C.POINTER(C.c_int)), C.POINTER(C.c_int)],
         "mrgpu_plan_exchange": [C.c_int, C.c_int, u64p, u64p, u64p, u64p, u64p, u64p, C.POINTER(C.c_int)],
         "mrgpu_debug_partition": [vp, C.c_int, u64p],
         "mrgpu_convert": [vp, u64p],
@@ -266,9 +276,16 @@ class MapReduce:
         return self._count(lib().mrgpu_add, other._h)
 
     def aggregate(self, hash=None):
-        if hash is not None:
-            raise MRError(-1, "user hash callbacks run on the host; only the default hashlittle partition is built")
-        return self._count(lib().mrgpu_aggregate)
+        """aggregate(myhash) src/mapreduce.cpp:385.  hash = None: the default hashlittle partition, on the GPU.  A callable
+        hash(key: bytes, keybytes: int) -> int is host code like the reference's function pointer: it is evaluated here for
+        every pair (destination = hash % nprocs, src/mapreduce.cpp:470) and the exchange runs with those destinations."""
+        if hash is None:
+            return self._count(lib().mrgpu_aggregate)
+        import numpy as np
+
+        P = self.num_procs()
+        dest = np.array([hash(k, len(k)) % P for k, _ in self.scan_kv()], dtype=np.int32)
+        return self._count(lib().mrgpu_aggregate_dest, dest.ctypes.data if dest.size else None, dest.size)
 
     def debug_partition(self, nprocs):
         """local half of aggregate() for a virtual rank count (test / profiling hook); returns per-destination counts"""
@@ -280,8 +297,10 @@ class MapReduce:
         return self._count(lib().mrgpu_convert)
 
     def collate(self, hash=None):
+        """collate(myhash) src/mapreduce.cpp:710-738 = aggregate(myhash) + convert()"""
         if hash is not None:
-            raise MRError(-1, "user hash callbacks run on the host; only the default hashlittle partition is built")
+            self.aggregate(hash)
+            return self.convert()
         return self._count(lib().mrgpu_collate)
 
     def reduce(self, functor: str):
@@ -354,46 +373,53 @@ class MapReduce:
         return out
 
     def scan_kv(self, fn=None):
-        """scan(myscan, ptr) src/mapreduce.cpp:1933-1976: walk every pair on the host; returns the list of
-        (key, value) when fn is None."""
-        ka, va = self.keyalign, self.valuealign
-        ta = max(ka, va, 4)
+        """scan(myscan, ptr) src/mapreduce.cpp:1933-1976 through mrgpu_scan_kv: fn(key, keybytes, value, valuebytes) for every
+        pair of this rank; returns the list of (key, value) when fn is None."""
         out = []
-        for nkey, page in self.kv_pages():
-            p = 0
-            for _ in range(nkey):
-                kb, vb = struct.unpack_from("<ii", page, p)
-                k0 = (p + 8 + ka - 1) // ka * ka
-                v0 = (k0 + kb + va - 1) // va * va
-                k, v = page[k0:k0 + kb], page[v0:v0 + vb]
-                if fn is None:
-                    out.append((k, v))
-                else:
-                    fn(k, kb, v, vb)
-                p = (v0 + vb + ta - 1) // ta * ta
+
+        def cb(k, kb, v, vb, _):
+            kk, vv = C.string_at(k, kb), C.string_at(v, vb)
+            if fn is None:
+                out.append((kk, vv))
+            else:
+                fn(kk, kb, vv, vb)
+
+        self._ck(lib().mrgpu_scan_kv(self._h, SCAN_KV_FN(cb), None, None))
         return out
 
     def scan_kmv(self, fn=None):
-        """scan(myscan, ptr) KMV form src/mapreduce.cpp:1984-2065: [(key, [values])]."""
-        ka, va = self.keyalign, self.valuealign
-        ta = max(ka, va, 4)
+        """scan(myscan, ptr) KMV form src/mapreduce.cpp:1984-2065 through mrgpu_scan_kmv: [(key, [values])].  A pair bigger
+        than a page arrives through the multivalue_blocks()/multivalue_block() protocol and is put together here."""
+        L = lib()
         out = []
-        for nkey, page, _ext in self.kmv_pages():
-            p = 0
-            for _ in range(nkey):
-                nv, kb, mvb = struct.unpack_from("<iii", page, p)
-                sizes = struct.unpack_from(f"<{nv}i", page, p + 12)
-                k0 = (p + 12 + 4 * nv + ka - 1) // ka * ka
-                v0 = (k0 + kb + va - 1) // va * va
-                vals, q = [], v0
-                for s in sizes:
-                    vals.append(page[q:q + s])
-                    q += s
-                if fn is None:
-                    out.append((page[k0:k0 + kb], vals))
-                else:
-                    fn(page[k0:k0 + kb], kb, page[v0:v0 + mvb], nv, sizes)
-                p = (v0 + mvb + ta - 1) // ta * ta
+
+        def split(mv, sizes, nv):
+            vals, q = [], 0
+            raw = C.string_at(mv, sum(sizes[i] for i in range(nv)))
+            for i in range(nv):
+                vals.append(raw[q:q + sizes[i]])
+                q += sizes[i]
+            return vals
+
+        def cb(k, kb, mv, nv, sizes, _):
+            key = C.string_at(k, kb)
+            if mv:
+                vals = split(mv, sizes, nv)
+            else:   # multivalue == NULL: CHECK_FOR_BLOCKS / BEGIN_BLOCK_LOOP of oink/blockmacros.h:12-32
+                nblock, total = C.c_int(), C.c_uint64()
+                self._ck(L.mrgpu_multivalue_blocks(self._h, C.byref(nblock), C.byref(total)))
+                vals = []
+                for ib in range(nblock.value):
+                    pm, ps, n = C.POINTER(C.c_char)(), C.POINTER(C.c_int)(), C.c_int()
+                    self._ck(L.mrgpu_multivalue_block(self._h, ib, C.byref(pm), C.byref(ps), C.byref(n)))
+                    vals += split(pm, ps, n.value)
+                assert len(vals) == total.value
+            if fn is None:
+                out.append((key, vals))
+            else:
+                fn(key, kb, b"".join(vals), len(vals), [len(v) for v in vals])
+
+        self._ck(L.mrgpu_scan_kmv(self._h, SCAN_KMV_FN(cb), None, None))
         return out
 
     def prof(self, enable=True):

@@ -4,8 +4,12 @@
 // file:line sites cited per method); no reference code is reused.
 #include "mapreduce.h"
 
+#include <arpa/inet.h>
 #include <dirent.h>
+#include <netinet/in.h>
 #include <stdio.h>
+#include <sys/socket.h>
+#include <unistd.h>
 #include <stdlib.h>
 #include <string.h>
 #include <sys/stat.h>
@@ -45,6 +49,10 @@ void cull(char *, int, char *, int, int *, KeyValue *, void *) {}
 void edge_to_vertices(uint64_t, char *, int, char *, int, KeyValue *, void *) {}
 void edge_to_vertex(uint64_t, char *, int, char *, int, KeyValue *, void *) {}
 void invert(uint64_t, char *, int, char *, int, KeyValue *, void *) {}
+void intcount(int, KeyValue *, void *) {}
+void rmat_generate(int, KeyValue *, void *) {}
+void fileread(int, char *, KeyValue *, void *) {}
+void href(int, char *, KeyValue *, void *) {}
 }  // namespace gpu
 
 typedef void (*ReduceFn)(char *, int, char *, int, int *, KeyValue *, void *);
@@ -111,6 +119,82 @@ void KeyValue::add(int n, char *key, int *keybytes, char *value, int *valuebytes
 
 // ---------------------------------------------------------------------------------------------- life cycle
 
+#ifdef MRGPU_MPI_STUB
+// Without MPI (cpp/mpi.h): the one thing the ranks have to share before NCCL can take over is the 128-byte unique
+// id.  Rank 0 makes it and serves it on a loopback TCP socket -- port MRGPU_PORT, else MASTER_PORT + 1 (next to the
+// launcher's own rendezvous port), else 29517 -- once per process; every MapReduce object of the process reuses it
+// (the library keeps one communicator per id).  One node only, which is what one process per GPU of one box needs.
+static bool bootstrap_id(int me, int nprocs, char id[128], std::string &why)
+{
+  static bool have = false;
+  static char cached[128];
+  if (have) {
+    memcpy(id, cached, 128);
+    return true;
+  }
+  int port = 29517;
+  if (getenv("MRGPU_PORT")) port = atoi(getenv("MRGPU_PORT"));
+  else if (getenv("MASTER_PORT")) port = atoi(getenv("MASTER_PORT")) + 1;
+  struct sockaddr_in addr;
+  memset(&addr, 0, sizeof(addr));
+  addr.sin_family = AF_INET;
+  addr.sin_port = htons((uint16_t) port);
+  addr.sin_addr.s_addr = htonl(INADDR_LOOPBACK);
+  if (me == 0) {
+    if (mrgpu_comm_unique_id(cached) != MRGPU_OK) {
+      why = mrgpu_last_error(NULL);
+      return false;
+    }
+    int srv = socket(AF_INET, SOCK_STREAM, 0), yes = 1;
+    setsockopt(srv, SOL_SOCKET, SO_REUSEADDR, &yes, sizeof(yes));
+    if (srv < 0 || bind(srv, (struct sockaddr *) &addr, sizeof(addr)) != 0 || listen(srv, nprocs) != 0) {
+      why = "rank 0 cannot listen on 127.0.0.1:" + std::to_string(port) + " to hand out the NCCL id (set MRGPU_PORT)";
+      if (srv >= 0) ::close(srv);
+      return false;
+    }
+    for (int served = 0; served < nprocs - 1; served++) {
+      int c = accept(srv, NULL, NULL);
+      if (c < 0) {
+        why = "accept() failed while handing out the NCCL id";
+        ::close(srv);
+        return false;
+      }
+      size_t off = 0;
+      while (off < 128) {
+        ssize_t w = ::write(c, cached + off, 128 - off);
+        if (w <= 0) break;
+        off += (size_t) w;
+      }
+      ::close(c);
+    }
+    ::close(srv);
+  } else {
+    bool got = false;
+    for (int attempt = 0; attempt < 2400 && !got; attempt++) {  // up to two minutes for rank 0 to come up
+      int c = socket(AF_INET, SOCK_STREAM, 0);
+      if (c >= 0 && connect(c, (struct sockaddr *) &addr, sizeof(addr)) == 0) {
+        size_t off = 0;
+        while (off < 128) {
+          ssize_t r = ::read(c, cached + off, 128 - off);
+          if (r <= 0) break;
+          off += (size_t) r;
+        }
+        got = off == 128;
+      }
+      if (c >= 0) ::close(c);
+      if (!got) usleep(50000);
+    }
+    if (!got) {
+      why = "could not fetch the NCCL id from rank 0 at 127.0.0.1:" + std::to_string(port);
+      return false;
+    }
+  }
+  have = true;
+  memcpy(id, cached, 128);
+  return true;
+}
+#endif
+
 void MapReduce::init(MPI_Comm caller)
 {
   comm = caller;
@@ -147,7 +231,15 @@ void MapReduce::init(MPI_Comm caller)
     fflush(stdout);
     exit(1);
   }
-#ifndef MRGPU_MPI_STUB
+  lib_blocks = 0;
+#ifdef MRGPU_MPI_STUB
+  if (nprocs > 1) {
+    char id[128];
+    std::string why;
+    if (!bootstrap_id(me, nprocs, id, why)) all(why.c_str());
+    if (mrgpu_comm_init(gpu, me, nprocs, id) != MRGPU_OK) all(mrgpu_last_error(gpu));
+  }
+#else
   if (nprocs > 1) {  // real MPI: NCCL bootstrap = one broadcast of 128 bytes
     char id[128];
     if (me == 0 && mrgpu_comm_unique_id(id) != MRGPU_OK) all(mrgpu_last_error(NULL));
@@ -360,8 +452,15 @@ void MapReduce::walk_kmv(mrgpu_mr *h, F f)
   }
 }
 
+// While the LIBRARY walks the KMV (scan), the block state lives there (mrgpu_multivalue_*); while this class walks it
+// (reduce / compress with a host callback) it lives here.
 uint64_t MapReduce::multivalue_blocks(int &nblock)
 {
+  if (!kmv_block_valid && lib_blocks) {
+    uint64_t total = 0;
+    if (mrgpu_multivalue_blocks(gpu, &nblock, &total) != MRGPU_OK) one(mrgpu_last_error(gpu));
+    return total;
+  }
   if (!kmv_block_valid) one("Invalid call to multivalue_blocks()");
   nblock = kmv_nblock;
   return kmv_nvalue_total;
@@ -369,12 +468,21 @@ uint64_t MapReduce::multivalue_blocks(int &nblock)
 
 void MapReduce::multivalue_block_select(int which)
 {
+  if (!kmv_block_valid && lib_blocks) {
+    if (mrgpu_multivalue_block_select(gpu, which) != MRGPU_OK) one(mrgpu_last_error(gpu));
+    return;
+  }
   if (!kmv_block_valid) one("Invalid call to multivalue_block_select()");
   if (which != 1 && which != 2) one("Invalid arg to multivalue_block_select()");
 }
 
 int MapReduce::multivalue_block(int iblock, char **pmultivalue, int **pvaluesizes)
 {
+  if (!kmv_block_valid && lib_blocks) {
+    int nv = 0;
+    if (mrgpu_multivalue_block(gpu, iblock, pmultivalue, pvaluesizes, &nv) != MRGPU_OK) one(mrgpu_last_error(gpu));
+    return nv;
+  }
   if (!kmv_block_valid) one("Invalid call to multivalue_block()");
   if (iblock < 0 || iblock >= kmv_nblock) one("Invalid page request to multivalue_block()");
   const int *sizes = (const int *) blk_sizes_base;
@@ -435,10 +543,54 @@ static void my_tasks(int nmap, int me, int nprocs, int mapstyle, std::vector<int
   }
 }
 
+// whole file -> pinned-free host buffer (the device functors take host or device memory)
+static bool slurp(const char *fname, std::vector<char> &buf)
+{
+  FILE *fp = fopen(fname, "rb");
+  if (!fp) return false;
+  fseek(fp, 0, SEEK_END);
+  long sz = ftell(fp);
+  fseek(fp, 0, SEEK_SET);
+  buf.resize(sz > 0 ? (size_t) sz : 0);
+  size_t got = sz > 0 ? fread(buf.data(), 1, (size_t) sz, fp) : 0;
+  fclose(fp);
+  buf.resize(got);
+  return true;
+}
+
 uint64_t MapReduce::map(int nmap, void (*appmap)(int, KeyValue *, void *), void *ptr, int addflag)
 {
   push_settings();
   start_timer();
+  if (appmap == gpu::intcount || appmap == gpu::rmat_generate) {
+    // stock callback = device functor: one library call per task of this rank, no pair touches the host.  The calls
+    // with a NULL count do not communicate; the last one (zero extra pairs) returns the global count.
+    std::vector<int> tasks;
+    my_tasks(nmap, me, nprocs, mapstyle, tasks);
+    int flag = addflag;
+    for (size_t i = 0; i < tasks.size(); i++) {
+      if (appmap == gpu::intcount) {
+        const gpu::IntCountInput *in = (const gpu::IntCountInput *) ptr;
+        ck(mrgpu_map_intcount(gpu, in->task_keys[tasks[i]], in->task_nkeys[tasks[i]], flag, NULL), 0);
+      } else {
+        gpu::RmatInput *in = (gpu::RmatInput *) ptr;
+        ck(mrgpu_map_rmat(gpu, in->ngenerate, in->nlevels, in->a, in->b, in->c, in->d, in->fraction, &in->state48, flag, NULL), 0);
+      }
+      flag = 1;
+    }
+    uint64_t n = 0;  // zero more pairs of the same shape: the call that returns the global count
+    if (appmap == gpu::intcount) ck(mrgpu_map_intcount(gpu, NULL, 0, flag, &n), 0);
+    else {
+      gpu::RmatInput *in = (gpu::RmatInput *) ptr;
+      ck(mrgpu_map_rmat(gpu, 0, in->nlevels, in->a, in->b, in->c, in->d, in->fraction, &in->state48, flag, &n), 0);
+    }
+    delete kv;
+    kv = new KeyValue(gpu);
+    kmv = NULL;
+    sync_kv_fields();
+    stats("Map", 0);
+    return n;
+  }
   KeyValue *out = begin_emit(gpu, addflag);
   std::vector<int> tasks;
   my_tasks(nmap, me, nprocs, mapstyle, tasks);
@@ -502,6 +654,31 @@ uint64_t MapReduce::map(int nstr, char **strings, int self, int recurse, int rea
   }
   (void) self;
   mapfilecount = (int) files.size();
+  if (appmap == gpu::fileread || appmap == gpu::href) {  // stock callback = device functor (tokenizer / href scanner)
+    std::vector<int> tasks;
+    my_tasks((int) files.size(), me, nprocs, mapstyle, tasks);
+    int flag = addflag;
+    std::vector<char> buf;
+    for (size_t i = 0; i < tasks.size(); i++) {
+      const std::string &f = files[tasks[i]];
+      if (!slurp(f.c_str(), buf)) one("Could not open file");
+      if (appmap == gpu::fileread) ck(mrgpu_map_tokenize(gpu, buf.data(), buf.size(), flag, NULL), 0);
+      else {
+        size_t slash = f.find_last_of('/');  // cpu/InvertedIndex.cpp:133: the value is the file's base name
+        ck(mrgpu_map_href(gpu, buf.data(), buf.size(), f.c_str() + (slash == std::string::npos ? 0 : slash + 1), flag, NULL), 0);
+      }
+      flag = 1;
+    }
+    uint64_t n = 0;  // zero more bytes: the call that returns the global count
+    if (appmap == gpu::fileread) ck(mrgpu_map_tokenize(gpu, NULL, 0, flag, &n), 0);
+    else ck(mrgpu_map_href(gpu, NULL, 0, "", flag, &n), 0);
+    delete kv;
+    kv = new KeyValue(gpu);
+    kmv = NULL;
+    sync_kv_fields();
+    stats("Map", 0);
+    return n;
+  }
   KeyValue *out = begin_emit(gpu, addflag);
   std::vector<int> tasks;
   my_tasks((int) files.size(), me, nprocs, mapstyle, tasks);
@@ -602,10 +779,16 @@ uint64_t MapReduce::add(MapReduce *mr)
 uint64_t MapReduce::aggregate(int (*hash)(char *, int))
 {
   if (kv == NULL) all("Cannot aggregate without KeyValue");
-  if (hash && nprocs > 1) all("aggregate() with a user hash function runs on the host and is not built for more than one rank");
   start_timer();
   uint64_t n = 0;
-  ck(mrgpu_aggregate(gpu, &n), 0);
+  if (hash && nprocs > 1) {
+    // the user's hash is host code: evaluate it for every pair (src/mapreduce.cpp:466-470: hash(key,keybytes) % nprocs),
+    // the exchange itself runs on the GPUs with these destinations
+    std::vector<int32_t> dest;
+    walk_kv(gpu, [&](char *k, int kb, char *, int) { dest.push_back(hash(k, kb) % nprocs); });
+    ck(mrgpu_aggregate_dest(gpu, dest.data(), dest.size(), &n), 0);
+  } else
+    ck(mrgpu_aggregate(gpu, &n), 0);
   sync_kv_fields();
   stats("Aggregate", 0);
   return n;
@@ -627,10 +810,16 @@ uint64_t MapReduce::convert()
 uint64_t MapReduce::collate(int (*hash)(char *, int))
 {
   if (kv == NULL) all("Cannot collate without KeyValue");
-  if (hash && nprocs > 1) all("collate() with a user hash function runs on the host and is not built for more than one rank");
   start_timer();
   uint64_t n = 0;
-  ck(mrgpu_collate(gpu, &n), 0);
+  if (hash && nprocs > 1) {  // src/mapreduce.cpp:726-727: aggregate(hash); convert();
+    int vsave = verbosity, tsave = timer;
+    verbosity = timer = 0;
+    aggregate(hash);
+    verbosity = vsave, timer = tsave;
+    ck(mrgpu_convert(gpu, &n), 0);
+  } else
+    ck(mrgpu_collate(gpu, &n), 0);
   delete kv;
   kv = NULL;
   kmv = &g_kmv_marker;
@@ -683,22 +872,53 @@ uint64_t MapReduce::compress(ReduceFn appcompress, void *ptr)
   return reduce_impl(appcompress, ptr, "Compress");
 }
 
+// scan(): the library stages the pages and calls back (mrgpu_scan_kv / mrgpu_scan_kmv); the trampolines only restore
+// the reference's convention of passing the MapReduce object in the valuesizes slot of a multi-block pair
+struct ScanCtxKV {
+  void (*fn)(char *, int, char *, int, void *);
+  void *ptr;
+};
+struct ScanCtxKMV {
+  void (*fn)(char *, int, char *, int, int *, void *);
+  void *ptr;
+  MapReduce *self;
+  mrgpu_mr *handle;
+};
+static void scan_tramp_kv(char *k, int kb, char *v, int vb, void *p)
+{
+  ScanCtxKV *c = (ScanCtxKV *) p;
+  c->fn(k, kb, v, vb, c->ptr);
+}
+static void scan_tramp_kmv(char *k, int kb, char *mv, int nv, int *sizes, void *p)
+{
+  ScanCtxKMV *c = (ScanCtxKMV *) p;
+  if (mv == NULL && nv == 0 && (void *) sizes == (void *) c->handle) sizes = (int *) c->self;
+  c->fn(k, kb, mv, nv, sizes, c->ptr);
+}
+
 uint64_t MapReduce::scan(void (*appscan)(char *, int, char *, int, void *), void *ptr)
 {
   if (kv == NULL) all("Cannot scan without KeyValue");
   start_timer();
-  walk_kv(gpu, [&](char *k, int kb, char *v, int vb) { appscan(k, kb, v, vb, ptr); });
+  ScanCtxKV c = {appscan, ptr};
+  uint64_t n = 0;
+  ck(mrgpu_scan_kv(gpu, scan_tramp_kv, &c, &n), 0);
   stats("Scan", 0);
-  return kv_stats(0);
+  return n;
 }
 
 uint64_t MapReduce::scan(void (*appscan)(char *, int, char *, int, int *, void *), void *ptr)
 {
   if (kmv == NULL) all("Cannot scan without KeyMultiValue");
   start_timer();
-  walk_kmv(gpu, [&](char *k, int kb, char *mv, int nv, int *sizes) { appscan(k, kb, mv, nv, sizes, ptr); });
+  ScanCtxKMV c = {appscan, ptr, this, gpu};
+  uint64_t n = 0;
+  lib_blocks = 1;
+  int rc = mrgpu_scan_kmv(gpu, scan_tramp_kmv, &c, &n);
+  lib_blocks = 0;
+  ck(rc, 0);
   stats("Scan", 1);
-  return kmv_stats(0);
+  return n;
 }
 
 // ---------------------------------------------------------------------------------------------- sorting

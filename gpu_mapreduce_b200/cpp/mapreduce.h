@@ -1,7 +1,8 @@
 /* MapReduce: source-compatible mirror of the reference's public class (src/mapreduce.h:22-131) over the
  * C-ABI CUDA library (include/mrgpu.h).  Same namespace, public settings, method names, signatures, return
  * values (global pair counts) and error behaviour ("ERROR: msg" + exit(1), src/error.cpp:33-67), so callers
- * written for MR-MPI compile unchanged.  Written from scratch; nothing here is the reference's code.
+ * written for MR-MPI compile unchanged.  The public declarations are the reference's interface, restated (that is the
+ * source-compatibility contract); everything behind them is new.
  *
  * Where the work runs:
  *   aggregate / convert / collate / gather / broadcast / clone / collapse / scrunch / sort_keys(flag) /
@@ -124,6 +125,7 @@ class MapReduce {
   int settings_pushed;
 
   // multi-block KMV state while a host reduce callback runs (src/mapreduce.h:189-194)
+  int lib_blocks;  // the library is walking the KMV (scan): multivalue_*() forward to it
   int kmv_block_valid, kmv_nblock;
   uint64_t kmv_nvalue_total;
   const char *blk_sizes_base, *blk_values_base;  // inside the staged extended pair

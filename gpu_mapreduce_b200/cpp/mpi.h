@@ -1,8 +1,12 @@
-/* Minimal single-process stand-in for <mpi.h>, for building reference callers (examples/wordfreq.cpp,
- * examples/rmat.cpp, cpu/IntCount.cpp ...) against this library on a box without MPI -- the role the
- * reference's own mpistubs/ plays (mpistubs/mpi.h:19-125).  Written from scratch; only what those callers
- * use.  One process = rank 0 of 1.  With a real MPI, use its mpi.h instead: MapReduce(MPI_Comm) then
- * bootstraps NCCL with one MPI_Bcast of 128 bytes. */
+/* Minimal stand-in for <mpi.h>, for building reference callers (examples/wordfreq.cpp, examples/rmat.cpp,
+ * cpu/IntCount.cpp ...) against this library on a box without MPI -- the role the reference's own mpistubs/
+ * plays (mpistubs/mpi.h:19-125).  Written from scratch; only what those callers use.
+ * Unlike mpistubs it is not limited to one process: rank and size come from the environment a process launcher
+ * sets (RANK / WORLD_SIZE as torch.distributed.run does, or OMPI_COMM_WORLD_* / PMI_*), one process per GPU, and
+ * MapReduce(MPI_Comm) hands the 128-byte NCCL id from rank 0 to the others over a loopback TCP socket
+ * (cpp/mapreduce.cpp, MRGPU_PORT).  Data never goes through this header: every exchange is NCCL inside the library.
+ * With a real MPI, use its mpi.h instead: MapReduce(MPI_Comm) then bootstraps NCCL with one MPI_Bcast of 128 bytes
+ * (INTEGRATION.md section 1). */
 #ifndef MRGPU_MPI_STUB_H
 #define MRGPU_MPI_STUB_H
 
@@ -23,14 +27,23 @@ static inline int MPI_Initialized(int *flag)
   return 0;
 }
 static inline int MPI_Finalize() { return 0; }
+static inline int mrgpu_stub_env(const char *a, const char *b, const char *c, int dflt)
+{
+  const char *names[3] = {a, b, c};
+  for (int i = 0; i < 3; i++) {
+    const char *v = names[i] ? getenv(names[i]) : NULL;
+    if (v && *v) return atoi(v);
+  }
+  return dflt;
+}
 static inline int MPI_Comm_rank(MPI_Comm, int *me)
 {
-  *me = 0;
+  *me = mrgpu_stub_env("RANK", "OMPI_COMM_WORLD_RANK", "PMI_RANK", 0);
   return 0;
 }
 static inline int MPI_Comm_size(MPI_Comm, int *n)
 {
-  *n = 1;
+  *n = mrgpu_stub_env("WORLD_SIZE", "OMPI_COMM_WORLD_SIZE", "PMI_SIZE", 1);
   return 0;
 }
 static inline int MPI_Barrier(MPI_Comm) { return 0; }

@@ -168,6 +168,7 @@ static void order_after(mrgpu_mr *mr, mrgpu_mr *other)
 #include "ops_partition.cuh"
 #include "ops_aggregate.cuh"
 #include "ops_pages.cuh"
+#include "ops_scan.cuh"
 
 // ================================================================================================
 // lifetime, settings
@@ -220,6 +221,7 @@ static int destroy_impl(mrgpu_mr *mr, bool collective)
     }
     comm_destroy(mr);
   }
+  scan_forget(mr);
   if (mr->order_ev) cudaEventDestroy(mr->order_ev);
   if (mr->copy_stream) cudaStreamDestroy(mr->copy_stream);
   for (auto e : mr->copy_ev)

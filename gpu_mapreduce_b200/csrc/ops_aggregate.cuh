@@ -409,7 +409,29 @@ static void peer_store_teardown(mrgpu_mr *mr)
   }
 }
 
-static void aggregate_impl(mrgpu_mr *mr)
+// destinations chosen by the caller (a user hash function evaluated on the host, src/mapreduce.cpp:466-470):
+// the same outputs as partition_dest_kernel; a destination outside [0, nprocs) raises the flag
+__global__ void __launch_bounds__(256)
+user_dest_kernel(const int32_t *__restrict__ udest, uint64_t n, uint32_t nprocs, uint32_t *__restrict__ dest, uint32_t *__restrict__ idx,
+                 unsigned long long *hist, unsigned long long *bad)
+{
+  __shared__ unsigned sh[RADIX];
+  sh[threadIdx.x] = 0;
+  __syncthreads();
+  uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const int32_t d = udest[i];
+    const uint32_t du = (d < 0 || (uint32_t) d >= nprocs) ? 0u : (uint32_t) d;
+    if (du != (uint32_t) d) *bad = 1;
+    dest[i] = du;
+    idx[i] = (uint32_t) i;
+    atomicAdd(&sh[du], 1u);
+  }
+  __syncthreads();
+  if (sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], (unsigned long long) sh[threadIdx.x]);
+}
+
+static void aggregate_impl(mrgpu_mr *mr, const int32_t *user_dest = nullptr)
 {
   freeze(mr);
   const int P = mr->nranks;
@@ -424,7 +446,7 @@ static void aggregate_impl(mrgpu_mr *mr)
   // header-less rows travel as they are when every rank that holds pairs holds the same header-less shape;
   // otherwise they are written out as records first
   if (kv->weighted) kv_unpack(mr, kv);  // a second aggregate() in a row: start from the records again
-  if (kv->packed && !partition_eligible(mr, kv)) kv_unpack(mr, kv);
+  if (kv->packed && (user_dest || !partition_eligible(mr, kv))) kv_unpack(mr, kv);
 
   // The combiner.  Pairs that share one value (IntCount's int 1, OINK's NULL values) cannot be told apart once their
   // keys are equal, so what the destination needs from this rank is, per distinct key, how many it had.  When every
@@ -437,7 +459,7 @@ static void aggregate_impl(mrgpu_mr *mr)
   // result.  The receiver holds the rows as a weighted KV (store.cuh): same pair count, statistics and page table
   // as the plain exchange; the pairs of one source come out grouped by key instead of in arrival order.
   // Setting "combine" = 0 keeps the plain exchange (exact delivery order of the reference).
-  bool combine = mr->combine && kv->nkv && kv->packed && kv->cval_on && kv->kb == 4 && (kv->vb == 0 || kv->vb == 4 || kv->vb == 8) &&
+  bool combine = !user_dest && mr->combine && kv->nkv && kv->packed && kv->cval_on && kv->kb == 4 && (kv->vb == 0 || kv->vb == 4 || kv->vb == 8) &&
                  ((uintptr_t) kv->data % 16) == 0;
   if (combine) {
     if (!(kv->counted && kv->ahead_n == kv->nkv && mr->dense_owner == kv->uid)) dense_count_shared4(mr, kv);
@@ -478,7 +500,7 @@ static void aggregate_impl(mrgpu_mr *mr)
   // uniform records: pass 1 of the single-pass partition (ops_partition.cuh) gives the per-destination counts now;
   // pass 2 writes the pairs later -- straight into the peers' receive buffers when the peer-store exchange is
   // possible, else into a local send buffer for NCCL
-  const bool fast = n && partition_eligible(mr, kv);
+  const bool fast = n && !user_dest && partition_eligible(mr, kv);
   PartPlan pl_local;
   // pass 1 may have been done by map_intcount while it wrote this KV (emit_and_plan)
   const bool planned = fast && kv->plan && kv->ahead_n == n && kv->plan_nranks == P;
@@ -496,7 +518,13 @@ static void aggregate_impl(mrgpu_mr *mr)
     Buf<uint32_t> d0(pool, n), d1(pool, n), i0(pool, n), i1(pool, n);
     Buf<unsigned long long> hist(pool, 8 * RADIX);
     MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
-    if (n) {
+    unsigned long long h_bad = 0;
+    if (n && user_dest) {
+      MR_CUDA(cudaMemsetAsync(mr->d_small + 4, 0, 8, s));
+      user_dest_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>(user_dest, n, (uint32_t) P, d0.p, i0.p, hist.p, mr->d_small + 4);
+      MR_CUDA(cudaGetLastError());
+      MR_CUDA(cudaMemcpyAsync(&h_bad, mr->d_small + 4, 8, cudaMemcpyDeviceToHost, s));
+    } else if (n) {
       ProfScope ps(pool, "aggregate_partition", (double) kv->nbytes + 8.0 * n);
       partition_dest_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>(kv->data, kv->uniform ? nullptr : kv->offs, kv->recsize, n, al, (uint32_t) P, d0.p,
                                                                   i0.p, hist.p);
@@ -505,6 +533,9 @@ static void aggregate_impl(mrgpu_mr *mr)
     std::vector<unsigned long long> cnt(RADIX);
     MR_CUDA(cudaMemcpyAsync(cnt.data(), hist.p, RADIX * 8, cudaMemcpyDeviceToHost, s));
     sync(mr);
+    // (the reference indexes its send counts with whatever the hash returned; a rank outside the communicator is
+    //  a crash there -- here the pair goes to rank 0 and the call reports the misuse after the exchange)
+    if (h_bad) mr->err = "aggregate: the user hash returned a processor outside [0, nprocs)";
     // bytes 1..3 of the dest "key" are all zero: mark them as known-constant
     MR_CUDA(cudaMemsetAsync(hist.p + RADIX, 0, 3 * RADIX * 8, s));
     int cur = radix_sort_pairs<uint32_t, uint32_t, true>(pool, d0.p, d1.p, i0.p, i1.p, n, 0x1, true, hist.p);
@@ -681,6 +712,29 @@ extern "C" int mrgpu_aggregate(mrgpu_mr *mr, uint64_t *nkv)
   aggregate_impl(mr);
   sync(mr);
   if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);  // pairs only moved: the global count is the one before
+  API_END(mr)
+}
+
+// aggregate(myhash) src/mapreduce.cpp:385-563 with proclist[i] = myhash(key,keybytes) % nprocs (:466-470) evaluated by the
+// CALLER: dest[i] = destination rank of pair i (host or device memory, one int per pair of this rank's KV in order).
+extern "C" int mrgpu_aggregate_dest(mrgpu_mr *mr, const int32_t *dest, uint64_t ndest, uint64_t *nkv)
+{
+  API_BEGIN(mr)
+  if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot aggregate without KeyValue");
+  if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  if (ndest != mr->kv->nkv) MR_FAIL(MRGPU_EINVAL, "aggregate: one destination per pair is required");
+  if (ndest && !dest) MR_FAIL(MRGPU_EINVAL, "null destinations");
+  if (mr->nranks > 1) {
+    Buf<int32_t> tmp;
+    // an empty rank still takes part in the collective calls
+    static const int32_t none = 0;
+    const int32_t *dd = ndest ? stage_input(mr, dest, ndest, tmp, false) : &none;
+    mr->err.clear();
+    aggregate_impl(mr, dd);
+    sync(mr);
+    if (!mr->err.empty()) MR_FAIL(MRGPU_EINVAL, mr->err);
+  }
+  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);
   API_END(mr)
 }
 

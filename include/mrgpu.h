@@ -165,6 +165,12 @@ int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv);
 /* MapReduce::aggregate(NULL) src/mapreduce.cpp:385-563 + Irregular src/irregular.cpp:95-301: pairs move to
  * rank hashlittle(key,keybytes,nprocs) % nprocs; arrival order = (source rank, original order). */
 int mrgpu_aggregate(mrgpu_mr *mr, uint64_t *nkv);
+/* MapReduce::aggregate(myhash) src/mapreduce.cpp:385-563 with a user hash function: the reference computes
+ * proclist[i] = myhash(key,keybytes) % nprocs on the host (:466-470); here the caller does exactly that (the hash is
+ * host code) and passes one destination rank per pair of this rank's KeyValue, in KV order, in host or device memory.
+ * Delivery order as always: by source rank, original order within a source.  A destination outside [0, nprocs) is
+ * reported as MRGPU_EINVAL (the reference would index out of bounds). */
+int mrgpu_aggregate_dest(mrgpu_mr *mr, const int32_t *dest, uint64_t ndest, uint64_t *nkv);
 /* The host half of Irregular::setup (src/irregular.cpp:95-242): given the all-gathered table of what every
  * rank sends -- row q (2*nranks+2 u64): {records, bytes} per destination, then {kind 0 empty / 1 variable / 2
  * uniform, keybytes<<32|valuebytes} -- compute what `rank` receives from each source (rcount, rbytes),
@@ -232,6 +238,21 @@ int mrgpu_kv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst);
  * reference's multivalue_blocks()/multivalue_block() protocol (src/mapreduce.cpp:1874-1925). */
 int mrgpu_kmv_page_info(mrgpu_mr *mr, uint64_t ipage, uint64_t *nkey, uint64_t *alignsize, int *is_extended);
 int mrgpu_kmv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst);
+
+/* MapReduce::scan(myscan, ptr) src/mapreduce.cpp:1933-1976 (KV form) and :1984-2065 (KMV form): read-only walk that
+ * calls a HOST function for every pair.  Pages are staged to the host one at a time; the pointers a callback gets are
+ * valid only during the callback (the reference's rule).  Returns the global pair count like the reference.
+ * A KMV pair bigger than a page reaches the callback as multivalue == NULL, nvalues == 0 with the handle in the
+ * valuesizes slot (the reference passes its MapReduce* there, src/mapreduce.cpp:2041-2053); inside the callback
+ * mrgpu_multivalue_blocks / _block_select / _block give the values block by block:
+ * MapReduce::multivalue_blocks src/mapreduce.cpp:1874, multivalue_block_select :1887, multivalue_block :1901. */
+typedef void (*mrgpu_scan_kv_fn)(char *key, int keybytes, char *value, int valuebytes, void *ptr);
+typedef void (*mrgpu_scan_kmv_fn)(char *key, int keybytes, char *multivalue, int nvalues, int *valuesizes, void *ptr);
+int mrgpu_scan_kv(mrgpu_mr *mr, mrgpu_scan_kv_fn fn, void *ptr, uint64_t *nkv);
+int mrgpu_scan_kmv(mrgpu_mr *mr, mrgpu_scan_kmv_fn fn, void *ptr, uint64_t *nkmv);
+int mrgpu_multivalue_blocks(mrgpu_mr *mr, int *nblock, uint64_t *nvalue_total);
+int mrgpu_multivalue_block_select(mrgpu_mr *mr, int which);
+int mrgpu_multivalue_block(mrgpu_mr *mr, int iblock, char **multivalue, int **valuesizes, int *nvalues);
 
 /* No counterpart in the reference (its pages live in host memory: KeyValue::request_page src/keyvalue.cpp:288).
  * Device views for callers that stay on the GPU (device functors of their own, torch tensors, bench):

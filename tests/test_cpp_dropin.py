@@ -77,3 +77,37 @@ def test_reference_wordfreq_example_unmodified():
     counts = [int(x.split()[0]) for x in r[:10]]
     assert len(set(counts)) == 10, "fixture should have distinct top counts (ties are ordered by an unspecified qsort order)"
     assert g == r
+
+
+MR_REF, MR_GPU = os.path.join(REF, "multirank_ref"), os.path.join(BIN, "multirank_gpu")
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not (os.path.exists(MR_REF) and os.path.exists(MR_GPU)), reason="multi-rank drop-in binaries not built")
+def test_class_api_one_and_two_ranks_without_mpi():
+    """tests/cpp/multirank_smoke.cpp (class API only: default and USER hash partition, host and stock device callbacks,
+    gather, scan) linked with the reference library on 1 rank vs the GPU mirror on 1 rank and -- with two GPUs -- as two
+    processes that find each other through RANK / WORLD_SIZE / MRGPU_PORT (cpp/mpi.h, no MPI): rank 0 must print exactly
+    what the reference prints, rank 1 nothing."""
+    import torch
+
+    ref = _run(MR_REF).stdout
+    assert ref.count("\n") > 1500 and "== user hash: pairs 24000 unique 211" in ref
+    assert _run(MR_GPU).stdout == ref
+    if torch.cuda.device_count() < 2:
+        return
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r), MRGPU_PORT="29731")
+        procs.append(subprocess.Popen([MR_GPU], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    outs = []
+    for p in procs:
+        try:
+            outs.append(p.communicate(timeout=300))
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+    assert all(p.returncode == 0 for p in procs), [o[0][-800:] + o[1][-800:] for o in outs]
+    assert outs[0][0] == ref
+    assert outs[1][0] == ""
