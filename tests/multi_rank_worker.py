@@ -87,6 +87,19 @@ def main_nccl():
                     assert orc.hashlittle(k, world) % world == q
         mr.destroy()
 
+    # aggregate(myhash), src/mapreduce.cpp:466-470: destination = myhash(key, keybytes) % nprocs, evaluated on the host
+    def myhash(key, keybytes):
+        return (key[0] if keybytes else 0) * 31 + keybytes
+
+    for case in range(4):
+        mr = g.MapReduce(device=local, rank=rank, nranks=world, unique_id=uid)
+        total = sum(len(shard_records(case, q)) for q in range(world))
+        mr.kv_add(shard_records(case, rank))
+        assert mr.aggregate(myhash) == total
+        want = [rec for q in range(world) for rec in shard_records(case, q) if myhash(rec[0], len(rec[0])) % world == rank]
+        assert mr.scan_kv() == want, f"user hash, case {case}: wrong pairs/order on rank {rank}"
+        mr.destroy()
+
     # gather(numprocs), src/mapreduce.cpp:893-1036: rank r < numprocs ends with its own pairs followed by those of
     # ranks r+numprocs, r+2*numprocs, ... ; the others end empty
     for case in range(4):
