@@ -117,6 +117,7 @@ def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
     mr = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
     T = Timer()
     truth = torch.zeros(nurls, dtype=torch.int64, device=DEV)
+    truth2 = torch.zeros(nurls * nfiles, dtype=torch.int32, device=DEV)   # postings per (url, file)
     per_file = total_bytes // nfiles
     rows_per_file = per_file // rowlen
     nlinks, nbytes, start = 0, 0, 0
@@ -126,7 +127,9 @@ def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
         z = W.splitmix64_torch(idx, W.HTML_SEED)
         u = W._lsr_t(z, 11).to(torch.float64) * (1.0 / 9007199254740992.0)
         k = torch.clamp(torch.searchsorted(cdf_t, u, right=True), max=nurls - 1)
-        truth += torch.bincount(k, minlength=nurls)
+        bc = torch.bincount(k, minlength=nurls)
+        truth += bc
+        truth2.view(nurls, nfiles)[:, f] += bc.to(torch.int32)
         text = row_t.repeat(rows_per_file, 1)
         h = k % 10000
         for j in range(4):
@@ -144,21 +147,47 @@ def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
     assert nuniq == int((truth > 0).sum().item())
     st = mr.kmv_stats()
     assert st.nvalue == nlinks and st.valuesize == nlinks * len("part-00000\0")
-    # postings -> per-URL posting counts, against the generator
-    assert T.run("reduce", lambda: mr.reduce("count")) == nuniq
-    mr.sort_keys(5)
-    counts = []
-    for nkey, page in mr.kv_pages():
-        counts.append(np.frombuffer(page, dtype=np.uint8).reshape(nkey, -1)[:, -4:].copy().view(np.int32).reshape(-1))
-    counts = np.concatenate(counts)
-    want = truth.cpu().numpy()
-    # URL strings sort like (host, path) strings; compare as multisets of counts plus the total
-    assert int(counts.sum()) == nlinks and np.array_equal(np.sort(counts), np.sort(want[want > 0]))
+    # reduce = the reference's postings callback (cpu/InvertedIndex.cpp:335-385) as a device functor: (URL, "f1 f2 ... fn ")
+    assert T.run("reduce", lambda: mr.reduce("postings")) == nuniq
+    # ---- check: EVERY posting list against the generator.  The result stays on the GPU; its records are parsed there:
+    # record = int 30 | int vb | URL (30 bytes) | pad to 40 | n x "part-NNNNN " | NUL.  (url, file) -> how many postings.
+    import ctypes
+
+    d, nb, o, _ = mr.kv_device_view()
+    sync()
+    rt = ctypes.CDLL("libcudart.so.12")
+    data = torch.empty(nb, dtype=torch.uint8, device=DEV)
+    offs = torch.empty(nuniq + 1, dtype=torch.int64, device=DEV)
+    assert rt.cudaMemcpy(ctypes.c_void_p(data.data_ptr()), ctypes.c_void_p(d), ctypes.c_size_t(nb), 3) == 0
+    assert rt.cudaMemcpy(ctypes.c_void_p(offs.data_ptr()), ctypes.c_void_p(o), ctypes.c_size_t(8 * (nuniq + 1)), 3) == 0
+    sync()
+    rec = offs[:-1]
+    hdr = data.view(torch.int32)
+    assert bool((hdr[rec // 4] == 30).all()), "key length"
+    vb = hdr[rec // 4 + 1].to(torch.int64)
+    assert bool(((vb - 1) % 11 == 0).all()) and bool((offs[1:] - rec == ((40 + vb + 3) // 4) * 4).all()), "record layout"
+    npost = (vb - 1) // 11
+    assert int(npost.sum().item()) == nlinks
+    url = torch.zeros(nuniq, dtype=torch.int64, device=DEV)
+    for j in range(7):
+        url = url * 10 + (data[rec + 8 + 23 + j].to(torch.int64) - 48)
+    owner = torch.repeat_interleave(torch.arange(nuniq, device=DEV), npost)
+    first = torch.cumsum(npost, 0) - npost
+    within = torch.arange(nlinks, device=DEV) - first[owner]
+    pos = rec[owner] + 40 + 11 * within
+    fid = torch.zeros(nlinks, dtype=torch.int64, device=DEV)
+    for j in range(5):
+        fid = fid * 10 + (data[pos + 5 + j].to(torch.int64) - 48)
+    assert bool((data[pos + 10] == 32).all()) and bool((data[rec + 40 + vb - 1] == 0).all()), "separators"
+    got2 = torch.bincount(url[owner] * nfiles + fid, minlength=nurls * nfiles)
+    nbad = int((got2 != truth2).sum().item())
+    assert nbad == 0, f"{nbad} (url, file) posting counts differ from the generator's"
+    del data, got2, owner, within, pos, fid
     mr.destroy()
     secs = T.t["map"] + T.t["aggregate"] + T.t["convert"] + T.t["reduce"]
-    return {"config": "InvertedIndex: 16 GiB synthetic HTML in 128 files, map(href FSM)->aggregate->convert->reduce", "pairs": nlinks,
+    return {"config": "InvertedIndex: 16 GiB synthetic HTML in 128 files, map(href FSM)->aggregate->convert->reduce(postings)", "pairs": nlinks,
             "text_bytes": nbytes, "unique": nuniq, "secs": T.t, "pairs_per_s": nlinks / secs, "text_gbs": nbytes / 1e9 / T.t["map"],
-            "check": "posting counts per URL equal the generator's bincount (as multiset) and sum to the number of links"}
+            "check": "every posting list: the number of postings of every (URL, file) pair equals the generator's count"}
 
 
 # ------------------------------------------------------------------------------------------ configs 4/5: R-MAT + degree

@@ -21,7 +21,7 @@ __all__ = ["MapReduce", "MRError", "lib", "LIB_PATH", "Stats"]
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MRGPU_LIB", os.path.join(_HERE, "libmrgpu.so"))  # MRGPU_LIB: an alternative build, for A/B timing
 
-REDUCE = {"count": 0, "sum": 1, "cull": 2}
+REDUCE = {"count": 0, "sum": 1, "cull": 2, "postings": 3, "nonzero": 4, "degree": 5, "histo": 6}
 MAPMR = {"edge_to_vertices": 0, "edge_to_vertex": 1, "invert": 2}
 
 

@@ -46,6 +46,10 @@ namespace gpu {
 void count(char *, int, char *, int, int *, KeyValue *, void *) {}
 void sum(char *, int, char *, int, int *, KeyValue *, void *) {}
 void cull(char *, int, char *, int, int *, KeyValue *, void *) {}
+void postings(char *, int, char *, int, int *, KeyValue *, void *) {}
+void nonzero(char *, int, char *, int, int *, KeyValue *, void *) {}
+void degree(char *, int, char *, int, int *, KeyValue *, void *) {}
+void histo(char *, int, char *, int, int *, KeyValue *, void *) {}
 void edge_to_vertices(uint64_t, char *, int, char *, int, KeyValue *, void *) {}
 void edge_to_vertex(uint64_t, char *, int, char *, int, KeyValue *, void *) {}
 void invert(uint64_t, char *, int, char *, int, KeyValue *, void *) {}
@@ -63,6 +67,10 @@ static int stock_reduce(ReduceFn f)
   if (f == gpu::count) return MRGPU_REDUCE_COUNT;
   if (f == gpu::sum) return MRGPU_REDUCE_SUM;
   if (f == gpu::cull) return MRGPU_REDUCE_CULL;
+  if (f == gpu::postings) return MRGPU_REDUCE_POSTINGS;
+  if (f == gpu::nonzero) return MRGPU_REDUCE_NONZERO;
+  if (f == gpu::degree) return MRGPU_REDUCE_DEGREE;
+  if (f == gpu::histo) return MRGPU_REDUCE_HISTO;
   return -1;
 }
 static int stock_mapmr(MapMrFn f)

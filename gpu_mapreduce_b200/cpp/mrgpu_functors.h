@@ -40,6 +40,11 @@ void href(int, char *, KeyValue *, void *);
 void count(char *, int, char *, int, int *, KeyValue *, void *);
 void sum(char *, int, char *, int, int *, KeyValue *, void *);
 void cull(char *, int, char *, int, int *, KeyValue *, void *);
+// cpu/InvertedIndex.cpp:335-385 as a pair instead of a file line: (key, "v1 v2 ... vn " + NUL); examples/rmat.cpp:266-295
+void postings(char *, int, char *, int, int *, KeyValue *, void *);
+void nonzero(char *, int, char *, int, int *, KeyValue *, void *);
+void degree(char *, int, char *, int, int *, KeyValue *, void *);
+void histo(char *, int, char *, int, int *, KeyValue *, void *);
 void edge_to_vertices(uint64_t, char *, int, char *, int, KeyValue *, void *);
 void edge_to_vertex(uint64_t, char *, int, char *, int, KeyValue *, void *);
 void invert(uint64_t, char *, int, char *, int, KeyValue *, void *);

@@ -40,11 +40,21 @@ __device__ __forceinline__ KmvHead kmv_head(const uint8_t *rec, Align al)
   return h;
 }
 
-// output value of functor f for a KMV pair: count/sum -> the int nvalue; cull -> first value
+// output key / value sizes of functor f for a KMV pair:
+//   count / sum / histo -> (key, int nvalues);  cull -> (key, first value);  nonzero -> (first half of the key, NULL);
+//   degree -> (int nvalues, NULL);  postings -> (key, every value with its terminating NUL turned into ' ', then one NUL)
 __device__ __forceinline__ uint32_t reduce_out_vb(int functor, const KmvHead &h)
 {
-  if (functor == MRGPU_REDUCE_CULL) return *(const uint32_t *) h.sizes;
+  if (functor == MRGPU_REDUCE_CULL) return h.nv ? *(const uint32_t *) h.sizes : 0;
+  if (functor == MRGPU_REDUCE_NONZERO || functor == MRGPU_REDUCE_DEGREE) return 0;
+  if (functor == MRGPU_REDUCE_POSTINGS) return h.mvb + 1;
   return 4;
+}
+__device__ __forceinline__ uint32_t reduce_out_kb(int functor, const KmvHead &h)
+{
+  if (functor == MRGPU_REDUCE_NONZERO) return h.kb / 2;
+  if (functor == MRGPU_REDUCE_DEGREE) return 4;
+  return h.kb;
 }
 
 // fast path: 4-byte keys, default alignment, count/sum -> one 16-byte store per pair
@@ -111,15 +121,75 @@ reduce_generic_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restric
   uint8_t *dst = out + (ooffs ? ooffs[u] : u * ors);
   if (functor == MRGPU_REDUCE_CULL) {
     write_kv_record(dst, al, h.kb, h.key, *(const uint32_t *) h.sizes, h.values);
+  } else if (functor == MRGPU_REDUCE_NONZERO) {
+    write_kv_record(dst, al, h.kb / 2, h.key, 0, h.key);
+  } else if (functor == MRGPU_REDUCE_DEGREE) {
+    uint32_t cnt = h.nv;
+    write_kv_record(dst, al, 4, (const uint8_t *) &cnt, 0, h.key);
   } else {
     uint32_t cnt = h.nv;
     write_kv_record(dst, al, h.kb, h.key, 4, (const uint8_t *) &cnt);
   }
 }
 
+// postings (cpu/InvertedIndex.cpp:335-385 prints, per KMV pair, `key \t v1 v2 ... vn \n`: each value as a C string followed
+// by a space): one warp per KMV pair writes the header and key, then streams the value bytes -- the values of a KMV
+// pair are contiguous -- replacing the last byte of every value (its NUL) by a space; one NUL closes the string.
+// Which bytes are "last bytes" comes from the value sizes: lanes take values round-robin and poke the spaces in after
+// the bulk copy (a value's last byte is at the running sum of the sizes, found with a warp scan per 32 values).
+__global__ void __launch_bounds__(256)
+reduce_postings_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restrict__ offs, uint64_t U, Align al, uint8_t *__restrict__ out,
+                       const uint64_t *__restrict__ ooffs)
+{
+  const uint64_t u = ((uint64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (u >= U) return;
+  KmvHead h = kmv_head(kmv + offs[u], al);
+  uint8_t *dst = out + ooffs[u];
+  const uint32_t vb = h.mvb + 1, ko = kv_key_off(al), vo = kv_val_off(al, h.kb), end = kv_rec_size(al, h.kb, vb);
+  if (lane == 0) {
+    ((uint32_t *) dst)[0] = h.kb;
+    ((uint32_t *) dst)[1] = vb;
+  }
+  for (uint32_t q = 8 + lane; q < ko; q += 32) dst[q] = 0;
+  for (uint32_t q = lane; q < h.kb; q += 32) dst[ko + q] = h.key[q];
+  for (uint32_t q = ko + h.kb + lane; q < vo; q += 32) dst[q] = 0;
+  for (uint32_t q = lane; q < h.mvb; q += 32) dst[vo + q] = h.values[q];
+  for (uint32_t q = vo + h.mvb + lane; q < end; q += 32) dst[q] = 0;  // the closing NUL and the padding
+  __syncwarp();
+  // spaces: value i ends at (sum of sizes[0..i]) - 1
+  const uint32_t *sizes = (const uint32_t *) h.sizes;
+  uint32_t base = 0;
+  for (uint32_t i0 = 0; i0 < h.nv; i0 += 32) {
+    const uint32_t i = i0 + lane;
+    uint32_t sz = i < h.nv ? sizes[i] : 0, incl = sz;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (i < h.nv && sz) dst[vo + base + incl - 1] = ' ';
+    base += __shfl_sync(0xFFFFFFFFu, incl, 31);
+  }
+}
+
+// factored KMV (key words, count, shared value) -> nonzero / degree records, one thread per pair
+__global__ void __launch_bounds__(256)
+reduce_factored_shape_kernel(const uint32_t *__restrict__ fkey, const uint32_t *__restrict__ fcnt, uint64_t U, int functor, Align al, uint32_t kb,
+                             uint8_t *out, uint64_t ors)
+{
+  uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= U) return;
+  const uint8_t *key = (const uint8_t *) (fkey + u * (kb / 4));
+  const uint32_t cnt = fcnt[u];
+  if (functor == MRGPU_REDUCE_NONZERO) write_kv_record(out + u * ors, al, kb / 2, key, 0, key);
+  else write_kv_record(out + u * ors, al, 4, (const uint8_t *) &cnt, 0, key);
+}
+
 static void reduce_impl(mrgpu_mr *mr, int functor)
 {
-  if (functor < 0 || functor > MRGPU_REDUCE_CULL) MR_FAIL(MRGPU_EINVAL, "unknown reduce functor");
+  if (functor < 0 || functor > MRGPU_REDUCE_HISTO) MR_FAIL(MRGPU_EINVAL, "unknown reduce functor");
+  if (functor == MRGPU_REDUCE_HISTO) functor = MRGPU_REDUCE_COUNT;  // examples/rmat.cpp:289-295 emits (key, int nvalues): the same pair
   DevKMV *kmv = mr->kmv;
   Pool &pool = mr->pool;
   cudaStream_t s = pool.stream;
@@ -130,15 +200,24 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
     const uint8_t *kd = kmv->data;
     const uint64_t *ko = kmv->offs;
     bool cull = functor == MRGPU_REDUCE_CULL;
-    bool uni = kmv->ukb >= 0 && (!cull || kmv->uvb >= 0);
+    const bool shape = functor == MRGPU_REDUCE_NONZERO || functor == MRGPU_REDUCE_DEGREE;
+    if (functor == MRGPU_REDUCE_NONZERO && kmv->ukb >= 0 && (kmv->ukb % 2)) MR_FAIL(MRGPU_EINVAL, "reduce(nonzero): the key is not a pair of vertices");
+    if (functor == MRGPU_REDUCE_POSTINGS) kmv_expand(mr, kmv);  // reads the values
+    bool uni = kmv->ukb >= 0 && (!cull || kmv->uvb >= 0) && functor != MRGPU_REDUCE_POSTINGS;
     if (U == 0) {
       // empty KV
     } else if (uni) {
-      uint32_t kb = (uint32_t) kmv->ukb, vb = cull ? (uint32_t) kmv->uvb : 4;
+      const uint32_t ikb = (uint32_t) kmv->ukb;  // key bytes of the KMV pairs
+      uint32_t kb = functor == MRGPU_REDUCE_NONZERO ? ikb / 2 : (functor == MRGPU_REDUCE_DEGREE ? 4 : ikb);
+      uint32_t vb = shape ? 0 : (cull ? (uint32_t) kmv->uvb : 4);
       uint32_t rs = kv_rec_size(al, kb, vb);
       kv->reserve_bytes(U * rs);
-      ProfScope ps(pool, "reduce", (double) U * (12 + 4 + kb + rs));
-      if (kmv->factored) {
+      ProfScope ps(pool, "reduce", (double) U * (12 + 4 + ikb + rs));
+      if (shape && kmv->factored)
+        reduce_factored_shape_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kmv->fkey, kmv->fcnt, U, functor, al, ikb, kv->data, rs);
+      else if (shape)
+        reduce_generic_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, functor, al, kv->data, nullptr, rs);
+      else if (kmv->factored) {
         if (!cull && kb == 4 && rs == 16 && kv_key_off(al) == 8 && al.k == 4)
           reduce_factored16_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kmv->fkey, kmv->fcnt, U, (int4 *) kv->data);
         else if (al.k == 4 && al.v == 4 && rs == 8 + kb + vb)
@@ -164,13 +243,17 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
       kv->uniform = false;
       kv->reserve_offs(U + 1);
       uint64_t *oo = kv->offs;
-      unsigned long long *vsum = mr->d_small + 1;
+      unsigned long long *vsum = mr->d_small + 1, *toobig = mr->d_small + 5;
       MR_CUDA(cudaMemsetAsync(vsum, 0, 8, s));
+      MR_CUDA(cudaMemsetAsync(toobig, 0, 8, s));
+      const uint64_t pagesize = mr->pagesize;
       scan_apply(
           pool, U,
           [=] __device__(uint64_t u) -> unsigned long long {
             KmvHead h = kmv_head(kd + ko[u], al);
-            return kv_rec_size(al, h.kb, reduce_out_vb(functor, h));
+            const uint64_t sz = round_up(round_up(round_up(8, al.k) + reduce_out_kb(functor, h), al.v) + (uint64_t) reduce_out_vb(functor, h), al.t);
+            if (sz > pagesize || sz > 0x7FFFFFFFull) *toobig = 1;  // KeyValue::add: "Single key/value pair exceeds page size"
+            return sz;
           },
           [=] __device__(uint64_t u, unsigned long long e, unsigned long long) {
             oo[u] = e;
@@ -178,15 +261,20 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
             warp_add(vsum, reduce_out_vb(functor, h));
           },
           mr->d_small);
-      fetch_small(mr, 2);
+      fetch_small(mr, 6);
+      if (mr->h_small[5]) MR_FAIL(MRGPU_ELIMIT, "Single key/value pair exceeds page size");
       uint64_t total = mr->h_small[0];
       MR_CUDA(cudaMemcpyAsync(oo + U, &total, 8, cudaMemcpyHostToDevice, s));
       kv->reserve_bytes(total);
-      reduce_generic_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, functor, al, kv->data, oo, 0);
+      if (functor == MRGPU_REDUCE_POSTINGS) {
+        ProfScope ps(pool, "reduce_postings", (double) kmv->nbytes + (double) total);
+        reduce_postings_kernel<<<(unsigned) ((U * 32 + 255) / 256), 256, 0, s>>>(kd, ko, U, al, kv->data, oo);
+      } else
+        reduce_generic_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, functor, al, kv->data, oo, 0);
       MR_CUDA(cudaGetLastError());
       kv->nbytes = total;
       kv->nkv = U;
-      kv->ksize = kmv->ksize;
+      kv->ksize = functor == MRGPU_REDUCE_NONZERO ? kmv->ksize / 2 : (functor == MRGPU_REDUCE_DEGREE ? 4 * U : kmv->ksize);
       kv->vsize = mr->h_small[1];
     }
     sync(mr);

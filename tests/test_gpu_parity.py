@@ -734,6 +734,72 @@ def test_invindex_golden(MR, golden):
     assert H.canon_kmv(mr.scan_kmv()) == H.canon_kmv(H.kmv_decode(golden["invindex.kmv"]))
 
 
+def _postings_line(values):
+    """cpu/InvertedIndex.cpp:352-361: every value printed as a C string followed by a space"""
+    return b"".join(v[:v.index(b"\0")] + b" " for v in values) + b"\0"
+
+
+@pytest.mark.parametrize("compact", [1, 0])
+def test_reduce_postings_golden(MR, golden, compact):
+    """InvertedIndex end to end: href scanner -> aggregate -> convert -> reduce(postings); the postings string of every URL
+    is the reference's output line (values of the reference's own KMV fixture, in ITS arrival order, printed by its rule)"""
+    mr = MR(compact=compact)
+    for i in range(4):
+        mr.map_href(golden[f"invindex.in{i}"], f"part-{i:05d}", addflag=1 if i else 0)
+    mr.aggregate()
+    nu = mr.convert()
+    want = {k: _postings_line(vals) for k, vals in H.kmv_decode(golden["invindex.kmv"])}
+    assert mr.reduce("postings") == nu == len(want)
+    got = mr.scan_kv()
+    assert dict(got) == want and len(got) == len(want)
+    st = mr.kv_stats()
+    assert st.keysize == sum(len(k) for k in want) and st.valuesize == sum(len(v) for v in want.values())
+
+
+def test_reduce_postings_mixed_lengths_and_page_limit(MR):
+    import gpu_mapreduce_b200 as g
+
+    r = np.random.RandomState(21)
+    docs = [b"d%d" % i + b"x" * (i % 9) + b"\0" for i in range(40)]
+    recs = [(b"url%03d" % r.randint(0, 60), docs[r.randint(0, 40)]) for _ in range(5000)]
+    recs += [(b"hot", docs[i % 40]) for i in range(3000)]           # one key with thousands of postings (warp loop over > 32 values)
+    mr = MR()
+    mr.kv_add(recs)
+    mr.convert()
+    want = {}
+    for k, v in recs:
+        want.setdefault(k, []).append(v)
+    mr.reduce("postings")
+    assert dict(mr.scan_kv()) == {k: _postings_line(v) for k, v in want.items()}
+    small = MR(memsize=-4096)                                        # 4 KiB pages: the hot key's line cannot be a pair
+    small.kv_add(recs)
+    small.convert()
+    with pytest.raises(g.MRError, match="exceeds page size"):
+        small.reduce("postings")
+
+
+@pytest.mark.parametrize("compact", [1, 0])
+def test_rmat_example_reduces_nonzero_degree_histo(MR, compact):
+    """examples/rmat.cpp:266-295 (32-bit vertices): nonzero -> collate -> degree -> collate -> histo"""
+    from collections import Counter
+
+    r = np.random.RandomState(5)
+    edges = {(int(a), int(b)) for a, b in r.zipf(1.5, size=(6000, 2)) % 200}
+    mr = MR(compact=compact)
+    mr.kv_add([(struct.pack("<ii", a, b), b"") for a, b in edges] * 2)       # every edge twice, as before the cull
+    assert mr.collate() == len(edges)
+    assert mr.reduce("nonzero") == len(edges)
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv([(struct.pack("<i", a), b"") for a, _ in edges])
+    rows = Counter(a for a, _ in edges)
+    assert mr.collate() == len(rows)
+    assert mr.reduce("degree") == len(rows)
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv([(struct.pack("<i", c), b"") for c in rows.values()])
+    hist = Counter(rows.values())
+    assert mr.collate() == len(hist)
+    assert mr.reduce("histo") == len(hist)
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv([(struct.pack("<i", c), struct.pack("<i", n)) for c, n in hist.items()])
+
+
 def test_href_fsm_random_vs_oracle(MR, oracle):
     r = np.random.RandomState(77)
     toks = [b"<", b"a", b" ", b"h", b"r", b"e", b"f", b"=", b'"', b"x", b"href", b"<a href=\"", b"u", b">", b"\t"]
