@@ -161,6 +161,7 @@ static void order_after(mrgpu_mr *mr, mrgpu_mr *other)
 #include "ops_map.cuh"
 #include "ops_convert.cuh"
 #include "ops_convert_dense.cuh"
+#include "ops_convert_hash.cuh"
 #include "ops_text.cuh"
 #include "ops_reduce.cuh"
 #include "ops_sort.cuh"

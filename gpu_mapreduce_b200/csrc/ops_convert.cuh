@@ -556,6 +556,7 @@ static void convert_general(mrgpu_mr *mr)
 }
 
 static bool convert_dense(mrgpu_mr *mr);
+static bool convert_hash(mrgpu_mr *mr);
 
 static void convert_impl(mrgpu_mr *mr)
 {
@@ -637,6 +638,9 @@ static void convert_impl(mrgpu_mr *mr)
         done = true;
       }
     }
+    // variable-length keys without values (words): count by hashing; falls through to the fingerprint sort when the
+    // table overflows (too many distinct keys) or two keys share a fingerprint
+    if (!done && !kv->uniform) done = convert_hash(mr);
     if (!done) convert_general(mr);
   }
   // convert consumes the KV (src/mapreduce.cpp:876-878: "delete kv; kv = NULL")

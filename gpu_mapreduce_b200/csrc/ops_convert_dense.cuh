@@ -377,8 +377,14 @@ dense_fill_kernel(uint32_t *__restrict__ out, uint64_t total_words, const uint64
 }
 
 // factored KMV -> the reference's record stream (kmv->data, kmv->offs); no-op for any other KMV
+static void kmv_expand_fvar(mrgpu_mr *mr, DevKMV *kmv);  // ops_convert_hash.cuh
+
 static void kmv_expand(mrgpu_mr *mr, DevKMV *kmv)
 {
+  if (kmv && kmv->fvar) {
+    kmv_expand_fvar(mr, kmv);
+    return;
+  }
   if (!kmv || !kmv->factored) return;
   Pool &pool = mr->pool;
   cudaStream_t s = pool.stream;

@@ -1,0 +1,284 @@
+// convert() by hashing: group-by-key for pairs that carry no value bytes, keys of any length.
+//
+// Reference: KeyMultiValue::convert hashes every key into a chained table of "Unique" records (kv2unique
+// src/keymultivalue.cpp:645-789, find :1403, hash :1428) and later re-hashes every pair to append its value
+// (kv2kmv :1139-1209).  When no pair has a value the KMV is fully described by (key, number of pairs) per distinct
+// key, so grouping is counting and a hash table is the right tool: no pair moves at all.  (Pairs WITH values keep the
+// stable sort of ops_convert.cuh: it delivers each key's values in arrival order, which atomics cannot.)
+//
+// One pass over the records:
+//   * fingerprint of the key: 64 bits = hashlittle(key, kb, seed) : a second hash (the high half is the reference's
+//     own bucket hash for seed 0);
+//   * block-local open-addressing table in shared memory (linear probing, claimed with a 64-bit CAS): the keys that
+//     come up again and again -- a text corpus is Zipf distributed -- are counted there and never reach L2;
+//   * what does not fit goes to an open-addressing table in global memory small enough to stay in L2 (CAS to claim,
+//     RED to count); each block adds its shared entries at the end;
+//   * exactness: an entry remembers one record of its group (`rep`, kept with atomicMin, which hands back the previous
+//     one); whoever joins a group compares its key BYTE FOR BYTE with the record it displaced or found there.  By
+//     induction every member equals the first, so two different keys can never be merged; if two ever share a
+//     fingerprint, or the global table fills up (more distinct keys than it holds), a flag is raised and the caller
+//     falls back to the fingerprint sort.
+// The non-empty entries are then compacted, ordered by fingerprint (the order the sort path produces) and become
+// a factored KMV with variable-length keys (DevKMV::fvar): key bytes once, a count per key.  Included by mrgpu.cu.
+#pragma once
+
+constexpr int HG_THREADS = 512;
+constexpr uint32_t HG_SLOTS = 4096;             // per block: 4096 x (8 + 4 + 4) bytes = 64 KB, three blocks per SM
+constexpr uint32_t HG_PROBES = 8;
+constexpr uint32_t HG_GLOBAL_LOG2 = 21;         // 2^21 entries x 16 bytes = 32 MB: stays in the 126 MB L2
+constexpr uint32_t HG_GLOBAL_PROBES = 64;
+constexpr uint32_t HG_UNSET = 0xFFFFFFFFu;
+
+struct HgEntry {
+  unsigned long long fp;  // 0 = empty
+  unsigned cnt;
+  unsigned rep;           // a record of this group (the smallest index seen so far)
+};
+
+struct HgRecs {
+  const uint8_t *data;
+  const uint64_t *offs;   // nullptr for uniform records
+  uint64_t recsize;
+  Align al;
+};
+
+__device__ __forceinline__ const uint8_t *hg_key(const HgRecs &r, uint64_t i, uint32_t &kb)
+{
+  const uint8_t *p = r.data + rec_off(r.offs, r.recsize, i);
+  kb = *(const uint32_t *) p;
+  return p + kv_key_off(r.al);
+}
+
+__device__ __forceinline__ bool hg_same_key(const HgRecs &r, uint32_t i, uint32_t j)
+{
+  uint32_t ka, kb;
+  const uint8_t *a = hg_key(r, i, ka), *b = hg_key(r, j, kb);
+  if (ka != kb) return false;
+  uint32_t q = 0;
+  if (((((uintptr_t) a) | ((uintptr_t) b)) & 3) == 0)
+    for (; q + 4 <= ka; q += 4)
+      if (*(const uint32_t *) (a + q) != *(const uint32_t *) (b + q)) return false;
+  for (; q < ka; q++)
+    if (a[q] != b[q]) return false;
+  return true;
+}
+
+// add `cnt` pairs represented by record `rep` to the global table; flags: 1 = table full, 2 = fingerprint collision
+__device__ __forceinline__ void hg_global_add(HgEntry *__restrict__ g, uint32_t gmask, unsigned long long fp, unsigned cnt, unsigned rep,
+                                              const HgRecs &r, unsigned long long *flags)
+{
+  uint32_t slot = (uint32_t) (fp >> 20) & gmask;
+  for (uint32_t p = 0; p < HG_GLOBAL_PROBES; p++) {
+    unsigned long long cur = g[slot].fp;
+    if (cur == 0) cur = atomicCAS(&g[slot].fp, 0ull, fp);
+    if (cur == 0 || cur == fp) {
+      atomicAdd(&g[slot].cnt, cnt);
+      const unsigned old = atomicMin(&g[slot].rep, rep);
+      if (old != HG_UNSET && old != rep && !hg_same_key(r, rep, old)) atomicOr(flags, 2ull);
+      return;
+    }
+    slot = (slot + 1) & gmask;
+  }
+  atomicOr(flags, 1ull);
+}
+
+__global__ void __launch_bounds__(HG_THREADS)
+hash_group_kernel(HgRecs r, uint64_t n, uint32_t seed, HgEntry *__restrict__ g, uint32_t gmask, unsigned long long *flags)
+{
+  extern __shared__ __align__(16) unsigned char hg_sm[];
+  unsigned long long *s_fp = (unsigned long long *) hg_sm;
+  unsigned *s_cnt = (unsigned *) (s_fp + HG_SLOTS), *s_rep = s_cnt + HG_SLOTS;
+  for (uint32_t i = threadIdx.x; i < HG_SLOTS; i += blockDim.x) s_fp[i] = 0, s_cnt[i] = 0, s_rep[i] = HG_UNSET;
+  __syncthreads();
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint32_t kb;
+    const uint8_t *k = hg_key(r, i, kb);
+    unsigned long long fp = ((unsigned long long) hashlittle(k, kb, seed) << 32) | fingerprint_lo(k, kb, seed * 0x9E3779B9u + 1);
+    if (fp == 0) fp = 1;
+    uint32_t slot = (uint32_t) (fp ^ (fp >> 37)) & (HG_SLOTS - 1);
+    bool done = false;
+#pragma unroll 1
+    for (uint32_t p = 0; p < HG_PROBES && !done; p++) {
+      unsigned long long cur = s_fp[slot];
+      if (cur == 0) cur = atomicCAS(&s_fp[slot], 0ull, fp);
+      if (cur == 0 || cur == fp) {
+        atomicAdd(&s_cnt[slot], 1u);
+        const unsigned old = atomicMin(&s_rep[slot], (unsigned) i);
+        if (old != HG_UNSET && old != (unsigned) i && !hg_same_key(r, (uint32_t) i, old)) atomicOr(flags, 2ull);
+        done = true;
+      } else
+        slot = (slot + 1) & (HG_SLOTS - 1);
+    }
+    if (!done) hg_global_add(g, gmask, fp, 1u, (unsigned) i, r, flags);  // the block's table is taken by more frequent keys
+  }
+  __syncthreads();
+  for (uint32_t s = threadIdx.x; s < HG_SLOTS; s += blockDim.x)
+    if (s_fp[s]) hg_global_add(g, gmask, s_fp[s], s_cnt[s], s_rep[s], r, flags);
+}
+
+// factored KMV with variable-length keys -> the reference's record stream (every value is empty: the size array of a
+// pair is nv zeros, there are no value bytes)
+__global__ void __launch_bounds__(256)
+fvar_expand_kernel(const uint8_t *__restrict__ vkey, const uint64_t *__restrict__ vkoff, const uint32_t *__restrict__ fcnt, uint64_t U, Align al,
+                   uint8_t *__restrict__ out, const uint64_t *__restrict__ offs)
+{
+  const uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= U) return;
+  const uint32_t kb = (uint32_t) (vkoff[u + 1] - vkoff[u]);
+  const uint64_t nv = fcnt[u];
+  uint8_t *rec = out + offs[u];
+  ((uint32_t *) rec)[0] = (uint32_t) nv;
+  ((uint32_t *) rec)[1] = kb;
+  ((uint32_t *) rec)[2] = 0;
+  uint8_t *k = rec + kmv_key_off(al, nv);
+  const uint8_t *src = vkey + vkoff[u];
+  for (uint32_t q = 0; q < kb; q++) k[q] = src[q];
+}
+
+static void kmv_expand_fvar(mrgpu_mr *mr, DevKMV *kmv)
+{
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const Align al = mr->al;
+  const uint64_t U = kmv->nkmv;
+  kmv->offs = (uint64_t *) pool.alloc((U + 1) * 8);
+  kmv->offs_cap = U + 1;
+  uint64_t *offs = kmv->offs;
+  const uint32_t *pc = kmv->fcnt;
+  const uint64_t *ko = kmv->vkoff;
+  scan_apply(
+      pool, U, [=] __device__(uint64_t u) -> unsigned long long { return kmv_rec_size(al, pc[u], (uint32_t) (ko[u + 1] - ko[u]), 0); },
+      [=] __device__(uint64_t u, unsigned long long e, unsigned long long) { offs[u] = e; }, mr->d_small, "convert_kmv_sizes", 12.0 * U);
+  fetch_small(mr, 1);
+  const uint64_t total = mr->h_small[0];
+  MR_CUDA(cudaMemcpyAsync(offs + U, &total, 8, cudaMemcpyHostToDevice, s));
+  kmv->data = (uint8_t *) pool.alloc(total ? total : 16);
+  kmv->cap = total ? total : 16;
+  kmv->nbytes = total;
+  if (total) {
+    ProfScope ps(pool, "convert_fvar_fill", (double) total);
+    MR_CUDA(cudaMemsetAsync(kmv->data, 0, total, s));  // value sizes (all zero) and padding
+    fvar_expand_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kmv->vkey, kmv->vkoff, kmv->fcnt, U, al, kmv->data, offs);
+    MR_CUDA(cudaGetLastError());
+  }
+  sync(mr);
+  pool.free(kmv->vkey, 0);
+  pool.free(kmv->vkoff, 0);
+  pool.free(kmv->fcnt, 0);
+  kmv->vkey = nullptr;
+  kmv->vkoff = nullptr;
+  kmv->fcnt = nullptr;
+  kmv->fcap = 0;
+  kmv->fvar = false;
+  kmv->h_offs_valid = false;
+}
+
+// returns true if the hash path produced mr->kmv; false = not applicable or abandoned (nothing changed)
+static bool convert_hash(mrgpu_mr *mr)
+{
+  DevKV *kv = mr->kv;
+  Pool &pool = mr->pool;
+  cudaStream_t s = pool.stream;
+  const Align al = mr->al;
+  const uint64_t n = kv->nkv;
+  static const bool disabled = getenv("MRGPU_NO_HASH_CONVERT") && atoi(getenv("MRGPU_NO_HASH_CONVERT"));
+  if (disabled || !mr->compact || kv->packed || kv->vsize != 0 || n < (1u << 12) || (al.k % 4)) return false;
+  const uint32_t gslots = 1u << HG_GLOBAL_LOG2;
+  Buf<HgEntry> table(pool, gslots);
+  unsigned long long *flags = mr->d_small + 6;
+  HgRecs r{kv->data, kv->uniform ? nullptr : kv->offs, kv->recsize, al};
+  // empty table: fp 0, count 0, rep UNSET (0xFFFFFFFF): two fills
+  static std::atomic<bool> attr[64];
+  const size_t smem = (size_t) HG_SLOTS * 16;
+  if (mr->device < 64 && !attr[mr->device].load()) {
+    MR_CUDA(cudaFuncSetAttribute(hash_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    attr[mr->device].store(true);
+  }
+  HgEntry *g = table.p;
+  {
+    ProfScope ps(pool, "convert_hash_clear", (double) gslots * 16);
+    for_each_kernel<<<grid_for(gslots, 256, 16), 256, 0, s>>>((uint64_t) gslots, [=] __device__(uint64_t i) { g[i] = HgEntry{0ull, 0u, HG_UNSET}; });
+    MR_CUDA(cudaGetLastError());
+  }
+  MR_CUDA(cudaMemsetAsync(flags, 0, 8, s));
+  {
+    ProfScope ps(pool, "convert_hash_group", (double) kv->nbytes + (kv->uniform ? 0.0 : 8.0 * n));
+    hash_group_kernel<<<kSMs * 3, HG_THREADS, smem, s>>>(r, n, 0u, g, gslots - 1, flags);
+    MR_CUDA(cudaGetLastError());
+  }
+  // non-empty entries -> (fingerprint, count, rep) arrays
+  auto used = [=] __device__(uint64_t i) -> bool { return g[i].fp != 0; };
+  FlagTiles ft;
+  flag_tiles(pool, gslots, used, ft, mr->d_small, "convert_hash_compact", (double) gslots * 16);
+  MR_CUDA(cudaMemcpyAsync(mr->h_small + 6, flags, 8, cudaMemcpyDeviceToHost, s));
+  fetch_small(mr, 1);
+  if (mr->h_small[6]) return false;  // table full or a fingerprint collision: the sort path decides
+  const uint64_t U = mr->h_small[0];
+  Buf<uint64_t> fp0(pool, U), fp1(pool, U);
+  Buf<uint32_t> ix0(pool, U), ix1(pool, U), cnt(pool, U), rep(pool, U);
+  {
+    uint64_t *pf = fp0.p;
+    uint32_t *pi = ix0.p, *pc = cnt.p, *pr = rep.p;
+    flag_sink(pool, ft, used, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
+      if (h) {
+        pf[e] = g[i].fp;
+        pi[e] = (uint32_t) e;
+        pc[e] = g[i].cnt;
+        pr[e] = g[i].rep;
+      }
+    }, "convert_hash_compact", (double) gslots * 16 + 20.0 * U);
+  }
+  table.release();
+  // KMV pairs come out in fingerprint order, like the sort path's
+  Buf<unsigned long long> hist(pool, 8 * RADIX);
+  const int cur = radix_sort_pairs<uint64_t, uint32_t, true>(pool, fp0.p, fp1.p, ix0.p, ix1.p, U, 0xFF, false, hist.p);
+  const uint32_t *perm = cur ? ix1.p : ix0.p;
+
+  DevKMV *kmv = new DevKMV(&pool);
+  try {
+    kmv->vkoff = (uint64_t *) pool.alloc((U + 1) * 8);
+    kmv->fcnt = (uint32_t *) pool.alloc((U ? U : 1) * 4);
+    kmv->fcap = U ? U : 1;
+    uint64_t *vko = kmv->vkoff;
+    uint32_t *fc = kmv->fcnt;
+    const uint32_t *pc = cnt.p, *pr = rep.p;
+    scan_apply(
+        pool, U,
+        [=] __device__(uint64_t u) -> unsigned long long {
+          uint32_t kb;
+          hg_key(r, pr[perm[u]], kb);
+          return kb;
+        },
+        [=] __device__(uint64_t u, unsigned long long e, unsigned long long) {
+          vko[u] = e;
+          fc[u] = pc[perm[u]];
+        },
+        mr->d_small, "convert_hash_keys", 24.0 * U);
+    fetch_small(mr, 1);
+    const uint64_t kbytes = mr->h_small[0];
+    MR_CUDA(cudaMemcpyAsync(vko + U, &kbytes, 8, cudaMemcpyHostToDevice, s));
+    kmv->vkey = (uint8_t *) pool.alloc(kbytes ? kbytes : 16);
+    uint8_t *vk = kmv->vkey;
+    for_each_kernel<<<grid_for(U, 256, 64), 256, 0, s>>>(U, [=] __device__(uint64_t u) {
+      uint32_t kb;
+      const uint8_t *k = hg_key(r, pr[perm[u]], kb);
+      uint8_t *d = vk + vko[u];
+      for (uint32_t q = 0; q < kb; q++) d[q] = k[q];
+    });
+    MR_CUDA(cudaGetLastError());
+    kmv->fvar = true;
+    kmv->nkmv = U;
+    kmv->nvalue = n;
+    kmv->ksize = kbytes;
+    kmv->vsize = 0;
+    kmv->ukb = kv->uniform ? (int64_t) kv->kb : -1;
+    kmv->uvb = 0;
+    sync(mr);
+  } catch (...) {
+    delete kmv;
+    throw;
+  }
+  mr->kmv = kmv;
+  return true;
+}

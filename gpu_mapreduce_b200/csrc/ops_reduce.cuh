@@ -186,6 +186,17 @@ reduce_factored_shape_kernel(const uint32_t *__restrict__ fkey, const uint32_t *
   else write_kv_record(out + u * ors, al, 4, (const uint8_t *) &cnt, 0, key);
 }
 
+// factored KMV with variable-length keys (convert's hash path): count / sum -> (key, int count), one thread per pair
+__global__ void __launch_bounds__(256)
+reduce_fvar_kernel(const uint8_t *__restrict__ vkey, const uint64_t *__restrict__ vkoff, const uint32_t *__restrict__ fcnt, uint64_t U, Align al,
+                   uint8_t *__restrict__ out, const uint64_t *__restrict__ ooffs)
+{
+  const uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= U) return;
+  const uint32_t cnt = fcnt[u];
+  write_kv_record(out + ooffs[u], al, (uint32_t) (vkoff[u + 1] - vkoff[u]), vkey + vkoff[u], 4, (const uint8_t *) &cnt);
+}
+
 static void reduce_impl(mrgpu_mr *mr, int functor)
 {
   if (functor < 0 || functor > MRGPU_REDUCE_HISTO) MR_FAIL(MRGPU_EINVAL, "unknown reduce functor");
@@ -195,14 +206,43 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
   cudaStream_t s = pool.stream;
   const Align al = mr->al;
   const uint64_t U = kmv->nkmv;
+  if (kmv->fvar && !(functor == MRGPU_REDUCE_COUNT || functor == MRGPU_REDUCE_SUM)) kmv_expand(mr, kmv);
+  if (functor == MRGPU_REDUCE_POSTINGS) kmv_expand(mr, kmv);  // reads the values
   DevKV *kv = new DevKV(&pool);
   try {
+    if (kmv->fvar && U) {
+      const uint64_t *vko = kmv->vkoff;
+      kv->uniform = false;
+      kv->reserve_offs(U + 1);
+      uint64_t *oo = kv->offs;
+      scan_apply(
+          pool, U, [=] __device__(uint64_t u) -> unsigned long long { return kv_rec_size(al, (uint32_t) (vko[u + 1] - vko[u]), 4); },
+          [=] __device__(uint64_t u, unsigned long long e, unsigned long long) { oo[u] = e; }, mr->d_small, "reduce_sizes", 16.0 * U);
+      fetch_small(mr, 1);
+      const uint64_t total = mr->h_small[0];
+      MR_CUDA(cudaMemcpyAsync(oo + U, &total, 8, cudaMemcpyHostToDevice, s));
+      kv->reserve_bytes(total);
+      {
+        ProfScope ps(pool, "reduce", (double) kmv->ksize + 12.0 * U + (double) total);
+        reduce_fvar_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kmv->vkey, kmv->vkoff, kmv->fcnt, U, al, kv->data, oo);
+        MR_CUDA(cudaGetLastError());
+      }
+      kv->nbytes = total;
+      kv->nkv = U;
+      kv->ksize = kmv->ksize;
+      kv->vsize = 4 * U;
+      sync(mr);
+      delete mr->kmv;
+      mr->kmv = nullptr;
+      delete mr->kv;
+      mr->kv = kv;
+      return;
+    }
     const uint8_t *kd = kmv->data;
     const uint64_t *ko = kmv->offs;
     bool cull = functor == MRGPU_REDUCE_CULL;
     const bool shape = functor == MRGPU_REDUCE_NONZERO || functor == MRGPU_REDUCE_DEGREE;
     if (functor == MRGPU_REDUCE_NONZERO && kmv->ukb >= 0 && (kmv->ukb % 2)) MR_FAIL(MRGPU_EINVAL, "reduce(nonzero): the key is not a pair of vertices");
-    if (functor == MRGPU_REDUCE_POSTINGS) kmv_expand(mr, kmv);  // reads the values
     bool uni = kmv->ukb >= 0 && (!cull || kmv->uvb >= 0) && functor != MRGPU_REDUCE_POSTINGS;
     if (U == 0) {
       // empty KV

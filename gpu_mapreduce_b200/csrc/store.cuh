@@ -127,6 +127,11 @@ struct DevKMV {
   uint32_t fkw = 1;
   uint64_t fcap = 0;                          // pairs allocated
   uint32_t fval[2] = {0, 0};  // the shared value (uvb bytes)
+  // ... and its variable-length-key form (convert's hash path, ops_convert_hash.cuh; every value is empty):
+  // key u = vkey[vkoff[u] .. vkoff[u+1]), fcnt[u] pairs
+  bool fvar = false;
+  uint8_t *vkey = nullptr;
+  uint64_t *vkoff = nullptr;
 
   explicit DevKMV(Pool *p) : pool(p) {}
   ~DevKMV()
@@ -135,6 +140,8 @@ struct DevKMV {
     pool->free(offs, offs_cap * 8);
     pool->free(fkey, fcap * 4 * fkw);
     pool->free(fcnt, fcap * 4);
+    pool->free(vkey, 0);
+    pool->free(vkoff, 0);
   }
 };
 

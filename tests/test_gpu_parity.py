@@ -676,6 +676,49 @@ def test_wordfreq_golden(MR, golden):
     assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(golden["wordfreq.final"]))
 
 
+@pytest.mark.parametrize("kalign", [4, 8])
+def test_convert_by_hashing_variable_length_keys(MR, oracle, kalign):
+    """value-less pairs with variable-length keys (words) are grouped by the hash path (ops_convert_hash.cuh): same KMV --
+    pairs, order, statistics, pages -- as the fingerprint sort that compact=0 takes, and as the oracle after canonical sort"""
+    r = np.random.RandomState(8)
+    vocab = [bytes(r.randint(97, 123, size=r.randint(1, 20)).astype(np.uint8)) + b"\0" for _ in range(5000)]
+    vocab += [b"", b"\0", b"ab", b"ab\0", b"ab\0\0"]                       # keys that differ only in length / trailing NULs
+    idx = r.zipf(1.2, size=150_000) % len(vocab)
+    recs = [(vocab[i], b"") for i in idx]
+    want = H.kmv_decode(oracle.convert(H.kv_encode(recs)))
+    out = {}
+    for compact in (1, 0):
+        mr = MR(compact=compact, keyalign=kalign)
+        mr.kv_add(recs)
+        assert mr.convert() == len(want)
+        st = mr.kmv_stats().asdict()
+        kmv = mr.scan_kmv()
+        assert H.canon_kmv(kmv) == H.canon_kmv(want)
+        out[compact] = (st, kmv, mr.kmv_pages())
+    assert out[1] == out[0]
+    for cb in ("count", "sum", "cull"):
+        mr = MR(keyalign=kalign)
+        mr.kv_add(recs)
+        mr.convert()
+        mr.reduce(cb)
+        assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(oracle.reduce(oracle.convert(H.kv_encode(recs)), cb)))
+
+
+def test_convert_by_hashing_gives_up_on_too_many_distinct_keys(MR):
+    """more distinct keys than the L2-resident table holds: the hash pass raises its flag and the fingerprint sort runs"""
+    n = 2_300_000
+    text = b" ".join(b"%d" % i for i in range(n)) + b" 7 7 7"
+    mr = MR()
+    assert mr.map_tokenize(text) == n + 3
+    assert mr.convert() == n
+    st = mr.kmv_stats()
+    assert st.nvalue == n + 3 and st.keysize == sum(len(b"%d" % i) + 1 for i in range(n))
+    assert mr.reduce("count") == n
+    mr.sort_keys(5)
+    recs = mr.scan_kv()
+    assert len(recs) == n and dict(recs)[b"7\0"] == struct.pack("<i", 4) and dict(recs)[b"8\0"] == struct.pack("<i", 1)
+
+
 def test_tokenize_edge_cases(MR, oracle):
     for text in [b"", b" ", b"a", b" a", b"a ", b"\t\n\f\r", b"one\x00two three", b"\x00abc", b"x" * 5000, b"a b " * 3000 + b"z"]:
         mr = MR()
