@@ -79,12 +79,15 @@ def wordfreq(total_bytes=1 << 30, nfiles=8, nvocab=1 << 17):
     # the pipeline runs twice on the same handle; the second pass (allocator warm, as in a long-running job) is reported
     for rep in range(2):
         T = Timer()
+        mr.prof(rep == 1)
         for f, (text, upto) in enumerate(texts):
             got = T.run("map", lambda: mr.map_tokenize(text, addflag=1 if f else 0))
             assert got == upto
         nuniq = T.run("collate", mr.collate)
         assert nuniq == int((truth > 0).sum().item())
         assert T.run("reduce", lambda: mr.reduce("sum")) == nuniq
+    kern = {k["tag"]: round(k["ms"], 3) for k in mr.prof_report()[0] if k["ms"] > 0.05}
+    mr.prof(False)
     del texts
     # ground truth: the count of vocabulary word i is the number of times index i was drawn
     recs = mr.scan_kv() if nuniq <= 300000 else None
@@ -95,7 +98,7 @@ def wordfreq(total_bytes=1 << 30, nfiles=8, nvocab=1 << 17):
     mr.destroy()
     secs = sum(T.t.values())
     return {"config": "wordfreq: 1 GiB synthetic text, 8 files, map(tokenize)->collate->reduce(sum)", "pairs": nwords_total, "text_bytes": nbytes_total,
-            "unique": nuniq, "secs": T.t, "pairs_per_s": nwords_total / secs, "text_gbs": nbytes_total / 1e9 / T.t["map"],
+            "unique": nuniq, "secs": T.t, "pairs_per_s": nwords_total / secs, "text_gbs": nbytes_total / 1e9 / T.t["map"], "kernels_ms": kern,
             "check": "every (word,count) equals the generator's bincount"}
 
 
@@ -115,6 +118,7 @@ def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
     row_t = torch.from_numpy(row.copy()).to(DEV)
     cdf_t = torch.from_numpy(W.zipf_cdf(nurls, 1.0)).to(DEV)
     mr = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
+    mr.prof(True)
     T = Timer()
     truth = torch.zeros(nurls, dtype=torch.int64, device=DEV)
     truth2 = torch.zeros(nurls * nfiles, dtype=torch.int32, device=DEV)   # postings per (url, file)
@@ -149,6 +153,8 @@ def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
     assert st.nvalue == nlinks and st.valuesize == nlinks * len("part-00000\0")
     # reduce = the reference's postings callback (cpu/InvertedIndex.cpp:335-385) as a device functor: (URL, "f1 f2 ... fn ")
     assert T.run("reduce", lambda: mr.reduce("postings")) == nuniq
+    kern = {k["tag"]: round(k["ms"], 3) for k in mr.prof_report()[0] if k["ms"] > 0.5}
+    mr.prof(False)
     # ---- check: EVERY posting list against the generator.  The result stays on the GPU; its records are parsed there:
     # record = int 30 | int vb | URL (30 bytes) | pad to 40 | n x "part-NNNNN " | NUL.  (url, file) -> how many postings.
     import ctypes
@@ -186,7 +192,7 @@ def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
     mr.destroy()
     secs = T.t["map"] + T.t["aggregate"] + T.t["convert"] + T.t["reduce"]
     return {"config": "InvertedIndex: 16 GiB synthetic HTML in 128 files, map(href FSM)->aggregate->convert->reduce(postings)", "pairs": nlinks,
-            "text_bytes": nbytes, "unique": nuniq, "secs": T.t, "pairs_per_s": nlinks / secs, "text_gbs": nbytes / 1e9 / T.t["map"],
+            "text_bytes": nbytes, "unique": nuniq, "secs": T.t, "pairs_per_s": nlinks / secs, "text_gbs": nbytes / 1e9 / T.t["map"], "kernels_ms": kern,
             "check": "every posting list: the number of postings of every (URL, file) pair equals the generator's count"}
 
 

@@ -397,103 +397,169 @@ static inline int href_step(int st, int c)
   }
 }
 
-__constant__ uint32_t c_href_trans[256];  // packed transition function per byte value
-constexpr uint32_t HREF_IDENT = 0 | (1 << 3) | (2 << 6) | (3 << 9) | (4 << 12) | (5 << 15) | (6 << 18) | (7 << 21);
-constexpr int HREF_CHUNK = 32;  // bytes per thread
+// The DFA as data.  A transition function (state -> state) of the 8 states is kept in two forms:
+//   byte form  HF{lo, hi}: byte st of the 64-bit pair = f(st).  Composition "f then g" is two PRMT instructions: the
+//              selector of a byte permute is four nibbles, each naming one of the eight bytes of (g.lo, g.hi) -- exactly
+//              g[f[st]] when the nibbles are f's values (hf_sel packs four bytes into four nibbles);
+//   nibble form u32: nibble st = f(st), for walking from ONE known state (shift, mask).
+// Per byte value both forms sit in a 256-entry table that every block copies into shared memory (the first version
+// read a __constant__ table with a different index in every lane -- serialised -- and fetched the text one byte
+// per load, lanes 32 bytes apart: 38.6 GB/s of text).
+struct HF {
+  uint32_t lo, hi;
+};
+__device__ uint32_t g_href_nib[256];
+__device__ uint2 g_href_byte[256];
+constexpr uint32_t HF_IDENT_LO = 0x03020100u, HF_IDENT_HI = 0x07060504u;
+constexpr int HREF_CHUNK = 32;  // bytes per thread: two 16-byte loads, a warp reads 1 KiB contiguous
 
 static void href_upload_table()
 {
-  static bool done[64] = {false};
+  static std::atomic<bool> done[64];
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev < 64 && done[dev]) return;
-  uint32_t tab[256];
+  if (dev < 64 && done[dev].load()) return;
+  uint32_t nib[256];
+  uint2 byt[256];
   for (int c = 0; c < 256; c++) {
     uint32_t f = 0;
-    for (int st = 0; st < 8; st++) f |= (uint32_t) href_step(st, c) << (3 * st);
-    tab[c] = f;
+    unsigned long long b = 0;
+    for (int st = 0; st < 8; st++) {
+      f |= (uint32_t) href_step(st, c) << (4 * st);
+      b |= (unsigned long long) href_step(st, c) << (8 * st);
+    }
+    nib[c] = f;
+    byt[c] = make_uint2((uint32_t) b, (uint32_t) (b >> 32));
   }
-  MR_CUDA(cudaMemcpyToSymbol(c_href_trans, tab, sizeof(tab)));
-  if (dev < 64) done[dev] = true;
+  MR_CUDA(cudaMemcpyToSymbol(g_href_nib, nib, sizeof(nib)));
+  MR_CUDA(cudaMemcpyToSymbol(g_href_byte, byt, sizeof(byt)));
+  if (dev < 64) done[dev].store(true);
 }
 
-// h = g after f
-__device__ __forceinline__ uint32_t href_compose(uint32_t f, uint32_t g)
+__device__ __forceinline__ uint32_t hf_sel(uint32_t x)
 {
-  uint32_t h = 0;
+  const uint32_t y = (x | (x >> 4)) & 0x00FF00FFu;
+  return (y | (y >> 8)) & 0xFFFFu;
+}
+// f first, then g
+__device__ __forceinline__ HF hf_then(HF f, HF g) { return HF{__byte_perm(g.lo, g.hi, hf_sel(f.lo)), __byte_perm(g.lo, g.hi, hf_sel(f.hi))}; }
+__device__ __forceinline__ int hf_at(HF f, int st) { return (int) (((st < 4 ? f.lo : f.hi) >> (8 * (st & 3))) & 7u); }
+
+// the 32 bytes of chunk g (zero beyond the text); returns how many of them are text
+__device__ __forceinline__ int href_load32(const uint8_t *__restrict__ t, uint64_t n, uint64_t c0, bool aligned, uint32_t (&w)[8])
+{
 #pragma unroll
-  for (int st = 0; st < 8; st++) h |= ((g >> (3 * ((f >> (3 * st)) & 7))) & 7) << (3 * st);
-  return h;
+  for (int q = 0; q < 8; q++) w[q] = 0;
+  if (c0 >= n) return 0;
+  if (aligned && c0 + HREF_CHUNK <= n) {
+    const uint4 a = *reinterpret_cast<const uint4 *>(t + c0), b = *reinterpret_cast<const uint4 *>(t + c0 + 16);
+    w[0] = a.x, w[1] = a.y, w[2] = a.z, w[3] = a.w, w[4] = b.x, w[5] = b.y, w[6] = b.z, w[7] = b.w;
+    return HREF_CHUNK;
+  }
+  const int m = (int) (n - c0 < (uint64_t) HREF_CHUNK ? n - c0 : (uint64_t) HREF_CHUNK);
+  for (int q = 0; q < m; q++) w[q >> 2] |= (uint32_t) t[c0 + q] << (8 * (q & 3));
+  return m;
 }
 
 __global__ void __launch_bounds__(256)
-href_compose_kernel(const uint8_t *__restrict__ t, uint64_t n, uint32_t *__restrict__ tfun /*exclusive prefix per thread-chunk*/,
-                    uint32_t *__restrict__ bfun /*per block*/)
+href_compose_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, uint2 *__restrict__ tfun /*exclusive prefix per thread-chunk*/,
+                    uint2 *__restrict__ bfun /*per block*/)
 {
-  __shared__ uint32_t sh[256];
-  uint64_t c0 = ((uint64_t) blockIdx.x * 256 + threadIdx.x) * HREF_CHUNK;
-  uint32_t f = HREF_IDENT;
-  for (int q = 0; q < HREF_CHUNK; q++) {
-    uint64_t i = c0 + q;
-    if (i < n) f = href_compose(f, c_href_trans[t[i]]);
-  }
+  __shared__ uint2 s_tab[256];
+  __shared__ uint2 sh[256];
+  s_tab[threadIdx.x] = g_href_byte[threadIdx.x];
+  __syncthreads();
+  const uint64_t c0 = ((uint64_t) blockIdx.x * 256 + threadIdx.x) * HREF_CHUNK;
+  uint32_t w[8];
+  const int m = href_load32(t, n, c0, aligned, w);
+  HF f{HF_IDENT_LO, HF_IDENT_HI};
+#pragma unroll
+  for (int q = 0; q < HREF_CHUNK; q++)
+    if (q < m) {
+      const uint2 g = s_tab[(w[q >> 2] >> (8 * (q & 3))) & 0xFFu];
+      f = hf_then(f, HF{g.x, g.y});
+    }
   // inclusive scan under composition (Hillis-Steele in shared memory; order matters: earlier first)
-  sh[threadIdx.x] = f;
+  sh[threadIdx.x] = make_uint2(f.lo, f.hi);
   __syncthreads();
   for (int o = 1; o < 256; o <<= 1) {
-    uint32_t mine = sh[threadIdx.x], prev = threadIdx.x >= o ? sh[threadIdx.x - o] : HREF_IDENT;
+    const uint2 mine = sh[threadIdx.x], prev = threadIdx.x >= o ? sh[threadIdx.x - o] : make_uint2(HF_IDENT_LO, HF_IDENT_HI);
     __syncthreads();
-    sh[threadIdx.x] = href_compose(prev, mine);
+    const HF c = hf_then(HF{prev.x, prev.y}, HF{mine.x, mine.y});
+    sh[threadIdx.x] = make_uint2(c.lo, c.hi);
     __syncthreads();
   }
-  tfun[(uint64_t) blockIdx.x * 256 + threadIdx.x] = threadIdx.x ? sh[threadIdx.x - 1] : HREF_IDENT;
+  tfun[(uint64_t) blockIdx.x * 256 + threadIdx.x] = threadIdx.x ? sh[threadIdx.x - 1] : make_uint2(HF_IDENT_LO, HF_IDENT_HI);
   if (threadIdx.x == 255) bfun[blockIdx.x] = sh[255];
 }
 
 // thread the state through the blocks: bstate[b] = state at the first byte of block b
-__global__ void href_blockstate_kernel(const uint32_t *__restrict__ bfun, uint64_t nblocks, uint8_t *__restrict__ bstate)
+__global__ void href_blockstate_kernel(const uint2 *__restrict__ bfun, uint64_t nblocks, uint8_t *__restrict__ bstate)
 {
-  __shared__ uint32_t sh[1024];
+  __shared__ uint2 sh[1024];
   int st = HS_START;
   for (uint64_t base = 0; base < nblocks; base += 1024) {
     uint64_t i = base + threadIdx.x;
-    sh[threadIdx.x] = i < nblocks ? bfun[i] : HREF_IDENT;
+    sh[threadIdx.x] = i < nblocks ? bfun[i] : make_uint2(HF_IDENT_LO, HF_IDENT_HI);
     __syncthreads();
     if (threadIdx.x == 0) {
       uint64_t m = nblocks - base < 1024 ? nblocks - base : 1024;
       for (uint64_t q = 0; q < m; q++) {
         bstate[base + q] = (uint8_t) st;
-        st = (sh[q] >> (3 * st)) & 7;
+        st = hf_at(HF{sh[q].x, sh[q].y}, st);
       }
     }
     __syncthreads();
   }
 }
 
-// walk one chunk from state st; calls on_entry(pos of first URL byte) / on_exit(pos of closing quote)
+// walk one chunk (already in registers) from state st; calls on_entry(pos of first URL byte) / on_exit(pos of closing quote)
 template <typename FE, typename FX>
-__device__ __forceinline__ void href_walk(const uint8_t *__restrict__ t, uint64_t n, uint64_t c0, int st, FE on_entry, FX on_exit)
+__device__ __forceinline__ void href_walk(const uint32_t (&w)[8], int m, const uint32_t *__restrict__ s_nib, uint64_t c0, int st, FE on_entry, FX on_exit)
 {
-  for (int q = 0; q < HREF_CHUNK; q++) {
-    uint64_t i = c0 + q;
-    if (i >= n) break;
-    int nx = (c_href_trans[t[i]] >> (3 * st)) & 7;
-    if (st == HS_HREF && nx == HS_LINK) on_entry(i + 1);
-    if (st == HS_LINK && nx == HS_START) on_exit(i);
-    st = nx;
-  }
+#pragma unroll
+  for (int q = 0; q < HREF_CHUNK; q++)
+    if (q < m) {
+      const int nx = (int) ((s_nib[(w[q >> 2] >> (8 * (q & 3))) & 0xFFu] >> (4 * st)) & 7u);
+      if (st == HS_HREF && nx == HS_LINK) on_entry(c0 + q + 1);
+      if (st == HS_LINK && nx == HS_START) on_exit(c0 + q);
+      st = nx;
+    }
 }
 
 __global__ void __launch_bounds__(256)
-href_count_kernel(const uint8_t *__restrict__ t, uint64_t n, const uint32_t *__restrict__ tfun, const uint8_t *__restrict__ bstate,
+href_count_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, const uint2 *__restrict__ tfun, const uint8_t *__restrict__ bstate,
                   uint8_t *__restrict__ tstate, unsigned long long *__restrict__ cnt)
 {
-  uint64_t g = (uint64_t) blockIdx.x * 256 + threadIdx.x;
-  int st = (tfun[g] >> (3 * bstate[blockIdx.x])) & 7;
+  __shared__ uint32_t s_nib[256];
+  s_nib[threadIdx.x] = g_href_nib[threadIdx.x];
+  __syncthreads();
+  const uint64_t g = (uint64_t) blockIdx.x * 256 + threadIdx.x;
+  const uint2 tf = tfun[g];
+  const int st = hf_at(HF{tf.x, tf.y}, bstate[blockIdx.x]);
   tstate[g] = (uint8_t) st;
+  uint32_t w[8];
+  const int m = href_load32(t, n, g * HREF_CHUNK, aligned, w);
   unsigned ne = 0, nx = 0;
-  href_walk(t, n, g * HREF_CHUNK, st, [&](uint64_t) { ne++; }, [&](uint64_t) { nx++; });
+  href_walk(w, m, s_nib, g * HREF_CHUNK, st, [&](uint64_t) { ne++; }, [&](uint64_t) { nx++; });
   cnt[g] = ((unsigned long long) ne << 32) | nx;
+}
+
+// second walk: every entry / exit position goes to its slot (exclusive counts from the scan of cnt[])
+__global__ void __launch_bounds__(256)
+href_sink_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, uint64_t nthr, const uint8_t *__restrict__ tstate,
+                 const unsigned long long *__restrict__ cnt, const unsigned long long *__restrict__ excl, uint32_t *__restrict__ entry,
+                 uint32_t *__restrict__ exitp)
+{
+  __shared__ uint32_t s_nib[256];
+  s_nib[threadIdx.x] = g_href_nib[threadIdx.x];
+  __syncthreads();
+  const uint64_t g = (uint64_t) blockIdx.x * 256 + threadIdx.x;
+  if (g >= nthr || cnt[g] == 0) return;  // nothing starts or ends in most chunks
+  uint32_t w[8];
+  const int m = href_load32(t, n, g * HREF_CHUNK, aligned, w);
+  uint32_t ie = (uint32_t) (excl[g] >> 32), ix = (uint32_t) excl[g];
+  href_walk(w, m, s_nib, g * HREF_CHUNK, tstate[g], [&](uint64_t p) { entry[ie++] = (uint32_t) p; }, [&](uint64_t p) { exitp[ix++] = (uint32_t) p; });
 }
 
 __global__ void __launch_bounds__(256)
@@ -532,15 +598,22 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
   if (nbytes) {
     const uint64_t n = nbytes;
     const uint64_t nblk = (n + 256 * HREF_CHUNK - 1) / (256 * HREF_CHUNK), nthr = nblk * 256;
-    Buf<uint32_t> tfun(pool, nthr), bfun(pool, nblk);
+    Buf<uint2> tfun(pool, nthr), bfun(pool, nblk);
     Buf<uint8_t> bstate(pool, nblk), tstate(pool, nthr);
-    Buf<unsigned long long> cnt(pool, nthr);
-    href_compose_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, tfun.p, bfun.p);
-    MR_CUDA(cudaGetLastError());
-    href_blockstate_kernel<<<1, 1024, 0, s>>>(bfun.p, nblk, bstate.p);
-    MR_CUDA(cudaGetLastError());
-    href_count_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, tfun.p, bstate.p, tstate.p, cnt.p);
-    MR_CUDA(cudaGetLastError());
+    Buf<unsigned long long> cnt(pool, nthr), excl(pool, nthr);
+    const bool aligned = ((uintptr_t) t % 16) == 0;
+    {
+      ProfScope ps(pool, "href_compose", (double) n, 2);
+      href_compose_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, aligned, tfun.p, bfun.p);
+      MR_CUDA(cudaGetLastError());
+      href_blockstate_kernel<<<1, 1024, 0, s>>>(bfun.p, nblk, bstate.p);
+      MR_CUDA(cudaGetLastError());
+    }
+    {
+      ProfScope ps(pool, "href_count", (double) n);
+      href_count_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, aligned, tfun.p, bstate.p, tstate.p, cnt.p);
+      MR_CUDA(cudaGetLastError());
+    }
     const unsigned long long *pc = cnt.p;
     auto val = [=] __device__(uint64_t g) -> unsigned long long { return pc[g]; };
     ScanTiles st;
@@ -550,11 +623,13 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
     if (nurl) {
       Buf<uint32_t> entry(pool, nentry), exitp(pool, nurl);
       uint32_t *pe = entry.p, *px = exitp.p;
-      const uint8_t *pts = tstate.p;
-      scan_sink(pool, st, val, [=] __device__(uint64_t g, unsigned long long e, unsigned long long) {
-        uint32_t ie = (uint32_t) (e >> 32), ix = (uint32_t) e;
-        href_walk(t, n, g * HREF_CHUNK, pts[g], [&](uint64_t p) { pe[ie++] = (uint32_t) p; }, [&](uint64_t p) { px[ix++] = (uint32_t) p; });
-      });
+      unsigned long long *pex = excl.p;
+      scan_sink(pool, st, val, [=] __device__(uint64_t g, unsigned long long e, unsigned long long) { pex[g] = e; });
+      {
+        ProfScope ps(pool, "href_positions", (double) n);
+        href_sink_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, aligned, nthr, tstate.p, cnt.p, excl.p, pe, px);
+        MR_CUDA(cudaGetLastError());
+      }
       VarAppend va = kv_append_var_begin(mr, kv, nurl);
       uint64_t *oo = va.offs;
       uint64_t base = va.base;
@@ -572,8 +647,11 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
       kv_append_var_reserve(mr, kv, va, nurl, total);
       Buf<uint8_t> dname(pool, fnb);
       MR_CUDA(cudaMemcpyAsync(dname.p, fname, fnb, cudaMemcpyHostToDevice, s));
-      href_write_kernel<<<(unsigned) ((nurl + 255) / 256), 256, 0, s>>>(t, pe, px, nurl, dname.p, fnb, kv->data, kv->offs + kv->nkv, al);
-      MR_CUDA(cudaGetLastError());
+      {
+        ProfScope ps(pool, "href_write", (double) total + 8.0 * nurl);
+        href_write_kernel<<<(unsigned) ((nurl + 255) / 256), 256, 0, s>>>(t, pe, px, nurl, dname.p, fnb, kv->data, kv->offs + kv->nkv, al);
+        MR_CUDA(cudaGetLastError());
+      }
       kv->nbytes = va.base + total;
       kv->nkv += nurl;
       kv->ksize += ksize;
