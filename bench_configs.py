@@ -109,7 +109,7 @@ _ROW = (b'<a href="http://h0000.example/p/0000000">link</a><p>lorem ipsum dolor 
         b'<img src="i.png"> plain words here &amp; there, with <b>bold</b> and <i>italic</i> filler\n')
 
 
-def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
+def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22, reps=2):
     """cpu/InvertedIndex.cpp: map(href FSM) -> aggregate -> convert (-> postings).  128 files x 128 MiB of synthetic HTML,
     one <a href> per ~256-byte row, URLs Zipf(1.0) over 2^22."""
     row = np.frombuffer(_ROW, dtype=np.uint8)
@@ -118,34 +118,38 @@ def invindex(total_bytes=16 << 30, nfiles=128, nurls=1 << 22):
     row_t = torch.from_numpy(row.copy()).to(DEV)
     cdf_t = torch.from_numpy(W.zipf_cdf(nurls, 1.0)).to(DEV)
     mr = MapReduce(device=0, stream=torch.cuda.current_stream().cuda_stream)
-    mr.prof(True)
-    T = Timer()
     truth = torch.zeros(nurls, dtype=torch.int64, device=DEV)
     truth2 = torch.zeros(nurls * nfiles, dtype=torch.int32, device=DEV)   # postings per (url, file)
     per_file = total_bytes // nfiles
     rows_per_file = per_file // rowlen
-    nlinks, nbytes, start = 0, 0, 0
-    for f in range(nfiles):
-        idx = torch.arange(start, start + rows_per_file, dtype=torch.int64, device=DEV)
-        start += rows_per_file
-        z = W.splitmix64_torch(idx, W.HTML_SEED)
-        u = W._lsr_t(z, 11).to(torch.float64) * (1.0 / 9007199254740992.0)
-        k = torch.clamp(torch.searchsorted(cdf_t, u, right=True), max=nurls - 1)
-        bc = torch.bincount(k, minlength=nurls)
-        truth += bc
-        truth2.view(nurls, nfiles)[:, f] += bc.to(torch.int32)
-        text = row_t.repeat(rows_per_file, 1)
-        h = k % 10000
-        for j in range(4):
-            text[:, host_pos + 3 - j] = (48 + (h // 10 ** j) % 10).to(torch.uint8)
-        for j in range(7):
-            text[:, path_pos + 6 - j] = (48 + (k // 10 ** j) % 10).to(torch.uint8)
-        text = text.reshape(-1)
-        nlinks += rows_per_file
-        nbytes += text.numel()
-        got = T.run("map", lambda: mr.map_href(text, f"part-{f:05d}", addflag=1 if f else 0))
-        assert got == nlinks, (got, nlinks)
-        del text, idx, z, u, h
+    # the map phase (text generated file by file, then scanned) runs twice on the same handle: the first pass pays
+    # cudaMalloc for every size the store grows through; the second (allocator warm, as in a long-running job) is reported
+    for rep in range(reps):
+      T = Timer()
+      mr.prof(rep == reps - 1)
+      nlinks, nbytes, start = 0, 0, 0
+      for f in range(nfiles):
+            idx = torch.arange(start, start + rows_per_file, dtype=torch.int64, device=DEV)
+            start += rows_per_file
+            z = W.splitmix64_torch(idx, W.HTML_SEED)
+            u = W._lsr_t(z, 11).to(torch.float64) * (1.0 / 9007199254740992.0)
+            k = torch.clamp(torch.searchsorted(cdf_t, u, right=True), max=nurls - 1)
+            if rep == 0:
+                bc = torch.bincount(k, minlength=nurls)
+                truth += bc
+                truth2.view(nurls, nfiles)[:, f] += bc.to(torch.int32)
+            text = row_t.repeat(rows_per_file, 1)
+            h = k % 10000
+            for j in range(4):
+                text[:, host_pos + 3 - j] = (48 + (h // 10 ** j) % 10).to(torch.uint8)
+            for j in range(7):
+                text[:, path_pos + 6 - j] = (48 + (k // 10 ** j) % 10).to(torch.uint8)
+            text = text.reshape(-1)
+            nlinks += rows_per_file
+            nbytes += text.numel()
+            got = T.run("map", lambda: mr.map_href(text, f"part-{f:05d}", addflag=1 if f else 0))
+            assert got == nlinks, (got, nlinks)
+            del text, idx, z, u, h
     T.run("aggregate", mr.aggregate)
     nuniq = T.run("convert", mr.convert)
     assert nuniq == int((truth > 0).sum().item())
@@ -354,6 +358,8 @@ if __name__ == "__main__":
                 assert r["iterations"] == man[fx[0]]["iterations"], (r["iterations"], man[fx[0]]["iterations"])
         elif w.startswith("rmat"):
             r = rmat(int(w[4:]))
+        elif w == "wordfreq_mid":   # short enough to sit under ncu
+            r = wordfreq(total_bytes=1 << 28, nfiles=2, nvocab=1 << 17)
         elif w == "wordfreq_small":
             r = wordfreq(total_bytes=1 << 24, nfiles=2, nvocab=1 << 10)
         elif w == "invindex_small":

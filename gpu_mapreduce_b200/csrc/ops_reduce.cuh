@@ -133,43 +133,59 @@ reduce_generic_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restric
 }
 
 // postings (cpu/InvertedIndex.cpp:335-385 prints, per KMV pair, `key \t v1 v2 ... vn \n`: each value as a C string followed
-// by a space): one warp per KMV pair writes the header and key, then streams the value bytes -- the values of a KMV
-// pair are contiguous -- replacing the last byte of every value (its NUL) by a space; one NUL closes the string.
-// Which bytes are "last bytes" comes from the value sizes: lanes take values round-robin and poke the spaces in after
-// the bulk copy (a value's last byte is at the running sum of the sizes, found with a warp scan per 32 values).
+// by a space).  The values of a KMV pair are contiguous, each a string with its NUL, so the postings text is the
+// multivalue with every NUL turned into a space, closed by one NUL.  Two kernels, neither of which cares how the bytes
+// are spread over the pairs (Zipf: the hottest URL alone has millions of postings, tens of MB):
+//   head: one thread per pair writes lengths, key, the closing NUL and the padding;
+//   body: the multivalues of all pairs, end to end, are one byte space; a thread takes 16 consecutive bytes of it,
+//         finds their pair with a binary search over the running sum of the multivalue sizes and copies them across.
 __global__ void __launch_bounds__(256)
-reduce_postings_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restrict__ offs, uint64_t U, Align al, uint8_t *__restrict__ out,
-                       const uint64_t *__restrict__ ooffs)
+reduce_postings_head_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restrict__ offs, uint64_t U, Align al, uint8_t *__restrict__ out,
+                            const uint64_t *__restrict__ ooffs)
 {
-  const uint64_t u = ((uint64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
+  const uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= U) return;
   KmvHead h = kmv_head(kmv + offs[u], al);
   uint8_t *dst = out + ooffs[u];
   const uint32_t vb = h.mvb + 1, ko = kv_key_off(al), vo = kv_val_off(al, h.kb), end = kv_rec_size(al, h.kb, vb);
-  if (lane == 0) {
-    ((uint32_t *) dst)[0] = h.kb;
-    ((uint32_t *) dst)[1] = vb;
-  }
-  for (uint32_t q = 8 + lane; q < ko; q += 32) dst[q] = 0;
-  for (uint32_t q = lane; q < h.kb; q += 32) dst[ko + q] = h.key[q];
-  for (uint32_t q = ko + h.kb + lane; q < vo; q += 32) dst[q] = 0;
-  for (uint32_t q = lane; q < h.mvb; q += 32) dst[vo + q] = h.values[q];
-  for (uint32_t q = vo + h.mvb + lane; q < end; q += 32) dst[q] = 0;  // the closing NUL and the padding
-  __syncwarp();
-  // spaces: value i ends at (sum of sizes[0..i]) - 1
-  const uint32_t *sizes = (const uint32_t *) h.sizes;
-  uint32_t base = 0;
-  for (uint32_t i0 = 0; i0 < h.nv; i0 += 32) {
-    const uint32_t i = i0 + lane;
-    uint32_t sz = i < h.nv ? sizes[i] : 0, incl = sz;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-      if (lane >= o) incl += t;
+  ((uint32_t *) dst)[0] = h.kb;
+  ((uint32_t *) dst)[1] = vb;
+  for (uint32_t q = 8; q < ko; q++) dst[q] = 0;
+  for (uint32_t q = 0; q < h.kb; q++) dst[ko + q] = h.key[q];
+  for (uint32_t q = ko + h.kb; q < vo; q++) dst[q] = 0;
+  for (uint32_t q = vo + h.mvb; q < end; q++) dst[q] = 0;  // the closing NUL and the padding
+}
+
+__global__ void __launch_bounds__(256)
+reduce_postings_body_kernel(const uint8_t *__restrict__ kmv, const uint64_t *__restrict__ offs, uint64_t U, Align al, uint8_t *__restrict__ out,
+                            const uint64_t *__restrict__ ooffs, const uint64_t *__restrict__ cum /*[U+1] multivalue bytes before pair u*/,
+                            uint64_t total)
+{
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x * 16;
+  for (uint64_t x0 = ((uint64_t) blockIdx.x * blockDim.x + threadIdx.x) * 16; x0 < total; x0 += stride) {
+    uint64_t lo = 0, hi = U - 1;  // last pair whose multivalue starts at or before x0
+    while (lo < hi) {
+      const uint64_t mid = (lo + hi + 1) >> 1;
+      if (__ldg(cum + mid) <= x0) lo = mid;
+      else hi = mid - 1;
     }
-    if (i < h.nv && sz) dst[vo + base + incl - 1] = ' ';
-    base += __shfl_sync(0xFFFFFFFFu, incl, 31);
+    uint64_t u = lo, cnext = __ldg(cum + u + 1);
+    while (cnext <= x0) u++, cnext = __ldg(cum + u + 1);  // pairs without values share a start
+    KmvHead h = kmv_head(kmv + offs[u], al);
+    const uint8_t *src = h.values - __ldg(cum + u);                 // src[x] = byte x of the space
+    uint8_t *dst = out + ooffs[u] + kv_val_off(al, h.kb) - __ldg(cum + u);
+    const uint64_t x1 = x0 + 16 < total ? x0 + 16 : total;
+    for (uint64_t x = x0; x < x1; x++) {
+      while (x >= cnext) {  // the 16 bytes run into the next pair(s)
+        u++;
+        cnext = __ldg(cum + u + 1);
+        h = kmv_head(kmv + offs[u], al);
+        src = h.values - __ldg(cum + u);
+        dst = out + ooffs[u] + kv_val_off(al, h.kb) - __ldg(cum + u);
+      }
+      const uint8_t c = src[x];
+      dst[x] = c ? c : (uint8_t) ' ';
+    }
   }
 }
 
@@ -307,8 +323,19 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
       MR_CUDA(cudaMemcpyAsync(oo + U, &total, 8, cudaMemcpyHostToDevice, s));
       kv->reserve_bytes(total);
       if (functor == MRGPU_REDUCE_POSTINGS) {
-        ProfScope ps(pool, "reduce_postings", (double) kmv->nbytes + (double) total);
-        reduce_postings_kernel<<<(unsigned) ((U * 32 + 255) / 256), 256, 0, s>>>(kd, ko, U, al, kv->data, oo);
+        Buf<uint64_t> cum(pool, U + 1);
+        uint64_t *pcum = cum.p;
+        scan_apply(
+            pool, U, [=] __device__(uint64_t u) -> unsigned long long { return ((const uint32_t *) (kd + ko[u]))[2]; },
+            [=] __device__(uint64_t u, unsigned long long e, unsigned long long) { pcum[u] = e; }, mr->d_small + 2, "reduce_postings_scan", 16.0 * U);
+        MR_CUDA(cudaMemcpyAsync(pcum + U, mr->d_small + 2, 8, cudaMemcpyDeviceToDevice, s));
+        fetch_small(mr, 3);
+        const uint64_t vtotal = mr->h_small[2];
+        ProfScope ps(pool, "reduce_postings", (double) kmv->nbytes + (double) total, 2);
+        reduce_postings_head_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, al, kv->data, oo);
+        if (vtotal) reduce_postings_body_kernel<<<grid_for((vtotal + 15) / 16, 256, 32), 256, 0, s>>>(kd, ko, U, al, kv->data, oo, pcum, vtotal);
+        MR_CUDA(cudaGetLastError());
+        sync(mr);  // cum is released on return
       } else
         reduce_generic_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, functor, al, kv->data, oo, 0);
       MR_CUDA(cudaGetLastError());

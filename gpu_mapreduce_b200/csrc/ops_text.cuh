@@ -457,7 +457,15 @@ __device__ __forceinline__ int href_load32(const uint8_t *__restrict__ t, uint64
     return HREF_CHUNK;
   }
   const int m = (int) (n - c0 < (uint64_t) HREF_CHUNK ? n - c0 : (uint64_t) HREF_CHUNK);
-  for (int q = 0; q < m; q++) w[q >> 2] |= (uint32_t) t[c0 + q] << (8 * (q & 3));
+  // static register indices only (a run-time index would send w[] to local memory)
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    uint32_t x = 0;
+#pragma unroll
+    for (int b = 0; b < 4; b++)
+      if (4 * j + b < m) x |= (uint32_t) t[c0 + 4 * j + b] << (8 * b);
+    w[j] = x;
+  }
   return m;
 }
 

@@ -56,8 +56,9 @@ enum {
   MRGPU_REDUCE_CULL = 2,  /* oink/reduce_cull.cpp:12-20    value = first value                     */
   /* cpu/InvertedIndex.cpp:335-385 (the InvertedIndex reduce writes `key \t v1 v2 ... vn \n` to a file): emits
    * (key, postings) where postings = every value, its terminating NUL turned into a space, in arrival order, closed
-   * by one NUL -- the pair's text form `key \t value \n` is the reference's output line.  Values must be
-   * NUL-terminated strings; a postings string that does not fit a page is MRGPU_ELIMIT. */
+   * by one NUL -- the pair's text form `key \t value \n` is the reference's output line.  Values are
+   * NUL-terminated strings (what the href scanner emits): every NUL byte of the multivalue becomes the space.
+   * A postings string that does not fit a page is MRGPU_ELIMIT. */
   MRGPU_REDUCE_POSTINGS = 3,
   MRGPU_REDUCE_NONZERO = 4, /* examples/rmat.cpp:266-271  (first vertex of the edge key, NULL)             */
   MRGPU_REDUCE_DEGREE = 5,  /* examples/rmat.cpp:279-283  (int nvalues, NULL)                               */
