@@ -362,6 +362,8 @@ if __name__ == "__main__":
             r = wordfreq(total_bytes=1 << 28, nfiles=2, nvocab=1 << 17)
         elif w == "wordfreq_small":
             r = wordfreq(total_bytes=1 << 24, nfiles=2, nvocab=1 << 10)
+        elif w == "invindex_mid":   # short enough to sit under ncu
+            r = invindex(total_bytes=1 << 30, nfiles=8, nurls=1 << 20, reps=1)
         elif w == "invindex_small":
             r = invindex(total_bytes=1 << 24, nfiles=2, nurls=1 << 12)
         else:

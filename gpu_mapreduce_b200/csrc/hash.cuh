@@ -96,23 +96,61 @@ __host__ __device__ __forceinline__ uint32_t hashlittle_words(const uint32_t *w,
   return c;
 }
 
-// Second, independent 32-bit hash used only as the low half of convert()'s 64-bit grouping fingerprint for
-// keys longer than 8 bytes (FNV-1a folded through a murmur finaliser).  It never decides placement or
-// results: groups formed by fingerprint are verified byte-for-byte against the key (see convert).
-__host__ __device__ inline uint32_t fingerprint_lo(const uint8_t *k, uint32_t length, uint32_t seed)
+// 64-bit grouping fingerprint of convert(): (c << 32) | b of ONE lookup3 pass (Jenkins' hashlittle2 returns the same two
+// words as a 64-bit hash); for seed 0 the high half is exactly hashlittle(key, kb, 0), the reference's bucket hash
+// (src/keymultivalue.cpp:1428).  It never decides results: groups formed by fingerprint are verified byte for byte.
+// Two bodies with the same value: keys that start on a 4-byte boundary (every key of a page with keyalign >= 4) are
+// read as whole words and the bytes past the key are masked off -- no branch depends on the key LENGTH beyond the
+// 12-byte rounds, which matters on a GPU: the byte-wise tail takes a different path for every length and a warp of
+// words of 11 different lengths ran it 11 times over (ncu: 1-4 active threads per instruction, 4000 thread
+// instructions per word).  Whole-word reads stay inside the record: the key field is padded to a multiple of 4.
+__device__ __forceinline__ unsigned long long key_fingerprint(const uint8_t *k, uint32_t length, uint32_t seed)
 {
-  uint32_t h = 2166136261u ^ seed;
-  for (uint32_t i = 0; i < length; i++) {
-    h ^= k[i];
-    h *= 16777619u;
+  uint32_t a, b, c;
+  a = b = c = 0xdeadbeefu + length + seed;
+  if ((((uintptr_t) k) & 3) == 0) {
+    const uint32_t *w = (const uint32_t *) k;
+    uint32_t rem = length;
+    while (rem > 12) {
+      a += w[0];
+      b += w[1];
+      c += w[2];
+      MR_MIX(a, b, c);
+      w += 3;
+      rem -= 12;
+    }
+    if (rem) {
+      uint32_t w0 = w[0], w1 = rem > 4 ? w[1] : 0u, w2 = rem > 8 ? w[2] : 0u;
+      const uint32_t tailbytes = rem & 3u;
+      const uint32_t m = tailbytes ? (0xFFFFFFFFu >> (32 - 8 * tailbytes)) : 0xFFFFFFFFu;
+      w0 &= rem <= 4 ? m : 0xFFFFFFFFu;
+      w1 &= (rem > 4 && rem <= 8) ? m : 0xFFFFFFFFu;
+      w2 &= rem > 8 ? m : 0xFFFFFFFFu;
+      a += w0;
+      b += w1;
+      c += w2;
+      MR_FINAL(a, b, c);
+    }
+  } else {
+    while (length > 12) {
+      a += le_bytes(k, 4);
+      b += le_bytes(k + 4, 4);
+      c += le_bytes(k + 8, 4);
+      MR_MIX(a, b, c);
+      length -= 12;
+      k += 12;
+    }
+    if (length) {
+      int la = length < 4 ? (int) length : 4;
+      int lb = length < 4 ? 0 : (length < 8 ? (int) length - 4 : 4);
+      int lc = length < 8 ? 0 : (int) length - 8;
+      a += le_bytes(k, la);
+      if (lb) b += le_bytes(k + 4, lb);
+      if (lc) c += le_bytes(k + 8, lc);
+      MR_FINAL(a, b, c);
+    }
   }
-  h ^= length;
-  h ^= h >> 16;
-  h *= 0x85ebca6bu;
-  h ^= h >> 13;
-  h *= 0xc2b2ae35u;
-  h ^= h >> 16;
-  return h;
+  return ((unsigned long long) c << 32) | b;
 }
 
 }  // namespace mrgpu

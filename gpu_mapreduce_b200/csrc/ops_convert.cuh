@@ -180,7 +180,7 @@ extract_fp_kernel(const uint8_t *__restrict__ data, const uint64_t *__restrict__
     const uint8_t *r = data + rec_off(offs, recsize, i);
     uint32_t kb = *(const uint32_t *) r;
     const uint8_t *k = r + kv_key_off(al);
-    uint64_t fp = ((uint64_t) hashlittle(k, kb, seed) << 32) | fingerprint_lo(k, kb, seed * 0x9E3779B9u + 1);
+    uint64_t fp = key_fingerprint(k, kb, seed);
     keys[i] = fp;
     idx[i] = (uint32_t) i;
     hist_accumulate<uint64_t>(fp, prev, run, sh);

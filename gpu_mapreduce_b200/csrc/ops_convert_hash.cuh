@@ -7,8 +7,8 @@
 // stable sort of ops_convert.cuh: it delivers each key's values in arrival order, which atomics cannot.)
 //
 // One pass over the records:
-//   * fingerprint of the key: 64 bits = hashlittle(key, kb, seed) : a second hash (the high half is the reference's
-//     own bucket hash for seed 0);
+//   * fingerprint of the key: the two result words of one lookup3 pass (key_fingerprint, hash.cuh; the high half is the
+//     reference's own bucket hash);
 //   * block-local open-addressing table in shared memory (linear probing, claimed with a 64-bit CAS): the keys that
 //     come up again and again -- a text corpus is Zipf distributed -- are counted there and never reach L2;
 //   * what does not fit goes to an open-addressing table in global memory small enough to stay in L2 (CAS to claim,
@@ -94,7 +94,7 @@ hash_group_kernel(HgRecs r, uint64_t n, uint32_t seed, HgEntry *__restrict__ g, 
   for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     uint32_t kb;
     const uint8_t *k = hg_key(r, i, kb);
-    unsigned long long fp = ((unsigned long long) hashlittle(k, kb, seed) << 32) | fingerprint_lo(k, kb, seed * 0x9E3779B9u + 1);
+    unsigned long long fp = key_fingerprint(k, kb, seed);
     if (fp == 0) fp = 1;
     uint32_t slot = (uint32_t) (fp ^ (fp >> 37)) & (HG_SLOTS - 1);
     bool done = false;
