@@ -91,26 +91,33 @@ hash_group_kernel(HgRecs r, uint64_t n, uint32_t seed, HgEntry *__restrict__ g, 
   for (uint32_t i = threadIdx.x; i < HG_SLOTS; i += blockDim.x) s_fp[i] = 0, s_cnt[i] = 0, s_rep[i] = HG_UNSET;
   __syncthreads();
   const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
-  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    uint32_t kb;
-    const uint8_t *k = hg_key(r, i, kb);
-    unsigned long long fp = key_fingerprint(k, kb, seed);
-    if (fp == 0) fp = 1;
-    uint32_t slot = (uint32_t) (fp ^ (fp >> 37)) & (HG_SLOTS - 1);
-    bool done = false;
+  // every lane of a warp makes the same number of trips and the warp is brought back together at the top of each:
+  // the probe / verify branches below split it, and without the barrier the pieces kept running apart -- each
+  // hashing its next word alone (ncu: 1 to 4 active threads per instruction in the hash code)
+  for (uint64_t base = (uint64_t) blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n; base += stride) {
+    __syncwarp();
+    const uint64_t i = base + (threadIdx.x & 31u);
+    if (i < n) {
+      uint32_t kb;
+      const uint8_t *k = hg_key(r, i, kb);
+      unsigned long long fp = key_fingerprint(k, kb, seed);
+      if (fp == 0) fp = 1;
+      uint32_t slot = (uint32_t) (fp ^ (fp >> 37)) & (HG_SLOTS - 1);
+      bool done = false;
 #pragma unroll 1
-    for (uint32_t p = 0; p < HG_PROBES && !done; p++) {
-      unsigned long long cur = s_fp[slot];
-      if (cur == 0) cur = atomicCAS(&s_fp[slot], 0ull, fp);
-      if (cur == 0 || cur == fp) {
-        atomicAdd(&s_cnt[slot], 1u);
-        const unsigned old = atomicMin(&s_rep[slot], (unsigned) i);
-        if (old != HG_UNSET && old != (unsigned) i && !hg_same_key(r, (uint32_t) i, old)) atomicOr(flags, 2ull);
-        done = true;
-      } else
-        slot = (slot + 1) & (HG_SLOTS - 1);
+      for (uint32_t p = 0; p < HG_PROBES && !done; p++) {
+        unsigned long long cur = s_fp[slot];
+        if (cur == 0) cur = atomicCAS(&s_fp[slot], 0ull, fp);
+        if (cur == 0 || cur == fp) {
+          atomicAdd(&s_cnt[slot], 1u);
+          const unsigned old = atomicMin(&s_rep[slot], (unsigned) i);
+          if (old != HG_UNSET && old != (unsigned) i && !hg_same_key(r, (uint32_t) i, old)) atomicOr(flags, 2ull);
+          done = true;
+        } else
+          slot = (slot + 1) & (HG_SLOTS - 1);
+      }
+      if (!done) hg_global_add(g, gmask, fp, 1u, (unsigned) i, r, flags);  // the block's table is taken by more frequent keys
     }
-    if (!done) hg_global_add(g, gmask, fp, 1u, (unsigned) i, r, flags);  // the block's table is taken by more frequent keys
   }
   __syncthreads();
   for (uint32_t s = threadIdx.x; s < HG_SLOTS; s += blockDim.x)

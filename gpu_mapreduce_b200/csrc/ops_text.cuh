@@ -402,14 +402,13 @@ static inline int href_step(int st, int c)
 //              selector of a byte permute is four nibbles, each naming one of the eight bytes of (g.lo, g.hi) -- exactly
 //              g[f[st]] when the nibbles are f's values (hf_sel packs four bytes into four nibbles);
 //   nibble form u32: nibble st = f(st), for walking from ONE known state (shift, mask).
-// Per byte value both forms sit in a 256-entry table that every block copies into shared memory (the first version
-// read a __constant__ table with a different index in every lane -- serialised -- and fetched the text one byte
-// per load, lanes 32 bytes apart: 38.6 GB/s of text).
+// Per byte value the nibble form sits in a 256-entry table that every block copies into shared memory (the first
+// version read a __constant__ table with a different index in every lane -- serialised -- and fetched the text one
+// byte per load, lanes 32 bytes apart: 38.6 GB/s of text).
 struct HF {
   uint32_t lo, hi;
 };
 __device__ uint32_t g_href_nib[256];
-__device__ uint2 g_href_byte[256];
 constexpr uint32_t HF_IDENT_LO = 0x03020100u, HF_IDENT_HI = 0x07060504u;
 constexpr int HREF_CHUNK = 32;  // bytes per thread: two 16-byte loads, a warp reads 1 KiB contiguous
 
@@ -420,19 +419,12 @@ static void href_upload_table()
   cudaGetDevice(&dev);
   if (dev < 64 && done[dev].load()) return;
   uint32_t nib[256];
-  uint2 byt[256];
   for (int c = 0; c < 256; c++) {
     uint32_t f = 0;
-    unsigned long long b = 0;
-    for (int st = 0; st < 8; st++) {
-      f |= (uint32_t) href_step(st, c) << (4 * st);
-      b |= (unsigned long long) href_step(st, c) << (8 * st);
-    }
+    for (int st = 0; st < 8; st++) f |= (uint32_t) href_step(st, c) << (4 * st);
     nib[c] = f;
-    byt[c] = make_uint2((uint32_t) b, (uint32_t) (b >> 32));
   }
   MR_CUDA(cudaMemcpyToSymbol(g_href_nib, nib, sizeof(nib)));
-  MR_CUDA(cudaMemcpyToSymbol(g_href_byte, byt, sizeof(byt)));
   if (dev < 64) done[dev].store(true);
 }
 
@@ -469,23 +461,27 @@ __device__ __forceinline__ int href_load32(const uint8_t *__restrict__ t, uint64
   return m;
 }
 
+// Function of one 32-byte chunk.  Folding from the RIGHT keeps the accumulated function in byte form and takes the
+// table in selector (nibble) form: Q_k = Q_(k+1) after T_k, i.e. byte st of the result = Q_(k+1)[T_k[st]] = two PRMTs of
+// the accumulator with T_k's nibbles as selectors -- no conversion between the forms (the left fold needed one per
+// byte: 26 instructions per byte, ALU-bound at 0.9 TB/s of text in ncu).
 __global__ void __launch_bounds__(256)
 href_compose_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, uint2 *__restrict__ tfun /*exclusive prefix per thread-chunk*/,
                     uint2 *__restrict__ bfun /*per block*/)
 {
-  __shared__ uint2 s_tab[256];
+  __shared__ uint32_t s_nib[256];
   __shared__ uint2 sh[256];
-  s_tab[threadIdx.x] = g_href_byte[threadIdx.x];
+  s_nib[threadIdx.x] = g_href_nib[threadIdx.x];
   __syncthreads();
   const uint64_t c0 = ((uint64_t) blockIdx.x * 256 + threadIdx.x) * HREF_CHUNK;
   uint32_t w[8];
   const int m = href_load32(t, n, c0, aligned, w);
   HF f{HF_IDENT_LO, HF_IDENT_HI};
 #pragma unroll
-  for (int q = 0; q < HREF_CHUNK; q++)
+  for (int q = HREF_CHUNK - 1; q >= 0; q--)
     if (q < m) {
-      const uint2 g = s_tab[(w[q >> 2] >> (8 * (q & 3))) & 0xFFu];
-      f = hf_then(f, HF{g.x, g.y});
+      const uint32_t sel = s_nib[(w[q >> 2] >> (8 * (q & 3))) & 0xFFu];
+      f = HF{__byte_perm(f.lo, f.hi, sel), __byte_perm(f.lo, f.hi, sel >> 16)};
     }
   // inclusive scan under composition (Hillis-Steele in shared memory; order matters: earlier first)
   sh[threadIdx.x] = make_uint2(f.lo, f.hi);
@@ -501,22 +497,44 @@ href_compose_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, uin
   if (threadIdx.x == 255) bfun[blockIdx.x] = sh[255];
 }
 
-// thread the state through the blocks: bstate[b] = state at the first byte of block b
-__global__ void href_blockstate_kernel(const uint2 *__restrict__ bfun, uint64_t nblocks, uint8_t *__restrict__ bstate)
+// thread the state through the blocks: bstate[b] = state at the first byte of block b.  One block; a thread composes
+// 16 consecutive block functions, the 1024 partial results are scanned, every thread then walks its 16 blocks from
+// the state it starts in (the first version walked all blocks with one thread: 0.25 ms per 128 MiB of text, more
+// than the rest of the scanner together).
+constexpr int HREF_BS_PER = 16;
+__global__ void __launch_bounds__(1024) href_blockstate_kernel(const uint2 *__restrict__ bfun, uint64_t nblocks, uint8_t *__restrict__ bstate)
 {
   __shared__ uint2 sh[1024];
-  int st = HS_START;
-  for (uint64_t base = 0; base < nblocks; base += 1024) {
-    uint64_t i = base + threadIdx.x;
-    sh[threadIdx.x] = i < nblocks ? bfun[i] : make_uint2(HF_IDENT_LO, HF_IDENT_HI);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      uint64_t m = nblocks - base < 1024 ? nblocks - base : 1024;
-      for (uint64_t q = 0; q < m; q++) {
-        bstate[base + q] = (uint8_t) st;
-        st = hf_at(HF{sh[q].x, sh[q].y}, st);
+  __shared__ int s_state;
+  if (threadIdx.x == 0) s_state = HS_START;
+  __syncthreads();
+  for (uint64_t base = 0; base < nblocks; base += 1024 * HREF_BS_PER) {
+    const uint64_t i0 = base + (uint64_t) threadIdx.x * HREF_BS_PER;
+    HF f{HF_IDENT_LO, HF_IDENT_HI};
+    for (int j = 0; j < HREF_BS_PER; j++)
+      if (i0 + j < nblocks) {
+        const uint2 g = bfun[i0 + j];
+        f = hf_then(f, HF{g.x, g.y});
       }
+    sh[threadIdx.x] = make_uint2(f.lo, f.hi);
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+      const uint2 mine = sh[threadIdx.x], prev = threadIdx.x >= o ? sh[threadIdx.x - o] : make_uint2(HF_IDENT_LO, HF_IDENT_HI);
+      __syncthreads();
+      const HF c = hf_then(HF{prev.x, prev.y}, HF{mine.x, mine.y});
+      sh[threadIdx.x] = make_uint2(c.lo, c.hi);
+      __syncthreads();
     }
+    const int st0 = s_state;
+    int st = threadIdx.x ? hf_at(HF{sh[threadIdx.x - 1].x, sh[threadIdx.x - 1].y}, st0) : st0;
+    for (int j = 0; j < HREF_BS_PER; j++)
+      if (i0 + j < nblocks) {
+        bstate[i0 + j] = (uint8_t) st;
+        const uint2 g = bfun[i0 + j];
+        st = hf_at(HF{g.x, g.y}, st);
+      }
+    __syncthreads();
+    if (threadIdx.x == 1023) s_state = hf_at(HF{sh[1023].x, sh[1023].y}, st0);
     __syncthreads();
   }
 }
