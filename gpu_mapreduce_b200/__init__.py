@@ -97,6 +97,7 @@ def lib():
         "mrgpu_clone": [vp, u64p],
         "mrgpu_collapse": [vp, C.c_char_p, C.c_int, u64p],
         "mrgpu_scrunch": [vp, C.c_int, C.c_char_p, C.c_int, u64p],
+        "mrgpu_global_count": [vp, C.c_int, u64p],
         "mrgpu_kv_stats": [vp, C.POINTER(Stats)],
         "mrgpu_kmv_stats": [vp, C.POINTER(Stats)],
         "mrgpu_kv_page_info": [vp, C.c_uint64, u64p, u64p, u64p, u64p],

@@ -5,6 +5,8 @@
 #ifndef KEY_VALUE_H
 #define KEY_VALUE_H
 
+#include "mpi.h"     // the reference's keyvalue.h brings these three in (src/keyvalue.h:17-19); callers rely on it
+#include <stdio.h>
 #include <stdint.h>
 #include <vector>
 
@@ -29,6 +31,11 @@ class KeyValue {
   void add(char *key, int keybytes, char *value, int valuebytes);               // src/keyvalue.cpp:343
   void add(int n, char *key, int keybytes, char *value, int valuebytes);        // src/keyvalue.cpp:399
   void add(int n, char *key, int *keybytes, char *value, int *valuebytes);      // src/keyvalue.cpp:419
+
+  // Callers that feed one MapReduce's KeyValue from a callback running on ANOTHER one bracket the adds themselves
+  // (oink/sssp.cpp:112-137: mrvert->kv->append(); mrpath->map(mrpath, move_to_new_mr, mrvert); mrvert->kv->complete();)
+  void append();    // src/keyvalue.cpp:185-209: re-open for more pairs
+  void complete();  // src/keyvalue.cpp:216-255: finish; the statistics fields above are current afterwards
 
  private:
   explicit KeyValue(mrgpu_mr *h);

@@ -20,6 +20,7 @@
 
 #include "../../include/mrgpu.h"
 #include "keyvalue.h"
+#include "keymultivalue.h"
 #include "mrgpu_functors.h"
 
 #ifndef MRMPI_MEMSIZE
@@ -28,8 +29,7 @@
 
 namespace MAPREDUCE_NS {
 
-class KeyMultiValue {};  // opaque: callers only test MapReduce::kmv for NULL
-static KeyMultiValue g_kmv_marker;
+static KeyMultiValue g_kmv_marker;  // opaque: callers only test MapReduce::kmv for NULL
 
 MapReduce *MapReduce::mrptr = NULL;
 int MapReduce::instances_now = 0;
@@ -62,8 +62,33 @@ void href(int, char *, KeyValue *, void *) {}
 typedef void (*ReduceFn)(char *, int, char *, int, int *, KeyValue *, void *);
 typedef void (*MapMrFn)(uint64_t, char *, int, char *, int, KeyValue *, void *);
 
+// callbacks of the application tied to device functors by address (MapReduce::device_reduce / _map_mr / _map_task)
+typedef void (*MapTaskFn)(int, KeyValue *, void *);
+// (function-local statics: registration happens from static initialisers of other translation units)
+static std::vector<std::pair<ReduceFn, int> > &reg_reduce()
+{
+  static std::vector<std::pair<ReduceFn, int> > v;
+  return v;
+}
+static std::vector<std::pair<MapMrFn, int> > &reg_mapmr()
+{
+  static std::vector<std::pair<MapMrFn, int> > v;
+  return v;
+}
+static std::vector<std::pair<MapTaskFn, MapReduce::DeviceMapTask> > &reg_maptask()
+{
+  static std::vector<std::pair<MapTaskFn, MapReduce::DeviceMapTask> > v;
+  return v;
+}
+
+void MapReduce::device_reduce(ReduceFn host, int functor) { reg_reduce().push_back(std::make_pair(host, functor)); }
+void MapReduce::device_map_mr(MapMrFn host, int functor) { reg_mapmr().push_back(std::make_pair(host, functor)); }
+void MapReduce::device_map_task(MapTaskFn host, DeviceMapTask dev) { reg_maptask().push_back(std::make_pair(host, dev)); }
+
 static int stock_reduce(ReduceFn f)
 {
+  for (size_t i = 0; i < reg_reduce().size(); i++)
+    if (reg_reduce()[i].first == f) return reg_reduce()[i].second;
   if (f == gpu::count) return MRGPU_REDUCE_COUNT;
   if (f == gpu::sum) return MRGPU_REDUCE_SUM;
   if (f == gpu::cull) return MRGPU_REDUCE_CULL;
@@ -75,6 +100,8 @@ static int stock_reduce(ReduceFn f)
 }
 static int stock_mapmr(MapMrFn f)
 {
+  for (size_t i = 0; i < reg_mapmr().size(); i++)
+    if (reg_mapmr()[i].first == f) return reg_mapmr()[i].second;
   if (f == gpu::edge_to_vertices) return MRGPU_MAP_EDGE_TO_VERTICES;
   if (f == gpu::edge_to_vertex) return MRGPU_MAP_EDGE_TO_VERTEX;
   if (f == gpu::invert) return MRGPU_MAP_INVERT;
@@ -100,6 +127,31 @@ void KeyValue::flush()
   vbuf.clear();
   klen.clear();
   vlen.clear();
+}
+
+static void kv_fatal(mrgpu_mr *h)
+{
+  printf("ERROR: %s\n", mrgpu_last_error(h));
+  fflush(stdout);
+  exit(1);
+}
+
+void KeyValue::append()
+{
+  if (mrgpu_kv_open(handle, 1) != MRGPU_OK) kv_fatal(handle);
+}
+
+void KeyValue::complete()
+{
+  flush();
+  if (mrgpu_kv_close(handle, NULL) != MRGPU_OK) kv_fatal(handle);
+  mrgpu_stats s;
+  if (mrgpu_kv_stats(handle, &s) != MRGPU_OK) kv_fatal(handle);
+  nkv = s.npair;
+  ksize = s.keysize;
+  vsize = s.valuesize;
+  esize = s.exactsize;
+  npage = (int) s.npage;
 }
 
 void KeyValue::add(char *key, int keybytes, char *value, int valuebytes)
@@ -371,12 +423,13 @@ uint64_t MapReduce::kv_stats(int level)
   if (kv == NULL) all("Cannot print stats without KeyValue");
   mrgpu_stats s;
   ck(mrgpu_kv_stats(gpu, &s), 0);
+  uint64_t nall = s.npair;  // the reference returns (and prints) the pair count summed over all ranks (src/mapreduce.cpp:2945-2958)
+  ck(mrgpu_global_count(gpu, 0, &nall), 0);
   const double mbyte = 1024.0 * 1024.0;
-  // single rank or counts already global through the op return values; sizes are this rank's
   if (level >= 1 && me == 0)
-    printf("%lu pairs, %.3g Mb keys, %.3g Mb values, %.3g Mb, %d pages\n", (unsigned long) s.npair, s.keysize / mbyte, s.valuesize / mbyte,
+    printf("%lu pairs, %.3g Mb keys, %.3g Mb values, %.3g Mb, %d pages\n", (unsigned long) nall, s.keysize / mbyte, s.valuesize / mbyte,
            s.exactsize / mbyte, (int) s.npage);
-  return s.npair;
+  return nall;
 }
 
 uint64_t MapReduce::kmv_stats(int level)
@@ -384,11 +437,13 @@ uint64_t MapReduce::kmv_stats(int level)
   if (kmv == NULL) all("Cannot print stats without KeyMultiValue");
   mrgpu_stats s;
   ck(mrgpu_kmv_stats(gpu, &s), 0);
+  uint64_t nall = s.npair;
+  ck(mrgpu_global_count(gpu, 1, &nall), 0);
   const double mbyte = 1024.0 * 1024.0;
   if (level >= 1 && me == 0)
-    printf("%lu pairs, %.3g Mb keys, %.3g Mb values, %.3g Mb, %d pages\n", (unsigned long) s.npair, s.keysize / mbyte, s.valuesize / mbyte,
+    printf("%lu pairs, %.3g Mb keys, %.3g Mb values, %.3g Mb, %d pages\n", (unsigned long) nall, s.keysize / mbyte, s.valuesize / mbyte,
            s.exactsize / mbyte, (int) s.npage);
-  return s.npair;
+  return nall;
 }
 
 void MapReduce::cummulative_stats(int, int) {}
@@ -569,6 +624,8 @@ static bool slurp(const char *fname, std::vector<char> &buf)
 uint64_t MapReduce::map(int nmap, void (*appmap)(int, KeyValue *, void *), void *ptr, int addflag)
 {
   push_settings();
+  for (size_t i = 0; i < reg_maptask().size(); i++)
+    if (reg_maptask()[i].first == appmap) return reg_maptask()[i].second(this, nmap, ptr, addflag);
   start_timer();
   if (appmap == gpu::intcount || appmap == gpu::rmat_generate) {
     // stock callback = device functor: one library call per task of this rank, no pair touches the host.  The calls

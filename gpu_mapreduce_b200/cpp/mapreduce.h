@@ -117,6 +117,18 @@ class MapReduce {
   // extension: the C-ABI handle, for callers that mix in mrgpu_* calls (device functors of their own)
   mrgpu_mr *gpu_handle() { return gpu; }
 
+  // extension: an application's OWN callback can be tied to a device functor by address, without touching the call
+  // sites: whenever map() / reduce() / compress() is then called with that function pointer, the device functor runs
+  // instead of the host function (cpp/oink_gpu_register.cpp ties OINK's rmat_generate, cull, count, edge_to_vertices
+  // ... this way, so the unmodified OINK commands run their hot loops on the GPU).
+  //   device_reduce / device_map_mr: the MRGPU_REDUCE_* / MRGPU_MAP_* functor that has the same effect
+  //   device_map_task: a function that performs the whole map() call (it typically converts `ptr` and calls
+  //                    map(nmap, gpu::<stock functor>, ...)) and returns the global pair count
+  typedef uint64_t (*DeviceMapTask)(MapReduce *mr, int nmap, void *ptr, int addflag);
+  static void device_reduce(void (*host)(char *, int, char *, int, int *, class KeyValue *, void *), int functor);
+  static void device_map_mr(void (*host)(uint64_t, char *, int, char *, int, class KeyValue *, void *), int functor);
+  static void device_map_task(void (*host)(int, class KeyValue *, void *), DeviceMapTask dev);
+
  private:
   MPI_Comm comm;
   int me, nprocs;

@@ -47,6 +47,58 @@ static inline int MPI_Comm_size(MPI_Comm, int *n)
   return 0;
 }
 static inline int MPI_Barrier(MPI_Comm) { return 0; }
+
+// Host-side collectives, as far as OINK's front-end uses them (oink/*.cpp: MPI_Bcast of input lines, MPI_Allreduce of
+// counters, MPI_Comm_split for "universe" partitions).  With one process they are copies, as in mpistubs/mpi.cpp.
+// With several processes this header cannot move host data between them -- only the library moves data (NCCL) -- so
+// they stop the program instead of returning a wrong answer: a multi-rank OINK needs a real MPI.
+typedef int MPI_Datatype;
+typedef int MPI_Op;
+#define MPI_INT 1
+#define MPI_CHAR 2
+#define MPI_BYTE 3
+#define MPI_UNSIGNED_LONG 4
+#define MPI_DOUBLE 5
+#define MPI_FLOAT 6
+#define MPI_LONG 7
+#define MPI_UNSIGNED_LONG_LONG 8
+#define MPI_SUM 1
+#define MPI_MIN 2
+#define MPI_MAX 3
+static inline size_t mrgpu_stub_type_size(MPI_Datatype t)
+{
+  switch (t) {
+    case MPI_INT: case MPI_FLOAT: return 4;
+    case MPI_CHAR: case MPI_BYTE: return 1;
+    default: return 8;
+  }
+}
+static inline void mrgpu_stub_single_process_only(const char *what)
+{
+  if (mrgpu_stub_env("WORLD_SIZE", "OMPI_COMM_WORLD_SIZE", "PMI_SIZE", 1) > 1) {
+    printf("ERROR: %s among %s needs a real MPI (cpp/mpi.h is a stand-in that moves no host data)\n", what, "several processes");
+    fflush(stdout);
+    exit(1);
+  }
+}
+static inline int MPI_Allreduce(void *in, void *out, int n, MPI_Datatype t, MPI_Op, MPI_Comm)
+{
+  mrgpu_stub_single_process_only("MPI_Allreduce");
+  if (in != out) memcpy(out, in, (size_t) n * mrgpu_stub_type_size(t));
+  return 0;
+}
+static inline int MPI_Bcast(void *, int, MPI_Datatype, int, MPI_Comm)
+{
+  mrgpu_stub_single_process_only("MPI_Bcast");
+  return 0;
+}
+static inline int MPI_Comm_split(MPI_Comm comm, int, int, MPI_Comm *out)
+{
+  mrgpu_stub_single_process_only("MPI_Comm_split");
+  *out = comm;
+  return 0;
+}
+static inline int MPI_Comm_free(MPI_Comm *) { return 0; }
 static inline int MPI_Abort(MPI_Comm, int code)
 {
   exit(code);

@@ -146,6 +146,22 @@ extern "C" int mrgpu_kmv_stats(mrgpu_mr *mr, mrgpu_stats *out)
   API_END(mr)
 }
 
+// the pair count summed over the ranks, as MapReduce::kv_stats / kmv_stats return it (src/mapreduce.cpp:2945, 2988).
+// COLLECTIVE (one all-reduce unless the last operation already produced the number).
+extern "C" int mrgpu_global_count(mrgpu_mr *mr, int which, uint64_t *n)
+{
+  API_BEGIN(mr)
+  if (!n) MR_FAIL(MRGPU_EINVAL, "null out");
+  if (which == 0) {
+    if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot print stats without KeyValue");
+    *n = global_count(mr, mr->kv->nkv, G_KV, true);
+  } else {
+    if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "Cannot print stats without KeyMultiValue");
+    *n = global_count(mr, mr->kmv->nkmv, G_KMV, true);
+  }
+  API_END(mr)
+}
+
 extern "C" int mrgpu_kv_page_info(mrgpu_mr *mr, uint64_t ipage, uint64_t *nkey, uint64_t *keysize, uint64_t *valuesize, uint64_t *alignsize)
 {
   API_BEGIN(mr)

@@ -235,6 +235,10 @@ typedef struct {
 int mrgpu_kv_stats(mrgpu_mr *mr, mrgpu_stats *out);
 int mrgpu_kmv_stats(mrgpu_mr *mr, mrgpu_stats *out);
 
+/* The return value of MapReduce::kv_stats / kmv_stats (src/mapreduce.cpp:2945-2958, 2988-3001): the pair count of the
+ * KeyValue (which = 0) or KeyMultiValue (which = 1) summed over all ranks.  COLLECTIVE, unlike the two calls above. */
+int mrgpu_global_count(mrgpu_mr *mr, int which, uint64_t *n);
+
 /* KeyValue::request_info / request_page src/keyvalue.cpp:277-308: page ipage of the KV in the reference's
  * byte layout (int keybytes | int valuebytes | pad | key | pad | value | pad).  mrgpu_kv_page_info gives
  * nkey and sizes; mrgpu_kv_page_copy writes alignsize bytes to host memory `dst` (padding zeroed). */
