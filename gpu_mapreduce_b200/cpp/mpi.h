@@ -20,13 +20,13 @@ typedef int MPI_Comm;
 #define MPI_MAX_PROCESSOR_NAME 128
 #define MRGPU_MPI_STUB 1
 
-static inline int MPI_Init(int *, char ***) { return 0; }
+static inline int MPI_Init(int *argc, char ***argv) { return 0; }
 static inline int MPI_Initialized(int *flag)
 {
   *flag = 1;
   return 0;
 }
-static inline int MPI_Finalize() { return 0; }
+static inline int MPI_Finalize(void) { return 0; }
 static inline int mrgpu_stub_env(const char *a, const char *b, const char *c, int dflt)
 {
   const char *names[3] = {a, b, c};
@@ -36,17 +36,17 @@ static inline int mrgpu_stub_env(const char *a, const char *b, const char *c, in
   }
   return dflt;
 }
-static inline int MPI_Comm_rank(MPI_Comm, int *me)
+static inline int MPI_Comm_rank(MPI_Comm comm, int *me)
 {
   *me = mrgpu_stub_env("RANK", "OMPI_COMM_WORLD_RANK", "PMI_RANK", 0);
   return 0;
 }
-static inline int MPI_Comm_size(MPI_Comm, int *n)
+static inline int MPI_Comm_size(MPI_Comm comm, int *n)
 {
   *n = mrgpu_stub_env("WORLD_SIZE", "OMPI_COMM_WORLD_SIZE", "PMI_SIZE", 1);
   return 0;
 }
-static inline int MPI_Barrier(MPI_Comm) { return 0; }
+static inline int MPI_Barrier(MPI_Comm comm) { return 0; }
 
 // Host-side collectives, as far as OINK's front-end uses them (oink/*.cpp: MPI_Bcast of input lines, MPI_Allreduce of
 // counters, MPI_Comm_split for "universe" partitions).  With one process they are copies, as in mpistubs/mpi.cpp.
@@ -81,30 +81,30 @@ static inline void mrgpu_stub_single_process_only(const char *what)
     exit(1);
   }
 }
-static inline int MPI_Allreduce(void *in, void *out, int n, MPI_Datatype t, MPI_Op, MPI_Comm)
+static inline int MPI_Allreduce(void *in, void *out, int n, MPI_Datatype t, MPI_Op op, MPI_Comm comm)
 {
   mrgpu_stub_single_process_only("MPI_Allreduce");
   if (in != out) memcpy(out, in, (size_t) n * mrgpu_stub_type_size(t));
   return 0;
 }
-static inline int MPI_Bcast(void *, int, MPI_Datatype, int, MPI_Comm)
+static inline int MPI_Bcast(void *buf, int n, MPI_Datatype t, int root, MPI_Comm comm)
 {
   mrgpu_stub_single_process_only("MPI_Bcast");
   return 0;
 }
-static inline int MPI_Comm_split(MPI_Comm comm, int, int, MPI_Comm *out)
+static inline int MPI_Comm_split(MPI_Comm comm, int color, int key, MPI_Comm *out)
 {
   mrgpu_stub_single_process_only("MPI_Comm_split");
   *out = comm;
   return 0;
 }
-static inline int MPI_Comm_free(MPI_Comm *) { return 0; }
-static inline int MPI_Abort(MPI_Comm, int code)
+static inline int MPI_Comm_free(MPI_Comm *comm) { return 0; }
+static inline int MPI_Abort(MPI_Comm comm, int code)
 {
   exit(code);
   return 0;
 }
-static inline double MPI_Wtime()
+static inline double MPI_Wtime(void)
 {
   struct timeval tv;
   gettimeofday(&tv, NULL);

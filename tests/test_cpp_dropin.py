@@ -55,10 +55,13 @@ def test_same_caller_same_output_on_both_libraries():
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(not os.path.exists(os.path.join(BIN, "wordfreq_gpu")), reason="wordfreq binaries not built")
-def test_reference_wordfreq_example_unmodified():
-    """examples/wordfreq.cpp: map(files, fileread) -> collate -> reduce(sum) -> sort_values -> map(mr) -> gather ->
-    sort_values -> top 10, all through host callbacks on both libraries."""
+@pytest.mark.parametrize("prog", ["wordfreq", "cwordfreq"])
+def test_reference_wordfreq_example_unmodified(prog):
+    """examples/wordfreq.cpp (class API) and examples/cwordfreq.c (the MR_* C interface, cpp/cmapreduce.h):
+    map(files, fileread) -> collate -> reduce(sum) -> sort_values -> map(mr) -> gather -> sort_values -> top 10, all through
+    host callbacks, on both libraries."""
+    if not (os.path.exists(os.path.join(BIN, prog + "_gpu")) and os.path.exists(os.path.join(REF, prog + "_ref"))):
+        pytest.skip(f"{prog} binaries not built")
     with tempfile.TemporaryDirectory() as td:
         names = []
         for i in range(3):
@@ -66,8 +69,8 @@ def test_reference_wordfreq_example_unmodified():
             with open(p, "wb") as f:
                 f.write(W.words_text(30000, nvocab=400, exponent=1.3, start=i * 30000))
             names.append(p)
-        ref = _run(os.path.join(REF, "wordfreq_ref"), names).stdout
-        gpu = _run(os.path.join(BIN, "wordfreq_gpu"), names).stdout
+        ref = _run(os.path.join(REF, prog + "_ref"), names).stdout
+        gpu = _run(os.path.join(BIN, prog + "_gpu"), names).stdout
 
     def results(text):
         return [ln for ln in text.splitlines() if re.match(r"^\d+ \S+$", ln) or "total words" in ln]
