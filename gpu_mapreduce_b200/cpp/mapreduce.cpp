@@ -379,6 +379,7 @@ void MapReduce::push_settings()
   ck(mrgpu_set(gpu, "memsize", memsize), 0);
   ck(mrgpu_set(gpu, "keyalign", keyalign), 0);
   ck(mrgpu_set(gpu, "valuealign", valuealign), 0);
+  ck(mrgpu_set(gpu, "outofcore", outofcore), 0);  // 1: stores beyond one page live in host memory (the library's out-of-core tier)
 }
 
 void MapReduce::set_fpath(const char *str)

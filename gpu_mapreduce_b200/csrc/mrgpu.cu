@@ -59,6 +59,12 @@ struct mrgpu_mr {
   // setting "combine": aggregate() ships one row [key | count] per distinct key instead of every pair when the pairs
   // cannot be told apart (ops_aggregate.cuh); 0 = always the plain exchange in the reference's delivery order
   int64_t combine = 1;
+  // setting "hbm_budget" (MB, 0 = unlimited): a KeyValue whose device part outgrows it moves to pinned host memory
+  // piece by piece; convert / reduce / stats / pages / scan work on such stores (ops_spool.cuh)
+  int64_t hbm_budget = 0;
+  std::vector<HostKV> kv_spool;     // host pieces that precede the device part mr->kv, in order
+  std::vector<HostKMV> kmv_spool;   // host pieces of the KMV (the device part mr->kmv is then empty)
+  uint64_t spool_kv_pairs = 0, spool_kmv_pairs = 0;
   int64_t debug_fail_alloc = -1;    // test hook: the n-th next pool allocation fails (-1 = off); mirrors pool.fail_after
   cudaEvent_t order_ev = nullptr;   // orders this handle's stream behind another handle's (add, map(mr))
   // The global pair count of the current store when the last collective call computed it (1 = of the KV, 2 = of the
@@ -139,6 +145,15 @@ static bool is_device_ptr(const void *p)
 // global sum over ranks of a per-rank count (the MPI_Allreduce at the end of every reference op)
 static uint64_t allreduce_sum(mrgpu_mr *mr, uint64_t v);
 enum { G_NONE = 0, G_KV = 1, G_KMV = 2 };
+// pairs of the handle's KV / KMV on this rank: host pieces (out-of-core tier) + the part in HBM
+static uint64_t kv_total(const mrgpu_mr *mr) { return (mr->kv ? mr->kv->nkv : 0) + mr->spool_kv_pairs; }
+static uint64_t kmv_total(const mrgpu_mr *mr) { return (mr->kmv ? mr->kmv->nkmv : 0) + mr->spool_kmv_pairs; }
+static void spool_clear_kv(mrgpu_mr *mr);
+static void spool_clear_kmv(mrgpu_mr *mr);
+static void spool_after_map(mrgpu_mr *mr);
+static void spool_make_resident(mrgpu_mr *mr);
+static void convert_spooled(mrgpu_mr *mr);
+static void reduce_spooled(mrgpu_mr *mr, int functor);
 static uint64_t global_count(mrgpu_mr *mr, uint64_t local, int what, bool reuse)
 {
   if (reuse && mr->g_what == what) return mr->g_count;
@@ -168,6 +183,7 @@ static void order_after(mrgpu_mr *mr, mrgpu_mr *other)
 #include "ops_shape.cuh"
 #include "ops_partition.cuh"
 #include "ops_aggregate.cuh"
+#include "ops_spool.cuh"
 #include "ops_pages.cuh"
 #include "ops_scan.cuh"
 
@@ -223,6 +239,8 @@ static int destroy_impl(mrgpu_mr *mr, bool collective)
     comm_destroy(mr);
   }
   scan_forget(mr);
+  spool_clear_kv(mr);
+  spool_clear_kmv(mr);
   if (mr->order_ev) cudaEventDestroy(mr->order_ev);
   if (mr->copy_stream) cudaStreamDestroy(mr->copy_stream);
   for (auto e : mr->copy_ev)
@@ -247,7 +265,7 @@ static int64_t *setting(mrgpu_mr *mr, const char *name)
              {"verbosity", &mr->verbosity}, {"timer", &mr->timer},         {"all2all", &mr->all2all},
              {"mapstyle", &mr->mapstyle},   {"minpage", &mr->minpage},     {"maxpage", &mr->maxpage},
              {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage},   {"compact", &mr->compact},     {"ahead", &mr->ahead},
-             {"l2pin", &mr->l2pin},         {"combine", &mr->combine},
+             {"l2pin", &mr->l2pin},         {"combine", &mr->combine},     {"hbm_budget", &mr->hbm_budget},
                     {"debug_fail_alloc", &mr->debug_fail_alloc}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) return t.p;
@@ -428,7 +446,8 @@ extern "C" int mrgpu_kv_close(mrgpu_mr *mr, uint64_t *nkv)
   }
   sync(mr);
   s.clear();
-  if (nkv) *nkv = allreduce_sum(mr, kv->nkv);
+  spool_after_map(mr);
+  if (nkv) *nkv = allreduce_sum(mr, kv_total(mr));
   API_END(mr)
 }
 

@@ -709,9 +709,10 @@ extern "C" int mrgpu_aggregate(mrgpu_mr *mr, uint64_t *nkv)
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot aggregate without KeyValue");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  if (mr->nranks > 1) spool_make_resident(mr);  // the exchange works on the store in HBM (one rank: nothing moves)
   aggregate_impl(mr);
   sync(mr);
-  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);  // pairs only moved: the global count is the one before
+  if (nkv) *nkv = global_count(mr, kv_total(mr), G_KV, true);  // pairs only moved: the global count is the one before
   API_END(mr)
 }
 
@@ -722,7 +723,7 @@ extern "C" int mrgpu_aggregate_dest(mrgpu_mr *mr, const int32_t *dest, uint64_t 
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot aggregate without KeyValue");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
-  if (ndest != mr->kv->nkv) MR_FAIL(MRGPU_EINVAL, "aggregate: one destination per pair is required");
+  if (ndest != kv_total(mr)) MR_FAIL(MRGPU_EINVAL, "aggregate: one destination per pair is required");
   if (ndest && !dest) MR_FAIL(MRGPU_EINVAL, "null destinations");
   if (mr->nranks > 1) {
     Buf<int32_t> tmp;
@@ -730,11 +731,12 @@ extern "C" int mrgpu_aggregate_dest(mrgpu_mr *mr, const int32_t *dest, uint64_t 
     static const int32_t none = 0;
     const int32_t *dd = ndest ? stage_input(mr, dest, ndest, tmp, false) : &none;
     mr->err.clear();
+    spool_make_resident(mr);
     aggregate_impl(mr, dd);
     sync(mr);
     if (!mr->err.empty()) MR_FAIL(MRGPU_EINVAL, mr->err);
   }
-  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);
+  if (nkv) *nkv = global_count(mr, kv_total(mr), G_KV, true);
   API_END(mr)
 }
 
@@ -743,11 +745,12 @@ extern "C" int mrgpu_collate(mrgpu_mr *mr, uint64_t *nkmv)
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot collate without KeyValue");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
+  if (mr->nranks > 1) spool_make_resident(mr);
   aggregate_impl(mr);  // src/mapreduce.cpp:726-727: aggregate(hash); convert();
   mr->g_what = G_NONE;
   convert_impl(mr);
   sync(mr);
-  if (nkmv) *nkmv = global_count(mr, mr->kmv->nkmv, G_KMV, false);
+  if (nkmv) *nkmv = global_count(mr, kmv_total(mr), G_KMV, false);
   API_END(mr)
 }
 
@@ -862,6 +865,7 @@ extern "C" int mrgpu_gather(mrgpu_mr *mr, int numprocs, uint64_t *nkv)
   if (numprocs < 1 || numprocs > mr->nranks) MR_FAIL(MRGPU_EINVAL, "Invalid processor count for gather");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
   mr->g_what = G_NONE;
+  spool_make_resident(mr);
   gather_impl(mr, numprocs);
   if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
   API_END(mr)
@@ -940,6 +944,7 @@ extern "C" int mrgpu_broadcast(mrgpu_mr *mr, int root, uint64_t *nkv)
   if (root < 0 || root >= mr->nranks) MR_FAIL(MRGPU_EINVAL, "Invalid root for broadcast");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
   mr->g_what = G_NONE;
+  spool_make_resident(mr);
   broadcast_impl(mr, root);
   if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
   API_END(mr)
@@ -954,6 +959,7 @@ extern "C" int mrgpu_scrunch(mrgpu_mr *mr, int numprocs, const void *key, int ke
   if (keybytes < 0 || (keybytes && !key)) MR_FAIL(MRGPU_EINVAL, "bad key");
   if (mr->nranks > 1 && !mr->comm) MR_FAIL(MRGPU_ECOMM, "communicator not initialised");
   mr->g_what = G_NONE;
+  spool_make_resident(mr);
   gather_impl(mr, numprocs);
   collapse_impl(mr, key, keybytes);
   if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);

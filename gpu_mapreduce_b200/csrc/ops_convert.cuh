@@ -558,7 +558,7 @@ static void convert_general(mrgpu_mr *mr)
 static bool convert_dense(mrgpu_mr *mr);
 static bool convert_hash(mrgpu_mr *mr);
 
-static void convert_impl(mrgpu_mr *mr)
+static void convert_resident(mrgpu_mr *mr)
 {
   freeze(mr);
   DevKV *kv = mr->kv;
@@ -648,6 +648,15 @@ static void convert_impl(mrgpu_mr *mr)
   mr->kv = nullptr;
 }
 
+// convert(): of the KV in HBM, or -- when part of it lives in host memory (out-of-core tier, ops_spool.cuh) -- set by set
+static void convert_impl(mrgpu_mr *mr)
+{
+  freeze(mr);
+  spool_clear_kmv(mr);
+  if (!mr->kv_spool.empty()) convert_spooled(mr);
+  else convert_resident(mr);
+}
+
 extern "C" int mrgpu_convert(mrgpu_mr *mr, uint64_t *nkmv)
 {
   API_BEGIN(mr)
@@ -655,6 +664,6 @@ extern "C" int mrgpu_convert(mrgpu_mr *mr, uint64_t *nkmv)
   mr->g_what = G_NONE;
   convert_impl(mr);
   sync(mr);
-  if (nkmv) *nkmv = global_count(mr, mr->kmv->nkmv, G_KMV, false);
+  if (nkmv) *nkmv = global_count(mr, kmv_total(mr), G_KMV, false);
   API_END(mr)
 }

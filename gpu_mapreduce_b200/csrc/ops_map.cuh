@@ -20,6 +20,8 @@ static void kv_begin_map(mrgpu_mr *mr, int addflag, bool keep_packed = false)
   mr->g_what = G_NONE;
   delete mr->kmv;
   mr->kmv = nullptr;
+  spool_clear_kmv(mr);
+  if (!addflag) spool_clear_kv(mr);
   if (!addflag || !mr->kv) {
     delete mr->kv;
     mr->kv = new DevKV(&mr->pool);
@@ -317,9 +319,10 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
     emit_from_host(mr, kv, keys, n, count);
     kv_commit_uniform(kv, 4, 4, 16, n);
     kv->h_offs_valid = false;
+    spool_after_map(mr);
     if (nkv) {
       sync(mr);
-      *nkv = global_count(mr, kv->nkv, G_KV, false);
+      *nkv = global_count(mr, kv_total(mr), G_KV, false);
     }
     return MRGPU_OK;
   }
@@ -354,9 +357,10 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
     kv_commit_uniform(kv, 4, 4, 16, n);
     kv->h_offs_valid = false;
     tmp.release();
+    spool_after_map(mr);
     if (nkv) {
       sync(mr);
-      *nkv = global_count(mr, kv->nkv, G_KV, false);
+      *nkv = global_count(mr, kv_total(mr), G_KV, false);
     }
     return MRGPU_OK;
   }
@@ -373,9 +377,10 @@ extern "C" int mrgpu_map_intcount(mrgpu_mr *mr, const uint32_t *keys, uint64_t n
   }
   kv_commit_uniform(kv, 4, 4, rs, n);
   tmp.release();
+  spool_after_map(mr);
   if (nkv) {
     sync(mr);
-    *nkv = global_count(mr, kv->nkv, G_KV, false);
+    *nkv = global_count(mr, kv_total(mr), G_KV, false);
   }
   API_END(mr)
 }
@@ -439,6 +444,7 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
   API_BEGIN(mr)
   if (!srcmr) MR_FAIL(MRGPU_EINVAL, "null source");
   if (!srcmr->kv) MR_FAIL(MRGPU_ENOKV, "MapReduce passed to map() does not have KeyValue pairs");
+  spool_make_resident(srcmr);  // the functors walk the source in HBM
   if (srcmr->device != mr->device) MR_FAIL(MRGPU_EINVAL, "source and destination live on different devices");
   freeze(mr);
   freeze(srcmr);
@@ -518,8 +524,9 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
   if (self) delete src;
   // another stream read srcmr's store: it must be done before srcmr (whose pool reuses memory in ITS stream's order)
   // is used again
+  spool_after_map(mr);
   if (nkv || mr->pool.stream != srcmr->pool.stream) sync(mr);
-  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, false);
+  if (nkv) *nkv = global_count(mr, kv_total(mr), G_KV, false);
   API_END(mr)
 }
 
@@ -639,9 +646,10 @@ extern "C" int mrgpu_map_rmat(mrgpu_mr *mr, uint64_t ngenerate, int nlevels, dou
   unsigned long long D = fraction > 0.0 ? 5ull * nlevels : (unsigned long long) nlevels;
   lcg_jump(ngenerate * D, x);
   *state48 = x;
+  spool_after_map(mr);
   if (nkv) {
     sync(mr);
-    *nkv = global_count(mr, kv->nkv, G_KV, false);
+    *nkv = global_count(mr, kv_total(mr), G_KV, false);
   }
   API_END(mr)
 }
@@ -653,6 +661,34 @@ __global__ void shift_offsets_kernel(uint64_t *dst, const uint64_t *src, uint64_
 {
   uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n_plus_1) dst[i] = src[i] + delta;
+}
+
+// append the pairs of record-stream KV `o` to record-stream KV `kv` (both on this device; the copy runs on mr's stream)
+static void kv_concat(mrgpu_mr *mr, DevKV *kv, const DevKV *o)
+{
+  cudaStream_t s = mr->pool.stream;
+  if (!o->nkv) return;
+  uint64_t base = kv->nbytes;
+  bool fits = o->uniform && (kv->nkv == 0 || (kv->uniform && kv->kb == o->kb && kv->vb == o->vb));
+  if (fits) {
+    kv_append_uniform(mr, kv, o->kb, o->vb, o->nkv);
+  } else {
+    kv_make_general(mr, kv);
+    kv->reserve_offs(kv->nkv + o->nkv + 1);
+    if (o->uniform) {
+      kv_append_uniform(mr, kv, o->kb, o->vb, o->nkv);  // general branch fills the offsets
+    } else {
+      shift_offsets_kernel<<<(unsigned) ((o->nkv + 1 + 255) / 256), 256, 0, s>>>(kv->offs + kv->nkv, o->offs, o->nkv + 1, base);
+      MR_CUDA(cudaGetLastError());
+      kv->reserve_bytes(base + o->nbytes);
+    }
+  }
+  MR_CUDA(cudaMemcpyAsync(kv->data + base, o->data, o->nbytes, cudaMemcpyDeviceToDevice, s));
+  kv->nbytes += o->nbytes;
+  kv->nkv += o->nkv;
+  kv->ksize += o->ksize;
+  kv->vsize += o->vsize;
+  kv->h_offs_valid = false;
 }
 
 extern "C" int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv)
@@ -667,34 +703,13 @@ extern "C" int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv)
   if (mr->al.k != other->al.k || mr->al.v != other->al.v) MR_FAIL(MRGPU_EINVAL, "add: alignments differ");
   if (mr->device != other->device) MR_FAIL(MRGPU_EINVAL, "add: the two MapReduce objects live on different devices");
   if (!mr->kv) mr->kv = new DevKV(&mr->pool);
+  spool_make_resident(mr);
+  spool_make_resident(other);
   DevKV *kv = mr->kv, *o = other->kv;
   kv_unpack(mr, kv);
   kv_unpack(other, o);   // enqueued on other's stream ...
   order_after(mr, other);  // ... and read below on mine
-  cudaStream_t s = mr->pool.stream;
-  if (o->nkv) {
-    uint64_t base = kv->nbytes;
-    bool fits = o->uniform && (kv->nkv == 0 || (kv->uniform && kv->kb == o->kb && kv->vb == o->vb));
-    if (fits) {
-      kv_append_uniform(mr, kv, o->kb, o->vb, o->nkv);
-    } else {
-      kv_make_general(mr, kv);
-      kv->reserve_offs(kv->nkv + o->nkv + 1);
-      if (o->uniform) {
-        kv_append_uniform(mr, kv, o->kb, o->vb, o->nkv);  // general branch fills the offsets
-      } else {
-        shift_offsets_kernel<<<(unsigned) ((o->nkv + 1 + 255) / 256), 256, 0, s>>>(kv->offs + kv->nkv, o->offs, o->nkv + 1, base);
-        MR_CUDA(cudaGetLastError());
-        kv->reserve_bytes(base + o->nbytes);
-      }
-    }
-    MR_CUDA(cudaMemcpyAsync(kv->data + base, o->data, o->nbytes, cudaMemcpyDeviceToDevice, s));
-    kv->nbytes += o->nbytes;
-    kv->nkv += o->nkv;
-    kv->ksize += o->ksize;
-    kv->vsize += o->vsize;
-    kv->h_offs_valid = false;
-  }
+  kv_concat(mr, kv, o);
   sync(mr);
   if (nkv) *nkv = global_count(mr, kv->nkv, G_KV, false);
   API_END(mr)

@@ -22,38 +22,31 @@ static void fetch_offs(mrgpu_mr *mr, const uint64_t *d_offs, uint64_t count, std
 
 static constexpr uint64_t kIntMax = 0x7FFFFFFFull;
 
-// page i of a KV
-static PageSlice kv_page(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
+// page i of a KV given by its record count, shape and (host) offset index: the reference's greedy fill
+static PageSlice kv_slice(uint64_t nkv, bool uniform, uint64_t recsize, const uint64_t *o, uint64_t ps, uint64_t ipage, uint64_t *npage_out)
 {
-  DevKV *kv = mr->kv;
-  const uint64_t ps = mr->pagesize;
   PageSlice sl{0, 0, 0, 0, 0};
-  if (kv->nkv == 0) {  // the reference always has one (empty) page
+  if (nkv == 0) {  // the reference always has one (empty) page
     if (npage_out) *npage_out = 1;
     return sl;
   }
-  if (kv->uniform) {
-    uint64_t rpp = std::min<uint64_t>(ps / kv->recsize, kIntMax);
-    uint64_t np = (kv->nkv + rpp - 1) / rpp;
+  if (uniform) {
+    uint64_t rpp = std::min<uint64_t>(ps / recsize, kIntMax);
+    uint64_t np = (nkv + rpp - 1) / rpp;
     if (npage_out) *npage_out = np;
     if (ipage < np) {
       sl.first = ipage * rpp;
-      sl.nkey = std::min(rpp, kv->nkv - sl.first);
-      sl.begin = sl.first * kv->recsize;
-      sl.end = sl.begin + sl.nkey * kv->recsize;
+      sl.nkey = std::min(rpp, nkv - sl.first);
+      sl.begin = sl.first * recsize;
+      sl.end = sl.begin + sl.nkey * recsize;
     }
     return sl;
   }
-  if (!kv->h_offs_valid) {
-    fetch_offs(mr, kv->offs, kv->nkv + 1, kv->h_offs);
-    kv->h_offs_valid = true;
-  }
-  const std::vector<uint64_t> &o = kv->h_offs;
   uint64_t first = 0, page = 0;
-  while (first < kv->nkv) {
+  while (first < nkv) {
     // last record whose end is within first's start + pagesize
     uint64_t limit = o[first] + ps;
-    uint64_t hi = std::upper_bound(o.begin() + first + 1, o.begin() + kv->nkv + 1, limit) - o.begin() - 1;
+    uint64_t hi = std::upper_bound(o + first + 1, o + nkv + 1, limit) - o - 1;
     if (hi - first > kIntMax) hi = first + kIntMax;
     if (page == ipage) {
       sl.first = first;
@@ -68,25 +61,54 @@ static PageSlice kv_page(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
   return sl;
 }
 
-// page i of a KMV; a pair that alone exceeds the page (or INTMAX values / bytes) is an "extended" pair on a
-// page run of its own, as in unique2kmv_all src/keymultivalue.cpp:840-928
-static PageSlice kmv_page(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
+// page i of the part of the KV that is in HBM
+static PageSlice kv_page(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
 {
-  DevKMV *kmv = mr->kmv;
-  kmv_expand(mr, kmv);  // page boundaries and bytes are those of the record stream
-  const uint64_t ps = mr->pagesize;
+  DevKV *kv = mr->kv;
+  if (kv->nkv && !kv->uniform && !kv->h_offs_valid) {
+    fetch_offs(mr, kv->offs, kv->nkv + 1, kv->h_offs);
+    kv->h_offs_valid = true;
+  }
+  return kv_slice(kv->nkv, kv->uniform, kv->recsize, kv->h_offs.data(), mr->pagesize, ipage, npage_out);
+}
+
+// A page of the whole KV = host pieces (out-of-core tier, ops_spool.cuh) in order, then the part in HBM.  Every piece
+// paginates on its own: a piece boundary ends a page, as a spill does in the reference.  piece = -1: the HBM part.
+struct PageLoc {
+  int piece;
+  PageSlice sl;
+};
+static PageLoc kv_page_locate(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
+{
+  PageLoc loc{-1, PageSlice{0, 0, 0, 0, 0}};
+  uint64_t before = 0;
+  bool found = false;
+  for (size_t i = 0; i < mr->kv_spool.size(); i++) {
+    const HostKV &h = mr->kv_spool[i];
+    uint64_t np = 0;
+    PageSlice sl = kv_slice(h.nkv, h.uniform, h.recsize, h.offs, mr->pagesize, ipage >= before ? ipage - before : ~0ull, &np);
+    if (!found && ipage >= before && ipage - before < np) loc = PageLoc{(int) i, sl}, found = true;
+    before += np;
+  }
+  if (mr->kv_spool.empty() || (mr->kv && mr->kv->nkv)) {
+    uint64_t np = 0;
+    PageSlice sl = kv_page(mr, ipage >= before ? ipage - before : ~0ull, &np);
+    if (!found && ipage >= before && ipage - before < np) loc = PageLoc{-1, sl}, found = true;
+    before += np;
+  }
+  if (npage_out) *npage_out = before;
+  return loc;
+}
+
+static PageSlice kmv_slice(uint64_t nkmv, const uint64_t *o, uint64_t ps, uint64_t ipage, uint64_t *npage_out)
+{
   PageSlice sl{0, 0, 0, 0, 0};
-  if (kmv->nkmv == 0) {
+  if (nkmv == 0) {
     if (npage_out) *npage_out = 1;
     return sl;
   }
-  if (!kmv->h_offs_valid) {
-    fetch_offs(mr, kmv->offs, kmv->nkmv + 1, kmv->h_offs);
-    kmv->h_offs_valid = true;
-  }
-  const std::vector<uint64_t> &o = kmv->h_offs;
   uint64_t first = 0, page = 0;
-  while (first < kmv->nkmv) {
+  while (first < nkmv) {
     uint64_t hi;
     int ext = 0;
     if (o[first + 1] - o[first] > ps) {
@@ -94,7 +116,7 @@ static PageSlice kmv_page(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
       ext = 1;
     } else {
       uint64_t limit = o[first] + ps;
-      hi = std::upper_bound(o.begin() + first + 1, o.begin() + kmv->nkmv + 1, limit) - o.begin() - 1;
+      hi = std::upper_bound(o + first + 1, o + nkmv + 1, limit) - o - 1;
       if (hi - first > kIntMax) hi = first + kIntMax;
     }
     if (page == ipage) {
@@ -111,6 +133,41 @@ static PageSlice kmv_page(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
   return sl;
 }
 
+// page i of the part of the KMV that is in HBM; a pair that alone exceeds the page (or INTMAX values / bytes) is an
+// "extended" pair on a page run of its own, as in unique2kmv_all src/keymultivalue.cpp:840-928
+static PageSlice kmv_page(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
+{
+  DevKMV *kmv = mr->kmv;
+  kmv_expand(mr, kmv);  // page boundaries and bytes are those of the record stream
+  if (kmv->nkmv && !kmv->h_offs_valid) {
+    fetch_offs(mr, kmv->offs, kmv->nkmv + 1, kmv->h_offs);
+    kmv->h_offs_valid = true;
+  }
+  return kmv_slice(kmv->nkmv, kmv->h_offs.data(), mr->pagesize, ipage, npage_out);
+}
+
+static PageLoc kmv_page_locate(mrgpu_mr *mr, uint64_t ipage, uint64_t *npage_out)
+{
+  PageLoc loc{-1, PageSlice{0, 0, 0, 0, 0}};
+  uint64_t before = 0;
+  bool found = false;
+  for (size_t i = 0; i < mr->kmv_spool.size(); i++) {
+    const HostKMV &h = mr->kmv_spool[i];
+    uint64_t np = 0;
+    PageSlice sl = kmv_slice(h.nkmv, h.offs, mr->pagesize, ipage >= before ? ipage - before : ~0ull, &np);
+    if (!found && ipage >= before && ipage - before < np) loc = PageLoc{(int) i, sl}, found = true;
+    before += np;
+  }
+  if (mr->kmv_spool.empty() || (mr->kmv && mr->kmv->nkmv)) {
+    uint64_t np = 0;
+    PageSlice sl = kmv_page(mr, ipage >= before ? ipage - before : ~0ull, &np);
+    if (!found && ipage >= before && ipage - before < np) loc = PageLoc{-1, sl}, found = true;
+    before += np;
+  }
+  if (npage_out) *npage_out = before;
+  return loc;
+}
+
 extern "C" int mrgpu_kv_stats(mrgpu_mr *mr, mrgpu_stats *out)
 {
   API_BEGIN(mr)
@@ -119,12 +176,18 @@ extern "C" int mrgpu_kv_stats(mrgpu_mr *mr, mrgpu_stats *out)
   freeze(mr);
   DevKV *kv = mr->kv;
   out->npair = kv->nkv;
-  out->nvalue = kv->nkv;
   out->keysize = kv->ksize;
   out->valuesize = kv->vsize;
-  out->exactsize = 8 * kv->nkv + kv->ksize + kv->vsize;  // src/keyvalue.cpp:671-672
   out->alignsize = kv->nbytes;
-  kv_page(mr, ~0ull, &out->npage);
+  for (const HostKV &h : mr->kv_spool) {  // pieces in host memory (out-of-core tier)
+    out->npair += h.nkv;
+    out->keysize += h.ksize;
+    out->valuesize += h.vsize;
+    out->alignsize += h.nbytes;
+  }
+  out->nvalue = out->npair;
+  out->exactsize = 8 * out->npair + out->keysize + out->valuesize;  // src/keyvalue.cpp:671-672
+  kv_page_locate(mr, ~0ull, &out->npage);
   API_END(mr)
 }
 
@@ -140,9 +203,16 @@ extern "C" int mrgpu_kmv_stats(mrgpu_mr *mr, mrgpu_stats *out)
   out->nvalue = kmv->nvalue;
   out->keysize = kmv->ksize;
   out->valuesize = kmv->vsize;
-  out->exactsize = 12 * kmv->nkmv + 4 * kmv->nvalue + kmv->ksize + kmv->vsize;  // src/keymultivalue.cpp:1460-1461
   out->alignsize = kmv->nbytes;
-  kmv_page(mr, ~0ull, &out->npage);
+  for (const HostKMV &h : mr->kmv_spool) {
+    out->npair += h.nkmv;
+    out->nvalue += h.nvalue;
+    out->keysize += h.ksize;
+    out->valuesize += h.vsize;
+    out->alignsize += h.nbytes;
+  }
+  out->exactsize = 12 * out->npair + 4 * out->nvalue + out->keysize + out->valuesize;  // src/keymultivalue.cpp:1460-1461
+  kmv_page_locate(mr, ~0ull, &out->npage);
   API_END(mr)
 }
 
@@ -154,10 +224,10 @@ extern "C" int mrgpu_global_count(mrgpu_mr *mr, int which, uint64_t *n)
   if (!n) MR_FAIL(MRGPU_EINVAL, "null out");
   if (which == 0) {
     if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot print stats without KeyValue");
-    *n = global_count(mr, mr->kv->nkv, G_KV, true);
+    *n = global_count(mr, kv_total(mr), G_KV, true);
   } else {
     if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "Cannot print stats without KeyMultiValue");
-    *n = global_count(mr, mr->kmv->nkmv, G_KMV, true);
+    *n = global_count(mr, kmv_total(mr), G_KMV, true);
   }
   API_END(mr)
 }
@@ -168,12 +238,24 @@ extern "C" int mrgpu_kv_page_info(mrgpu_mr *mr, uint64_t ipage, uint64_t *nkey, 
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot request a page without KeyValue");
   freeze(mr);
   uint64_t np;
-  PageSlice sl = kv_page(mr, ipage, &np);
+  const PageLoc loc = kv_page_locate(mr, ipage, &np);
+  const PageSlice sl = loc.sl;
   if (ipage >= np) MR_FAIL(MRGPU_EINVAL, "page index out of range");
   DevKV *kv = mr->kv;
   if (nkey) *nkey = sl.nkey;
   if (alignsize) *alignsize = sl.end - sl.begin;
-  if (keysize || valuesize) {
+  if (loc.piece >= 0) {  // a piece in host memory: its records are right here
+    const HostKV &h = mr->kv_spool[loc.piece];
+    uint64_t ks = 0, vs = 0;
+    if (h.uniform) ks = sl.nkey * h.kb, vs = sl.nkey * h.vb;
+    else
+      for (uint64_t i = sl.first; i < sl.first + sl.nkey; i++) {
+        const uint32_t *r = (const uint32_t *) (h.data + h.offs[i]);
+        ks += r[0], vs += r[1];
+      }
+    if (keysize) *keysize = ks;
+    if (valuesize) *valuesize = vs;
+  } else if (keysize || valuesize) {
     uint64_t ks = 0, vs = 0;
     if (kv->uniform) {
       ks = sl.nkey * kv->kb;
@@ -199,9 +281,13 @@ extern "C" int mrgpu_kv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot request a page without KeyValue");
   freeze(mr);
   uint64_t np;
-  PageSlice sl = kv_page(mr, ipage, &np);
+  const PageLoc loc = kv_page_locate(mr, ipage, &np);
+  const PageSlice sl = loc.sl;
   if (ipage >= np) MR_FAIL(MRGPU_EINVAL, "page index out of range");
-  if (sl.end > sl.begin) {
+  if (loc.piece >= 0) {
+    if (sl.end > sl.begin && !dst) MR_FAIL(MRGPU_EINVAL, "null destination");
+    if (sl.end > sl.begin) memcpy(dst, mr->kv_spool[loc.piece].data + sl.begin, sl.end - sl.begin);
+  } else if (sl.end > sl.begin) {
     if (!dst) MR_FAIL(MRGPU_EINVAL, "null destination");
     if (mr->kv->weighted) kv_unpack(mr, mr->kv);  // rows [key | count] -> records, once; pages are then plain slices
     if (mr->kv->packed) {  // header-less rows: write this page's records out, the KV itself stays as it is
@@ -222,7 +308,7 @@ extern "C" int mrgpu_kmv_page_info(mrgpu_mr *mr, uint64_t ipage, uint64_t *nkey,
   if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "Cannot request a page without KeyMultiValue");
   freeze(mr);
   uint64_t np;
-  PageSlice sl = kmv_page(mr, ipage, &np);
+  const PageSlice sl = kmv_page_locate(mr, ipage, &np).sl;
   if (ipage >= np) MR_FAIL(MRGPU_EINVAL, "page index out of range");
   if (nkey) *nkey = sl.nkey;
   if (alignsize) *alignsize = sl.end - sl.begin;
@@ -236,9 +322,13 @@ extern "C" int mrgpu_kmv_page_copy(mrgpu_mr *mr, uint64_t ipage, void *dst)
   if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "Cannot request a page without KeyMultiValue");
   freeze(mr);
   uint64_t np;
-  PageSlice sl = kmv_page(mr, ipage, &np);
+  const PageLoc loc = kmv_page_locate(mr, ipage, &np);
+  const PageSlice sl = loc.sl;
   if (ipage >= np) MR_FAIL(MRGPU_EINVAL, "page index out of range");
-  if (sl.end > sl.begin) {
+  if (loc.piece >= 0) {
+    if (sl.end > sl.begin && !dst) MR_FAIL(MRGPU_EINVAL, "null destination");
+    if (sl.end > sl.begin) memcpy(dst, mr->kmv_spool[loc.piece].data + sl.begin, sl.end - sl.begin);
+  } else if (sl.end > sl.begin) {
     if (!dst) MR_FAIL(MRGPU_EINVAL, "null destination");
     MR_CUDA(cudaMemcpyAsync(dst, mr->kmv->data + sl.begin, sl.end - sl.begin, cudaMemcpyDeviceToHost, mr->pool.stream));
   }
@@ -250,6 +340,7 @@ extern "C" int mrgpu_kv_device_view(mrgpu_mr *mr, const void **data, uint64_t *n
 {
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "no KeyValue");
+  spool_make_resident(mr);
   DevKV *kv = mr->kv;
   kv_unpack(mr, kv);  // the view is of the record stream
   if (data) *data = kv->data;
@@ -263,6 +354,7 @@ extern "C" int mrgpu_kmv_device_view(mrgpu_mr *mr, const void **data, uint64_t *
 {
   API_BEGIN(mr)
   if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "no KeyMultiValue");
+  spool_make_resident(mr);
   kmv_expand(mr, mr->kmv);
   if (data) *data = mr->kmv->data;
   if (nbytes) *nbytes = mr->kmv->nbytes;

@@ -532,6 +532,7 @@ extern "C" int mrgpu_debug_partition(mrgpu_mr *mr, int nprocs, uint64_t *counts)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot aggregate without KeyValue");
   if (nprocs < 1 || nprocs > PART_MAXP) MR_FAIL(MRGPU_EINVAL, "bad nprocs");
   freeze(mr);
+  spool_make_resident(mr);
   if (mr->kv->weighted) kv_unpack(mr, mr->kv);
   DevKV *kv = mr->kv;
   DevKV *nk = new DevKV(&mr->pool);

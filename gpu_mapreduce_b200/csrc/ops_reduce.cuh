@@ -362,9 +362,10 @@ extern "C" int mrgpu_reduce(mrgpu_mr *mr, int functor, uint64_t *nkv)
   if (!mr->kmv) MR_FAIL(MRGPU_ENOKMV, "Cannot reduce without KeyMultiValue");
   const bool had = mr->g_what == G_KMV;  // every stock functor emits exactly one pair per KMV pair
   mr->g_what = G_NONE;
-  reduce_impl(mr, functor);
+  if (!mr->kmv_spool.empty()) reduce_spooled(mr, functor);
+  else reduce_impl(mr, functor);
   if (had) mr->g_what = G_KV;
-  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);
+  if (nkv) *nkv = global_count(mr, kv_total(mr), G_KV, true);
   API_END(mr)
 }
 
@@ -377,7 +378,8 @@ extern "C" int mrgpu_compress(mrgpu_mr *mr, int functor, uint64_t *nkv)
   if (functor < 0 || functor > MRGPU_REDUCE_CULL) MR_FAIL(MRGPU_EINVAL, "unknown reduce functor");
   mr->g_what = G_NONE;
   convert_impl(mr);
-  reduce_impl(mr, functor);
-  if (nkv) *nkv = allreduce_sum(mr, mr->kv->nkv);
+  if (!mr->kmv_spool.empty()) reduce_spooled(mr, functor);
+  else reduce_impl(mr, functor);
+  if (nkv) *nkv = allreduce_sum(mr, kv_total(mr));
   API_END(mr)
 }

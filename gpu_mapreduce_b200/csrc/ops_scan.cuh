@@ -42,7 +42,7 @@ extern "C" int mrgpu_scan_kv(mrgpu_mr *mr, mrgpu_scan_kv_fn fn, void *ptr, uint6
   freeze(mr);
   const Align al = mr->al;
   uint64_t np = 0;
-  kv_page(mr, ~0ull, &np);
+  kv_page_locate(mr, ~0ull, &np);
   std::vector<char> page;
   for (uint64_t ip = 0; ip < np; ip++) {
     uint64_t nkey = 0, asz = 0;
@@ -57,7 +57,7 @@ extern "C" int mrgpu_scan_kv(mrgpu_mr *mr, mrgpu_scan_kv_fn fn, void *ptr, uint6
       p = round_up(v0 + vb, al.t);
     }
   }
-  if (nkv) *nkv = global_count(mr, mr->kv->nkv, G_KV, true);
+  if (nkv) *nkv = global_count(mr, kv_total(mr), G_KV, true);
   API_END(mr)
 }
 
@@ -69,7 +69,7 @@ extern "C" int mrgpu_scan_kmv(mrgpu_mr *mr, mrgpu_scan_kmv_fn fn, void *ptr, uin
   freeze(mr);
   const Align al = mr->al;
   uint64_t np = 0;
-  kmv_page(mr, ~0ull, &np);
+  kmv_page_locate(mr, ~0ull, &np);
   std::vector<char> page;
   ScanBlocks *sb = scan_blocks(mr, true);
   for (uint64_t ip = 0; ip < np; ip++) {
@@ -100,7 +100,7 @@ extern "C" int mrgpu_scan_kmv(mrgpu_mr *mr, mrgpu_scan_kmv_fn fn, void *ptr, uin
       p = round_up(v0 + (uint64_t) (unsigned) mvb, al.t);
     }
   }
-  if (nkmv) *nkmv = global_count(mr, mr->kmv->nkmv, G_KMV, true);
+  if (nkmv) *nkmv = global_count(mr, kmv_total(mr), G_KMV, true);
   API_END(mr)
 }
 

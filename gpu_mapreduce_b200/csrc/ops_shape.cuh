@@ -58,6 +58,7 @@ static void clone_impl(mrgpu_mr *mr)
   const uint64_t n = kv->nkv;
   delete mr->kmv;
   mr->kmv = nullptr;
+  spool_clear_kmv(mr);
   DevKMV *kmv = empty_kmv(mr);
   try {
     if (n) {
@@ -131,6 +132,7 @@ static void collapse_impl(mrgpu_mr *mr, const void *key, int keybytes)
   if (2 * n > 0x7FFFFFFFull || mvb > 0x7FFFFFFFull || total > mr->pagesize) MR_FAIL(MRGPU_ELIMIT, "Collapse of multi-block KMV not yet supported");
   delete mr->kmv;
   mr->kmv = nullptr;
+  spool_clear_kmv(mr);
   DevKMV *kmv = new DevKMV(&pool);
   try {
     kmv->offs = (uint64_t *) pool.alloc(16);
@@ -181,6 +183,7 @@ extern "C" int mrgpu_clone(mrgpu_mr *mr, uint64_t *nkmv)
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot clone without KeyValue");
   mr->g_what = G_NONE;
+  spool_make_resident(mr);
   clone_impl(mr);
   if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
   API_END(mr)
@@ -192,6 +195,7 @@ extern "C" int mrgpu_collapse(mrgpu_mr *mr, const void *key, int keybytes, uint6
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot collapse without KeyValue");
   if (keybytes < 0 || (keybytes && !key)) MR_FAIL(MRGPU_EINVAL, "bad key");
   mr->g_what = G_NONE;
+  spool_make_resident(mr);
   collapse_impl(mr, key, keybytes);
   if (nkmv) *nkmv = allreduce_sum(mr, mr->kmv->nkmv);
   API_END(mr)

@@ -261,6 +261,7 @@ extern "C" int mrgpu_sort_keys(mrgpu_mr *mr, int flag, uint64_t *nkv)
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot sort_keys without KeyValue");
   freeze(mr);
+  spool_make_resident(mr);
   kv_unpack(mr, mr->kv);
   sort_keys_impl(mr, flag);
   sync(mr);
@@ -273,6 +274,7 @@ extern "C" int mrgpu_sort_values(mrgpu_mr *mr, int flag, uint64_t *nkv)
   API_BEGIN(mr)
   if (!mr->kv) MR_FAIL(MRGPU_ENOKV, "Cannot sort_values without KeyValue");
   freeze(mr);
+  spool_make_resident(mr);
   kv_unpack(mr, mr->kv);
   sort_keys_impl(mr, flag, true);
   sync(mr);

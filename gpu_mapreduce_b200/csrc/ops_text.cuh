@@ -363,7 +363,8 @@ extern "C" int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbyte
   }
   tmp.release();
   sync(mr);
-  if (nkv) *nkv = allreduce_sum(mr, kv->nkv);
+  spool_after_map(mr);
+  if (nkv) *nkv = allreduce_sum(mr, kv_total(mr));
   API_END(mr)
 }
 
@@ -685,6 +686,7 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
   }
   tmp.release();
   sync(mr);
-  if (nkv) *nkv = allreduce_sum(mr, kv->nkv);
+  spool_after_map(mr);
+  if (nkv) *nkv = allreduce_sum(mr, kv_total(mr));
   API_END(mr)
 }

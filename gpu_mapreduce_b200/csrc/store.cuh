@@ -145,6 +145,22 @@ struct DevKMV {
   }
 };
 
+// Out-of-core tier (ops_spool.cuh): a piece of a KeyValue / KeyMultiValue that lives in pinned host memory, in the
+// reference's record-stream layout (what a page copy returns), with the offset index when records differ in size
+struct HostKV {
+  uint8_t *data = nullptr;
+  uint64_t *offs = nullptr;  // [nkv + 1], nullptr when uniform
+  uint64_t nbytes = 0, nkv = 0, ksize = 0, vsize = 0;
+  bool uniform = true;
+  uint32_t kb = 0, vb = 0, recsize = 0;
+};
+struct HostKMV {
+  uint8_t *data = nullptr;
+  uint64_t *offs = nullptr;  // [nkmv + 1]
+  uint64_t nbytes = 0, nkmv = 0, nvalue = 0, ksize = 0, vsize = 0;
+  int64_t ukb = -1, uvb = -1;
+};
+
 // host-side staging of pairs added one by one (KeyValue::add from a host callback)
 struct Staging {
   bool open = false;

@@ -108,6 +108,15 @@ const char *mrgpu_last_error(const mrgpu_mr *mr);
  * plain exchange; the one observable difference is the ORDER of the pairs inside the KeyValue after aggregate():
  * still by source rank, but within a source by ascending key instead of arrival order.  0 = always the plain
  * exchange, in the reference's delivery order.  Must be the same on every rank.
+ * "hbm_budget" (MB, default 0 = unlimited) and the reference's "outofcore" (1 = force data out of core; here: a budget
+ * of one page): the out-of-core tier.  After a map-type call a KeyValue whose part in HBM exceeds the budget moves to
+ * pinned host memory as a piece (the analogue of the reference's page spill files, src/keyvalue.cpp:216-255,
+ * src/spool.cpp:76-195); later calls with addflag append to a fresh part in HBM.  convert() of such a KeyValue splits
+ * every piece by key hash into sets that fit (KeyMultiValue::convert's partitions, src/keymultivalue.cpp:522-638,
+ * 1056), converts set by set and leaves the KeyMultiValue in host pieces; reduce() with a stock functor walks them;
+ * statistics, pages and scan read the pieces where they are.  Values of a key keep their arrival order.  Every other
+ * operation brings the whole store back into HBM first.  The budget is checked between calls: one call's output is
+ * the unit that moves.
  * "l2pin" (MiB, default 56; 0 = off): convert()'s counting path keeps the busy part of its count table resident in
  * L2 while it streams the keys past it.  For the duration of that ONE kernel launch it (a) puts a persisting
  * access-policy window on the handle's stream and (b) raises the DEVICE-WIDE limit cudaLimitPersistingL2CacheSize

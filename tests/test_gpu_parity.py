@@ -956,6 +956,69 @@ def test_add_and_map_mr_across_streams():
             h.destroy()
 
 
+# ------------------------------------------------------------------------------------------- out-of-core tier
+
+def test_out_of_core_intcount_pipeline(MR, oracle):
+    """hbm_budget = 1 MB: the KV moves to host memory piece by piece while map appends; stats / pages / scan read the
+    pieces; convert splits them into sets by key hash; reduce walks the KMV pieces: same results as in core"""
+    r = np.random.RandomState(31)
+    parts = [(r.zipf(1.3, size=200_000) % 50_000).astype(np.uint32) for _ in range(5)]
+    allkeys = np.concatenate(parts)
+    want_kv = [(struct.pack("<I", int(k)), struct.pack("<i", 1)) for k in allkeys]
+    res = {}
+    for budget in (1, 0):
+        mr = MR(hbm_budget=budget)
+        n = 0
+        for i, p in enumerate(parts):
+            n = mr.map_intcount(p, addflag=1 if i else 0)
+        assert n == len(allkeys)
+        st = mr.kv_stats()
+        assert st.npair == len(allkeys) and st.keysize == 4 * len(allkeys) and st.alignsize == 16 * len(allkeys)
+        assert mr.scan_kv() == want_kv                              # pieces in order, then the part in HBM
+        assert mr.aggregate() == len(allkeys)                       # one rank: nothing moves, nothing comes back
+        nu = mr.convert()
+        ks = mr.kmv_stats()
+        assert ks.npair == nu and ks.nvalue == len(allkeys) and ks.exactsize == 12 * nu + 4 * len(allkeys) + 4 * nu + 4 * len(allkeys)
+        kmv = mr.scan_kmv()
+        assert mr.reduce("count") == nu
+        res[budget] = (nu, H.canon_kmv(kmv), H.canon_kv(mr.scan_kv()))
+    assert res[1] == res[0]
+    want = H.kv_decode(oracle.reduce(oracle.convert(oracle.intcount_map(allkeys)), "count"))
+    assert res[1][2] == H.canon_kv(want)
+
+
+def test_out_of_core_keeps_value_arrival_order(MR, oracle):
+    """variable-length keys and values added in batches that spill: every key's values stay in arrival order across
+    pieces and sets (the reference's KMV value order), cull takes the first one"""
+    r = np.random.RandomState(32)
+    vocab = [bytes(r.randint(97, 123, size=r.randint(1, 12)).astype(np.uint8)) for _ in range(700)]
+    batches = [[(vocab[r.randint(len(vocab))], b"v%d" % (1000 * b + i)) for i in range(20_000)] for b in range(4)]
+    flat = [rec for b in batches for rec in b]
+    mr = MR(memsize=-(256 << 10), outofcore=1)                      # the reference's switch: one 256 KiB page stays in memory
+    for i, b in enumerate(batches):
+        mr.kv_add(b, addflag=1 if i else 0)
+    assert mr.kv_stats().npair == len(flat) and mr.kv_stats().npage > 4
+    want = H.kmv_decode(oracle.convert(H.kv_encode(flat)))
+    assert mr.convert() == len(want)
+    assert H.canon_kmv(mr.scan_kmv()) == H.canon_kmv(want)          # value order inside a key is compared as is
+    mr.reduce("cull")
+    assert H.canon_kv(mr.scan_kv()) == H.canon_kv(H.kv_decode(oracle.reduce(oracle.convert(H.kv_encode(flat)), "cull")))
+
+
+def test_out_of_core_store_comes_back_for_other_ops(MR, oracle):
+    r = np.random.RandomState(33)
+    parts = [r.randint(0, 1 << 20, size=150_000).astype(np.uint32) for _ in range(3)]
+    mr, other = MR(hbm_budget=1), MR()
+    for i, p in enumerate(parts):
+        mr.map_intcount(p, addflag=1 if i else 0)
+    allkeys = np.concatenate(parts)
+    assert mr.sort_keys(1) == len(allkeys)                          # needs the whole KV in HBM: it is brought back
+    got = np.array([struct.unpack("<I", k)[0] for k, _ in mr.scan_kv()], dtype=np.uint32)
+    assert np.array_equal(got, np.sort(allkeys, kind="stable"))
+    other.kv_add([(b"x", b"y")])
+    assert other.add(mr) == len(allkeys) + 1
+
+
 # ------------------------------------------------------------------------------------------- scale properties
 
 def test_intcount_16M_properties(MR):
