@@ -355,6 +355,32 @@ def multirank_cases(MapReduce, local, rank, world, uid, stream):
     return ncase
 
 
+def bind_near_gpu(local: int):
+    """Run this rank on the CPU cores next to its GPU (NVML's ideal affinity), so that the pinned host buffers it
+    allocates afterwards are on that socket's memory: at 8 ranks the end-to-end path is eight concurrent 4 GiB DMAs,
+    and buffers on the far socket cross the inter-socket link.  Host placement only; returns what it did."""
+    try:
+        import pynvml as nv
+        import torch
+
+        nv.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(local).uuid)
+            h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            h = nv.nvmlDeviceGetHandleByIndex(local)
+        ncpu = os.cpu_count() or 1
+        words = nv.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return f"{len(cpus)} cores near GPU {local}"
+    except Exception as ex:  # placement is an optimisation, never a requirement
+        return f"not bound ({type(ex).__name__})"
+    return "not bound"
+
+
 # ------------------------------------------------------------------------------------------ CUDA arm
 
 def main():
@@ -389,6 +415,8 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU path)"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    all_cpus = os.sched_getaffinity(0)
+    host_binding = bind_near_gpu(local)
     uid = None
     if world > 1:
         import torch.distributed as dist
@@ -595,7 +623,7 @@ def main():
         e2e_step()
         ems = timed(args.steps, e2e_step)
         e2e = {"value": world * n * args.steps / (ems / 1e3), "unit": UNIT, "h2d_bytes_per_step": 4 * n, "d2h_bytes_per_step": int(res_bytes),
-               "ms_per_step": ems / args.steps}
+               "ms_per_step": ems / args.steps, "host_placement": host_binding}
         checks.append(parity(mr, "end-to-end (host keys in, result pages out), last timed step"))
         del hkeys, pinned_out
     mr.destroy()
@@ -629,6 +657,7 @@ def main():
         mr2.destroy()
         del mr2
 
+    os.sched_setaffinity(0, all_cpus)  # the CPU baseline below uses every host core
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
