@@ -22,8 +22,8 @@
 // a factored KMV with variable-length keys (DevKMV::fvar): key bytes once, a count per key.  Included by mrgpu.cu.
 #pragma once
 
-constexpr int HG_THREADS = 512;
-constexpr uint32_t HG_SLOTS = 4096;             // per block: 4096 x (8 + 4 + 4) bytes = 64 KB, three blocks per SM
+constexpr int HG_THREADS = 768;
+constexpr uint32_t HG_SLOTS = 2560;             // per block: 2560 x (16 + 8 + 4 + 4 + 4) bytes = 90 KB, two blocks per SM
 constexpr uint32_t HG_PROBES = 8;
 constexpr uint32_t HG_GLOBAL_LOG2 = 21;         // 2^21 entries x 16 bytes = 32 MB: stays in the 126 MB L2
 constexpr uint32_t HG_GLOBAL_PROBES = 64;
@@ -82,13 +82,23 @@ __device__ __forceinline__ void hg_global_add(HgEntry *__restrict__ g, uint32_t 
   atomicOr(flags, 1ull);
 }
 
+// Keys of up to 16 bytes -- nearly every word of a text -- are kept INSIDE the block's table entry next to the
+// fingerprint, so a hit is decided by comparing four words in shared memory.  (The first version verified every hit
+// against the representative record in global memory: ncu counted 12 GB of L1 misses per 31 M words and 15.6 of 23
+// stall cycles per issue on the long scoreboard.)  Longer keys still verify against the representative.
+// Entry life cycle: fp 0 -> claimed by a 64-bit CAS on fp -> the owner writes key words and rep, fences, publishes
+// len (kb + 1; bit 31 set for keys that are not inline).  A reader that finds its fingerprint but no published length
+// yet (the owner is a few instructions behind, possibly in the same warp) does not wait: it sends its pair to the
+// global table, which is always correct.
 __global__ void __launch_bounds__(HG_THREADS)
 hash_group_kernel(HgRecs r, uint64_t n, uint32_t seed, HgEntry *__restrict__ g, uint32_t gmask, unsigned long long *flags)
 {
   extern __shared__ __align__(16) unsigned char hg_sm[];
-  unsigned long long *s_fp = (unsigned long long *) hg_sm;
+  uint4 *s_w = (uint4 *) hg_sm;                                              // inline key words
+  unsigned long long *s_fp = (unsigned long long *) (s_w + HG_SLOTS);
   unsigned *s_cnt = (unsigned *) (s_fp + HG_SLOTS), *s_rep = s_cnt + HG_SLOTS;
-  for (uint32_t i = threadIdx.x; i < HG_SLOTS; i += blockDim.x) s_fp[i] = 0, s_cnt[i] = 0, s_rep[i] = HG_UNSET;
+  volatile unsigned *s_len = s_rep + HG_SLOTS;
+  for (uint32_t i = threadIdx.x; i < HG_SLOTS; i += blockDim.x) s_fp[i] = 0, s_cnt[i] = 0, s_rep[i] = HG_UNSET, s_len[i] = 0;
   __syncthreads();
   const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
   // every lane of a warp makes the same number of trips and the warp is brought back together at the top of each:
@@ -102,19 +112,54 @@ hash_group_kernel(HgRecs r, uint64_t n, uint32_t seed, HgEntry *__restrict__ g, 
       const uint8_t *k = hg_key(r, i, kb);
       unsigned long long fp = key_fingerprint(k, kb, seed);
       if (fp == 0) fp = 1;
-      uint32_t slot = (uint32_t) (fp ^ (fp >> 37)) & (HG_SLOTS - 1);
-      bool done = false;
+      // the key as four words, bytes past its end zeroed (only meaningful when it fits: kb <= 16 and word aligned)
+      const bool inl = kb <= 16 && ((((uintptr_t) k) & 3) == 0);
+      uint4 kw = make_uint4(0, 0, 0, 0);
+      if (inl) {
+        const uint32_t *w = (const uint32_t *) k;
+        const uint32_t nw = (kb + 3) >> 2, tail = kb & 3u, m = tail ? (0xFFFFFFFFu >> (32 - 8 * tail)) : 0xFFFFFFFFu;
+        if (nw > 0) kw.x = w[0] & (nw == 1 ? m : 0xFFFFFFFFu);
+        if (nw > 1) kw.y = w[1] & (nw == 2 ? m : 0xFFFFFFFFu);
+        if (nw > 2) kw.z = w[2] & (nw == 3 ? m : 0xFFFFFFFFu);
+        if (nw > 3) kw.w = w[3] & m;
+      }
+      const uint32_t mylen = (kb + 1) | (inl ? 0u : 0x80000000u);
+      uint32_t slot = __umulhi((uint32_t) (fp ^ (fp >> 29)), HG_SLOTS);
+      bool done = false, to_global = false;
 #pragma unroll 1
-      for (uint32_t p = 0; p < HG_PROBES && !done; p++) {
+      for (uint32_t p = 0; p < HG_PROBES && !done && !to_global; p++) {
         unsigned long long cur = s_fp[slot];
-        if (cur == 0) cur = atomicCAS(&s_fp[slot], 0ull, fp);
-        if (cur == 0 || cur == fp) {
-          atomicAdd(&s_cnt[slot], 1u);
-          const unsigned old = atomicMin(&s_rep[slot], (unsigned) i);
-          if (old != HG_UNSET && old != (unsigned) i && !hg_same_key(r, (uint32_t) i, old)) atomicOr(flags, 2ull);
-          done = true;
-        } else
-          slot = (slot + 1) & (HG_SLOTS - 1);
+        if (cur == 0) {
+          cur = atomicCAS(&s_fp[slot], 0ull, fp);
+          if (cur == 0) {  // mine: fill in, then publish
+            s_w[slot] = kw;
+            s_rep[slot] = (unsigned) i;
+            atomicAdd(&s_cnt[slot], 1u);
+            __threadfence_block();
+            s_len[slot] = mylen;
+            done = true;
+            break;
+          }
+        }
+        if (cur == fp) {
+          const uint32_t len = s_len[slot];
+          __threadfence_block();  // the key words and rep below were written before len was published
+          if (len == 0) to_global = true;  // claimed but not yet published
+          else if (len != mylen) atomicOr(flags, 2ull), done = true;  // same fingerprint, another key
+          else if (inl) {
+            const uint4 e = s_w[slot];
+            if (e.x == kw.x && e.y == kw.y && e.z == kw.z && e.w == kw.w) atomicAdd(&s_cnt[slot], 1u);
+            else atomicOr(flags, 2ull);
+            done = true;
+          } else {
+            atomicAdd(&s_cnt[slot], 1u);
+            if (!hg_same_key(r, (uint32_t) i, s_rep[slot])) atomicOr(flags, 2ull);
+            done = true;
+          }
+        } else {
+          slot++;
+          if (slot == HG_SLOTS) slot = 0;
+        }
       }
       if (!done) hg_global_add(g, gmask, fp, 1u, (unsigned) i, r, flags);  // the block's table is taken by more frequent keys
     }
@@ -197,7 +242,7 @@ static bool convert_hash(mrgpu_mr *mr)
   HgRecs r{kv->data, kv->uniform ? nullptr : kv->offs, kv->recsize, al};
   // empty table: fp 0, count 0, rep UNSET (0xFFFFFFFF): two fills
   static std::atomic<bool> attr[64];
-  const size_t smem = (size_t) HG_SLOTS * 16;
+  const size_t smem = (size_t) HG_SLOTS * 36;
   if (mr->device < 64 && !attr[mr->device].load()) {
     MR_CUDA(cudaFuncSetAttribute(hash_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     attr[mr->device].store(true);
@@ -211,7 +256,7 @@ static bool convert_hash(mrgpu_mr *mr)
   MR_CUDA(cudaMemsetAsync(flags, 0, 8, s));
   {
     ProfScope ps(pool, "convert_hash_group", (double) kv->nbytes + (kv->uniform ? 0.0 : 8.0 * n));
-    hash_group_kernel<<<kSMs * 3, HG_THREADS, smem, s>>>(r, n, 0u, g, gslots - 1, flags);
+    hash_group_kernel<<<kSMs * 2, HG_THREADS, smem, s>>>(r, n, 0u, g, gslots - 1, flags);
     MR_CUDA(cudaGetLastError());
   }
   // non-empty entries -> (fingerprint, count, rep) arrays
