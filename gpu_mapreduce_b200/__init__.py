@@ -77,6 +77,7 @@ def lib():
                            C.c_int, u64p],
         "mrgpu_map_mr": [vp, vp, C.c_int, C.c_int, u64p],
         "mrgpu_add": [vp, vp, u64p],
+        "mrgpu_copy": [vp, vp],
         "mrgpu_aggregate": [vp, u64p],
         "mrgpu_aggregate_dest": [vp, vp, C.c_uint64, u64p],
         "mrgpu_scan_kv": [vp, SCAN_KV_FN, vp, u64p],
@@ -275,6 +276,12 @@ class MapReduce:
     # -- the hot path
     def add(self, other: "MapReduce"):
         return self._count(lib().mrgpu_add, other._h)
+
+    def copy(self):
+        """copy() src/mapreduce.cpp:290: a new object with the same settings and a deep copy of the KV / KMV"""
+        m = MapReduce(device=self.device)
+        m._ck(lib().mrgpu_copy(m._h, self._h))
+        return m
 
     def aggregate(self, hash=None):
         """aggregate(myhash) src/mapreduce.cpp:385.  hash = None: the default hashlittle partition, on the GPU.  A callable

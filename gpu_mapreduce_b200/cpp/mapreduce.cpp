@@ -758,15 +758,130 @@ uint64_t MapReduce::map(int nstr, char **strings, int self, int recurse, int rea
   return n;
 }
 
-uint64_t MapReduce::map(int, int, char **, int, int, char, int, void (*)(int, char *, int, KeyValue *, void *), void *, int)
+// map(nmap, nstr, strings, recurse, readflag, sepchar | sepstr, delta, mymap, ptr, addflag): the files are cut into
+// nmap chunks at separators and mymap(itask, str, size, kv, ptr) sees one chunk (src/mapreduce.cpp:1232-1536).  The
+// rules that decide what a task sees are the reference's: tasks per file proportional to file size (at least one,
+// adjusted until they sum to nmap, reduced where a chunk would not exceed delta); task j of n of a file reads bytes
+// [j*size/n, (j+1)*size/n + delta); a task that is not the file's first starts after (char) / at (string) the first
+// separator found within delta; one that is not the last ends after (char) / before (string) the first separator at
+// or beyond its nominal end.  The chunk is NUL terminated and size counts the NUL.
+uint64_t MapReduce::map_chunks(int nmap, int nstr, char **strings, int recurse, int readflag, int sepwhich, char sepchar, const char *sepstr,
+                               int delta, void (*appmap)(int, char *, int, KeyValue *, void *), void *ptr, int addflag)
 {
-  all("map() of file chunks is not built in the GPU library (SURVEY.md 8f)");
-  return 0;
+  push_settings();
+  start_timer();
+  std::vector<std::string> files;
+  for (int i = 0; i < nstr; i++) {
+    if (readflag) {
+      FILE *fp = fopen(strings[i], "r");
+      if (!fp) one("Could not open file of file names");
+      char line[4096];
+      while (fgets(line, sizeof(line), fp)) {
+        char *w = strtok(line, " \t\n\f\r");
+        if (w) list_files(w, recurse, files);
+      }
+      fclose(fp);
+    } else
+      list_files(strings[i], recurse, files);
+  }
+  const int nfile = (int) files.size();
+  mapfilecount = nfile;
+  if (nfile > nmap) nmap = nfile;
+  std::vector<uint64_t> fsize(nfile);
+  uint64_t ntotal = 0;
+  for (int i = 0; i < nfile; i++) {
+    struct stat st;
+    if (stat(files[i].c_str(), &st) < 0) one("Could not query file size");
+    fsize[i] = (uint64_t) st.st_size;
+    ntotal += fsize[i];
+  }
+  const uint64_t nideal = std::max<uint64_t>(1, nmap ? ntotal / nmap : 1);
+  std::vector<int> per(nfile);
+  int ntasks = 0;
+  for (int i = 0; i < nfile; i++) {
+    per[i] = (int) std::max<uint64_t>(1, fsize[i] / nideal);
+    ntasks += per[i];
+  }
+  while (ntasks < nmap) {
+    const int before = ntasks;
+    for (int i = 0; i < nfile && ntasks < nmap; i++)
+      if (fsize[i] > nideal) per[i]++, ntasks++;
+    if (ntasks == before) break;  // no file is big enough to take another task
+  }
+  while (ntasks > nmap) {
+    const int before = ntasks;
+    for (int i = 0; i < nfile && ntasks > nmap; i++)
+      if (per[i] > 1) per[i]--, ntasks--;
+    if (ntasks == before) break;
+  }
+  nmap = ntasks;
+  bool shrunk = false;
+  for (int i = 0; i < nfile; i++) {
+    if (fsize[i] / per[i] > (uint64_t) delta) continue;
+    shrunk = true;
+    while (per[i] > 1) {
+      per[i]--;
+      nmap--;
+      if (fsize[i] / per[i] > (uint64_t) delta) break;
+    }
+  }
+  if (shrunk && me == 0) printf("WARNING: File(s) too small for file delta - decreased map tasks to %d\n", nmap);
+  std::vector<int> whichfile, whichtask;
+  for (int i = 0; i < nfile; i++)
+    for (int j = 0; j < per[i]; j++) whichfile.push_back(i), whichtask.push_back(j);
+
+  KeyValue *out = begin_emit(gpu, addflag);
+  std::vector<int> tasks;
+  my_tasks(nmap, me, nprocs, mapstyle, tasks);
+  std::vector<char> str;
+  for (size_t t = 0; t < tasks.size(); t++) {
+    const int imap = tasks[t], f = whichfile[imap], itask = whichtask[imap], ntask = per[f];
+    const uint64_t filesize = fsize[f];
+    const uint64_t readstart = (uint64_t) itask * filesize / ntask, readnext = (uint64_t) (itask + 1) * filesize / ntask;
+    if (readnext - readstart + delta + 1 > 0x7FFFFFFFull) one("Single file read exceeds int size");
+    uint64_t readsize = std::min<uint64_t>(readnext - readstart + delta, filesize - readstart);
+    str.assign(readsize + 1, 0);
+    FILE *fp = fopen(files[f].c_str(), "rb");
+    if (!fp) one("Could not open map file");
+    fseek(fp, (long) readstart, SEEK_SET);
+    const size_t got = fread(str.data(), 1, readsize, fp);
+    fclose(fp);
+    str[got] = 0;
+    size_t strstart = 0;
+    if (itask > 0) {
+      char *p = sepwhich ? strchr(str.data(), sepchar) : strstr(str.data(), sepstr);
+      if (p == NULL || p - str.data() > delta) one("Could not find file separator within delta");
+      strstart = (size_t) (p - str.data()) + (sepwhich ? 1 : 0);
+    }
+    size_t strstop = readsize;
+    if (itask < ntask - 1) {
+      char *from = &str[readnext - readstart];
+      char *p = sepwhich ? strchr(from, sepchar) : strstr(from, sepstr);
+      if (p == NULL) one("Could not find file separator within delta");
+      if (sepwhich) p++;
+      *p = 0;
+      strstop = (size_t) (p - str.data());
+    }
+    appmap(imap, &str[strstart], (int) (strstop - strstart + 1), out, ptr);
+  }
+  uint64_t n = end_emit(gpu, out);
+  delete kv;
+  kv = new KeyValue(gpu);
+  kmv = NULL;
+  sync_kv_fields();
+  stats("Map", 0);
+  return n;
 }
-uint64_t MapReduce::map(int, int, char **, int, int, char *, int, void (*)(int, char *, int, KeyValue *, void *), void *, int)
+
+uint64_t MapReduce::map(int nmap, int nstr, char **strings, int recurse, int readflag, char sepchar, int delta,
+                        void (*appmap)(int, char *, int, KeyValue *, void *), void *ptr, int addflag)
 {
-  all("map() of file chunks is not built in the GPU library (SURVEY.md 8f)");
-  return 0;
+  return map_chunks(nmap, nstr, strings, recurse, readflag, 1, sepchar, NULL, delta, appmap, ptr, addflag);
+}
+uint64_t MapReduce::map(int nmap, int nstr, char **strings, int recurse, int readflag, char *sepstr, int delta,
+                        void (*appmap)(int, char *, int, KeyValue *, void *), void *ptr, int addflag)
+{
+  return map_chunks(nmap, nstr, strings, recurse, readflag, 0, 0, sepstr, delta, appmap, ptr, addflag);
 }
 
 // map(mr2, mymap, ptr, addflag): src/mapreduce.cpp:1560-1642
@@ -1066,16 +1181,95 @@ uint64_t MapReduce::sort_values(int flag)
   return n;
 }
 
-uint64_t MapReduce::sort_multivalues(int)
+// sort_multivalues(): the values of every KMV pair sorted among themselves (src/mapreduce.cpp:2189-2350).  The compare
+// is host code (a function pointer, or one of the flag functions below), so the pairs come to the host page by
+// page; each pair's values are sorted and go back as (key, value) pairs in sorted order, and convert() -- a STABLE
+// group-by: values keep their arrival order -- rebuilds the KMV.  Pairs bigger than a page arrive block by block.
+static int cmp_flag(int flag, const char *a, int alen, const char *b, int blen)
 {
-  all("sort_multivalues() is not built in the GPU library (SURVEY.md 8f)");
-  return 0;
+  const int f = flag < 0 ? -flag : flag;
+  int r = 0;
+  if (f == 1) {
+    int x, y;
+    memcpy(&x, a, 4), memcpy(&y, b, 4);
+    r = x < y ? -1 : (x > y ? 1 : 0);
+  } else if (f == 2) {
+    uint64_t x, y;
+    memcpy(&x, a, 8), memcpy(&y, b, 8);
+    r = x < y ? -1 : (x > y ? 1 : 0);
+  } else if (f == 3) {
+    float x, y;
+    memcpy(&x, a, 4), memcpy(&y, b, 4);
+    r = x < y ? -1 : (x > y ? 1 : 0);
+  } else if (f == 4) {
+    double x, y;
+    memcpy(&x, a, 8), memcpy(&y, b, 8);
+    r = x < y ? -1 : (x > y ? 1 : 0);
+  } else if (f == 5) r = strcmp(a, b);
+  else r = strncmp(a, b, alen < blen ? alen : blen);
+  return flag < 0 ? -r : r;
 }
-uint64_t MapReduce::sort_multivalues(int (*)(char *, int, char *, int))
+
+uint64_t MapReduce::sort_multivalues_impl(int flag, int (*appcompare)(char *, int, char *, int))
 {
-  all("sort_multivalues() is not built in the GPU library (SURVEY.md 8f)");
-  return 0;
+  if (kmv == NULL) all("Cannot sort_multivalues without KeyMultiValue");
+  if (!appcompare && (flag == 0 || flag > 6 || flag < -6)) all("Invalid compare method for sort multivalues");
+  start_timer();
+  mrgpu_mr *side = make_side_handle(this, memsize, keyalign, valuealign);
+  if (!side) all(mrgpu_last_error(NULL));
+  KeyValue *out = begin_emit(side, 0);
+  struct Val {
+    const char *p;
+    int len;
+  };
+  std::vector<Val> vals;
+  std::vector<char> pool;
+  walk_kmv(gpu, [&](char *k, int kb, char *mv, int nv, int *sizes) {
+    vals.clear();
+    pool.clear();
+    if (mv) {
+      for (int i = 0; i < nv; i++) {
+        vals.push_back(Val{mv, sizes[i]});
+        mv += sizes[i];
+      }
+    } else {  // a pair bigger than a page: gather its blocks (pointers die with each block, so the bytes are copied)
+      int nblock;
+      multivalue_blocks(nblock);
+      std::vector<std::pair<size_t, int> > where;
+      for (int b = 0; b < nblock; b++) {
+        char *bm;
+        int *bs;
+        const int n = multivalue_block(b, &bm, &bs);
+        for (int i = 0; i < n; i++) {
+          where.push_back(std::make_pair(pool.size(), bs[i]));
+          pool.insert(pool.end(), bm, bm + bs[i]);
+          pool.push_back(0);
+          bm += bs[i];
+        }
+      }
+      for (size_t i = 0; i < where.size(); i++) vals.push_back(Val{&pool[where[i].first], where[i].second});
+    }
+    std::stable_sort(vals.begin(), vals.end(), [&](const Val &x, const Val &y) {
+      return appcompare ? appcompare((char *) x.p, x.len, (char *) y.p, y.len) < 0 : cmp_flag(flag, x.p, x.len, y.p, y.len) < 0;
+    });
+    for (size_t i = 0; i < vals.size(); i++) out->add(k, kb, (char *) vals[i].p, vals[i].len);
+  });
+  end_emit(side, out);
+  uint64_t n = 0;
+  ck(mrgpu_kv_open(gpu, 0), 0);  // drops the KMV
+  ck(mrgpu_kv_close(gpu, &n), 0);
+  ck(mrgpu_add(gpu, side, &n), 0);
+  mrgpu_destroy(side);
+  ck(mrgpu_convert(gpu, &n), 0);
+  delete kv;
+  kv = NULL;
+  kmv = &g_kmv_marker;
+  stats("Sort_multivalues", 1);
+  return n;
 }
+
+uint64_t MapReduce::sort_multivalues(int flag) { return sort_multivalues_impl(flag, NULL); }
+uint64_t MapReduce::sort_multivalues(int (*appcompare)(char *, int, char *, int)) { return sort_multivalues_impl(0, appcompare); }
 
 // ---------------------------------------------------------------------------------------------- the rest
 
@@ -1104,8 +1298,17 @@ MapReduce *MapReduce::copy()
   m->maxpage = maxpage;
   m->keyalign = keyalign;
   m->valuealign = valuealign;
-  if (kmv) all("copy() of a MapReduce holding KeyMultiValue pairs is not built in the GPU library");
-  if (kv) m->add(this);
+  m->outofcore = outofcore;
+  push_settings();
+  m->push_settings();
+  if (kv || kmv) {  // deep copy of whichever store this object holds (src/mapreduce.cpp:314-338)
+    ck(mrgpu_copy(m->gpu, gpu), 0);
+    if (kv) {
+      m->kv = new KeyValue(m->gpu);
+      m->sync_kv_fields();
+    } else
+      m->kmv = &g_kmv_marker;
+  }
   return m;
 }
 

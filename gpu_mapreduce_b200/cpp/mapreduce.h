@@ -13,9 +13,8 @@
  *   map / reduce / compress / scan / sort_*(compare fn) with any other function ptr  the callback runs on the
  *     host, one page at a time, exactly as in the reference; pages are staged D2H, emitted pairs H2D
  *
- * Not built (out of this round's scope): sort_multivalues, the two file-chunk map() variants.
- * They fail with
- * the reference's error convention instead of silently doing something else. */
+ * sort_multivalues and the two file-chunk map() variants are host code over staged pages / files, like any other
+ * host callback. */
 #ifndef MAP_REDUCE_H
 #define MAP_REDUCE_H
 
@@ -158,6 +157,9 @@ class MapReduce {
   template <typename F> void walk_kmv(mrgpu_mr *h, F f);
   void print_pairs(FILE *fp, int nstride, int kflag, int vflag);
   uint64_t host_sort(int (*)(char *, int, char *, int), int by_value);
+  uint64_t sort_multivalues_impl(int flag, int (*)(char *, int, char *, int));
+  uint64_t map_chunks(int nmap, int nstr, char **strings, int recurse, int readflag, int sepwhich, char sepchar, const char *sepstr, int delta,
+                      void (*)(int, char *, int, class KeyValue *, void *), void *, int addflag);
   uint64_t reduce_impl(void (*)(char *, int, char *, int, int *, class KeyValue *, void *), void *, const char *heading);
 };
 

@@ -464,3 +464,52 @@ static void reduce_spooled(mrgpu_mr *mr, int functor)
   mr->spool_kmv_pairs = 0;
   mr->kv = acc;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// MapReduce::copy() src/mapreduce.cpp:290-340: a second object with the same settings and a deep copy of the KV or KMV
+
+extern "C" int mrgpu_copy(mrgpu_mr *mr, mrgpu_mr *src)
+{
+  API_BEGIN(mr)
+  if (!src || src == mr) MR_FAIL(MRGPU_EINVAL, "copy needs another MapReduce");
+  if (src->device != mr->device) MR_FAIL(MRGPU_EINVAL, "copy: the two MapReduce objects live on different devices");
+  freeze(src);
+  if (!mr->frozen) {  // settings travel with the copy (src/mapreduce.cpp:296-312)
+    mr->memsize = src->memsize, mr->keyalign = src->keyalign, mr->valuealign = src->valuealign;
+    mr->mapstyle = src->mapstyle, mr->all2all = src->all2all, mr->verbosity = src->verbosity, mr->timer = src->timer;
+    mr->minpage = src->minpage, mr->maxpage = src->maxpage, mr->outofcore = src->outofcore, mr->hbm_budget = src->hbm_budget;
+  }
+  freeze(mr);
+  if (mr->al.k != src->al.k || mr->al.v != src->al.v) MR_FAIL(MRGPU_EINVAL, "copy: alignments differ");
+  mr->g_what = G_NONE;
+  delete mr->kv;
+  delete mr->kmv;
+  mr->kv = nullptr, mr->kmv = nullptr;
+  spool_clear_kv(mr);
+  spool_clear_kmv(mr);
+  spool_make_resident(src);
+  cudaStream_t s = mr->pool.stream;
+  if (src->kv) {
+    kv_unpack(src, src->kv);
+    order_after(mr, src);
+    mr->kv = new DevKV(&mr->pool);
+    kv_concat(mr, mr->kv, src->kv);
+  }
+  if (src->kmv) {
+    DevKMV *k = src->kmv;
+    kmv_expand(src, k);
+    order_after(mr, src);
+    DevKMV *c = new DevKMV(&mr->pool);
+    mr->kmv = c;
+    c->data = (uint8_t *) mr->pool.alloc(k->nbytes ? k->nbytes : 16);
+    c->cap = k->nbytes ? k->nbytes : 16;
+    c->offs = (uint64_t *) mr->pool.alloc((k->nkmv + 1) * 8);
+    c->offs_cap = k->nkmv + 1;
+    if (k->nbytes) MR_CUDA(cudaMemcpyAsync(c->data, k->data, k->nbytes, cudaMemcpyDeviceToDevice, s));
+    MR_CUDA(cudaMemcpyAsync(c->offs, k->offs, (k->nkmv + 1) * 8, cudaMemcpyDeviceToDevice, s));
+    c->nkmv = k->nkmv, c->nvalue = k->nvalue, c->ksize = k->ksize, c->vsize = k->vsize, c->nbytes = k->nbytes;
+    c->ukb = k->ukb, c->uvb = k->uvb;
+  }
+  sync(mr);
+  API_END(mr)
+}

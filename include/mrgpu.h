@@ -180,6 +180,9 @@ int mrgpu_map_mr(mrgpu_mr *dst, mrgpu_mr *src, int functor, int addflag, uint64_
 
 /* MapReduce::add(MapReduce *) src/mapreduce.cpp:348-374 */
 int mrgpu_add(mrgpu_mr *mr, mrgpu_mr *other, uint64_t *nkv);
+/* MapReduce::copy() src/mapreduce.cpp:290-340: `mr` (freshly created) takes src's settings and a deep copy of its
+ * KeyValue or KeyMultiValue */
+int mrgpu_copy(mrgpu_mr *mr, mrgpu_mr *src);
 /* MapReduce::aggregate(NULL) src/mapreduce.cpp:385-563 + Irregular src/irregular.cpp:95-301: pairs move to
  * rank hashlittle(key,keybytes,nprocs) % nprocs; arrival order = (source rank, original order). */
 int mrgpu_aggregate(mrgpu_mr *mr, uint64_t *nkv);

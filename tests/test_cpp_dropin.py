@@ -51,7 +51,17 @@ def test_same_caller_same_output_on_both_libraries():
     ref = _run(os.path.join(REF, "dropin_ref")).stdout
     gpu = _run(os.path.join(BIN, "dropin_gpu")).stdout
     assert len(ref.splitlines()) > 900
-    assert gpu == ref
+    common, _, extra = gpu.partition("== GPU-only from here\n")
+    assert common == ref
+    # sort_multivalues (the reference's is broken, see the program): every key's values ascending / descending, and the
+    # same values as in the unsorted KMV of section 6
+    sections = re.split(r"^== (.*) \(\d+\)\n", extra, flags=re.M)
+    got = {sections[i]: sections[i + 1].splitlines() for i in range(1, len(sections), 2)}
+    orig = re.split(r"^== copied kmv \(\d+\)\n", common, flags=re.M)[1].splitlines()[:300]
+    want = {ln.split(":")[0]: sorted(int(x) for x in ln.split(":")[1].split()) for ln in orig}
+    asc = {ln.split(":")[0]: [int(x) for x in ln.split(":")[1].split()] for ln in got["sort_multivalues(1)"]}
+    desc = {ln.split(":")[0]: [int(x) for x in ln.split(":")[1].split()] for ln in got["sort_multivalues(descending compare)"]}
+    assert len(want) == 300 and asc == want and desc == {k: v[::-1] for k, v in want.items()}
 
 
 @pytest.mark.gpu
