@@ -155,6 +155,13 @@ static void chunk_words(int itask, char *str, int size, KeyValue *kv, void *ptr)
   }
 }
 
+// reduce for value-less pairs: (key, {nvalues, 0})
+static void countonly(char *key, int keybytes, char *, int nvalues, int *, KeyValue *kv, void *)
+{
+  int64_t out[2] = {nvalues, 0};
+  kv->add(key, keybytes, (char *) out, sizeof(out));
+}
+
 static int int_desc(char *p1, int, char *p2, int)
 {
   int a, b;
@@ -252,7 +259,7 @@ int main(int narg, char **args)
     MapReduce *mc = new MapReduce(MPI_COMM_WORLD);
     uint64_t nw = variant == 0 ? mc->map(7, 1, fnames, 0, 0, '\n', 80, chunk_words, NULL) : mc->map(5, 1, fnames, 0, 0, sepstr, 80, chunk_words, NULL);
     uint64_t nu = mc->collate(NULL);
-    mc->reduce(sumvals, mc);
+    mc->reduce(countonly, NULL);
     mc->sort_keys(5);
     printf("file chunks variant %d: words %lu unique %lu\n", variant, (unsigned long) nw, (unsigned long) nu);
     mc->scan(collect_str, NULL);
