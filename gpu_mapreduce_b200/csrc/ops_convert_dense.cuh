@@ -76,6 +76,24 @@ __device__ __forceinline__ void dense_count4(const uint32_t (&key)[4], unsigned 
   uint32_t slot[4], tag[4], e[4];
 #pragma unroll
   for (int q = 0; q < 4; q++) dense_slot(key[q], slot[q], tag[q]);
+#if MRGPU_DENSE_EXPERIMENT == 4
+  // A/B variant (measured: 2.74 ms against 2.61 for the fused pass, 2.262 against 2.261 for the count alone, so not
+  // the default): one RETURNING shared atomic per key instead of a load plus an atomic.  The add is speculative: the
+  // value it returns carries the slot's tag; a key that finds another key's tag takes its add back and goes to the
+  // table, one that finds the slot empty tries to stamp its tag on exactly its own count.
+#pragma unroll
+  for (int q = 0; q < 4; q++) e[q] = (valid_mask >> q & 1) ? atomicAdd(&cache[slot[q]], 0x1000u) : 0u;
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    if (!(valid_mask >> q & 1)) continue;
+    const uint32_t t = e[q] & 0xFFFu;
+    if (t == tag[q]) continue;  // hit: already counted
+    if (t == 0 && atomicCAS(&cache[slot[q]], e[q] + 0x1000u, (e[q] + 0x1000u) | tag[q]) == e[q] + 0x1000u) continue;  // claimed with my 1
+    atomicSub(&cache[slot[q]], 0x1000u);
+    atomicAdd(&table[key[q]], 1u);
+  }
+  return;
+#endif
 #pragma unroll
   for (int q = 0; q < 4; q++) e[q] = cache[slot[q]];
 #pragma unroll
