@@ -9,7 +9,9 @@
 #include <string.h>
 #include <stdlib.h>
 #include <map>
+#include <mutex>
 #include <set>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -101,10 +103,35 @@ struct Pool {
   std::vector<std::pair<uint8_t *, uint64_t>> chunks;
   static constexpr uint64_t kGran = 512;
 
+  // Every handle has its own pool, and a pool keeps what it once obtained (that is the point of it).  When one
+  // pool's cudaMalloc fails, the memory is often sitting idle in ANOTHER handle's cache (R-MAT's edge handle holds
+  // 100 GB of freed sort scratch while the degree handle asks for its first 34 GB): the pools of this host thread
+  // on this device are asked to give their wholly-free chunks back before the allocation is declared failed.
+  // (Only this thread's: a handle is not thread-safe, and another thread may be inside its own pool.)
+  std::thread::id owner;
+  static std::mutex &registry_mu()
+  {
+    static std::mutex m;
+    return m;
+  }
+  static std::set<Pool *> &registry()
+  {
+    static std::set<Pool *> r;
+    return r;
+  }
   void init(int dev, cudaStream_t s)
   {
     device = dev;
     stream = s;
+    owner = std::this_thread::get_id();
+    std::lock_guard<std::mutex> lk(registry_mu());
+    registry().insert(this);
+  }
+  void trim_siblings()
+  {
+    std::lock_guard<std::mutex> lk(registry_mu());
+    for (Pool *p : registry())
+      if (p != this && p->device == device && p->owner == owner) p->trim();
   }
   void erase_free(std::map<uint8_t *, Block>::iterator it)
   {
@@ -157,6 +184,11 @@ struct Pool {
       if (e != cudaSuccess) {
         cudaGetLastError();
         trim();
+        e = cudaMalloc(&q, csize);
+      }
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        trim_siblings();
         e = cudaMalloc(&q, csize);
       }
       if (e != cudaSuccess) {
@@ -217,6 +249,10 @@ struct Pool {
   }
   ~Pool()
   {
+    {
+      std::lock_guard<std::mutex> lk(registry_mu());
+      registry().erase(this);
+    }
     if (chunks.empty()) return;
     cudaStreamSynchronize(stream);
     for (size_t c = 0; c < chunks.size(); c++)

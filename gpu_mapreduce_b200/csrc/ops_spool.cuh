@@ -419,6 +419,10 @@ static void convert_spooled(mrgpu_mr *mr)
         host_free(sl.data);
         host_free(sl.sizes);
       }
+    spool_clear_kv(mr);   // pieces already consumed are gone: the handle is left without a KeyValue rather than with half of one
+    spool_clear_kmv(mr);
+    delete mr->kv;
+    mr->kv = nullptr;
     throw;
   }
   delete mr->kv;
@@ -458,6 +462,7 @@ static void reduce_spooled(mrgpu_mr *mr, int functor)
     }
   } catch (...) {
     delete acc;
+    spool_clear_kmv(mr);
     throw;
   }
   mr->kmv_spool.clear();

@@ -911,6 +911,36 @@ def test_map_mr_self_and_invert(MR, oracle):
     assert m3.scan_kv() == [(v, k) for k, v in recs2]
 
 
+def test_copy_global_count_and_abandon(MR, oracle):
+    """mrgpu_copy (MapReduce::copy, src/mapreduce.cpp:290): deep copies of a KV (incl. the header-less form) and of a KMV
+    (incl. the factored form) that outlive and do not follow the original; mrgpu_global_count; mrgpu_abandon"""
+    import ctypes as C
+
+    import gpu_mapreduce_b200 as g
+
+    r = np.random.RandomState(41)
+    keys = r.randint(0, 5000, size=100_000).astype(np.uint32)
+    a = MR()
+    a.map_intcount(keys)                                  # header-less KV
+    b = a.copy()
+    want_kv = [(struct.pack("<I", int(k)), struct.pack("<i", 1)) for k in keys]
+    assert b.scan_kv() == want_kv
+    n = C.c_uint64()
+    assert g.lib().mrgpu_global_count(b._h, 0, C.byref(n)) == 0 and n.value == len(keys)
+    assert g.lib().mrgpu_global_count(b._h, 1, C.byref(n)) == g.lib().mrgpu_global_count(b._h, 1, C.byref(n)) != 0   # no KMV: an error, not a crash
+    nu = a.convert()                                      # factored KMV
+    c = a.copy()
+    a.reduce("count")                                     # the original moves on; the copy still holds the KMV
+    assert g.lib().mrgpu_global_count(c._h, 1, C.byref(n)) == 0 and n.value == nu
+    want = H.kmv_decode(oracle.convert(H.kv_encode(want_kv)))
+    assert H.canon_kmv(c.scan_kmv()) == H.canon_kmv(want)
+    assert c.reduce("count") == nu and H.canon_kv(c.scan_kv()) == H.canon_kv(a.scan_kv())
+    assert b.scan_kv() == want_kv                         # untouched by everything above
+    for h in (b, c):
+        assert g.lib().mrgpu_abandon(h._h) == 0           # non-collective teardown (what the Python finaliser uses)
+        object.__setattr__(h, "_h", None)
+
+
 def test_add_appends_other_mr(MR):
     a, b = MR(), MR()
     ra = [(b"k%d" % i, b"v") for i in range(100)]
