@@ -263,7 +263,7 @@ def rmat(nlevels=24, ef=16, a=.57, b=.19, c=.19, d=.05, fraction=0.0, seed=12345
         kern, _ = h.prof_report()
         x = [k for k in kern if k["tag"] == "aggregate_exchange_nvlink"]
         return (_allmax(max(sum(k["bytes"] for k in x), sum(k.get("moved", 0) for k in x)), local), _allmax(sum(k["ms"] for k in x), local),
-                {k["tag"]: round(k["ms"], 3) for k in kern if k["ms"] > 0.5})
+                {k["tag"]: round(k["ms"], 3) for k in kern if k["ms"] > 0.2})
 
     # the whole job runs `reps` times on the same handles; the last pass (allocator warm) is reported
     for rep in range(reps):
@@ -332,7 +332,7 @@ def rmat(nlevels=24, ef=16, a=.57, b=.19, c=.19, d=.05, fraction=0.0, seed=12345
                                         "frac_of_900": xb / 1e9 / (xms / 1e3) / 900 if xms else None}
         out["shuffle_degree_collate"] = {"bytes_max_over_ranks": db, "ms": dms, "bus_gbs": db / 1e9 / (dms / 1e3) if dms else None,
                                          "frac_of_900": db / 1e9 / (dms / 1e3) / 900 if dms else None}
-    out["kernels_ms_rank0"] = {"rmat": kern_rmat, "degree": kern_deg}
+    out["kernels_ms_rank0"] = {"rmat": kern_rmat, "rmat_last_round": xchg[-1][2], "degree": kern_deg}
     if hi:
         out["pool_hiwater_bytes_max_over_ranks"] = hi
     return out if rank == 0 else None

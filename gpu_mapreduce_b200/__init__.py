@@ -146,7 +146,7 @@ class MapReduce:
 
     _SETTINGS = ("mapstyle", "all2all", "verbosity", "timer", "memsize", "minpage", "maxpage", "freepage",
                  "outofcore", "zeropage", "keyalign", "valuealign",
-                 "compact", "ahead", "l2pin", "combine", "hbm_budget", "debug_fail_alloc")  # not reference members: 0 = stores always hold the reference's record streams (see mrgpu.h)
+                 "compact", "ahead", "l2pin", "combine", "presorted", "hbm_budget", "debug_fail_alloc")  # not reference members: 0 = stores always hold the reference's record streams (see mrgpu.h)
 
     def __init__(self, device: int = 0, stream: int | None = None, rank: int = 0, nranks: int = 1,
                  unique_id: bytes | None = None):

@@ -22,6 +22,7 @@
 #include "radix.cuh"
 #include "scan.cuh"
 #include "flagscan.cuh"
+#include "merge.cuh"
 #include "store.cuh"
 
 using namespace mrgpu;
@@ -59,6 +60,9 @@ struct mrgpu_mr {
   // setting "combine": aggregate() ships one row [key | count] per distinct key instead of every pair when the pairs
   // cannot be told apart (ops_aggregate.cuh); 0 = always the plain exchange in the reference's delivery order
   int64_t combine = 1;
+  // setting "presorted": convert() looks for a long ascending run among the sort keys (the previous round's output of
+  // an iterative job) and, if one covers half of them, sorts only the rest and merges (merge.cuh); 0 = always sort
+  int64_t presorted = 1;
   // setting "hbm_budget" (MB, 0 = unlimited): a KeyValue whose device part outgrows it moves to pinned host memory
   // piece by piece; convert / reduce / stats / pages / scan work on such stores (ops_spool.cuh)
   int64_t hbm_budget = 0;
@@ -265,7 +269,7 @@ static int64_t *setting(mrgpu_mr *mr, const char *name)
              {"verbosity", &mr->verbosity}, {"timer", &mr->timer},         {"all2all", &mr->all2all},
              {"mapstyle", &mr->mapstyle},   {"minpage", &mr->minpage},     {"maxpage", &mr->maxpage},
              {"freepage", &mr->freepage},   {"outofcore", &mr->outofcore}, {"zeropage", &mr->zeropage},   {"compact", &mr->compact},     {"ahead", &mr->ahead},
-             {"l2pin", &mr->l2pin},         {"combine", &mr->combine},     {"hbm_budget", &mr->hbm_budget},
+             {"l2pin", &mr->l2pin},         {"combine", &mr->combine},     {"hbm_budget", &mr->hbm_budget}, {"presorted", &mr->presorted},
                     {"debug_fail_alloc", &mr->debug_fail_alloc}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) return t.p;

@@ -108,6 +108,10 @@ const char *mrgpu_last_error(const mrgpu_mr *mr);
  * plain exchange; the one observable difference is the ORDER of the pairs inside the KeyValue after aggregate():
  * still by source rank, but within a source by ascending key instead of arrival order.  0 = always the plain
  * exchange, in the reference's delivery order.  Must be the same on every rank.
+ * "presorted" (default 1): convert() of pairs that cannot be told apart looks for one long ascending run among the
+ * sort keys -- what an iterative job (generate, collate, cull, repeat) hands it: the previous round's output plus a
+ * few new pairs -- and, when a run covers at least half of them, sorts only the others and merges.  The result is the
+ * same KeyMultiValue; 0 = always sort everything.
  * "hbm_budget" (MB, default 0 = unlimited) and the reference's "outofcore" (1 = force data out of core; here: a budget
  * of one page): the out-of-core tier.  After a map-type call a KeyValue whose part in HBM exceeds the budget moves to
  * pinned host memory as a piece (the analogue of the reference's page spill files, src/keyvalue.cpp:216-255,

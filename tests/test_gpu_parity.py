@@ -884,6 +884,54 @@ def test_rmat_degree_golden(MR, golden):
         assert H.canon_kv(mrv.scan_kv()) == H.canon_kv(H.kv_decode(golden[f"rmat{ci}.degree"]))
 
 
+def _edges(mr):
+    return np.sort(np.frombuffer(b"".join(k for k, _ in mr.scan_kv()), dtype=np.dtype([("i", "<u8"), ("j", "<u8")])), order=("j", "i"))
+
+
+def test_rmat_later_rounds_merge_instead_of_sorting(MR):
+    """From the second round on, collate's input is the previous round's edges (in key order) plus the new ones: only
+    the new ones are sorted and merged in.  Same edges and rounds as with the merge switched off."""
+    runs = {}
+    for presorted in (1, 0):
+        mr = MR()
+        mr.presorted = presorted
+        mr.prof(True)
+        niter = _gpu_rmat(mr, 17, 8, .57, .19, .19, .05, 0.1, 77, 1)
+        tags = {t["tag"] for t in mr.prof_report()[0]}
+        assert ("merge_sorted" in tags) == bool(presorted)
+        runs[presorted] = (niter, _edges(mr))
+    assert runs[1][0] == runs[0][0] > 2
+    assert len(runs[1][1]) == (1 << 17) * 8 and np.array_equal(runs[1][1], runs[0][1])
+    assert len(np.unique(runs[1][1])) == len(runs[1][1])
+
+
+def test_presorted_run_in_the_middle_and_all_sorted(MR, oracle):
+    """the long run may sit anywhere (after an exchange it follows what lower ranks sent); an input with no descent at
+    all is not sorted again; 4- and 8-byte keys"""
+    r = np.random.RandomState(5)
+    for dt, hi in ((np.uint32, 1 << 30), (np.uint64, 1 << 40)):
+        bulk = np.unique(r.randint(0, hi, size=400_000).astype(dt))
+        head, tail = r.randint(0, hi, size=3000).astype(dt), r.randint(0, hi, size=5000).astype(dt)
+        for parts in ((head, bulk, tail), (bulk,), (bulk, tail), (head, bulk)):
+            keys = np.concatenate(parts)
+            mr = MR()
+            mr.prof(True)
+            import gpu_mapreduce_b200 as g
+            L = g.lib()
+            mr._ck(L.mrgpu_kv_open(mr._h, 0))
+            mr._ck(L.mrgpu_kv_add(mr._h, len(keys), keys.ctypes.data, None, keys.itemsize, None, None, 0))
+            cnt = ctypes.c_uint64()
+            mr._ck(L.mrgpu_kv_close(mr._h, ctypes.byref(cnt)))
+            u, c = np.unique(keys, return_counts=True)
+            assert mr.convert() == len(u)
+            tags = {t["tag"] for t in mr.prof_report()[0]}
+            assert "presorted_count" in tags and ("merge_sorted" in tags) == (len(parts) > 1)
+            assert "onesweep_pass" not in tags or len(parts) > 1
+            mr.reduce("count")
+            got = dict((int.from_bytes(k, "little"), int.from_bytes(v, "little")) for k, v in mr.scan_kv())
+            assert got == dict(zip(u.tolist(), c.tolist()))
+
+
 def test_rmat_generate_stream_matches_oracle(MR, oracle):
     """one rmat_generate call = the reference's sequential drand48 stream, edge for edge, state included"""
     for fr in (0.0, 0.2):
