@@ -541,9 +541,11 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
 
 constexpr unsigned long long LCG_A = 0x5DEECE66Dull, LCG_C = 0xBull, LCG_M = (1ull << 48) - 1;
 
-__host__ __device__ inline void lcg_jump(unsigned long long k, unsigned long long &x)
+// the k-step jump as an affine map: x_k = ra * x_0 + rc (mod 2^48)
+__host__ __device__ inline void lcg_affine(unsigned long long k, unsigned long long &ra, unsigned long long &rc)
 {
-  unsigned long long ra = 1, rc = 0, ba = LCG_A, bc = LCG_C;
+  unsigned long long ba = LCG_A, bc = LCG_C;
+  ra = 1, rc = 0;
   while (k) {
     if (k & 1) {
       ra = (ba * ra) & LCG_M;
@@ -553,6 +555,12 @@ __host__ __device__ inline void lcg_jump(unsigned long long k, unsigned long lon
     ba = (ba * ba) & LCG_M;
     k >>= 1;
   }
+}
+
+__host__ __device__ inline void lcg_jump(unsigned long long k, unsigned long long &x)
+{
+  unsigned long long ra, rc;
+  lcg_affine(k, ra, rc);
   x = (ra * x + rc) & LCG_M;
 }
 
@@ -566,58 +574,89 @@ struct RmatParams {
   unsigned long long order;
   int nlevels;
   double a, b, c, d, fraction;
+  // fraction == 0: the quadrant tests "drand48() < a", "< a+b", "< a+b+c" on the raw 48-bit state.  drand48() is
+  // X / 2^48 exactly (X < 2^48 fits a double's mantissa) and scaling by a power of two is exact, so
+  // X / 2^48 < t  <=>  X < t * 2^48  <=>  X < ceil(t * 2^48) for an integer X: the same decisions without the
+  // int-to-double conversion and the double compares.  ta/tab/tabc are those ceilings, clamped to [0, 2^48].
+  unsigned long long ta, tab, tabc;
+  // one grid step ahead in the stream: thread m handles edges m, m + T, m + 2T, ... (T = threads in the grid); its
+  // first edge costs a full O(log) jump, every later one this single affine step of T * D draws
+  unsigned long long sa, sc;
 };
 
+static inline unsigned long long rmat_threshold(double t)
+{
+  const double s = ceil(t * 281474976710656.0);
+  if (!(s > 0.0)) return 0;
+  if (s >= 281474976710656.0) return 1ull << 48;
+  return (unsigned long long) s;
+}
+
+template <bool INT>
 __global__ void __launch_bounds__(256)
 rmat_generate_kernel(RmatParams p, unsigned long long state0, uint64_t ngenerate, uint8_t *out, uint32_t rs, uint32_t koff, bool fast)
 {
+  const uint64_t T = (uint64_t) gridDim.x * blockDim.x;
   uint64_t m = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= ngenerate) return;
   const int D = p.fraction > 0.0 ? 5 * p.nlevels : p.nlevels;
-  unsigned long long x = state0;
-  lcg_jump(m * (unsigned long long) D, x);
-  unsigned long long delta = p.order >> 1, i = 0, j = 0;
-  double a1 = p.a, b1 = p.b, c1 = p.c, d1 = p.d;
-  for (int l = 0; l < p.nlevels; l++) {
-    double rn = lcg_next(x);
-    double ab = __dadd_rn(a1, b1);
-    if (rn < a1) {
-    } else if (rn < ab) {
-      j += delta;
-    } else if (rn < __dadd_rn(ab, c1)) {
-      i += delta;
+  unsigned long long xs = state0;
+  lcg_jump(m * (unsigned long long) D, xs);
+  for (; m < ngenerate; m += T, xs = (p.sa * xs + p.sc) & LCG_M) {
+    unsigned long long x = xs, i = 0, j = 0;
+    if (INT) {
+      // level l decides bit nlevels-1-l of i and j: shift them in, most significant first
+      for (int l = 0; l < p.nlevels; l++) {
+        x = (LCG_A * x + LCG_C) & LCG_M;
+        const bool bi = x >= p.tab, bj = (x >= p.ta && x < p.tab) || x >= p.tabc;
+        i = (i << 1) | (unsigned long long) bi;
+        j = (j << 1) | (unsigned long long) bj;
+      }
     } else {
-      i += delta;
-      j += delta;
+      unsigned long long delta = p.order >> 1;
+      double a1 = p.a, b1 = p.b, c1 = p.c, d1 = p.d;
+      for (int l = 0; l < p.nlevels; l++) {
+        double rn = lcg_next(x);
+        double ab = __dadd_rn(a1, b1);
+        if (rn < a1) {
+        } else if (rn < ab) {
+          j += delta;
+        } else if (rn < __dadd_rn(ab, c1)) {
+          i += delta;
+        } else {
+          i += delta;
+          j += delta;
+        }
+        delta >>= 1;
+        if (p.fraction > 0.0) {
+          // a1 += a1*fraction * (drand48() - 0.5): ((a1*fraction) * (r-0.5)) then add, left to right as in C
+          a1 = __dadd_rn(a1, __dmul_rn(__dmul_rn(a1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
+          b1 = __dadd_rn(b1, __dmul_rn(__dmul_rn(b1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
+          c1 = __dadd_rn(c1, __dmul_rn(__dmul_rn(c1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
+          d1 = __dadd_rn(d1, __dmul_rn(__dmul_rn(d1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
+          double total = __dadd_rn(__dadd_rn(__dadd_rn(a1, b1), c1), d1);
+          a1 = __ddiv_rn(a1, total);
+          b1 = __ddiv_rn(b1, total);
+          c1 = __ddiv_rn(c1, total);
+          d1 = __ddiv_rn(d1, total);
+        }
+      }
     }
-    delta >>= 1;
-    if (p.fraction > 0.0) {
-      // a1 += a1*fraction * (drand48() - 0.5): ((a1*fraction) * (r-0.5)) then add, left to right as in C
-      a1 = __dadd_rn(a1, __dmul_rn(__dmul_rn(a1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
-      b1 = __dadd_rn(b1, __dmul_rn(__dmul_rn(b1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
-      c1 = __dadd_rn(c1, __dmul_rn(__dmul_rn(c1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
-      d1 = __dadd_rn(d1, __dmul_rn(__dmul_rn(d1, p.fraction), __dadd_rn(lcg_next(x), -0.5)));
-      double total = __dadd_rn(__dadd_rn(__dadd_rn(a1, b1), c1), d1);
-      a1 = __ddiv_rn(a1, total);
-      b1 = __ddiv_rn(b1, total);
-      c1 = __ddiv_rn(c1, total);
-      d1 = __ddiv_rn(d1, total);
+    uint32_t *r = (uint32_t *) (out + m * rs);
+    if (fast) {
+      // 24-byte record = three 8-byte stores (records are 8-byte aligned)
+      ((uint2 *) r)[0] = make_uint2(16, 0);
+      ((unsigned long long *) r)[1] = i;
+      ((unsigned long long *) r)[2] = j;
+    } else {
+      for (uint32_t q = 0; q < rs / 4; q++) r[q] = 0;
+      r[0] = 16;
+      r[1] = 0;
+      r[koff / 4] = (uint32_t) i;
+      r[koff / 4 + 1] = (uint32_t) (i >> 32);
+      r[koff / 4 + 2] = (uint32_t) j;
+      r[koff / 4 + 3] = (uint32_t) (j >> 32);
     }
-  }
-  uint32_t *r = (uint32_t *) (out + m * rs);
-  if (fast) {
-    // 24-byte record = three 8-byte stores (records are 8-byte aligned)
-    ((uint2 *) r)[0] = make_uint2(16, 0);
-    ((unsigned long long *) r)[1] = i;
-    ((unsigned long long *) r)[2] = j;
-  } else {
-    for (uint32_t q = 0; q < rs / 4; q++) r[q] = 0;
-    r[0] = 16;
-    r[1] = 0;
-    r[koff / 4] = (uint32_t) i;
-    r[koff / 4 + 1] = (uint32_t) (i >> 32);
-    r[koff / 4 + 2] = (uint32_t) j;
-    r[koff / 4 + 3] = (uint32_t) (j >> 32);
   }
 }
 
@@ -636,9 +675,19 @@ extern "C" int mrgpu_map_rmat(mrgpu_mr *mr, uint64_t ngenerate, int nlevels, dou
   RmatParams p{1ull << nlevels, nlevels, a, b, c, d, fraction};
   if (ngenerate) {
     bool fast = rs == 24 && kv_key_off(mr->al) == 8 && (base % 8) == 0;
+    const unsigned grid = grid_for(ngenerate, 256, 8);
+    const unsigned long long Dd = fraction > 0.0 ? 5ull * nlevels : (unsigned long long) nlevels;
+    lcg_affine((unsigned long long) grid * 256 * Dd, p.sa, p.sc);
+    // the sums as the reference forms them, in double: a1+b1, then (a1+b1)+c1 (oink/map_rmat_generate.cpp:42-50)
+    const double ab = a + b, abc = ab + c;
+    p.ta = rmat_threshold(a), p.tab = rmat_threshold(ab), p.tabc = rmat_threshold(abc);
+    // the integer form assumes a <= a+b <= a+b+c, as for any sane parameters; anything else takes the double path
+    const bool ints = !(fraction > 0.0) && a <= ab && ab <= abc;
     ProfScope ps(mr->pool, "map_rmat_generate", (double) ngenerate * 24);
-    rmat_generate_kernel<<<(unsigned) ((ngenerate + 255) / 256), 256, 0, mr->pool.stream>>>(p, *state48 & LCG_M, ngenerate, kv->data + base,
-                                                                                         rs, kv_key_off(mr->al), fast);
+    if (ints)
+      rmat_generate_kernel<true><<<grid, 256, 0, mr->pool.stream>>>(p, *state48 & LCG_M, ngenerate, kv->data + base, rs, kv_key_off(mr->al), fast);
+    else
+      rmat_generate_kernel<false><<<grid, 256, 0, mr->pool.stream>>>(p, *state48 & LCG_M, ngenerate, kv->data + base, rs, kv_key_off(mr->al), fast);
     MR_CUDA(cudaGetLastError());
   }
   kv_commit_uniform(kv, 16, 0, rs, ngenerate);

@@ -942,6 +942,18 @@ def test_rmat_generate_stream_matches_oracle(MR, oracle):
         assert n == 5000 and st == st1
         got = np.frombuffer(b"".join(k for k, _ in mr.scan_kv()), dtype=np.uint64).reshape(-1, 2)
         assert np.array_equal(got, edges)
+    # more edges than one grid of threads: a thread's later edges are reached by the precomputed grid-wide jump;
+    # fraction == 0 decides the quadrants on the integer state (thresholds ceil(t * 2^48)), incl. degenerate a, b, c, d
+    for n, nl, (a, b, c, d), fr in ((700_001, 20, (.57, .19, .19, .05), 0.0), (650_000, 9, (.25, .25, .25, .25), 0.0),
+                                    (610_000, 31, (0.0, 1.0, 0.0, 0.0), 0.0), (620_000, 12, (1e-9, .5, .5 - 1e-9, 0.0), 0.0),
+                                    (640_000, 16, (.45, .15, .15, .25), 0.05)):
+        st0 = oracle.lib.orc_srand48(99 + nl)
+        st1, edges = oracle.rmat_generate(st0, n, nl, a, b, c, d, fr)
+        mr = MR()
+        cnt, st = mr.map_rmat(n, nl, a, b, c, d, fr, st0, addflag=0)
+        assert cnt == n and st == st1
+        pages = [np.frombuffer(pg, dtype=np.uint64).reshape(nk, 3)[:, 1:] for nk, pg in mr.kv_pages()]
+        assert np.array_equal(np.concatenate(pages), edges)
 
 
 def test_map_mr_self_and_invert(MR, oracle):
