@@ -236,6 +236,30 @@ struct Pool {
     }
     add_free(p, b);
   }
+  // grow a live block in place when the bytes behind it are free (same cudaMalloc allocation): a store that is being
+  // appended to then keeps its address and nothing is copied
+  bool try_extend(void *ptr, uint64_t bytes)
+  {
+    if (!ptr || fail_after >= 0) return false;
+    bytes = (bytes + kGran - 1) / kGran * kGran;
+    auto u = used.find((uint8_t *) ptr);
+    if (u == used.end()) return false;
+    Block &b = u->second;
+    if (bytes <= b.size) return true;
+    auto nx = freeb.find((uint8_t *) ptr + b.size);
+    if (nx == freeb.end() || nx->second.chunk != b.chunk || b.size + nx->second.size < bytes) return false;
+    const uint64_t take = bytes - b.size, left = nx->second.size - take;
+    uint8_t *np = nx->first;
+    const int chunk = nx->second.chunk;
+    erase_free(nx);
+    uint64_t got = take;
+    if (left >= (1ull << 16)) add_free(np + take, Block{left, chunk});
+    else got += left;
+    b.size += got;
+    live += got;
+    if (live > hiwater) hiwater = live;
+    return true;
+  }
   // the cudaMalloc allocation a live block belongs to (for CUDA IPC, which shares whole allocations)
   std::set<int> exported;  // chunks whose CUDA IPC handle went to peer ranks: kept until the pool dies
   bool chunk_of(const void *ptr, uint8_t **base, uint64_t *size)

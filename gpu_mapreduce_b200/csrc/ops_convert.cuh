@@ -283,7 +283,8 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
   cudaStream_t s = pool.stream;
   const Align al = mr->al;
   const uint64_t n = kv->nkv;
-  const uint32_t kb = kv->kb, vb = kv->vb, rs = kv->recsize, koff = kv_key_off(al), voff = kv_val_off(al, kb);
+  const RowLayout lay = kv_layout(mr, kv);  // records, or header-less rows [key | value]
+  const uint32_t kb = kv->kb, vb = kv->vb, rs = lay.rs, koff = lay.koff, voff = lay.voff;
   using P = typename std::conditional<PMODE == 2, uint64_t, uint32_t>::type;
   constexpr bool HASP = PMODE != 0;
 
@@ -647,8 +648,11 @@ static void convert_resident(mrgpu_mr *mr)
     mr->kmv = kmv;
   } else {
     bool done = convert_dense(mr);  // small integer keys + indistinguishable pairs: count, do not sort
-    if (!done) kv_unpack(mr, kv);   // the sort paths read records
+    // the uniform sort path reads header-less rows [key | value] as they are; rows with a shared value or with
+    // multiplicities become records first
+    if (!done && kv->packed && (kv->weighted || kv->cval_on)) kv_unpack(mr, kv);
     const Align al = mr->al;
+    const RowLayout lay = kv_layout(mr, kv);
     // exact path needs word-aligned records/keys and a value that is empty, 4 or 8 bytes, or gatherable
     if (!done && kv->uniform && (al.k % 4) == 0) {
       CompactKey ck{};
@@ -661,19 +665,19 @@ static void convert_resident(mrgpu_mr *mr)
       } else if (kv->kb <= 1024) {
         Buf<unsigned> mask(mr->pool, kv->kb);
         MR_CUDA(cudaMemsetAsync(mask.p, 0, kv->kb * 4, mr->pool.stream));
-        const bool words = kv->kb % 4 == 0 && kv->kb <= 32 && kv->recsize % 4 == 0 && kv_key_off(al) % 4 == 0;
+        const bool words = kv->kb % 4 == 0 && kv->kb <= 32 && lay.rs % 4 == 0 && lay.koff % 4 == 0;
         {
-          ProfScope ps(mr->pool, "convert_key_diff", (double) kv->nbytes);
+          ProfScope ps(mr->pool, "convert_key_diff", (double) n * lay.rs);
           if (words)
-            key_diff_words_kernel<<<grid_for(n, 256 * 8, 8), 256, 0, mr->pool.stream>>>((const uint32_t *) kv->data, n, kv->recsize / 4, kv_key_off(al) / 4,
+            key_diff_words_kernel<<<grid_for(n, 256 * 8, 8), 256, 0, mr->pool.stream>>>((const uint32_t *) kv->data, n, lay.rs / 4, lay.koff / 4,
                                                                                          kv->kb / 4, mask.p);
           else
-            key_diff_kernel<<<grid_for(n, 256 * 8, 4), 256, kv->kb * 4, mr->pool.stream>>>(kv->data, n, kv->recsize, kv_key_off(al), kv->kb, mask.p);
+            key_diff_kernel<<<grid_for(n, 256 * 8, 4), 256, kv->kb * 4, mr->pool.stream>>>(kv->data, n, lay.rs, lay.koff, kv->kb, mask.p);
           MR_CUDA(cudaGetLastError());
         }
         std::vector<unsigned> hm(kv->kb);
         MR_CUDA(cudaMemcpyAsync(hm.data(), mask.p, kv->kb * 4, cudaMemcpyDeviceToHost, mr->pool.stream));
-        MR_CUDA(cudaMemcpyAsync(key0.data(), kv->data + kv_key_off(al), kv->kb, cudaMemcpyDeviceToHost, mr->pool.stream));
+        MR_CUDA(cudaMemcpyAsync(key0.data(), kv->data + lay.koff, kv->kb, cudaMemcpyDeviceToHost, mr->pool.stream));
         sync(mr);
         if (words) {  // word ORs -> one flag per key byte
           std::vector<unsigned> bytes(kv->kb);
@@ -692,8 +696,8 @@ static void convert_resident(mrgpu_mr *mr)
         ok = false;
       if (ok) {
         bool small = ck.nvb <= 4;
-        bool v32 = kv->vb == 4 && (kv_val_off(al, kv->kb) % 4) == 0;
-        bool v64 = kv->vb == 8 && (kv_val_off(al, kv->kb) % 4) == 0;
+        bool v32 = kv->vb == 4 && (lay.voff % 4) == 0;
+        bool v64 = kv->vb == 8 && (lay.voff % 4) == 0;
         int pm = kv->vb == 0 ? 0 : (v32 ? 1 : (v64 ? 2 : 3));
 #define CONV_CASE(K, PM) convert_uniform<K, PM>(mr, ck, ident, key0)
         if (small) {
@@ -714,7 +718,10 @@ static void convert_resident(mrgpu_mr *mr)
     // variable-length keys without values (words): count by hashing; falls through to the fingerprint sort when the
     // table overflows (too many distinct keys) or two keys share a fingerprint
     if (!done && !kv->uniform) done = convert_hash(mr);
-    if (!done) convert_general(mr);
+    if (!done) {
+      kv_unpack(mr, kv);  // the general path reads records
+      convert_general(mr);
+    }
   }
   // convert consumes the KV (src/mapreduce.cpp:876-878: "delete kv; kv = NULL")
   delete mr->kv;

@@ -38,6 +38,32 @@ static bool kv_can_pack(const mrgpu_mr *mr, uint32_t kb, uint32_t vb)
   return mr->compact && mr->al.k == 4 && mr->al.v == 4 && kb > 0 && kb % 4 == 0 && vb % 4 == 0;
 }
 
+// where key and value sit in what a uniform KV stores per pair: records {kb, vb, key, value}, or header-less rows
+struct RowLayout {
+  uint32_t rs, koff, voff;
+};
+static RowLayout kv_layout(const mrgpu_mr *mr, const DevKV *kv)
+{
+  if (kv->packed) return RowLayout{kv->prow(), 0, kv->kb};
+  return RowLayout{kv->recsize, kv_key_off(mr->al), kv_val_off(mr->al, kv->kb)};
+}
+
+// a map that emits value-less (kb, 0) pairs may write header-less rows when the KV is empty or already holds such rows
+static bool kv_rows_ok(const mrgpu_mr *mr, const DevKV *kv, uint32_t kb)
+{
+  return kv_can_pack(mr, kb, 0) && (kv->nkv == 0 || (kv->uniform && kv->packed && !kv->weighted && !kv->cval_on && kv->kb == kb && kv->vb == 0));
+}
+static void kv_rows_begin(DevKV *kv, uint32_t kb, uint32_t recsize)
+{
+  if (kv->nkv) return;
+  kv->uniform = kv->packed = true;
+  kv->cval_on = kv->weighted = false;
+  kv->cval[0] = kv->cval[1] = 0;
+  kv->kb = kb;
+  kv->vb = 0;
+  kv->recsize = recsize;
+}
+
 // 4-byte key + 4-byte value (stored or shared): one 16-byte record per thread
 __global__ void __launch_bounds__(256) kv_unpack16_kernel(const uint32_t *__restrict__ rows, uint64_t n, bool cval_on, uint32_t c0, int4 *__restrict__ out)
 {
@@ -408,7 +434,9 @@ edge_to_vertices_kernel(const uint8_t *__restrict__ src, const uint64_t *__restr
   int nout = both ? 2 : 1;
   for (int e = 0; e < nout; e++) {
     uint32_t *o = (uint32_t *) (dst + (i * nout + e) * out_rs);
-    if (out_rs == 16 && out_koff == 8) {
+    if (out_koff == 0) {  // header-less row
+      *(uint2 *) o = make_uint2(w[2 * e], w[2 * e + 1]);
+    } else if (out_rs == 16 && out_koff == 8) {
       *(int4 *) o = make_int4(8, 0, (int) w[2 * e], (int) w[2 * e + 1]);
     } else {
       for (uint32_t q = 0; q < out_rs / 4; q++) o[q] = 0;
@@ -450,29 +478,40 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
   freeze(srcmr);
   // src == dst: the reference detaches the old KV, builds the new one, then deletes the old (:1584-1602, 1634)
   DevKV *src = srcmr->kv;
-  kv_unpack(srcmr, src);  // the functors read records
+  // edge_to_vertex(es) read keys only and take header-less rows as they are; the other functors read records
+  const bool e2v = functor == MRGPU_MAP_EDGE_TO_VERTICES || functor == MRGPU_MAP_EDGE_TO_VERTEX;
+  if (!(e2v && src->packed && !src->weighted)) kv_unpack(srcmr, src);
   order_after(mr, srcmr);  // the kernels below run on mr's stream and read what srcmr's stream wrote
   bool self = (srcmr == mr);
   if (self) mr->kv = nullptr;
   try {
-    kv_begin_map(mr, self ? 0 : addflag);
+    kv_begin_map(mr, self ? 0 : addflag, e2v);
     DevKV *kv = mr->kv;
     const Align al = mr->al;
     const uint64_t n = src->nkv;
     cudaStream_t s = mr->pool.stream;
-    if (functor == MRGPU_MAP_EDGE_TO_VERTICES || functor == MRGPU_MAP_EDGE_TO_VERTEX) {
+    if (e2v) {
       int both = functor == MRGPU_MAP_EDGE_TO_VERTICES;
       uint32_t need = both ? 16 : 8;
       if (n && src->uniform && src->kb < need) MR_FAIL(MRGPU_EINVAL, "edge_to_vertices: source keys are shorter than an EDGE");
       if (n && (srcmr->al.k % 4)) MR_FAIL(MRGPU_EINVAL, "edge_to_vertices needs keyalign >= 4");
       uint64_t nout = n * (both ? 2 : 1);
-      uint64_t base = kv_append_uniform(mr, kv, 8, 0, nout);
+      const bool rows = kv_rows_ok(mr, kv, 8);  // the vertices as header-less 8-byte rows
+      if (!rows) kv_unpack(mr, kv);
       uint32_t rs = kv_rec_size(al, 8, 0);
+      uint64_t base;
+      if (rows) {
+        kv_rows_begin(kv, 8, rs);
+        kv->reserve_bytes((kv->nkv + nout) * 8);
+        kv->h_offs_valid = false;
+        base = kv->nkv * 8;
+      } else
+        base = kv_append_uniform(mr, kv, 8, 0, nout);
       if (n) {
-        ProfScope ps(mr->pool, "map_edge_to_vertices", (double) n * (8 + src->kb + src->vb) + (double) nout * 16);
-        edge_to_vertices_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(src->data, src->uniform ? nullptr : src->offs, src->recsize,
-                                                                           kv_key_off(srcmr->al), n, both, kv->data + base, rs,
-                                                                           kv_key_off(al));
+        const RowLayout sl = src->uniform ? kv_layout(srcmr, src) : RowLayout{0, kv_key_off(srcmr->al), 0};
+        ProfScope ps(mr->pool, "map_edge_to_vertices", (double) n * (src->uniform ? sl.rs : 8 + src->kb + src->vb) + (double) nout * (rows ? 8 : rs));
+        edge_to_vertices_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(src->data, src->uniform ? nullptr : src->offs, sl.rs, sl.koff, n, both,
+                                                                           kv->data + base, rows ? 8 : rs, rows ? 0 : kv_key_off(al));
         MR_CUDA(cudaGetLastError());
       }
       kv_commit_uniform(kv, 8, 0, rs, nout);
@@ -594,7 +633,7 @@ static inline unsigned long long rmat_threshold(double t)
 
 template <bool INT>
 __global__ void __launch_bounds__(256)
-rmat_generate_kernel(RmatParams p, unsigned long long state0, uint64_t ngenerate, uint8_t *out, uint32_t rs, uint32_t koff, bool fast)
+rmat_generate_kernel(RmatParams p, unsigned long long state0, uint64_t ngenerate, uint8_t *out, uint32_t rs, uint32_t koff, int fast)
 {
   const uint64_t T = (uint64_t) gridDim.x * blockDim.x;
   uint64_t m = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -643,7 +682,10 @@ rmat_generate_kernel(RmatParams p, unsigned long long state0, uint64_t ngenerate
       }
     }
     uint32_t *r = (uint32_t *) (out + m * rs);
-    if (fast) {
+    if (fast == 2) {
+      // header-less row = the 16 key bytes
+      *(ulonglong2 *) r = make_ulonglong2(i, j);
+    } else if (fast) {
       // 24-byte record = three 8-byte stores (records are 8-byte aligned)
       ((uint2 *) r)[0] = make_uint2(16, 0);
       ((unsigned long long *) r)[1] = i;
@@ -667,14 +709,26 @@ extern "C" int mrgpu_map_rmat(mrgpu_mr *mr, uint64_t ngenerate, int nlevels, dou
   if (!state48) MR_FAIL(MRGPU_EINVAL, "null state");
   if (nlevels < 1 || nlevels > 62) MR_FAIL(MRGPU_EINVAL, "Illegal rmat command");
   if (fraction >= 1.0) MR_FAIL(MRGPU_EINVAL, "RMAT fraction must be < 1");
-  kv_begin_map(mr, addflag);
+  kv_begin_map(mr, addflag, true);
   DevKV *kv = mr->kv;
   if (mr->al.k % 4) MR_FAIL(MRGPU_EINVAL, "rmat_generate needs keyalign >= 4");
-  uint64_t base = kv_append_uniform(mr, kv, 16, 0, ngenerate);
+  // header-less rows (the 16 key bytes; store.cuh) when the KV is empty or holds such rows already: what reduce(cull)
+  // leaves behind in R-MAT's loop
+  const bool rows = kv_rows_ok(mr, kv, 16);
+  if (!rows) kv_unpack(mr, kv);
+  uint64_t base;
   uint32_t rs = kv_rec_size(mr->al, 16, 0);
+  if (rows) {
+    kv_rows_begin(kv, 16, rs);
+    kv->reserve_bytes((kv->nkv + ngenerate) * 16);
+    kv->h_offs_valid = false;
+    base = kv->nkv * 16;
+  } else
+    base = kv_append_uniform(mr, kv, 16, 0, ngenerate);
   RmatParams p{1ull << nlevels, nlevels, a, b, c, d, fraction};
   if (ngenerate) {
-    bool fast = rs == 24 && kv_key_off(mr->al) == 8 && (base % 8) == 0;
+    const int fast = rows ? 2 : (rs == 24 && kv_key_off(mr->al) == 8 && (base % 8) == 0);
+    const uint32_t out_rs = rows ? 16 : rs;
     const unsigned grid = grid_for(ngenerate, 256, 8);
     const unsigned long long Dd = fraction > 0.0 ? 5ull * nlevels : (unsigned long long) nlevels;
     lcg_affine((unsigned long long) grid * 256 * Dd, p.sa, p.sc);
@@ -683,11 +737,11 @@ extern "C" int mrgpu_map_rmat(mrgpu_mr *mr, uint64_t ngenerate, int nlevels, dou
     p.ta = rmat_threshold(a), p.tab = rmat_threshold(ab), p.tabc = rmat_threshold(abc);
     // the integer form assumes a <= a+b <= a+b+c, as for any sane parameters; anything else takes the double path
     const bool ints = !(fraction > 0.0) && a <= ab && ab <= abc;
-    ProfScope ps(mr->pool, "map_rmat_generate", (double) ngenerate * 24);
+    ProfScope ps(mr->pool, "map_rmat_generate", (double) ngenerate * out_rs);
     if (ints)
-      rmat_generate_kernel<true><<<grid, 256, 0, mr->pool.stream>>>(p, *state48 & LCG_M, ngenerate, kv->data + base, rs, kv_key_off(mr->al), fast);
+      rmat_generate_kernel<true><<<grid, 256, 0, mr->pool.stream>>>(p, *state48 & LCG_M, ngenerate, kv->data + base, out_rs, kv_key_off(mr->al), fast);
     else
-      rmat_generate_kernel<false><<<grid, 256, 0, mr->pool.stream>>>(p, *state48 & LCG_M, ngenerate, kv->data + base, rs, kv_key_off(mr->al), fast);
+      rmat_generate_kernel<false><<<grid, 256, 0, mr->pool.stream>>>(p, *state48 & LCG_M, ngenerate, kv->data + base, out_rs, kv_key_off(mr->al), fast);
     MR_CUDA(cudaGetLastError());
   }
   kv_commit_uniform(kv, 16, 0, rs, ngenerate);

@@ -267,9 +267,22 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
       uint32_t kb = functor == MRGPU_REDUCE_NONZERO ? ikb / 2 : (functor == MRGPU_REDUCE_DEGREE ? 4 : ikb);
       uint32_t vb = shape ? 0 : (cull ? (uint32_t) kmv->uvb : 4);
       uint32_t rs = kv_rec_size(al, kb, vb);
-      kv->reserve_bytes(U * rs);
-      ProfScope ps(pool, "reduce", (double) U * (12 + 4 + ikb + rs));
-      if (shape && kmv->factored)
+      // cull = (key, first value) of every key.  The factored KMV's key array IS that KV in header-less form (rows =
+      // keys, the one shared value kept aside: store.cuh), so the array changes owner and nothing is copied.
+      const bool handover = cull && kmv->factored && kmv->fkey && kmv->fkw * 4 == kb && kv_can_pack(mr, kb, vb);
+      if (handover) {
+        kv->data = (uint8_t *) kmv->fkey;
+        kv->cap = kmv->fcap * 4 * kmv->fkw;
+        kmv->fkey = nullptr;
+        kv->packed = true;
+        kv->cval_on = vb > 0;
+        kv->cval[0] = kmv->fval[0];
+        kv->cval[1] = kmv->fval[1];
+      } else
+        kv->reserve_bytes(U * rs);
+      ProfScope ps(pool, "reduce", handover ? 0.0 : (double) U * (12 + 4 + ikb + rs), handover ? 0 : 1);
+      if (handover) {
+      } else if (shape && kmv->factored)
         reduce_factored_shape_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kmv->fkey, kmv->fcnt, U, functor, al, ikb, kv->data, rs);
       else if (shape)
         reduce_generic_kernel<<<(unsigned) ((U + 255) / 256), 256, 0, s>>>(kd, ko, U, functor, al, kv->data, nullptr, rs);

@@ -77,6 +77,10 @@ struct DevKV {
   void reserve_bytes(uint64_t need)
   {
     if (need <= cap) return;
+    if (data && phys_bytes() && pool->try_extend(data, need)) {  // the bytes behind the store are free: no copy
+      cap = need;
+      return;
+    }
     uint64_t ncap = cap ? cap : 0;
     ncap = need > 2 * ncap ? need : 2 * ncap;
     // large stores are sized exactly when first filled; one that is being appended to (map with addflag, add,

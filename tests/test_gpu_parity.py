@@ -543,6 +543,60 @@ def test_headerless_kv_meets_other_shapes(MR, oracle):
     assert H.kv_encode(a.scan_kv()) == oracle.sort_keys(oracle.intcount_map(keys), 1)
 
 
+def test_headerless_edge_and_vertex_rows_meet_other_ops(MR, oracle):
+    """rmat_generate, reduce(cull) and edge_to_vertices keep value-less pairs as header-less rows (store.cuh); every
+    other op sees the reference's records: pages, scan, add, append of another shape, invert, sort, clone, copy"""
+    st0 = oracle.lib.orc_srand48(7)
+    _, edges = oracle.rmat_generate(st0, 3000, 9, .57, .19, .19, .05, 0.0)
+    recs = [(e.tobytes(), b"") for e in edges]
+
+    def gen(**settings):
+        mr = MR(**settings)
+        assert mr.map_rmat(3000, 9, .57, .19, .19, .05, 0.0, st0, addflag=0)[0] == 3000
+        return mr
+
+    a = gen()
+    assert a.scan_kv() == recs
+    (nk, page), = a.kv_pages()
+    assert nk == 3000 and page == b"".join(struct.pack("<II", 16, 0) + k for k, _ in recs)
+    st = a.kv_stats()
+    assert (st.npair, st.keysize, st.valuesize) == (3000, 48000, 0)
+    # append pairs of another shape: the rows become records first
+    a.kv_add([(b"xy", b"z")], addflag=1)
+    assert a.scan_kv() == recs + [(b"xy", b"z")]
+    # add() in both directions, copy, invert
+    b, c = gen(), MR()
+    c.kv_add([(b"k" * 16, b"")])
+    assert c.add(b) == 3001 and c.scan_kv() == [(b"k" * 16, b"")] + recs
+    assert b.add(c) == 6001 and b.scan_kv() == recs + [(b"k" * 16, b"")] + recs
+    d = gen().copy()
+    assert d.scan_kv() == recs
+    e = MR()
+    e.map_mr(d, "invert")
+    assert e.scan_kv() == [(v, k) for k, v in recs]
+    # cull hands the KMV's key array over as rows; a second round appends rows to it; compact=0 does none of this
+    out = {}
+    for compact in (1, 0):
+        m = gen(compact=compact)
+        m.collate()
+        nu = m.reduce("cull")
+        assert H.canon_kv(m.scan_kv()) == H.canon_kv(sorted(set(recs)))
+        m.map_rmat(500, 9, .57, .19, .19, .05, 0.0, st0 + 12345, addflag=1)
+        _, more = oracle.rmat_generate(st0 + 12345, 500, 9, .57, .19, .19, .05, 0.0)
+        assert sorted(m.scan_kv()) == sorted(list(set(recs)) + [(x.tobytes(), b"") for x in more])
+        assert m.kv_stats().npair == nu + 500
+        v = MR(compact=compact)
+        assert v.map_mr(m, "edge_to_vertices") == 2 * (nu + 500)
+        assert v.map_mr(m, "edge_to_vertex", addflag=1) == 3 * (nu + 500)
+        out[compact] = (H.kv_encode(v.scan_kv()), [p for _, p in v.kv_pages()])
+        v.sort_keys(2)
+        ks = [int.from_bytes(k, "little") for k, _ in v.scan_kv()]
+        assert ks == sorted(ks) and len(ks) == 3 * (nu + 500)
+        m.clone()
+        assert len(m.scan_kmv()) == nu + 500
+    assert out[1] == out[0]
+
+
 # ------------------------------------------------------------------------------------------- sort_keys
 
 @pytest.mark.parametrize("flag", [1, 2, 3, 4, 5, 6])
