@@ -34,10 +34,13 @@ struct CompactKey {
 
 // ---- uniform records: extract sort key (+ payload) and histogram in one read of the KV -----------------
 
-template <typename K, int PMODE /*0 none, 1 val32, 2 val64, 3 idx*/, bool IDENT /*key bytes 0..kb-1, kb<=8, word loads*/>
+// KEY16: 16-byte keys at a 4-byte aligned offset (R-MAT's EDGE): the key is read as words (one 16-byte load when
+// `vec16`: rows and key offset are multiples of 16) and the varying bytes are picked out of two 64-bit halves with
+// shifts by amounts that are the same in every thread -- instead of one byte load per varying byte.
+template <typename K, int PMODE /*0 none, 1 val32, 2 val64, 3 idx*/, bool IDENT /*key bytes 0..kb-1, kb<=8, word loads*/, bool KEY16 = false>
 __global__ void __launch_bounds__(256)
 extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs, uint32_t koff, uint32_t voff, uint32_t kb, CompactKey ck,
-                       K *__restrict__ keys, void *__restrict__ pay, unsigned long long *hist, unsigned long long *vdiff)
+                       K *__restrict__ keys, void *__restrict__ pay, unsigned long long *hist, unsigned long long *vdiff, bool vec16 = false)
 {
   __shared__ unsigned sh[sizeof(K) * RADIX];
   for (int i = threadIdx.x; i < (int) sizeof(K) * RADIX; i += blockDim.x) sh[i] = 0;
@@ -68,6 +71,25 @@ extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs
         unsigned long long m = kb >= 8 ? ~0ull : ((1ull << (8 * kb)) - 1);
         k64 &= m;
       }
+      key = (K) k64;
+    } else if (KEY16) {
+      unsigned long long lo, hi;
+      if (vec16) {
+        const uint4 v = *(const uint4 *) (r + koff);
+        lo = (unsigned long long) v.x | ((unsigned long long) v.y << 32);
+        hi = (unsigned long long) v.z | ((unsigned long long) v.w << 32);
+      } else {
+        const uint32_t *w = (const uint32_t *) (r + koff);
+        lo = (unsigned long long) w[0] | ((unsigned long long) w[1] << 32);
+        hi = (unsigned long long) w[2] | ((unsigned long long) w[3] << 32);
+      }
+      unsigned long long k64 = 0;
+#pragma unroll
+      for (int q = 0; q < 8; q++)
+        if (q < ck.nvb) {
+          const unsigned p = ck.pos[q];
+          k64 |= (((p < 8 ? lo : hi) >> (8 * (p & 7))) & 0xFFull) << (8 * q);
+        }
       key = (K) k64;
     } else {
       unsigned long long k64 = 0;
@@ -301,6 +323,9 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
     extract16_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>((const int4 *) kv->data, n, (uint32_t *) k0.p, (uint32_t *) p0.p, hist.p, vdiff);
   else if (ident)
     extract_uniform_kernel<K, PMODE, true><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p, vdiff);
+  else if (kb == 16 && rs % 4 == 0 && koff % 4 == 0 && ((uintptr_t) kv->data % 16) == 0)
+    extract_uniform_kernel<K, PMODE, false, true><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p, vdiff,
+                                                                                         rs % 16 == 0 && koff % 16 == 0);
   else
     extract_uniform_kernel<K, PMODE, false><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p, vdiff);
   MR_CUDA(cudaGetLastError());
@@ -385,7 +410,30 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
             }
           return x;
         };
-        if (kw % 4 == 0) {
+        if (kw == 4 && !ident) {
+          // 16-byte keys: the first key with its varying bytes cleared, as two 64-bit halves; byte q of the sort key
+          // is shifted into its place (the position is the same in every thread: no divergence, no table)
+          unsigned long long h0[2] = {0, 0};
+          memcpy(h0, key0.data(), 16);
+          for (int q = 0; q < ck.nvb; q++) h0[ck.pos[q] >> 3] &= ~(0xFFull << (8 * (ck.pos[q] & 7)));
+          const unsigned long long lo0 = h0[0], hi0 = h0[1];
+          auto mk = [=] __device__(uint64_t u) {
+            const uint32_t s0 = __ldg(st + u);
+            fc[u] = __ldg(st + u + 1) - s0;
+            const unsigned long long key = (unsigned long long) __ldg(sk + s0);
+            unsigned long long lo = lo0, hi = hi0;
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+              if (q < ckc.nvb) {
+                const unsigned p = ckc.pos[q];
+                const unsigned long long b = ((key >> (8 * q)) & 0xFFull) << (8 * (p & 7));
+                if (p < 8) lo |= b;
+                else hi |= b;
+              }
+            ((ulonglong2 *) fkw32)[u] = make_ulonglong2(lo, hi);
+          };
+          for_each_kernel<<<grid_for(U, 256, 64), 256, 0, s>>>(U, mk);
+        } else if (kw % 4 == 0) {
           auto mk = [=] __device__(uint64_t u) {
             const uint32_t s0 = __ldg(st + u);
             fc[u] = __ldg(st + u + 1) - s0;
