@@ -81,8 +81,9 @@ constexpr int TOKV_THREADS = 256;
 constexpr uint32_t TOKV_CHUNK = TOKV_THREADS * 16;
 
 // bit i set iff byte i of the 16 is one of " \t\n\f\r"; bytes at or after `end` count as whitespace
-__device__ __forceinline__ uint32_t tok_ws_mask16(const uint8_t *__restrict__ t, uint64_t p, uint64_t end)
+__device__ __forceinline__ uint32_t tok_ws_mask16(const uint8_t *__restrict__ t, uint64_t p, uint64_t end, uint32_t *nul = nullptr)
 {
+  if (nul) *nul = 0;
   if (p >= end) return 0xFFFFu;
   uint32_t w[4] = {0, 0, 0, 0};
   if (end - p >= 16) {
@@ -104,14 +105,21 @@ __device__ __forceinline__ uint32_t tok_ws_mask16(const uint8_t *__restrict__ t,
     }
     // gather the four flag bits (bit 7 of each byte) into a nibble
     m |= (((hit >> 7) * 0x00204081u) >> 21 & 0xFu) << (4 * q);
+    if (nul) {  // the same test for NUL bytes (strtok's text ends at the first one)
+      const uint32_t z = ~(((w[q] & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | w[q]) & 0x80808080u;
+      *nul |= (((z >> 7) * 0x00204081u) >> 21 & 0xFu) << (4 * q);
+    }
   }
-  if (end - p < 16) m |= 0xFFFFu << (uint32_t) (end - p);
+  if (end - p < 16) {
+    m |= 0xFFFFu << (uint32_t) (end - p);
+    if (nul) *nul &= ~(0xFFFFu << (uint32_t) (end - p));
+  }
   return m & 0xFFFFu;
 }
 
-__device__ __forceinline__ void tokv_masks(const uint8_t *__restrict__ t, uint64_t p, uint64_t end, uint32_t &S, uint32_t &E)
+__device__ __forceinline__ void tokv_masks(const uint8_t *__restrict__ t, uint64_t p, uint64_t end, uint32_t &S, uint32_t &E, uint32_t *nul = nullptr)
 {
-  const uint32_t m = tok_ws_mask16(t, p, end);
+  const uint32_t m = tok_ws_mask16(t, p, end, nul);
   const uint32_t prev = (p == 0 || p > end) ? 1u : (tok_ws(t[p - 1]) ? 1u : 0u);
   const uint32_t next = (p + 16 >= end) ? 1u : (tok_ws(t[p + 16]) ? 1u : 0u);
   const uint32_t nm = ~m & 0xFFFFu;
@@ -120,14 +128,23 @@ __device__ __forceinline__ void tokv_masks(const uint8_t *__restrict__ t, uint64
 }
 
 // per chunk: words starting in it, and (position + 1) of its last start (0 = none)
+// NUL: also report the position of the first NUL byte (atomicMin into *nulpos): the caller counts as if there were
+// none and counts again up to it in the rare case that there is one -- a pass of its own over the text otherwise
+template <bool NUL>
 __global__ void __launch_bounds__(TOKV_THREADS)
-tokv_count_kernel(const uint8_t *__restrict__ t, uint64_t end, uint64_t nchunks, uint32_t *__restrict__ cnt, uint32_t *__restrict__ last)
+tokv_count_kernel(const uint8_t *__restrict__ t, uint64_t end, uint64_t nchunks, uint32_t *__restrict__ cnt, uint32_t *__restrict__ last,
+                  unsigned long long *nulpos)
 {
   __shared__ uint32_t s_cnt[TOKV_THREADS / 32], s_last[TOKV_THREADS / 32];
   for (uint64_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
     const uint64_t p = c * TOKV_CHUNK + (uint64_t) threadIdx.x * 16;
-    uint32_t S, E;
-    tokv_masks(t, p, end, S, E);
+    uint32_t S, E, Z = 0;
+    tokv_masks(t, p, end, S, E, NUL ? &Z : nullptr);
+    if (NUL && __any_sync(0xFFFFFFFFu, Z != 0)) {
+      unsigned long long z = Z ? p + (__ffs(Z) - 1) : ~0ull;
+      for (int o = 16; o; o >>= 1) z = min(z, __shfl_xor_sync(0xFFFFFFFFu, z, o));
+      if ((threadIdx.x & 31) == 0) atomicMin(nulpos, z);
+    }
     uint32_t n = __popc(S), l = S ? (uint32_t) p + (31 - __clz(S)) + 1 : 0;
     n = __reduce_add_sync(0xFFFFFFFFu, n);
     l = __reduce_max_sync(0xFFFFFFFFu, l);
@@ -182,10 +199,13 @@ tokv_scan_kernel(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ 
 // every END finds its word's index and start and writes (start, end) of that word
 __global__ void __launch_bounds__(TOKV_THREADS)
 tokv_pairs_kernel(const uint8_t *__restrict__ t, uint64_t end, uint64_t nchunks, const uint32_t *__restrict__ base,
-                  const uint32_t *__restrict__ carry, uint32_t *__restrict__ starts, uint32_t *__restrict__ ends)
+                  const uint32_t *__restrict__ carry, uint32_t *__restrict__ starts, uint32_t *__restrict__ ends, unsigned long long *keybytes)
 {
   __shared__ uint32_t s_cnt[TOKV_THREADS / 32], s_last[TOKV_THREADS / 32];
+  __shared__ unsigned long long s_kb;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned long long kbytes = 0;  // key bytes (word + NUL) of the words this thread closes: one sum per block at the end
+  if (threadIdx.x == 0) s_kb = 0;
   for (uint64_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
     const uint64_t p = c * TOKV_CHUNK + (uint64_t) threadIdx.x * 16;
     uint32_t S, E;
@@ -211,11 +231,17 @@ tokv_pairs_kernel(const uint8_t *__restrict__ t, uint64_t end, uint64_t nchunks,
       e &= e - 1;
       const uint32_t sle = S & ((2u << bit) - 1);  // starts at or before this end, inside the 16 bytes
       const uint32_t w = before + __popc(sle) - 1;
-      starts[w] = sle ? (uint32_t) p + (31 - __clz(sle)) : lastb - 1;
-      ends[w] = (uint32_t) p + bit + 1;
+      const uint32_t ws = sle ? (uint32_t) p + (31 - __clz(sle)) : lastb - 1, we = (uint32_t) p + bit + 1;
+      starts[w] = ws;
+      ends[w] = we;
+      kbytes += we - ws + 1;
     }
     __syncthreads();
   }
+  for (int o = 16; o; o >>= 1) kbytes += __shfl_down_sync(0xFFFFFFFFu, kbytes, o);
+  if (lane == 0 && kbytes) atomicAdd(&s_kb, kbytes);
+  __syncthreads();
+  if (threadIdx.x == 0 && s_kb) atomicAdd(keybytes, s_kb);
 }
 
 // one thread per word, 4-byte stores; the key bytes come from two aligned 32-bit loads and a funnel shift
@@ -279,41 +305,61 @@ extern "C" int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbyte
   const uint8_t *t = stage_input(mr, (const uint8_t *) text, nbytes, tmp, false);  // read several times: stage it
   uint64_t nwords = 0;
   if (nbytes) {
-    unsigned long long *d = mr->d_small;
-    MR_CUDA(cudaMemsetAsync(d, 0xFF, 8, s));
-    {
-      ProfScope ps(pool, "tok_first_nul", (double) nbytes, 2);
-      const uint64_t nvec = ((uintptr_t) t % 16) == 0 ? nbytes / 16 : 0;
-      if (nvec) first_nul16_kernel<<<grid_for(nvec, 256 * 4, 8), 256, 0, s>>>(t, nvec, d);
-      if (nbytes > nvec * 16) first_nul_kernel<<<grid_for(nbytes - nvec * 16, 256 * 16, 8), 256, 0, s>>>(t, nvec * 16, nbytes, d);
-      MR_CUDA(cudaGetLastError());
-    }
-    fetch_small(mr, 1);
-    const uint64_t end = std::min<uint64_t>(mr->h_small[0], nbytes);
     // 16 bytes per thread when the text is 16-byte aligned (MRGPU_TOK_BYTEWISE=1 forces the per-byte form)
     static const bool force_bytewise = getenv("MRGPU_TOK_BYTEWISE") && atoi(getenv("MRGPU_TOK_BYTEWISE"));
     const bool vec = ((uintptr_t) t % 16) == 0 && !force_bytewise;
+    uint64_t end = nbytes;
+    if (!vec) {
+      unsigned long long *d = mr->d_small;
+      MR_CUDA(cudaMemsetAsync(d, 0xFF, 8, s));
+      {
+        ProfScope ps(pool, "tok_first_nul", (double) nbytes, 2);
+        const uint64_t nvec = ((uintptr_t) t % 16) == 0 ? nbytes / 16 : 0;
+        if (nvec) first_nul16_kernel<<<grid_for(nvec, 256 * 4, 8), 256, 0, s>>>(t, nvec, d);
+        if (nbytes > nvec * 16) first_nul_kernel<<<grid_for(nbytes - nvec * 16, 256 * 16, 8), 256, 0, s>>>(t, nvec * 16, nbytes, d);
+        MR_CUDA(cudaGetLastError());
+      }
+      fetch_small(mr, 1);
+      end = std::min<uint64_t>(mr->h_small[0], nbytes);
+    }
     Buf<uint32_t> starts, ends;
     auto isstart = [=] __device__(uint64_t i) -> unsigned long long { return (!tok_ws(t[i]) && (i == 0 || tok_ws(t[i - 1]))) ? 1ull : 0ull; };
     if (vec) {
-      const uint64_t nchunks = (end + TOKV_CHUNK - 1) / TOKV_CHUNK;
+      uint64_t nchunks = (end + TOKV_CHUNK - 1) / TOKV_CHUNK;
       Buf<uint32_t> cnt(pool, nchunks), last(pool, nchunks), cbase(pool, nchunks), carry(pool, nchunks);
+      // the count pass looks for the first NUL as well and counts as if there were none; a text that does hold one
+      // (strtok stops there, examples/wordfreq.cpp:104-130) is counted again up to it
       MR_CUDA(cudaMemsetAsync(mr->d_small, 0, 8, s));
-      if (nchunks) {
-        {
+      MR_CUDA(cudaMemsetAsync(mr->d_small + 2, 0xFF, 8, s));
+      {
+        ProfScope ps(pool, "tok_count", (double) end, 2);
+        tokv_count_kernel<true><<<grid_for(nchunks, 1, 16), TOKV_THREADS, 0, s>>>(t, end, nchunks, cnt.p, last.p, mr->d_small + 2);
+        MR_CUDA(cudaGetLastError());
+        tokv_scan_kernel<<<1, 1024, 0, s>>>(cnt.p, last.p, nchunks, cbase.p, carry.p, mr->d_small);
+        MR_CUDA(cudaGetLastError());
+      }
+      fetch_small(mr, 3);
+      if (mr->h_small[2] < nbytes) {
+        end = mr->h_small[2];
+        nchunks = (end + TOKV_CHUNK - 1) / TOKV_CHUNK;
+        MR_CUDA(cudaMemsetAsync(mr->d_small, 0, 8, s));
+        if (nchunks) {
           ProfScope ps(pool, "tok_count", (double) end, 2);
-          tokv_count_kernel<<<grid_for(nchunks, 1, 16), TOKV_THREADS, 0, s>>>(t, end, nchunks, cnt.p, last.p);
+          tokv_count_kernel<false><<<grid_for(nchunks, 1, 16), TOKV_THREADS, 0, s>>>(t, end, nchunks, cnt.p, last.p, nullptr);
           MR_CUDA(cudaGetLastError());
           tokv_scan_kernel<<<1, 1024, 0, s>>>(cnt.p, last.p, nchunks, cbase.p, carry.p, mr->d_small);
           MR_CUDA(cudaGetLastError());
         }
         fetch_small(mr, 1);
+      }
+      if (nchunks) {
         nwords = mr->h_small[0];
         if (nwords) {
           starts.alloc(pool, nwords);
           ends.alloc(pool, nwords);
           ProfScope ps(pool, "tok_pairs", (double) end + 8.0 * nwords);
-          tokv_pairs_kernel<<<grid_for(nchunks, 1, 16), TOKV_THREADS, 0, s>>>(t, end, nchunks, cbase.p, carry.p, starts.p, ends.p);
+          MR_CUDA(cudaMemsetAsync(mr->d_small + 1, 0, 8, s));
+          tokv_pairs_kernel<<<grid_for(nchunks, 1, 16), TOKV_THREADS, 0, s>>>(t, end, nchunks, cbase.p, carry.p, starts.p, ends.p, mr->d_small + 1);
           MR_CUDA(cudaGetLastError());
         }
       }
@@ -339,7 +385,7 @@ extern "C" int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbyte
       uint64_t base = va.base;
       // total key bytes by a reduction of its own (one atomic per warp on a single counter took 2 of this step's 3.2 ms
       // per GiB of text: four million same-address atomics)
-      {
+      if (!vec) {  // (the 16-bytes-per-thread pairs kernel has summed them already)
         ScanTiles kt;
         scan_tiles(pool, nwords, [=] __device__(uint64_t j) -> unsigned long long { return pe[j] - ps[j] + 1; }, kt, mr->d_small + 1, "tok_sizes", 8.0 * nwords);
       }

@@ -85,9 +85,13 @@ struct DevKV {
     ncap = need > 2 * ncap ? need : 2 * ncap;
     // large stores are sized exactly when first filled; one that is being appended to (map with addflag, add,
     // gather) grows by half again so that a run of appends does not copy the whole store every time
-    if (need > (1ull << 28)) ncap = (cap && nbytes) ? std::max<uint64_t>(need, cap + cap / 2) : need;
+    // (doubling up to 4 GiB: a file-by-file map copies the store once over in total instead of twice)
+    if (need > (1ull << 28)) ncap = (cap && nbytes) ? std::max<uint64_t>(need, need > (4ull << 30) ? cap + cap / 2 : 2 * cap) : need;
     uint8_t *nd = (uint8_t *) pool->alloc(ncap);
-    if (phys_bytes()) MR_CUDA(cudaMemcpyAsync(nd, data, phys_bytes(), cudaMemcpyDeviceToDevice, pool->stream));
+    if (phys_bytes()) {
+      ProfScope ps(*pool, "kv_grow", 2.0 * phys_bytes(), 0);
+      MR_CUDA(cudaMemcpyAsync(nd, data, phys_bytes(), cudaMemcpyDeviceToDevice, pool->stream));
+    }
     pool->free(data, cap);
     data = nd;
     cap = ncap;
@@ -95,10 +99,17 @@ struct DevKV {
   void reserve_offs(uint64_t entries)
   {
     if (entries <= offs_cap) return;
+    if (offs && !uniform && nkv && pool->try_extend(offs, entries * 8)) {
+      offs_cap = entries;
+      return;
+    }
     uint64_t ncap = entries > 2 * offs_cap ? entries : 2 * offs_cap;
-    if (entries > (1ull << 25)) ncap = (offs_cap && nkv) ? std::max<uint64_t>(entries, offs_cap + offs_cap / 2) : entries;
+    if (entries > (1ull << 25)) ncap = (offs_cap && nkv) ? std::max<uint64_t>(entries, entries > (1ull << 29) ? offs_cap + offs_cap / 2 : 2 * offs_cap) : entries;
     uint64_t *no = (uint64_t *) pool->alloc(ncap * 8);
-    if (offs && !uniform && nkv) MR_CUDA(cudaMemcpyAsync(no, offs, (nkv + 1) * 8, cudaMemcpyDeviceToDevice, pool->stream));
+    if (offs && !uniform && nkv) {
+      ProfScope ps(*pool, "kv_grow", 16.0 * (nkv + 1), 0);
+      MR_CUDA(cudaMemcpyAsync(no, offs, (nkv + 1) * 8, cudaMemcpyDeviceToDevice, pool->stream));
+    }
     pool->free(offs, offs_cap * 8);
     offs = no;
     offs_cap = ncap;
