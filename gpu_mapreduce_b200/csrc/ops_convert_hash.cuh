@@ -25,14 +25,19 @@
 constexpr int HG_THREADS = 768;
 constexpr uint32_t HG_SLOTS = 2560;             // per block: 2560 x (16 + 8 + 4 + 4 + 4) bytes = 90 KB, two blocks per SM
 constexpr uint32_t HG_PROBES = 8;
-constexpr uint32_t HG_GLOBAL_LOG2 = 21;         // 2^21 entries x 16 bytes = 32 MB: stays in the 126 MB L2
+constexpr uint32_t HG_GLOBAL_LOG2 = 21;         // 2^21 entries x 32 bytes = 64 MB; the part in use stays in the 126 MB L2
 constexpr uint32_t HG_GLOBAL_PROBES = 64;
 constexpr uint32_t HG_UNSET = 0xFFFFFFFFu;
 
-struct HgEntry {
+// One 32-byte sector per entry.  Keys of up to 12 bytes (an 11-letter word and its NUL) are kept in the entry, so
+// joining a group in the global table is one 16-byte read of (key words, len) and one RED on the count; without them
+// every join walked entry -> representative's offset -> representative's record, three dependent L2 reads.
+struct __align__(32) HgEntry {
   unsigned long long fp;  // 0 = empty
   unsigned cnt;
   unsigned rep;           // a record of this group (the smallest index seen so far)
+  unsigned kw[3];         // the key, zero padded, when it fits
+  unsigned len;           // 0 = not published yet; else keybytes + 1, bit 31 set when the key is not in kw
 };
 
 struct HgRecs {
@@ -63,16 +68,41 @@ __device__ __forceinline__ bool hg_same_key(const HgRecs &r, uint32_t i, uint32_
   return true;
 }
 
-// add `cnt` pairs represented by record `rep` to the global table; flags: 1 = table full, 2 = fingerprint collision
+// add `cnt` pairs represented by record `rep` to the global table; flags: 1 = table full, 2 = fingerprint collision.
+// kw / len: the key's first words (zero padded) and keybytes + 1; in12 = the key fits the entry's 12 bytes.
+// Exactness: whoever claims an entry also enters the representative chain (atomicMin on rep hands back the previous
+// representative, against which the newcomer compares its key byte for byte), so the claimer's key equals every key
+// that joined through the chain; a key that joins by comparing with the published words equals the claimer's.
 __device__ __forceinline__ void hg_global_add(HgEntry *__restrict__ g, uint32_t gmask, unsigned long long fp, unsigned cnt, unsigned rep,
-                                              const HgRecs &r, unsigned long long *flags)
+                                              const HgRecs &r, unsigned long long *flags, uint4 kw, uint32_t len, bool in12)
 {
   uint32_t slot = (uint32_t) (fp >> 20) & gmask;
+  const uint32_t mylen = in12 ? len : (len | 0x80000000u);
   for (uint32_t p = 0; p < HG_GLOBAL_PROBES; p++) {
-    unsigned long long cur = g[slot].fp;
-    if (cur == 0) cur = atomicCAS(&g[slot].fp, 0ull, fp);
-    if (cur == 0 || cur == fp) {
+    unsigned long long cur = __ldcg(&g[slot].fp);
+    bool mine = false;
+    if (cur == 0) {
+      cur = atomicCAS(&g[slot].fp, 0ull, fp);
+      mine = cur == 0;
+    }
+    if (mine || cur == fp) {
       atomicAdd(&g[slot].cnt, cnt);
+      if (mine) {  // publish the key: words first, then the length
+        if (in12) g[slot].kw[0] = kw.x, g[slot].kw[1] = kw.y, g[slot].kw[2] = kw.z;
+        __threadfence();
+        atomicExch(&g[slot].len, mylen);
+      } else if (in12) {
+        const uint4 e = __ldcg((const uint4 *) &g[slot].kw[0]);  // (kw0, kw1, kw2, len) in one read
+        if (e.w == mylen) {
+          if (e.x != kw.x || e.y != kw.y || e.z != kw.z) atomicOr(flags, 2ull);
+          return;
+        }
+        if (e.w != 0) {  // same fingerprint, a key of another length
+          atomicOr(flags, 2ull);
+          return;
+        }
+        // claimed but not published yet: the representative chain below decides
+      }
       const unsigned old = atomicMin(&g[slot].rep, rep);
       if (old != HG_UNSET && old != rep && !hg_same_key(r, rep, old)) atomicOr(flags, 2ull);
       return;
@@ -161,12 +191,15 @@ hash_group_kernel(HgRecs r, uint64_t n, uint32_t seed, HgEntry *__restrict__ g, 
           if (slot == HG_SLOTS) slot = 0;
         }
       }
-      if (!done) hg_global_add(g, gmask, fp, 1u, (unsigned) i, r, flags);  // the block's table is taken by more frequent keys
+      if (!done) hg_global_add(g, gmask, fp, 1u, (unsigned) i, r, flags, kw, kb + 1, inl && kb <= 12);  // the block's table is taken by more frequent keys
     }
   }
   __syncthreads();
   for (uint32_t s = threadIdx.x; s < HG_SLOTS; s += blockDim.x)
-    if (s_fp[s]) hg_global_add(g, gmask, s_fp[s], s_cnt[s], s_rep[s], r, flags);
+    if (s_fp[s]) {
+      const uint32_t len = s_len[s];
+      hg_global_add(g, gmask, s_fp[s], s_cnt[s], s_rep[s], r, flags, s_w[s], len & 0x7FFFFFFFu, !(len & 0x80000000u) && (len & 0x7FFFFFFFu) <= 13);
+    }
 }
 
 // factored KMV with variable-length keys -> the reference's record stream (every value is empty: the size array of a
@@ -249,8 +282,8 @@ static bool convert_hash(mrgpu_mr *mr)
   }
   HgEntry *g = table.p;
   {
-    ProfScope ps(pool, "convert_hash_clear", (double) gslots * 16);
-    for_each_kernel<<<grid_for(gslots, 256, 16), 256, 0, s>>>((uint64_t) gslots, [=] __device__(uint64_t i) { g[i] = HgEntry{0ull, 0u, HG_UNSET}; });
+    ProfScope ps(pool, "convert_hash_clear", (double) gslots * sizeof(HgEntry));
+    for_each_kernel<<<grid_for(gslots, 256, 16), 256, 0, s>>>((uint64_t) gslots, [=] __device__(uint64_t i) { g[i] = HgEntry{0ull, 0u, HG_UNSET, {0u, 0u, 0u}, 0u}; });
     MR_CUDA(cudaGetLastError());
   }
   MR_CUDA(cudaMemsetAsync(flags, 0, 8, s));
@@ -262,7 +295,7 @@ static bool convert_hash(mrgpu_mr *mr)
   // non-empty entries -> (fingerprint, count, rep) arrays
   auto used = [=] __device__(uint64_t i) -> bool { return g[i].fp != 0; };
   FlagTiles ft;
-  flag_tiles(pool, gslots, used, ft, mr->d_small, "convert_hash_compact", (double) gslots * 16);
+  flag_tiles(pool, gslots, used, ft, mr->d_small, "convert_hash_compact", (double) gslots * sizeof(HgEntry));
   MR_CUDA(cudaMemcpyAsync(mr->h_small + 6, flags, 8, cudaMemcpyDeviceToHost, s));
   fetch_small(mr, 1);
   if (mr->h_small[6]) return false;  // table full or a fingerprint collision: the sort path decides
@@ -279,7 +312,7 @@ static bool convert_hash(mrgpu_mr *mr)
         pc[e] = g[i].cnt;
         pr[e] = g[i].rep;
       }
-    }, "convert_hash_compact", (double) gslots * 16 + 20.0 * U);
+    }, "convert_hash_compact", (double) gslots * sizeof(HgEntry) + 20.0 * U);
   }
   table.release();
   // KMV pairs come out in fingerprint order, like the sort path's
