@@ -222,7 +222,11 @@ __device__ __forceinline__ bool keys_equal(const uint8_t *data, const uint64_t *
   if (ka != kbb) return false;
   a += kv_key_off(al);
   b += kv_key_off(al);
-  for (uint32_t q = 0; q < ka; q++)
+  uint32_t q = 0;
+  if (((((uintptr_t) a) | ((uintptr_t) b)) & 3) == 0)  // word-aligned keys (any alignment setting that is a multiple of 4)
+    for (; q + 4 <= ka; q += 4)
+      if (*(const uint32_t *) (a + q) != *(const uint32_t *) (b + q)) return false;
+  for (; q < ka; q++)
     if (a[q] != b[q]) return false;
   return true;
 }
@@ -565,14 +569,17 @@ static void convert_general(mrgpu_mr *mr)
   Buf<unsigned long long> hist(pool, 8 * RADIX);
   const uint64_t *sk = nullptr;
   const uint32_t *sp = nullptr;
-  ScanTiles heads;
+  FlagTiles heads;
   uint64_t U = 0;
   for (uint32_t attempt = 0;; attempt++) {
     if (attempt == 8) MR_FAIL(MRGPU_EINVAL, "convert: fingerprint collisions persisted over 8 seeds");
     MR_CUDA(cudaMemsetAsync(hist.p, 0, 8 * RADIX * 8, s));
     // seed 0 makes the high half exactly the reference's bucket hash hashlittle(key,kb,0) (keymultivalue.cpp:1428)
-    extract_fp_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>(data, ko, rs, n, al, attempt, k0.p, p0.p, hist.p);
-    MR_CUDA(cudaGetLastError());
+    {
+      ProfScope ps(pool, "convert_fp_extract", (double) kv->nbytes + 20.0 * n);
+      extract_fp_kernel<<<grid_for(n, 256 * 4, 8), 256, 0, s>>>(data, ko, rs, n, al, attempt, k0.p, p0.p, hist.p);
+      MR_CUDA(cudaGetLastError());
+    }
     int cur = radix_sort_pairs<uint64_t, uint32_t, true>(pool, k0.p, k1.p, p0.p, p1.p, n, 0xFF, true, hist.p);
     sk = cur ? k1.p : k0.p;
     sp = cur ? p1.p : p0.p;
@@ -581,34 +588,48 @@ static void convert_general(mrgpu_mr *mr)
     unsigned long long *flag = mr->d_small + 1;
     MR_CUDA(cudaMemsetAsync(flag, 0, 8, s));
     // run heads by fingerprint; inside a run every element must equal its predecessor byte for byte
-    auto head = [=] __device__(uint64_t i) -> unsigned long long {
-      if (i == 0) return 1ull;
-      if (skc[i] != skc[i - 1]) return 1ull;
-      if (!keys_equal(data, ko, rs, al, spc[i], spc[i - 1])) *flag = 1;
-      return 0ull;
+    auto head = [=] __device__(uint64_t i) -> bool {
+      if (i == 0) return true;
+      if (__ldg(skc + i) != __ldg(skc + i - 1)) return true;
+      if (!keys_equal(data, ko, rs, al, __ldg(spc + i), __ldg(spc + i - 1))) *flag = 1;
+      return false;
     };
-    scan_tiles(pool, n, head, heads, mr->d_small);
+    FlagTiles ht;
+    flag_tiles(pool, n, head, ht, mr->d_small, "convert_fp_heads", 12.0 * n);
     fetch_small(mr, 2);
     U = mr->h_small[0];
-    if (mr->h_small[1] == 0) break;
+    if (mr->h_small[1] == 0) {
+      heads = static_cast<FlagTiles &&>(ht);
+      break;
+    }
   }
   const uint64_t *skc = sk;
   const uint32_t *spc = sp;
-  auto head = [=] __device__(uint64_t i) -> unsigned long long { return (i == 0 || skc[i] != skc[i - 1]) ? 1ull : 0ull; };
+  auto head = [=] __device__(uint64_t i) -> bool { return i == 0 || __ldg(skc + i) != __ldg(skc + i - 1); };
 
   // start[u], and G[i] = value bytes before sorted element i
   Buf<uint32_t> start(pool, U + 1);
   Buf<uint64_t> G(pool, n + 1);
   uint32_t *st = start.p;
   uint64_t *g = G.p;
-  scan_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
+  flag_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
     if (h) st[e] = (uint32_t) i;
-  });
+  }, "convert_fp_starts", 8.0 * n);
   uint32_t n32 = (uint32_t) n;
   MR_CUDA(cudaMemcpyAsync(st + U, &n32, 4, cudaMemcpyHostToDevice, s));
+  // value bytes of every pair as a column in arrival order (one coalesced pass), gathered in sorted order: 4-byte
+  // reads from 4n bytes instead of from the records themselves
+  Buf<uint32_t> vbs(pool, n);
+  {
+    uint32_t *pv = vbs.p;
+    ProfScope ps(pool, "convert_fp_valuebytes", 12.0 * n);
+    for_each_kernel<<<grid_for(n, 256, 64), 256, 0, s>>>(n, [=] __device__(uint64_t i) { pv[i] = ((const uint32_t *) (data + rec_off(ko, rs, i)))[1]; });
+    MR_CUDA(cudaGetLastError());
+  }
+  const uint32_t *cvb = vbs.p;
   scan_apply(
-      pool, n, [=] __device__(uint64_t i) -> unsigned long long { return ((const uint32_t *) (data + rec_off(ko, rs, spc[i])))[1]; },
-      [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { g[i] = e; }, mr->d_small + 2);
+      pool, n, [=] __device__(uint64_t i) -> unsigned long long { return __ldg(cvb + __ldg(spc + i)); },
+      [=] __device__(uint64_t i, unsigned long long e, unsigned long long) { g[i] = e; }, mr->d_small + 2, "convert_fp_valuebytes", 16.0 * n);
   MR_CUDA(cudaMemcpyAsync(g + n, mr->d_small + 2, 8, cudaMemcpyDeviceToDevice, s));
 
   DevKMV *kmv = new DevKMV(&pool);
@@ -629,7 +650,7 @@ static void convert_general(mrgpu_mr *mr)
           offs[u] = e;
           warp_add(ksum, *(const uint32_t *) (data + rec_off(ko, rs, spc[st[u]])));
         },
-        mr->d_small);
+        mr->d_small, "convert_fp_sizes", 32.0 * U);
     fetch_small(mr, 4);
     const uint64_t total = mr->h_small[0];
     MR_CUDA(cudaMemcpyAsync(offs + U, &total, 8, cudaMemcpyHostToDevice, s));
@@ -638,7 +659,7 @@ static void convert_general(mrgpu_mr *mr)
     kmv->nbytes = total;
     kmv->ksize = mr->h_small[3];
     uint8_t *out = kmv->data;
-    scan_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
+    flag_sink(pool, heads, head, [=] __device__(uint64_t i, unsigned long long e, unsigned long long h) {
       uint64_t u = e + h - 1;
       uint32_t s0 = st[u], s1 = st[u + 1];
       uint64_t nv = s1 - s0, r = i - s0;
@@ -663,7 +684,7 @@ static void convert_general(mrgpu_mr *mr)
       const uint8_t *v = src + kv_val_off(al, kb);
       uint8_t *d = rec + vo + (g[i] - g[s0]);
       for (uint32_t q = 0; q < vb; q++) d[q] = v[q];
-    });
+    }, "convert_fp_write", (double) kv->nbytes + (double) total);
     kmv->nkmv = U;
     kmv->nvalue = n;
     kmv->vsize = kv->vsize;

@@ -586,23 +586,13 @@ __global__ void __launch_bounds__(1024) href_blockstate_kernel(const uint2 *__re
   }
 }
 
-// walk one chunk (already in registers) from state st; calls on_entry(pos of first URL byte) / on_exit(pos of closing quote)
-template <typename FE, typename FX>
-__device__ __forceinline__ void href_walk(const uint32_t (&w)[8], int m, const uint32_t *__restrict__ s_nib, uint64_t c0, int st, FE on_entry, FX on_exit)
-{
-#pragma unroll
-  for (int q = 0; q < HREF_CHUNK; q++)
-    if (q < m) {
-      const int nx = (int) ((s_nib[(w[q >> 2] >> (8 * (q & 3))) & 0xFFu] >> (4 * st)) & 7u);
-      if (st == HS_HREF && nx == HS_LINK) on_entry(c0 + q + 1);
-      if (st == HS_LINK && nx == HS_START) on_exit(c0 + q);
-      st = nx;
-    }
-}
-
+// The walk from the chunk's now-known start state.  Its result is kept as two 32-bit masks per chunk -- bit q of the
+// high word: a URL's first byte is q + 1 bytes into the chunk (the opening quote is byte q); bit q of the low word: a
+// closing quote at byte q -- so that the pass that writes the positions needs neither the text nor a second walk
+// (it was a third read of the text and as expensive as this kernel: nearly every warp holds a chunk with a link).
 __global__ void __launch_bounds__(256)
 href_count_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, const uint2 *__restrict__ tfun, const uint8_t *__restrict__ bstate,
-                  uint8_t *__restrict__ tstate, unsigned long long *__restrict__ cnt)
+                  unsigned long long *__restrict__ masks)
 {
   __shared__ uint32_t s_nib[256];
   s_nib[threadIdx.x] = g_href_nib[threadIdx.x];
@@ -610,47 +600,75 @@ href_count_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, const
   const uint64_t g = (uint64_t) blockIdx.x * 256 + threadIdx.x;
   const uint2 tf = tfun[g];
   const int st = hf_at(HF{tf.x, tf.y}, bstate[blockIdx.x]);
-  tstate[g] = (uint8_t) st;
   uint32_t w[8];
-  const int m = href_load32(t, n, g * HREF_CHUNK, aligned, w);
-  unsigned ne = 0, nx = 0;
-  href_walk(w, m, s_nib, g * HREF_CHUNK, st, [&](uint64_t) { ne++; }, [&](uint64_t) { nx++; });
-  cnt[g] = ((unsigned long long) ne << 32) | nx;
+  const uint64_t c0 = g * HREF_CHUNK;
+  const int m = href_load32(t, n, c0, aligned, w);
+  // L: bit q = the state after byte q is LINK.  LINK is entered only from HREF (by the opening quote) and left only to
+  // START (by the closing quote), so entries and exits are the rising and falling edges of L.
+  unsigned L = 0;
+  int cur = st;
+#pragma unroll
+  for (int q = 0; q < HREF_CHUNK; q++)
+    if (q < m) {
+      cur = (int) ((s_nib[(w[q >> 2] >> (8 * (q & 3))) & 0xFFu] >> (4 * cur)) & 7u);
+      L |= (cur == HS_LINK ? 1u : 0u) << q;
+    }
+  const unsigned valid = m >= 32 ? 0xFFFFFFFFu : ((1u << m) - 1u), prev = (L << 1) | (st == HS_LINK ? 1u : 0u);
+  const unsigned em = L & ~prev & valid, xm = ~L & prev & valid;
+  masks[g] = ((unsigned long long) em << 32) | xm;
 }
 
-// second walk: every entry / exit position goes to its slot (exclusive counts from the scan of cnt[])
+// every entry / exit position goes to its slot (exclusive counts from the scan of the masks' bit counts)
 __global__ void __launch_bounds__(256)
-href_sink_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, uint64_t nthr, const uint8_t *__restrict__ tstate,
-                 const unsigned long long *__restrict__ cnt, const unsigned long long *__restrict__ excl, uint32_t *__restrict__ entry,
+href_sink_kernel(uint64_t nthr, const unsigned long long *__restrict__ masks, const unsigned long long *__restrict__ excl, uint32_t *__restrict__ entry,
                  uint32_t *__restrict__ exitp)
 {
-  __shared__ uint32_t s_nib[256];
-  s_nib[threadIdx.x] = g_href_nib[threadIdx.x];
-  __syncthreads();
   const uint64_t g = (uint64_t) blockIdx.x * 256 + threadIdx.x;
-  if (g >= nthr || cnt[g] == 0) return;  // nothing starts or ends in most chunks
-  uint32_t w[8];
-  const int m = href_load32(t, n, g * HREF_CHUNK, aligned, w);
-  uint32_t ie = (uint32_t) (excl[g] >> 32), ix = (uint32_t) excl[g];
-  href_walk(w, m, s_nib, g * HREF_CHUNK, tstate[g], [&](uint64_t p) { entry[ie++] = (uint32_t) p; }, [&](uint64_t p) { exitp[ix++] = (uint32_t) p; });
+  if (g >= nthr) return;
+  const unsigned long long mk = masks[g];
+  if (mk == 0) return;  // nothing starts or ends in most chunks
+  uint32_t em = (uint32_t) (mk >> 32), xm = (uint32_t) mk;
+  const unsigned long long e = excl[g];
+  uint32_t ie = (uint32_t) (e >> 32), ix = (uint32_t) e;
+  const uint32_t c0 = (uint32_t) (g * HREF_CHUNK);
+  while (em) {
+    entry[ie++] = c0 + (uint32_t) __ffs(em);  // bit q: first URL byte at c0 + q + 1
+    em &= em - 1;
+  }
+  while (xm) {
+    exitp[ix++] = c0 + (uint32_t) __ffs(xm) - 1;
+    xm &= xm - 1;
+  }
 }
 
+// eight lanes per record, one 4-byte store per lane and trip (a warp writes four records' worth of contiguous words);
+// one thread per record with byte stores took 0.135 ms per 128 MiB file for 30 MB of records
 __global__ void __launch_bounds__(256)
 href_write_kernel(const uint8_t *__restrict__ t, const uint32_t *__restrict__ entry, const uint32_t *__restrict__ exitp, uint64_t nurl,
                   const uint8_t *__restrict__ fname, uint32_t fnb, uint8_t *__restrict__ out, const uint64_t *__restrict__ offs, Align al)
 {
-  uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t j = ((uint64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  const uint32_t l = threadIdx.x & 7u;
   if (j >= nurl) return;
-  uint32_t s = entry[j], kb = exitp[j] - s;
+  const uint32_t s = entry[j], kb = exitp[j] - s;
   uint8_t *r = out + offs[j];
-  uint32_t ko = kv_key_off(al), vo = kv_val_off(al, kb), end = kv_rec_size(al, kb, fnb);
-  ((uint32_t *) r)[0] = kb;
-  ((uint32_t *) r)[1] = fnb;
-  for (uint32_t q = 8; q < ko; q++) r[q] = 0;
-  for (uint32_t q = 0; q < kb; q++) r[ko + q] = t[s + q];
-  for (uint32_t q = ko + kb; q < vo; q++) r[q] = 0;
-  for (uint32_t q = 0; q < fnb; q++) r[vo + q] = fname[q];
-  for (uint32_t q = vo + fnb; q < end; q++) r[q] = 0;
+  const uint32_t ko = kv_key_off(al), vo = kv_val_off(al, kb), end = kv_rec_size(al, kb, fnb);
+  auto byte_at = [&](uint32_t pos) -> uint32_t {
+    if (pos < 4) return (kb >> (8 * pos)) & 0xFFu;
+    if (pos < 8) return (fnb >> (8 * (pos - 4))) & 0xFFu;
+    if (pos >= ko && pos < ko + kb) return t[s + (pos - ko)];
+    if (pos >= vo && pos < vo + fnb) return fname[pos - vo];
+    return 0u;
+  };
+  if ((((uintptr_t) r) & 3) == 0) {
+    const uint32_t nwords = end >> 2;
+    for (uint32_t wq = l; wq < nwords; wq += 8) {
+      const uint32_t p = 4 * wq;
+      ((uint32_t *) r)[wq] = byte_at(p) | (byte_at(p + 1) << 8) | (byte_at(p + 2) << 16) | (byte_at(p + 3) << 24);
+    }
+    for (uint32_t p = 4 * nwords + l; p < end; p += 8) r[p] = (uint8_t) byte_at(p);
+  } else
+    for (uint32_t p = l; p < end; p += 8) r[p] = (uint8_t) byte_at(p);
 }
 
 extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, const char *fname, int addflag, uint64_t *nkv)
@@ -672,7 +690,7 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
     const uint64_t n = nbytes;
     const uint64_t nblk = (n + 256 * HREF_CHUNK - 1) / (256 * HREF_CHUNK), nthr = nblk * 256;
     Buf<uint2> tfun(pool, nthr), bfun(pool, nblk);
-    Buf<uint8_t> bstate(pool, nblk), tstate(pool, nthr);
+    Buf<uint8_t> bstate(pool, nblk);
     Buf<unsigned long long> cnt(pool, nthr), excl(pool, nthr);
     const bool aligned = ((uintptr_t) t % 16) == 0;
     {
@@ -684,11 +702,14 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
     }
     {
       ProfScope ps(pool, "href_count", (double) n);
-      href_count_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, aligned, tfun.p, bstate.p, tstate.p, cnt.p);
+      href_count_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, aligned, tfun.p, bstate.p, cnt.p);
       MR_CUDA(cudaGetLastError());
     }
     const unsigned long long *pc = cnt.p;
-    auto val = [=] __device__(uint64_t g) -> unsigned long long { return pc[g]; };
+    auto val = [=] __device__(uint64_t g) -> unsigned long long {  // (entries, exits) of the chunk, packed like their totals
+      const unsigned long long mk = pc[g];
+      return ((unsigned long long) __popc((unsigned) (mk >> 32)) << 32) | (unsigned) __popc((unsigned) mk);
+    };
     ScanTiles st;
     scan_tiles(pool, nthr, val, st, mr->d_small);
     fetch_small(mr, 1);
@@ -699,8 +720,8 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
       unsigned long long *pex = excl.p;
       scan_sink(pool, st, val, [=] __device__(uint64_t g, unsigned long long e, unsigned long long) { pex[g] = e; });
       {
-        ProfScope ps(pool, "href_positions", (double) n);
-        href_sink_kernel<<<(unsigned) nblk, 256, 0, s>>>(t, n, aligned, nthr, tstate.p, cnt.p, excl.p, pe, px);
+        ProfScope ps(pool, "href_positions", 16.0 * nthr + 8.0 * nurl);
+        href_sink_kernel<<<(unsigned) nblk, 256, 0, s>>>(nthr, cnt.p, excl.p, pe, px);
         MR_CUDA(cudaGetLastError());
       }
       VarAppend va = kv_append_var_begin(mr, kv, nurl);
@@ -720,7 +741,7 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
       MR_CUDA(cudaMemcpyAsync(dname.p, fname, fnb, cudaMemcpyHostToDevice, s));
       {
         ProfScope ps(pool, "href_write", (double) total + 8.0 * nurl);
-        href_write_kernel<<<(unsigned) ((nurl + 255) / 256), 256, 0, s>>>(t, pe, px, nurl, dname.p, fnb, kv->data, kv->offs + kv->nkv, al);
+        href_write_kernel<<<(unsigned) ((nurl * 8 + 255) / 256), 256, 0, s>>>(t, pe, px, nurl, dname.p, fnb, kv->data, kv->offs + kv->nkv, al);
         MR_CUDA(cudaGetLastError());
       }
       kv->nbytes = va.base + total;
