@@ -621,24 +621,36 @@ href_count_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, const
 // every entry / exit position goes to its slot (exclusive counts from the scan of the masks' bit counts)
 __global__ void __launch_bounds__(256)
 href_sink_kernel(uint64_t nthr, const unsigned long long *__restrict__ masks, const unsigned long long *__restrict__ excl, uint32_t *__restrict__ entry,
-                 uint32_t *__restrict__ exitp)
+                 uint32_t *__restrict__ exitp, unsigned long long *keybytes /* += sum of exits - sum of entries (mod 2^64) */)
 {
+  __shared__ unsigned long long s_sum;
+  if (threadIdx.x == 0) s_sum = 0;
+  __syncthreads();
   const uint64_t g = (uint64_t) blockIdx.x * 256 + threadIdx.x;
-  if (g >= nthr) return;
-  const unsigned long long mk = masks[g];
-  if (mk == 0) return;  // nothing starts or ends in most chunks
-  uint32_t em = (uint32_t) (mk >> 32), xm = (uint32_t) mk;
-  const unsigned long long e = excl[g];
-  uint32_t ie = (uint32_t) (e >> 32), ix = (uint32_t) e;
-  const uint32_t c0 = (uint32_t) (g * HREF_CHUNK);
-  while (em) {
-    entry[ie++] = c0 + (uint32_t) __ffs(em);  // bit q: first URL byte at c0 + q + 1
-    em &= em - 1;
+  const unsigned long long mk = g < nthr ? masks[g] : 0ull;
+  unsigned long long sum = 0;
+  if (mk) {  // nothing starts or ends in most chunks
+    uint32_t em = (uint32_t) (mk >> 32), xm = (uint32_t) mk;
+    const unsigned long long e = excl[g];
+    uint32_t ie = (uint32_t) (e >> 32), ix = (uint32_t) e;
+    const uint32_t c0 = (uint32_t) (g * HREF_CHUNK);
+    while (em) {
+      const uint32_t p = c0 + (uint32_t) __ffs(em);  // bit q: first URL byte at c0 + q + 1
+      entry[ie++] = p;
+      sum -= p;
+      em &= em - 1;
+    }
+    while (xm) {
+      const uint32_t p = c0 + (uint32_t) __ffs(xm) - 1;
+      exitp[ix++] = p;
+      sum += p;
+      xm &= xm - 1;
+    }
   }
-  while (xm) {
-    exitp[ix++] = c0 + (uint32_t) __ffs(xm) - 1;
-    xm &= xm - 1;
-  }
+  for (int o = 16; o; o >>= 1) sum += __shfl_down_sync(0xFFFFFFFFu, sum, o);
+  if ((threadIdx.x & 31) == 0 && sum) atomicAdd(&s_sum, sum);
+  __syncthreads();
+  if (threadIdx.x == 0 && s_sum) atomicAdd(keybytes, s_sum);
 }
 
 // eight lanes per record, one 4-byte store per lane and trip (a warp writes four records' worth of contiguous words);
@@ -721,14 +733,15 @@ extern "C" int mrgpu_map_href(mrgpu_mr *mr, const void *text, uint64_t nbytes, c
       scan_sink(pool, st, val, [=] __device__(uint64_t g, unsigned long long e, unsigned long long) { pex[g] = e; });
       {
         ProfScope ps(pool, "href_positions", 16.0 * nthr + 8.0 * nurl);
-        href_sink_kernel<<<(unsigned) nblk, 256, 0, s>>>(nthr, cnt.p, excl.p, pe, px);
+        MR_CUDA(cudaMemsetAsync(mr->d_small + 1, 0, 8, s));
+        href_sink_kernel<<<(unsigned) nblk, 256, 0, s>>>(nthr, cnt.p, excl.p, pe, px, mr->d_small + 1);
         MR_CUDA(cudaGetLastError());
       }
       VarAppend va = kv_append_var_begin(mr, kv, nurl);
       uint64_t *oo = va.offs;
       uint64_t base = va.base;
-      {
-        ScanTiles kt;  // total key bytes (a reduction: no same-address atomics)
+      if (nentry != nurl) {  // a URL still open at the end of the text: the sums of the positions pass do not pair up
+        ScanTiles kt;        // total key bytes by a reduction of its own
         scan_tiles(pool, nurl, [=] __device__(uint64_t j) -> unsigned long long { return px[j] - pe[j]; }, kt, mr->d_small + 1, "href_sizes", 8.0 * nurl);
       }
       scan_apply(
