@@ -484,6 +484,46 @@ __device__ __forceinline__ uint32_t hf_sel(uint32_t x)
 __device__ __forceinline__ HF hf_then(HF f, HF g) { return HF{__byte_perm(g.lo, g.hi, hf_sel(f.lo)), __byte_perm(g.lo, g.hi, hf_sel(f.hi))}; }
 __device__ __forceinline__ int hf_at(HF f, int st) { return (int) (((st < 4 ? f.lo : f.hi) >> (8 * (st & 3))) & 7u); }
 
+__device__ __forceinline__ HF hf_shfl_up(HF f, int o) { return HF{__shfl_up_sync(0xFFFFFFFFu, f.lo, o), __shfl_up_sync(0xFFFFFFFFu, f.hi, o)}; }
+
+// Scan of one function per thread under composition (earlier thread first), NW warps per block: inclusive scan inside
+// each warp by shuffles, the warp totals scanned by warp 0, two barriers in all.  (The first version was a
+// Hillis-Steele scan in shared memory: log2(threads) rounds of two barriers each -- ncu's top stall of the compose
+// kernel was the barrier.)  Returns the EXCLUSIVE prefix of the calling thread; *total = the block's composition
+// (valid in every thread).  sh must hold NW entries.
+template <int NW>
+__device__ __forceinline__ HF hf_block_scan(HF f, uint2 *sh, HF *total)
+{
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const HF g = hf_shfl_up(f, o);
+    if (lane >= o) f = hf_then(g, f);
+  }
+  if (lane == 31) sh[warp] = make_uint2(f.lo, f.hi);
+  __syncthreads();
+  if (warp == 0) {
+    const uint2 t = lane < NW ? sh[lane] : make_uint2(HF_IDENT_LO, HF_IDENT_HI);
+    HF w{t.x, t.y};
+#pragma unroll
+    for (int o = 1; o < NW; o <<= 1) {
+      const HF g = hf_shfl_up(w, o);
+      if (lane >= o) w = hf_then(g, w);
+    }
+    if (lane < NW) sh[lane] = make_uint2(w.lo, w.hi);  // inclusive over warps
+  }
+  __syncthreads();
+  HF ex = hf_shfl_up(f, 1);  // inclusive of the previous lane = exclusive of this one, inside the warp
+  if (lane == 0) ex = HF{HF_IDENT_LO, HF_IDENT_HI};
+  if (warp) {
+    const uint2 p = sh[warp - 1];
+    ex = hf_then(HF{p.x, p.y}, ex);
+  }
+  const uint2 t = sh[NW - 1];
+  *total = HF{t.x, t.y};
+  return ex;
+}
+
 // the 32 bytes of chunk g (zero beyond the text); returns how many of them are text
 __device__ __forceinline__ int href_load32(const uint8_t *__restrict__ t, uint64_t n, uint64_t c0, bool aligned, uint32_t (&w)[8])
 {
@@ -517,7 +557,7 @@ href_compose_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, uin
                     uint2 *__restrict__ bfun /*per block*/)
 {
   __shared__ uint32_t s_nib[256];
-  __shared__ uint2 sh[256];
+  __shared__ uint2 sh[8];
   s_nib[threadIdx.x] = g_href_nib[threadIdx.x];
   __syncthreads();
   const uint64_t c0 = ((uint64_t) blockIdx.x * 256 + threadIdx.x) * HREF_CHUNK;
@@ -530,18 +570,10 @@ href_compose_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, uin
       const uint32_t sel = s_nib[(w[q >> 2] >> (8 * (q & 3))) & 0xFFu];
       f = HF{__byte_perm(f.lo, f.hi, sel), __byte_perm(f.lo, f.hi, sel >> 16)};
     }
-  // inclusive scan under composition (Hillis-Steele in shared memory; order matters: earlier first)
-  sh[threadIdx.x] = make_uint2(f.lo, f.hi);
-  __syncthreads();
-  for (int o = 1; o < 256; o <<= 1) {
-    const uint2 mine = sh[threadIdx.x], prev = threadIdx.x >= o ? sh[threadIdx.x - o] : make_uint2(HF_IDENT_LO, HF_IDENT_HI);
-    __syncthreads();
-    const HF c = hf_then(HF{prev.x, prev.y}, HF{mine.x, mine.y});
-    sh[threadIdx.x] = make_uint2(c.lo, c.hi);
-    __syncthreads();
-  }
-  tfun[(uint64_t) blockIdx.x * 256 + threadIdx.x] = threadIdx.x ? sh[threadIdx.x - 1] : make_uint2(HF_IDENT_LO, HF_IDENT_HI);
-  if (threadIdx.x == 255) bfun[blockIdx.x] = sh[255];
+  HF total;
+  const HF ex = hf_block_scan<8>(f, sh, &total);
+  tfun[(uint64_t) blockIdx.x * 256 + threadIdx.x] = make_uint2(ex.lo, ex.hi);
+  if (threadIdx.x == 255) bfun[blockIdx.x] = make_uint2(total.lo, total.hi);
 }
 
 // thread the state through the blocks: bstate[b] = state at the first byte of block b.  One block; a thread composes
@@ -551,7 +583,7 @@ href_compose_kernel(const uint8_t *__restrict__ t, uint64_t n, bool aligned, uin
 constexpr int HREF_BS_PER = 16;
 __global__ void __launch_bounds__(1024) href_blockstate_kernel(const uint2 *__restrict__ bfun, uint64_t nblocks, uint8_t *__restrict__ bstate)
 {
-  __shared__ uint2 sh[1024];
+  __shared__ uint2 sh[32];
   __shared__ int s_state;
   if (threadIdx.x == 0) s_state = HS_START;
   __syncthreads();
@@ -563,17 +595,10 @@ __global__ void __launch_bounds__(1024) href_blockstate_kernel(const uint2 *__re
         const uint2 g = bfun[i0 + j];
         f = hf_then(f, HF{g.x, g.y});
       }
-    sh[threadIdx.x] = make_uint2(f.lo, f.hi);
-    __syncthreads();
-    for (int o = 1; o < 1024; o <<= 1) {
-      const uint2 mine = sh[threadIdx.x], prev = threadIdx.x >= o ? sh[threadIdx.x - o] : make_uint2(HF_IDENT_LO, HF_IDENT_HI);
-      __syncthreads();
-      const HF c = hf_then(HF{prev.x, prev.y}, HF{mine.x, mine.y});
-      sh[threadIdx.x] = make_uint2(c.lo, c.hi);
-      __syncthreads();
-    }
+    HF total;
+    const HF ex = hf_block_scan<32>(f, sh, &total);
     const int st0 = s_state;
-    int st = threadIdx.x ? hf_at(HF{sh[threadIdx.x - 1].x, sh[threadIdx.x - 1].y}, st0) : st0;
+    int st = hf_at(ex, st0);
     for (int j = 0; j < HREF_BS_PER; j++)
       if (i0 + j < nblocks) {
         bstate[i0 + j] = (uint8_t) st;
@@ -581,7 +606,7 @@ __global__ void __launch_bounds__(1024) href_blockstate_kernel(const uint2 *__re
         st = hf_at(HF{g.x, g.y}, st);
       }
     __syncthreads();
-    if (threadIdx.x == 1023) s_state = hf_at(HF{sh[1023].x, sh[1023].y}, st0);
+    if (threadIdx.x == 0) s_state = hf_at(total, st0);
     __syncthreads();
   }
 }
