@@ -183,6 +183,33 @@ def main_nccl():
         assert sum(counts) == total
         mr.destroy()
 
+    # reduce(cull) of a factored KMV hands the key array over as header-less rows (the shared value kept once); a second
+    # aggregate() sends such rows as they are: 8- and 16-byte keys, with and without a value
+    def cull_shard(q, kb, vb):
+        rs = np.random.RandomState(77 * q + kb + vb)
+        return [(rs.randint(0, 40, size=kb // 4).astype("<u4").tobytes(), b"\x07" * vb) for _ in range(3000)]
+
+    for kb, vb in ((8, 4), (16, 8), (16, 0), (8, 0)):
+        mr = g.MapReduce(device=local, rank=rank, nranks=world, unique_id=uid)
+        mr.kv_add(cull_shard(rank, kb, vb))
+        mr.collate()
+        nu = mr.reduce("cull")
+        want = sorted({rec for q in range(world) for rec in cull_shard(q, kb, vb) if orc.hashlittle(rec[0], world) % world == rank})
+        assert sorted(mr.scan_kv()) == want, f"cull rows kb {kb} vb {vb}: wrong pairs on rank {rank}"
+        # every rank appends the same pairs once more; the next exchange carries rows and records mixed per rank
+        if rank % 2 == 0:
+            mr.kv_add(cull_shard(rank, kb, vb)[:500], addflag=1)
+        else:
+            mr.kv_add([], addflag=1)
+        extra = sum(500 for q in range(world) if q % 2 == 0)
+        assert mr.aggregate() == nu + extra
+        want2 = sorted(want + [rec for q in range(0, world, 2) for rec in cull_shard(q, kb, vb)[:500] if orc.hashlittle(rec[0], world) % world == rank])
+        assert sorted(mr.scan_kv()) == want2, f"cull rows + append kb {kb} vb {vb}: wrong pairs on rank {rank}"
+        assert mr.convert() == nu
+        mr.reduce("count")
+        assert sorted(k for k, _ in mr.scan_kv()) == [k for k, _ in want]
+        mr.destroy()
+
     # R-MAT with one drand48 stream per rank (oink/rmat.cpp:94 srand48(seed+me)) + degree, vs the reference run with P virtual ranks
     import json
 
