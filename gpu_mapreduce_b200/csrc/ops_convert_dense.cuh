@@ -35,7 +35,17 @@ constexpr uint32_t DENSE_MASK = DENSE_SLOTS - 1;
 // the load -> compare -> atomic -> check chain of one key at a time, hence the batches of four below.
 constexpr uint32_t DENSE_CACHE = 57344;
 constexpr uint32_t DENSE_MULT = 0x278DC01u;         // odd; spreads consecutive integers over the 26-bit range
-constexpr uint32_t DENSE_ROUND_LIMIT = (1u << 20) - 1;
+// A round = the keys a block takes between two sweeps of its cache.  MRGPU_DENSE_LAZY (default): a sweep sends to the
+// table, and resets, only what it must -- entries it evicts and entries whose 20-bit count could overflow before the
+// next sweep (count >= 2^19, rounds of at most 2^19 keys); all others keep counting and reach the table once, at the
+// end.  With 0 every sweep flushes every entry (rounds of < 2^20 keys): on the IntCount stream one RED in four was
+// such a flush (ncu: 2.46e8 RED sectors for 2^30 pairs; simulated, tools/cache_sim.c: 18.0 % misses + 4.9 % flushes
+// against 16.2 % + 4.3 % with the lazy sweep).
+#ifndef MRGPU_DENSE_LAZY
+#define MRGPU_DENSE_LAZY 1
+#endif
+constexpr uint32_t DENSE_ROUND_LIMIT = MRGPU_DENSE_LAZY ? (1u << 19) : (1u << 20) - 1;
+constexpr uint32_t DENSE_FLUSH_AT = 1u << 19;
 #ifndef MRGPU_DENSE_KEEP
 #define MRGPU_DENSE_KEEP 2
 #endif
@@ -118,11 +128,11 @@ __device__ __forceinline__ void dense_count4(const uint32_t (&key)[4], unsigned 
 }
 
 // cache -> table; counts back to zero, tags of keys that earned their slot stay
-__device__ __forceinline__ void dense_flush(unsigned *__restrict__ cache, unsigned *__restrict__ table)
+__device__ __forceinline__ void dense_flush(unsigned *__restrict__ cache, unsigned *__restrict__ table, bool final)
 {
   for (uint32_t i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x) {
     const uint32_t e = cache[i], c = e >> 12;
-    if (c) {
+    if (c && (!MRGPU_DENSE_LAZY || final || c < DENSE_KEEP || c >= DENSE_FLUSH_AT)) {
       // h lies in [lo, lo + 1171) where lo = ceil(i * 2^26 / DENSE_CACHE), and its low 11 bits are tag - 1
       const uint32_t lo = (uint32_t) ((((uint64_t) i << DENSE_BITS) + DENSE_CACHE - 1) / DENSE_CACHE);
       const uint32_t h = lo + (((e & 0xFFFu) - 1u - lo) & 2047u);
@@ -256,7 +266,7 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
       bad = true;
       continue;
     }
-    dense_flush(cache, table);
+    dense_flush(cache, table, it1 >= iters);
     __syncthreads();
   }
   if (MODE == 0 || MODE == 3) {  // the few keys after the last full vector
