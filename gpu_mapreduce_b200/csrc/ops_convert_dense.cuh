@@ -80,12 +80,66 @@ __device__ __forceinline__ void dense_slot(uint32_t key, uint32_t &slot, uint32_
   tag = (h & 2047u) + 1u;
 }
 
+// A/B variant, off by default (measured: no gain).  ncu shows the L1 data pipe 87 % busy in this kernel, 45 % of its
+// wavefronts from shared atomics and two thirds of those counted as bank-conflict replays; with Zipf's hottest key in
+// 3.7 of a warp's 32 lanes, a model in which lanes on the same word are served one per pass gives 6.8 passes per
+// atomic instruction against 3.7 for distinct addresses alone.  MRGPU_DENSE_DEDUP=1 lets lanes that hold one of two
+// keys the warp has lately seen several times per instruction (learned from the stream) elect a leader that adds for
+// all of them; =2 fixes the two keys to the stream's hottest (0 and 1).  Fused pass at 2^30 keys: 2.511 ms without,
+// 2.452 with the fixed keys, 2.591 with learning -- so lanes on the same word are evidently merged by the hardware
+// and the replays are the ordinary bank conflicts of 32 random words (3.7 passes, twice as many wavefronts for an
+// atomic as for a load).
+#ifndef MRGPU_DENSE_DEDUP
+#define MRGPU_DENSE_DEDUP 0
+#endif
+struct DenseHot {
+  uint32_t k0 = 0xFFFFFFFFu, k1 = 0xFFFFFFFFu;  // tracked keys (no valid key is >= 2^26)
+  uint32_t s0 = 0, s1 = 0;                      // lanes they were found in since the last review
+  uint32_t tick = 0;
+};
+
 // four keys at a time: the four tag loads are independent, then the four updates
-__device__ __forceinline__ void dense_count4(const uint32_t (&key)[4], unsigned valid_mask, unsigned *__restrict__ cache, unsigned *__restrict__ table)
+__device__ __forceinline__ void dense_count4(const uint32_t (&key)[4], unsigned valid_mask, unsigned *__restrict__ cache, unsigned *__restrict__ table,
+                                             DenseHot &hot)
 {
   uint32_t slot[4], tag[4], e[4];
 #pragma unroll
   for (int q = 0; q < 4; q++) dense_slot(key[q], slot[q], tag[q]);
+#if MRGPU_DENSE_DEDUP
+  uint32_t wgt[4];
+  {
+    const unsigned act = __activemask(), lt = lanemask_lt();
+    // the lanes taking part agree on the two keys by construction, but nothing else in the kernel depends on that:
+    // take them from the first lane, so that a group can never mix lanes that compared against different keys
+#if MRGPU_DENSE_DEDUP == 2  // timing experiment: the two hottest keys of the IntCount stream, no learning
+    hot.k0 = 0, hot.k1 = 1;
+#else
+    hot.k0 = __shfl_sync(act, hot.k0, __ffs(act) - 1);
+    hot.k1 = __shfl_sync(act, hot.k1, __ffs(act) - 1);
+#endif
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const bool v = (valid_mask >> q) & 1u;
+      const bool is0 = v && key[q] == hot.k0, is1 = v && key[q] == hot.k1;
+      const unsigned m0 = __ballot_sync(act, is0), m1 = __ballot_sync(act, is1);
+      hot.s0 += __popc(m0);
+      hot.s1 += __popc(m1);
+      const unsigned mine = is0 ? m0 : (is1 ? m1 : 0u);
+      wgt[q] = mine ? ((mine & lt) ? 0u : (uint32_t) __popc(mine)) : 1u;
+    }
+    // review every 16 calls: the key of the lowest active lane challenges the weaker of the two
+    if (MRGPU_DENSE_DEDUP != 2 && (++hot.tick & 15u) == 0) {
+      const uint32_t x = __shfl_sync(act, key[0], __ffs(act) - 1);
+      const uint32_t c = (uint32_t) __popc(__ballot_sync(act, (valid_mask & 1u) && key[0] == x));
+      if (x != hot.k0 && x != hot.k1 && c >= 2) {  // seen c times in one instruction; s counts 64 instructions
+        if (hot.s0 <= hot.s1) {
+          if (c * 32u > hot.s0) hot.k0 = x;
+        } else if (c * 32u > hot.s1) hot.k1 = x;
+      }
+      hot.s0 = hot.s1 = 0;
+    }
+  }
+#endif
 #if MRGPU_DENSE_EXPERIMENT == 4
   // A/B variant (measured: 2.74 ms against 2.61 for the fused pass, 2.262 against 2.261 for the count alone, so not
   // the default): one RETURNING shared atomic per key instead of a load plus an atomic.  The add is speculative: the
@@ -120,6 +174,11 @@ __device__ __forceinline__ void dense_count4(const uint32_t (&key)[4], unsigned 
     if (t != tag[q]) atomicAdd(&table[key[q]], 1u);
 #elif MRGPU_DENSE_EXPERIMENT == 3  // timing experiment: only the tag loads
     if (t == 0xFFFu) atomicAdd(&table[key[q]], 1u);
+#elif MRGPU_DENSE_DEDUP
+    if (wgt[q]) {  // 0: another lane of the warp adds for this pair
+      if (t == tag[q]) atomicAdd(&cache[slot[q]], wgt[q] << 12);
+      else atomicAdd(&table[key[q]], wgt[q]);
+    }
 #else
     if (t == tag[q]) atomicAdd(&cache[slot[q]], 0x1000u);
     else atomicAdd(&table[key[q]], 1u);
@@ -159,6 +218,7 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
   if (a.vb >= 4) v0a = *(const uint32_t *) (a.data + a.voff);
   if (a.vb == 8) v0b = *(const uint32_t *) (a.data + a.voff + 4);
   bool bad = false;
+  DenseHot hot;
   const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
   const uint64_t tid0 = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
   // keys a block takes per loop iteration; a round ends before any cache count can reach 2^20
@@ -189,8 +249,8 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
             if (any >= DENSE_SLOTS) bad = true;
             else if (!bad) {
               const uint32_t k0[4] = {r[u][0], r[u][1], r[u][2], r[u][3]}, k1[4] = {r[u][4], r[u][5], r[u][6], r[u][7]};
-              dense_count4(k0, 0xFu, cache, table);
-              dense_count4(k1, 0xFu, cache, table);
+              dense_count4(k0, 0xFu, cache, table, hot);
+              dense_count4(k1, 0xFu, cache, table, hot);
             }
           }
         }
@@ -209,7 +269,7 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
             const uint32_t k[4] = {(uint32_t) r[u].x, (uint32_t) r[u].y, (uint32_t) r[u].z, (uint32_t) r[u].w};
             kor |= k[0] | k[1] | k[2] | k[3];
             if ((k[0] | k[1] | k[2] | k[3]) >= DENSE_SLOTS) bad = true;
-            else if (!bad) dense_count4(k, 0xFu, cache, table);
+            else if (!bad) dense_count4(k, 0xFu, cache, table, hot);
           }
         }
       } else if (MODE == 1) {
@@ -236,7 +296,7 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
               kor |= k[q];
             }
           }
-          if (!bad) dense_count4(k, vm, cache, table);
+          if (!bad) dense_count4(k, vm, cache, table, hot);
         }
       } else {
         uint32_t k[4];
@@ -257,7 +317,7 @@ dense_count_kernel(DenseArgs a, unsigned *__restrict__ table, unsigned long long
             kor |= k[q];
           }
         }
-        if (!bad) dense_count4(k, vm, cache, table);
+        if (!bad) dense_count4(k, vm, cache, table, hot);
       }
     }
     if (__syncthreads_or(bad)) {
