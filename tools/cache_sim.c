@@ -63,5 +63,30 @@ int main(int argc, char **argv)
         printf("mode %d keep %d round %7llu: misses %.4f + flush REDs %.4f = %.4f of the pairs\n", mode, keep, (unsigned long long) rnd, (double) miss / n,
                (double) flush / n, (double) (miss + flush) / n);
       }
+  // lane-group-private caches: the warp's lanes are split into G groups, each with CACHE / G entries in its own banks
+  // (fewer bank conflicts per instruction, smaller caches): RED fraction of one group's share of the block's stream
+  for (uint32_t G = 1; G <= 32; G <<= 1) {
+    const uint32_t C = CACHE / G;
+    const uint64_t ng = n / G, rnd = (1u << 19) / G;
+    memset(tag, 0xFF, CACHE * 4);
+    memset(cnt, 0, CACHE * 4);
+    uint64_t miss = 0, flush = 0;
+    for (uint64_t i = 0; i < ng; i++) {
+      const uint32_t k = keys[i * G];
+      const uint32_t h = (k * 0x278DC01u) & ((1u << 26) - 1);
+      const uint32_t a = (uint32_t) (((uint64_t) (h << 6) * C) >> 32);
+      if (tag[a] == k) cnt[a]++;
+      else if (tag[a] == 0xFFFFFFFFu) { tag[a] = k; cnt[a] = 1; }
+      else miss++;
+      if ((i + 1) % rnd == 0 || i + 1 == ng)
+        for (uint32_t s2 = 0; s2 < C; s2++) {
+          if (!cnt[s2]) continue;
+          if (i + 1 == ng) { flush++; cnt[s2] = 0; }
+          else if (cnt[s2] < 2) { flush++; tag[s2] = 0xFFFFFFFFu; cnt[s2] = 0; }
+        }
+    }
+    printf("groups %2u (%5u entries each): misses %.4f + flush REDs %.4f = %.4f of the pairs\n", G, C, (double) miss / ng, (double) flush / ng,
+           (double) (miss + flush) / ng);
+  }
   return 0;
 }
