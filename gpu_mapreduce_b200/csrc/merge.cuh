@@ -107,26 +107,42 @@ descent_sample_kernel(const K *__restrict__ k, uint64_t n, uint64_t win, unsigne
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, (unsigned long long) c);
 }
 
-// longest run: run r spans [r ? dpos[r-1] : 0, r < D ? dpos[r] : n); best = max of (length << 32 | r)
+// One pass over the keys: how many descents there are (k[i] < k[i-1]), and the run that holds the middle element --
+// it starts at the last descent at or before n/2 and ends at the first one after it.  A run that covers at least half
+// of the keys contains the middle element, so no list of descents is needed to find it.
+// out[0] += descents, out[1] = max(start), out[2] = min(end); the caller sets out = {0, 0, n}.
+template <typename K>
 __global__ void __launch_bounds__(256)
-longest_run_kernel(const uint32_t *__restrict__ dpos, uint64_t D, uint64_t n, unsigned long long *best)
+descent_scan_kernel(const K *__restrict__ k, uint64_t n, uint64_t mid, unsigned long long *out)
 {
-  __shared__ unsigned long long sh[8];
-  const uint64_t r = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-  unsigned long long v = 0;
-  if (r <= D) {
-    const uint64_t a = r ? dpos[r - 1] : 0, b = r < D ? dpos[r] : n;
-    v = ((unsigned long long) (b - a) << 32) | r;
-  }
+  __shared__ unsigned long long sh[3][8];
+  unsigned long long cnt = 0, a = 0, b = n;
+  const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x + 1; i < n; i += stride)
+    if (__ldg(k + i) < __ldg(k + i - 1)) {
+      cnt++;
+      if (i <= mid) a = i > a ? i : a;
+      else b = i < b ? i : b;
+    }
   for (int o = 16; o; o >>= 1) {
-    const unsigned long long t = __shfl_down_sync(0xFFFFFFFFu, v, o);
-    v = t > v ? t : v;
+    cnt += __shfl_down_sync(0xFFFFFFFFu, cnt, o);
+    const unsigned long long ta = __shfl_down_sync(0xFFFFFFFFu, a, o), tb = __shfl_down_sync(0xFFFFFFFFu, b, o);
+    a = ta > a ? ta : a;
+    b = tb < b ? tb : b;
   }
-  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  if ((threadIdx.x & 31) == 0) sh[0][threadIdx.x >> 5] = cnt, sh[1][threadIdx.x >> 5] = a, sh[2][threadIdx.x >> 5] = b;
   __syncthreads();
   if (threadIdx.x == 0) {
-    for (int w = 1; w < 8; w++) v = sh[w] > v ? sh[w] : v;
-    if (v) atomicMax(best, v);
+    for (int w = 1; w < 8; w++) {
+      cnt += sh[0][w];
+      a = sh[1][w] > a ? sh[1][w] : a;
+      b = sh[2][w] < b ? sh[2][w] : b;
+    }
+    if (cnt) {
+      atomicAdd(out, cnt);
+      atomicMax(out + 1, a);
+      atomicMin(out + 2, b);
+    }
   }
 }
 

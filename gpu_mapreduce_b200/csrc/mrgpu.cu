@@ -63,6 +63,10 @@ struct mrgpu_mr {
   // setting "presorted": convert() looks for a long ascending run among the sort keys (the previous round's output of
   // an iterative job) and, if one covers half of them, sorts only the rest and merges (merge.cuh); 0 = always sort
   int64_t presorted = 1;
+  // which bytes of a 16-byte uniform key varied in the last convert(): the next one extracts its sort keys on that
+  // guess while it checks it, instead of scanning the keys beforehand (ops_convert.cuh)
+  int guess_nvb = -1;
+  unsigned char guess_pos[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   // setting "hbm_budget" (MB, 0 = unlimited): a KeyValue whose device part outgrows it moves to pinned host memory
   // piece by piece; convert / reduce / stats / pages / scan work on such stores (ops_spool.cuh)
   int64_t hbm_budget = 0;

@@ -40,7 +40,8 @@ struct CompactKey {
 template <typename K, int PMODE /*0 none, 1 val32, 2 val64, 3 idx*/, bool IDENT /*key bytes 0..kb-1, kb<=8, word loads*/, bool KEY16 = false>
 __global__ void __launch_bounds__(256)
 extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs, uint32_t koff, uint32_t voff, uint32_t kb, CompactKey ck,
-                       K *__restrict__ keys, void *__restrict__ pay, unsigned long long *hist, unsigned long long *vdiff, bool vec16 = false)
+                       K *__restrict__ keys, void *__restrict__ pay, unsigned long long *hist, unsigned long long *vdiff, bool vec16 = false,
+                       unsigned *wmask = nullptr /* KEY16: OR of (key ^ first key), four words */)
 {
   __shared__ unsigned sh[sizeof(K) * RADIX];
   for (int i = threadIdx.x; i < (int) sizeof(K) * RADIX; i += blockDim.x) sh[i] = 0;
@@ -53,6 +54,12 @@ extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs
   unsigned prev[sizeof(K)], run[sizeof(K)];
 #pragma unroll
   for (int b = 0; b < (int) sizeof(K); b++) prev[b] = 0, run[b] = 0;
+  unsigned long long f_lo = 0, f_hi = 0, acc_lo = 0, acc_hi = 0;  // KEY16 with wmask: the first key, and what differs from it
+  if (KEY16 && wmask) {
+    const uint32_t *w = (const uint32_t *) (data + koff);
+    f_lo = (unsigned long long) w[0] | ((unsigned long long) w[1] << 32);
+    f_hi = (unsigned long long) w[2] | ((unsigned long long) w[3] << 32);
+  }
   // A thread's successive records lie 256 apart inside one tile of 4096, not a whole grid apart: in input that is in
   // key order already (the bulk of an iterative job's later rounds) the high digits then repeat from one record of a
   // thread to the next and stay in its run counter; with a grid-wide stride every record ended a run, and the 32
@@ -83,6 +90,8 @@ extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs
         lo = (unsigned long long) w[0] | ((unsigned long long) w[1] << 32);
         hi = (unsigned long long) w[2] | ((unsigned long long) w[3] << 32);
       }
+      acc_lo |= lo ^ f_lo;
+      acc_hi |= hi ^ f_hi;
       unsigned long long k64 = 0;
 #pragma unroll
       for (int q = 0; q < 8; q++)
@@ -113,6 +122,14 @@ extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs
   }
   hist_flush<K>(prev, run, sh, hist);
   if (__syncthreads_or(vd) && threadIdx.x == 0) *vdiff = 1;
+  if (KEY16 && wmask) {
+    const uint32_t a[4] = {(uint32_t) acc_lo, (uint32_t) (acc_lo >> 32), (uint32_t) acc_hi, (uint32_t) (acc_hi >> 32)};
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+      const uint32_t r = __reduce_or_sync(0xFFFFFFFFu, a[w]);
+      if ((threadIdx.x & 31) == 0 && r) atomicOr(&wmask[w], r);
+    }
+  }
 }
 
 // IntCount layout {kb=4, vb=4, key, value} in one 16-byte load per record
@@ -265,33 +282,20 @@ static int sort_keys_presorted(mrgpu_mr *mr, K *k0, K *k1, uint64_t n, unsigned 
   fetch_small(mr, 1);
   if (mr->h_small[0] > WIN * NBLK / 16) return -1;
 
-  auto desc = [=] __device__(uint64_t i) -> bool { return i > 0 && __ldg(k0 + i) < __ldg(k0 + i - 1); };
-  FlagTiles runs;
-  flag_tiles(pool, n, desc, runs, mr->d_small, "presorted_count", (double) n * sizeof(K));
-  fetch_small(mr, 1);
+  const unsigned long long init[3] = {0ull, 0ull, (unsigned long long) n};
+  {
+    MR_CUDA(cudaMemcpyAsync(mr->d_small, init, sizeof(init), cudaMemcpyHostToDevice, s));
+    ProfScope ps(pool, "presorted_scan", (double) n * sizeof(K));
+    descent_scan_kernel<K><<<grid_for(n, 256 * 16, 16), 256, 0, s>>>(k0, n, n / 2, mr->d_small);
+    MR_CUDA(cudaGetLastError());
+  }
+  fetch_small(mr, 3);
   const uint64_t D = mr->h_small[0];
   if (D == 0) return 0;
   if (D > n / 16) return -1;
-  Buf<uint32_t> dpos(pool, D);
-  {
-    uint32_t *dp = dpos.p;
-    flag_sink(pool, runs, desc, [=] __device__(uint64_t i, unsigned long long e, unsigned long long f) {
-      if (f) dp[e] = (uint32_t) i;
-    }, "presorted_runs", (double) n * sizeof(K) + 4.0 * D);
-  }
-  MR_CUDA(cudaMemsetAsync(mr->d_small, 0, 8, s));
-  longest_run_kernel<<<(unsigned) ((D + 1 + 255) / 256), 256, 0, s>>>(dpos.p, D, n, mr->d_small);
-  MR_CUDA(cudaGetLastError());
-  fetch_small(mr, 1);
-  const uint64_t L = mr->h_small[0] >> 32, r = mr->h_small[0] & 0xFFFFFFFFull;
+  // the run that holds the middle element: [a, b)
+  const uint64_t a = mr->h_small[1], b = mr->h_small[2], L = b - a, R = n - L;
   if (L < n / 2) return -1;
-  uint32_t a32 = 0;
-  if (r) {
-    MR_CUDA(cudaMemcpyAsync(&a32, dpos.p + (r - 1), 4, cudaMemcpyDeviceToHost, s));
-    sync(mr);
-  }
-  dpos.release();
-  const uint64_t a = a32, b = a + L, R = n - L;
   Buf<K> r0(pool, R), r1(pool, R);
   if (a) MR_CUDA(cudaMemcpyAsync(r0.p, k0, a * sizeof(K), cudaMemcpyDeviceToDevice, s));
   if (n > b) MR_CUDA(cudaMemcpyAsync(r0.p + a, k0 + b, (n - b) * sizeof(K), cudaMemcpyDeviceToDevice, s));
@@ -301,8 +305,10 @@ static int sort_keys_presorted(mrgpu_mr *mr, K *k0, K *k1, uint64_t n, unsigned 
   return 1;
 }
 
+// verify: `ck` is a guess (the bytes that varied last time).  The extract pass then also ORs every key against the
+// first one; if a byte outside the guess varies, false is returned and nothing has changed.  key0 is filled in here.
 template <typename K, int PMODE>
-static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, const std::vector<uint8_t> &key0)
+static bool convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, std::vector<uint8_t> &key0, bool verify = false)
 {
   DevKV *kv = mr->kv;
   Pool &pool = mr->pool;
@@ -319,6 +325,8 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
   Buf<unsigned long long> hist(pool, 8 * RADIX + 8);
   MR_CUDA(cudaMemsetAsync(hist.p, 0, (8 * RADIX + 8) * 8, s));
   unsigned long long *vdiff = hist.p + 8 * RADIX;
+  Buf<unsigned> wmask(pool, 4);
+  if (verify) MR_CUDA(cudaMemsetAsync(wmask.p, 0, 16, s));
 
   // 1. one read of the KV: sort keys, payload, byte histograms
   {
@@ -329,10 +337,25 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
     extract_uniform_kernel<K, PMODE, true><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p, vdiff);
   else if (kb == 16 && rs % 4 == 0 && koff % 4 == 0 && ((uintptr_t) kv->data % 16) == 0)
     extract_uniform_kernel<K, PMODE, false, true><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p, vdiff,
-                                                                                         rs % 16 == 0 && koff % 16 == 0);
+                                                                                         rs % 16 == 0 && koff % 16 == 0, verify ? wmask.p : nullptr);
+  else if (verify) MR_FAIL(MRGPU_EINVAL, "internal: convert on a guessed byte set needs the 16-byte-key extract");
   else
     extract_uniform_kernel<K, PMODE, false><<<grid_for(n, 256 * 8, 8), 256, 0, s>>>(kv->data, n, rs, koff, voff, kb, ck, k0.p, p0.p, hist.p, vdiff);
   MR_CUDA(cudaGetLastError());
+  }
+
+  if (verify) {
+    unsigned hm[4];
+    key0.resize(kb);
+    MR_CUDA(cudaMemcpyAsync(hm, wmask.p, 16, cudaMemcpyDeviceToHost, s));
+    MR_CUDA(cudaMemcpyAsync(key0.data(), kv->data + koff, kb, cudaMemcpyDeviceToHost, s));
+    sync(mr);
+    for (uint32_t q = 0; q < 16; q++)
+      if ((hm[q / 4] >> (8 * (q % 4))) & 0xFFu) {
+        bool in = false;
+        for (int j = 0; j < ck.nvb; j++) in = in || ck.pos[j] == q;
+        if (!in) return false;  // a byte the guess does not cover varies: the caller scans the keys and comes back
+      }
   }
 
   // 2. stable LSD radix sort on the varying bytes only
@@ -472,7 +495,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
       throw;
     }
     mr->kmv = kmv;
-    return;
+    return true;
   }
 
   // 4. KMV record sizes -> offs[u]
@@ -551,6 +574,7 @@ static void convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, cons
     throw;
   }
   mr->kmv = kmv;
+  return true;
 }
 
 static void convert_general(mrgpu_mr *mr)
@@ -728,7 +752,28 @@ static void convert_resident(mrgpu_mr *mr)
       bool ident = kv->kb <= 8;
       std::vector<uint8_t> key0(kv->kb);
       bool ok = true;
-      if (ident) {
+      // 16-byte keys again (an iterative job's next round): extract on the byte set of last time, checked on the way
+      if (!ident && kv->kb == 16 && mr->guess_nvb >= 0 && lay.rs % 4 == 0 && lay.koff % 4 == 0 && ((uintptr_t) kv->data % 16) == 0 && n >= (1u << 16)) {
+        ck.nvb = mr->guess_nvb;
+        memcpy(ck.pos, mr->guess_pos, 8);
+        const int pm = kv->vb == 0 ? 0 : ((kv->vb == 4 && lay.voff % 4 == 0) ? 1 : ((kv->vb == 8 && lay.voff % 4 == 0) ? 2 : 3));
+#define CONV_GUESS(K, PM) done = convert_uniform<K, PM>(mr, ck, false, key0, true)
+        if (ck.nvb <= 4) {
+          if (pm == 0) CONV_GUESS(uint32_t, 0);
+          else if (pm == 1) CONV_GUESS(uint32_t, 1);
+          else if (pm == 2) CONV_GUESS(uint32_t, 2);
+          else CONV_GUESS(uint32_t, 3);
+        } else {
+          if (pm == 0) CONV_GUESS(uint64_t, 0);
+          else if (pm == 1) CONV_GUESS(uint64_t, 1);
+          else if (pm == 2) CONV_GUESS(uint64_t, 2);
+          else CONV_GUESS(uint64_t, 3);
+        }
+#undef CONV_GUESS
+        ck = CompactKey{};
+      }
+      if (done) {
+      } else if (ident) {
         ck.nvb = (int) kv->kb;
         for (int q = 0; q < 8; q++) ck.pos[q] = (unsigned char) q;
       } else if (kv->kb <= 1024) {
@@ -761,9 +806,13 @@ static void convert_resident(mrgpu_mr *mr)
           }
         if (nv > 8 || kv->kb > 256) ok = false;
         ck.nvb = nv;
+        if (ok && kv->kb == 16) {
+          mr->guess_nvb = nv;
+          memcpy(mr->guess_pos, ck.pos, 8);
+        }
       } else
         ok = false;
-      if (ok) {
+      if (ok && !done) {
         bool small = ck.nvb <= 4;
         bool v32 = kv->vb == 4 && (lay.voff % 4) == 0;
         bool v64 = kv->vb == 8 && (lay.voff % 4) == 0;

@@ -959,6 +959,25 @@ def test_rmat_later_rounds_merge_instead_of_sorting(MR):
     assert len(np.unique(runs[1][1])) == len(runs[1][1])
 
 
+def test_convert_on_guessed_key_bytes_falls_back_when_more_bytes_vary(MR, oracle):
+    """the second convert() of 16-byte keys on one handle extracts its sort keys on the byte set of the first while
+    checking it; keys that vary in other bytes as well must take the scan and come out right, and so must keys that
+    vary in fewer"""
+    mr = MR()
+    mr.prof(True)
+    for nl, n in ((7, 100_000), (20, 150_000), (20, 120_000), (5, 90_000)):
+        st0 = oracle.lib.orc_srand48(nl + n)
+        _, edges = oracle.rmat_generate(st0, n, nl, .57, .19, .19, .05, 0.0)
+        assert mr.map_rmat(n, nl, .57, .19, .19, .05, 0.0, st0, addflag=0)[0] == n
+        want = np.unique(edges, axis=0)
+        assert mr.convert() == len(want)
+        assert mr.reduce("cull") == len(want)
+        got = np.frombuffer(b"".join(k for k, _ in mr.scan_kv()), dtype=np.uint64).reshape(-1, 2)
+        assert np.array_equal(np.unique(got, axis=0), want) and len(got) == len(want)
+    calls = {t["tag"]: t["calls"] for t in mr.prof_report()[0]}
+    assert calls["convert_key_diff"] == 2  # the first call and the one whose keys outgrew the guess
+
+
 def test_presorted_run_in_the_middle_and_all_sorted(MR, oracle):
     """the long run may sit anywhere (after an exchange it follows what lower ranks sent); an input with no descent at
     all is not sorted again; 4- and 8-byte keys"""
@@ -979,7 +998,7 @@ def test_presorted_run_in_the_middle_and_all_sorted(MR, oracle):
             u, c = np.unique(keys, return_counts=True)
             assert mr.convert() == len(u)
             tags = {t["tag"] for t in mr.prof_report()[0]}
-            assert "presorted_count" in tags and ("merge_sorted" in tags) == (len(parts) > 1)
+            assert "presorted_scan" in tags and ("merge_sorted" in tags) == (len(parts) > 1)
             assert "onesweep_pass" not in tags or len(parts) > 1
             mr.reduce("count")
             got = dict((int.from_bytes(k, "little"), int.from_bytes(v, "little")) for k, v in mr.scan_kv())
