@@ -850,6 +850,7 @@ static void gather_impl(mrgpu_mr *mr, int numprocs)
       at_b += r[1];
     }
   }
+  kv->sorted_flag = 0;
   kv->nkv += add_n;
   kv->nbytes += add_b;
   kv->ksize += add_k;

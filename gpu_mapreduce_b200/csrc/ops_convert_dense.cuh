@@ -882,6 +882,7 @@ static bool convert_dense(mrgpu_mr *mr)
     }, "convert_dense_bins", (double) span * 4 + 12.0 * U);
     mr->dense_owner = 0;  // the sink that re-zeroes every counted slot is enqueued: clean again
     kmv->factored = true;
+    kmv->ascending = true;  // table order = ascending keys
     kmv->fval[0] = cv[0];
     kmv->fval[1] = cv[1];
     kmv->nkmv = U;

@@ -25,8 +25,10 @@ static void kv_begin_map(mrgpu_mr *mr, int addflag, bool keep_packed = false)
   if (!addflag || !mr->kv) {
     delete mr->kv;
     mr->kv = new DevKV(&mr->pool);
-  } else if (!keep_packed)
-    kv_unpack(mr, mr->kv);
+  } else {
+    mr->kv->sorted_flag = 0;  // pairs are about to be appended
+    if (!keep_packed) kv_unpack(mr, mr->kv);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -771,6 +773,7 @@ static void kv_concat(mrgpu_mr *mr, DevKV *kv, const DevKV *o)
 {
   cudaStream_t s = mr->pool.stream;
   if (!o->nkv) return;
+  kv->sorted_flag = 0;
   uint64_t base = kv->nbytes;
   bool fits = o->uniform && (kv->nkv == 0 || (kv->uniform && kv->kb == o->kb && kv->vb == o->vb));
   if (fits) {

@@ -308,6 +308,9 @@ static void reduce_impl(mrgpu_mr *mr, int functor)
       kv->nkv = U;
       kv->ksize = U * kb;
       kv->vsize = U * vb;
+      // one pair per key, in the KMV's order, key unchanged: keys that came out of the counting convert in ascending
+      // order are still in it, so sort_keys(1) on int keys / sort_keys(2) on uint64_t keys has nothing to do
+      if (kmv->factored && kmv->ascending && !shape && (kb == 4 || kb == 8)) kv->mark_sorted(kb == 4 ? 1 : 2);
     } else {
       kv->uniform = false;
       kv->reserve_offs(U + 1);

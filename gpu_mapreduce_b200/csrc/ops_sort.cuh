@@ -198,6 +198,7 @@ static void sort_keys_impl(mrgpu_mr *mr, int flag, bool by_value = false)
   const uint64_t n = kv->nkv;
   if (n >= 0xFFFFFFFFull) MR_FAIL(MRGPU_ELIMIT, "sort_keys: more than 2^32-2 pairs on one GPU is not supported yet");
   if (n < 2) return;
+  if (!by_value && kv->known_sorted(flag)) return;  // reduce() of a counting convert left them in this very order
   uint32_t nchunks = 1;
   if (absflag >= 5) {
     uint64_t maxkb = by_value ? kv->vb : kv->kb;

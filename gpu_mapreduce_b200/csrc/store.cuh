@@ -65,6 +65,19 @@ struct DevKV {
   PartPlan *plan = nullptr;
   int plan_nranks = 0;
   std::vector<uint64_t> plan_scount;
+  // The pairs are known to be in ascending order under sort_keys(sorted_flag) (1: int keys, 2: uint64_t keys): set by
+  // reduce() when its input came from the counting convert, which emits keys in ascending order.  Valid only while the
+  // store is the same (nkv and data pointer as recorded): sort_keys(flag) is then the identity and returns at once.
+  int sorted_flag = 0;
+  uint64_t sorted_n = 0;
+  const uint8_t *sorted_ptr = nullptr;
+  void mark_sorted(int flag)
+  {
+    sorted_flag = flag;
+    sorted_n = nkv;
+    sorted_ptr = data;
+  }
+  bool known_sorted(int flag) const { return flag > 0 && sorted_flag == flag && sorted_n == nkv && sorted_ptr == data && uniform; }
   uint32_t prow() const { return weighted ? kb + 4 : kb + (cval_on ? 0 : vb); }                  // bytes per stored row
   uint64_t phys_bytes() const { return packed ? (weighted ? nrows : nkv) * prow() : nbytes; }   // bytes of data in use
 
@@ -138,6 +151,7 @@ struct DevKMV {
   // (data/offs above) is then written only when somebody needs its bytes (kmv_expand: pages, device views, a
   // functor that reads multivalues); reduce's stock functors read this form directly.
   bool factored = false;
+  bool ascending = false;  // factored keys are in ascending order as unsigned integers (the counting convert's table order)
   uint32_t *fkey = nullptr, *fcnt = nullptr;  // keys: [nkmv * fkw] words (ukb = 4 * fkw bytes each); counts: [nkmv]
   uint32_t fkw = 1;
   uint64_t fcap = 0;                          // pairs allocated

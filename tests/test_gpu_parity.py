@@ -412,6 +412,45 @@ def test_sort_keys_leaves_sorted_pairs_alone_and_still_sorts_the_rest(MR, oracle
     assert H.kv_encode(mr2.scan_kv()) == oracle.sort_keys(H.kv_encode(swapped), 1)
 
 
+def test_sort_keys_after_the_counting_convert_is_free_until_the_kv_changes(MR, oracle):
+    """reduce() after the counting convert leaves keys ascending and says so; sort_keys(1) then returns at once -- but
+    not after an append, an add, a descending sort, or for another compare flag"""
+    keys = W.intcount_keys_np(0, 200_000, ndistinct=5000)
+
+    def tags_of(mr, fn):
+        mr.prof(True)
+        fn()
+        return {t["tag"] for t in mr.prof_report()[0]}
+
+    mr = MR()
+    mr.map_intcount(keys)
+    mr.collate()
+    nu = mr.reduce("count")
+    want = oracle.sort_keys(oracle.reduce(oracle.convert(oracle.intcount_map(keys)), "count"), 1)
+    assert tags_of(mr, lambda: mr.sort_keys(1)) == set()          # nothing launched
+    assert H.kv_encode(mr.scan_kv()) == want
+    assert "sort_extract" in tags_of(mr, lambda: mr.sort_keys(3))  # another compare type: the usual path
+    mr.sort_keys(1)
+    # append one small key: the order is gone and sort_keys must find that out
+    mr.kv_add([(struct.pack("<I", 0), struct.pack("<i", 7))], addflag=1)
+    assert "sort_extract" in tags_of(mr, lambda: mr.sort_keys(1))
+    got = mr.scan_kv()
+    assert [k for k, _ in got] == sorted((k for k, _ in got), key=lambda b: struct.unpack("<i", b)[0]) and len(got) == nu + 1
+    # add() of another object, and a descending sort in between
+    a, b = MR(), MR()
+    for m in (a, b):
+        m.map_intcount(keys)
+        m.collate()
+        m.reduce("count")
+    a.add(b)
+    a.sort_keys(1)
+    ks = [struct.unpack("<i", k)[0] for k, _ in a.scan_kv()]
+    assert ks == sorted(ks) and len(ks) == 2 * nu
+    b.sort_keys(-1)
+    b.sort_keys(1)
+    assert H.kv_encode(b.scan_kv()) == want
+
+
 # ------------------------------------------------------------------------------------------- compact stores
 
 @pytest.mark.parametrize("compact", [0, 1])
