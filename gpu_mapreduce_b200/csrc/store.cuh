@@ -90,16 +90,22 @@ struct DevKV {
   void reserve_bytes(uint64_t need)
   {
     if (need <= cap) return;
-    if (data && phys_bytes() && pool->try_extend(data, need)) {  // the bytes behind the store are free: no copy
-      cap = need;
-      return;
-    }
     uint64_t ncap = cap ? cap : 0;
     ncap = need > 2 * ncap ? need : 2 * ncap;
     // large stores are sized exactly when first filled; one that is being appended to (map with addflag, add,
     // gather) grows by half again so that a run of appends does not copy the whole store every time
     // (doubling up to 4 GiB: a file-by-file map copies the store once over in total instead of twice)
     if (need > (1ull << 28)) ncap = (cap && nbytes) ? std::max<uint64_t>(need, need > (4ull << 30) ? cap + cap / 2 : 2 * cap) : need;
+    if (data && phys_bytes()) {  // the bytes behind the store are free: grow in place, nothing is copied
+      if (pool->try_extend(data, ncap)) {
+        cap = ncap;
+        return;
+      }
+      if (ncap > need && pool->try_extend(data, need)) {
+        cap = need;
+        return;
+      }
+    }
     uint8_t *nd = (uint8_t *) pool->alloc(ncap);
     if (phys_bytes()) {
       ProfScope ps(*pool, "kv_grow", 2.0 * phys_bytes(), 0);
@@ -112,12 +118,18 @@ struct DevKV {
   void reserve_offs(uint64_t entries)
   {
     if (entries <= offs_cap) return;
-    if (offs && !uniform && nkv && pool->try_extend(offs, entries * 8)) {
-      offs_cap = entries;
-      return;
-    }
     uint64_t ncap = entries > 2 * offs_cap ? entries : 2 * offs_cap;
     if (entries > (1ull << 25)) ncap = (offs_cap && nkv) ? std::max<uint64_t>(entries, entries > (1ull << 29) ? offs_cap + offs_cap / 2 : 2 * offs_cap) : entries;
+    if (offs && !uniform && nkv) {
+      if (pool->try_extend(offs, ncap * 8)) {
+        offs_cap = ncap;
+        return;
+      }
+      if (ncap > entries && pool->try_extend(offs, entries * 8)) {
+        offs_cap = entries;
+        return;
+      }
+    }
     uint64_t *no = (uint64_t *) pool->alloc(ncap * 8);
     if (offs && !uniform && nkv) {
       ProfScope ps(*pool, "kv_grow", 16.0 * (nkv + 1), 0);
