@@ -56,3 +56,21 @@ def test_product_never_touches_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 src = open(os.path.join(dp, f), errors="replace").read()
                 assert "mr_oracle" not in src and "oracle/" not in src and "mrhelpers" not in src, f
+
+
+def test_settings_are_documented_and_known_to_the_library():
+    """every setting the Python mirror exposes beside the reference's public members is explained in include/mrgpu.h
+    and listed in INTEGRATION.md, and is a name the library's settings table knows (read from the source: no device
+    is needed)"""
+    ref_members = {"mapstyle", "all2all", "verbosity", "timer", "memsize", "minpage", "maxpage", "freepage", "outofcore",
+                   "zeropage", "keyalign", "valuealign"}
+    extra = [s for s in g.MapReduce._SETTINGS if s not in ref_members and s != "debug_fail_alloc"]
+    assert {"compact", "ahead", "combine", "presorted", "l2pin", "hbm_budget"} <= set(extra)
+    header = open(os.path.join(ROOT, "include", "mrgpu.h")).read()
+    integ = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    table = open(os.path.join(ROOT, "gpu_mapreduce_b200", "csrc", "mrgpu.cu")).read()
+    for s in g.MapReduce._SETTINGS:
+        assert f'{{"{s}", &mr->{s}}}' in table.replace("  ", " "), s
+    for s in extra:
+        assert f'"{s}"' in header, s
+        assert f"`{s}`" in integ, s
