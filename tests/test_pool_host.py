@@ -1,0 +1,22 @@
+"""CPU: the HBM pool's bookkeeping (best fit, split, coalesce, growth in place, trim, injected failures) and a store's
+growth, with the CUDA runtime calls replaced by host stand-ins (tests/cpp/pool_host_test.cu).  nvcc compiles the test
+because the headers hold device code; nothing is launched, so it runs without a GPU."""
+import os
+import shutil
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_pool_and_store_growth_on_the_host():
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    if not (os.path.exists(nvcc) or shutil.which(nvcc)):
+        pytest.skip("no nvcc")
+    out = os.path.join(ROOT, "tests", "cpp", "_bin", "pool_host_test")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O1", "-std=c++17", "--extended-lambda", "-w", "-o", out,
+                           os.path.join(ROOT, "tests", "cpp", "pool_host_test.cu")])
+    res = subprocess.run([out], capture_output=True, text=True)
+    assert res.returncode == 0 and "POOL_HOST_OK" in res.stdout, res.stdout + res.stderr
