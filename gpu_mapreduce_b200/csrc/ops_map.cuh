@@ -580,30 +580,7 @@ extern "C" int mrgpu_map_mr(mrgpu_mr *mr, mrgpu_mr *srcmr, int functor, int addf
 // compares only when fraction == 0; for fraction > 0 every multiply/add goes through the round-to-nearest
 // intrinsics so that no FMA contraction changes a bit.
 
-constexpr unsigned long long LCG_A = 0x5DEECE66Dull, LCG_C = 0xBull, LCG_M = (1ull << 48) - 1;
-
-// the k-step jump as an affine map: x_k = ra * x_0 + rc (mod 2^48)
-__host__ __device__ inline void lcg_affine(unsigned long long k, unsigned long long &ra, unsigned long long &rc)
-{
-  unsigned long long ba = LCG_A, bc = LCG_C;
-  ra = 1, rc = 0;
-  while (k) {
-    if (k & 1) {
-      ra = (ba * ra) & LCG_M;
-      rc = (ba * rc + bc) & LCG_M;
-    }
-    bc = (ba * bc + bc) & LCG_M;
-    ba = (ba * ba) & LCG_M;
-    k >>= 1;
-  }
-}
-
-__host__ __device__ inline void lcg_jump(unsigned long long k, unsigned long long &x)
-{
-  unsigned long long ra, rc;
-  lcg_affine(k, ra, rc);
-  x = (ra * x + rc) & LCG_M;
-}
+#include "rmat_lcg.cuh"  // LCG constants, lcg_affine / lcg_jump, rmat_threshold (host-testable: tests/cpp/rmat_host_test.cu)
 
 __device__ __forceinline__ double lcg_next(unsigned long long &x)
 {
@@ -624,14 +601,6 @@ struct RmatParams {
   // first edge costs a full O(log) jump, every later one this single affine step of T * D draws
   unsigned long long sa, sc;
 };
-
-static inline unsigned long long rmat_threshold(double t)
-{
-  const double s = ceil(t * 281474976710656.0);
-  if (!(s > 0.0)) return 0;
-  if (s >= 281474976710656.0) return 1ull << 48;
-  return (unsigned long long) s;
-}
 
 template <bool INT>
 __global__ void __launch_bounds__(256)

@@ -10,13 +10,23 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def test_pool_and_store_growth_on_the_host():
+def _build_and_run(name, ok):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     if not (os.path.exists(nvcc) or shutil.which(nvcc)):
         pytest.skip("no nvcc")
-    out = os.path.join(ROOT, "tests", "cpp", "_bin", "pool_host_test")
+    out = os.path.join(ROOT, "tests", "cpp", "_bin", name)
     os.makedirs(os.path.dirname(out), exist_ok=True)
     subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O1", "-std=c++17", "--extended-lambda", "-w", "-o", out,
-                           os.path.join(ROOT, "tests", "cpp", "pool_host_test.cu")])
+                           os.path.join(ROOT, "tests", "cpp", name + ".cu")])
     res = subprocess.run([out], capture_output=True, text=True)
-    assert res.returncode == 0 and "POOL_HOST_OK" in res.stdout, res.stdout + res.stderr
+    assert res.returncode == 0 and ok in res.stdout, res.stdout + res.stderr
+
+
+def test_pool_and_store_growth_on_the_host():
+    _build_and_run("pool_host_test", "POOL_HOST_OK")
+
+
+def test_rmat_generator_arithmetic_against_the_c_library():
+    """the restated drand48 step, the k-step jump and the integer form of "drand48() < t" (rmat_lcg.cuh) against glibc's
+    srand48 / drand48 / seed48 on the host: what makes the device generator bit-exact is checked without a device"""
+    _build_and_run("rmat_host_test", "RMAT_HOST_OK")
