@@ -104,7 +104,7 @@ __host__ __device__ __forceinline__ uint32_t hashlittle_words(const uint32_t *w,
 // 12-byte rounds, which matters on a GPU: the byte-wise tail takes a different path for every length and a warp of
 // words of 11 different lengths ran it 11 times over (ncu: 1-4 active threads per instruction, 4000 thread
 // instructions per word).  Whole-word reads stay inside the record: the key field is padded to a multiple of 4.
-__device__ __forceinline__ unsigned long long key_fingerprint(const uint8_t *k, uint32_t length, uint32_t seed)
+__host__ __device__ __forceinline__ unsigned long long key_fingerprint(const uint8_t *k, uint32_t length, uint32_t seed)
 {
   uint32_t a, b, c;
   a = b = c = 0xdeadbeefu + length + seed;

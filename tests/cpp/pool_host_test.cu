@@ -1,6 +1,6 @@
 // Host-only test of the HBM pool and of a store's growth (common.cuh, store.cuh): the CUDA runtime calls they make are
 // replaced by host stand-ins, so the allocator's bookkeeping -- best fit, split, coalesce, growth in place, trimming --
-// runs on a machine without a GPU.  Built and run by tests/test_pool_host.py (nvcc compiles it: the headers hold device
+// runs on a machine without a GPU.  Built and run by tests/test_host_logic.py (nvcc compiles it: the headers hold device
 // code; no kernel is launched).
 #include <cuda_runtime.h>
 

@@ -1,7 +1,7 @@
 // Host-only test of the R-MAT generator's arithmetic (gpu_mapreduce_b200/csrc/rmat_lcg.cuh) against the C library
 // itself: the LCG is glibc's drand48, the k-step jump equals k single steps, and the integer threshold decides
 // "drand48() < t" exactly as the double comparison of the reference does (oink/map_rmat_generate.cpp:40-50).
-// Built and run by tests/test_pool_host.py; nothing is launched on a device.
+// Built and run by tests/test_host_logic.py; nothing is launched on a device.
 #include <cuda_runtime.h>
 
 #include <stdint.h>

@@ -10,7 +10,7 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _build_and_run(name, ok):
+def _build_and_run(name, ok, *args):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     if not (os.path.exists(nvcc) or shutil.which(nvcc)):
         pytest.skip("no nvcc")
@@ -18,7 +18,7 @@ def _build_and_run(name, ok):
     os.makedirs(os.path.dirname(out), exist_ok=True)
     subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O1", "-std=c++17", "--extended-lambda", "-w", "-o", out,
                            os.path.join(ROOT, "tests", "cpp", name + ".cu")])
-    res = subprocess.run([out], capture_output=True, text=True)
+    res = subprocess.run([out] + list(args), capture_output=True, text=True)
     assert res.returncode == 0 and ok in res.stdout, res.stdout + res.stderr
 
 
@@ -30,3 +30,15 @@ def test_rmat_generator_arithmetic_against_the_c_library():
     """the restated drand48 step, the k-step jump and the integer form of "drand48() < t" (rmat_lcg.cuh) against glibc's
     srand48 / drand48 / seed48 on the host: what makes the device generator bit-exact is checked without a device"""
     _build_and_run("rmat_host_test", "RMAT_HOST_OK")
+
+
+def test_device_hash_restatement_against_reference_kats(golden):
+    """hash.cuh is __host__ __device__ code: the functions the partition and convert kernels call are run on the host
+    against the known answers recorded from the reference's src/hash.cpp, at every alignment, and the grouping
+    fingerprint's two bodies (word-wise for aligned keys, byte-wise otherwise) against each other"""
+    kats = os.path.join(ROOT, "tests", "cpp", "_bin", "hash_kats.txt")
+    os.makedirs(os.path.dirname(kats), exist_ok=True)
+    with open(kats, "w") as fp:
+        for iv, hexkey, h in golden.manifest["hash"]:
+            fp.write(f"{iv} {hexkey or '-'} {h}\n")
+    _build_and_run("hash_host_test", "HASH_HOST_OK", kats)
