@@ -21,7 +21,7 @@ constexpr int MG_TILE = MG_THREADS * MG_IPT;
 
 // number of A elements among the first `diag` outputs; equal keys take A's first
 template <typename K, typename I>
-__device__ __forceinline__ I merge_path(const K *A, I na, const K *B, I nb, I diag)
+__host__ __device__ __forceinline__ I merge_path(const K *A, I na, const K *B, I nb, I diag)
 {
   I lo = diag > nb ? diag - nb : 0, hi = diag < na ? diag : na;
   while (lo < hi) {
@@ -30,6 +30,22 @@ __device__ __forceinline__ I merge_path(const K *A, I na, const K *B, I nb, I di
     else hi = mid;
   }
   return lo;
+}
+
+// one thread's share of a tile: MG_IPT outputs starting at diagonal d of the tile's two runs (sa, sb)
+template <typename K>
+__host__ __device__ __forceinline__ void merge_steps(const K *sa, unsigned la, const K *sb, unsigned lb, unsigned d, K (&r)[MG_IPT])
+{
+  unsigned i = merge_path<K, unsigned>(sa, la, sb, lb, d), j = d - i;
+#pragma unroll
+  for (int q = 0; q < MG_IPT; q++) {
+    const bool ha = i < la, hb = j < lb;
+    const K x = ha ? sa[i] : K(0), y = hb ? sb[j] : K(0);
+    const bool ta = ha && (!hb || x <= y);
+    r[q] = ta ? x : y;
+    i += ta;
+    j += !ta && hb;
+  }
 }
 
 template <typename K>
@@ -59,17 +75,8 @@ merge_tiles_kernel(const K *__restrict__ A, uint64_t na, const K *__restrict__ B
   const K *sa = sh, *sb = sh + la;
   unsigned d = threadIdx.x * MG_IPT;
   if (d > m) d = m;
-  unsigned i = merge_path<K, unsigned>(sa, la, sb, lb, d), j = d - i;
   K r[MG_IPT];
-#pragma unroll
-  for (int q = 0; q < MG_IPT; q++) {
-    const bool ha = i < la, hb = j < lb;
-    const K x = ha ? sa[i] : K(0), y = hb ? sb[j] : K(0);
-    const bool ta = ha && (!hb || x <= y);
-    r[q] = ta ? x : y;
-    i += ta;
-    j += !ta && hb;
-  }
+  merge_steps<K>(sa, la, sb, lb, d, r);
   __syncthreads();
 #pragma unroll
   for (int q = 0; q < MG_IPT; q++)

@@ -18,9 +18,7 @@
 // frequency-weighted) and only misses go to the table in L2.  Included by mrgpu.cu.
 #pragma once
 
-constexpr uint32_t DENSE_BITS = 26;                 // table of 2^26 u32 counts = 256 MB (touched part stays in L2)
-constexpr uint32_t DENSE_SLOTS = 1u << DENSE_BITS;
-constexpr uint32_t DENSE_MASK = DENSE_SLOTS - 1;
+#include "dense_hash.cuh"  // DENSE_BITS / DENSE_CACHE / DENSE_MULT, dense_slot, dense_key_of (host-testable)
 // Per-block cache: DENSE_CACHE 4-byte entries = 224 KB of shared memory, one 1024-thread block per SM.
 // An entry is {count : 20 | tag : 12}.  Keys are < 2^26; h = key * odd mod 2^26 is a bijection, the slot is
 // floor(h * DENSE_CACHE / 2^26), and the at most 1171 values of h that share a slot differ in their low 11
@@ -33,8 +31,6 @@ constexpr uint32_t DENSE_MASK = DENSE_SLOTS - 1;
 // 16-byte records, 2.95 ms on header-less keys); L2 atomics on one address are slow (forwarding the hottest
 // key every 32 hits cost 20 ms).  That version issued at 1.6 IPC with every pipe under 60 %: latency-bound on
 // the load -> compare -> atomic -> check chain of one key at a time, hence the batches of four below.
-constexpr uint32_t DENSE_CACHE = 57344;
-constexpr uint32_t DENSE_MULT = 0x278DC01u;         // odd; spreads consecutive integers over the 26-bit range
 // A round = the keys a block takes between two sweeps of its cache.  MRGPU_DENSE_LAZY (default): a sweep sends to the
 // table, and resets, only what it must -- entries it evicts and entries whose 20-bit count could overflow before the
 // next sweep (count >= 2^19, rounds of at most 2^19 keys); all others keep counting and reach the table once, at the
@@ -50,15 +46,6 @@ constexpr uint32_t DENSE_FLUSH_AT = 1u << 19;
 #define MRGPU_DENSE_KEEP 2
 #endif
 constexpr uint32_t DENSE_KEEP = MRGPU_DENSE_KEEP;  // count per round below which a cache entry is evicted at the flush
-constexpr uint32_t dense_inv26(uint32_t a)
-{
-  uint32_t x = a;  // Newton: each step doubles the number of correct low bits
-  for (int i = 0; i < 6; i++) x *= 2u - a * x;
-  return x & DENSE_MASK;
-}
-constexpr uint32_t DENSE_MULT_INV = dense_inv26(DENSE_MULT);
-static_assert(((DENSE_MULT * DENSE_MULT_INV) & DENSE_MASK) == 1u, "inverse of the hash multiplier");
-static_assert((DENSE_SLOTS + DENSE_CACHE - 1) / DENSE_CACHE <= 2048, "an 11-bit tag must separate the keys of a slot");
 
 struct DenseArgs {
   const uint8_t *data;
@@ -73,12 +60,6 @@ struct DenseArgs {
 #define MRGPU_DENSE_THREADS 1024
 #endif
 
-__device__ __forceinline__ void dense_slot(uint32_t key, uint32_t &slot, uint32_t &tag)
-{
-  const uint32_t h = (key * DENSE_MULT) & DENSE_MASK;
-  slot = __umulhi(h << (32 - DENSE_BITS), DENSE_CACHE);
-  tag = (h & 2047u) + 1u;
-}
 
 // A/B variant, off by default (measured: no gain).  ncu shows the L1 data pipe 87 % busy in this kernel, 45 % of its
 // wavefronts from shared atomics and two thirds of those counted as bank-conflict replays; with Zipf's hottest key in
@@ -192,10 +173,7 @@ __device__ __forceinline__ void dense_flush(unsigned *__restrict__ cache, unsign
   for (uint32_t i = threadIdx.x; i < DENSE_CACHE; i += blockDim.x) {
     const uint32_t e = cache[i], c = e >> 12;
     if (c && (!MRGPU_DENSE_LAZY || final || c < DENSE_KEEP || c >= DENSE_FLUSH_AT)) {
-      // h lies in [lo, lo + 1171) where lo = ceil(i * 2^26 / DENSE_CACHE), and its low 11 bits are tag - 1
-      const uint32_t lo = (uint32_t) ((((uint64_t) i << DENSE_BITS) + DENSE_CACHE - 1) / DENSE_CACHE);
-      const uint32_t h = lo + (((e & 0xFFFu) - 1u - lo) & 2047u);
-      atomicAdd(&table[(h * DENSE_MULT_INV) & DENSE_MASK], c);
+      atomicAdd(&table[dense_key_of(i, e & 0xFFFu)], c);
       // a slot whose key came up only once in a whole round is given back: the next key to arrive there is more
       // likely a frequent one (simulated on the IntCount stream: 25.6 % -> 22.7 % of the pairs end as REDs)
       cache[i] = c >= DENSE_KEEP ? (e & 0xFFFu) : 0u;

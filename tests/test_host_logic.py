@@ -42,3 +42,14 @@ def test_device_hash_restatement_against_reference_kats(golden):
         for iv, hexkey, h in golden.manifest["hash"]:
             fp.write(f"{iv} {hexkey or '-'} {h}\n")
     _build_and_run("hash_host_test", "HASH_HOST_OK", kats)
+
+
+def test_merge_path_and_thread_steps_against_std_merge():
+    """merge.cuh's split search and per-thread steps, driven on the host the way the two kernels drive them, against
+    std::merge: duplicates, empty runs, lengths around tile boundaries (800 cases)"""
+    _build_and_run("merge_host_test", "MERGE_HOST_OK")
+
+
+def test_count_cache_addressing_over_the_whole_key_range():
+    """every key below 2^26 -> (slot, tag) -> the same key back (dense_hash.cuh), 1170-1171 keys per slot"""
+    _build_and_run("dense_host_test", "DENSE_HOST_OK")
