@@ -53,3 +53,36 @@ def test_merge_path_and_thread_steps_against_std_merge():
 def test_count_cache_addressing_over_the_whole_key_range():
     """every key below 2^26 -> (slot, tag) -> the same key back (dense_hash.cuh), 1170-1171 keys per slot"""
     _build_and_run("dense_host_test", "DENSE_HOST_OK")
+
+
+def test_record_layout_arithmetic_against_the_oracle(oracle):
+    """kv_rec_size / kmv_rec_size (common.cuh, the functions every kernel uses to place a record) for every alignment
+    pair and a grid of sizes, against the oracle's pinned restatement of the reference's layout"""
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    if not (os.path.exists(nvcc) or shutil.which(nvcc)):
+        pytest.skip("no nvcc")
+    out = os.path.join(ROOT, "tests", "cpp", "_bin", "layout_host_test")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O1", "-std=c++17", "-w", "-o", out,
+                           os.path.join(ROOT, "tests", "cpp", "layout_host_test.cu")])
+    cases, want = [], []
+    aligns = (1, 2, 4, 8, 16, 32)
+    sizes = (0, 1, 2, 3, 4, 5, 7, 8, 9, 15, 16, 17, 31, 33, 100, 255, 1 << 20)
+    for ka in aligns:
+        for va in aligns:
+            for kb in sizes:
+                for vb in sizes[:12]:
+                    cases.append(f"kv {ka} {va} 0 {kb} {vb}")
+                    want.append(oracle.lib.orc_kv_record_size(kb, vb, ka, va))
+                for nv in (0, 1, 2, 3, 7, 1000, 1 << 26):
+                    mvb = nv * 5
+                    cases.append(f"kmv {ka} {va} {nv} {kb} {mvb}")
+                    want.append(oracle.lib.orc_kmv_record_size(nv, kb, mvb, ka, va))
+    res = subprocess.run([out], input="\n".join(cases) + "\n", capture_output=True, text=True)
+    assert res.returncode == 0
+    lines = res.stdout.split("\n")[:len(cases)]
+    assert len(lines) == len(cases)
+    for case, line, w in zip(cases, lines, want):
+        koff, voff, size = (int(x) for x in line.split())
+        assert size == w, (case, line, w)
+        assert koff <= voff <= size
