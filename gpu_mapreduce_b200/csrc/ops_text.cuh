@@ -426,23 +426,7 @@ extern "C" int mrgpu_map_tokenize(mrgpu_mr *mr, const void *text, uint64_t nbyte
 // start state and counts LINK entries / exits; a prefix sum places them; pass 3 writes their positions.
 // URL k = text[entry_k, exit_k): entries and exits alternate, so the k-th of each pair up.
 
-enum { HS_START, HS_TAG, HS_ATAG, HS_H1, HS_H2, HS_H3, HS_HREF, HS_LINK };
-
-static inline int href_start_on(int c) { return c == '<' ? HS_TAG : HS_START; }
-
-static inline int href_step(int st, int c)
-{
-  switch (st) {
-    case HS_START: return href_start_on(c);
-    case HS_TAG: return c == 'a' ? HS_ATAG : (c == ' ' ? HS_TAG : HS_START);     // cpu/InvertedIndex.cpp:211-221
-    case HS_ATAG: return c == 'h' ? HS_H1 : (c == ' ' ? HS_ATAG : HS_START);      // :222-243
-    case HS_H1: return c == 'r' ? HS_H2 : href_start_on(c);                       // failed peek: START at the 'h',
-    case HS_H2: return c == 'e' ? HS_H3 : href_start_on(c);                       // then these bytes are rescanned
-    case HS_H3: return c == 'f' ? HS_HREF : href_start_on(c);                     // from START
-    case HS_HREF: return (c == ' ' || c == '=') ? HS_HREF : (c == '"' ? HS_LINK : HS_START);  // :244-253
-    default: return c == '"' ? HS_START : HS_LINK;                                // :254-267
-  }
-}
+#include "href_dfa.cuh"  // the eight states and href_step(state, byte): host code, checked against the reference on the host
 
 // The DFA as data.  A transition function (state -> state) of the 8 states is kept in two forms:
 //   byte form  HF{lo, hi}: byte st of the 64-bit pair = f(st).  Composition "f then g" is two PRMT instructions: the

@@ -86,3 +86,31 @@ def test_record_layout_arithmetic_against_the_oracle(oracle):
         koff, voff, size = (int(x) for x in line.split())
         assert size == w, (case, line, w)
         assert koff <= voff <= size
+
+
+def test_href_automaton_against_the_reference_scanner(oracle):
+    """href_dfa.cuh -- the transition function the device's per-byte table is built from -- walked over random
+    adversarial HTML on the host: the URLs it delimits are the ones the reference's scanner emits"""
+    import numpy as np
+
+    import mrhelpers as H
+
+    out = os.path.join(ROOT, "tests", "cpp", "_bin", "href_host_test")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    subprocess.check_call(["g++", "-O1", "-x", "c++", "-o", out, os.path.join(ROOT, "tests", "cpp", "href_host_test.cu")])
+    r = np.random.RandomState(2024)
+    toks = [b"<", b"a", b" ", b"h", b"r", b"e", b"f", b"=", b'"', b"x", b"href", b"<a href=\"", b"u", b">", b"\t", b"<a  href = \"",
+            b"<ab href=\"", b"<a hrex=\"", b"<<a href=\"", b"hr", b"<a h", b"\n"]
+    path = os.path.join(ROOT, "tests", "cpp", "_bin", "href_case.txt")
+    total = 0
+    for trial in range(60):
+        text = b"".join(toks[r.randint(len(toks))] for _ in range(r.randint(1, 6000)))
+        with open(path, "wb") as fp:
+            fp.write(text)
+        res = subprocess.run([out, path], capture_output=True, text=True)
+        assert res.returncode == 0
+        got = [text[int(a):int(b)] for a, b in (ln.split() for ln in res.stdout.splitlines())]
+        want = [k for k, _ in H.kv_decode(oracle.href(text, "f.html"))]
+        assert got == want, trial
+        total += len(want)
+    assert total > 1000
