@@ -114,3 +114,9 @@ def test_href_automaton_against_the_reference_scanner(oracle):
         assert got == want, trial
         total += len(want)
     assert total > 1000
+
+
+def test_tokenizer_swar_masks_against_a_byte_loop():
+    """tok_swar.cuh (whitespace / NUL masks by SWAR compares, word starts and ends as bit operations) on 600 k random
+    16-byte vectors with every delimiter, NULs and bytes with the high bit set, against the byte-wise definitions"""
+    _build_and_run("tok_host_test", "TOK_HOST_OK")
