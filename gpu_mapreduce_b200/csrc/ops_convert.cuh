@@ -27,10 +27,7 @@ __global__ void __launch_bounds__(256) for_each_kernel(uint64_t n, F f)
   for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
 }
 
-struct CompactKey {
-  int nvb;               // number of varying key bytes (<= 8)
-  unsigned char pos[8];  // their positions inside the key
-};
+#include "compact_key.cuh"  // struct CompactKey; 16-byte key <-> sort key of its varying bytes (host-testable)
 
 // ---- uniform records: extract sort key (+ payload) and histogram in one read of the KV -----------------
 
@@ -92,14 +89,7 @@ extract_uniform_kernel(const uint8_t *__restrict__ data, uint64_t n, uint32_t rs
       }
       acc_lo |= lo ^ f_lo;
       acc_hi |= hi ^ f_hi;
-      unsigned long long k64 = 0;
-#pragma unroll
-      for (int q = 0; q < 8; q++)
-        if (q < ck.nvb) {
-          const unsigned p = ck.pos[q];
-          k64 |= (((p < 8 ? lo : hi) >> (8 * (p & 7))) & 0xFFull) << (8 * q);
-        }
-      key = (K) k64;
+      key = (K) compact_of_key16(lo, hi, ck);
     } else {
       unsigned long long k64 = 0;
       for (int q = 0; q < ck.nvb; q++) k64 |= (unsigned long long) r[koff + ck.pos[q]] << (8 * q);
@@ -442,21 +432,14 @@ static bool convert_uniform(mrgpu_mr *mr, const CompactKey &ck, bool ident, std:
           // is shifted into its place (the position is the same in every thread: no divergence, no table)
           unsigned long long h0[2] = {0, 0};
           memcpy(h0, key0.data(), 16);
-          for (int q = 0; q < ck.nvb; q++) h0[ck.pos[q] >> 3] &= ~(0xFFull << (8 * (ck.pos[q] & 7)));
+          key16_clear_varying(h0[0], h0[1], ck);
           const unsigned long long lo0 = h0[0], hi0 = h0[1];
           auto mk = [=] __device__(uint64_t u) {
             const uint32_t s0 = __ldg(st + u);
             fc[u] = __ldg(st + u + 1) - s0;
             const unsigned long long key = (unsigned long long) __ldg(sk + s0);
-            unsigned long long lo = lo0, hi = hi0;
-#pragma unroll
-            for (int q = 0; q < 8; q++)
-              if (q < ckc.nvb) {
-                const unsigned p = ckc.pos[q];
-                const unsigned long long b = ((key >> (8 * q)) & 0xFFull) << (8 * (p & 7));
-                if (p < 8) lo |= b;
-                else hi |= b;
-              }
+            unsigned long long lo, hi;
+            key16_of_compact(key, lo0, hi0, ckc, lo, hi);
             ((ulonglong2 *) fkw32)[u] = make_ulonglong2(lo, hi);
           };
           for_each_kernel<<<grid_for(U, 256, 64), 256, 0, s>>>(U, mk);

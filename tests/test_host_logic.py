@@ -120,3 +120,9 @@ def test_tokenizer_swar_masks_against_a_byte_loop():
     """tok_swar.cuh (whitespace / NUL masks by SWAR compares, word starts and ends as bit operations) on 600 k random
     16-byte vectors with every delimiter, NULs and bytes with the high bit set, against the byte-wise definitions"""
     _build_and_run("tok_host_test", "TOK_HOST_OK")
+
+
+def test_compact_sort_keys_of_16_byte_keys():
+    """compact_key.cuh: sort key <-> key round trip for random varying-byte sets, and the sort keys order the keys as
+    128-bit little-endian integers (what lets an iterative job's later rounds be merged instead of sorted)"""
+    _build_and_run("compact_host_test", "COMPACT_HOST_OK")
