@@ -18,40 +18,7 @@
 // Included by mrgpu.cu.
 #pragma once
 
-__device__ __forceinline__ uint32_t f32_order(uint32_t b)
-{
-  if ((b << 1) == 0) b = 0;  // -0 -> +0
-  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-}
-__device__ __forceinline__ uint64_t f64_order(uint64_t b)
-{
-  if ((b << 1) == 0) b = 0;
-  return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
-}
-
-// chunk c (8 bytes, big-endian) of the NUL-terminated string stored in key[0..kb)
-__device__ __forceinline__ uint64_t str_chunk(const uint8_t *key, uint32_t kb, uint32_t c)
-{
-  uint64_t v = 0;
-  uint32_t lo = c * 8;
-  // bytes after the first NUL compare as 0; find whether a NUL occurs before this chunk
-  bool ended = false;
-  for (uint32_t q = 0; q < lo && q < kb; q++)
-    if (key[q] == 0) {
-      ended = true;
-      break;
-    }
-  for (uint32_t q = 0; q < 8; q++) {
-    uint32_t p = lo + q;
-    uint8_t b = 0;
-    if (!ended && p < kb) {
-      b = key[p];
-      if (b == 0) ended = true;
-    }
-    v = (v << 8) | b;
-  }
-  return v;
-}
+#include "sort_order.cuh"  // f32_order, f64_order, str_chunk: host-callable, checked against the C comparisons on the host
 
 template <typename K>
 __global__ void __launch_bounds__(256)

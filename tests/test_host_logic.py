@@ -126,3 +126,9 @@ def test_compact_sort_keys_of_16_byte_keys():
     """compact_key.cuh: sort key <-> key round trip for random varying-byte sets, and the sort keys order the keys as
     128-bit little-endian integers (what lets an iterative job's later rounds be merged instead of sorted)"""
     _build_and_run("compact_host_test", "COMPACT_HOST_OK")
+
+
+def test_sort_order_transforms_against_the_c_comparisons():
+    """sort_order.cuh: the float / double / string transforms of sort_keys compare like <, > and strcmp (the
+    reference's compare functions), incl. signed zeros, infinities, denormals and bytes >= 0x80"""
+    _build_and_run("sortorder_host_test", "SORTORDER_HOST_OK")
